@@ -1,0 +1,209 @@
+"""The "DNNw" weight-blob format and random-init LPCNet models written in it.
+
+Blob layout (reference: src/write_lpcnet_weights.c:47-67, src/nnet.h:41-61,
+src/parse_lpcnet_weights.c:36-77): a sequence of records, each a 64-byte head
+``{char head[4]="DNNw"; int32 version; int32 type; int32 size; int32 block_size;
+char name[44]}`` followed by ``size`` payload bytes zero-padded to
+``block_size = ceil(size/64)*64``.  Arrays are looked up by name and exact byte
+size (parse_lpcnet_weights.c:79-88).
+
+The array list and per-array layouts follow training_tf2/dump_lpcnet.py
+(printSparseVector 85-121, dump_sparse_gru 131-169, dump_grub 172-218,
+dump_mdense_layer 257-282, main 440-470).  Models cannot be downloaded offline, so
+`random_model` draws random-init weights in exactly that layout.
+"""
+from __future__ import annotations
+
+import struct
+from collections import OrderedDict
+
+import numpy as np
+
+WEIGHT_TYPE_FLOAT = 0
+WEIGHT_TYPE_INT = 1
+WEIGHT_TYPE_QWEIGHT = 2
+WEIGHT_BLOCK_SIZE = 64
+
+_TYPE_OF_DTYPE = {
+    np.dtype(np.float32): WEIGHT_TYPE_FLOAT,
+    np.dtype(np.int32): WEIGHT_TYPE_INT,
+    np.dtype(np.int8): WEIGHT_TYPE_QWEIGHT,
+}
+
+
+def write_blob(arrays: "OrderedDict[str, np.ndarray]") -> bytes:
+    """Serialise named arrays (float32 / int32 / int8) as a DNNw blob."""
+    out = bytearray()
+    for name, arr in arrays.items():
+        arr = np.ascontiguousarray(arr)
+        wtype = _TYPE_OF_DTYPE[arr.dtype]
+        payload = arr.tobytes()
+        size = len(payload)
+        if size == 0:
+            # parse_weights aborts on a zero-size record (parse_lpcnet_weights.c:62-73)
+            raise ValueError(f"array {name} is empty; the reference parser rejects it")
+        block = (size + WEIGHT_BLOCK_SIZE - 1) // WEIGHT_BLOCK_SIZE * WEIGHT_BLOCK_SIZE
+        bname = name.encode()
+        if len(bname) > 43:
+            raise ValueError(f"array name too long: {name}")
+        out += struct.pack("<4siiii44s", b"DNNw", 0, wtype, size, block, bname)
+        out += payload
+        out += b"\0" * (block - size)
+    return bytes(out)
+
+
+def parse_blob(data: bytes) -> "OrderedDict[str, np.ndarray]":
+    """Inverse of `write_blob`, with parse_record's validation (36-51)."""
+    arrays: "OrderedDict[str, np.ndarray]" = OrderedDict()
+    off = 0
+    n = len(data)
+    while n - off > 0:
+        if n - off < WEIGHT_BLOCK_SIZE:
+            raise ValueError("truncated record head")
+        _head, _ver, wtype, size, block, bname = struct.unpack_from("<4siiii44s", data, off)
+        if block < size or block > n - off - WEIGHT_BLOCK_SIZE or bname[-1] != 0 or size <= 0:
+            raise ValueError("bad record")
+        name = bname.split(b"\0", 1)[0].decode()
+        dtype = {0: np.float32, 1: np.int32, 2: np.int8}.get(wtype, np.uint8)
+        arrays[name] = np.frombuffer(data, dtype=dtype, count=size // np.dtype(dtype).itemsize,
+                                     offset=off + WEIGHT_BLOCK_SIZE).copy()
+        off += WEIGHT_BLOCK_SIZE + block
+    return arrays
+
+
+def block_sparse_encode(q: np.ndarray, mask: np.ndarray):
+    """Encode q[in][out] (int8 values) into the 8x4 block-sparse stream.
+
+    `mask[in/4][out/8]` says which blocks are present.  Emission order follows
+    printSparseVector (dump_lpcnet.py:98-118): for each 8-output group, a count, then
+    per kept 4-input group its position 4*j and the 32 weights ordered
+    [output r][input c] (the DOT_PROD transpose, line 110).
+    """
+    n_in, n_out = q.shape
+    w = []
+    idx = []
+    for i in range(n_out // 8):
+        js = np.nonzero(mask[:, i])[0]
+        idx.append(len(js))
+        for j in js:
+            idx.append(4 * int(j))
+            blk = q[4 * j:4 * j + 4, 8 * i:8 * i + 8]  # [c][r]
+            w.append(blk.T.reshape(-1))               # [r][c]
+    wq = np.concatenate(w).astype(np.int8) if w else np.zeros((0,), np.int8)
+    return wq, np.asarray(idx, dtype=np.int32)
+
+
+def dotp_layout(q: np.ndarray) -> np.ndarray:
+    """Dense int8 'dotp' layout [out/8][in/4][8][4] (dump_lpcnet.py:56-60)."""
+    n_in, n_out = q.shape
+    v = q.reshape(n_in // 4, 4, n_out // 8, 8).transpose(2, 0, 3, 1)
+    return np.ascontiguousarray(v).reshape(-1).astype(np.int8)
+
+
+def _rand_mask(rng, n_in4, n_out8, density):
+    total = n_in4 * n_out8
+    k = int(round(density * total))
+    m = np.zeros(total, dtype=bool)
+    m[rng.choice(total, size=k, replace=False)] = True
+    return m.reshape(n_in4, n_out8)
+
+
+def random_model(seed: int = 1234, N: int = 384, NB: int = 16, C: int = 128,
+                 density=(0.05, 0.05, 0.2), qmax=(40, 40, 20), qmax_b_in: int = 8,
+                 qmax_b_rec: int = 40, gru_b_density: float = 1.0,
+                 sigma: float = 0.1) -> "OrderedDict[str, np.ndarray]":
+    """Random-init LPCNet model in the reference's array layout.
+
+    int8 blocks are uniform in [-qmax, qmax] so that |q[2k]|+|q[2k+1]| <= 127 and the
+    AVX2 `vpmaddubsw` s16 intermediate never saturates (training_tf2/lpcnet.py:287-309).
+    """
+    rng = np.random.default_rng(seed)
+    f32 = np.float32
+    A: "OrderedDict[str, np.ndarray]" = OrderedDict()
+
+    def normal(shape, s=sigma):
+        return (rng.standard_normal(shape) * s).astype(f32)
+
+    # --- order mirrors dump_lpcnet.py main (440-470) ---
+    for nm in ("sig", "pred", "exc"):
+        A[f"gru_a_embed_{nm}_weights"] = normal((256, 3 * N))
+    A["gru_a_dense_feature_weights"] = normal((C, 3 * N))
+    A["gru_a_dense_feature_bias"] = normal((3 * N,))
+    A["gru_b_dense_feature_weights"] = normal((C, 3 * NB))
+    A["gru_b_dense_feature_bias"] = np.zeros((3 * NB,), f32)
+
+    # GRU-B: input weights (block-sparse stream, dense by default), recurrent (dotp)
+    qb = rng.integers(-qmax_b_in, qmax_b_in + 1, size=(N, 3 * NB)).astype(np.int32)
+    mask_b = _rand_mask(rng, N // 4, 3 * NB // 8, gru_b_density)
+    qb = qb * np.repeat(np.repeat(mask_b, 4, axis=0), 8, axis=1)
+    wq, idx = block_sparse_encode(qb, mask_b)
+    A["gru_b_weights"] = wq
+    A["gru_b_weights_idx"] = idx
+    qb2 = rng.integers(-qmax_b_rec, qmax_b_rec + 1, size=(NB, 3 * NB)).astype(np.int32)
+    A["gru_b_recurrent_weights"] = dotp_layout(qb2)
+    bias_b = normal((2, 3 * NB))
+    A["gru_b_bias"] = bias_b.reshape(-1)
+    sub = bias_b.astype(np.float64).copy()
+    sub[0] -= qb.sum(axis=0) * (1.0 / 128.0)
+    sub[1] -= qb2.sum(axis=0) * (1.0 / 128.0)
+    A["gru_b_subias"] = sub.astype(f32).reshape(-1)
+
+    A["feature_conv1_weights"] = normal((3, 84, C))
+    A["feature_conv1_bias"] = normal((C,))
+    A["feature_conv2_weights"] = normal((3, C, C))
+    A["feature_conv2_bias"] = normal((C,))
+    A["embed_pitch_weights"] = normal((256, 64))
+    A["embed_sig_weights"] = normal((256, 128))
+    A["feature_dense1_weights"] = normal((C, C))
+    A["feature_dense1_bias"] = normal((C,))
+    A["feature_dense2_weights"] = normal((C, C))
+    A["feature_dense2_bias"] = normal((C,))
+    A["dual_fc_weights"] = normal((256, 2, NB), 0.5)
+    A["dual_fc_bias"] = normal((2, 256))
+    A["dual_fc_factor"] = (2.0 + 0.2 * rng.standard_normal((2, 256))).astype(f32)
+
+    # GRU-A recurrent: diag + block-sparse int8 per gate
+    A["sparse_gru_a_recurrent_weights_diag"] = normal((3 * N,), 0.3)
+    qa = np.zeros((N, 3 * N), np.int32)
+    mask_a = np.zeros((N // 4, 3 * N // 8), bool)
+    for g in range(3):
+        m = _rand_mask(rng, N // 4, N // 8, density[g])
+        mask_a[:, g * (N // 8):(g + 1) * (N // 8)] = m
+        qg = rng.integers(-qmax[g], qmax[g] + 1, size=(N, N)).astype(np.int32)
+        qa[:, g * N:(g + 1) * N] = qg * np.repeat(np.repeat(m, 4, axis=0), 8, axis=1)
+    wq, idx = block_sparse_encode(qa, mask_a)
+    A["sparse_gru_a_recurrent_weights"] = wq
+    A["sparse_gru_a_recurrent_weights_idx"] = idx
+    bias_a = normal((2, 3 * N))
+    A["sparse_gru_a_bias"] = bias_a.reshape(-1)
+    sub = bias_a.astype(np.float64).copy()
+    sub[1] -= qa.sum(axis=0) * (1.0 / 128.0)
+    A["sparse_gru_a_subias"] = sub.astype(f32).reshape(-1)
+
+    for k in list(A.keys()):
+        A[k] = np.ascontiguousarray(A[k]).reshape(-1)
+    return A
+
+
+def saturation_free(wq: np.ndarray) -> bool:
+    """True if no adjacent input pair of any block row can saturate vpmaddubsw's s16:
+    255*(|q0|+|q1|) <= 32767, i.e. |q0|+|q1| <= 128."""
+    w = wq.astype(np.int32).reshape(-1, 2)
+    return bool((np.abs(w).sum(axis=1) * 255 <= 32767).all())
+
+
+def synthetic_features(n_frames: int, stream: int = 0, total: int = 36) -> np.ndarray:
+    """Synthetic feature file content for one stream: [n_frames][36]."""
+    rng = np.random.default_rng(1000 + stream)
+    f = np.zeros((n_frames, total), np.float32)
+    f[:, 0] = 2.0 + 0.5 * rng.standard_normal(n_frames)
+    f[:, 1:18] = 0.5 * rng.standard_normal((n_frames, 17))
+    f[:, 18] = rng.uniform(-1.0, 2.0, n_frames)
+    f[:, 19] = rng.uniform(-0.5, 0.5, n_frames)
+    return f
+
+
+def stream_seed(stream: int) -> bytes:
+    """Per-stream kiss99 seed string; stream 0 is the reference default "LPCNet"
+    (lpcnet.c:176-181)."""
+    return b"LPCNet" if stream == 0 else b"LPCNet" + str(stream).encode()

@@ -1,0 +1,52 @@
+/* Internal structures of the CPU oracle.  TEST INFRASTRUCTURE ONLY. */
+#ifndef ORC_INTERNAL_H
+#define ORC_INTERNAL_H
+#include "lpcnet_oracle.h"
+
+typedef struct { const float *bias, *w; int nin, nout, act; } OrcDense;      /* nnet.h:64-70 */
+typedef struct { const float *bias, *w; int nin, k, nout, act; } OrcConv;    /* nnet.h:105-112 */
+typedef struct { const float *w; int n, dim; } OrcEmbed;                      /* nnet.h:114-118 */
+typedef struct {                                                              /* nnet.h:82-92 */
+  const float *bias, *subias; const signed char *w_in; const int *idx_in; const signed char *w_rec;
+  int nin, n, nblocks;
+} OrcGRU;
+typedef struct {                                                              /* nnet.h:94-103 */
+  const float *bias, *subias, *diag; const signed char *w; const int *idx; int n, nblocks;
+} OrcSparseGRU;
+typedef struct { const float *bias, *w, *factor; int nin, n, c; } OrcMDense; /* nnet.h:72-80 */
+
+enum { ORC_LINEAR = 0, ORC_SIGMOID = 1, ORC_TANH = 2 };
+
+struct OrcModel {
+  unsigned char *blob; int len;
+  int features_delay; float lpc_gamma;
+  OrcEmbed e_sig, e_pred, e_exc, e_pitch;
+  OrcDense a_feat, b_feat, dense1, dense2;
+  OrcConv conv1, conv2;
+  OrcGRU gru_b;
+  OrcSparseGRU gru_a;
+  OrcMDense dual_fc;
+  float logit_table[256];
+};
+
+struct OrcState {
+  const OrcModel *m;
+  uint32_t rng[4];
+  /* everything below is zeroed by reset (lpcnet_private.h:33, lpcnet.c:174-182) */
+  float conv1_state[168], conv2_state[256], gru_a_state[384], gru_b_state[16];
+  int last_exc;
+  float last_sig[ORC_LPC_ORDER];
+  float old_lpc[ORC_MAX_DELAY][ORC_LPC_ORDER];
+  float gru_a_condition[1152], gru_b_condition[48];
+  int frame_count;
+  float deemph_mem;
+  float lpc[ORC_LPC_ORDER];
+};
+
+void orc_vec_act(float *y, const float *x, int n, int act);
+void orc_dense(const OrcDense *l, float *out, const float *in);
+void orc_conv1d(const OrcConv *l, float *out, float *mem, const float *in);
+void orc_sample_tail(const OrcModel *m, OrcState *s, int16_t *out, int N, int preload);
+int orc_sample_network(const OrcModel *m, OrcState *s, int last_exc, int u_sig, int u_pred);
+void orc_all_node_logits(const OrcModel *m, const OrcState *s, float *logits);
+#endif

@@ -1,0 +1,186 @@
+"""ctypes binding to oracle/liblpcnet_oracle.so (our CPU restatement of the hot path).
+
+TEST INFRASTRUCTURE ONLY: importable from tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs, never from lpcnet_b200/.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from .refpy import SNAP_DTYPE, TRACE_DTYPE, _p
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "liblpcnet_oracle.so")
+
+
+def available() -> bool:
+    return os.path.exists(LIB_PATH)
+
+
+class OrcLib:
+    def __init__(self):
+        self.lib = L = C.CDLL(LIB_PATH)
+        L.orc_model_load.restype = C.c_void_p
+        L.orc_model_load.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_float, C.c_void_p]
+        L.orc_model_free.argtypes = [C.c_void_p]
+        L.orc_model_nblocks_a.argtypes = [C.c_void_p]
+        L.orc_model_nblocks_b.argtypes = [C.c_void_p]
+        L.orc_state_new.restype = C.c_void_p
+        L.orc_state_new.argtypes = [C.c_void_p]
+        L.orc_state_free.argtypes = [C.c_void_p]
+        L.orc_state_reset.argtypes = [C.c_void_p]
+        L.orc_seed.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+        L.orc_get.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_set.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_synthesize.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+        L.orc_run.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p,
+                              C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_frame_network.argtypes = [C.c_void_p] * 6
+        for n in ("orc_rcp", "orc_tanh_approx", "orc_sigmoid_approx", "orc_ulaw2lin"):
+            getattr(L, n).restype = C.c_float
+            getattr(L, n).argtypes = [C.c_float]
+        L.orc_lin2ulaw.argtypes = [C.c_float]
+        L.orc_kiss99_rand.restype = C.c_uint32
+        L.orc_set_rcp_table.argtypes = [C.c_void_p]
+
+    def default_rcp_table(self):
+        t = np.zeros(2048, np.uint32)
+        self.lib.orc_default_rcp_table(_p(t))
+        return t
+
+    def set_rcp_table(self, tab):
+        self.lib.orc_set_rcp_table(_p(np.ascontiguousarray(tab, np.uint32)) if tab is not None else None)
+
+    def map1(self, name, x):
+        f = getattr(self.lib, name)
+        return np.array([f(C.c_float(float(v))) for v in np.asarray(x, np.float32)])
+
+    def ps_to_epi8(self, x):
+        x = np.ascontiguousarray(x, np.float32)
+        y = np.zeros(x.size, np.uint8)
+        self.lib.orc_ps_to_epi8(_p(y), _p(x), C.c_int(x.size))
+        return y
+
+    def sparse_sgemv(self, out, w, idx, x):
+        out = np.ascontiguousarray(out, np.float32).copy()
+        self.lib.orc_sparse_sgemv_accum8x4(_p(out), _p(np.ascontiguousarray(w, np.int8)), C.c_int(out.size),
+                                           C.c_int(x.size), _p(np.ascontiguousarray(idx, np.int32)),
+                                           _p(np.ascontiguousarray(x, np.float32)))
+        return out
+
+    def sgemv8x4(self, out, w, x):
+        out = np.ascontiguousarray(out, np.float32).copy()
+        self.lib.orc_sgemv_accum8x4(_p(out), _p(np.ascontiguousarray(w, np.int8)), C.c_int(out.size),
+                                    C.c_int(x.size), _p(np.ascontiguousarray(x, np.float32)))
+        return out
+
+    def sgemv(self, out, w, cols, x):
+        out = np.ascontiguousarray(out, np.float32).copy()
+        self.lib.orc_sgemv_accum(_p(out), _p(np.ascontiguousarray(w, np.float32)), C.c_int(out.size),
+                                 C.c_int(cols), C.c_int(out.size), _p(np.ascontiguousarray(x, np.float32)))
+        return out
+
+    def kiss99_srand(self, seed: bytes):
+        st = np.zeros(4, np.uint32)
+        self.lib.orc_kiss99_srand(_p(st), seed, C.c_int(len(seed)))
+        return st
+
+    def kiss99_rand(self, st):
+        return int(self.lib.orc_kiss99_rand(_p(st)))
+
+    def lpc_from_cepstrum(self, ceps):
+        ceps = np.ascontiguousarray(ceps, np.float32)
+        lpc = np.zeros(16, np.float32)
+        self.lib.orc_lpc_from_cepstrum(_p(lpc), _p(ceps))
+        return lpc
+
+    def fft_tables(self):
+        tw = np.zeros((320, 2), np.float32)
+        br = np.zeros(320, np.int16)
+        dct = np.zeros(18 * 18, np.float32)
+        self.lib.orc_fft_tables(_p(tw), _p(br), _p(dct))
+        return tw, br, dct
+
+    def decode_packet(self, vq_mem, buf: bytes, codebooks):
+        feats = np.zeros((4, 36), np.float32)
+        self.lib.orc_decode_packet(_p(feats), _p(vq_mem), buf, _p(np.ascontiguousarray(codebooks, np.float32)))
+        return feats
+
+
+class OrcModel:
+    def __init__(self, lib: OrcLib, blob: bytes, features_delay: int = 2, lpc_gamma: float = 1.0, rcp_table=None):
+        self.L = lib
+        tab = np.ascontiguousarray(rcp_table, np.uint32) if rcp_table is not None else None
+        self.h = lib.lib.orc_model_load(blob, len(blob), features_delay, C.c_float(lpc_gamma),
+                                        _p(tab) if tab is not None else None)
+        if not self.h:
+            raise RuntimeError("oracle rejected the blob")
+        self.features_delay = features_delay
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.lib.orc_model_free(self.h)
+            self.h = None
+
+    @property
+    def nblocks_a(self):
+        return self.L.lib.orc_model_nblocks_a(self.h)
+
+    @property
+    def nblocks_b(self):
+        return self.L.lib.orc_model_nblocks_b(self.h)
+
+
+class OrcStream:
+    def __init__(self, model: OrcModel, seed: bytes | None = None):
+        self.m = model
+        self.L = model.L
+        self.h = self.L.lib.orc_state_new(model.h)
+        if seed is not None:
+            self.L.lib.orc_seed(self.h, seed, len(seed))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.lib.orc_state_free(self.h)
+            self.h = None
+
+    def run(self, feats, forced=None, trace=False, logits=False):
+        feats = np.ascontiguousarray(feats, np.float32)
+        n_frames, stride = feats.shape
+        pcm = np.zeros(n_frames * 160, np.int16)
+        tr = np.zeros(n_frames * 160, TRACE_DTYPE) if trace else None
+        lg = np.zeros((n_frames * 160, 256), np.float32) if logits else None
+        if forced is not None:
+            forced = np.ascontiguousarray(forced, np.int16)
+        self.L.lib.orc_run(self.m.h, self.h, _p(feats), stride, n_frames, _p(pcm),
+                           _p(forced) if forced is not None else None,
+                           _p(tr) if trace else None, _p(lg) if logits else None)
+        return pcm, tr, lg
+
+    def synthesize(self, features, n=160, preload=0, out=None):
+        f = np.ascontiguousarray(features, np.float32)
+        if out is None:
+            out = np.zeros(n, np.int16)
+        self.L.lib.orc_synthesize(self.m.h, self.h, _p(f), _p(out), n, preload)
+        return out
+
+    def frame_network(self, features):
+        f = np.ascontiguousarray(features, np.float32)
+        ga = np.zeros(1152, np.float32)
+        gb = np.zeros(48, np.float32)
+        lpc = np.zeros(16, np.float32)
+        self.L.lib.orc_frame_network(self.m.h, self.h, _p(f), _p(ga), _p(gb), _p(lpc))
+        return ga, gb, lpc
+
+    def snapshot(self):
+        s = np.zeros(1, SNAP_DTYPE)
+        self.L.lib.orc_get(self.h, _p(s))
+        return s[0]
+
+    def restore(self, snap):
+        s = np.zeros(1, SNAP_DTYPE)
+        s[0] = snap
+        self.L.lib.orc_set(self.h, _p(s))
