@@ -1,0 +1,186 @@
+/* lpcnet_b200.h -- C ABI of the B200-native LPCNet synthesis engine (liblpcnet_b200.so).
+ *
+ * Two groups of entry points, all `extern "C"`, plain pointers and sizes:
+ *
+ *  1. Drop-in symbols: same names, argument meaning and return conventions as the
+ *     reference's include/lpcnet.h for the synthesis path, so a program compiled against
+ *     the reference header links against this library unchanged.  Each declaration cites
+ *     the reference line it replaces.  The opaque state is a small host handle; the real
+ *     per-stream state lives in HBM.
+ *
+ *  2. The batched multi-stream API (lpcnet_batch_*): the entry point BASELINE.json's
+ *     north_star adds next to the reference API.  One batch = n_streams independent
+ *     LPCNetStates advanced in lock step by one persistent CUDA kernel.
+ *
+ * There is no CPU fallback: every call that needs the GPU fails (non-zero return /
+ * latched error) when no CUDA device is present.
+ */
+#ifndef LPCNET_B200_H
+#define LPCNET_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef LPCNET_B200_EXPORT
+#define LPCNET_B200_EXPORT __attribute__((visibility("default")))
+#endif
+
+/* Same values as include/lpcnet.h:45-53 of the reference. */
+#define LPCNET_B200_NB_FEATURES 20
+#define LPCNET_B200_NB_TOTAL_FEATURES 36
+#define LPCNET_B200_FRAME_SIZE 160
+#define LPCNET_B200_PACKET_BYTES 8
+#define LPCNET_B200_PACKET_SAMPLES 640
+
+/* ------------------------------------------------------------------------------------
+ * 1. Drop-in symbols (reference: include/lpcnet.h; implementation src/lpcnet.c)
+ * ------------------------------------------------------------------------------------ */
+typedef struct LPCNetState LPCNetState;       /* include/lpcnet.h:55 */
+typedef struct LPCNetDecState LPCNetDecState; /* include/lpcnet.h:57 */
+
+/* include/lpcnet.h:160, src/lpcnet.c:169-172.  Size of the host handle. */
+LPCNET_B200_EXPORT int lpcnet_get_size(void);
+/* include/lpcnet.h:169, src/lpcnet.c:184-200.  Returns 0.  Like the reference's
+ * USE_WEIGHTS_FILE build, the state has no model until lpcnet_load_model is called. */
+LPCNET_B200_EXPORT int lpcnet_init(LPCNetState *st);
+/* include/lpcnet.h:174, src/lpcnet.c:213-219. */
+LPCNET_B200_EXPORT LPCNetState *lpcnet_create(void);
+/* include/lpcnet.h:179, src/lpcnet.c:221-224. */
+LPCNET_B200_EXPORT void lpcnet_destroy(LPCNetState *st);
+/* include/lpcnet.h:78, src/lpcnet.c:174-182: zero the stream state, last_exc=128,
+ * reseed kiss99 with "LPCNet". */
+LPCNET_B200_EXPORT void lpcnet_reset(LPCNetState *st);
+/* include/lpcnet.h:214, src/lpcnet.c:202-210.  0 on success, -1 on a malformed blob
+ * (same validation as src/parse_lpcnet_weights.c:36-113) or when no GPU is available.
+ * The blob is copied to the device; it need not outlive the call (a superset of the
+ * reference, which borrows it). */
+LPCNET_B200_EXPORT int lpcnet_load_model(LPCNetState *st, const unsigned char *data, int len);
+/* include/lpcnet.h:188, src/lpcnet.c:279-281: one frame-network evaluation on
+ * features[0..20), then N (<=160) samples into output.  void like the reference: a CUDA
+ * failure is latched and reported by lpcnet_b200_last_error(). */
+LPCNET_B200_EXPORT void lpcnet_synthesize(LPCNetState *st, const float *features, short *output, int N);
+
+/* include/lpcnet.h:67-96, src/lpcnet.c:285-319. */
+LPCNET_B200_EXPORT int lpcnet_decoder_get_size(void);
+LPCNET_B200_EXPORT int lpcnet_decoder_init(LPCNetDecState *st);
+LPCNET_B200_EXPORT LPCNetDecState *lpcnet_decoder_create(void);
+LPCNET_B200_EXPORT void lpcnet_decoder_destroy(LPCNetDecState *st);
+/* buf: 8 bytes; pcm: 640 samples.  Returns 0.  The VQ codebooks are compiled into the
+ * reference (ceps_codebooks.c, absent from the tree); here they are looked up in the
+ * blob under their C names (ceps_codebook1/2/3, ceps_codebook_diff4) or installed with
+ * lpcnet_b200_set_codebooks().  Extension, not in the reference header: */
+LPCNET_B200_EXPORT int lpcnet_decoder_load_model(LPCNetDecState *st, const unsigned char *data, int len);
+LPCNET_B200_EXPORT int lpcnet_decode(LPCNetDecState *st, const unsigned char *buf, short *pcm);
+
+/* ------------------------------------------------------------------------------------
+ * 2. Batched multi-stream API (new; SURVEY.md 8b last row)
+ * ------------------------------------------------------------------------------------ */
+typedef struct LPCNetBatch LPCNetBatch;
+
+/* Host-visible per-stream state: the mutable part of the reference's LPCNetState
+ * (src/lpcnet_private.h:28-48) for the default model sizes, used for snapshot/restore
+ * and for cross-loading states to and from the reference. */
+typedef struct {
+  float conv1_state[168];
+  float conv2_state[256];
+  float gru_a_state[384];
+  float gru_b_state[16];
+  float last_sig[16];
+  float lpc[16];
+  float old_lpc[2][16];
+  float gru_a_condition[1152];
+  float gru_b_condition[48];
+  float deemph_mem;
+  int32_t last_exc;
+  int32_t frame_count;
+  uint32_t rng[4]; /* kiss99: z, w, jsr, jcong */
+} LPCNetB200StreamState;
+
+/* Per-step debug record (teacher-forced parity runs). */
+typedef struct {
+  int32_t exc;      /* last_exc after the step */
+  int32_t u_sig;    /* lin2ulaw(last_sig[0]) fed to the step (src/lpcnet.c:253) */
+  int32_t u_pred;   /* lin2ulaw(pred) fed to the step (src/lpcnet.c:254) */
+  uint32_t rng_z;   /* kiss99 state after the step */
+  uint32_t rng_w;
+  uint32_t xa_hash; /* FNV-1a over the u8-quantised GRU-A state after the step */
+  uint32_t xb_hash; /* same for GRU-B */
+  int32_t pcm;      /* output sample (or the forced one) */
+} LPCNetB200Trace;
+
+/* features_delay and lpc_gamma are FEATURES_DELAY / LPC_GAMMA of the generated
+ * nnet_data.h (training_tf2/dump_lpcnet.py:437-439); they are not stored in the blob.
+ * device < 0 selects the current CUDA device.  Returns NULL on error (see
+ * lpcnet_b200_last_error). */
+LPCNET_B200_EXPORT LPCNetBatch *lpcnet_batch_create(const unsigned char *blob, int len, int n_streams,
+                                                   int device, int features_delay, float lpc_gamma);
+LPCNET_B200_EXPORT void lpcnet_batch_destroy(LPCNetBatch *b);
+LPCNET_B200_EXPORT int lpcnet_batch_n_streams(const LPCNetBatch *b);
+/* lpcnet_reset for every stream (stream < 0) or one stream. */
+LPCNET_B200_EXPORT int lpcnet_batch_reset(LPCNetBatch *b, int stream);
+/* kiss99_srand(&st->rng, data, n) (src/kiss99.c:32-57) for one stream. */
+LPCNET_B200_EXPORT int lpcnet_batch_set_seed(LPCNetBatch *b, int stream, const unsigned char *data, int n);
+/* Run on this cudaStream_t (as void*) instead of the batch's own stream. */
+LPCNET_B200_EXPORT int lpcnet_batch_set_cuda_stream(LPCNetBatch *b, void *cuda_stream);
+/* Streams per CTA tile: 0 = automatic (by n_streams), else one of 8, 16, 32, 64. */
+LPCNET_B200_EXPORT int lpcnet_batch_set_tile(LPCNetBatch *b, int streams_per_cta);
+
+/* HOST buffers.  features: [n_streams][n_frames][feature_stride] floats (only [0,20) of
+ * each frame is read, src/lpcnet_demo.c:213-215); pcm: [n_streams][n_frames*160].
+ * forced_pcm (nullable): teacher forcing through the reference's preload rule
+ * (src/lpcnet.c:256-258) on every step.  trace / node_logits (nullable, debug):
+ * [n_streams][n_frames*160] records / [n_streams][n_frames*160][256] floats
+ * (entry 0 unused).  Copies host<->device inside the call; synchronous. */
+LPCNET_B200_EXPORT int lpcnet_batch_synthesize(LPCNetBatch *b, const float *features, int feature_stride,
+                                               int n_frames, short *pcm, const short *forced_pcm,
+                                               LPCNetB200Trace *trace, float *node_logits);
+/* Same with DEVICE buffers, asynchronous on the batch's CUDA stream; samples_per_frame
+ * (<=160) is the N of lpcnet_synthesize.  pcm: [n_streams][n_frames*samples_per_frame]. */
+LPCNET_B200_EXPORT int lpcnet_batch_synthesize_device(LPCNetBatch *b, const float *d_features,
+                                                      int feature_stride, int n_frames,
+                                                      int samples_per_frame, short *d_pcm,
+                                                      const short *d_forced_pcm, LPCNetB200Trace *d_trace,
+                                                      float *d_node_logits);
+/* Frame network only (debug/parity): evaluates n_frames frames, advancing the conv
+ * states, old_lpc and frame_count, and returns the conditioning per frame (host buffers,
+ * [n_streams][n_frames][1152|48|16]; any may be NULL). */
+LPCNET_B200_EXPORT int lpcnet_batch_frame_network(LPCNetBatch *b, const float *features, int feature_stride,
+                                                  int n_frames, float *gru_a_condition,
+                                                  float *gru_b_condition, float *lpc);
+/* packets: [n_streams][n_packets][8]; pcm: [n_streams][n_packets*640] (host buffers).
+ * lpcnet_decode for every stream (src/lpcnet.c:310-319).  features_out (nullable):
+ * [n_streams][n_packets*4][36] decoded features. */
+LPCNET_B200_EXPORT int lpcnet_batch_decode(LPCNetBatch *b, const unsigned char *packets, int n_packets,
+                                           short *pcm, float *features_out);
+/* codebooks: ceps_codebook1|2|3 [1024*17 each] then ceps_codebook_diff4 [4096*18]. */
+LPCNET_B200_EXPORT int lpcnet_batch_set_codebooks(LPCNetBatch *b, const float *codebooks, int n_floats);
+LPCNET_B200_EXPORT int lpcnet_batch_get_state(LPCNetBatch *b, int stream, LPCNetB200StreamState *out);
+LPCNET_B200_EXPORT int lpcnet_batch_set_state(LPCNetBatch *b, int stream, const LPCNetB200StreamState *in);
+LPCNET_B200_EXPORT int lpcnet_batch_sync(LPCNetBatch *b);
+/* Number of block-sparse 8x4 blocks in GRU-A / GRU-B input (for the op counts). */
+LPCNET_B200_EXPORT int lpcnet_batch_nblocks(const LPCNetBatch *b, int which);
+/* Kernels launched by this batch so far (for bench.py's gpu_launches). */
+LPCNET_B200_EXPORT long long lpcnet_batch_launch_count(const LPCNetBatch *b);
+
+/* The reference's tanh/sigmoid multiply by `rcpps` (src/vec_avx.h:408,437), a CPU
+ * hardware estimate that is exactly a 2048-entry table over the top 11 mantissa bits.
+ * Default: the Intel table model (oracle/orc_prim.c).  A process-wide override takes the
+ * 2048 binary32 bit patterns of rcpps(1 + i/2048); applies to batches created later. */
+LPCNET_B200_EXPORT void lpcnet_b200_set_rcp_table(const uint32_t *table2048);
+LPCNET_B200_EXPORT void lpcnet_b200_default_rcp_table(uint32_t *table2048);
+
+/* FEATURES_DELAY / LPC_GAMMA used by the drop-in lpcnet_load_model (compile-time constants of
+ * the reference's generated nnet_data.h; default 2 and 1.0). */
+LPCNET_B200_EXPORT void lpcnet_b200_set_model_constants(int features_delay, float lpc_gamma);
+
+/* Last error message of the calling thread ("" if none); sticky until read. */
+LPCNET_B200_EXPORT const char *lpcnet_b200_last_error(void);
+LPCNET_B200_EXPORT int lpcnet_b200_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

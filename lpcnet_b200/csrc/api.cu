@@ -1,0 +1,584 @@
+// C-ABI host shim: the reference's lpcnet.h entry points for the synthesis path and the batched
+// multi-stream API, over the CUDA kernels in frame.cu / sample.cu.  No CPU fallback anywhere.
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
+#include <new>
+#include <string>
+
+#include "../../include/lpcnet_b200.h"
+#include "engine.h"
+
+using namespace lpcb;
+
+namespace {
+
+thread_local std::string g_err;
+thread_local std::string g_err_ret;
+std::mutex g_cfg_mu;
+bool g_have_rcp = false;
+uint32_t g_rcp[2048];
+int g_default_delay = 2;
+float g_default_gamma = 1.0f;
+
+int fail(const std::string &msg) {
+  g_err = msg;
+  return -1;
+}
+int fail_cuda(const char *what, cudaError_t e) { return fail(std::string(what) + ": " + cudaGetErrorString(e)); }
+
+#define CK(call)                                        \
+  do {                                                  \
+    cudaError_t e_ = (call);                            \
+    if (e_ != cudaSuccess) return fail_cuda(#call, e_); \
+  } while (0)
+
+void lpcnet_kiss99_srand_host(uint32_t st[4], const unsigned char *d, int n) {
+  // kiss99_srand (src/kiss99.c:32-57)
+  auto next = [&]() {
+    st[0] = 36969u * (st[0] & 0xFFFF) + (st[0] >> 16);
+    st[1] = 18000u * (st[1] & 0xFFFF) + (st[1] >> 16);
+    st[2] ^= st[2] << 13; st[2] ^= st[2] >> 17; st[2] ^= st[2] << 5;
+    st[3] = 69069u * st[3] + 1234567u;
+  };
+  st[0] = 362436069u; st[1] = 521288629u; st[2] = 123456789u; st[3] = 380116160u;
+  int i;
+  for (i = 3; i < n; i += 4) {
+    st[0] ^= d[i - 3]; st[1] ^= d[i - 2]; st[2] ^= d[i - 1]; st[3] ^= d[i];
+    next();
+  }
+  if (i - 3 < n) st[0] ^= d[i - 3];
+  if (i - 2 < n) st[1] ^= d[i - 2];
+  if (i - 1 < n) st[2] ^= d[i - 1];
+  if (st[0] == 0 || st[0] == 0x9068FFFFu) st[0]++;
+  if (st[1] == 0 || st[1] == 0x464FFFFFu) st[1]++;
+  if (st[2] == 0) st[2]++;
+}
+
+}  // namespace
+
+struct LPCNetBatch {
+  int device = 0;
+  int n_streams = 0;
+  int n_sms = 0;
+  int tile = 0;  // 0 = auto
+  Model model;
+  DevState st{};
+  void *st_alloc = nullptr;
+  FrameBuffers fb;
+  void *fb_alloc = nullptr;
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t stream = nullptr;
+  long long launches = 0;
+  // grow-only staging for the host-buffer entry points
+  void *d_feat = nullptr; size_t d_feat_bytes = 0;
+  void *d_pcm = nullptr; size_t d_pcm_bytes = 0;
+  void *d_forced = nullptr; size_t d_forced_bytes = 0;
+  void *d_trace = nullptr; size_t d_trace_bytes = 0;
+  void *d_logits = nullptr; size_t d_logits_bytes = 0;
+  void *d_packets = nullptr; size_t d_packets_bytes = 0;
+};
+
+namespace {
+
+int grow(void **p, size_t *have, size_t want) {
+  if (*have >= want) return 0;
+  if (*p) cudaFree(*p);
+  *p = nullptr; *have = 0;
+  CK(cudaMalloc(p, want));
+  *have = want;
+  return 0;
+}
+
+int alloc_state(LPCNetBatch *b) {
+  const size_t B = b->n_streams;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t r = off; off += (bytes + 255) & ~size_t(255); return r; };
+  const size_t o_c1 = take(B * 168 * 4), o_c2 = take(B * 256 * 4), o_a = take(B * kN * 4), o_b = take(B * kNB * 4);
+  const size_t o_ls = take(B * 16 * 4), o_ol = take(B * kMaxDelay * 16 * 4), o_lpc = take(B * 16 * 4);
+  const size_t o_ca = take(B * kRowsA * 4), o_cb = take(B * kRowsB * 4), o_de = take(B * 4), o_le = take(B * 4);
+  const size_t o_fc = take(B * 4), o_rng = take(B * 16), o_vq = take(B * 18 * 4);
+  CK(cudaMalloc(&b->st_alloc, off));
+  CK(cudaMemset(b->st_alloc, 0, off));
+  char *p = static_cast<char *>(b->st_alloc);
+  b->st.conv1_state = (float *)(p + o_c1); b->st.conv2_state = (float *)(p + o_c2);
+  b->st.gru_a = (float *)(p + o_a); b->st.gru_b = (float *)(p + o_b); b->st.last_sig = (float *)(p + o_ls);
+  b->st.old_lpc = (float *)(p + o_ol); b->st.lpc = (float *)(p + o_lpc); b->st.cond_a = (float *)(p + o_ca);
+  b->st.cond_b = (float *)(p + o_cb); b->st.deemph = (float *)(p + o_de); b->st.last_exc = (int *)(p + o_le);
+  b->st.frame_count = (int *)(p + o_fc); b->st.rng = (uint32_t *)(p + o_rng); b->st.vq_mem = (float *)(p + o_vq);
+  return 0;
+}
+
+int chunk_frames(const LPCNetBatch *b, int n_frames) {
+  // conditioning is 4864 B per stream-frame; keep a chunk under ~256 MB and at most 32 frames
+  long long cap = (256ll << 20) / ((long long)b->n_streams * 4864);
+  if (cap < 1) cap = 1;
+  if (cap > 32) cap = 32;
+  return n_frames < cap ? n_frames : (int)cap;
+}
+
+int ensure_frame_buffers(LPCNetBatch *b, int F) {
+  if (b->fb.cap_frames >= F) return 0;
+  if (b->fb_alloc) cudaFree(b->fb_alloc);
+  b->fb_alloc = nullptr; b->fb.cap_frames = 0;
+  const size_t B = b->n_streams;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t r = off; off += (bytes + 255) & ~size_t(255); return r; };
+  const size_t o_iv = take(B * (F + 2) * kConvIn * 4), o_c1 = take(B * (F + 2) * kC * 4);
+  const size_t o_ca = take((size_t)F * B * kRowsA * 4), o_cb = take((size_t)F * B * kRowsB * 4);
+  const size_t o_lpc = take((size_t)F * B * 16 * 4), o_act = take((size_t)F * B);
+  const size_t fft_threads = ((B * F + 63) / 64) * 64;
+  const size_t o_fft = take(fft_threads * 640 * 4);
+  CK(cudaMalloc(&b->fb_alloc, off));
+  char *p = static_cast<char *>(b->fb_alloc);
+  b->fb.in_vec = (float *)(p + o_iv); b->fb.c1 = (float *)(p + o_c1); b->fb.cond_a = (float *)(p + o_ca);
+  b->fb.cond_b = (float *)(p + o_cb); b->fb.lpc = (float *)(p + o_lpc); b->fb.active = (uint8_t *)(p + o_act);
+  b->fb.fft_scratch = (float *)(p + o_fft);
+  b->fb.cap_frames = F;
+  return 0;
+}
+
+int auto_tile(const LPCNetBatch *b) {
+  if (b->tile) return b->tile;
+  const int B = b->n_streams, sms = b->n_sms;
+  if (B <= 8 * sms) return 8;
+  if (B <= 16 * sms) return 16;
+  if (B <= 32 * sms) return 32;
+  return 64;
+}
+
+// frame network for frames [f0, f0+F) of the call, results left in b->fb
+int run_frames(LPCNetBatch *b, const float *d_features, int stride, int f0, int F, int total_frames) {
+  FrameArgs fa{};
+  fa.m = b->model.d; fa.st = b->st; fa.fb = b->fb; fa.n_streams = b->n_streams; fa.n_frames = F;
+  fa.features = d_features; fa.feature_stride = stride; fa.frame0 = f0; fa.total_frames = total_frames;
+  int nl = 0;
+  CK(launch_frame_network(fa, b->stream, &nl));
+  b->launches += nl;
+  // keep the last frame's conditioning in the stream state (lpcnet_private.h:43-47)
+  const size_t B = b->n_streams;
+  CK(cudaMemcpyAsync(b->st.cond_a, b->fb.cond_a + (size_t)(F - 1) * B * kRowsA, B * kRowsA * 4, cudaMemcpyDeviceToDevice, b->stream));
+  CK(cudaMemcpyAsync(b->st.cond_b, b->fb.cond_b + (size_t)(F - 1) * B * kRowsB, B * kRowsB * 4, cudaMemcpyDeviceToDevice, b->stream));
+  return 0;
+}
+
+int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_frames, int spf, short *d_pcm,
+                 const short *d_forced, LPCNetB200Trace *d_trace, float *d_logits) {
+  if (!b) return fail("null batch");
+  if (n_frames <= 0) return 0;
+  if (spf <= 0 || spf > kFrame) return fail("samples_per_frame must be 1..160");
+  if (stride < kFeat) return fail("feature_stride must be >= 20");
+  CK(cudaSetDevice(b->device));
+  const int Fc = chunk_frames(b, n_frames);
+  if (ensure_frame_buffers(b, Fc)) return -1;
+  const int tile = auto_tile(b);
+  for (int f0 = 0; f0 < n_frames; f0 += Fc) {
+    const int F = (n_frames - f0) < Fc ? (n_frames - f0) : Fc;
+    if (run_frames(b, d_features, stride, f0, F, n_frames)) return -1;
+    SampleArgs sa{};
+    sa.m = b->model.d; sa.st = b->st; sa.n_streams = b->n_streams; sa.n_frames = F; sa.spf = spf;
+    sa.frame0 = f0; sa.total_frames = n_frames;
+    sa.cond_a = b->fb.cond_a; sa.cond_b = b->fb.cond_b; sa.lpc = b->fb.lpc; sa.active = b->fb.active;
+    sa.pcm = d_pcm; sa.forced = d_forced; sa.trace = d_trace; sa.logits = d_logits;
+    int nl = 0;
+    CK(launch_sample_kernel(sa, tile, b->n_sms, b->stream, &nl));
+    b->launches += nl;
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *lpcnet_b200_last_error(void) {
+  g_err_ret = g_err;
+  g_err.clear();
+  return g_err_ret.c_str();
+}
+
+int lpcnet_b200_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+void lpcnet_b200_set_rcp_table(const uint32_t *t) {
+  std::lock_guard<std::mutex> lk(g_cfg_mu);
+  if (t) { memcpy(g_rcp, t, sizeof(g_rcp)); g_have_rcp = true; }
+  else g_have_rcp = false;
+}
+void lpcnet_b200_default_rcp_table(uint32_t *t) { default_rcp_table(t); }
+
+void lpcnet_b200_set_model_constants(int features_delay, float lpc_gamma) {
+  std::lock_guard<std::mutex> lk(g_cfg_mu);
+  g_default_delay = features_delay;
+  g_default_gamma = lpc_gamma;
+}
+
+LPCNetBatch *lpcnet_batch_create(const unsigned char *blob, int len, int n_streams, int device, int features_delay,
+                                 float lpc_gamma) {
+  if (n_streams <= 0) { fail("n_streams must be positive"); return nullptr; }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    fail("no CUDA device available (liblpcnet_b200 has no CPU fallback)");
+    return nullptr;
+  }
+  if (device < 0) { if (cudaGetDevice(&device) != cudaSuccess) device = 0; }
+  if (device >= ndev) { fail("device index out of range"); return nullptr; }
+  if (cudaSetDevice(device) != cudaSuccess) { fail("cudaSetDevice failed"); return nullptr; }
+  LPCNetBatch *b = new (std::nothrow) LPCNetBatch();
+  if (!b) { fail("out of memory"); return nullptr; }
+  b->device = device;
+  b->n_streams = n_streams;
+  cudaDeviceProp prop;
+  cudaGetDeviceProperties(&prop, device);
+  b->n_sms = prop.multiProcessorCount;
+  uint32_t rcp[2048];
+  bool have;
+  {
+    std::lock_guard<std::mutex> lk(g_cfg_mu);
+    have = g_have_rcp;
+    if (have) memcpy(rcp, g_rcp, sizeof(rcp));
+  }
+  std::string err;
+  if (!load_model(b->model, blob, len, features_delay, lpc_gamma, have ? rcp : nullptr, err)) {
+    fail(err);
+    delete b;
+    return nullptr;
+  }
+  const size_t need = sample_kernel_smem(64, b->model.d);
+  if (need > (size_t)prop.sharedMemPerBlockOptin) {
+    fail("model does not fit the shared-memory-resident kernel on this GPU");
+    free_model(b->model); delete b;
+    return nullptr;
+  }
+  if (alloc_state(b) != 0) { free_model(b->model); delete b; return nullptr; }
+  if (cudaStreamCreateWithFlags(&b->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
+    fail("cudaStreamCreate failed");
+    lpcnet_batch_destroy(b);
+    return nullptr;
+  }
+  b->stream = b->own_stream;
+  if (lpcnet_batch_reset(b, -1) != 0) { lpcnet_batch_destroy(b); return nullptr; }
+  return b;
+}
+
+void lpcnet_batch_destroy(LPCNetBatch *b) {
+  if (!b) return;
+  cudaSetDevice(b->device);
+  if (b->stream) cudaStreamSynchronize(b->stream);
+  free_model(b->model);
+  void *ptrs[] = {b->st_alloc, b->fb_alloc, b->d_feat, b->d_pcm, b->d_forced, b->d_trace, b->d_logits, b->d_packets};
+  for (void *p : ptrs) if (p) cudaFree(p);
+  if (b->own_stream) cudaStreamDestroy(b->own_stream);
+  delete b;
+}
+
+int lpcnet_batch_n_streams(const LPCNetBatch *b) { return b ? b->n_streams : 0; }
+int lpcnet_batch_nblocks(const LPCNetBatch *b, int which) { return !b ? 0 : (which == 0 ? b->model.nblocks_a : b->model.nblocks_b); }
+long long lpcnet_batch_launch_count(const LPCNetBatch *b) { return b ? b->launches : 0; }
+
+int lpcnet_batch_set_cuda_stream(LPCNetBatch *b, void *s) {
+  if (!b) return fail("null batch");
+  b->stream = s ? static_cast<cudaStream_t>(s) : b->own_stream;
+  return 0;
+}
+
+int lpcnet_batch_set_tile(LPCNetBatch *b, int t) {
+  if (!b) return fail("null batch");
+  if (t != 0 && t != 8 && t != 16 && t != 32 && t != 64) return fail("tile must be 0, 8, 16, 32 or 64");
+  b->tile = t;
+  return 0;
+}
+
+int lpcnet_batch_sync(LPCNetBatch *b) {
+  if (!b) return fail("null batch");
+  CK(cudaSetDevice(b->device));
+  CK(cudaStreamSynchronize(b->stream));
+  return 0;
+}
+
+// lpcnet_reset (src/lpcnet.c:174-182)
+int lpcnet_batch_reset(LPCNetBatch *b, int stream) {
+  if (!b) return fail("null batch");
+  if (stream >= b->n_streams) return fail("stream index out of range");
+  CK(cudaSetDevice(b->device));
+  CK(cudaStreamSynchronize(b->stream));
+  uint32_t seed[4];
+  lpcnet_kiss99_srand_host(seed, reinterpret_cast<const unsigned char *>("LPCNet"), 6);
+  const int s0 = stream < 0 ? 0 : stream, n = stream < 0 ? b->n_streams : 1;
+  const DevState &S = b->st;
+  CK(cudaMemset(S.conv1_state + (size_t)s0 * 168, 0, (size_t)n * 168 * 4));
+  CK(cudaMemset(S.conv2_state + (size_t)s0 * 256, 0, (size_t)n * 256 * 4));
+  CK(cudaMemset(S.gru_a + (size_t)s0 * kN, 0, (size_t)n * kN * 4));
+  CK(cudaMemset(S.gru_b + (size_t)s0 * kNB, 0, (size_t)n * kNB * 4));
+  CK(cudaMemset(S.last_sig + (size_t)s0 * 16, 0, (size_t)n * 16 * 4));
+  CK(cudaMemset(S.old_lpc + (size_t)s0 * kMaxDelay * 16, 0, (size_t)n * kMaxDelay * 16 * 4));
+  CK(cudaMemset(S.lpc + (size_t)s0 * 16, 0, (size_t)n * 16 * 4));
+  CK(cudaMemset(S.cond_a + (size_t)s0 * kRowsA, 0, (size_t)n * kRowsA * 4));
+  CK(cudaMemset(S.cond_b + (size_t)s0 * kRowsB, 0, (size_t)n * kRowsB * 4));
+  CK(cudaMemset(S.deemph + s0, 0, (size_t)n * 4));
+  CK(cudaMemset(S.frame_count + s0, 0, (size_t)n * 4));
+  CK(cudaMemset(S.vq_mem + (size_t)s0 * 18, 0, (size_t)n * 18 * 4));
+  std::vector<int> le(n, 128);  // lin2ulaw(0) = 128
+  std::vector<uint32_t> rng((size_t)n * 4);
+  for (int i = 0; i < n; i++) memcpy(&rng[(size_t)i * 4], seed, 16);
+  CK(cudaMemcpy(S.last_exc + s0, le.data(), (size_t)n * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(S.rng + (size_t)s0 * 4, rng.data(), (size_t)n * 16, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+int lpcnet_batch_set_seed(LPCNetBatch *b, int stream, const unsigned char *data, int n) {
+  if (!b) return fail("null batch");
+  if (stream < 0 || stream >= b->n_streams) return fail("stream index out of range");
+  CK(cudaSetDevice(b->device));
+  CK(cudaStreamSynchronize(b->stream));
+  uint32_t st[4];
+  lpcnet_kiss99_srand_host(st, data, n);
+  CK(cudaMemcpy(b->st.rng + (size_t)stream * 4, st, 16, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+int lpcnet_batch_set_codebooks(LPCNetBatch *b, const float *cb, int n) {
+  if (!b) return fail("null batch");
+  CK(cudaSetDevice(b->device));
+  std::string err;
+  if (!install_codebooks(b->model, cb, n, err)) return fail(err);
+  return 0;
+}
+
+int lpcnet_batch_synthesize_device(LPCNetBatch *b, const float *d_features, int stride, int n_frames, int spf,
+                                   short *d_pcm, const short *d_forced, LPCNetB200Trace *d_trace, float *d_logits) {
+  return synth_device(b, d_features, stride, n_frames, spf, d_pcm, d_forced, d_trace, d_logits);
+}
+
+int lpcnet_batch_synthesize(LPCNetBatch *b, const float *features, int stride, int n_frames, short *pcm,
+                            const short *forced, LPCNetB200Trace *trace, float *logits) {
+  if (!b) return fail("null batch");
+  if (n_frames <= 0) return 0;
+  if (!features || !pcm) return fail("null buffer");
+  CK(cudaSetDevice(b->device));
+  const size_t B = b->n_streams, T = (size_t)n_frames * kFrame;
+  const size_t fbytes = B * n_frames * (size_t)stride * 4, pbytes = B * T * 2;
+  if (grow(&b->d_feat, &b->d_feat_bytes, fbytes) || grow(&b->d_pcm, &b->d_pcm_bytes, pbytes)) return -1;
+  CK(cudaMemcpyAsync(b->d_feat, features, fbytes, cudaMemcpyHostToDevice, b->stream));
+  if (forced) {
+    if (grow(&b->d_forced, &b->d_forced_bytes, pbytes)) return -1;
+    CK(cudaMemcpyAsync(b->d_forced, forced, pbytes, cudaMemcpyHostToDevice, b->stream));
+  }
+  if (trace && grow(&b->d_trace, &b->d_trace_bytes, B * T * sizeof(LPCNetB200Trace))) return -1;
+  if (logits && grow(&b->d_logits, &b->d_logits_bytes, B * T * 256 * 4)) return -1;
+  if (synth_device(b, static_cast<const float *>(b->d_feat), stride, n_frames, kFrame, static_cast<short *>(b->d_pcm),
+                   forced ? static_cast<const short *>(b->d_forced) : nullptr,
+                   trace ? static_cast<LPCNetB200Trace *>(b->d_trace) : nullptr,
+                   logits ? static_cast<float *>(b->d_logits) : nullptr))
+    return -1;
+  CK(cudaMemcpyAsync(pcm, b->d_pcm, pbytes, cudaMemcpyDeviceToHost, b->stream));
+  if (trace) CK(cudaMemcpyAsync(trace, b->d_trace, B * T * sizeof(LPCNetB200Trace), cudaMemcpyDeviceToHost, b->stream));
+  if (logits) CK(cudaMemcpyAsync(logits, b->d_logits, B * T * 256 * 4, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  return 0;
+}
+
+int lpcnet_batch_frame_network(LPCNetBatch *b, const float *features, int stride, int n_frames, float *ga, float *gb,
+                               float *lpc) {
+  if (!b) return fail("null batch");
+  if (n_frames <= 0) return 0;
+  if (stride < kFeat) return fail("feature_stride must be >= 20");
+  CK(cudaSetDevice(b->device));
+  const size_t B = b->n_streams;
+  const size_t fbytes = B * n_frames * (size_t)stride * 4;
+  if (grow(&b->d_feat, &b->d_feat_bytes, fbytes)) return -1;
+  CK(cudaMemcpyAsync(b->d_feat, features, fbytes, cudaMemcpyHostToDevice, b->stream));
+  const int Fc = chunk_frames(b, n_frames);
+  if (ensure_frame_buffers(b, Fc)) return -1;
+  for (int f0 = 0; f0 < n_frames; f0 += Fc) {
+    const int F = (n_frames - f0) < Fc ? (n_frames - f0) : Fc;
+    if (run_frames(b, static_cast<const float *>(b->d_feat), stride, f0, F, n_frames)) return -1;
+    CK(cudaStreamSynchronize(b->stream));
+    // device [F][B][W] -> host [B][n_frames][W]
+    auto fetch = [&](float *dst, const float *src, int W) -> int {
+      if (!dst) return 0;
+      for (int f = 0; f < F; f++)
+        CK(cudaMemcpy2D(dst + (size_t)(f0 + f) * W, (size_t)n_frames * W * 4, src + (size_t)f * B * W, (size_t)W * 4,
+                        (size_t)W * 4, B, cudaMemcpyDeviceToHost));
+      return 0;
+    };
+    if (fetch(ga, b->fb.cond_a, kRowsA) || fetch(gb, b->fb.cond_b, kRowsB) || fetch(lpc, b->fb.lpc, 16)) return -1;
+  }
+  return 0;
+}
+
+int lpcnet_batch_decode(LPCNetBatch *b, const unsigned char *packets, int n_packets, short *pcm, float *features_out) {
+  if (!b) return fail("null batch");
+  if (n_packets <= 0) return 0;
+  if (!b->model.has_codebooks) return fail("no VQ codebooks: put ceps_codebook* arrays in the blob or call lpcnet_batch_set_codebooks");
+  CK(cudaSetDevice(b->device));
+  const size_t B = b->n_streams;
+  const int n_frames = 4 * n_packets;
+  const size_t pk_bytes = B * n_packets * 8, fbytes = B * n_frames * 36 * 4, pbytes = B * (size_t)n_frames * kFrame * 2;
+  if (grow(&b->d_packets, &b->d_packets_bytes, pk_bytes) || grow(&b->d_feat, &b->d_feat_bytes, fbytes) ||
+      grow(&b->d_pcm, &b->d_pcm_bytes, pbytes))
+    return -1;
+  CK(cudaMemcpyAsync(b->d_packets, packets, pk_bytes, cudaMemcpyHostToDevice, b->stream));
+  DecodeArgs da{};
+  da.m = b->model.d; da.st = b->st; da.n_streams = b->n_streams; da.n_packets = n_packets;
+  da.packets = static_cast<const unsigned char *>(b->d_packets); da.features = static_cast<float *>(b->d_feat);
+  int nl = 0;
+  CK(launch_decode_packets(da, b->stream, &nl));
+  b->launches += nl;
+  if (synth_device(b, static_cast<const float *>(b->d_feat), 36, n_frames, kFrame, static_cast<short *>(b->d_pcm), nullptr,
+                   nullptr, nullptr))
+    return -1;
+  if (pcm) CK(cudaMemcpyAsync(pcm, b->d_pcm, pbytes, cudaMemcpyDeviceToHost, b->stream));
+  if (features_out) CK(cudaMemcpyAsync(features_out, b->d_feat, fbytes, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  return 0;
+}
+
+int lpcnet_batch_get_state(LPCNetBatch *b, int s, LPCNetB200StreamState *o) {
+  if (!b || !o) return fail("null argument");
+  if (s < 0 || s >= b->n_streams) return fail("stream index out of range");
+  CK(cudaSetDevice(b->device));
+  CK(cudaStreamSynchronize(b->stream));
+  const DevState &S = b->st;
+  memset(o, 0, sizeof(*o));
+  CK(cudaMemcpy(o->conv1_state, S.conv1_state + (size_t)s * 168, 168 * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(o->conv2_state, S.conv2_state + (size_t)s * 256, 256 * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(o->gru_a_state, S.gru_a + (size_t)s * kN, kN * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(o->gru_b_state, S.gru_b + (size_t)s * kNB, kNB * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(o->last_sig, S.last_sig + (size_t)s * 16, 64, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(o->lpc, S.lpc + (size_t)s * 16, 64, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(o->old_lpc, S.old_lpc + (size_t)s * kMaxDelay * 16, (size_t)b->model.d.features_delay * 64, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(o->gru_a_condition, S.cond_a + (size_t)s * kRowsA, kRowsA * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(o->gru_b_condition, S.cond_b + (size_t)s * kRowsB, kRowsB * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(&o->deemph_mem, S.deemph + s, 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(&o->last_exc, S.last_exc + s, 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(&o->frame_count, S.frame_count + s, 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(o->rng, S.rng + (size_t)s * 4, 16, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int lpcnet_batch_set_state(LPCNetBatch *b, int s, const LPCNetB200StreamState *in) {
+  if (!b || !in) return fail("null argument");
+  if (s < 0 || s >= b->n_streams) return fail("stream index out of range");
+  CK(cudaSetDevice(b->device));
+  CK(cudaStreamSynchronize(b->stream));
+  const DevState &S = b->st;
+  CK(cudaMemcpy(S.conv1_state + (size_t)s * 168, in->conv1_state, 168 * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(S.conv2_state + (size_t)s * 256, in->conv2_state, 256 * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(S.gru_a + (size_t)s * kN, in->gru_a_state, kN * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(S.gru_b + (size_t)s * kNB, in->gru_b_state, kNB * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(S.last_sig + (size_t)s * 16, in->last_sig, 64, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(S.lpc + (size_t)s * 16, in->lpc, 64, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(S.old_lpc + (size_t)s * kMaxDelay * 16, in->old_lpc, (size_t)b->model.d.features_delay * 64, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(S.cond_a + (size_t)s * kRowsA, in->gru_a_condition, kRowsA * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(S.cond_b + (size_t)s * kRowsB, in->gru_b_condition, kRowsB * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(S.deemph + s, &in->deemph_mem, 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(S.last_exc + s, &in->last_exc, 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(S.frame_count + s, &in->frame_count, 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(S.rng + (size_t)s * 4, in->rng, 16, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+/* ---------------------------------------------------------------------------------------------
+ * Drop-in lpcnet.h symbols: a one-stream batch behind the reference's opaque state.
+ * ------------------------------------------------------------------------------------------- */
+struct LPCNetState {
+  uint32_t magic;
+  LPCNetBatch *batch;
+  float *pinned_feat;   // 36 floats
+  short *pinned_pcm;    // 160 samples
+};
+struct LPCNetDecState {
+  LPCNetState lpcnet_state;
+};
+static const uint32_t kMagic = 0x4C50434Eu;
+
+int lpcnet_get_size(void) { return (int)sizeof(LPCNetState); }
+
+int lpcnet_init(LPCNetState *st) {
+  memset(st, 0, sizeof(*st));
+  st->magic = kMagic;
+  return 0;
+}
+
+LPCNetState *lpcnet_create(void) {
+  LPCNetState *st = static_cast<LPCNetState *>(calloc(1, sizeof(LPCNetState)));
+  if (st) lpcnet_init(st);
+  return st;
+}
+
+static void state_release(LPCNetState *st) {
+  if (st->batch) lpcnet_batch_destroy(st->batch);
+  if (st->pinned_feat) cudaFreeHost(st->pinned_feat);
+  if (st->pinned_pcm) cudaFreeHost(st->pinned_pcm);
+  st->batch = nullptr; st->pinned_feat = nullptr; st->pinned_pcm = nullptr;
+}
+
+void lpcnet_destroy(LPCNetState *st) {
+  if (!st) return;
+  state_release(st);
+  free(st);
+}
+
+int lpcnet_load_model(LPCNetState *st, const unsigned char *data, int len) {
+  if (!st || st->magic != kMagic) return fail("lpcnet_load_model: state not initialised"), -1;
+  state_release(st);
+  int delay; float gamma;
+  { std::lock_guard<std::mutex> lk(g_cfg_mu); delay = g_default_delay; gamma = g_default_gamma; }
+  st->batch = lpcnet_batch_create(data, len, 1, -1, delay, gamma);
+  if (!st->batch) return -1;
+  if (cudaMallocHost(&st->pinned_feat, 36 * 4) != cudaSuccess || cudaMallocHost(&st->pinned_pcm, 640 * 2) != cudaSuccess) {
+    state_release(st);
+    return fail("cudaMallocHost failed"), -1;
+  }
+  return 0;
+}
+
+void lpcnet_reset(LPCNetState *st) {
+  if (st && st->batch) lpcnet_batch_reset(st->batch, -1);
+}
+
+void lpcnet_synthesize(LPCNetState *st, const float *features, short *output, int N) {
+  if (!st || !st->batch) { fail("lpcnet_synthesize: no model loaded (call lpcnet_load_model first)"); return; }
+  if (N <= 0) return;
+  if (N > kFrame) { fail("lpcnet_synthesize: N > 160"); return; }
+  LPCNetBatch *b = st->batch;
+  if (cudaSetDevice(b->device) != cudaSuccess) { fail("cudaSetDevice failed"); return; }
+  memcpy(st->pinned_feat, features, kFeat * 4);
+  if (grow(&b->d_feat, &b->d_feat_bytes, 36 * 4) || grow(&b->d_pcm, &b->d_pcm_bytes, kFrame * 2)) return;
+  if (cudaMemcpyAsync(b->d_feat, st->pinned_feat, kFeat * 4, cudaMemcpyHostToDevice, b->stream) != cudaSuccess) { fail("H2D failed"); return; }
+  if (synth_device(b, static_cast<const float *>(b->d_feat), kFeat, 1, N, static_cast<short *>(b->d_pcm), nullptr, nullptr, nullptr)) return;
+  if (cudaMemcpyAsync(st->pinned_pcm, b->d_pcm, (size_t)N * 2, cudaMemcpyDeviceToHost, b->stream) != cudaSuccess) { fail("D2H failed"); return; }
+  cudaError_t e = cudaStreamSynchronize(b->stream);
+  if (e != cudaSuccess) { fail_cuda("lpcnet_synthesize", e); return; }
+  memcpy(output, st->pinned_pcm, (size_t)N * 2);
+}
+
+int lpcnet_decoder_get_size(void) { return (int)sizeof(LPCNetDecState); }
+int lpcnet_decoder_init(LPCNetDecState *st) { return lpcnet_init(&st->lpcnet_state); }
+LPCNetDecState *lpcnet_decoder_create(void) {
+  LPCNetDecState *st = static_cast<LPCNetDecState *>(calloc(1, sizeof(LPCNetDecState)));
+  if (st) lpcnet_decoder_init(st);
+  return st;
+}
+void lpcnet_decoder_destroy(LPCNetDecState *st) {
+  if (!st) return;
+  state_release(&st->lpcnet_state);
+  free(st);
+}
+int lpcnet_decoder_load_model(LPCNetDecState *st, const unsigned char *data, int len) {
+  return lpcnet_load_model(&st->lpcnet_state, data, len);
+}
+int lpcnet_decode(LPCNetDecState *st, const unsigned char *buf, short *pcm) {
+  if (!st || !st->lpcnet_state.batch) return fail("lpcnet_decode: no model loaded");
+  return lpcnet_batch_decode(st->lpcnet_state.batch, buf, 1, pcm, nullptr);
+}
+
+}  // extern "C"

@@ -1,0 +1,111 @@
+// Device arithmetic that must reproduce the reference's AVX2 DOT_PROD build bit for bit.
+// This translation unit is compiled with -fmad=false: every `*` and `+` below is one IEEE
+// binary32 operation, and a fused multiply-add appears only where the reference itself uses
+// _mm256_fmadd_ps (written fmaf()).
+#pragma once
+#include <stdint.h>
+
+namespace lpcb {
+
+// `rcpps` (src/vec_avx.h:408,437): exactly a table over the top 11 mantissa bits; the
+// exponent just negates.  tab[i] = bits of rcpps(1 + i/2048).
+__device__ __forceinline__ float rcp_estimate(float x, const uint32_t *__restrict__ tab) {
+  uint32_t b = __float_as_uint(x);
+  uint32_t e = (b >> 23) & 0xffu;
+  return __uint_as_float(tab[(b >> 12) & 0x7ffu] - ((e - 127u) << 23));
+}
+
+// tanh8_approx (src/vec_avx.h:393-411)
+__device__ __forceinline__ float tanh_ref(float x, const uint32_t *__restrict__ tab) {
+  const float N0 = 952.52801514f, N1 = 96.39235687f, N2 = 0.60863042f;
+  const float D0 = 952.72399902f, D1 = 413.36801147f, D2 = 11.88600922f;
+  float X2 = x * x;
+  float num = fmaf(fmaf(N2, X2, N1), X2, N0);
+  float den = fmaf(fmaf(D2, X2, D1), X2, D0);
+  num = num * x;
+  den = rcp_estimate(den, tab);
+  num = num * den;
+  num = (1.f < num) ? 1.f : num;
+  num = (-1.f > num) ? -1.f : num;
+  return num;
+}
+
+// sigmoid8_approx (src/vec_avx.h:421-440)
+__device__ __forceinline__ float sigmoid_ref(float x, const uint32_t *__restrict__ tab) {
+  const float N0 = 238.13200378f, N1 = 6.02452230f, N2 = 0.00950985f;
+  const float D0 = 952.72399902f, D1 = 103.34200287f, D2 = 0.74287558f;
+  float X2 = x * x;
+  float num = fmaf(fmaf(N2, X2, N1), X2, N0);
+  float den = fmaf(fmaf(D2, X2, D1), X2, D0);
+  num = num * x;
+  den = rcp_estimate(den, tab);
+  num = fmaf(num, den, 0.5f);
+  num = (1.f < num) ? 1.f : num;
+  num = (0.f > num) ? 0.f : num;
+  return num;
+}
+
+// log2_approx + lin2ulaw (src/common.h:18-33, 47-58)
+__device__ __forceinline__ float log2_approx_ref(float x) {
+  int32_t i = (int32_t)__float_as_uint(x);
+  int integer = (i >> 23) - 127;
+  i -= integer << 23;
+  float frac = __uint_as_float((uint32_t)i) - 1.5f;
+  frac = -0.41445418f + frac * (0.95909232f + frac * (-0.33951290f + frac * 0.16541097f));
+  return (float)(1 + integer) + frac;
+}
+
+__device__ __forceinline__ int lin2ulaw_ref(float x) {
+  const float scale = 255.f / 32768.f;
+  float s = x >= 0 ? 1.f : -1.f;
+  x = fabsf(x);
+  float u = s * (128.f * (0.69315f * log2_approx_ref(1.f + scale * x)) / 5.5451774445f);
+  u = 128.f + u;
+  if (u < 0) u = 0;
+  if (u > 255) u = 255;
+  return (int)floor(.5 + (double)u);
+}
+
+// kiss99_rand (src/kiss99.c:59-81); st = {z, w, jsr, jcong}
+__device__ __forceinline__ uint32_t kiss99_next(uint32_t &z, uint32_t &w, uint32_t &jsr, uint32_t &jcong) {
+  z = 36969u * (z & 0xFFFFu) + (z >> 16);
+  w = 18000u * (w & 0xFFFFu) + (w >> 16);
+  uint32_t mwc = (z << 16) + w;
+  jsr ^= jsr << 13;
+  jsr ^= jsr >> 17;
+  jsr ^= jsr << 5;
+  jcong = 69069u * jcong + 1234567u;
+  return (mwc ^ jcong) + jsr;
+}
+
+// cvtps2dq (round to nearest even; out of range -> 0x80000000), as used to seed the int32
+// accumulators (src/vec_avx.h:703-705, 804-806).
+__device__ __forceinline__ int32_t cvt_rne_ref(float x) {
+  if (!(x >= -2147483648.f && x < 2147483648.f)) return (int32_t)0x80000000;
+  return __float2int_rn(x);
+}
+
+// vector_ps_to_epi8 (src/vec_avx.h:321-336): u8 = packus(packus(cvtps2dq(fma(x,127,127))))
+__device__ __forceinline__ uint32_t quant_u8_ref(float x) {
+  int32_t v = cvt_rne_ref(fmaf(x, 127.f, 127.f));
+  int32_t t = v < 0 ? 0 : (v > 65535 ? 65535 : v);   // packus_epi32
+  int32_t s = (int32_t)(int16_t)(uint16_t)t;        // packus_epi16 reads it as signed 16
+  return (uint32_t)(s < 0 ? 0 : (s > 255 ? 255 : s));
+}
+
+#define LPCB_SCALE (128.f * 127.f)
+#define LPCB_SCALE_1 (1.f / 128.f / 127.f)
+
+__device__ __forceinline__ int32_t acc_seed(float v) { return cvt_rne_ref(v * LPCB_SCALE); }
+__device__ __forceinline__ float acc_out(int32_t acc) { return (float)acc * LPCB_SCALE_1; }
+
+// D += A(u8, 16x32 row) * B(s8, 32x8 col), int32 accumulate.  SASS: IMMA.16832.U8.S8
+__device__ __forceinline__ void mma_u8s8(int32_t (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                         uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+      : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+}  // namespace lpcb

@@ -1,0 +1,166 @@
+// Internal structures shared by the host shim and the CUDA kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+namespace lpcb {
+
+// Default model dimensions (training_tf2/lpcnet.py:312-325).  The blob loader
+// checks every array against them, exactly like the reference's generated init function.
+constexpr int kN = 384;        // GRU_A_STATE_SIZE
+constexpr int kNB = 16;        // GRU_B_STATE_SIZE
+constexpr int kC = 128;        // FEATURE_DENSE2_OUT_SIZE
+constexpr int kPitchEmb = 64;  // EMBED_PITCH_OUT_SIZE
+constexpr int kFeat = 20;      // NB_FEATURES
+constexpr int kConvIn = kFeat + kPitchEmb;  // 84
+constexpr int kLpcOrder = 16;
+constexpr int kFrame = 160;
+constexpr int kMaxDelay = 2;
+constexpr int kRowsA = 3 * kN;   // 1152
+constexpr int kRowsB = 3 * kNB;  // 48
+
+// u8 activation rows in shared memory are padded to an odd word stride so that the
+// per-lane 4-byte gathers of the MMA A fragments spread over the banks.
+constexpr int kXaStride = kN / 4 + 1;    // words per stream
+constexpr int kXbStride = kNB / 4 + 1;
+
+// Block-sparse int8 matrix re-tiled for mma.sync.m16n8k32 B fragments.
+// A "chunk" is 8 blocks (K = 32) of one 8-row group.
+struct PackedSparse {
+  int n_groups = 0;   // rows / 8
+  int n_chunks = 0;
+  int n_blocks = 0;   // real (un-padded) blocks
+  std::vector<uint32_t> chunk_start;  // [n_groups + 1]
+  std::vector<uint8_t> pos;           // [n_chunks][8]  column position / 4
+  std::vector<uint32_t> w;            // [n_chunks][2][32] words, fragment order
+};
+
+struct DevSparse {
+  int n_groups, n_chunks;
+  const uint32_t *chunk_start;  // device
+  const uint2 *pos;             // device, [n_chunks]
+  const uint32_t *w;            // device, [n_chunks][64]
+};
+
+// Device-side model: pointers into one device allocation.
+struct DevModel {
+  // 100 Hz frame network (fp32, blob layout)
+  const float *embed_pitch;                 // [256][64]
+  const float *conv1_w, *conv1_b;           // [3*84][128], [128]
+  const float *conv2_w, *conv2_b;           // [3*128][128], [128]
+  const float *dense1_w, *dense1_b, *dense2_w, *dense2_b;
+  const float *a_feat_w, *a_feat_b;         // [128][1152], [1152]
+  const float *b_feat_w, *b_feat_b;         // [128][48], [48]
+  // 16 kHz sample network
+  const float *e_sig, *e_pred, *e_exc;      // [256][1152]
+  const float *a_subias_rec;                // [1152] = &sparse_gru_a_subias[3N]
+  const float *a_diag;                      // [1152]
+  DevSparse a_rec;                          // 1152 x 384 block-sparse
+  const float *b_subias;                    // [96]
+  DevSparse b_in;                           // 48 x 384 (sparse stream format, dense by default)
+  DevSparse b_rec;                          // 48 x 16 dense
+  const float *fc_w, *fc_bias, *fc_factor;  // [256][2][16], [2][256], [2][256]
+  const uint32_t *rcp_tab;                  // [2048]
+  const float *ulaw2lin_tab;                // [256]
+  const float *logit_tab;                   // [256]
+  // DSP tables
+  const float *fft_tw;                      // [320][2]
+  const int16_t *fft_bitrev;                // [320]
+  const float *dct;                         // [18*18]
+  const float *codebooks;                   // cb1|cb2|cb3|diff4 or NULL
+  int features_delay;
+  float lpc_gamma;
+};
+
+// Per-stream mutable state, structure-of-arrays in HBM ([field][stream] where noted).
+struct DevState {
+  float *conv1_state;   // [B][168]
+  float *conv2_state;   // [B][256]
+  float *gru_a;         // [B][384]
+  float *gru_b;         // [B][16]
+  float *last_sig;      // [B][16]
+  float *old_lpc;       // [B][2][16]
+  float *lpc;           // [B][16]      (current frame)
+  float *cond_a;        // [B][1152]    (current frame)
+  float *cond_b;        // [B][48]
+  float *deemph;        // [B]
+  int *last_exc;        // [B]
+  int *frame_count;     // [B]
+  uint32_t *rng;        // [B][4]
+  float *vq_mem;        // [B][18]
+};
+
+struct Model {
+  DevModel d{};
+  void *dev_blob = nullptr;
+  size_t dev_bytes = 0;
+  int nblocks_a = 0, nblocks_b = 0;
+  bool has_codebooks = false;
+};
+
+// Loads and validates a DNNw blob (src/parse_lpcnet_weights.c) and builds the device model.
+// Returns false and fills `err` on failure.
+bool load_model(Model &m, const unsigned char *blob, int len, int features_delay, float lpc_gamma,
+                const uint32_t *rcp_tab, std::string &err);
+void free_model(Model &m);
+bool install_codebooks(Model &m, const float *cb, int n, std::string &err);
+
+void default_rcp_table(uint32_t *tab);
+
+// Per-chunk scratch: conditioning for F frames.
+struct FrameBuffers {
+  int cap_frames = 0;
+  float *in_vec = nullptr;   // [B][F+2][84]   frame-network input rows incl. 2 history rows
+  float *c1 = nullptr;       // [B][F+2][128]  conv1 outputs incl. 2 history rows
+  float *cond_a = nullptr;   // [F][B][1152]
+  float *cond_b = nullptr;   // [F][B][48]
+  float *lpc = nullptr;      // [F][B][16]
+  uint8_t *active = nullptr; // [F][B]
+  float *fft_scratch = nullptr;  // [2][320][2][B*F]  (ping-pong not needed: in-place) -> [320][2][B*F]
+};
+
+struct SampleArgs {
+  DevModel m;
+  DevState st;
+  int n_streams;
+  int n_frames;              // frames in this chunk
+  int spf;                   // samples per frame (<=160)
+  int frame0;                // index of the chunk's first frame within the call
+  int total_frames;          // frames in the whole call (pcm row length = total_frames*spf)
+  const float *cond_a;       // [F][B][1152]
+  const float *cond_b;       // [F][B][48]
+  const float *lpc;          // [F][B][16]
+  const uint8_t *active;     // [F][B]
+  short *pcm;                // [B][total_frames*spf]
+  const short *forced;       // nullable, same layout
+  void *trace;               // nullable LPCNetB200Trace [B][total_frames*spf]
+  float *logits;             // nullable [B][total_frames*spf][256]
+};
+
+cudaError_t launch_sample_kernel(const SampleArgs &a, int tile_streams, int n_sms, cudaStream_t s,
+                                 int *n_launches);
+size_t sample_kernel_smem(int tile_streams, const DevModel &m);
+
+struct FrameArgs {
+  DevModel m;
+  DevState st;
+  FrameBuffers fb;
+  int n_streams, n_frames;
+  const float *features;     // device [B][total_frames][stride]
+  int feature_stride;
+  int frame0, total_frames;
+};
+cudaError_t launch_frame_network(const FrameArgs &a, cudaStream_t s, int *n_launches);
+
+struct DecodeArgs {
+  DevModel m;
+  DevState st;
+  int n_streams, n_packets;
+  const unsigned char *packets;  // device [B][n_packets][8]
+  float *features;               // device [B][n_packets*4][36]
+};
+cudaError_t launch_decode_packets(const DecodeArgs &a, cudaStream_t s, int *n_launches);
+
+}  // namespace lpcb

@@ -1,0 +1,465 @@
+// The 100 Hz frame network (run_frame_network, src/lpcnet.c:82-120) for a chunk of frames of
+// every stream at once, plus the cepstrum -> LPC chain (src/freq.c:202-320, src/kiss_fft.c) and
+// the 1.6 kb/s packet decoder (src/lpcnet_dec.c:59-155).
+//
+// The k=3 convolutions of the reference are dense layers over [two previous inputs | input]
+// (src/nnet.c:452-470), so nothing is recurrent across frames except those two-row histories:
+// every (stream, frame) row of the chunk is evaluated in parallel, with the histories carried
+// in the stream state between chunks.  All matvecs accumulate with fmaf in ascending input
+// order starting from the bias, which is exactly sgemv_accum16 (src/vec_avx.h:618-643).
+#include "bitexact.cuh"
+#include "engine.h"
+
+namespace lpcb {
+
+namespace {
+
+constexpr int kRowsPerBlock = 8;
+constexpr int kFT = 128;  // threads per block of the dense kernels
+
+__device__ __forceinline__ int frame_count_at(int fc0, int f) { return min(fc0 + f, 1000); }
+
+// K0: in_vec rows (history + features|pitch embedding) and the per-frame active flags.
+__global__ void frame_inputs_kernel(FrameArgs A) {
+  const int B = A.n_streams, F = A.n_frames;
+  const int row = blockIdx.x;  // (stream, r) with r in [0, F+2)
+  const int s = row / (F + 2), r = row % (F + 2);
+  float *dst = A.fb.in_vec + ((size_t)s * (F + 2) + r) * kConvIn;
+  const int tid = threadIdx.x;
+  if (r < 2) {
+    // feature_conv1_state = [older input | newer input] (src/nnet.c:460-469)
+    if (tid < kConvIn) dst[tid] = A.st.conv1_state[(size_t)s * 2 * kConvIn + r * kConvIn + tid];
+    // conv2 history rows of c1
+    for (int i = tid; i < kC; i += blockDim.x)
+      A.fb.c1[((size_t)s * (F + 2) + r) * kC + i] = A.st.conv2_state[(size_t)s * 2 * kC + r * kC + i];
+    return;
+  }
+  const int f = r - 2;
+  const float *feat = A.features + ((size_t)s * A.total_frames + A.frame0 + f) * A.feature_stride;
+  // pitch = (int)floor(.1 + 50*features[18] + 100), clamped to [33,255] (src/lpcnet.c:93-94)
+  int pitch = (int)floor(.1 + (double)(50.f * feat[18]) + 100);
+  pitch = pitch > 255 ? 255 : (pitch < 33 ? 33 : pitch);
+  if (tid < kFeat) dst[tid] = feat[tid];
+  else if (tid < kConvIn) dst[tid] = A.m.embed_pitch[pitch * kPitchEmb + tid - kFeat];
+  if (tid == 0) {
+    const int fc0 = A.st.frame_count[s];
+    // lpcnet_synthesize_tail_impl runs after frame_count++ (src/lpcnet.c:119, 239)
+    A.fb.active[(size_t)f * B + s] = (frame_count_at(fc0, f + 1) > A.m.features_delay) ? 1 : 0;
+  }
+}
+
+// out[r][i] = act(bias[i] + sum_j W[j*N+i] * x[r][j]), j ascending, fmaf: sgemv_accum16 order.
+template <int R>
+__device__ __forceinline__ void dense_rows(const float *__restrict__ W, const float *__restrict__ bias, int K, int N,
+                                           const float *x /*smem [R][K]*/, float *out /*[R][N] smem or global rows*/,
+                                           int out_stride, bool do_tanh, const uint32_t *rcp, int tid, int nthreads,
+                                           const bool *zero_row) {
+  for (int i = tid; i < N; i += nthreads) {
+    float acc[R];
+    const float b = __ldg(bias + i);
+#pragma unroll
+    for (int r = 0; r < R; r++) acc[r] = b;
+    for (int j = 0; j < K; j++) {
+      const float w = __ldg(W + (size_t)j * N + i);
+#pragma unroll
+      for (int r = 0; r < R; r++) acc[r] = fmaf(w, x[r * K + j], acc[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      float v = do_tanh ? tanh_ref(acc[r], rcp) : acc[r];
+      if (zero_row && zero_row[r]) v = 0.f;
+      out[(size_t)r * out_stride + i] = v;
+    }
+  }
+}
+
+// K1: conv1 for R rows per block.
+__global__ void __launch_bounds__(kFT) conv1_kernel(FrameArgs A) {
+  constexpr int R = kRowsPerBlock;
+  __shared__ float x[R][3 * kConvIn];
+  __shared__ float y[R][kC];
+  __shared__ bool zero[R];
+  __shared__ uint32_t rcp[2048];
+  const int F = A.n_frames, total = A.n_streams * F;
+  const int tid = threadIdx.x;
+  for (int i = tid; i < 2048; i += kFT) rcp[i] = A.m.rcp_tab[i];
+  for (int r = 0; r < R; r++) {
+    const int row = min(blockIdx.x * R + r, total - 1);
+    const int s = row / F, f = row % F;
+    const float *src = A.fb.in_vec + ((size_t)s * (F + 2) + f) * kConvIn;  // rows f, f+1, f+2 are contiguous
+    for (int i = tid; i < 3 * kConvIn; i += kFT) x[r][i] = src[i];
+    if (tid == 0) zero[r] = frame_count_at(A.st.frame_count[s], f) < 1;  // FEATURE_CONV1_DELAY (src/lpcnet.c:99)
+  }
+  __syncthreads();
+  dense_rows<R>(A.m.conv1_w, A.m.conv1_b, 3 * kConvIn, kC, &x[0][0], &y[0][0], kC, true, rcp, tid, kFT, zero);
+  __syncthreads();
+  for (int r = 0; r < R; r++) {
+    const int row = blockIdx.x * R + r;
+    if (row >= total) break;
+    const int s = row / F, f = row % F;
+    for (int i = tid; i < kC; i += kFT) A.fb.c1[((size_t)s * (F + 2) + f + 2) * kC + i] = y[r][i];
+  }
+}
+
+// K2: conv2 -> dense1 -> dense2 -> gru_a/gru_b conditioning for R rows per block.
+__global__ void __launch_bounds__(kFT) cond_kernel(FrameArgs A) {
+  constexpr int R = kRowsPerBlock;
+  __shared__ float x[R][3 * kC];
+  __shared__ float y[R][kC];
+  __shared__ float z[R][kC];
+  __shared__ bool zero[R];
+  __shared__ int row_s[R], row_f[R];
+  __shared__ uint32_t rcp[2048];
+  const int F = A.n_frames, B = A.n_streams, total = B * F;
+  const int tid = threadIdx.x;
+  for (int i = tid; i < 2048; i += kFT) rcp[i] = A.m.rcp_tab[i];
+  for (int r = 0; r < R; r++) {
+    const int row = min(blockIdx.x * R + r, total - 1);
+    const int s = row / F, f = row % F;
+    const float *src = A.fb.c1 + ((size_t)s * (F + 2) + f) * kC;
+    for (int i = tid; i < 3 * kC; i += kFT) x[r][i] = src[i];
+    if (tid == 0) {
+      zero[r] = frame_count_at(A.st.frame_count[s], f) < A.m.features_delay;  // src/lpcnet.c:101
+      row_s[r] = s; row_f[r] = f;
+    }
+  }
+  __syncthreads();
+  dense_rows<R>(A.m.conv2_w, A.m.conv2_b, 3 * kC, kC, &x[0][0], &y[0][0], kC, true, rcp, tid, kFT, zero);
+  __syncthreads();
+  dense_rows<R>(A.m.dense1_w, A.m.dense1_b, kC, kC, &y[0][0], &z[0][0], kC, true, rcp, tid, kFT, nullptr);
+  __syncthreads();
+  dense_rows<R>(A.m.dense2_w, A.m.dense2_b, kC, kC, &z[0][0], &y[0][0], kC, true, rcp, tid, kFT, nullptr);
+  __syncthreads();
+  // linear heads, written straight to [F][B][*]
+  for (int i = tid; i < kRowsA + kRowsB; i += kFT) {
+    const bool isA = i < kRowsA;
+    const int col = isA ? i : i - kRowsA, N = isA ? kRowsA : kRowsB;
+    const float *W = isA ? A.m.a_feat_w : A.m.b_feat_w;
+    float acc[R];
+    const float b = __ldg((isA ? A.m.a_feat_b : A.m.b_feat_b) + col);
+#pragma unroll
+    for (int r = 0; r < R; r++) acc[r] = b;
+    for (int j = 0; j < kC; j++) {
+      const float w = __ldg(W + (size_t)j * N + col);
+#pragma unroll
+      for (int r = 0; r < R; r++) acc[r] = fmaf(w, y[r][j], acc[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      if (blockIdx.x * R + r >= total) break;
+      float *dst = isA ? A.fb.cond_a + ((size_t)row_f[r] * B + row_s[r]) * kRowsA
+                       : A.fb.cond_b + ((size_t)row_f[r] * B + row_s[r]) * kRowsB;
+      dst[col] = acc[r];
+    }
+  }
+}
+
+// ---- kiss_fft, nfft = 320 = 5*4*4*4 (float build), per-thread, scratch interleaved over threads ----
+struct Cpx { float r, i; };
+#define C_MUL(m, a, b) do { (m).r = (a).r * (b).r - (a).i * (b).i; (m).i = (a).r * (b).i + (a).i * (b).r; } while (0)
+#define C_ADD(res, a, b) do { (res).r = (a).r + (b).r; (res).i = (a).i + (b).i; } while (0)
+#define C_SUB(res, a, b) do { (res).r = (a).r - (b).r; (res).i = (a).i - (b).i; } while (0)
+#define C_ADDTO(res, a) do { (res).r += (a).r; (res).i += (a).i; } while (0)
+
+struct Scratch {
+  float *base;   // [320][2][stride]
+  size_t stride;
+  __device__ __forceinline__ Cpx ld(int k) const { Cpx c; c.r = base[(size_t)(2 * k) * stride]; c.i = base[(size_t)(2 * k + 1) * stride]; return c; }
+  __device__ __forceinline__ void st(int k, Cpx c) const { base[(size_t)(2 * k) * stride] = c.r; base[(size_t)(2 * k + 1) * stride] = c.i; }
+};
+
+__device__ __forceinline__ Cpx twd(const float *tw, int k) { Cpx c; c.r = __ldg(tw + 2 * k); c.i = __ldg(tw + 2 * k + 1); return c; }
+
+// kf_bfly4 (src/kiss_fft.c:96-162)
+__device__ void bfly4(const Scratch &S, const float *tw, int fstride, int m, int N, int mm) {
+  if (m == 1) {
+    for (int i = 0; i < N; i++) {
+      const int o = 4 * i;
+      Cpx f0 = S.ld(o), f1 = S.ld(o + 1), f2 = S.ld(o + 2), f3 = S.ld(o + 3), s0, s1;
+      C_SUB(s0, f0, f2);
+      C_ADDTO(f0, f2);
+      C_ADD(s1, f1, f3);
+      C_SUB(f2, f0, s1);
+      C_ADDTO(f0, s1);
+      C_SUB(s1, f1, f3);
+      f1.r = s0.r + s1.i; f1.i = s0.i - s1.r;
+      f3.r = s0.r - s1.i; f3.i = s0.i + s1.r;
+      S.st(o, f0); S.st(o + 1, f1); S.st(o + 2, f2); S.st(o + 3, f3);
+    }
+  } else {
+    const int m2 = 2 * m, m3 = 3 * m;
+    for (int i = 0; i < N; i++) {
+      const int base = i * mm;
+      for (int j = 0; j < m; j++) {
+        const int o = base + j;
+        Cpx s[6];
+        Cpx f0 = S.ld(o), fm = S.ld(o + m), fm2 = S.ld(o + m2), fm3 = S.ld(o + m3);
+        const Cpx t1 = twd(tw, j * fstride), t2 = twd(tw, j * fstride * 2), t3 = twd(tw, j * fstride * 3);
+        C_MUL(s[0], fm, t1);
+        C_MUL(s[1], fm2, t2);
+        C_MUL(s[2], fm3, t3);
+        C_SUB(s[5], f0, s[1]);
+        C_ADDTO(f0, s[1]);
+        C_ADD(s[3], s[0], s[2]);
+        C_SUB(s[4], s[0], s[2]);
+        C_SUB(fm2, f0, s[3]);
+        C_ADDTO(f0, s[3]);
+        fm.r = s[5].r + s[4].i; fm.i = s[5].i - s[4].r;
+        fm3.r = s[5].r - s[4].i; fm3.i = s[5].i + s[4].r;
+        S.st(o, f0); S.st(o + m, fm); S.st(o + m2, fm2); S.st(o + m3, fm3);
+      }
+    }
+  }
+}
+
+// kf_bfly5 (src/kiss_fft.c:229-295)
+__device__ void bfly5(const Scratch &S, const float *tw, int fstride, int m, int N, int mm) {
+  const Cpx ya = twd(tw, fstride * m), yb = twd(tw, fstride * 2 * m);
+  for (int i = 0; i < N; i++) {
+    const int base = i * mm;
+    for (int u = 0; u < m; ++u) {
+      const int o = base + u;
+      Cpx s[13];
+      Cpx F0 = S.ld(o), F1 = S.ld(o + m), F2 = S.ld(o + 2 * m), F3 = S.ld(o + 3 * m), F4 = S.ld(o + 4 * m);
+      s[0] = F0;
+      C_MUL(s[1], F1, twd(tw, u * fstride));
+      C_MUL(s[2], F2, twd(tw, 2 * u * fstride));
+      C_MUL(s[3], F3, twd(tw, 3 * u * fstride));
+      C_MUL(s[4], F4, twd(tw, 4 * u * fstride));
+      C_ADD(s[7], s[1], s[4]);
+      C_SUB(s[10], s[1], s[4]);
+      C_ADD(s[8], s[2], s[3]);
+      C_SUB(s[9], s[2], s[3]);
+      F0.r = F0.r + (s[7].r + s[8].r);
+      F0.i = F0.i + (s[7].i + s[8].i);
+      s[5].r = s[0].r + (s[7].r * ya.r + s[8].r * yb.r);
+      s[5].i = s[0].i + (s[7].i * ya.r + s[8].i * yb.r);
+      s[6].r = s[10].i * ya.i + s[9].i * yb.i;
+      s[6].i = -(s[10].r * ya.i + s[9].r * yb.i);
+      C_SUB(F1, s[5], s[6]);
+      C_ADD(F4, s[5], s[6]);
+      s[11].r = s[0].r + (s[7].r * yb.r + s[8].r * ya.r);
+      s[11].i = s[0].i + (s[7].i * yb.r + s[8].i * ya.r);
+      s[12].r = s[9].i * ya.i - s[10].i * yb.i;
+      s[12].i = s[10].r * yb.i - s[9].r * ya.i;
+      C_ADD(F2, s[11], s[12]);
+      C_SUB(F3, s[11], s[12]);
+      S.st(o, F0); S.st(o + m, F1); S.st(o + 2 * m, F2); S.st(o + 3 * m, F3); S.st(o + 4 * m, F4);
+    }
+  }
+}
+
+__constant__ short c_eband5ms[18] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 10, 12, 14, 16, 20, 24, 28, 34, 40};
+__constant__ float c_compensation[18] = {0.8f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 0.666667f, 0.5f, 0.5f,
+                                         0.5f, 0.333333f, 0.25f, 0.25f, 0.2f, 0.166667f, 0.173913f};
+
+// lpc_from_cepstrum (src/freq.c:310-320) and everything below it; one thread per (stream, frame).
+__device__ void lpc_from_cepstrum_dev(const DevModel &M, const float *cepstrum, float *lpc, const Scratch &S) {
+  float tmp[18], Ex[18];
+  for (int i = 0; i < 18; i++) tmp[i] = cepstrum[i];
+  tmp[0] += 4;
+  // idct (freq.c:230-240)
+  for (int i = 0; i < 18; i++) {
+    float sum = 0;
+    for (int j = 0; j < 18; j++) sum += tmp[j] * __ldg(M.dct + i * 18 + j);
+    Ex[i] = (float)((double)sum * sqrt(2. / 18));
+  }
+  for (int i = 0; i < 18; i++) Ex[i] = (float)(pow((double)10.f, (double)Ex[i]) * (double)c_compensation[i]);
+  // interp_band_gain (freq.c:202-215) written straight into the bit-reversed FFT input
+  // (opus_fft_c, kiss_fft.c:566-585: fout[bitrev[i]] = scale * fin[i]); bins 160 and above band 17 are 0.
+  const float scale = 1.f / 320;
+  for (int k = 0; k < 320; k++) { Cpx zc; zc.r = 0.f; zc.i = 0.f; S.st(k, zc); }
+  for (int i = 0; i < 17; i++) {
+    const int band_size = (c_eband5ms[i + 1] - c_eband5ms[i]) * 4;
+    for (int j = 0; j < band_size; j++) {
+      const float frac = (float)j / (float)band_size;
+      const float v = (1.f - frac) * Ex[i] + frac * Ex[i + 1];
+      const int k = c_eband5ms[i] * 4 + j;   // 0..159
+      Cpx c;
+      c.r = scale * v; c.i = scale * 0.f;
+      S.st(__ldg(M.fft_bitrev + k), c);
+      if (k > 0) {
+        // inverse_transform (freq.c:256-273): x[320-k] = conj(x[k])
+        Cpx cc;
+        cc.r = scale * v; cc.i = scale * (-0.f);
+        S.st(__ldg(M.fft_bitrev + 320 - k), cc);
+      }
+    }
+  }
+  // opus_fft_impl (kiss_fft.c:518-563), factors {5,64, 4,16, 4,4, 4,1}
+  const float *tw = M.fft_tw;
+  bfly4(S, tw, 80, 1, 80, 1);    // i=3: p=4, m=1,  fstride=5*4*4, N=fstride, mm=m2=4
+  bfly4(S, tw, 20, 4, 20, 16);   // i=2: p=4, m=4
+  bfly4(S, tw, 5, 16, 5, 64);    // i=1: p=4, m=16
+  bfly5(S, tw, 1, 64, 1, 1);     // i=0: p=5, m=64
+  float ac[17];
+  ac[0] = 320.f * S.ld(0).r;
+  for (int i = 1; i < 17; i++) ac[i] = 320.f * S.ld(320 - i).r;
+  // lpc_from_bands (freq.c:290-296): noise floor and lag window in double
+  ac[0] = (float)((double)ac[0] + ((double)ac[0] * 1e-4 + 320 / 12 / 38.));
+  for (int i = 1; i < 17; i++) ac[i] = (float)((double)ac[i] * (1 - 6e-5 * i * i));
+  // lpcn_lpc (freq.c:86-127)
+  float error = ac[0];
+  for (int i = 0; i < 16; i++) lpc[i] = 0;
+  if (ac[0] != 0) {
+    for (int i = 0; i < 16; i++) {
+      float rr = 0;
+      for (int j = 0; j < i; j++) rr += lpc[j] * ac[i - j];
+      rr += ac[i + 1];
+      const float r = -rr / error;
+      lpc[i] = r;
+      for (int j = 0; j < (i + 1) >> 1; j++) {
+        const float t1 = lpc[j], t2 = lpc[i - 1 - j];
+        lpc[j] = t1 + r * t2;
+        lpc[i - 1 - j] = t2 + r * t1;
+      }
+      error = error - (r * r) * error;
+      if (error < .001f * ac[0]) break;
+    }
+  }
+}
+
+// K3a: raw LPC per (stream, frame) into fb.lpc[f][s] (delay line applied by K3b).
+__global__ void lpc_kernel(FrameArgs A) {
+  const int B = A.n_streams, F = A.n_frames;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t nthreads = (size_t)gridDim.x * blockDim.x;
+  if (idx >= B * F) return;
+  const int s = idx / F, f = idx % F;
+  Scratch S{A.fb.fft_scratch + idx, nthreads};
+  const float *feat = A.features + ((size_t)s * A.total_frames + A.frame0 + f) * A.feature_stride;
+  float lpc[16];
+  lpc_from_cepstrum_dev(A.m, feat, lpc, S);
+  float *dst = A.fb.lpc + ((size_t)f * B + s) * 16;
+  for (int i = 0; i < 16; i++) dst[i] = lpc[i];
+}
+
+// K3b: the FEATURES_DELAY delay line (src/lpcnet.c:109-115), lpc_weighting (freq.c:299-308), and the
+// per-stream frame-state update (conv histories, old_lpc, frame_count).  One thread per stream,
+// frames walked newest to oldest so the in-place shift never reads an overwritten row.
+__global__ void frame_finalize_kernel(FrameArgs A) {
+  const int B = A.n_streams, F = A.n_frames, D = A.m.features_delay;
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= B) return;
+  if (D > 0) {
+    float newest[kMaxDelay][16];   // new_lpc[F-1-k]
+    for (int k = 0; k < D; k++)
+      for (int i = 0; i < 16; i++)
+        newest[k][i] = (F - 1 - k >= 0) ? A.fb.lpc[((size_t)(F - 1 - k) * B + s) * 16 + i]
+                                        : A.st.old_lpc[((size_t)s * kMaxDelay + (k - F)) * 16 + i];
+    for (int f = F - 1; f >= 0; f--) {
+      float *dst = A.fb.lpc + ((size_t)f * B + s) * 16;
+      const float *src = (f - D >= 0) ? A.fb.lpc + ((size_t)(f - D) * B + s) * 16
+                                      : A.st.old_lpc + ((size_t)s * kMaxDelay + (D - 1 - f)) * 16;
+      float v[16];
+      for (int i = 0; i < 16; i++) v[i] = src[i];
+      for (int i = 0; i < 16; i++) dst[i] = v[i];
+    }
+    for (int k = 0; k < D; k++)
+      for (int i = 0; i < 16; i++) A.st.old_lpc[((size_t)s * kMaxDelay + k) * 16 + i] = newest[k][i];
+  }
+  for (int f = 0; f < F; f++) {
+    float *dst = A.fb.lpc + ((size_t)f * B + s) * 16;
+    float gamma_i = A.m.lpc_gamma;
+    for (int i = 0; i < 16; i++) { dst[i] = dst[i] * gamma_i; gamma_i = gamma_i * A.m.lpc_gamma; }
+  }
+  // histories: the last two in_vec / c1 rows (rows F and F+1 of the [F+2] buffers)
+  for (int r = 0; r < 2; r++) {
+    const float *iv = A.fb.in_vec + ((size_t)s * (F + 2) + F + r) * kConvIn;
+    for (int i = 0; i < kConvIn; i++) A.st.conv1_state[(size_t)s * 2 * kConvIn + r * kConvIn + i] = iv[i];
+    const float *cv = A.fb.c1 + ((size_t)s * (F + 2) + F + r) * kC;
+    for (int i = 0; i < kC; i++) A.st.conv2_state[(size_t)s * 2 * kC + r * kC + i] = cv[i];
+  }
+  // current-frame conditioning kept in the stream state like the reference (lpcnet_private.h:43-47)
+  for (int i = 0; i < 16; i++) A.st.lpc[(size_t)s * 16 + i] = A.fb.lpc[((size_t)(F - 1) * B + s) * 16 + i];
+  A.st.frame_count[s] = frame_count_at(A.st.frame_count[s], F);
+}
+
+// ---- packet decoder (src/lpcnet_dec.c:59-155, src/common.c:37-65), one thread per stream ----
+__device__ __forceinline__ unsigned bits_take(const unsigned char *p, int &bitpos, int n) {
+  unsigned d = 0;
+  for (int k = 0; k < n; k++, bitpos++) d = (d << 1) | ((p[bitpos >> 3] >> (7 - (bitpos & 7))) & 1u);
+  return d;
+}
+
+__device__ __forceinline__ void single_interp_dev(float *x, const float *left, const float *right, int id) {
+  for (int i = 0; i < 18; i++) {
+    if (id == 0) x[i] = .5f * (left[i] + right[i]);
+    else if (id == 1) x[i] = left[i];
+    else x[i] = right[i];
+  }
+}
+
+__global__ void decode_packets_kernel(DecodeArgs A) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= A.n_streams) return;
+  const float *cb1 = A.m.codebooks, *cb2 = cb1 + 1024 * 17, *cb3 = cb2 + 1024 * 17, *diff4 = cb3 + 1024 * 17;
+  float vq_mem[18];
+  for (int i = 0; i < 18; i++) vq_mem[i] = A.st.vq_mem[(size_t)s * 18 + i];
+  for (int pk = 0; pk < A.n_packets; pk++) {
+    const unsigned char *buf = A.packets + ((size_t)s * A.n_packets + pk) * 8;
+    float *F = A.features + ((size_t)s * A.n_packets + pk) * 4 * 36;
+    int bp = 0;
+    const int c0_id = bits_take(buf, bp, 7);
+    const int main_pitch = bits_take(buf, bp, 6);
+    int modulation = bits_take(buf, bp, 3);
+    const int corr_id = bits_take(buf, bp, 2);
+    int vq_end[3];
+    vq_end[0] = bits_take(buf, bp, 10); vq_end[1] = bits_take(buf, bp, 10); vq_end[2] = bits_take(buf, bp, 10);
+    int vq_mid = bits_take(buf, bp, 13);
+    int interp_id = bits_take(buf, bp, 3);
+    for (int i = 0; i < 4 * 36; i++) F[i] = 0.f;
+    int voiced = 1;
+    modulation -= 4;
+    if (modulation == -4) { voiced = 0; modulation = 0; }
+    const float frame_corr = voiced ? 0.3875f + .175f * (float)corr_id : 0.0375f + .075f * (float)corr_id;
+    for (int sub = 0; sub < 4; sub++) {
+      float p = (float)(pow((double)2.f, main_pitch / 21.) * 32);
+      p *= 1.f + (float)modulation / 16.f / 7.f * (float)(2 * sub - 3);
+      p = 33 > p ? 33 : p;
+      p = 255 < p ? 255 : p;
+      F[sub * 36 + 18] = .02f * (p - 100.f);
+      F[sub * 36 + 19] = frame_corr - .5f;
+    }
+    float *F0 = F, *F1 = F + 36, *F2 = F + 72, *F3 = F + 108;
+    F3[0] = (float)(c0_id - 64) / 4.f;
+    for (int i = 0; i < 17; i++) F3[i + 1] = cb1[vq_end[0] * 17 + i] + cb2[vq_end[1] * 17 + i] + cb3[vq_end[2] * 17 + i];
+    float sign = 1;
+    if (vq_mid >= 4096) { vq_mid -= 4096; sign = -1; }
+    for (int i = 0; i < 18; i++) F1[i] = sign * diff4[vq_mid * 18 + i];
+    if ((vq_mid & 3) < 2) {
+      for (int i = 0; i < 18; i++) F1[i] += .5f * (vq_mem[i] + F3[i]);
+    } else if ((vq_mid & 3) == 2) {
+      for (int i = 0; i < 18; i++) F1[i] += vq_mem[i];
+    } else {
+      for (int i = 0; i < 18; i++) F1[i] += F3[i];
+    }
+    interp_id += (interp_id >= 7);
+    single_interp_dev(F0, vq_mem, F1, interp_id / 3);
+    single_interp_dev(F2, F1, F3, interp_id % 3);
+    for (int i = 0; i < 18; i++) vq_mem[i] = F3[i];
+  }
+  for (int i = 0; i < 18; i++) A.st.vq_mem[(size_t)s * 18 + i] = vq_mem[i];
+}
+
+}  // namespace
+
+cudaError_t launch_frame_network(const FrameArgs &a, cudaStream_t s, int *n_launches) {
+  const int B = a.n_streams, F = a.n_frames;
+  const int rows = B * F;
+  frame_inputs_kernel<<<B * (F + 2), 128, 0, s>>>(a);
+  conv1_kernel<<<(rows + kRowsPerBlock - 1) / kRowsPerBlock, kFT, 0, s>>>(a);
+  cond_kernel<<<(rows + kRowsPerBlock - 1) / kRowsPerBlock, kFT, 0, s>>>(a);
+  lpc_kernel<<<(rows + 63) / 64, 64, 0, s>>>(a);
+  frame_finalize_kernel<<<(B + 127) / 128, 128, 0, s>>>(a);
+  if (n_launches) *n_launches += 5;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_decode_packets(const DecodeArgs &a, cudaStream_t s, int *n_launches) {
+  decode_packets_kernel<<<(a.n_streams + 63) / 64, 64, 0, s>>>(a);
+  if (n_launches) *n_launches += 1;
+  return cudaGetLastError();
+}
+
+}  // namespace lpcb

@@ -1,0 +1,314 @@
+// Weight-blob loader: validates a "DNNw" blob with the rules of the reference parser
+// (src/parse_lpcnet_weights.c:36-113), looks the LPCNet arrays up by name and exact size
+// (the call list of the generated nnet_data.c, training_tf2/dump_lpcnet.py),
+// re-tiles the block-sparse int8 matrices into mma.sync B-fragment order and uploads
+// everything to the GPU in one allocation.
+#include <math.h>
+#include <string.h>
+
+#include <map>
+
+#include "engine.h"
+
+namespace lpcb {
+
+namespace {
+
+struct Arr {
+  const unsigned char *data;
+  int size;
+};
+
+// parse_record / parse_weights (parse_lpcnet_weights.c:36-77): 64-byte head
+// {char[4], int version, int type, int size, int block_size, char name[44]}.
+bool parse_records(const unsigned char *d, int len, std::map<std::string, Arr> &out, std::string &err) {
+  while (len > 0) {
+    if (len < 64) { err = "truncated record head"; return false; }
+    int32_t size, block;
+    memcpy(&size, d + 12, 4);
+    memcpy(&block, d + 16, 4);
+    const char *name = reinterpret_cast<const char *>(d) + 20;
+    if (block < size || block > len - 64 || name[43] != 0 || size <= 0) {
+      err = "malformed weight record";
+      return false;
+    }
+    if (!out.count(name)) out[name] = Arr{d + 64, size};  // first match wins (find_array_entry)
+    d += 64 + block;
+    len -= 64 + block;
+  }
+  return true;
+}
+
+struct Builder {
+  std::vector<unsigned char> buf;
+  size_t add(const void *p, size_t bytes) {
+    size_t off = (buf.size() + 255) & ~size_t(255);
+    buf.resize(off + bytes);
+    if (bytes) memcpy(buf.data() + off, p, bytes);
+    return off;
+  }
+};
+
+// find_idx_check (parse_lpcnet_weights.c:90-113) + re-tiling.  `idx` NULL means a dense
+// dotp-layout matrix [rows/8][cols/4][8][4] (dump_lpcnet.py:56-60).
+bool pack_sparse(PackedSparse &ps, const int32_t *idx, int idx_len, const int8_t *w, int w_bytes, int rows,
+                 int cols, std::string &err, const char *what) {
+  ps.n_groups = rows / 8;
+  ps.chunk_start.assign(ps.n_groups + 1, 0);
+  std::vector<std::vector<int>> gpos(ps.n_groups);
+  int total = 0;
+  if (idx) {
+    int remain = idx_len, grp = 0;
+    const int32_t *p = idx;
+    while (remain > 0) {
+      int nb = *p++;
+      if (nb < 0 || remain < nb + 1 || grp >= ps.n_groups) { err = std::string(what) + ": bad block index stream"; return false; }
+      for (int k = 0; k < nb; k++) {
+        int pos = *p++;
+        if (pos + 3 >= cols || (pos & 3) || pos < 0) { err = std::string(what) + ": bad block position"; return false; }
+        gpos[grp].push_back(pos);
+      }
+      remain -= nb + 1;
+      total += nb;
+      grp++;
+    }
+    if (grp != ps.n_groups) { err = std::string(what) + ": block index stream does not cover all rows"; return false; }
+  } else {
+    for (int g = 0; g < ps.n_groups; g++)
+      for (int pos = 0; pos < cols; pos += 4) gpos[g].push_back(pos);
+    total = ps.n_groups * (cols / 4);
+  }
+  if (w_bytes != 32 * total) { err = std::string(what) + ": weight array size does not match the block count"; return false; }
+  // The AVX2 kernel sums adjacent input pairs in a saturating s16 (vpmaddubsw,
+  // src/vec_avx.h:814-818).  Integer tensor-core accumulation cannot saturate, so bit-exactness
+  // needs 255*(|q0|+|q1|) <= 32767 for every pair -- guaranteed by the training-time WeightClip
+  // (training_tf2/lpcnet.py:287-309).  Refuse blobs that violate it.
+  for (int i = 0; i + 1 < w_bytes; i += 2) {
+    int s = abs((int)w[i]) + abs((int)w[i + 1]);
+    if (255 * s > 32767) { err = std::string(what) + ": int8 pair would saturate vpmaddubsw; not representable bit-exactly"; return false; }
+  }
+  ps.n_blocks = total;
+  int nchunks = 0;
+  for (int g = 0; g < ps.n_groups; g++) {
+    ps.chunk_start[g] = nchunks;
+    nchunks += ((int)gpos[g].size() + 7) / 8;
+  }
+  ps.chunk_start[ps.n_groups] = nchunks;
+  ps.n_chunks = nchunks;
+  ps.pos.assign((size_t)nchunks * 8, 0);
+  ps.w.assign((size_t)nchunks * 64, 0);
+  const int8_t *wp = w;
+  for (int g = 0; g < ps.n_groups; g++) {
+    int nb = (int)gpos[g].size();
+    for (int b = 0; b < nb; b++) {
+      int c = ps.chunk_start[g] + b / 8, slot = b % 8;
+      ps.pos[(size_t)c * 8 + slot] = (uint8_t)(gpos[g][b] / 4);
+      // B fragment of mma.m16n8k32: register slot/4, lane = row*4 + slot%4 holds the four
+      // input weights of output row `row` of block `slot`.
+      for (int r = 0; r < 8; r++) {
+        uint32_t word;
+        memcpy(&word, wp + r * 4, 4);
+        ps.w[(size_t)c * 64 + (slot / 4) * 32 + r * 4 + (slot % 4)] = word;
+      }
+      wp += 32;
+    }
+  }
+  return true;
+}
+
+}  // namespace
+
+// Model of the Intel `rcpps` estimate: entry i = 1/midpoint of bucket i rounded to 2^-13
+// (measured; oracle/orc_prim.c).
+void default_rcp_table(uint32_t *tab) {
+  for (int i = 0; i < 2048; i++) {
+    uint32_t k = 4097u + 2u * (uint32_t)i;
+    uint32_t q = (uint32_t)(((1ull << 26) / k + 1) >> 1);
+    tab[i] = 0x3f000000u + ((q - 4096u) << 11);
+  }
+}
+
+void free_model(Model &m) {
+  if (m.dev_blob) cudaFree(m.dev_blob);
+  m.dev_blob = nullptr;
+}
+
+bool load_model(Model &m, const unsigned char *blob, int len, int features_delay, float lpc_gamma,
+                const uint32_t *rcp_tab, std::string &err) {
+  if (features_delay < 0 || features_delay > kMaxDelay) { err = "features_delay must be 0..2"; return false; }
+  if (!blob || len <= 0) { err = "empty blob"; return false; }
+  std::map<std::string, Arr> A;
+  if (!parse_records(blob, len, A, err)) return false;
+  // find_array_check (parse_lpcnet_weights.c:84-88): name and exact byte size.
+  auto need = [&](const char *name, int bytes) -> const unsigned char * {
+    auto it = A.find(name);
+    if (it == A.end()) { if (err.empty()) err = std::string("missing array ") + name; return nullptr; }
+    if (it->second.size != bytes) { if (err.empty()) err = std::string("wrong size for array ") + name; return nullptr; }
+    return it->second.data;
+  };
+  Builder B;
+  struct Fix { size_t off; const void **dst; };
+  std::vector<Fix> fixes;
+  auto put = [&](const void **dst, const void *src, size_t bytes) { fixes.push_back(Fix{B.add(src, bytes), dst}); };
+  auto put_f = [&](const float **dst, const char *name, int n) -> bool {
+    const unsigned char *p = need(name, n * 4);
+    if (!p) return false;
+    put(reinterpret_cast<const void **>(dst), p, (size_t)n * 4);
+    return true;
+  };
+  DevModel &d = m.d;
+  bool ok = true;
+  ok &= put_f(&d.e_sig, "gru_a_embed_sig_weights", 256 * kRowsA);
+  ok &= put_f(&d.e_pred, "gru_a_embed_pred_weights", 256 * kRowsA);
+  ok &= put_f(&d.e_exc, "gru_a_embed_exc_weights", 256 * kRowsA);
+  ok &= put_f(&d.a_feat_b, "gru_a_dense_feature_bias", kRowsA);
+  ok &= put_f(&d.a_feat_w, "gru_a_dense_feature_weights", kC * kRowsA);
+  ok &= put_f(&d.b_feat_b, "gru_b_dense_feature_bias", kRowsB);
+  ok &= put_f(&d.b_feat_w, "gru_b_dense_feature_weights", kC * kRowsB);
+  ok &= put_f(&d.conv1_b, "feature_conv1_bias", kC);
+  ok &= put_f(&d.conv1_w, "feature_conv1_weights", 3 * kConvIn * kC);
+  ok &= put_f(&d.conv2_b, "feature_conv2_bias", kC);
+  ok &= put_f(&d.conv2_w, "feature_conv2_weights", 3 * kC * kC);
+  ok &= put_f(&d.embed_pitch, "embed_pitch_weights", 256 * kPitchEmb);
+  ok &= need("embed_sig_weights", 256 * 128 * 4) != nullptr;  // loaded by the reference, unused at inference
+  ok &= put_f(&d.dense1_b, "feature_dense1_bias", kC);
+  ok &= put_f(&d.dense1_w, "feature_dense1_weights", kC * kC);
+  ok &= put_f(&d.dense2_b, "feature_dense2_bias", kC);
+  ok &= put_f(&d.dense2_w, "feature_dense2_weights", kC * kC);
+  ok &= put_f(&d.fc_bias, "dual_fc_bias", 2 * 256);
+  ok &= put_f(&d.fc_w, "dual_fc_weights", 256 * 2 * kNB);
+  ok &= put_f(&d.fc_factor, "dual_fc_factor", 2 * 256);
+  ok &= put_f(&d.a_diag, "sparse_gru_a_recurrent_weights_diag", kRowsA);
+  ok &= put_f(&d.b_subias, "gru_b_subias", 2 * kRowsB);
+  ok &= need("gru_b_bias", 2 * kRowsB * 4) != nullptr;
+  ok &= need("sparse_gru_a_bias", 2 * kRowsA * 4) != nullptr;
+  const unsigned char *sub_a = need("sparse_gru_a_subias", 2 * kRowsA * 4);
+  ok &= sub_a != nullptr;
+  if (!ok) return false;
+  put(reinterpret_cast<const void **>(&d.a_subias_rec), sub_a + kRowsA * 4, kRowsA * 4);
+
+  // int8 matrices
+  PackedSparse pa, pb, pr;
+  {
+    auto ia = A.find("sparse_gru_a_recurrent_weights_idx"), wa = A.find("sparse_gru_a_recurrent_weights");
+    if (ia == A.end() || wa == A.end()) { err = "missing GRU-A recurrent arrays"; return false; }
+    if (!pack_sparse(pa, reinterpret_cast<const int32_t *>(ia->second.data), ia->second.size / 4,
+                     reinterpret_cast<const int8_t *>(wa->second.data), wa->second.size, kRowsA, kN, err, "sparse_gru_a"))
+      return false;
+    auto ib = A.find("gru_b_weights_idx"), wb = A.find("gru_b_weights");
+    if (ib == A.end() || wb == A.end()) { err = "missing GRU-B input arrays"; return false; }
+    if (!pack_sparse(pb, reinterpret_cast<const int32_t *>(ib->second.data), ib->second.size / 4,
+                     reinterpret_cast<const int8_t *>(wb->second.data), wb->second.size, kRowsB, kN, err, "gru_b"))
+      return false;
+    const unsigned char *wr = need("gru_b_recurrent_weights", kRowsB * kNB);
+    if (!wr) return false;
+    if (!pack_sparse(pr, nullptr, 0, reinterpret_cast<const int8_t *>(wr), kRowsB * kNB, kRowsB, kNB, err, "gru_b_recurrent"))
+      return false;
+  }
+  m.nblocks_a = pa.n_blocks;
+  m.nblocks_b = pb.n_blocks;
+  auto put_sparse = [&](DevSparse &ds, const PackedSparse &ps) {
+    ds.n_groups = ps.n_groups;
+    ds.n_chunks = ps.n_chunks;
+    put(reinterpret_cast<const void **>(&ds.chunk_start), ps.chunk_start.data(), ps.chunk_start.size() * 4);
+    put(reinterpret_cast<const void **>(&ds.pos), ps.pos.data(), ps.pos.size());
+    put(reinterpret_cast<const void **>(&ds.w), ps.w.data(), ps.w.size() * 4);
+  };
+  put_sparse(d.a_rec, pa);
+  put_sparse(d.b_in, pb);
+  put_sparse(d.b_rec, pr);
+
+  // tables
+  std::vector<uint32_t> rcp(2048);
+  if (rcp_tab) memcpy(rcp.data(), rcp_tab, 2048 * 4);
+  else default_rcp_table(rcp.data());
+  put(reinterpret_cast<const void **>(&d.rcp_tab), rcp.data(), 2048 * 4);
+  float u2l[256], logit[256];
+  for (int i = 0; i < 256; i++) {
+    // ulaw2lin (src/common.h:37-45): double exp, then float
+    float u = (float)i - 128.f;
+    float s = u >= 0.f ? 1.f : -1.f;
+    float scale_1 = 32768.f / 255.f;
+    u = fabsf(u);
+    u2l[i] = (float)((double)(s * scale_1) * (exp((double)u / 128. * (double)5.5451774445f) - 1));
+    // sampling_logit_table (src/lpcnet.c:188-191)
+    float prob = .025f + .95f * (float)i / 255.f;
+    logit[i] = (float)(-log((double)(((float)1 - prob) / prob)));
+  }
+  put(reinterpret_cast<const void **>(&d.ulaw2lin_tab), u2l, sizeof(u2l));
+  put(reinterpret_cast<const void **>(&d.logit_tab), logit, sizeof(logit));
+  // kiss_fft tables for nfft = 320 (src/kiss_fft.c:409-424, 312-345; factors {5,64,4,16,4,4,4,1}
+  // src/lpcnet_tables.c:197-205) and the 18x18 DCT (src/dump_lpcnet_tables.c:83-99).
+  {
+    std::vector<float> tw(640);
+    for (int i = 0; i < 320; i++) {
+      const double pi = 3.14159265358979323846264338327;
+      double phase = (-2 * pi / 320) * i;
+      tw[2 * i] = (float)cos(phase);
+      tw[2 * i + 1] = (float)sin(phase);
+    }
+    put(reinterpret_cast<const void **>(&d.fft_tw), tw.data(), tw.size() * 4);
+    static const int factors[8] = {5, 64, 4, 16, 4, 4, 4, 1};
+    std::vector<int16_t> br(320);
+    struct Rec {
+      static void go(int Fout, int16_t *f, int fstride, const int *fac) {
+        int p = *fac++, mm = *fac++;
+        if (mm == 1) {
+          for (int j = 0; j < p; j++) { *f = (int16_t)(Fout + j); f += fstride; }
+        } else {
+          for (int j = 0; j < p; j++) { go(Fout, f, fstride * p, fac); f += fstride; Fout += mm; }
+        }
+      }
+    };
+    Rec::go(0, br.data(), 1, factors);
+    put(reinterpret_cast<const void **>(&d.fft_bitrev), br.data(), br.size() * 2);
+    std::vector<float> dct(18 * 18);
+    for (int i = 0; i < 18; i++)
+      for (int j = 0; j < 18; j++) {
+        float v = (float)cos((i + .5) * j * M_PI / 18);
+        if (j == 0) v = (float)((double)v * sqrt(.5));
+        dct[i * 18 + j] = v;
+      }
+    put(reinterpret_cast<const void **>(&d.dct), dct.data(), dct.size() * 4);
+  }
+  // optional VQ codebooks carried in the blob under their C names (src/lpcnet_private.h:109-112)
+  d.codebooks = nullptr;
+  {
+    auto c1 = A.find("ceps_codebook1"), c2 = A.find("ceps_codebook2"), c3 = A.find("ceps_codebook3"),
+         c4 = A.find("ceps_codebook_diff4");
+    if (c1 != A.end() && c2 != A.end() && c3 != A.end() && c4 != A.end() && c1->second.size == 1024 * 17 * 4 &&
+        c2->second.size == 1024 * 17 * 4 && c3->second.size == 1024 * 17 * 4 && c4->second.size == 4096 * 18 * 4) {
+      std::vector<float> cb(3 * 1024 * 17 + 4096 * 18);
+      memcpy(cb.data(), c1->second.data, 1024 * 17 * 4);
+      memcpy(cb.data() + 1024 * 17, c2->second.data, 1024 * 17 * 4);
+      memcpy(cb.data() + 2 * 1024 * 17, c3->second.data, 1024 * 17 * 4);
+      memcpy(cb.data() + 3 * 1024 * 17, c4->second.data, 4096 * 18 * 4);
+      put(reinterpret_cast<const void **>(&d.codebooks), cb.data(), cb.size() * 4);
+      m.has_codebooks = true;
+    }
+  }
+  d.features_delay = features_delay;
+  d.lpc_gamma = lpc_gamma;
+
+  cudaError_t e = cudaMalloc(&m.dev_blob, B.buf.size());
+  if (e != cudaSuccess) { err = std::string("cudaMalloc(model): ") + cudaGetErrorString(e); return false; }
+  m.dev_bytes = B.buf.size();
+  e = cudaMemcpy(m.dev_blob, B.buf.data(), B.buf.size(), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) { err = std::string("cudaMemcpy(model): ") + cudaGetErrorString(e); free_model(m); return false; }
+  for (auto &f : fixes) *f.dst = static_cast<const unsigned char *>(m.dev_blob) + f.off;
+  return true;
+}
+
+bool install_codebooks(Model &m, const float *cb, int n, std::string &err) {
+  const int want = 3 * 1024 * 17 + 4096 * 18;
+  if (n != want) { err = "codebooks: expected 3*1024*17 + 4096*18 floats"; return false; }
+  float *dcb = nullptr;
+  cudaError_t e = cudaMalloc(&dcb, (size_t)want * 4);
+  if (e == cudaSuccess) e = cudaMemcpy(dcb, cb, (size_t)want * 4, cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) { err = std::string("codebooks: ") + cudaGetErrorString(e); return false; }
+  m.d.codebooks = dcb;  // lives until process exit or the next install (small; intentionally not freed with the model blob)
+  m.has_codebooks = true;
+  return true;
+}
+
+}  // namespace lpcb

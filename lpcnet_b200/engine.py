@@ -1,0 +1,305 @@
+"""ctypes host mirror of include/lpcnet_b200.h (the C-ABI of liblpcnet_b200.so).
+
+`Batch` mirrors the batched multi-stream API; `Synth` / `Decoder` mirror the reference's
+single-stream `lpcnet_create / lpcnet_load_model / lpcnet_synthesize / lpcnet_decode` calls
+(include/lpcnet.h:160-188, 67-96) with the same argument meaning and error behaviour.
+
+There is no CPU fallback: if the library is missing, or no CUDA device is present, the calls
+raise.  Nothing here imports the test oracle.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "liblpcnet_b200.so")
+
+FRAME_SIZE = 160
+NB_FEATURES = 20
+NB_TOTAL_FEATURES = 36
+
+TRACE_DTYPE = np.dtype([("exc", "<i4"), ("u_sig", "<i4"), ("u_pred", "<i4"), ("rng_z", "<u4"),
+                        ("rng_w", "<u4"), ("xa_hash", "<u4"), ("xb_hash", "<u4"), ("pcm", "<i4")])
+
+STATE_DTYPE = np.dtype([("conv1_state", "<f4", 168), ("conv2_state", "<f4", 256),
+                        ("gru_a_state", "<f4", 384), ("gru_b_state", "<f4", 16),
+                        ("last_sig", "<f4", 16), ("lpc", "<f4", 16), ("old_lpc", "<f4", (2, 16)),
+                        ("gru_a_condition", "<f4", 1152), ("gru_b_condition", "<f4", 48),
+                        ("deemph_mem", "<f4"), ("last_exc", "<i4"), ("frame_count", "<i4"),
+                        ("rng", "<u4", 4)])
+
+# every symbol include/lpcnet_b200.h declares (checked by tests/test_abi.py)
+EXPORTED_SYMBOLS = [
+    "lpcnet_get_size", "lpcnet_init", "lpcnet_create", "lpcnet_destroy", "lpcnet_reset",
+    "lpcnet_load_model", "lpcnet_synthesize", "lpcnet_decoder_get_size", "lpcnet_decoder_init",
+    "lpcnet_decoder_create", "lpcnet_decoder_destroy", "lpcnet_decoder_load_model", "lpcnet_decode",
+    "lpcnet_batch_create", "lpcnet_batch_destroy", "lpcnet_batch_n_streams", "lpcnet_batch_reset",
+    "lpcnet_batch_set_seed", "lpcnet_batch_set_cuda_stream", "lpcnet_batch_set_tile",
+    "lpcnet_batch_synthesize", "lpcnet_batch_synthesize_device", "lpcnet_batch_frame_network",
+    "lpcnet_batch_decode", "lpcnet_batch_set_codebooks", "lpcnet_batch_get_state",
+    "lpcnet_batch_set_state", "lpcnet_batch_sync", "lpcnet_batch_nblocks", "lpcnet_batch_launch_count",
+    "lpcnet_b200_set_rcp_table", "lpcnet_b200_default_rcp_table", "lpcnet_b200_set_model_constants",
+    "lpcnet_b200_last_error", "lpcnet_b200_device_count",
+]
+
+_lib = None
+
+
+class LPCNetError(RuntimeError):
+    pass
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def load_library() -> C.CDLL:
+    """dlopen liblpcnet_b200.so (built in-tree by lpcnet_b200/build.py).  Fails loudly."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise LPCNetError(f"{LIB_PATH} is missing: run `python -m lpcnet_b200.build` "
+                          "(the engine has no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    vp, ci, cf = C.c_void_p, C.c_int, C.c_float
+    L.lpcnet_b200_last_error.restype = C.c_char_p
+    L.lpcnet_batch_create.restype = vp
+    L.lpcnet_batch_create.argtypes = [vp, ci, ci, ci, ci, cf]
+    L.lpcnet_batch_destroy.argtypes = [vp]
+    L.lpcnet_batch_n_streams.argtypes = [vp]
+    L.lpcnet_batch_reset.argtypes = [vp, ci]
+    L.lpcnet_batch_set_seed.argtypes = [vp, ci, C.c_char_p, ci]
+    L.lpcnet_batch_set_cuda_stream.argtypes = [vp, vp]
+    L.lpcnet_batch_set_tile.argtypes = [vp, ci]
+    L.lpcnet_batch_synthesize.argtypes = [vp, vp, ci, ci, vp, vp, vp, vp]
+    L.lpcnet_batch_synthesize_device.argtypes = [vp, vp, ci, ci, ci, vp, vp, vp, vp]
+    L.lpcnet_batch_frame_network.argtypes = [vp, vp, ci, ci, vp, vp, vp]
+    L.lpcnet_batch_decode.argtypes = [vp, vp, ci, vp, vp]
+    L.lpcnet_batch_set_codebooks.argtypes = [vp, vp, ci]
+    L.lpcnet_batch_get_state.argtypes = [vp, ci, vp]
+    L.lpcnet_batch_set_state.argtypes = [vp, ci, vp]
+    L.lpcnet_batch_sync.argtypes = [vp]
+    L.lpcnet_batch_nblocks.argtypes = [vp, ci]
+    L.lpcnet_batch_launch_count.restype = C.c_longlong
+    L.lpcnet_batch_launch_count.argtypes = [vp]
+    L.lpcnet_b200_set_rcp_table.argtypes = [vp]
+    L.lpcnet_b200_default_rcp_table.argtypes = [vp]
+    L.lpcnet_b200_set_model_constants.argtypes = [ci, cf]
+    L.lpcnet_create.restype = vp
+    L.lpcnet_destroy.argtypes = [vp]
+    L.lpcnet_reset.argtypes = [vp]
+    L.lpcnet_load_model.argtypes = [vp, vp, ci]
+    L.lpcnet_synthesize.argtypes = [vp, vp, vp, ci]
+    L.lpcnet_synthesize.restype = None
+    L.lpcnet_decoder_create.restype = vp
+    L.lpcnet_decoder_destroy.argtypes = [vp]
+    L.lpcnet_decoder_load_model.argtypes = [vp, vp, ci]
+    L.lpcnet_decode.argtypes = [vp, vp, vp]
+    _lib = L
+    return L
+
+
+def last_error() -> str:
+    return load_library().lpcnet_b200_last_error().decode()
+
+
+def device_count() -> int:
+    return load_library().lpcnet_b200_device_count()
+
+
+def default_rcp_table() -> np.ndarray:
+    t = np.zeros(2048, np.uint32)
+    load_library().lpcnet_b200_default_rcp_table(_p(t))
+    return t
+
+
+def set_rcp_table(table) -> None:
+    L = load_library()
+    if table is None:
+        L.lpcnet_b200_set_rcp_table(None)
+    else:
+        t = np.ascontiguousarray(table, np.uint32)
+        assert t.size == 2048
+        L.lpcnet_b200_set_rcp_table(_p(t))
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise LPCNetError(f"{what}: {last_error()}")
+
+
+class Batch:
+    """n_streams independent LPCNet synthesis streams advanced in lock step on one GPU."""
+
+    def __init__(self, blob: bytes, n_streams: int, device: int = -1, features_delay: int = 2,
+                 lpc_gamma: float = 1.0):
+        self.L = load_library()
+        self._blob = np.frombuffer(blob, np.uint8)
+        self.h = self.L.lpcnet_batch_create(_p(self._blob), len(blob), n_streams, device, features_delay,
+                                            C.c_float(lpc_gamma))
+        if not self.h:
+            raise LPCNetError(f"lpcnet_batch_create: {last_error()}")
+        self.n_streams = n_streams
+        self.features_delay = features_delay
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.lpcnet_batch_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def reset(self, stream: int = -1):
+        _check(self.L.lpcnet_batch_reset(self.h, stream), "lpcnet_batch_reset")
+
+    def set_seed(self, stream: int, seed: bytes):
+        _check(self.L.lpcnet_batch_set_seed(self.h, stream, seed, len(seed)), "lpcnet_batch_set_seed")
+
+    def set_tile(self, streams_per_cta: int):
+        _check(self.L.lpcnet_batch_set_tile(self.h, streams_per_cta), "lpcnet_batch_set_tile")
+
+    def set_cuda_stream(self, handle: int):
+        _check(self.L.lpcnet_batch_set_cuda_stream(self.h, C.c_void_p(handle)), "lpcnet_batch_set_cuda_stream")
+
+    def sync(self):
+        _check(self.L.lpcnet_batch_sync(self.h), "lpcnet_batch_sync")
+
+    @property
+    def nblocks_a(self):
+        return self.L.lpcnet_batch_nblocks(self.h, 0)
+
+    @property
+    def nblocks_b(self):
+        return self.L.lpcnet_batch_nblocks(self.h, 1)
+
+    @property
+    def launch_count(self):
+        return int(self.L.lpcnet_batch_launch_count(self.h))
+
+    def synthesize(self, features, forced=None, trace=False, logits=False, pcm_out=None):
+        """features: [n_streams][n_frames][>=20] float32 (host).  Returns (pcm, trace, logits)."""
+        f = np.ascontiguousarray(features, np.float32)
+        assert f.ndim == 3 and f.shape[0] == self.n_streams, f.shape
+        n_frames, stride = f.shape[1], f.shape[2]
+        T = n_frames * FRAME_SIZE
+        pcm = pcm_out if pcm_out is not None else np.zeros((self.n_streams, T), np.int16)
+        fo = None
+        if forced is not None:
+            fo = np.ascontiguousarray(forced, np.int16)
+            assert fo.shape == (self.n_streams, T)
+        tr = np.zeros((self.n_streams, T), TRACE_DTYPE) if trace else None
+        lg = np.zeros((self.n_streams, T, 256), np.float32) if logits else None
+        _check(self.L.lpcnet_batch_synthesize(self.h, _p(f), stride, n_frames, _p(pcm), _p(fo), _p(tr), _p(lg)),
+               "lpcnet_batch_synthesize")
+        return pcm, tr, lg
+
+    def synthesize_device(self, d_features: int, stride: int, n_frames: int, d_pcm: int,
+                          samples_per_frame: int = FRAME_SIZE, d_forced: int = 0):
+        """Device-pointer entry point (asynchronous on the batch's CUDA stream)."""
+        _check(self.L.lpcnet_batch_synthesize_device(self.h, C.c_void_p(d_features), stride, n_frames,
+                                                     samples_per_frame, C.c_void_p(d_pcm),
+                                                     C.c_void_p(d_forced) if d_forced else None, None, None),
+               "lpcnet_batch_synthesize_device")
+
+    def frame_network(self, features):
+        f = np.ascontiguousarray(features, np.float32)
+        n_frames, stride = f.shape[1], f.shape[2]
+        ga = np.zeros((self.n_streams, n_frames, 1152), np.float32)
+        gb = np.zeros((self.n_streams, n_frames, 48), np.float32)
+        lpc = np.zeros((self.n_streams, n_frames, 16), np.float32)
+        _check(self.L.lpcnet_batch_frame_network(self.h, _p(f), stride, n_frames, _p(ga), _p(gb), _p(lpc)),
+               "lpcnet_batch_frame_network")
+        return ga, gb, lpc
+
+    def set_codebooks(self, codebooks):
+        cb = np.ascontiguousarray(codebooks, np.float32).reshape(-1)
+        _check(self.L.lpcnet_batch_set_codebooks(self.h, _p(cb), cb.size), "lpcnet_batch_set_codebooks")
+
+    def decode(self, packets, want_features=False):
+        """packets: [n_streams][n_packets][8] uint8.  Returns (pcm [n][n_packets*640], features)."""
+        pk = np.ascontiguousarray(packets, np.uint8)
+        assert pk.ndim == 3 and pk.shape[0] == self.n_streams and pk.shape[2] == 8
+        n_packets = pk.shape[1]
+        pcm = np.zeros((self.n_streams, n_packets * 640), np.int16)
+        feats = np.zeros((self.n_streams, n_packets * 4, 36), np.float32) if want_features else None
+        _check(self.L.lpcnet_batch_decode(self.h, _p(pk), n_packets, _p(pcm), _p(feats)), "lpcnet_batch_decode")
+        return pcm, feats
+
+    def get_state(self, stream: int):
+        s = np.zeros(1, STATE_DTYPE)
+        _check(self.L.lpcnet_batch_get_state(self.h, stream, _p(s)), "lpcnet_batch_get_state")
+        return s[0]
+
+    def set_state(self, stream: int, state):
+        s = np.zeros(1, STATE_DTYPE)
+        s[0] = state
+        _check(self.L.lpcnet_batch_set_state(self.h, stream, _p(s)), "lpcnet_batch_set_state")
+
+
+class Synth:
+    """The reference's single-stream API: lpcnet_create + lpcnet_load_model + lpcnet_synthesize."""
+
+    def __init__(self, blob: bytes):
+        self.L = load_library()
+        self.h = self.L.lpcnet_create()
+        self._blob = np.frombuffer(blob, np.uint8)
+        if self.L.lpcnet_load_model(self.h, _p(self._blob), len(blob)) != 0:
+            err = last_error()
+            self.L.lpcnet_destroy(self.h)
+            self.h = None
+            raise LPCNetError(f"lpcnet_load_model: {err}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.lpcnet_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def reset(self):
+        self.L.lpcnet_reset(self.h)
+
+    def synthesize(self, features, n: int = FRAME_SIZE):
+        f = np.ascontiguousarray(features, np.float32)
+        assert f.size >= NB_FEATURES
+        out = np.zeros(n, np.int16)
+        self.L.lpcnet_synthesize(self.h, _p(f), _p(out), n)
+        err = last_error()
+        if err:
+            raise LPCNetError(f"lpcnet_synthesize: {err}")
+        return out
+
+
+class Decoder:
+    """lpcnet_decoder_create + lpcnet_decode (include/lpcnet.h:67-96)."""
+
+    def __init__(self, blob: bytes):
+        self.L = load_library()
+        self.h = self.L.lpcnet_decoder_create()
+        self._blob = np.frombuffer(blob, np.uint8)
+        if self.L.lpcnet_decoder_load_model(self.h, _p(self._blob), len(blob)) != 0:
+            err = last_error()
+            self.L.lpcnet_decoder_destroy(self.h)
+            self.h = None
+            raise LPCNetError(f"lpcnet_decoder_load_model: {err}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.lpcnet_decoder_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def decode(self, packet: bytes):
+        assert len(packet) == 8
+        pcm = np.zeros(640, np.int16)
+        buf = np.frombuffer(packet, np.uint8)
+        _check(self.L.lpcnet_decode(self.h, _p(buf), _p(pcm)), "lpcnet_decode")
+        return pcm
