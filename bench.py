@@ -1,0 +1,395 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json's metric on BASELINE.json's config.
+
+A "step" is one pass of the hot path over one batch: `--streams` (default 1024) independent
+16 kHz streams x `--seconds` (default 10 s = 1000 frames) of synthetic features through the
+batched synthesis engine (frame network + per-sample network), random-init weights in the
+reference's blob layout.  That is BASELINE.json configs[1] ("batched -synthesis, 1024 streams
+x 10 s on 1 B200").  Under torchrun (N>1) every rank runs the same number of streams on its own
+GPU (weak scaling, no data-path collective: streams are independent).
+
+  value : aggregate samples/s, inputs resident in HBM (device-pointer entry point)
+  e2e   : the same through the host-buffer C-ABI call (pinned host features in, PCM out,
+          copies inside the timed region)
+  roofline / cpu_baseline / clocks / gpu_launches: see DESIGN.md "Measurement".
+
+`--impl reference` times the reference's own CPU implementation (oracle/_ref/lpcnet_demo_*,
+the unmodified sources built with the README's -Ofast flags) on all host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import shutil
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+FRAME = 160
+METRIC = "aggregate 16 kHz samples/sec"
+UNIT = "samples/s"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"],
+                "bf16_tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "src": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "src": "fallback"}
+
+
+# ------------------------------------------------------------------------------------------
+# CPU reference arm: the reference's own lpcnet_demo -synthesis, one process per host core
+# ------------------------------------------------------------------------------------------
+class CpuReference:
+    def __init__(self, blob_bytes: bytes, n_frames: int):
+        from lpcnet_b200 import blob
+        self.dir = tempfile.mkdtemp(prefix="lpcnet_ref_")
+        with open(os.path.join(self.dir, "weights_blob.bin"), "wb") as f:
+            f.write(blob_bytes)       # lpcnet_demo (USE_WEIGHTS_FILE) reads ./weights_blob.bin (lpcnet_demo.c:113)
+        self.cores = sorted(os.sched_getaffinity(0))
+        self.n_frames = n_frames
+        for i, _ in enumerate(self.cores):
+            blob.synthetic_features(n_frames, i).tofile(os.path.join(self.dir, f"feat{i}.f32"))
+        self.binary, self.kind = self._pick_binary()
+        self.blob_bytes = blob_bytes
+
+    def _pick_binary(self):
+        for name in ("lpcnet_demo_fast_native", "lpcnet_demo_fast_v3"):
+            p = os.path.join(ROOT, "oracle", "_ref", name)
+            if os.path.exists(p):
+                # -march=native was resolved on the build container; fall back if this host lacks the ISA
+                r = subprocess.run([p, "-synthesis", "feat0.f32", "probe.pcm"], cwd=self.dir,
+                                   stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+                if r.returncode == 0 and os.path.getsize(os.path.join(self.dir, "probe.pcm")) == self.n_frames * FRAME * 2:
+                    return p, "reference"
+        return None, "port"
+
+    def run_once(self) -> float:
+        """All cores at once, one 10 s stream each.  Returns aggregate samples/s."""
+        n = len(self.cores)
+        t0 = time.perf_counter()
+        if self.binary:
+            procs = []
+            for i, core in enumerate(self.cores):
+                cmd = [self.binary, "-synthesis", f"feat{i}.f32", f"out{i}.pcm"]
+                if shutil.which("taskset"):
+                    cmd = ["taskset", "-c", str(core)] + cmd
+                procs.append(subprocess.Popen(cmd, cwd=self.dir, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL))
+            for p in procs:
+                if p.wait() != 0:
+                    raise RuntimeError("reference lpcnet_demo failed")
+        else:
+            # the oracle port, single thread (only when oracle/_ref did not travel)
+            from lpcnet_b200 import blob
+            from oracle import orcpy
+            n = 1
+            om = orcpy.OrcModel(orcpy.OrcLib(), self.blob_bytes, 2, 1.0, None)
+            orcpy.OrcStream(om).run(blob.synthetic_features(self.n_frames, 0))
+        dt = time.perf_counter() - t0
+        return n * self.n_frames * FRAME / dt
+
+    def describe(self, n_runs):
+        n = len(self.cores) if self.binary else 1
+        what = os.path.basename(self.binary) if self.binary else "oracle port (liblpcnet_oracle.so)"
+        return (f"{n_runs} x ({n} concurrent processes, one per host core, each lpcnet_demo -synthesis of one "
+                f"{self.n_frames / 100:.0f} s stream) with {what}")
+
+    def close(self):
+        shutil.rmtree(self.dir, ignore_errors=True)
+
+
+def cpu_model():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
+# ------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.path = tempfile.mktemp(prefix="clocks_", suffix=".csv")
+        self.proc = None
+
+    def start(self):
+        if shutil.which("nvidia-smi") is None:
+            return
+        self.f = open(self.path, "w")
+        self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                                      "-lms", "200", "-i", str(self.idx)], stdout=self.f, stderr=subprocess.DEVNULL)
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        self.f.close()
+        sm, mx, reasons, power = [], [], set(), []
+        for line in open(self.path):
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2])); power.append(float(c[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
+                if v == "Active":
+                    reasons.add(name)
+        os.unlink(self.path)
+        if sm:
+            out = {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                   "power_w_max": max(power), "samples": len(sm)}
+        return out
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation on the host cores (rank 0 only)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from lpcnet_b200 import blob
+    b = blob.write_blob(blob.random_model())
+    n_frames = int(round(args.seconds * 100))
+    ref = CpuReference(b, n_frames)
+    try:
+        for _ in range(args.warmup):
+            ref.run_once()
+        t0 = time.perf_counter()
+        vals = [ref.run_once() for _ in range(args.steps)]
+        dt = time.perf_counter() - t0
+        value = statistics.mean(vals)
+        cores = len(ref.cores) if ref.binary else 1
+        line = {
+            "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8*s8->s32 + f32",
+            "data": "synthetic", "x_realtime": value / 16000.0,
+            "config": {"workload": f"lpcnet_demo -synthesis, {cores} streams x {args.seconds:g} s per step "
+                                   f"(bounded sample of batched -synthesis, {args.streams} streams x {args.seconds:g} s)",
+                       "model": "random-init, N=384 NB=16 density (0.05,0.05,0.2), reference blob layout",
+                       "cpu": cpu_model()},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": ref.kind,
+                             "sample": ref.describe(args.steps)},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        }
+        print(json.dumps(line), flush=True)
+    finally:
+        ref.close()
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    from lpcnet_b200 import blob, engine, sharding
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available() or engine.device_count() == 0:
+        raise SystemExit("bench.py: no CUDA device; the engine has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    B = args.streams                       # per GPU (weak scaling)
+    n_frames = int(round(args.seconds * 100))
+    T = n_frames * FRAME
+    stride = 36                            # the feature-file frame: 36 floats, 20 used (lpcnet_demo.c:213-215)
+    model_blob = blob.write_blob(blob.random_model())
+    lo, _ = sharding.shard_range(B * world, rank, world)
+
+    # synthetic inputs: 64 distinct feature tracks cycled over the streams, per-stream kiss99 seeds
+    tracks = np.stack([blob.synthetic_features(n_frames, k) for k in range(64)])
+    h_feat = torch.empty((B, n_frames, stride), dtype=torch.float32, pin_memory=True)
+    hf = h_feat.numpy()
+    for s in range(B):
+        hf[s] = tracks[(lo + s) % 64]
+    h_pcm = torch.empty((B, T), dtype=torch.int16, pin_memory=True)
+    d_feat = h_feat.to(dev)
+    d_pcm = torch.zeros((B, T), dtype=torch.int16, device=dev)
+
+    bt = engine.Batch(model_blob, B, device=local_rank)
+    if args.tile:
+        bt.set_tile(args.tile)
+    for s in range(B):
+        bt.set_seed(s, blob.stream_seed(lo + s))
+    # a dedicated (non-default) stream: the library and the timing events share it
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
+    bt.set_cuda_stream(stream.cuda_stream)
+
+    def step_device():
+        bt.synthesize_device(d_feat.data_ptr(), stride, n_frames, d_pcm.data_ptr())
+
+    def step_host():
+        bt.synthesize(hf, pcm_out=h_pcm.numpy())
+
+    # ---- warm-up ----
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+
+    # ---- timed: HBM-resident ----
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    bt.set_profiling(True)
+    bt.read_profile()
+    l0 = bt.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = bt.launch_count - l0
+    sample_ms, n_sample, frame_ms, n_frame = bt.read_profile()
+    bt.set_profiling(False)
+    clk = clocks.stop() if rank == 0 else None
+    nonzero = int((d_pcm[:, 320:] != 0).sum().item())
+    if nonzero == 0:
+        raise SystemExit("bench.py: output is all zeros -- the kernel did not run")
+
+    # ---- timed: end to end through the host-buffer C-ABI call ----
+    step_host()
+    barrier()
+    k_e2e = max(1, min(args.steps, 2))
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record(stream)
+    for _ in range(k_e2e):
+        step_host()
+    f1.record(stream)
+    barrier()
+    ms_e2e = f0.elapsed_time(f1)
+
+    t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = float(t[0]), float(t[1])
+    samples_per_step = B * world * T
+    value = samples_per_step * args.steps / (ms * 1e-3)
+    e2e_value = samples_per_step * k_e2e / (ms_e2e * 1e-3)
+
+    if rank == 0:
+        pk = peaks()
+        # ---- roofline of the dominant kernel (sample_kernel) ----
+        # algorithmic int8 ops per stream-sample: 2*(32*n_blk_A + 32*n_blk_B + 3*NB*NB)  
+        active_frames = n_frames - bt.features_delay
+        ops_per_sample = 2 * (32 * bt.nblocks_a + 32 * bt.nblocks_b + 3 * 16 * 16)
+        kernel_s = sample_ms * 1e-3 / max(1, n_sample)
+        samples_per_launch = B * active_frames * FRAME * args.steps / max(1, n_sample)
+        int8_tops = ops_per_sample * samples_per_launch / kernel_s / 1e12
+        int8_peak = 2.0 * pk["bf16_tflops_sustained"]        # dense int8 = 2 x dense bf16 on B200
+        # on-chip bytes the algorithm must move per stream-sample: 3 embedding rows + the conditioning row
+        gather_bytes = 4 * 1152 * 4
+        gather_gbs = gather_bytes * samples_per_launch / kernel_s / 1e9
+        try:
+            l2_peak = engine.measure_l2_gather(local_rank)
+        except Exception:
+            l2_peak = None
+        hbm_bytes_per_sample = 2.0 + (stride * 4 + (1152 + 48 + 16) * 4 * 2) / FRAME   # pcm + features + conditioning w/r
+        roofline = {"bound": "tensor", "kernel": "sample_kernel", "achieved": int8_tops, "peak": int8_peak,
+                    "unit": "TFLOP/s", "frac": int8_tops / int8_peak, "traffic": None,
+                    "peak_source": f"2 x bf16_tflops_sustained ({pk['src']})",
+                    "ops_per_stream_sample": ops_per_sample, "avg_launch_ms": kernel_s * 1e3,
+                    "launches": n_sample, "share_of_step": sample_ms / ms,
+                    "note": "int8 u8*s8->s32 tensor ops; the kernel is bound by on-chip gather bandwidth and issue "
+                            "slots, not by tensor throughput (DESIGN.md)"}
+        roof_l2 = {"bound": "l2_gather", "achieved": gather_gbs, "peak": l2_peak, "unit": "GB/s",
+                   "frac": (gather_gbs / l2_peak) if l2_peak else None,
+                   "bytes_per_stream_sample": gather_bytes,
+                   "peak_source": "lpcnet_b200_measure_l2_gather (random 4608 B rows from a 3.5 MB L2-resident table)"}
+        roof_hbm = {"bound": "hbm", "achieved": hbm_bytes_per_sample * value / world / 1e9, "peak": pk["hbm_gbs"],
+                    "unit": "GB/s", "frac": hbm_bytes_per_sample * value / world / 1e9 / pk["hbm_gbs"]}
+        # ---- CPU baseline: bounded sample of the same workload on the host cores ----
+        cpu = None
+        if not args.no_cpu_baseline:
+            ref = CpuReference(model_blob, n_frames)
+            try:
+                ref.run_once()
+                runs = 3
+                vals = [ref.run_once() for _ in range(runs)]
+                cpu = {"value": statistics.mean(vals), "unit": UNIT, "cores": len(ref.cores) if ref.binary else 1,
+                       "kind": ref.kind, "sample": ref.describe(runs), "cpu": cpu_model()}
+            finally:
+                ref.close()
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8*s8->s32 + f32", "data": "synthetic",
+            "x_realtime": value / 16000.0,
+            "step_latency_us": kernel_s * 1e6 / (active_frames * FRAME * args.steps / max(1, n_sample)),
+            "config": {"workload": f"batched -synthesis, {B} streams x {args.seconds:g} s per GPU (BASELINE configs[1])",
+                       "streams_per_gpu": B, "seconds": args.seconds, "tile_streams_per_cta": args.tile or "auto",
+                       "model": "random-init, N=384 NB=16 density (0.05,0.05,0.2), reference blob layout",
+                       "parallelism": f"streams sharded over {world} GPU(s), no collective",
+                       "l2": f"inputs larger than L2 (features {h_feat.numel() * 4 / 2**20:.0f} MiB + pcm "
+                             f"{h_pcm.numel() * 2 / 2**20:.0f} MiB per step)"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h_feat.numel() * 4 * world,
+                    "d2h_bytes_per_step": h_pcm.numel() * 2 * world, "steps": k_e2e},
+            "gpu_launches": launches, "clocks": clk,
+            "roofline": roofline, "roofline_l2": roof_l2, "roofline_hbm": roof_hbm,
+            "frame_network_share_of_step": frame_ms / ms,
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    bt.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--streams", type=int, default=1024, help="streams per GPU")
+    ap.add_argument("--seconds", type=float, default=10.0, help="audio per stream per step")
+    ap.add_argument("--tile", type=int, default=0, help="streams per CTA (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "b200":
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

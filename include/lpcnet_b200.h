@@ -165,6 +165,16 @@ LPCNET_B200_EXPORT int lpcnet_batch_nblocks(const LPCNetBatch *b, int which);
 /* Kernels launched by this batch so far (for bench.py's gpu_launches). */
 LPCNET_B200_EXPORT long long lpcnet_batch_launch_count(const LPCNetBatch *b);
 
+/* Profiling: when on, CUDA events bracket every sample-kernel launch and every frame-network
+ * launch group on the batch's stream; read_profile synchronises, returns the summed
+ * durations and counts since the last read, and clears them. */
+LPCNET_B200_EXPORT int lpcnet_batch_set_profiling(LPCNetBatch *b, int on);
+LPCNET_B200_EXPORT int lpcnet_batch_read_profile(LPCNetBatch *b, double *sample_ms, int *sample_launches,
+                                                 double *frame_ms, int *frame_groups);
+/* Micro-benchmark used for the on-chip roofline: GB/s achieved by all SMs gathering random
+ * 4608-byte rows (one embedding row) from an L2-resident 3.5 MB table with 128-bit loads. */
+LPCNET_B200_EXPORT int lpcnet_b200_measure_l2_gather(int device, double *gbytes_per_s);
+
 /* The reference's tanh/sigmoid multiply by `rcpps` (src/vec_avx.h:408,437), a CPU
  * hardware estimate that is exactly a 2048-entry table over the top 11 mantissa bits.
  * Default: the Intel table model (oracle/orc_prim.c).  A process-wide override takes the

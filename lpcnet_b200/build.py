@@ -12,7 +12,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "liblpcnet_b200.so")
-SOURCES = ["model.cu", "frame.cu", "sample.cu", "api.cu"]
+SOURCES = ["model.cu", "frame.cu", "sample.cu", "api.cu", "probe.cu"]
 HEADERS = ["engine.h", "bitexact.cuh", os.path.join("..", "..", "include", "lpcnet_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-fmad=false", "-Xcompiler", "-fPIC,-fvisibility=hidden", "-shared"]

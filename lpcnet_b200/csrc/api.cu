@@ -72,6 +72,8 @@ struct LPCNetBatch {
   cudaStream_t own_stream = nullptr;
   cudaStream_t stream = nullptr;
   long long launches = 0;
+  bool profiling = false;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_sample, ev_frame;
   // grow-only staging for the host-buffer entry points
   void *d_feat = nullptr; size_t d_feat_bytes = 0;
   void *d_pcm = nullptr; size_t d_pcm_bytes = 0;
@@ -155,7 +157,10 @@ int run_frames(LPCNetBatch *b, const float *d_features, int stride, int f0, int 
   fa.m = b->model.d; fa.st = b->st; fa.fb = b->fb; fa.n_streams = b->n_streams; fa.n_frames = F;
   fa.features = d_features; fa.feature_stride = stride; fa.frame0 = f0; fa.total_frames = total_frames;
   int nl = 0;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (b->profiling) { CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventRecord(e0, b->stream)); }
   CK(launch_frame_network(fa, b->stream, &nl));
+  if (b->profiling) { CK(cudaEventRecord(e1, b->stream)); b->ev_frame.emplace_back(e0, e1); }
   b->launches += nl;
   // keep the last frame's conditioning in the stream state (lpcnet_private.h:43-47)
   const size_t B = b->n_streams;
@@ -183,7 +188,10 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
     sa.cond_a = b->fb.cond_a; sa.cond_b = b->fb.cond_b; sa.lpc = b->fb.lpc; sa.active = b->fb.active;
     sa.pcm = d_pcm; sa.forced = d_forced; sa.trace = d_trace; sa.logits = d_logits;
     int nl = 0;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (b->profiling) { CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventRecord(e0, b->stream)); }
     CK(launch_sample_kernel(sa, tile, b->n_sms, b->stream, &nl));
+    if (b->profiling) { CK(cudaEventRecord(e1, b->stream)); b->ev_sample.emplace_back(e0, e1); }
     b->launches += nl;
   }
   return 0;
@@ -293,6 +301,37 @@ int lpcnet_batch_set_tile(LPCNetBatch *b, int t) {
   if (!b) return fail("null batch");
   if (t != 0 && t != 8 && t != 16 && t != 32 && t != 64) return fail("tile must be 0, 8, 16, 32 or 64");
   b->tile = t;
+  return 0;
+}
+
+int lpcnet_batch_set_profiling(LPCNetBatch *b, int on) {
+  if (!b) return fail("null batch");
+  b->profiling = on != 0;
+  return 0;
+}
+
+// Sums (and clears) the CUDA-event durations recorded around the sample-kernel launches and the
+// frame-network launch groups since the last read.  Synchronises the batch's stream.
+int lpcnet_batch_read_profile(LPCNetBatch *b, double *sample_ms, int *sample_launches, double *frame_ms,
+                              int *frame_groups) {
+  if (!b) return fail("null batch");
+  CK(cudaSetDevice(b->device));
+  CK(cudaStreamSynchronize(b->stream));
+  auto drain = [&](std::vector<std::pair<cudaEvent_t, cudaEvent_t>> &v, double *ms, int *n) -> int {
+    double tot = 0;
+    for (auto &p : v) {
+      float t = 0;
+      CK(cudaEventElapsedTime(&t, p.first, p.second));
+      tot += t;
+      cudaEventDestroy(p.first); cudaEventDestroy(p.second);
+    }
+    if (ms) *ms = tot;
+    if (n) *n = (int)v.size();
+    v.clear();
+    return 0;
+  };
+  if (drain(b->ev_sample, sample_ms, sample_launches)) return -1;
+  if (drain(b->ev_frame, frame_ms, frame_groups)) return -1;
   return 0;
 }
 

@@ -25,9 +25,8 @@ __device__ __forceinline__ float tanh_ref(float x, const uint32_t *__restrict__ 
   num = num * x;
   den = rcp_estimate(den, tab);
   num = num * den;
-  num = (1.f < num) ? 1.f : num;
-  num = (-1.f > num) ? -1.f : num;
-  return num;
+  // _mm256_max_ps(-1, _mm256_min_ps(1, num)); num is never NaN here, so FMNMX is equivalent
+  return fmaxf(-1.f, fminf(1.f, num));
 }
 
 // sigmoid8_approx (src/vec_avx.h:421-440)
@@ -40,9 +39,8 @@ __device__ __forceinline__ float sigmoid_ref(float x, const uint32_t *__restrict
   num = num * x;
   den = rcp_estimate(den, tab);
   num = fmaf(num, den, 0.5f);
-  num = (1.f < num) ? 1.f : num;
-  num = (0.f > num) ? 0.f : num;
-  return num;
+  // fma(.,.,0.5) is never -0, so fmaxf(0, .) equals _mm256_max_ps(0, .)
+  return fmaxf(0.f, fminf(1.f, num));
 }
 
 // log2_approx + lin2ulaw (src/common.h:18-33, 47-58)
@@ -55,6 +53,14 @@ __device__ __forceinline__ float log2_approx_ref(float x) {
   return (float)(1 + integer) + frac;
 }
 
+// (int)floor(.5 + (double)u) for |u| <= 32768 without double precision: u - floorf(u) is exact, so
+// the comparison implements round-half-up exactly (verified exhaustively over every binary32 in
+// [-32768, 32768] against the double formula; u + 0.5f alone fails for u = 0.49999997).
+__device__ __forceinline__ int round_half_up_ref(float u) {
+  const float r = floorf(u);
+  return (int)(r + ((u - r >= 0.5f) ? 1.f : 0.f));
+}
+
 __device__ __forceinline__ int lin2ulaw_ref(float x) {
   const float scale = 255.f / 32768.f;
   float s = x >= 0 ? 1.f : -1.f;
@@ -63,7 +69,7 @@ __device__ __forceinline__ int lin2ulaw_ref(float x) {
   u = 128.f + u;
   if (u < 0) u = 0;
   if (u > 255) u = 255;
-  return (int)floor(.5 + (double)u);
+  return round_half_up_ref(u);
 }
 
 // kiss99_rand (src/kiss99.c:59-81); st = {z, w, jsr, jcong}
@@ -93,16 +99,29 @@ __device__ __forceinline__ uint32_t quant_u8_ref(float x) {
   return (uint32_t)(s < 0 ? 0 : (s > 255 ? 255 : s));
 }
 
+// Hot-loop variants.  cvt.rni saturates where cvtps2dq returns 0x80000000; 0x7fffffff is not a
+// binary32 value, so it can only be the saturated result and is mapped back.  (A NaN input would
+// give 0 instead of 0x80000000; the gate arithmetic cannot produce NaN from finite weights.)
+__device__ __forceinline__ int32_t cvt_rne_fast(float x) {
+  const int32_t r = __float2int_rn(x);
+  return r == 0x7fffffff ? (int32_t)0x80000000 : r;
+}
+// For |x| < 257 the packus chain of vector_ps_to_epi8 is a plain clamp to [0,255]; GRU states are
+// convex combinations of values in [-1,1].
+__device__ __forceinline__ uint32_t quant_u8_fast(float x) {
+  return (uint32_t)min(max(__float2int_rn(fmaf(x, 127.f, 127.f)), 0), 255);
+}
+
 #define LPCB_SCALE (128.f * 127.f)
 #define LPCB_SCALE_1 (1.f / 128.f / 127.f)
 
-__device__ __forceinline__ int32_t acc_seed(float v) { return cvt_rne_ref(v * LPCB_SCALE); }
+__device__ __forceinline__ int32_t acc_seed(float v) { return cvt_rne_fast(v * LPCB_SCALE); }
 __device__ __forceinline__ float acc_out(int32_t acc) { return (float)acc * LPCB_SCALE_1; }
 
 // D += A(u8, 16x32 row) * B(s8, 32x8 col), int32 accumulate.  SASS: IMMA.16832.U8.S8
 __device__ __forceinline__ void mma_u8s8(int32_t (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
                                          uint32_t b0, uint32_t b1) {
-  asm volatile(
+  asm(
       "mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
       : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));

@@ -34,10 +34,14 @@ struct SmemLayout {
   unsigned subA, diagA, subB, rcp, u2l, logit;
   unsigned xa, xb, bst, lsig, lpc, condb, part;
   unsigned usig, upred, lexc, pred, deemph, rng, head, act;
+  unsigned fcw, fcb;   // dual_fc weights (node stride kFcStride floats) and bias|factor, when resident
   unsigned total;
 };
 
 __host__ __device__ inline int b_parts(int MT) { return MT == 1 ? 4 : (MT == 2 ? 2 : 1); }
+
+constexpr int kFcStride = 36;   // 32 weights per node padded so that 8 lanes' 16-byte reads hit disjoint banks
+__host__ __device__ inline bool fc_resident(int NS) { return NS <= 32; }
 
 __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int chBi, int chBr) {
   SmemLayout L;
@@ -56,6 +60,8 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
   L.part = take(MT * (b_parts(MT) + 1) * kRGroupsB * 128 * 4);
   L.usig = take(NS * 4); L.upred = take(NS * 4); L.lexc = take(NS * 4); L.pred = take(NS * 4);
   L.deemph = take(NS * 4); L.rng = take(4 * NS * 4); L.head = take(NS * 4); L.act = take(NS * 4);
+  L.fcw = L.fcb = 0;
+  if (fc_resident(NS)) { L.fcw = take(256 * kFcStride * 4); L.fcb = take(4 * 256 * 4); }
   L.total = o;
   return L;
 }

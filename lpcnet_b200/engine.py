@@ -41,6 +41,7 @@ EXPORTED_SYMBOLS = [
     "lpcnet_batch_synthesize", "lpcnet_batch_synthesize_device", "lpcnet_batch_frame_network",
     "lpcnet_batch_decode", "lpcnet_batch_set_codebooks", "lpcnet_batch_get_state",
     "lpcnet_batch_set_state", "lpcnet_batch_sync", "lpcnet_batch_nblocks", "lpcnet_batch_launch_count",
+    "lpcnet_batch_set_profiling", "lpcnet_batch_read_profile", "lpcnet_b200_measure_l2_gather",
     "lpcnet_b200_set_rcp_table", "lpcnet_b200_default_rcp_table", "lpcnet_b200_set_model_constants",
     "lpcnet_b200_last_error", "lpcnet_b200_device_count",
 ]
@@ -86,6 +87,9 @@ def load_library() -> C.CDLL:
     L.lpcnet_batch_nblocks.argtypes = [vp, ci]
     L.lpcnet_batch_launch_count.restype = C.c_longlong
     L.lpcnet_batch_launch_count.argtypes = [vp]
+    L.lpcnet_batch_set_profiling.argtypes = [vp, ci]
+    L.lpcnet_batch_read_profile.argtypes = [vp, vp, vp, vp, vp]
+    L.lpcnet_b200_measure_l2_gather.argtypes = [ci, vp]
     L.lpcnet_b200_set_rcp_table.argtypes = [vp]
     L.lpcnet_b200_default_rcp_table.argtypes = [vp]
     L.lpcnet_b200_set_model_constants.argtypes = [ci, cf]
@@ -125,6 +129,13 @@ def set_rcp_table(table) -> None:
         t = np.ascontiguousarray(table, np.uint32)
         assert t.size == 2048
         L.lpcnet_b200_set_rcp_table(_p(t))
+
+
+def measure_l2_gather(device: int = 0) -> float:
+    v = C.c_double(0)
+    if load_library().lpcnet_b200_measure_l2_gather(device, C.byref(v)) != 0:
+        raise LPCNetError(f"lpcnet_b200_measure_l2_gather: {last_error()}")
+    return v.value
 
 
 def _check(rc: int, what: str) -> None:
@@ -180,6 +191,17 @@ class Batch:
     @property
     def launch_count(self):
         return int(self.L.lpcnet_batch_launch_count(self.h))
+
+    def set_profiling(self, on: bool):
+        _check(self.L.lpcnet_batch_set_profiling(self.h, int(on)), "lpcnet_batch_set_profiling")
+
+    def read_profile(self):
+        """(sample_kernel_ms, n_sample_launches, frame_network_ms, n_frame_groups) since the last read."""
+        sm, fm = C.c_double(0), C.c_double(0)
+        sn, fn = C.c_int(0), C.c_int(0)
+        _check(self.L.lpcnet_batch_read_profile(self.h, C.byref(sm), C.byref(sn), C.byref(fm), C.byref(fn)),
+               "lpcnet_batch_read_profile")
+        return sm.value, sn.value, fm.value, fn.value
 
     def synthesize(self, features, forced=None, trace=False, logits=False, pcm_out=None):
         """features: [n_streams][n_frames][>=20] float32 (host).  Returns (pcm, trace, logits)."""

@@ -1,0 +1,128 @@
+"""Generates the golden fixtures in tests/golden/ by running the UNMODIFIED reference
+(oracle/_ref/libref_d2.so = /root/reference/src/*.c compiled in place by oracle/Makefile with
+-O2 -mavx2 -mfma -ffp-contract=off, plus oracle/ref_harness.c).  Run in the build container
+(needs /root/reference):   python tests/golden/make_golden.py
+The fixtures travel to the GPU box; the reference does not."""
+import hashlib
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from lpcnet_b200 import blob  # noqa: E402
+from oracle import refpy  # noqa: E402
+
+OUT = os.path.dirname(os.path.abspath(__file__))
+
+
+def prims(R):
+    rng = np.random.default_rng(7)
+    x = np.concatenate([rng.standard_normal(3000) * 3, rng.uniform(-12, 12, 1000),
+                        [0, -0.0, 1e-8, -1e-8, 40, -40, 1e4, -1e4]]).astype(np.float32)
+    d = {"act_x": x, "tanh": R.vec("ref_vec_tanh", x), "sigmoid": R.vec("ref_vec_sigmoid", x)}
+    lx = np.concatenate([rng.standard_normal(2000) * 3000, rng.uniform(-40000, 40000, 1000),
+                         [0, -0.0, 1, -1, 32767, -32768, 1e6, -1e6]]).astype(np.float32)
+    d["lin_x"] = lx
+    d["lin2ulaw"] = np.array([R.lib.ref_lin2ulaw(refpy.C.c_float(float(v))) for v in lx], np.int32)
+    d["ulaw2lin"] = np.array([R.lib.ref_ulaw2lin(refpy.C.c_float(float(u))) for u in range(256)], np.float32)
+    d["rcp_table"] = R.rcp_table().view(np.uint32)
+    # rcp at random mantissas/exponents: shows the estimate depends only on the top 11 bits
+    rx = (rng.uniform(1, 2, 500) * 2.0 ** rng.integers(-3, 40, 500)).astype(np.float32)
+    d["rcp_x"] = rx
+    d["rcp_y"] = np.array([R.lib.ref_rcp_ss(refpy.C.c_float(float(v))) for v in rx], np.float32)
+    for seed in (b"LPCNet", b"LPCNet17", b"x", b"", b"abcdefgh"):
+        st = R.kiss99_srand(seed)
+        seq = [st.copy()]
+        draws = []
+        for _ in range(16):
+            draws.append(R.kiss99_rand(st))
+            seq.append(st.copy())
+        d["kiss_state_" + seed.decode()] = np.stack(seq)
+        d["kiss_draws_" + seed.decode()] = np.array(draws, np.uint32)
+    q = rng.uniform(-1.3, 1.3, 512).astype(np.float32)
+    d["quant_x"] = q
+    d["quant_u8"] = R.ps_to_epi8(q)
+    # int8 kernels on a small block-sparse matrix
+    n_in, n_out = 64, 48
+    qw = rng.integers(-60, 61, size=(n_in, n_out)).astype(np.int32)
+    mask = rng.random((n_in // 4, n_out // 8)) < 0.4
+    qw = qw * np.repeat(np.repeat(mask, 4, 0), 8, 1)
+    wq, idx = blob.block_sparse_encode(qw, mask)
+    xin = rng.uniform(-1, 1, n_in).astype(np.float32)
+    out0 = (rng.standard_normal(n_out) * 0.5).astype(np.float32)
+    d["sp_w"], d["sp_idx"], d["sp_x"], d["sp_out0"] = wq, idx, xin, out0
+    d["sp_out"] = R.sparse_sgemv(out0, wq, idx, xin)
+    qd = rng.integers(-60, 61, size=(16, 48)).astype(np.int32)
+    wd = blob.dotp_layout(qd)
+    xd = rng.uniform(-1, 1, 16).astype(np.float32)
+    d["de_w"], d["de_x"] = wd, xd
+    d["de_out"] = R.sgemv8x4(out0, wd, xd)
+    wf = (rng.standard_normal((40, 32)) * 0.2).astype(np.float32)  # [cols][rows]
+    xf = rng.standard_normal(40).astype(np.float32)
+    of = rng.standard_normal(32).astype(np.float32)
+    d["f_w"], d["f_x"], d["f_out0"] = wf, xf, of
+    d["f_out"] = R.sgemv16(of, wf, 40, xf)
+    ceps = (rng.standard_normal((32, 18)) * 0.5).astype(np.float32)
+    ceps[:, 0] += 2
+    d["ceps"] = ceps
+    d["lpc"] = np.stack([R.lpc_from_cepstrum(c) for c in ceps])
+    np.savez_compressed(os.path.join(OUT, "prims.npz"), **d)
+
+
+def synth(R):
+    A = blob.random_model()
+    b = blob.write_blob(A)
+    d = {"blob_sha256": np.frombuffer(hashlib.sha256(b).digest(), np.uint8)}
+    F = 12
+    streams = [0, 3, 11]
+    d["streams"] = np.array(streams)
+    for s in streams:
+        f = blob.synthetic_features(F, s)
+        d[f"feat_{s}"] = f
+        rs = refpy.RefStream(R, b, blob.stream_seed(s))
+        pcm, tr, lg = rs.run(f, trace=True, logits=True)
+        d[f"pcm_{s}"], d[f"trace_{s}"] = pcm, tr
+        d[f"logits_{s}"] = lg[3 * 160:3 * 160 + 96].copy()   # steps 480..575
+        d[f"state_{s}"] = np.array([rs.snapshot()])
+        # teacher forced on a perturbed copy of its own output (so forcing actually changes the path)
+        forced = (pcm.astype(np.int32) // 2).astype(np.int16)
+        rs2 = refpy.RefStream(R, b, blob.stream_seed(s))
+        pcm2, tr2, lg2 = rs2.run(f, forced=forced, trace=True, logits=True)
+        d[f"forced_{s}"], d[f"fpcm_{s}"], d[f"ftrace_{s}"] = forced, pcm2, tr2
+        d[f"flogits_{s}"] = lg2[3 * 160:3 * 160 + 96].copy()
+    # the public API on stream 0, with a short last call (N=80)
+    rs = refpy.RefStream(R, b)
+    f = blob.synthetic_features(6, 0)
+    outs = [rs.synthesize(f[k], 160 if k < 5 else 80) for k in range(6)]
+    d["api_pcm"] = np.concatenate(outs)
+    # frame network alone
+    rs = refpy.RefStream(R, b)
+    ga = np.zeros((4, 1152), np.float32); gb = np.zeros((4, 48), np.float32); lp = np.zeros((4, 16), np.float32)
+    for k in range(4):
+        R.lib.ref_frame_network(refpy.C.c_void_p(rs.h), refpy._p(np.ascontiguousarray(f[k])), refpy._p(ga[k]), refpy._p(gb[k]), refpy._p(lp[k]))
+    d["fn_ga"], d["fn_gb"], d["fn_lpc"] = ga, gb, lp
+    d["logit_table"] = rs.logit_table()
+    np.savez_compressed(os.path.join(OUT, "synth.npz"), **d)
+
+
+def decode(R):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    rng = np.random.default_rng(5)
+    pk = rng.integers(0, 256, size=(24, 8)).astype(np.uint8)
+    pk[5, 1] &= 0xF8   # modulation field (bits 13..15) = 0 -> unvoiced branch
+    vq = np.zeros(18, np.float32)
+    feats = []
+    for p in pk:
+        feats.append(R.decode_packet(vq, p.tobytes()))
+    np.savez_compressed(os.path.join(OUT, "decode.npz"), packets=pk, features=np.stack(feats))
+
+
+if __name__ == "__main__":
+    R = refpy.RefLib(2)
+    prims(R)
+    synth(R)
+    decode(R)
+    for f in sorted(os.listdir(OUT)):
+        print(f, os.path.getsize(os.path.join(OUT, f)))

@@ -1,0 +1,287 @@
+"""Parity of the CUDA engine (through the C-ABI, lpcnet_b200/engine.py) against the CPU oracle
+and the golden vectors of the unmodified reference.  Bar: bit-exact for every integer quantity
+(mu-law indices, exc, kiss99 state, u8-quantised GRU states, PCM); floating-point node logits
+are compared bit-for-bit too and the derived 256-way pdf within 1e-4 (north_star tolerance)."""
+import numpy as np
+import pytest
+
+from lpcnet_b200 import blob, engine
+from oracle import orcpy
+
+pytestmark = pytest.mark.gpu
+
+PDF_TOL = 1e-4   # north_star: per-step output pdf within 1e-4 absolute
+
+
+def bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+def tree_to_pdf(logits):
+    """training_tf2/lpcnet.py:75-85: pdf of the 8-level binary tree from its 255 node logits."""
+    p = 1.0 / (1.0 + np.exp(-logits.astype(np.float64)))      # [T][256], node 0 unused
+    pdf = np.ones((logits.shape[0], 1))
+    for lvl in range(8):
+        nodes = p[:, (1 << lvl):(2 << lvl)]                    # [T][2^lvl]
+        pdf = np.stack([pdf * (1 - nodes), pdf * nodes], axis=-1).reshape(logits.shape[0], -1)
+    return pdf
+
+
+def oracle_run(orc_model, feats, seeds, forced=None, trace=True, logits=False):
+    out = []
+    for s, f in enumerate(feats):
+        st = orcpy.OrcStream(orc_model, seeds[s])
+        out.append(st.run(f, forced=None if forced is None else forced[s], trace=trace, logits=logits))
+    return out
+
+
+@pytest.fixture(scope="module")
+def eng(engine_lib):
+    assert engine.device_count() > 0, "no CUDA device: the gpu tests cannot run (there is no CPU fallback)"
+    return engine
+
+
+def make_batch(eng, model_blob, feats_ids, seeds, tile=0, **kw):
+    bt = eng.Batch(model_blob, len(feats_ids), **kw)
+    if tile:
+        bt.set_tile(tile)
+    for s, sd in enumerate(seeds):
+        bt.set_seed(s, sd)
+    return bt
+
+
+def test_frame_network_bit_exact(eng, model_blob, orc_model):
+    B, F = 6, 9
+    feats = np.stack([blob.synthetic_features(F, s) for s in range(B)])
+    bt = eng.Batch(model_blob, B)
+    ga, gb, lpc = bt.frame_network(feats)
+    for s in range(B):
+        st = orcpy.OrcStream(orc_model)
+        for f in range(F):
+            oga, ogb, olpc = st.frame_network(feats[s, f])
+            assert np.array_equal(bits(ga[s, f]), bits(oga)), (s, f)
+            assert np.array_equal(bits(gb[s, f]), bits(ogb)), (s, f)
+            assert np.array_equal(bits(lpc[s, f]), bits(olpc)), (s, f)
+    # frame state after the call (conv histories, old_lpc, frame_count)
+    snap, osnap = bt.get_state(B - 1), st.snapshot()
+    for name in ("conv1_state", "conv2_state", "old_lpc", "frame_count"):
+        assert np.array_equal(np.asarray(snap[name]), np.asarray(osnap[name])), name
+    bt.close()
+
+
+def test_frame_network_against_reference_golden(eng, model_blob, golden_synth):
+    g = golden_synth
+    f = blob.synthetic_features(6, 0)[None, :4]
+    bt = eng.Batch(model_blob, 1)
+    ga, gb, lpc = bt.frame_network(f)
+    assert np.array_equal(bits(ga[0]), bits(g["fn_ga"]))
+    assert np.array_equal(bits(gb[0]), bits(g["fn_gb"]))
+    assert np.array_equal(bits(lpc[0]), bits(g["fn_lpc"]))
+    bt.close()
+
+
+@pytest.mark.parametrize("tile", [8, 16, 32, 64])
+@pytest.mark.parametrize("forced_mode", [False, True])
+def test_synthesis_trace_bit_exact(eng, model_blob, orc_model, tile, forced_mode):
+    """Ragged batch (11 streams: partial tiles), per-stream seeds, every step compared."""
+    B, F = 11, 5
+    ids = list(range(20, 20 + B))
+    feats = np.stack([blob.synthetic_features(F, s) for s in ids])
+    seeds = [blob.stream_seed(s) for s in ids]
+    forced = None
+    if forced_mode:
+        free = oracle_run(orc_model, feats, seeds, trace=False)
+        forced = np.stack([(r[0].astype(np.int32) * 3 // 4).astype(np.int16) for r in free])
+    ref = oracle_run(orc_model, feats, seeds, forced=forced, logits=True)
+    bt = make_batch(eng, model_blob, ids, seeds, tile)
+    pcm, tr, lg = bt.synthesize(feats, forced=forced, trace=True, logits=True)
+    for s in range(B):
+        rp, rt, rl = ref[s]
+        bad = np.nonzero(tr[s] != rt)[0]
+        assert bad.size == 0, f"stream {s}: first divergence at step {bad[0]}: {tr[s][bad[0]]} vs {rt[bad[0]]}"
+        assert np.array_equal(pcm[s], rp)
+        assert np.array_equal(bits(lg[s]), bits(rl))
+        act = slice(2 * 160, None)
+        assert np.abs(tree_to_pdf(lg[s][act]) - tree_to_pdf(rl[act])).max() <= PDF_TOL
+    bt.close()
+
+
+@pytest.mark.parametrize("s", [0, 3, 11])
+def test_against_reference_golden(eng, model_blob, golden_synth, s):
+    """The committed outputs of the unmodified reference (free-running and teacher-forced)."""
+    g = golden_synth
+    f = g[f"feat_{s}"][None]
+    bt = make_batch(eng, model_blob, [s], [blob.stream_seed(s)])
+    pcm, tr, lg = bt.synthesize(f, trace=True, logits=True)
+    assert np.array_equal(pcm[0], g[f"pcm_{s}"])
+    assert np.array_equal(tr[0], g[f"trace_{s}"])
+    assert np.array_equal(bits(lg[0][480:576]), bits(g[f"logits_{s}"]))
+    snap, ref = bt.get_state(0), g[f"state_{s}"][0]
+    for name in snap.dtype.names:
+        assert np.array_equal(np.asarray(snap[name]), np.asarray(ref[name])), name
+    bt.reset()
+    bt.set_seed(0, blob.stream_seed(s))
+    pcm, tr, lg = bt.synthesize(f, forced=g[f"forced_{s}"][None], trace=True, logits=True)
+    assert np.array_equal(pcm[0], g[f"fpcm_{s}"])
+    assert np.array_equal(tr[0], g[f"ftrace_{s}"])
+    assert np.array_equal(bits(lg[0][480:576]), bits(g[f"flogits_{s}"]))
+    assert np.abs(tree_to_pdf(lg[0][480:576]) - tree_to_pdf(g[f"flogits_{s}"])).max() <= PDF_TOL
+    bt.close()
+
+
+def test_single_stream_api_matches_reference(eng, model_blob, golden_synth):
+    """lpcnet_create / lpcnet_load_model / lpcnet_synthesize, with a short last call (N=80)."""
+    syn = eng.Synth(model_blob)
+    f = blob.synthetic_features(6, 0)
+    outs = [syn.synthesize(f[k], 160 if k < 5 else 80) for k in range(6)]
+    assert np.array_equal(np.concatenate(outs), golden_synth["api_pcm"])
+    # lpcnet_reset: same output again
+    syn.reset()
+    outs2 = [syn.synthesize(f[k], 160 if k < 5 else 80) for k in range(6)]
+    assert np.array_equal(np.concatenate(outs2), golden_synth["api_pcm"])
+    syn.close()
+
+
+def test_chunked_and_split_calls_agree(eng, model_blob, orc_model):
+    """40 frames cross the 32-frame chunk boundary; two calls of 17+23 frames must equal one call."""
+    B, F = 3, 40
+    ids = [7, 8, 9]
+    feats = np.stack([blob.synthetic_features(F, s) for s in ids])
+    seeds = [blob.stream_seed(s) for s in ids]
+    ref = oracle_run(orc_model, feats, seeds, trace=False)
+    bt = make_batch(eng, model_blob, ids, seeds)
+    pcm, _, _ = bt.synthesize(feats)
+    for s in range(B):
+        assert np.array_equal(pcm[s], ref[s][0])
+    bt.reset()
+    for s, sd in enumerate(seeds):
+        bt.set_seed(s, sd)
+    p1, _, _ = bt.synthesize(feats[:, :17])
+    p2, _, _ = bt.synthesize(feats[:, 17:])
+    assert np.array_equal(np.concatenate([p1, p2], axis=1), pcm)
+    bt.close()
+
+
+def test_state_cross_loading_with_oracle(eng, model_blob, orc_model):
+    """Snapshot the oracle mid-stream, load it into the engine (and back), continue on both."""
+    f = blob.synthetic_features(10, 4)
+    st = orcpy.OrcStream(orc_model, b"LPCNet4")
+    st.run(f[:6])
+    snap = st.snapshot()
+    ref_tail = st.run(f[6:], trace=True)
+    bt = eng.Batch(model_blob, 2)
+    bt.set_state(1, snap)
+    got = bt.get_state(1)
+    for name in snap.dtype.names:
+        assert np.array_equal(np.asarray(got[name]), np.asarray(snap[name])), name
+    pcm, tr, _ = bt.synthesize(np.stack([f[6:], f[6:]]), trace=True)
+    assert np.array_equal(pcm[1], ref_tail[0]) and np.array_equal(tr[1], ref_tail[1])
+    # engine -> oracle
+    st2 = orcpy.OrcStream(orc_model)
+    st2.restore(bt.get_state(1))
+    more = blob.synthetic_features(3, 5)
+    a = st2.run(more)[0]
+    b, _, _ = bt.synthesize(np.stack([more, more]))
+    assert np.array_equal(b[1], a)
+    bt.close()
+
+
+@pytest.mark.parametrize("delay,gamma", [(0, 1.0), (1, 0.9), (2, 0.9)])
+def test_features_delay_and_lpc_gamma(eng, orclib, model_blob, delay, gamma):
+    om = orcpy.OrcModel(orclib, model_blob, delay, gamma, None)
+    f = blob.synthetic_features(5, 2)
+    ref = orcpy.OrcStream(om, b"LPCNet2").run(f, trace=True)
+    bt = eng.Batch(model_blob, 1, features_delay=delay, lpc_gamma=gamma)
+    bt.set_seed(0, b"LPCNet2")
+    pcm, tr, _ = bt.synthesize(f[None], trace=True)
+    assert np.array_equal(pcm[0], ref[0]) and np.array_equal(tr[0], ref[1])
+    bt.close()
+
+
+def test_other_density_model(eng, orclib):
+    """A denser GRU-A (0.1, 0.1, 0.4) and a sparse GRU-B input: the kernel is not tied to one block list."""
+    A = blob.random_model(seed=77, density=(0.1, 0.1, 0.4), gru_b_density=0.5)
+    b = blob.write_blob(A)
+    om = orcpy.OrcModel(orclib, b, 2, 1.0, None)
+    B, F = 9, 4
+    feats = np.stack([blob.synthetic_features(F, 40 + s) for s in range(B)])
+    seeds = [blob.stream_seed(40 + s) for s in range(B)]
+    ref = oracle_run(om, feats, seeds)
+    for tile in (8, 32):
+        bt = eng.Batch(b, B)
+        bt.set_tile(tile)
+        assert bt.nblocks_a == om.nblocks_a and bt.nblocks_b == om.nblocks_b
+        for s, sd in enumerate(seeds):
+            bt.set_seed(s, sd)
+        pcm, tr, _ = bt.synthesize(feats, trace=True)
+        for s in range(B):
+            assert np.array_equal(tr[s], ref[s][1]) and np.array_equal(pcm[s], ref[s][0])
+        bt.close()
+
+
+def test_rejects_bad_blobs(eng, model_blob):
+    A = blob.random_model()
+    with pytest.raises(eng.LPCNetError):
+        eng.Batch(model_blob[:-64], 1)                          # truncated last record
+    B2 = dict(A); del B2["dual_fc_bias"]
+    with pytest.raises(eng.LPCNetError):
+        eng.Batch(blob.write_blob(B2), 1)                       # missing array
+    B3 = dict(A); B3["dual_fc_bias"] = A["dual_fc_bias"][:-1]
+    with pytest.raises(eng.LPCNetError):
+        eng.Batch(blob.write_blob(B3), 1)                       # wrong size
+    B4 = dict(A); idx = A["sparse_gru_a_recurrent_weights_idx"].copy(); idx[1] = 2; B4["sparse_gru_a_recurrent_weights_idx"] = idx
+    with pytest.raises(eng.LPCNetError):
+        eng.Batch(blob.write_blob(B4), 1)                       # position not a multiple of 4
+    B5 = dict(A); w = A["gru_b_recurrent_weights"].copy(); w[:2] = 100; B5["gru_b_recurrent_weights"] = w
+    with pytest.raises(eng.LPCNetError):
+        eng.Batch(blob.write_blob(B5), 1)                       # would saturate vpmaddubsw
+
+
+def test_decode_matches_reference_golden(eng, model_blob, golden_decode, codebooks, orc_model):
+    g = golden_decode
+    pk = g["packets"]
+    bt = eng.Batch(model_blob, 2)
+    bt.set_codebooks(codebooks)
+    packets = np.stack([pk[:12], pk[12:]])
+    pcm, feats = bt.decode(packets, want_features=True)
+    # stream 0 starts from vq_mem = 0 exactly like the fixture; stream 1 does too but on other packets,
+    # so only stream 0's features are comparable to the fixture sequence
+    assert np.array_equal(bits(feats[0]), bits(g["features"][:12].reshape(48, 36)))
+    # synthesis from the decoded features == oracle on the same features
+    for s in range(2):
+        ref = orcpy.OrcStream(orc_model).run(feats[s])[0]
+        assert np.array_equal(pcm[s], ref)
+    bt.close()
+
+
+def test_decoder_api(eng, model_blob, codebooks, golden_decode, orc_model):
+    A = blob.random_model()
+    A["ceps_codebook1"] = codebooks[:1024 * 17]
+    A["ceps_codebook2"] = codebooks[1024 * 17:2 * 1024 * 17]
+    A["ceps_codebook3"] = codebooks[2 * 1024 * 17:3 * 1024 * 17]
+    A["ceps_codebook_diff4"] = codebooks[3 * 1024 * 17:]
+    dec = eng.Decoder(blob.write_blob(A))
+    pk = golden_decode["packets"][:3]
+    got = np.concatenate([dec.decode(p.tobytes()) for p in pk])
+    feats = golden_decode["features"][:3].reshape(12, 36)
+    ref = orcpy.OrcStream(orc_model).run(feats)[0]
+    assert np.array_equal(got, ref)
+    dec.close()
+
+
+def test_full_size_batch_invariance(eng, model_blob, orc_model):
+    """BASELINE config 2 size (1024 streams): a stream's output must not depend on its slot or
+    neighbours.  Streams s and s+512 get identical inputs and seeds; a sample is checked vs the oracle."""
+    B, F = 1024, 6
+    base = np.stack([blob.synthetic_features(F, s % 64) for s in range(512)])
+    feats = np.concatenate([base, base])
+    bt = eng.Batch(model_blob, B)
+    for s in range(B):
+        bt.set_seed(s, blob.stream_seed(s % 512))
+    pcm, _, _ = bt.synthesize(feats)
+    assert np.array_equal(pcm[:512], pcm[512:])
+    for s in (0, 63, 64, 200, 511):
+        ref = orcpy.OrcStream(orc_model, blob.stream_seed(s)).run(feats[s])[0]
+        assert np.array_equal(pcm[s], ref), s
+    assert (pcm[:, :320] == 0).all() and (pcm[:, 320:] != 0).any()
+    bt.close()
