@@ -60,31 +60,35 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
   L.part = take(MT * (b_parts(MT) + 1) * kRGroupsB * 128 * 4);
   L.usig = take(NS * 4); L.upred = take(NS * 4); L.lexc = take(NS * 4); L.pred = take(NS * 4);
   L.deemph = take(NS * 4); L.rng = take(4 * NS * 4); L.head = take(NS * 4); L.act = take(NS * 4);
-  L.fcw = L.fcb = 0;
-  if (fc_resident(NS)) { L.fcw = take(256 * kFcStride * 4); L.fcb = take(4 * 256 * 4); }
+  L.fcb = take(4 * 256 * 4);
+  L.fcw = fc_resident(NS) ? take(256 * kFcStride * 4) : 0;
   L.total = o;
   return L;
 }
 
 __device__ __forceinline__ float2 ldg2(const float *p) { return __ldg(reinterpret_cast<const float2 *>(p)); }
 
-// one dual-FC node logit (src/nnet.c:192-202); bv = GRU-B state
-__device__ __forceinline__ float node_logit(const DevModel &m, int i, const float (&bv)[16], const uint32_t *rcp) {
-  const float4 *w4 = reinterpret_cast<const float4 *>(m.fc_w + (size_t)i * 32);
+// one dual-FC node logit (src/nnet.c:192-202); bv = GRU-B state.  w: the node's 32 weights
+// [channel][input], bf: bias|factor as [bias c0 | bias c1 | factor c0 | factor c1][256].
+template <bool SMEM>
+__device__ __forceinline__ float node_logit(const float *__restrict__ wbase, int wstride, const float *__restrict__ bf,
+                                            int i, const float (&bv)[16], const uint32_t *rcp) {
+  const float4 *w4 = reinterpret_cast<const float4 *>(wbase + (size_t)i * wstride);
   float w[32];
 #pragma unroll
   for (int k = 0; k < 8; k++) {
-    float4 v = __ldg(w4 + k);
+    const float4 v = SMEM ? w4[k] : __ldg(w4 + k);
     w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
   }
-  float sum1 = __ldg(m.fc_bias + i), sum2 = __ldg(m.fc_bias + 256 + i);
+  float sum1 = bf[i], sum2 = bf[256 + i];       // bias|factor are always resident
+  const float f1 = bf[512 + i], f2 = bf[768 + i];
 #pragma unroll
   for (int j = 0; j < 16; j++) {
     sum1 = sum1 + w[j] * bv[j];
     sum2 = sum2 + w[16 + j] * bv[j];
   }
-  sum1 = __ldg(m.fc_factor + i) * tanh_ref(sum1, rcp);
-  sum2 = __ldg(m.fc_factor + 256 + i) * tanh_ref(sum2, rcp);
+  sum1 = f1 * tanh_ref(sum1, rcp);
+  sum2 = f2 * tanh_ref(sum2, rcp);
   return sum1 + sum2;
 }
 
@@ -99,6 +103,8 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   constexpr int NS = MT * VR;
   constexpr int NV = (VR == 16) ? 4 : 2;   // accumulator registers in use per thread
   constexpr int P = (MT == 1) ? 4 : (MT == 2 ? 2 : 1);
+  constexpr bool CREG = (MT == 1 && VR == 8);   // frame conditioning of GRU-A held in registers (18 per thread)
+  constexpr bool FCS = NS <= 32;            // dual_fc resident in shared memory (fc_resident)
   extern __shared__ __align__(16) unsigned char smem[];
   const DevModel &M = A.m;
   const SmemLayout L = make_layout(NS, MT, M.a_rec.n_chunks, M.b_in.n_chunks, M.b_rec.n_chunks);
@@ -133,6 +139,10 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   uint32_t *s_rng = reinterpret_cast<uint32_t *>(smem + L.rng);
   int *s_head = reinterpret_cast<int *>(smem + L.head);
   int *s_act = reinterpret_cast<int *>(smem + L.act);
+  // dual_fc weights: resident copy (padded node stride) or the blob array in global memory; bias|factor resident
+  const float *fc_w = FCS ? reinterpret_cast<const float *>(smem + L.fcw) : M.fc_w;
+  const int fc_stride = FCS ? kFcStride : 32;
+  const float *fc_bf = reinterpret_cast<const float *>(smem + L.fcb);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2, t = lane & 3;
@@ -159,6 +169,14 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
     copy_words(s_rcp, M.rcp_tab, 2048);
     copy_words(reinterpret_cast<uint32_t *>(s_u2l), reinterpret_cast<const uint32_t *>(M.ulaw2lin_tab), 256);
     copy_words(reinterpret_cast<uint32_t *>(s_logit), reinterpret_cast<const uint32_t *>(M.logit_tab), 256);
+    {
+      float *fb = reinterpret_cast<float *>(smem + L.fcb);
+      for (int i = tid; i < 512; i += kThreads) { fb[i] = __ldg(M.fc_bias + i); fb[512 + i] = __ldg(M.fc_factor + i); }
+    }
+    if (FCS) {
+      float *fw = reinterpret_cast<float *>(smem + L.fcw);
+      for (int i = tid; i < 256 * 32; i += kThreads) fw[(i >> 5) * kFcStride + (i & 31)] = __ldg(M.fc_w + i);
+    }
   }
 
   const int n_tiles = (B + NS - 1) / NS;
@@ -259,6 +277,15 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
       __syncthreads();
 
       const float *condA_f = A.cond_a + (size_t)f * B * kRowsA;
+      float2 cond_reg[3][3];
+      if (CREG) {
+        const int gs = min(stream0 + g, B - 1);
+#pragma unroll
+        for (int u = 0; u < 3; u++)
+#pragma unroll
+          for (int gate = 0; gate < 3; gate++)
+            cond_reg[u][gate] = ldg2(condA_f + (size_t)gs * kRowsA + gate * kN + (warp + u * kWarps) * 8 + 2 * t);
+      }
 
       for (int step = 0; step < A.spf; step++) {
         uint32_t *xa_cur = s_xa + cur * NS * kXaStride;
@@ -270,14 +297,55 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
 #pragma unroll
           for (int mt = 0; mt < MT; mt++) {
             const int sA = mt * VR + g;
-            int us[2], up[2], le[2], gs[2], ac[2];
+            int ac[2];
+            // (1) issue the gathers first: compute_gru_a_input (src/nnet.c:484-491) reads the frame
+            //     conditioning and one row of each embedding table; none of it feeds the recurrent product
+            float2 cv[3][NV / 2], e1[3][NV / 2], e2[3][NV / 2], e3[3][NV / 2];
 #pragma unroll
             for (int h = 0; h < NV / 2; h++) {
               const int s = sA + 8 * h;
-              us[h] = s_usig[s]; up[h] = s_upred[s]; le[h] = s_lexc[s]; ac[h] = s_act[s];
-              gs[h] = min(stream0 + s, B - 1);
+              const int us = s_usig[s], up = s_upred[s], le = s_lexc[s];
+              ac[h] = s_act[s];
+              const int gs = min(stream0 + s, B - 1);
+#pragma unroll
+              for (int gate = 0; gate < 3; gate++) {
+                const int col = gate * kN + ug * 8 + 2 * t;
+                if (CREG) cv[gate][h] = cond_reg[u][gate];
+                else cv[gate][h] = ldg2(condA_f + (size_t)gs * kRowsA + col);
+                e1[gate][h] = ldg2(M.e_sig + (size_t)us * kRowsA + col);
+                e2[gate][h] = ldg2(M.e_pred + (size_t)up * kRowsA + col);
+                e3[gate][h] = ldg2(M.e_exc + (size_t)le * kRowsA + col);
+              }
             }
+            // (2) sparse_sgemv_accum8x4 (src/vec_avx.h:790-858) on tensor cores: the three gates' block
+            //     lists walked together so their MMA chains interleave.  The int32 sum is exact in any
+            //     order, so the rne(16256*t) seed of the AVX2 kernel is added afterwards.
             int32_t acc[3][4];
+            int cb[3], ce[3];
+#pragma unroll
+            for (int gate = 0; gate < 3; gate++) {
+              acc[gate][0] = acc[gate][1] = acc[gate][2] = acc[gate][3] = 0;
+              cb[gate] = s_csA[gate * kUGroups + ug];
+              ce[gate] = s_csA[gate * kUGroups + ug + 1];
+            }
+            const int nmax = max(max(ce[0] - cb[0], ce[1] - cb[1]), ce[2] - cb[2]);
+            const uint32_t *xrow = xa_cur + sA * kXaStride;
+            for (int k = 0; k < nmax; k++) {
+#pragma unroll
+              for (int gate = 0; gate < 3; gate++) {
+                const int c = cb[gate] + k;
+                if (c < ce[gate]) {
+                  const uint2 pp = s_posA[c];
+                  const uint32_t b0 = s_wA[c * 64 + lane], b1 = s_wA[c * 64 + 32 + lane];
+                  const uint32_t plo = (pp.x >> (8 * t)) & 0xffu, phi = (pp.y >> (8 * t)) & 0xffu;
+                  const uint32_t a0 = xrow[plo], a2 = xrow[phi];
+                  uint32_t a1 = 0, a3 = 0;
+                  if (VR == 16) { a1 = xrow[8 * kXaStride + plo]; a3 = xrow[8 * kXaStride + phi]; }
+                  mma_u8s8(acc[gate], a0, a1, a2, a3, b0, b1);
+                }
+              }
+            }
+            // (3) seeds and gates: compute_sparse_gru (src/nnet.c:431-447)
             float gh[NV];
 #pragma unroll
             for (int gate = 0; gate < 3; gate++) {
@@ -286,37 +354,16 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               const float2 dg = *reinterpret_cast<const float2 *>(s_diagA + col);
 #pragma unroll
               for (int h = 0; h < NV / 2; h++) {
-                // compute_gru_a_input (src/nnet.c:484-491): cond + sig + pred + exc rows, left to right
-                const float2 c = ldg2(condA_f + (size_t)gs[h] * kRowsA + col);
-                const float2 e1 = ldg2(M.e_sig + (size_t)us[h] * kRowsA + col);
-                const float2 e2 = ldg2(M.e_pred + (size_t)up[h] * kRowsA + col);
-                const float2 e3 = ldg2(M.e_exc + (size_t)le[h] * kRowsA + col);
-                const float gx = ((c.x + e1.x) + e2.x) + e3.x;
-                const float gy = ((c.y + e1.y) + e2.y) + e3.y;
+                const float gx = ((cv[gate][h].x + e1[gate][h].x) + e2[gate][h].x) + e3[gate][h].x;
+                const float gy = ((cv[gate][h].y + e1[gate][h].y) + e2[gate][h].y) + e3[gate][h].y;
                 const float ax = a_reg[u][mt][2 * h], ay = a_reg[u][mt][2 * h + 1];
-                // compute_sparse_gru (src/nnet.c:431-440): bias + diag*state (+ input for z, r)
-                float tx = sub.x + dg.x * ax, ty = sub.y + dg.y * ay;
-                if (gate < 2) { tx = tx + gx; ty = ty + gy; }
+                float tx = sub.x + dg.x * ax, ty = sub.y + dg.y * ay;   // bias + diag*state
+                if (gate < 2) { tx = tx + gx; ty = ty + gy; }           // (+ input for z, r)
                 else { gh[2 * h] = gx; gh[2 * h + 1] = gy; }
-                acc[gate][2 * h] = acc_seed(tx);
-                acc[gate][2 * h + 1] = acc_seed(ty);
-              }
-              if (NV == 2) { acc[gate][2] = 0; acc[gate][3] = 0; }
-              // sparse_sgemv_accum8x4 (src/vec_avx.h:790-858) on tensor cores
-              const int rg = gate * kUGroups + ug;
-              const int c0 = s_csA[rg], c1 = s_csA[rg + 1];
-              const uint32_t *xrow = xa_cur + sA * kXaStride;
-              for (int c = c0; c < c1; c++) {
-                const uint2 pp = s_posA[c];
-                const uint32_t b0 = s_wA[c * 64 + lane], b1 = s_wA[c * 64 + 32 + lane];
-                const uint32_t plo = (pp.x >> (8 * t)) & 0xffu, phi = (pp.y >> (8 * t)) & 0xffu;
-                const uint32_t a0 = xrow[plo], a2 = xrow[phi];
-                uint32_t a1 = 0, a3 = 0;
-                if (VR == 16) { a1 = xrow[8 * kXaStride + plo]; a3 = xrow[8 * kXaStride + phi]; }
-                mma_u8s8(acc[gate], a0, a1, a2, a3, b0, b1);
+                acc[gate][2 * h] = (int32_t)((uint32_t)acc[gate][2 * h] + (uint32_t)acc_seed(tx));
+                acc[gate][2 * h + 1] = (int32_t)((uint32_t)acc[gate][2 * h + 1] + (uint32_t)acc_seed(ty));
               }
             }
-            // gates (src/nnet.c:442-447)
 #pragma unroll
             for (int k = 0; k < NV; k++) {
               const float z = sigmoid_ref(acc_out(acc[0][k]), s_rcp);
@@ -329,8 +376,14 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             }
 #pragma unroll
             for (int h = 0; h < NV / 2; h++) {
-              const uint32_t q = quant_u8_ref(a_reg[u][mt][2 * h]) | (quant_u8_ref(a_reg[u][mt][2 * h + 1]) << 8);
-              reinterpret_cast<unsigned short *>(xa_new)[((sA + 8 * h) * kXaStride * 4 + ug * 8 + 2 * t) >> 1] = (unsigned short)q;
+              // an inactive stream keeps the byte it already has (its state did not move)
+              if (ac[h]) {
+                const uint32_t q = quant_u8_fast(a_reg[u][mt][2 * h]) | (quant_u8_fast(a_reg[u][mt][2 * h + 1]) << 8);
+                reinterpret_cast<unsigned short *>(xa_new)[((sA + 8 * h) * kXaStride * 4 + ug * 8 + 2 * t) >> 1] = (unsigned short)q;
+              } else {
+                reinterpret_cast<unsigned short *>(xa_new)[((sA + 8 * h) * kXaStride * 4 + ug * 8 + 2 * t) >> 1] =
+                    reinterpret_cast<const unsigned short *>(xa_cur)[((sA + 8 * h) * kXaStride * 4 + ug * 8 + 2 * t) >> 1];
+              }
             }
           }
         }
@@ -404,7 +457,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             __syncwarp();
             if (act) {
               s_bst[s * 20 + l16] = b_new;
-              reinterpret_cast<unsigned char *>(s_xb)[s * kXbStride * 4 + l16] = (unsigned char)quant_u8_ref(b_new);
+              reinterpret_cast<unsigned char *>(s_xb)[s * kXbStride * 4 + l16] = (unsigned char)quant_u8_fast(b_new);
             }
             __syncwarp();
             // sample_mdense (src/nnet.c:163-214)
@@ -426,13 +479,13 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             const int m = l16 ? l16 : 1;              // heap index within a depth-4 subtree (lane 0 idles on node 1)
             const int d = 31 - __clz(m);
             // round 1: levels 0..3, nodes 1..15
-            int bit = s_logit[(r0 >> (8 * d)) & 0xffu] < node_logit(M, m, bv, s_rcp);
+            int bit = s_logit[(r0 >> (8 * d)) & 0xffu] < node_logit<FCS>(fc_w, fc_stride, fc_bf, m, bv, s_rcp);
             int n = 1;
 #pragma unroll
             for (int lvl = 0; lvl < 4; lvl++) n = 2 * n + __shfl_sync(0xffffffffu, bit, gbase + n);
             // round 2: levels 4..7 below node n
             const int node = (n << d) | (m - (1 << d));
-            bit = s_logit[(r1 >> (8 * d)) & 0xffu] < node_logit(M, node, bv, s_rcp);
+            bit = s_logit[(r1 >> (8 * d)) & 0xffu] < node_logit<FCS>(fc_w, fc_stride, fc_bf, node, bv, s_rcp);
             int mm = 1;
 #pragma unroll
             for (int lvl = 0; lvl < 4; lvl++) mm = 2 * mm + __shfl_sync(0xffffffffu, bit, gbase + mm);
@@ -441,7 +494,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               float *lg = A.logits + ((size_t)(stream0 + s) * row_len + out_base + step) * 256;
               for (int k = 0; k < 16; k++) {
                 const int nd = k * 16 + l16;
-                lg[nd] = (nd == 0 || !act) ? 0.f : node_logit(M, nd, bv, s_rcp);
+                lg[nd] = (nd == 0 || !act) ? 0.f : node_logit<FCS>(fc_w, fc_stride, fc_bf, nd, bv, s_rcp);
               }
             }
             // signal update (src/lpcnet.c:256-269), one lane per stream
@@ -474,8 +527,8 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
                 if (pcm < -32767.f) pcm = -32767.f;
                 if (pcm > 32767.f) pcm = 32767.f;
                 if (A.forced) outv = A.forced[oidx];
-                else { outv = (int)floor(.5 + (double)pcm); A.pcm[oidx] = (short)outv; }
-                if (A.forced) A.pcm[oidx] = (short)outv;
+                else outv = round_half_up_ref(pcm);
+                A.pcm[oidx] = (short)outv;
                 if (DEBUG && A.trace) {
                   LPCNetB200Trace tr;
                   tr.exc = exc; tr.u_sig = s_usig[s]; tr.u_pred = s_upred[s];
