@@ -2,42 +2,58 @@
 
 nvcc cross-compiles without a GPU.  `-fmad=false` is part of the numerics contract: the
 kernels mirror the reference's AVX2 build operation by operation and fuse multiply-adds only
-where the reference does (explicit fmaf)."""
+where the reference does (explicit fmaf / fma.rn.f32x2).  Translation units compile in parallel."""
 from __future__ import annotations
 
 import os
 import subprocess
 import sys
+from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
+OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "liblpcnet_b200.so")
-SOURCES = ["model.cu", "frame.cu", "sample.cu", "api.cu", "probe.cu"]
-HEADERS = ["engine.h", "bitexact.cuh", os.path.join("..", "..", "include", "lpcnet_b200.h")]
+SOURCES = ["model.cu", "frame.cu", "sample.cu", "sample_t8.cu", "sample_t16.cu", "sample_t32.cu", "sample_t64.cu",
+           "api.cu", "probe.cu"]
+HEADERS = ["engine.h", "bitexact.cuh", "sample_kernel.cuh", os.path.join("..", "..", "include", "lpcnet_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-              "-fmad=false", "-Xcompiler", "-fPIC,-fvisibility=hidden", "-shared"]
+              "-fmad=false", "-Xcompiler", "-fPIC,-fvisibility=hidden"]
 
 
-def _stale() -> bool:
-    if not os.path.exists(LIB):
-        return True
-    t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in SOURCES + HEADERS] + [os.path.abspath(__file__)]
-    return any(os.path.getmtime(d) > t for d in deps)
+def _mtime(p):
+    return os.path.getmtime(p) if os.path.exists(p) else 0.0
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not _stale():
-        return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
-          ["-o", LIB] + [os.path.join(CSRC, f) for f in SOURCES]
-    r = subprocess.run(cmd, capture_output=True, text=True)
-    if r.returncode != 0:
-        sys.stderr.write(r.stdout + r.stderr)
-        raise RuntimeError("nvcc failed building liblpcnet_b200.so")
-    if verbose:
-        sys.stderr.write(r.stdout + r.stderr)
+    os.makedirs(OBJ, exist_ok=True)
+    hdr_t = max([_mtime(os.path.join(CSRC, h)) for h in HEADERS] + [_mtime(os.path.abspath(__file__))])
+    jobs = []
+    for src in SOURCES:
+        obj = os.path.join(OBJ, src.replace(".cu", ".o"))
+        if force or _mtime(obj) < max(_mtime(os.path.join(CSRC, src)), hdr_t):
+            jobs.append((src, obj))
+
+    def compile_one(job):
+        src, obj = job
+        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj, os.path.join(CSRC, src)]
+        return src, subprocess.run(cmd, capture_output=True, text=True)
+
+    with ThreadPoolExecutor(max_workers=min(8, max(1, len(jobs)))) as ex:
+        for src, r in ex.map(compile_one, jobs):
+            if r.returncode != 0:
+                sys.stderr.write(r.stdout + r.stderr)
+                raise RuntimeError(f"nvcc failed on {src}")
+            if verbose:
+                sys.stderr.write(r.stdout + r.stderr)
+    objs = [os.path.join(OBJ, s.replace(".cu", ".o")) for s in SOURCES]
+    if jobs or not os.path.exists(LIB):
+        r = subprocess.run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs,
+                           capture_output=True, text=True)
+        if r.returncode != 0:
+            sys.stderr.write(r.stdout + r.stderr)
+            raise RuntimeError("link failed for liblpcnet_b200.so")
     return LIB
 
 

@@ -115,7 +115,9 @@ __device__ __forceinline__ uint32_t quant_u8_fast(float x) {
 #define LPCB_SCALE (128.f * 127.f)
 #define LPCB_SCALE_1 (1.f / 128.f / 127.f)
 
-__device__ __forceinline__ int32_t acc_seed(float v) { return cvt_rne_fast(v * LPCB_SCALE); }
+// The loader proves |16256*t| < 2^31 for every reachable pre-activation (model.cu), so the seed of the
+// int32 accumulators (src/vec_avx.h:804-806) is a plain round-to-nearest-even conversion.
+__device__ __forceinline__ int32_t acc_seed(float v) { return __float2int_rn(v * LPCB_SCALE); }
 __device__ __forceinline__ float acc_out(int32_t acc) { return (float)acc * LPCB_SCALE_1; }
 
 // D += A(u8, 16x32 row) * B(s8, 32x8 col), int32 accumulate.  SASS: IMMA.16832.U8.S8
@@ -125,6 +127,59 @@ __device__ __forceinline__ void mma_u8s8(int32_t (&c)[4], uint32_t a0, uint32_t 
       "mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
       : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// ---- packed binary32 pairs (FFMA2 / FADD2 / FMUL2 on sm_100): each half is the same IEEE operation ----
+// (operands travel as binary32 registers and are paired inside the asm: no type punning in C++)
+__device__ __forceinline__ float2 f2_fma(float2 a, float2 b, float2 c) {
+  float2 d;
+  asm("{ .reg .b64 ra, rb, rc, rd;\n\t"
+      "mov.b64 ra, {%2, %3}; mov.b64 rb, {%4, %5}; mov.b64 rc, {%6, %7};\n\t"
+      "fma.rn.f32x2 rd, ra, rb, rc;\n\t"
+      "mov.b64 {%0, %1}, rd; }"
+      : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+  return d;
+}
+__device__ __forceinline__ float2 f2_add(float2 a, float2 b) {
+  float2 d;
+  asm("{ .reg .b64 ra, rb, rd;\n\t"
+      "mov.b64 ra, {%2, %3}; mov.b64 rb, {%4, %5};\n\t"
+      "add.rn.f32x2 rd, ra, rb;\n\t"
+      "mov.b64 {%0, %1}, rd; }"
+      : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+  return d;
+}
+__device__ __forceinline__ float2 f2_mul(float2 a, float2 b) {
+  float2 d;
+  asm("{ .reg .b64 ra, rb, rd;\n\t"
+      "mov.b64 ra, {%2, %3}; mov.b64 rb, {%4, %5};\n\t"
+      "mul.rn.f32x2 rd, ra, rb;\n\t"
+      "mov.b64 {%0, %1}, rd; }"
+      : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+  return d;
+}
+__device__ __forceinline__ float2 f2_set(float v) { return make_float2(v, v); }
+
+// tanh8_approx / sigmoid8_approx on a pair
+__device__ __forceinline__ float2 tanh2_ref(float2 x, const uint32_t *__restrict__ tab) {
+  const float2 X2 = f2_mul(x, x);
+  float2 num = f2_fma(f2_fma(f2_set(0.60863042f), X2, f2_set(96.39235687f)), X2, f2_set(952.52801514f));
+  float2 den = f2_fma(f2_fma(f2_set(11.88600922f), X2, f2_set(413.36801147f)), X2, f2_set(952.72399902f));
+  num = f2_mul(num, x);
+  den.x = rcp_estimate(den.x, tab); den.y = rcp_estimate(den.y, tab);
+  num = f2_mul(num, den);
+  num.x = fmaxf(-1.f, fminf(1.f, num.x)); num.y = fmaxf(-1.f, fminf(1.f, num.y));
+  return num;
+}
+__device__ __forceinline__ float2 sigmoid2_ref(float2 x, const uint32_t *__restrict__ tab) {
+  const float2 X2 = f2_mul(x, x);
+  float2 num = f2_fma(f2_fma(f2_set(0.00950985f), X2, f2_set(6.02452230f)), X2, f2_set(238.13200378f));
+  float2 den = f2_fma(f2_fma(f2_set(0.74287558f), X2, f2_set(103.34200287f)), X2, f2_set(952.72399902f));
+  num = f2_mul(num, x);
+  den.x = rcp_estimate(den.x, tab); den.y = rcp_estimate(den.y, tab);
+  num = f2_fma(num, den, f2_set(0.5f));
+  num.x = fmaxf(0.f, fminf(1.f, num.x)); num.y = fmaxf(0.f, fminf(1.f, num.y));
+  return num;
 }
 
 }  // namespace lpcb

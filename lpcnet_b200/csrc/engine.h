@@ -35,6 +35,12 @@ struct PackedSparse {
   std::vector<uint32_t> chunk_start;  // [n_groups + 1]
   std::vector<uint8_t> pos;           // [n_chunks][8]  column position / 4
   std::vector<uint32_t> w;            // [n_chunks][2][32] words, fragment order
+  // GRU-A only ("slotted" layout): unit group ug owns the fixed chunks [ug*ST, (ug+1)*ST), ST = slots[0]+
+  // slots[1]+slots[2], gate-major inside; blocks that do not fit go to overflow chunks after the fixed region,
+  // with chunk_start indexed by ug*3+gate.  off: per chunk, per lane%4, the two gather byte offsets packed
+  // lo | hi << 16.
+  int slots[3] = {0, 0, 0};
+  std::vector<uint32_t> off;          // [n_chunks][4]
 };
 
 struct DevSparse {
@@ -42,6 +48,8 @@ struct DevSparse {
   const uint32_t *chunk_start;  // device
   const uint2 *pos;             // device, [n_chunks]
   const uint32_t *w;            // device, [n_chunks][64]
+  const uint32_t *off;          // device, [n_chunks][4] (slotted GRU-A layout only)
+  int slots[3];                 // fixed chunk slots per gate per unit group (0,0,0 = all chunks in the overflow lists)
 };
 
 // Device-side model: pointers into one device allocation.

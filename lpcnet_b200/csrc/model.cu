@@ -4,6 +4,7 @@
 // re-tiles the block-sparse int8 matrices into mma.sync B-fragment order and uploads
 // everything to the GPU in one allocation.
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <map>
@@ -52,7 +53,7 @@ struct Builder {
 // find_idx_check (parse_lpcnet_weights.c:90-113) + re-tiling.  `idx` NULL means a dense
 // dotp-layout matrix [rows/8][cols/4][8][4] (dump_lpcnet.py:56-60).
 bool pack_sparse(PackedSparse &ps, const int32_t *idx, int idx_len, const int8_t *w, int w_bytes, int rows,
-                 int cols, std::string &err, const char *what) {
+                 int cols, std::string &err, const char *what, bool slotted = false) {
   ps.n_groups = rows / 8;
   ps.chunk_start.assign(ps.n_groups + 1, 0);
   std::vector<std::vector<int>> gpos(ps.n_groups);
@@ -88,30 +89,76 @@ bool pack_sparse(PackedSparse &ps, const int32_t *idx, int idx_len, const int8_t
     if (255 * s > 32767) { err = std::string(what) + ": int8 pair would saturate vpmaddubsw; not representable bit-exactly"; return false; }
   }
   ps.n_blocks = total;
-  int nchunks = 0;
-  for (int g = 0; g < ps.n_groups; g++) {
-    ps.chunk_start[g] = nchunks;
-    nchunks += ((int)gpos[g].size() + 7) / 8;
+  // weight pointer of every block, in stream order
+  std::vector<std::vector<const int8_t *>> gw(ps.n_groups);
+  {
+    const int8_t *wp = w;
+    for (int g = 0; g < ps.n_groups; g++)
+      for (size_t b = 0; b < gpos[g].size(); b++, wp += 32) gw[g].push_back(wp);
   }
-  ps.chunk_start[ps.n_groups] = nchunks;
-  ps.n_chunks = nchunks;
-  ps.pos.assign((size_t)nchunks * 8, 0);
-  ps.w.assign((size_t)nchunks * 64, 0);
-  const int8_t *wp = w;
-  for (int g = 0; g < ps.n_groups; g++) {
-    int nb = (int)gpos[g].size();
-    for (int b = 0; b < nb; b++) {
-      int c = ps.chunk_start[g] + b / 8, slot = b % 8;
-      ps.pos[(size_t)c * 8 + slot] = (uint8_t)(gpos[g][b] / 4);
-      // B fragment of mma.m16n8k32: register slot/4, lane = row*4 + slot%4 holds the four
-      // input weights of output row `row` of block `slot`.
-      for (int r = 0; r < 8; r++) {
-        uint32_t word;
-        memcpy(&word, wp + r * 4, 4);
-        ps.w[(size_t)c * 64 + (slot / 4) * 32 + r * 4 + (slot % 4)] = word;
-      }
-      wp += 32;
+  auto emit = [&](int c, int slot, int pos, const int8_t *blk) {
+    ps.pos[(size_t)c * 8 + slot] = (uint8_t)(pos / 4);
+    // B fragment of mma.m16n8k32: register slot/4, lane = row*4 + slot%4 holds the four input
+    // weights of output row `row` of block `slot`.
+    for (int r = 0; r < 8; r++) {
+      uint32_t word;
+      memcpy(&word, blk + r * 4, 4);
+      ps.w[(size_t)c * 64 + (slot / 4) * 32 + r * 4 + (slot % 4)] = word;
     }
+  };
+  if (!slotted) {
+    int nchunks = 0;
+    for (int g = 0; g < ps.n_groups; g++) {
+      ps.chunk_start[g] = nchunks;
+      nchunks += ((int)gpos[g].size() + 7) / 8;
+    }
+    ps.chunk_start[ps.n_groups] = nchunks;
+    ps.n_chunks = nchunks;
+    ps.pos.assign((size_t)nchunks * 8, 0);
+    ps.w.assign((size_t)nchunks * 64, 0);
+    for (int g = 0; g < ps.n_groups; g++)
+      for (int b = 0; b < (int)gpos[g].size(); b++) emit(ps.chunk_start[g] + b / 8, b % 8, gpos[g][b], gw[g][b]);
+  } else {
+    // rows are gate-major: group index = gate*(n_groups/3) + ug
+    const int nug = ps.n_groups / 3;
+    for (int gate = 0; gate < 3; gate++) {
+      long long blocks = 0;
+      for (int ug = 0; ug < nug; ug++) blocks += (long long)gpos[gate * nug + ug].size();
+      const double mean = (double)blocks / nug;
+      int sl = (int)((mean + 7.999) / 8.0);         // chunks that hold the average row group
+      ps.slots[gate] = sl < 1 ? 1 : (sl > 3 ? 3 : sl);
+    }
+    // the kernel's unrolled fast path is built for (1,1,3); anything else runs the generic lists
+    if (!(ps.slots[0] == 1 && ps.slots[1] == 1 && ps.slots[2] == 3) || getenv("LPCNET_B200_NO_SLOTS"))
+      ps.slots[0] = ps.slots[1] = ps.slots[2] = 0;
+    const int ST = ps.slots[0] + ps.slots[1] + ps.slots[2];
+    int nchunks = nug * ST;
+    ps.chunk_start.assign(nug * 3 + 1, 0);
+    for (int ug = 0; ug < nug; ug++)
+      for (int gate = 0; gate < 3; gate++) {
+        ps.chunk_start[ug * 3 + gate] = nchunks;
+        const int over = (int)gpos[gate * nug + ug].size() - 8 * ps.slots[gate];
+        if (over > 0) nchunks += (over + 7) / 8;
+      }
+    ps.chunk_start[nug * 3] = nchunks;
+    ps.n_chunks = nchunks;
+    ps.pos.assign((size_t)nchunks * 8, 0);
+    ps.w.assign((size_t)nchunks * 64, 0);
+    for (int ug = 0; ug < nug; ug++) {
+      int slot0 = 0;
+      for (int gate = 0; gate < 3; gate++) {
+        const int g = gate * nug + ug, cap = 8 * ps.slots[gate];
+        for (int b = 0; b < (int)gpos[g].size(); b++) {
+          if (b < cap) emit(ug * ST + slot0 + b / 8, b % 8, gpos[g][b], gw[g][b]);
+          else emit(ps.chunk_start[ug * 3 + gate] + (b - cap) / 8, (b - cap) % 8, gpos[g][b], gw[g][b]);
+        }
+        slot0 += ps.slots[gate];
+      }
+    }
+    ps.off.assign((size_t)nchunks * 4, 0);
+    for (int c = 0; c < nchunks; c++)
+      for (int t = 0; t < 4; t++)
+        ps.off[(size_t)c * 4 + t] = (uint32_t)ps.pos[(size_t)c * 8 + t] * 4u | ((uint32_t)ps.pos[(size_t)c * 8 + 4 + t] * 4u) << 16;
   }
   return true;
 }
@@ -187,13 +234,41 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
   if (!ok) return false;
   put(reinterpret_cast<const void **>(&d.a_subias_rec), sub_a + kRowsA * 4, kRowsA * 4);
 
+  // The kernels seed their int32 accumulators with cvt.rni(16256*t) and skip the out-of-range fix-up of
+  // cvtps2dq (-> 0x80000000): prove here that no pre-activation t can reach 2^31/16256 for states in [-1,1].
+  {
+    auto amax = [](const unsigned char *p, size_t n) {
+      const float *f = reinterpret_cast<const float *>(p);
+      double m = 0;
+      for (size_t i = 0; i < n; i++) { double v = fabs((double)f[i]); if (!(v <= m)) m = v; }
+      return m;
+    };
+    auto cond_bound = [&](const char *bn, const char *wn, int nout) {   // |bias| + sum_j |W[j][i]| (inputs are tanh outputs)
+      const float *b = reinterpret_cast<const float *>(A[bn].data), *w = reinterpret_cast<const float *>(A[wn].data);
+      double m = 0;
+      for (int i = 0; i < nout; i++) {
+        double v = fabs((double)b[i]);
+        for (int j = 0; j < kC; j++) v += fabs((double)w[(size_t)j * nout + i]);
+        if (!(v <= m)) m = v;
+      }
+      return m;
+    };
+    const double ta = amax(sub_a, 2 * kRowsA) + amax(A["sparse_gru_a_recurrent_weights_diag"].data, kRowsA) +
+                      amax(A["gru_a_embed_sig_weights"].data, 256 * kRowsA) + amax(A["gru_a_embed_pred_weights"].data, 256 * kRowsA) +
+                      amax(A["gru_a_embed_exc_weights"].data, 256 * kRowsA) +
+                      cond_bound("gru_a_dense_feature_bias", "gru_a_dense_feature_weights", kRowsA);
+    const double tb = amax(A["gru_b_subias"].data, 2 * kRowsB) + cond_bound("gru_b_dense_feature_bias", "gru_b_dense_feature_weights", kRowsB);
+    const double lim = 2147483648.0 / 16256.0 * 0.99;
+    if (!(ta < lim) || !(tb < lim)) { err = "model pre-activations can exceed the int32 accumulator seed range (or contain NaN)"; return false; }
+  }
+
   // int8 matrices
   PackedSparse pa, pb, pr;
   {
     auto ia = A.find("sparse_gru_a_recurrent_weights_idx"), wa = A.find("sparse_gru_a_recurrent_weights");
     if (ia == A.end() || wa == A.end()) { err = "missing GRU-A recurrent arrays"; return false; }
     if (!pack_sparse(pa, reinterpret_cast<const int32_t *>(ia->second.data), ia->second.size / 4,
-                     reinterpret_cast<const int8_t *>(wa->second.data), wa->second.size, kRowsA, kN, err, "sparse_gru_a"))
+                     reinterpret_cast<const int8_t *>(wa->second.data), wa->second.size, kRowsA, kN, err, "sparse_gru_a", true))
       return false;
     auto ib = A.find("gru_b_weights_idx"), wb = A.find("gru_b_weights");
     if (ib == A.end() || wb == A.end()) { err = "missing GRU-B input arrays"; return false; }
@@ -213,6 +288,9 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
     put(reinterpret_cast<const void **>(&ds.chunk_start), ps.chunk_start.data(), ps.chunk_start.size() * 4);
     put(reinterpret_cast<const void **>(&ds.pos), ps.pos.data(), ps.pos.size());
     put(reinterpret_cast<const void **>(&ds.w), ps.w.data(), ps.w.size() * 4);
+    ds.off = nullptr;
+    for (int k = 0; k < 3; k++) ds.slots[k] = ps.slots[k];
+    if (!ps.off.empty()) put(reinterpret_cast<const void **>(&ds.off), ps.off.data(), ps.off.size() * 4);
   };
   put_sparse(d.a_rec, pa);
   put_sparse(d.b_in, pb);

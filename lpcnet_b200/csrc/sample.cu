@@ -1,582 +1,12 @@
-// The 16 kHz sample network as one persistent kernel: run_sample_network + the synthesis loop
-// of the reference (src/lpcnet.c:146-167, 235-271; src/nnet.c:163-214, 326-372, 410-448, 484-491;
-// src/vec_avx.h:321-336, 690-858) for a tile of NS = MT*VR independent streams per CTA.
-//
-// Layout of one CTA (512 threads, 16 warps), per sample step:
-//   phase A  (all warps)  GRU-A.  Warp w owns unit groups {w, w+16, w+32} (8 units each) of every
-//            16-row stream tile.  Per (unit group, tile) it gathers the three embedding rows and the
-//            frame conditioning (fp32, L1/L2), seeds int32 accumulators exactly like the AVX2 kernel,
-//            runs the block-sparse u8 x s8 product as mma.sync.m16n8k32 (streams = M, the 8 rows of a
-//            row group = N, 8 blocks of 4 inputs = K; activations gathered from shared memory),
-//            applies the Pade/rcpps gates in registers and keeps the fp32 state in registers.
-//   phase B1 (all warps)  GRU-B input (48x384) and recurrent (48x16) products, K-split into jobs,
-//            partial int32 sums to shared memory (integer addition is associative, so the split is exact).
-//   phase B2+T (16 lanes per stream) GRU-B gates, then the 8-level dual-FC tree sampler evaluated
-//            speculatively in two rounds of 15 nodes (identical decisions to the sequential descent),
-//            kiss99, mu-law, LPC prediction, de-emphasis and the PCM store.
-// Weights, index lists and tables stay resident in shared memory for the life of the CTA.
-#include <stdio.h>
-
-#include "../../include/lpcnet_b200.h"
-#include "bitexact.cuh"
-#include "engine.h"
+// Host-side dispatch of the persistent sample kernel (sample_kernel.cuh) by streams per CTA.
+#include "sample_kernel.cuh"
 
 namespace lpcb {
 
-constexpr int kThreads = 512;
-constexpr int kWarps = kThreads / 32;
-constexpr int kUGroups = kN / 8;           // 48 unit groups
-constexpr int kRGroupsB = kRowsB / 8;      // 6
-
-struct SmemLayout {
-  // byte offsets
-  unsigned wA, posA, csA, wBi, posBi, csBi, wBr, posBr, csBr;
-  unsigned subA, diagA, subB, rcp, u2l, logit;
-  unsigned xa, xb, bst, lsig, lpc, condb, part;
-  unsigned usig, upred, lexc, pred, deemph, rng, head, act;
-  unsigned fcw, fcb;   // dual_fc weights (node stride kFcStride floats) and bias|factor, when resident
-  unsigned total;
-};
-
-__host__ __device__ inline int b_parts(int MT) { return MT == 1 ? 4 : (MT == 2 ? 2 : 1); }
-
-constexpr int kFcStride = 36;   // 32 weights per node padded so that 8 lanes' 16-byte reads hit disjoint banks
-__host__ __device__ inline bool fc_resident(int NS) { return NS <= 32; }
-
-__host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int chBi, int chBr) {
-  SmemLayout L;
-  unsigned o = 0;
-  auto take = [&](unsigned bytes) { unsigned r = o; o += (bytes + 15u) & ~15u; return r; };
-  L.wA = take(chA * 256); L.posA = take(chA * 8); L.csA = take((kRowsA / 8 + 1) * 4);
-  L.wBi = take(chBi * 256); L.posBi = take(chBi * 8); L.csBi = take((kRGroupsB + 1) * 4);
-  L.wBr = take(chBr * 256); L.posBr = take(chBr * 8); L.csBr = take((kRGroupsB + 1) * 4);
-  L.subA = take(kRowsA * 4); L.diagA = take(kRowsA * 4); L.subB = take(2 * kRowsB * 4);
-  L.rcp = take(2048 * 4); L.u2l = take(256 * 4); L.logit = take(256 * 4);
-  L.xa = take(2 * NS * kXaStride * 4);
-  L.xb = take(NS * kXbStride * 4);
-  L.bst = take(NS * 20 * 4);
-  L.lsig = take(16 * NS * 4); L.lpc = take(16 * NS * 4);
-  L.condb = take(NS * kRowsB * 4);
-  L.part = take(MT * (b_parts(MT) + 1) * kRGroupsB * 128 * 4);
-  L.usig = take(NS * 4); L.upred = take(NS * 4); L.lexc = take(NS * 4); L.pred = take(NS * 4);
-  L.deemph = take(NS * 4); L.rng = take(4 * NS * 4); L.head = take(NS * 4); L.act = take(NS * 4);
-  L.fcb = take(4 * 256 * 4);
-  L.fcw = fc_resident(NS) ? take(256 * kFcStride * 4) : 0;
-  L.total = o;
-  return L;
-}
-
-__device__ __forceinline__ float2 ldg2(const float *p) { return __ldg(reinterpret_cast<const float2 *>(p)); }
-
-// one dual-FC node logit (src/nnet.c:192-202); bv = GRU-B state.  w: the node's 32 weights
-// [channel][input], bf: bias|factor as [bias c0 | bias c1 | factor c0 | factor c1][256].
-template <bool SMEM>
-__device__ __forceinline__ float node_logit(const float *__restrict__ wbase, int wstride, const float *__restrict__ bf,
-                                            int i, const float (&bv)[16], const uint32_t *rcp) {
-  const float4 *w4 = reinterpret_cast<const float4 *>(wbase + (size_t)i * wstride);
-  float w[32];
-#pragma unroll
-  for (int k = 0; k < 8; k++) {
-    const float4 v = SMEM ? w4[k] : __ldg(w4 + k);
-    w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
-  }
-  float sum1 = bf[i], sum2 = bf[256 + i];       // bias|factor are always resident
-  const float f1 = bf[512 + i], f2 = bf[768 + i];
-#pragma unroll
-  for (int j = 0; j < 16; j++) {
-    sum1 = sum1 + w[j] * bv[j];
-    sum2 = sum2 + w[16 + j] * bv[j];
-  }
-  sum1 = f1 * tanh_ref(sum1, rcp);
-  sum2 = f2 * tanh_ref(sum2, rcp);
-  return sum1 + sum2;
-}
-
-__device__ __forceinline__ uint32_t fnv1a_bytes(const unsigned char *p, int n) {
-  uint32_t h = 2166136261u;
-  for (int i = 0; i < n; i++) { h ^= p[i]; h *= 16777619u; }
-  return h;
-}
-
-template <int MT, int VR, bool DEBUG>
-__global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A) {
-  constexpr int NS = MT * VR;
-  constexpr int NV = (VR == 16) ? 4 : 2;   // accumulator registers in use per thread
-  constexpr int P = (MT == 1) ? 4 : (MT == 2 ? 2 : 1);
-  constexpr bool CREG = (MT == 1 && VR == 8);   // frame conditioning of GRU-A held in registers (18 per thread)
-  constexpr bool FCS = NS <= 32;            // dual_fc resident in shared memory (fc_resident)
-  extern __shared__ __align__(16) unsigned char smem[];
-  const DevModel &M = A.m;
-  const SmemLayout L = make_layout(NS, MT, M.a_rec.n_chunks, M.b_in.n_chunks, M.b_rec.n_chunks);
-
-  uint32_t *s_wA = reinterpret_cast<uint32_t *>(smem + L.wA);
-  uint2 *s_posA = reinterpret_cast<uint2 *>(smem + L.posA);
-  uint32_t *s_csA = reinterpret_cast<uint32_t *>(smem + L.csA);
-  uint32_t *s_wBi = reinterpret_cast<uint32_t *>(smem + L.wBi);
-  uint2 *s_posBi = reinterpret_cast<uint2 *>(smem + L.posBi);
-  uint32_t *s_csBi = reinterpret_cast<uint32_t *>(smem + L.csBi);
-  uint32_t *s_wBr = reinterpret_cast<uint32_t *>(smem + L.wBr);
-  uint2 *s_posBr = reinterpret_cast<uint2 *>(smem + L.posBr);
-  uint32_t *s_csBr = reinterpret_cast<uint32_t *>(smem + L.csBr);
-  float *s_subA = reinterpret_cast<float *>(smem + L.subA);
-  float *s_diagA = reinterpret_cast<float *>(smem + L.diagA);
-  float *s_subB = reinterpret_cast<float *>(smem + L.subB);
-  uint32_t *s_rcp = reinterpret_cast<uint32_t *>(smem + L.rcp);
-  float *s_u2l = reinterpret_cast<float *>(smem + L.u2l);
-  float *s_logit = reinterpret_cast<float *>(smem + L.logit);
-  uint32_t *s_xa = reinterpret_cast<uint32_t *>(smem + L.xa);
-  uint32_t *s_xb = reinterpret_cast<uint32_t *>(smem + L.xb);
-  float *s_bst = reinterpret_cast<float *>(smem + L.bst);
-  float *s_lsig = reinterpret_cast<float *>(smem + L.lsig);
-  float *s_lpc = reinterpret_cast<float *>(smem + L.lpc);
-  float *s_condb = reinterpret_cast<float *>(smem + L.condb);
-  int32_t *s_part = reinterpret_cast<int32_t *>(smem + L.part);
-  int *s_usig = reinterpret_cast<int *>(smem + L.usig);
-  int *s_upred = reinterpret_cast<int *>(smem + L.upred);
-  int *s_lexc = reinterpret_cast<int *>(smem + L.lexc);
-  float *s_pred = reinterpret_cast<float *>(smem + L.pred);
-  float *s_deemph = reinterpret_cast<float *>(smem + L.deemph);
-  uint32_t *s_rng = reinterpret_cast<uint32_t *>(smem + L.rng);
-  int *s_head = reinterpret_cast<int *>(smem + L.head);
-  int *s_act = reinterpret_cast<int *>(smem + L.act);
-  // dual_fc weights: resident copy (padded node stride) or the blob array in global memory; bias|factor resident
-  const float *fc_w = FCS ? reinterpret_cast<const float *>(smem + L.fcw) : M.fc_w;
-  const int fc_stride = FCS ? kFcStride : 32;
-  const float *fc_bf = reinterpret_cast<const float *>(smem + L.fcb);
-
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int g = lane >> 2, t = lane & 3;
-  const int B = A.n_streams;
-  const int row_len = A.total_frames * A.spf;
-
-  // ---- one-time: weights, index lists and tables into shared memory ----
-  {
-    auto copy_words = [&](uint32_t *dst, const uint32_t *src, int n) {
-      for (int i = tid; i < n; i += kThreads) dst[i] = __ldg(src + i);
-    };
-    copy_words(s_wA, M.a_rec.w, M.a_rec.n_chunks * 64);
-    copy_words(reinterpret_cast<uint32_t *>(s_posA), reinterpret_cast<const uint32_t *>(M.a_rec.pos), M.a_rec.n_chunks * 2);
-    copy_words(s_csA, M.a_rec.chunk_start, kRowsA / 8 + 1);
-    copy_words(s_wBi, M.b_in.w, M.b_in.n_chunks * 64);
-    copy_words(reinterpret_cast<uint32_t *>(s_posBi), reinterpret_cast<const uint32_t *>(M.b_in.pos), M.b_in.n_chunks * 2);
-    copy_words(s_csBi, M.b_in.chunk_start, kRGroupsB + 1);
-    copy_words(s_wBr, M.b_rec.w, M.b_rec.n_chunks * 64);
-    copy_words(reinterpret_cast<uint32_t *>(s_posBr), reinterpret_cast<const uint32_t *>(M.b_rec.pos), M.b_rec.n_chunks * 2);
-    copy_words(s_csBr, M.b_rec.chunk_start, kRGroupsB + 1);
-    copy_words(reinterpret_cast<uint32_t *>(s_subA), reinterpret_cast<const uint32_t *>(M.a_subias_rec), kRowsA);
-    copy_words(reinterpret_cast<uint32_t *>(s_diagA), reinterpret_cast<const uint32_t *>(M.a_diag), kRowsA);
-    copy_words(reinterpret_cast<uint32_t *>(s_subB), reinterpret_cast<const uint32_t *>(M.b_subias), 2 * kRowsB);
-    copy_words(s_rcp, M.rcp_tab, 2048);
-    copy_words(reinterpret_cast<uint32_t *>(s_u2l), reinterpret_cast<const uint32_t *>(M.ulaw2lin_tab), 256);
-    copy_words(reinterpret_cast<uint32_t *>(s_logit), reinterpret_cast<const uint32_t *>(M.logit_tab), 256);
-    {
-      float *fb = reinterpret_cast<float *>(smem + L.fcb);
-      for (int i = tid; i < 512; i += kThreads) { fb[i] = __ldg(M.fc_bias + i); fb[512 + i] = __ldg(M.fc_factor + i); }
-    }
-    if (FCS) {
-      float *fw = reinterpret_cast<float *>(smem + L.fcw);
-      for (int i = tid; i < 256 * 32; i += kThreads) fw[(i >> 5) * kFcStride + (i & 31)] = __ldg(M.fc_w + i);
-    }
-  }
-
-  const int n_tiles = (B + NS - 1) / NS;
-  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const int stream0 = tile * NS;
-    __syncthreads();
-    // ---- load the tile's stream state ----
-    float a_reg[3][MT][NV];
-    int cur = 0;
-#pragma unroll
-    for (int u = 0; u < 3; u++) {
-      const int ug = warp + u * kWarps;
-#pragma unroll
-      for (int mt = 0; mt < MT; mt++) {
-#pragma unroll
-        for (int k = 0; k < NV; k++) {
-          const int s = mt * VR + g + (k >> 1) * 8;
-          const int gs = min(stream0 + s, B - 1);
-          const int unit = ug * 8 + 2 * t + (k & 1);
-          float v = A.st.gru_a[(size_t)gs * kN + unit];
-          a_reg[u][mt][k] = v;
-          reinterpret_cast<unsigned char *>(s_xa)[(size_t)s * kXaStride * 4 + unit] = (unsigned char)quant_u8_ref(v);
-        }
-      }
-    }
-    for (int i = tid; i < NS * 16; i += kThreads) {
-      const int s = i >> 4, j = i & 15;
-      const int gs = min(stream0 + s, B - 1);
-      float v = A.st.gru_b[(size_t)gs * kNB + j];
-      s_bst[s * 20 + j] = v;
-      reinterpret_cast<unsigned char *>(s_xb)[s * kXbStride * 4 + j] = (unsigned char)quant_u8_ref(v);
-      s_lsig[j * NS + s] = A.st.last_sig[(size_t)gs * 16 + j];
-    }
-    for (int s = tid; s < NS; s += kThreads) {
-      const int gs = min(stream0 + s, B - 1);
-      s_deemph[s] = A.st.deemph[gs];
-      s_lexc[s] = A.st.last_exc[gs];
-      s_head[s] = 0;
-#pragma unroll
-      for (int k = 0; k < 4; k++) s_rng[k * NS + s] = A.st.rng[(size_t)gs * 4 + k];
-    }
-    __syncthreads();
-
-    for (int f = 0; f < A.n_frames; f++) {
-      // ---- frame prologue: LPC, GRU-B conditioning, active flags ----
-      for (int i = tid; i < NS * 16; i += kThreads) {
-        const int s = i >> 4, j = i & 15;
-        const int gs = min(stream0 + s, B - 1);
-        s_lpc[j * NS + s] = A.lpc[((size_t)f * B + gs) * 16 + j];
-      }
-      for (int i = tid; i < NS * kRowsB; i += kThreads) {
-        const int s = i / kRowsB, j = i % kRowsB;
-        const int gs = min(stream0 + s, B - 1);
-        s_condb[i] = A.cond_b[((size_t)f * B + gs) * kRowsB + j];
-      }
-      int my_act = 0;
-      if (tid < NS) {
-        const int gs = stream0 + tid;
-        my_act = (gs < B) ? (int)A.active[(size_t)f * B + gs] : 0;
-        s_act[tid] = my_act;
-      }
-      const int any_act = __syncthreads_or(my_act);
-      const size_t out_base = (size_t)(A.frame0 + f) * A.spf;
-      if (!any_act) {
-        // warm-up frames: N zeros, nothing else moves (src/lpcnet.c:239-243)
-        if (!A.forced || true) {
-          for (int i = tid; i < NS * A.spf; i += kThreads) {
-            const int s = i / A.spf, k = i % A.spf;
-            if (stream0 + s < B) {
-              A.pcm[(size_t)(stream0 + s) * row_len + out_base + k] = 0;
-              if (DEBUG && A.trace) {
-                LPCNetB200Trace tr = {0, 0, 0, 0, 0, 0, 0, 0};
-                reinterpret_cast<LPCNetB200Trace *>(A.trace)[(size_t)(stream0 + s) * row_len + out_base + k] = tr;
-              }
-            }
-          }
-          if (DEBUG && A.logits) {
-            for (size_t i = tid; i < (size_t)NS * A.spf * 256; i += kThreads) {
-              const int s = (int)(i / ((size_t)A.spf * 256));
-              const size_t r = i % ((size_t)A.spf * 256);
-              if (stream0 + s < B) A.logits[((size_t)(stream0 + s) * row_len + out_base) * 256 + r] = 0.f;
-            }
-          }
-        }
-        continue;
-      }
-      // LPC prediction + mu-law indices for step 0 (src/lpcnet.c:252-254)
-      auto predict = [&](int s) {
-        const int head = s_head[s];
-        float pred = 0.f;
-#pragma unroll
-        for (int j = 0; j < 16; j++) pred = pred - s_lsig[((head + j) & 15) * NS + s] * s_lpc[j * NS + s];
-        s_pred[s] = pred;
-        s_usig[s] = lin2ulaw_ref(s_lsig[head * NS + s]);
-        s_upred[s] = lin2ulaw_ref(pred);
-      };
-      if (tid < NS) predict(tid);
-      __syncthreads();
-
-      const float *condA_f = A.cond_a + (size_t)f * B * kRowsA;
-      float2 cond_reg[3][3];
-      if (CREG) {
-        const int gs = min(stream0 + g, B - 1);
-#pragma unroll
-        for (int u = 0; u < 3; u++)
-#pragma unroll
-          for (int gate = 0; gate < 3; gate++)
-            cond_reg[u][gate] = ldg2(condA_f + (size_t)gs * kRowsA + gate * kN + (warp + u * kWarps) * 8 + 2 * t);
-      }
-
-      for (int step = 0; step < A.spf; step++) {
-        uint32_t *xa_cur = s_xa + cur * NS * kXaStride;
-        uint32_t *xa_new = s_xa + (cur ^ 1) * NS * kXaStride;
-        // ================= phase A: GRU-A =================
-#pragma unroll
-        for (int u = 0; u < 3; u++) {
-          const int ug = warp + u * kWarps;
-#pragma unroll
-          for (int mt = 0; mt < MT; mt++) {
-            const int sA = mt * VR + g;
-            int ac[2];
-            // (1) issue the gathers first: compute_gru_a_input (src/nnet.c:484-491) reads the frame
-            //     conditioning and one row of each embedding table; none of it feeds the recurrent product
-            float2 cv[3][NV / 2], e1[3][NV / 2], e2[3][NV / 2], e3[3][NV / 2];
-#pragma unroll
-            for (int h = 0; h < NV / 2; h++) {
-              const int s = sA + 8 * h;
-              const int us = s_usig[s], up = s_upred[s], le = s_lexc[s];
-              ac[h] = s_act[s];
-              const int gs = min(stream0 + s, B - 1);
-#pragma unroll
-              for (int gate = 0; gate < 3; gate++) {
-                const int col = gate * kN + ug * 8 + 2 * t;
-                if (CREG) cv[gate][h] = cond_reg[u][gate];
-                else cv[gate][h] = ldg2(condA_f + (size_t)gs * kRowsA + col);
-                e1[gate][h] = ldg2(M.e_sig + (size_t)us * kRowsA + col);
-                e2[gate][h] = ldg2(M.e_pred + (size_t)up * kRowsA + col);
-                e3[gate][h] = ldg2(M.e_exc + (size_t)le * kRowsA + col);
-              }
-            }
-            // (2) sparse_sgemv_accum8x4 (src/vec_avx.h:790-858) on tensor cores: the three gates' block
-            //     lists walked together so their MMA chains interleave.  The int32 sum is exact in any
-            //     order, so the rne(16256*t) seed of the AVX2 kernel is added afterwards.
-            int32_t acc[3][4];
-            int cb[3], ce[3];
-#pragma unroll
-            for (int gate = 0; gate < 3; gate++) {
-              acc[gate][0] = acc[gate][1] = acc[gate][2] = acc[gate][3] = 0;
-              cb[gate] = s_csA[gate * kUGroups + ug];
-              ce[gate] = s_csA[gate * kUGroups + ug + 1];
-            }
-            const int nmax = max(max(ce[0] - cb[0], ce[1] - cb[1]), ce[2] - cb[2]);
-            const uint32_t *xrow = xa_cur + sA * kXaStride;
-            for (int k = 0; k < nmax; k++) {
-#pragma unroll
-              for (int gate = 0; gate < 3; gate++) {
-                const int c = cb[gate] + k;
-                if (c < ce[gate]) {
-                  const uint2 pp = s_posA[c];
-                  const uint32_t b0 = s_wA[c * 64 + lane], b1 = s_wA[c * 64 + 32 + lane];
-                  const uint32_t plo = (pp.x >> (8 * t)) & 0xffu, phi = (pp.y >> (8 * t)) & 0xffu;
-                  const uint32_t a0 = xrow[plo], a2 = xrow[phi];
-                  uint32_t a1 = 0, a3 = 0;
-                  if (VR == 16) { a1 = xrow[8 * kXaStride + plo]; a3 = xrow[8 * kXaStride + phi]; }
-                  mma_u8s8(acc[gate], a0, a1, a2, a3, b0, b1);
-                }
-              }
-            }
-            // (3) seeds and gates: compute_sparse_gru (src/nnet.c:431-447)
-            float gh[NV];
-#pragma unroll
-            for (int gate = 0; gate < 3; gate++) {
-              const int col = gate * kN + ug * 8 + 2 * t;
-              const float2 sub = *reinterpret_cast<const float2 *>(s_subA + col);
-              const float2 dg = *reinterpret_cast<const float2 *>(s_diagA + col);
-#pragma unroll
-              for (int h = 0; h < NV / 2; h++) {
-                const float gx = ((cv[gate][h].x + e1[gate][h].x) + e2[gate][h].x) + e3[gate][h].x;
-                const float gy = ((cv[gate][h].y + e1[gate][h].y) + e2[gate][h].y) + e3[gate][h].y;
-                const float ax = a_reg[u][mt][2 * h], ay = a_reg[u][mt][2 * h + 1];
-                float tx = sub.x + dg.x * ax, ty = sub.y + dg.y * ay;   // bias + diag*state
-                if (gate < 2) { tx = tx + gx; ty = ty + gy; }           // (+ input for z, r)
-                else { gh[2 * h] = gx; gh[2 * h + 1] = gy; }
-                acc[gate][2 * h] = (int32_t)((uint32_t)acc[gate][2 * h] + (uint32_t)acc_seed(tx));
-                acc[gate][2 * h + 1] = (int32_t)((uint32_t)acc[gate][2 * h + 1] + (uint32_t)acc_seed(ty));
-              }
-            }
-#pragma unroll
-            for (int k = 0; k < NV; k++) {
-              const float z = sigmoid_ref(acc_out(acc[0][k]), s_rcp);
-              const float r = sigmoid_ref(acc_out(acc[1][k]), s_rcp);
-              float hh = acc_out(acc[2][k]) * r + gh[k];
-              hh = tanh_ref(hh, s_rcp);
-              const float a_old = a_reg[u][mt][k];
-              const float a_nw = z * a_old + (1.f - z) * hh;
-              a_reg[u][mt][k] = ac[k >> 1] ? a_nw : a_old;
-            }
-#pragma unroll
-            for (int h = 0; h < NV / 2; h++) {
-              // an inactive stream keeps the byte it already has (its state did not move)
-              if (ac[h]) {
-                const uint32_t q = quant_u8_fast(a_reg[u][mt][2 * h]) | (quant_u8_fast(a_reg[u][mt][2 * h + 1]) << 8);
-                reinterpret_cast<unsigned short *>(xa_new)[((sA + 8 * h) * kXaStride * 4 + ug * 8 + 2 * t) >> 1] = (unsigned short)q;
-              } else {
-                reinterpret_cast<unsigned short *>(xa_new)[((sA + 8 * h) * kXaStride * 4 + ug * 8 + 2 * t) >> 1] =
-                    reinterpret_cast<const unsigned short *>(xa_cur)[((sA + 8 * h) * kXaStride * 4 + ug * 8 + 2 * t) >> 1];
-              }
-            }
-          }
-        }
-        __syncthreads();
-        // ================= phase B1: GRU-B products =================
-        {
-          constexpr int JOBS_PER_MT = kRGroupsB * (P + 1);
-          for (int job = warp; job < MT * JOBS_PER_MT; job += kWarps) {
-            const int mt = job / JOBS_PER_MT, r = job % JOBS_PER_MT;
-            const int rg = r / (P + 1), kind = r % (P + 1);
-            const int sA = mt * VR + g;
-            int32_t acc[4] = {0, 0, 0, 0};
-            if (kind < P) {
-              const int cs = s_csBi[rg], n = s_csBi[rg + 1] - cs;
-              const int lo = cs + (n * kind) / P, hi = cs + (n * (kind + 1)) / P;
-              const uint32_t *xrow = xa_new + sA * kXaStride;
-              for (int c = lo; c < hi; c++) {
-                const uint2 pp = s_posBi[c];
-                const uint32_t b0 = s_wBi[c * 64 + lane], b1 = s_wBi[c * 64 + 32 + lane];
-                const uint32_t plo = (pp.x >> (8 * t)) & 0xffu, phi = (pp.y >> (8 * t)) & 0xffu;
-                const uint32_t a0 = xrow[plo], a2 = xrow[phi];
-                uint32_t a1 = 0, a3 = 0;
-                if (VR == 16) { a1 = xrow[8 * kXaStride + plo]; a3 = xrow[8 * kXaStride + phi]; }
-                mma_u8s8(acc, a0, a1, a2, a3, b0, b1);
-              }
-            } else {
-              const uint32_t *xrow = s_xb + sA * kXbStride;
-              for (int c = s_csBr[rg]; c < (int)s_csBr[rg + 1]; c++) {
-                const uint2 pp = s_posBr[c];
-                const uint32_t b0 = s_wBr[c * 64 + lane], b1 = s_wBr[c * 64 + 32 + lane];
-                const uint32_t plo = (pp.x >> (8 * t)) & 0xffu, phi = (pp.y >> (8 * t)) & 0xffu;
-                const uint32_t a0 = xrow[plo], a2 = xrow[phi];
-                uint32_t a1 = 0, a3 = 0;
-                if (VR == 16) { a1 = xrow[8 * kXbStride + plo]; a3 = xrow[8 * kXbStride + phi]; }
-                mma_u8s8(acc, a0, a1, a2, a3, b0, b1);
-              }
-            }
-            int32_t *dst = s_part + ((mt * (P + 1) + kind) * kRGroupsB + rg) * 128;
-            *reinterpret_cast<int2 *>(dst + g * 8 + 2 * t) = make_int2(acc[0], acc[1]);
-            if (VR == 16) *reinterpret_cast<int2 *>(dst + (g + 8) * 8 + 2 * t) = make_int2(acc[2], acc[3]);
-          }
-        }
-        __syncthreads();
-        // ================= phase B2 + T: GRU-B gates, sampling, signal update =================
-        {
-          const int l16 = tid & 15, grp = tid >> 4;
-          const unsigned gbase = lane & 16;
-          for (int s = grp; s < ((NS + 1) & ~1); s += kThreads / 16) {
-            // pairs of streams share a warp; NS is even so both halves are valid together
-            const int mt = s / VR, row = s % VR;
-            const int act = s_act[s];
-            // compute_gruB (src/nnet.c:326-372)
-            float zrh[3], rec[3];
-#pragma unroll
-            for (int gate = 0; gate < 3; gate++) {
-              const int i = gate * kNB + l16;
-              const int rg = gate * 2 + (l16 >> 3);
-              const int e = row * 8 + (l16 & 7);
-              int32_t ai = acc_seed(s_subB[i] + s_condb[s * kRowsB + i]);
-#pragma unroll
-              for (int kind = 0; kind < P; kind++) ai += s_part[((mt * (P + 1) + kind) * kRGroupsB + rg) * 128 + e];
-              zrh[gate] = acc_out(ai);
-              const int32_t ar = acc_seed(s_subB[kRowsB + i]) + s_part[((mt * (P + 1) + P) * kRGroupsB + rg) * 128 + e];
-              rec[gate] = acc_out(ar);
-            }
-            const float z = sigmoid_ref(zrh[0] + rec[0], s_rcp);
-            const float r = sigmoid_ref(zrh[1] + rec[1], s_rcp);
-            const float hh = tanh_ref(zrh[2] + rec[2] * r, s_rcp);
-            const float b_old = s_bst[s * 20 + l16];
-            const float b_new = z * b_old + (1.f - z) * hh;
-            __syncwarp();
-            if (act) {
-              s_bst[s * 20 + l16] = b_new;
-              reinterpret_cast<unsigned char *>(s_xb)[s * kXbStride * 4 + l16] = (unsigned char)quant_u8_fast(b_new);
-            }
-            __syncwarp();
-            // sample_mdense (src/nnet.c:163-214)
-            uint32_t r0 = 0, r1 = 0;
-            if (l16 == 0) {
-              uint32_t zz = s_rng[s], ww = s_rng[NS + s], js = s_rng[2 * NS + s], jc = s_rng[3 * NS + s];
-              r0 = kiss99_next(zz, ww, js, jc);
-              r1 = kiss99_next(zz, ww, js, jc);
-              if (act) { s_rng[s] = zz; s_rng[NS + s] = ww; s_rng[2 * NS + s] = js; s_rng[3 * NS + s] = jc; }
-            }
-            r0 = __shfl_sync(0xffffffffu, r0, gbase);
-            r1 = __shfl_sync(0xffffffffu, r1, gbase);
-            float bv[16];
-#pragma unroll
-            for (int k = 0; k < 4; k++) {
-              const float4 v = *reinterpret_cast<const float4 *>(s_bst + s * 20 + 4 * k);
-              bv[4 * k] = v.x; bv[4 * k + 1] = v.y; bv[4 * k + 2] = v.z; bv[4 * k + 3] = v.w;
-            }
-            const int m = l16 ? l16 : 1;              // heap index within a depth-4 subtree (lane 0 idles on node 1)
-            const int d = 31 - __clz(m);
-            // round 1: levels 0..3, nodes 1..15
-            int bit = s_logit[(r0 >> (8 * d)) & 0xffu] < node_logit<FCS>(fc_w, fc_stride, fc_bf, m, bv, s_rcp);
-            int n = 1;
-#pragma unroll
-            for (int lvl = 0; lvl < 4; lvl++) n = 2 * n + __shfl_sync(0xffffffffu, bit, gbase + n);
-            // round 2: levels 4..7 below node n
-            const int node = (n << d) | (m - (1 << d));
-            bit = s_logit[(r1 >> (8 * d)) & 0xffu] < node_logit<FCS>(fc_w, fc_stride, fc_bf, node, bv, s_rcp);
-            int mm = 1;
-#pragma unroll
-            for (int lvl = 0; lvl < 4; lvl++) mm = 2 * mm + __shfl_sync(0xffffffffu, bit, gbase + mm);
-            int exc = ((n - 16) << 4) | (mm - 16);
-            if (DEBUG && A.logits && stream0 + s < B) {
-              float *lg = A.logits + ((size_t)(stream0 + s) * row_len + out_base + step) * 256;
-              for (int k = 0; k < 16; k++) {
-                const int nd = k * 16 + l16;
-                lg[nd] = (nd == 0 || !act) ? 0.f : node_logit<FCS>(fc_w, fc_stride, fc_bf, nd, bv, s_rcp);
-              }
-            }
-            // signal update (src/lpcnet.c:256-269), one lane per stream
-            if (l16 == 0 && stream0 + s < B) {
-              const size_t oidx = (size_t)(stream0 + s) * row_len + out_base + step;
-              if (!act) {
-                A.pcm[oidx] = 0;
-                if (DEBUG && A.trace) {
-                  LPCNetB200Trace tr = {0, 0, 0, 0, 0, 0, 0, 0};
-                  reinterpret_cast<LPCNetB200Trace *>(A.trace)[oidx] = tr;
-                }
-              } else {
-                const float pred = s_pred[s];
-                const float dm = s_deemph[s];
-                float pcm;
-                int outv;
-                if (A.forced) {
-                  const float fo = (float)A.forced[oidx];
-                  exc = lin2ulaw_ref(fo - 0.85f * dm - pred);
-                  pcm = fo - 0.85f * dm;
-                } else {
-                  pcm = pred + s_u2l[exc];
-                }
-                const int head = (s_head[s] + 15) & 15;
-                s_head[s] = head;
-                s_lsig[head * NS + s] = pcm;
-                s_lexc[s] = exc;
-                pcm = pcm + 0.85f * dm;
-                s_deemph[s] = pcm;
-                if (pcm < -32767.f) pcm = -32767.f;
-                if (pcm > 32767.f) pcm = 32767.f;
-                if (A.forced) outv = A.forced[oidx];
-                else outv = round_half_up_ref(pcm);
-                A.pcm[oidx] = (short)outv;
-                if (DEBUG && A.trace) {
-                  LPCNetB200Trace tr;
-                  tr.exc = exc; tr.u_sig = s_usig[s]; tr.u_pred = s_upred[s];
-                  tr.rng_z = s_rng[s]; tr.rng_w = s_rng[NS + s];
-                  tr.xa_hash = fnv1a_bytes(reinterpret_cast<const unsigned char *>(xa_new + s * kXaStride), kN);
-                  tr.xb_hash = fnv1a_bytes(reinterpret_cast<const unsigned char *>(s_xb + s * kXbStride), kNB);
-                  tr.pcm = outv;
-                  reinterpret_cast<LPCNetB200Trace *>(A.trace)[oidx] = tr;
-                }
-                if (step + 1 < A.spf) predict(s);
-              }
-            }
-          }
-        }
-        __syncthreads();
-        cur ^= 1;
-      }  // step
-    }    // frame
-
-    // ---- store the tile's stream state ----
-#pragma unroll
-    for (int u = 0; u < 3; u++) {
-      const int ug = warp + u * kWarps;
-#pragma unroll
-      for (int mt = 0; mt < MT; mt++)
-#pragma unroll
-        for (int k = 0; k < NV; k++) {
-          const int s = mt * VR + g + (k >> 1) * 8;
-          if (stream0 + s < B) A.st.gru_a[(size_t)(stream0 + s) * kN + ug * 8 + 2 * t + (k & 1)] = a_reg[u][mt][k];
-        }
-    }
-    for (int i = tid; i < NS * 16; i += kThreads) {
-      const int s = i >> 4, j = i & 15;
-      if (stream0 + s < B) {
-        A.st.gru_b[(size_t)(stream0 + s) * kNB + j] = s_bst[s * 20 + j];
-        A.st.last_sig[(size_t)(stream0 + s) * 16 + j] = s_lsig[((s_head[s] + j) & 15) * NS + s];
-      }
-    }
-    for (int s = tid; s < NS; s += kThreads) {
-      if (stream0 + s < B) {
-        A.st.deemph[stream0 + s] = s_deemph[s];
-        A.st.last_exc[stream0 + s] = s_lexc[s];
-#pragma unroll
-        for (int k = 0; k < 4; k++) A.st.rng[(size_t)(stream0 + s) * 4 + k] = s_rng[k * NS + s];
-      }
-    }
-  }  // tile
-}
+cudaError_t launch_sample_t8(const SampleArgs &a, int n_sms, cudaStream_t s);
+cudaError_t launch_sample_t16(const SampleArgs &a, int n_sms, cudaStream_t s);
+cudaError_t launch_sample_t32(const SampleArgs &a, int n_sms, cudaStream_t s);
+cudaError_t launch_sample_t64(const SampleArgs &a, int n_sms, cudaStream_t s);
 
 size_t sample_kernel_smem(int tile_streams, const DevModel &m) {
   const int VR = tile_streams == 8 ? 8 : 16;
@@ -584,27 +14,13 @@ size_t sample_kernel_smem(int tile_streams, const DevModel &m) {
   return make_layout(tile_streams, MT, m.a_rec.n_chunks, m.b_in.n_chunks, m.b_rec.n_chunks).total;
 }
 
-template <int MT, int VR>
-static cudaError_t launch_t(const SampleArgs &a, int n_sms, cudaStream_t s) {
-  const int NS = MT * VR;
-  const size_t smem = make_layout(NS, MT, a.m.a_rec.n_chunks, a.m.b_in.n_chunks, a.m.b_rec.n_chunks).total;
-  const bool dbg = a.trace || a.logits;
-  auto kern = dbg ? sample_kernel<MT, VR, true> : sample_kernel<MT, VR, false>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return e;
-  const int n_tiles = (a.n_streams + NS - 1) / NS;
-  const int grid = n_tiles < n_sms ? n_tiles : n_sms;
-  kern<<<grid, kThreads, smem, s>>>(a);
-  return cudaGetLastError();
-}
-
 cudaError_t launch_sample_kernel(const SampleArgs &a, int tile_streams, int n_sms, cudaStream_t s, int *n_launches) {
   cudaError_t e;
   switch (tile_streams) {
-    case 8: e = launch_t<1, 8>(a, n_sms, s); break;
-    case 16: e = launch_t<1, 16>(a, n_sms, s); break;
-    case 32: e = launch_t<2, 16>(a, n_sms, s); break;
-    case 64: e = launch_t<4, 16>(a, n_sms, s); break;
+    case 8: e = launch_sample_t8(a, n_sms, s); break;
+    case 16: e = launch_sample_t16(a, n_sms, s); break;
+    case 32: e = launch_sample_t32(a, n_sms, s); break;
+    case 64: e = launch_sample_t64(a, n_sms, s); break;
     default: return cudaErrorInvalidValue;
   }
   if (e == cudaSuccess && n_launches) ++*n_launches;

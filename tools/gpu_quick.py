@@ -36,6 +36,7 @@ def main():
                         print("  stream", s, "first diff step", bad[0], tr[s][bad[0]], ref[s][1][bad[0]]); break
             bt.close()
     print("PARITY", "OK" if allok else "FAILED", flush=True)
+    if os.environ.get("QUICK_NO_TIMING"): return
     cfgs = [(1024, 8), (2048, 16), (4096, 32), (4736, 32), (9472, 64)]
     if len(sys.argv) > 1:
         cfgs = [tuple(int(x) for x in a.split(":")) for a in sys.argv[1:]]
