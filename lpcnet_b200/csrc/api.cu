@@ -64,6 +64,7 @@ struct LPCNetBatch {
   int n_streams = 0;
   int n_sms = 0;
   int tile = 0;  // 0 = auto
+  int max_tile = 64;
   Model model;
   DevState st{};
   void *st_alloc = nullptr;
@@ -145,10 +146,10 @@ int ensure_frame_buffers(LPCNetBatch *b, int F) {
 int auto_tile(const LPCNetBatch *b) {
   if (b->tile) return b->tile;
   const int B = b->n_streams, sms = b->n_sms;
-  if (B <= 8 * sms) return 8;
-  if (B <= 16 * sms) return 16;
-  if (B <= 32 * sms) return 32;
-  return 64;
+  int t = 32;   // 32 streams per CTA is the throughput optimum (measured); smaller batches spread over all SMs
+  if (B <= 8 * sms) t = 8;
+  else if (B <= 16 * sms) t = 16;
+  return t < b->max_tile ? t : b->max_tile;
 }
 
 // frame network for frames [f0, f0+F) of the call, results left in b->fb
@@ -259,8 +260,11 @@ LPCNetBatch *lpcnet_batch_create(const unsigned char *blob, int len, int n_strea
     delete b;
     return nullptr;
   }
-  const size_t need = sample_kernel_smem(64, b->model.d);
-  if (need > (size_t)prop.sharedMemPerBlockOptin) {
+  // largest streams-per-CTA tile whose resident weights + per-stream buffers fit this GPU's shared memory
+  b->max_tile = 0;
+  for (int t : {64, 32, 16, 8})
+    if (!b->max_tile && sample_kernel_smem(t, b->model.d) <= (size_t)prop.sharedMemPerBlockOptin) b->max_tile = t;
+  if (!b->max_tile) {
     fail("model does not fit the shared-memory-resident kernel on this GPU");
     free_model(b->model); delete b;
     return nullptr;
@@ -300,6 +304,7 @@ int lpcnet_batch_set_cuda_stream(LPCNetBatch *b, void *s) {
 int lpcnet_batch_set_tile(LPCNetBatch *b, int t) {
   if (!b) return fail("null batch");
   if (t != 0 && t != 8 && t != 16 && t != 32 && t != 64) return fail("tile must be 0, 8, 16, 32 or 64");
+  if (t > b->max_tile) return fail("tile does not fit in shared memory for this model");
   b->tile = t;
   return 0;
 }

@@ -207,7 +207,7 @@ def test_other_density_model(eng, orclib):
     feats = np.stack([blob.synthetic_features(F, 40 + s) for s in range(B)])
     seeds = [blob.stream_seed(40 + s) for s in range(B)]
     ref = oracle_run(om, feats, seeds)
-    for tile in (8, 32):
+    for tile in (8, 16):
         bt = eng.Batch(b, B)
         bt.set_tile(tile)
         assert bt.nblocks_a == om.nblocks_a and bt.nblocks_b == om.nblocks_b
