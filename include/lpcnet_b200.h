@@ -160,7 +160,9 @@ LPCNET_B200_EXPORT int lpcnet_batch_set_codebooks(LPCNetBatch *b, const float *c
 LPCNET_B200_EXPORT int lpcnet_batch_get_state(LPCNetBatch *b, int stream, LPCNetB200StreamState *out);
 LPCNET_B200_EXPORT int lpcnet_batch_set_state(LPCNetBatch *b, int stream, const LPCNetB200StreamState *in);
 LPCNET_B200_EXPORT int lpcnet_batch_sync(LPCNetBatch *b);
-/* Number of block-sparse 8x4 blocks in GRU-A / GRU-B input (for the op counts). */
+/* Model facts.  which = 0 / 1: number of block-sparse 8x4 blocks in GRU-A / GRU-B input (for the op
+ * counts); 2: 1 when the rcpps estimate is computed arithmetically (the table was verified equal on this
+ * GPU), 0 when looked up; 3: 1 when GRU-A runs the unrolled fixed-slot path; 4: GRU-A chunks of 8 blocks. */
 LPCNET_B200_EXPORT int lpcnet_batch_nblocks(const LPCNetBatch *b, int which);
 /* Kernels launched by this batch so far (for bench.py's gpu_launches). */
 LPCNET_B200_EXPORT long long lpcnet_batch_launch_count(const LPCNetBatch *b);

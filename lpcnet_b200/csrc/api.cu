@@ -292,7 +292,17 @@ void lpcnet_batch_destroy(LPCNetBatch *b) {
 }
 
 int lpcnet_batch_n_streams(const LPCNetBatch *b) { return b ? b->n_streams : 0; }
-int lpcnet_batch_nblocks(const LPCNetBatch *b, int which) { return !b ? 0 : (which == 0 ? b->model.nblocks_a : b->model.nblocks_b); }
+int lpcnet_batch_nblocks(const LPCNetBatch *b, int which) {
+  if (!b) return 0;
+  switch (which) {
+    case 0: return b->model.nblocks_a;
+    case 1: return b->model.nblocks_b;
+    case 2: return b->model.d.rcp_arith;               // 1: reciprocal estimate computed, 0: table lookup
+    case 3: return b->model.d.a_rec.slots[2] != 0;     // 1: GRU-A runs the unrolled fixed-slot path
+    case 4: return b->model.d.a_rec.n_chunks;
+    default: return 0;
+  }
+}
 long long lpcnet_batch_launch_count(const LPCNetBatch *b) { return b ? b->launches : 0; }
 
 int lpcnet_batch_set_cuda_stream(LPCNetBatch *b, void *s) {
@@ -454,6 +464,16 @@ int lpcnet_batch_frame_network(LPCNetBatch *b, const float *features, int stride
       return 0;
     };
     if (fetch(ga, b->fb.cond_a, kRowsA) || fetch(gb, b->fb.cond_b, kRowsB) || fetch(lpc, b->fb.lpc, 16)) return -1;
+    if (ga) {
+      // back to the reference's column order (the device rows are in gru_a_col_index order)
+      float tmp[kRowsA];
+      for (size_t s = 0; s < (size_t)B; s++)
+        for (int f = 0; f < F; f++) {
+          float *row = ga + (s * n_frames + f0 + f) * kRowsA;
+          memcpy(tmp, row, sizeof(tmp));
+          for (int col = 0; col < kRowsA; col++) row[col] = tmp[gru_a_col_index(col)];
+        }
+    }
   }
   return 0;
 }
@@ -499,7 +519,11 @@ int lpcnet_batch_get_state(LPCNetBatch *b, int s, LPCNetB200StreamState *o) {
   CK(cudaMemcpy(o->last_sig, S.last_sig + (size_t)s * 16, 64, cudaMemcpyDeviceToHost));
   CK(cudaMemcpy(o->lpc, S.lpc + (size_t)s * 16, 64, cudaMemcpyDeviceToHost));
   CK(cudaMemcpy(o->old_lpc, S.old_lpc + (size_t)s * kMaxDelay * 16, (size_t)b->model.d.features_delay * 64, cudaMemcpyDeviceToHost));
-  CK(cudaMemcpy(o->gru_a_condition, S.cond_a + (size_t)s * kRowsA, kRowsA * 4, cudaMemcpyDeviceToHost));
+  {
+    float tmp[kRowsA];
+    CK(cudaMemcpy(tmp, S.cond_a + (size_t)s * kRowsA, kRowsA * 4, cudaMemcpyDeviceToHost));
+    for (int col = 0; col < kRowsA; col++) o->gru_a_condition[col] = tmp[gru_a_col_index(col)];
+  }
   CK(cudaMemcpy(o->gru_b_condition, S.cond_b + (size_t)s * kRowsB, kRowsB * 4, cudaMemcpyDeviceToHost));
   CK(cudaMemcpy(&o->deemph_mem, S.deemph + s, 4, cudaMemcpyDeviceToHost));
   CK(cudaMemcpy(&o->last_exc, S.last_exc + s, 4, cudaMemcpyDeviceToHost));
@@ -521,7 +545,11 @@ int lpcnet_batch_set_state(LPCNetBatch *b, int s, const LPCNetB200StreamState *i
   CK(cudaMemcpy(S.last_sig + (size_t)s * 16, in->last_sig, 64, cudaMemcpyHostToDevice));
   CK(cudaMemcpy(S.lpc + (size_t)s * 16, in->lpc, 64, cudaMemcpyHostToDevice));
   CK(cudaMemcpy(S.old_lpc + (size_t)s * kMaxDelay * 16, in->old_lpc, (size_t)b->model.d.features_delay * 64, cudaMemcpyHostToDevice));
-  CK(cudaMemcpy(S.cond_a + (size_t)s * kRowsA, in->gru_a_condition, kRowsA * 4, cudaMemcpyHostToDevice));
+  {
+    float tmp[kRowsA];
+    for (int col = 0; col < kRowsA; col++) tmp[gru_a_col_index(col)] = in->gru_a_condition[col];
+    CK(cudaMemcpy(S.cond_a + (size_t)s * kRowsA, tmp, kRowsA * 4, cudaMemcpyHostToDevice));
+  }
   CK(cudaMemcpy(S.cond_b + (size_t)s * kRowsB, in->gru_b_condition, kRowsB * 4, cudaMemcpyHostToDevice));
   CK(cudaMemcpy(S.deemph + s, &in->deemph_mem, 4, cudaMemcpyHostToDevice));
   CK(cudaMemcpy(S.last_exc + s, &in->last_exc, 4, cudaMemcpyHostToDevice));

@@ -15,8 +15,21 @@ __device__ __forceinline__ float rcp_estimate(float x, const uint32_t *__restric
   return __uint_as_float(tab[(b >> 12) & 0x7ffu] - ((e - 127u) << 23));
 }
 
+// The default table without the lookup: entry i is 1/(mid-point of bucket i) rounded half-up to 12
+// mantissa bits, so MUFU.RCP of the mid-point (exponent kept) plus an integer rounding gives the same
+// bits whenever the hardware estimate lands on the right side of every rounding boundary -- which
+// model.cu checks exhaustively on the GPU at load before a kernel variant using this is chosen.
+struct RcpArith {};
+__device__ __forceinline__ float rcp_estimate(float x, RcpArith) {
+  const float mid = __uint_as_float((__float_as_uint(x) & 0xfffff000u) | 0x800u);
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(mid));
+  return __uint_as_float((__float_as_uint(r) + 0x400u) & 0xfffff800u);
+}
+
 // tanh8_approx (src/vec_avx.h:393-411)
-__device__ __forceinline__ float tanh_ref(float x, const uint32_t *__restrict__ tab) {
+template <class R>
+__device__ __forceinline__ float tanh_ref(float x, R tab) {
   const float N0 = 952.52801514f, N1 = 96.39235687f, N2 = 0.60863042f;
   const float D0 = 952.72399902f, D1 = 413.36801147f, D2 = 11.88600922f;
   float X2 = x * x;
@@ -30,7 +43,8 @@ __device__ __forceinline__ float tanh_ref(float x, const uint32_t *__restrict__ 
 }
 
 // sigmoid8_approx (src/vec_avx.h:421-440)
-__device__ __forceinline__ float sigmoid_ref(float x, const uint32_t *__restrict__ tab) {
+template <class R>
+__device__ __forceinline__ float sigmoid_ref(float x, R tab) {
   const float N0 = 238.13200378f, N1 = 6.02452230f, N2 = 0.00950985f;
   const float D0 = 952.72399902f, D1 = 103.34200287f, D2 = 0.74287558f;
   float X2 = x * x;
@@ -161,7 +175,8 @@ __device__ __forceinline__ float2 f2_mul(float2 a, float2 b) {
 __device__ __forceinline__ float2 f2_set(float v) { return make_float2(v, v); }
 
 // tanh8_approx / sigmoid8_approx on a pair
-__device__ __forceinline__ float2 tanh2_ref(float2 x, const uint32_t *__restrict__ tab) {
+template <class R>
+__device__ __forceinline__ float2 tanh2_ref(float2 x, R tab) {
   const float2 X2 = f2_mul(x, x);
   float2 num = f2_fma(f2_fma(f2_set(0.60863042f), X2, f2_set(96.39235687f)), X2, f2_set(952.52801514f));
   float2 den = f2_fma(f2_fma(f2_set(11.88600922f), X2, f2_set(413.36801147f)), X2, f2_set(952.72399902f));
@@ -171,7 +186,8 @@ __device__ __forceinline__ float2 tanh2_ref(float2 x, const uint32_t *__restrict
   num.x = fmaxf(-1.f, fminf(1.f, num.x)); num.y = fmaxf(-1.f, fminf(1.f, num.y));
   return num;
 }
-__device__ __forceinline__ float2 sigmoid2_ref(float2 x, const uint32_t *__restrict__ tab) {
+template <class R>
+__device__ __forceinline__ float2 sigmoid2_ref(float2 x, R tab) {
   const float2 X2 = f2_mul(x, x);
   float2 num = f2_fma(f2_fma(f2_set(0.00950985f), X2, f2_set(6.02452230f)), X2, f2_set(238.13200378f));
   float2 den = f2_fma(f2_fma(f2_set(0.74287558f), X2, f2_set(103.34200287f)), X2, f2_set(952.72399902f));

@@ -21,10 +21,21 @@ constexpr int kMaxDelay = 2;
 constexpr int kRowsA = 3 * kN;   // 1152
 constexpr int kRowsB = 3 * kNB;  // 48
 
-// u8 activation rows in shared memory are padded to an odd word stride so that the
-// per-lane 4-byte gathers of the MMA A fragments spread over the banks.
-constexpr int kXaStride = kN / 4 + 1;    // words per stream
-constexpr int kXbStride = kNB / 4 + 1;
+// u8 activation rows in shared memory, word stride = 4 (mod 32): in a 4-byte gather of an MMA A
+// fragment lane (g, t) reads word 100*g + w[t], i.e. bank 4*g + w[t]; the eight streams of one t
+// cover the banks of one residue class mod 4, so a gather is conflict-free when its four block
+// positions have distinct residues -- model.cu orders every chunk's blocks that way.
+constexpr int kXaStride = kN / 4 + 4;    // words per stream (100)
+constexpr int kXbStride = kNB / 4;       // 4: eight streams x four words = 32 distinct banks
+
+// Column order of the GRU-A input rows (embedding tables, frame conditioning) in device memory:
+// the z and r values a lane needs sit in one 16-byte piece, [ug][t][z0 z1 r0 r1], followed by the
+// candidate gate in natural order.  col = gate*384 + unit  ->  storage index.
+__host__ __device__ inline int gru_a_col_index(int col) {
+  const int gate = col / kN, unit = col % kN;
+  if (gate == 2) return col;
+  return (unit >> 3) * 16 + ((unit & 7) >> 1) * 4 + gate * 2 + (unit & 1);
+}
 
 // Block-sparse int8 matrix re-tiled for mma.sync.m16n8k32 B fragments.
 // A "chunk" is 8 blocks (K = 32) of one 8-row group.
@@ -62,7 +73,7 @@ struct DevModel {
   const float *a_feat_w, *a_feat_b;         // [128][1152], [1152]
   const float *b_feat_w, *b_feat_b;         // [128][48], [48]
   // 16 kHz sample network
-  const float *e_sig, *e_pred, *e_exc;      // [256][1152]
+  const float *e_sig, *e_pred, *e_exc;      // [256][1152], columns in gru_a_col_index order
   const float *a_subias_rec;                // [1152] = &sparse_gru_a_subias[3N]
   const float *a_diag;                      // [1152]
   DevSparse a_rec;                          // 1152 x 384 block-sparse
@@ -71,6 +82,7 @@ struct DevModel {
   DevSparse b_rec;                          // 48 x 16 dense
   const float *fc_w, *fc_bias, *fc_factor;  // [256][2][16], [2][256], [2][256]
   const uint32_t *rcp_tab;                  // [2048]
+  int rcp_arith;                            // 1: the table equals mid-point MUFU.RCP rounded to 12 bits (checked on this GPU)
   const float *ulaw2lin_tab;                // [256]
   const float *logit_tab;                   // [256]
   // DSP tables
@@ -91,7 +103,7 @@ struct DevState {
   float *last_sig;      // [B][16]
   float *old_lpc;       // [B][2][16]
   float *lpc;           // [B][16]      (current frame)
-  float *cond_a;        // [B][1152]    (current frame)
+  float *cond_a;        // [B][1152]    (current frame), gru_a_col_index order
   float *cond_b;        // [B][48]
   float *deemph;        // [B]
   int *last_exc;        // [B]
@@ -122,7 +134,7 @@ struct FrameBuffers {
   int cap_frames = 0;
   float *in_vec = nullptr;   // [B][F+2][84]   frame-network input rows incl. 2 history rows
   float *c1 = nullptr;       // [B][F+2][128]  conv1 outputs incl. 2 history rows
-  float *cond_a = nullptr;   // [F][B][1152]
+  float *cond_a = nullptr;   // [F][B][1152], gru_a_col_index order
   float *cond_b = nullptr;   // [F][B][48]
   float *lpc = nullptr;      // [F][B][16]
   uint8_t *active = nullptr; // [F][B]
@@ -137,7 +149,7 @@ struct SampleArgs {
   int spf;                   // samples per frame (<=160)
   int frame0;                // index of the chunk's first frame within the call
   int total_frames;          // frames in the whole call (pcm row length = total_frames*spf)
-  const float *cond_a;       // [F][B][1152]
+  const float *cond_a;       // [F][B][1152], gru_a_col_index order
   const float *cond_b;       // [F][B][48]
   const float *lpc;          // [F][B][16]
   const uint8_t *active;     // [F][B]

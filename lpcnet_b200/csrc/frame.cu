@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(kFT) cond_kernel(FrameArgs A) {
       if (blockIdx.x * R + r >= total) break;
       float *dst = isA ? A.fb.cond_a + ((size_t)row_f[r] * B + row_s[r]) * kRowsA
                        : A.fb.cond_b + ((size_t)row_f[r] * B + row_s[r]) * kRowsB;
-      dst[col] = acc[r];
+      dst[isA ? gru_a_col_index(col) : col] = acc[r];   // GRU-A conditioning in the sample kernel's gather order
     }
   }
 }

@@ -7,9 +7,11 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <map>
 
 #include "engine.h"
+#include "bitexact.cuh"
 
 namespace lpcb {
 
@@ -96,13 +98,39 @@ bool pack_sparse(PackedSparse &ps, const int32_t *idx, int idx_len, const int8_t
     for (int g = 0; g < ps.n_groups; g++)
       for (size_t b = 0; b < gpos[g].size(); b++, wp += 32) gw[g].push_back(wp);
   }
-  auto emit = [&](int c, int slot, int pos, const int8_t *blk) {
-    ps.pos[(size_t)c * 8 + slot] = (uint8_t)(pos / 4);
+  // Order every row group's blocks so that each run of four (one 4-byte gather per lane%4, engine.h
+  // kXaStride) has four distinct positions mod 4 wherever the group allows it; the int32 sum does not
+  // depend on the order.  Unused slots repeat a position of their own run (same word: a broadcast,
+  // not a conflict) with zero weights.
+  struct Slot { int pos; const int8_t *w; };
+  std::vector<std::vector<Slot>> gslots(ps.n_groups);
+  for (int g = 0; g < ps.n_groups; g++) {
+    const int n = (int)gpos[g].size(), Q = 2 * ((n + 7) / 8);
+    std::vector<std::vector<Slot>> quad(Q);
+    std::vector<Slot> bucket[4], left;
+    for (int b = 0; b < n; b++) bucket[(gpos[g][b] / 4) & 3].push_back(Slot{gpos[g][b], gw[g][b]});
+    for (int r = 0; r < 4; r++)
+      for (size_t k = 0; k < bucket[r].size(); k++) {
+        if ((int)k < Q) quad[k].push_back(bucket[r][k]);
+        else left.push_back(bucket[r][k]);
+      }
+    // fullest runs first, so the sparse ones (which absorb the leftovers) end up last
+    std::stable_sort(quad.begin(), quad.end(), [](const std::vector<Slot> &a, const std::vector<Slot> &b) { return a.size() > b.size(); });
+    for (int q = Q - 1; q >= 0 && !left.empty(); q--)
+      while (quad[q].size() < 4 && !left.empty()) { quad[q].push_back(left.back()); left.pop_back(); }
+    for (int q = 0; q < Q; q++) {
+      const int fill = quad[q].empty() ? 0 : quad[q][0].pos;
+      for (int k = 0; k < 4; k++) gslots[g].push_back(k < (int)quad[q].size() ? quad[q][k] : Slot{fill, nullptr});
+    }
+  }
+  auto emit = [&](int c, int slot, const Slot &sl) {
+    ps.pos[(size_t)c * 8 + slot] = (uint8_t)(sl.pos / 4);
+    if (!sl.w) return;
     // B fragment of mma.m16n8k32: register slot/4, lane = row*4 + slot%4 holds the four input
     // weights of output row `row` of block `slot`.
     for (int r = 0; r < 8; r++) {
       uint32_t word;
-      memcpy(&word, blk + r * 4, 4);
+      memcpy(&word, sl.w + r * 4, 4);
       ps.w[(size_t)c * 64 + (slot / 4) * 32 + r * 4 + (slot % 4)] = word;
     }
   };
@@ -117,7 +145,7 @@ bool pack_sparse(PackedSparse &ps, const int32_t *idx, int idx_len, const int8_t
     ps.pos.assign((size_t)nchunks * 8, 0);
     ps.w.assign((size_t)nchunks * 64, 0);
     for (int g = 0; g < ps.n_groups; g++)
-      for (int b = 0; b < (int)gpos[g].size(); b++) emit(ps.chunk_start[g] + b / 8, b % 8, gpos[g][b], gw[g][b]);
+      for (int b = 0; b < (int)gslots[g].size(); b++) emit(ps.chunk_start[g] + b / 8, b % 8, gslots[g][b]);
   } else {
     // rows are gate-major: group index = gate*(n_groups/3) + ug
     const int nug = ps.n_groups / 3;
@@ -148,9 +176,9 @@ bool pack_sparse(PackedSparse &ps, const int32_t *idx, int idx_len, const int8_t
       int slot0 = 0;
       for (int gate = 0; gate < 3; gate++) {
         const int g = gate * nug + ug, cap = 8 * ps.slots[gate];
-        for (int b = 0; b < (int)gpos[g].size(); b++) {
-          if (b < cap) emit(ug * ST + slot0 + b / 8, b % 8, gpos[g][b], gw[g][b]);
-          else emit(ps.chunk_start[ug * 3 + gate] + (b - cap) / 8, (b - cap) % 8, gpos[g][b], gw[g][b]);
+        for (int b = 0; b < (int)gslots[g].size(); b++) {
+          if (b < cap) emit(ug * ST + slot0 + b / 8, b % 8, gslots[g][b]);
+          else emit(ps.chunk_start[ug * 3 + gate] + (b - cap) / 8, (b - cap) % 8, gslots[g][b]);
         }
         slot0 += ps.slots[gate];
       }
@@ -173,6 +201,18 @@ void default_rcp_table(uint32_t *tab) {
     uint32_t q = (uint32_t)(((1ull << 26) / k + 1) >> 1);
     tab[i] = 0x3f000000u + ((q - 4096u) << 11);
   }
+}
+
+// every mantissa bucket (both ends of it) x every exponent the activations can produce, and far beyond
+__global__ void rcp_check_kernel(const uint32_t *tab, int *mismatch) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;   // bucket*2 + end
+  const uint32_t mant = ((i >> 1) << 12) | ((i & 1) ? 0xfffu : 0u);
+  int bad = 0;
+  for (uint32_t e = 8; e <= 246; e++) {
+    const float x = __uint_as_float((e << 23) | mant);
+    bad |= __float_as_uint(rcp_estimate(x, tab)) != __float_as_uint(rcp_estimate(x, RcpArith{}));
+  }
+  if (bad) atomicOr(mismatch, 1);
 }
 
 void free_model(Model &m) {
@@ -205,9 +245,20 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
   };
   DevModel &d = m.d;
   bool ok = true;
-  ok &= put_f(&d.e_sig, "gru_a_embed_sig_weights", 256 * kRowsA);
-  ok &= put_f(&d.e_pred, "gru_a_embed_pred_weights", 256 * kRowsA);
-  ok &= put_f(&d.e_exc, "gru_a_embed_exc_weights", 256 * kRowsA);
+  // embedding rows are stored in the column order the sample kernel's 16-byte gathers want
+  auto put_embed = [&](const float **dst, const char *name) -> bool {
+    const unsigned char *p = need(name, 256 * kRowsA * 4);
+    if (!p) return false;
+    std::vector<float> t((size_t)256 * kRowsA);
+    for (int v = 0; v < 256; v++)
+      for (int col = 0; col < kRowsA; col++)
+        memcpy(&t[(size_t)v * kRowsA + gru_a_col_index(col)], p + ((size_t)v * kRowsA + col) * 4, 4);
+    put(reinterpret_cast<const void **>(dst), t.data(), t.size() * 4);
+    return true;
+  };
+  ok &= put_embed(&d.e_sig, "gru_a_embed_sig_weights");
+  ok &= put_embed(&d.e_pred, "gru_a_embed_pred_weights");
+  ok &= put_embed(&d.e_exc, "gru_a_embed_exc_weights");
   ok &= put_f(&d.a_feat_b, "gru_a_dense_feature_bias", kRowsA);
   ok &= put_f(&d.a_feat_w, "gru_a_dense_feature_weights", kC * kRowsA);
   ok &= put_f(&d.b_feat_b, "gru_b_dense_feature_bias", kRowsB);
@@ -374,6 +425,19 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
   e = cudaMemcpy(m.dev_blob, B.buf.data(), B.buf.size(), cudaMemcpyHostToDevice);
   if (e != cudaSuccess) { err = std::string("cudaMemcpy(model): ") + cudaGetErrorString(e); free_model(m); return false; }
   for (auto &f : fixes) *f.dst = static_cast<const unsigned char *>(m.dev_blob) + f.off;
+  // The sample kernel may replace the table lookup by MUFU.RCP of the bucket mid-point rounded to 12
+  // mantissa bits -- only if that reproduces this table on this GPU for every bucket and exponent.
+  d.rcp_arith = 0;
+  if (!getenv("LPCNET_B200_RCP_TABLE")) {
+    int *flag = nullptr;
+    if (cudaMalloc(&flag, 4) == cudaSuccess) {
+      cudaMemset(flag, 0, 4);
+      rcp_check_kernel<<<2048 * 2 / 256, 256>>>(d.rcp_tab, flag);
+      int bad = 1;
+      if (cudaMemcpy(&bad, flag, 4, cudaMemcpyDeviceToHost) == cudaSuccess) d.rcp_arith = bad == 0;
+      cudaFree(flag);
+    }
+  }
   return true;
 }
 

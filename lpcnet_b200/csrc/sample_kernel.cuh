@@ -69,11 +69,29 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
 
 __device__ __forceinline__ float2 ldg2(const float *p) { return __ldg(reinterpret_cast<const float2 *>(p)); }
 
+// the six GRU-A input values of lane t for one unit group from a row in gru_a_col_index order
+// (engine.h): one 16-byte piece [z0 z1 r0 r1] and one 8-byte piece [h0 h1]
+__device__ __forceinline__ void ldg_zrh(const float *row, int ug, int t, float2 &z, float2 &r, float2 &h) {
+  const float4 zr = __ldg(reinterpret_cast<const float4 *>(row + ug * 16 + t * 4));
+  h = ldg2(row + 2 * kN + ug * 8 + 2 * t);
+  z = make_float2(zr.x, zr.y);
+  r = make_float2(zr.z, zr.w);
+}
+
+template <bool ARITH> struct RcpSel {
+  typedef const uint32_t *type;
+  static __device__ __forceinline__ type make(const uint32_t *tab) { return tab; }
+};
+template <> struct RcpSel<true> {
+  typedef RcpArith type;
+  static __device__ __forceinline__ type make(const uint32_t *) { return RcpArith{}; }
+};
+
 // one dual-FC node logit (src/nnet.c:192-202); bv = GRU-B state.  w: the node's 32 weights
 // [channel][input], bf: bias|factor as [bias c0 | bias c1 | factor c0 | factor c1][256].
-template <bool SMEM>
+template <bool SMEM, class R>
 __device__ __forceinline__ float node_logit(const float *__restrict__ wbase, int wstride, const float *__restrict__ bf,
-                                            int i, const float (&bv)[16], const uint32_t *rcp) {
+                                            int i, const float (&bv)[16], R rcp) {
   const float4 *w4 = reinterpret_cast<const float4 *>(wbase + (size_t)i * wstride);
   float w[32];
 #pragma unroll
@@ -99,7 +117,7 @@ __device__ __forceinline__ uint32_t fnv1a_bytes(const unsigned char *p, int n) {
   return h;
 }
 
-template <int MT, int VR, bool DEBUG, bool FIX>
+template <int MT, int VR, bool DEBUG, bool FIX, bool RA>
 __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A) {
   constexpr int NS = MT * VR;
   constexpr int NV = (VR == 16) ? 4 : 2;   // accumulator registers in use per thread
@@ -122,7 +140,8 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   float *s_subA = reinterpret_cast<float *>(smem + L.subA);
   float *s_diagA = reinterpret_cast<float *>(smem + L.diagA);
   float *s_subB = reinterpret_cast<float *>(smem + L.subB);
-  uint32_t *s_rcp = reinterpret_cast<uint32_t *>(smem + L.rcp);
+  uint32_t *s_rcp_tab = reinterpret_cast<uint32_t *>(smem + L.rcp);
+  const typename RcpSel<RA>::type s_rcp = RcpSel<RA>::make(s_rcp_tab);   // table in shared memory, or arithmetic
   float *s_u2l = reinterpret_cast<float *>(smem + L.u2l);
   float *s_logit = reinterpret_cast<float *>(smem + L.logit);
   uint32_t *s_xa = reinterpret_cast<uint32_t *>(smem + L.xa);
@@ -167,7 +186,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
     copy_words(reinterpret_cast<uint32_t *>(s_subA), reinterpret_cast<const uint32_t *>(M.a_subias_rec), kRowsA);
     copy_words(reinterpret_cast<uint32_t *>(s_diagA), reinterpret_cast<const uint32_t *>(M.a_diag), kRowsA);
     copy_words(reinterpret_cast<uint32_t *>(s_subB), reinterpret_cast<const uint32_t *>(M.b_subias), 2 * kRowsB);
-    copy_words(s_rcp, M.rcp_tab, 2048);
+    if (!RA) copy_words(s_rcp_tab, M.rcp_tab, 2048);
     copy_words(reinterpret_cast<uint32_t *>(s_u2l), reinterpret_cast<const uint32_t *>(M.ulaw2lin_tab), 256);
     copy_words(reinterpret_cast<uint32_t *>(s_logit), reinterpret_cast<const uint32_t *>(M.logit_tab), 256);
     {
@@ -284,9 +303,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
         const int gs = min(stream0 + g, B - 1);
 #pragma unroll
         for (int u = 0; u < 3; u++)
-#pragma unroll
-          for (int gate = 0; gate < 3; gate++)
-            cond_reg[u][gate] = ldg2(condA_f + (size_t)gs * kRowsA + gate * kN + (warp + u * kWarps) * 8 + 2 * t);
+          ldg_zrh(condA_f + (size_t)gs * kRowsA, warp + u * kWarps, t, cond_reg[u][0], cond_reg[u][1], cond_reg[u][2]);
       }
 
       for (int step = 0; step < A.spf; step++) {
@@ -309,15 +326,11 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               const int us = s_usig[s], up = s_upred[s], le = s_lexc[s];
               ac[h] = s_act[s];
               const int gs = min(stream0 + s, B - 1);
-#pragma unroll
-              for (int gate = 0; gate < 3; gate++) {
-                const int col = gate * kN + ug * 8 + 2 * t;
-                if (CREG) cv[gate][h] = cond_reg[u][gate];
-                else cv[gate][h] = ldg2(condA_f + (size_t)gs * kRowsA + col);
-                e1[gate][h] = ldg2(M.e_sig + (size_t)us * kRowsA + col);
-                e2[gate][h] = ldg2(M.e_pred + (size_t)up * kRowsA + col);
-                e3[gate][h] = ldg2(M.e_exc + (size_t)le * kRowsA + col);
-              }
+              if (CREG) { cv[0][h] = cond_reg[u][0]; cv[1][h] = cond_reg[u][1]; cv[2][h] = cond_reg[u][2]; }
+              else ldg_zrh(condA_f + (size_t)gs * kRowsA, ug, t, cv[0][h], cv[1][h], cv[2][h]);
+              ldg_zrh(M.e_sig + (size_t)us * kRowsA, ug, t, e1[0][h], e1[1][h], e1[2][h]);
+              ldg_zrh(M.e_pred + (size_t)up * kRowsA, ug, t, e2[0][h], e2[1][h], e2[2][h]);
+              ldg_zrh(M.e_exc + (size_t)le * kRowsA, ug, t, e3[0][h], e3[1][h], e3[2][h]);
             }
             // (2) sparse_sgemv_accum8x4 (src/vec_avx.h:790-858) on tensor cores.  The int32 sum is exact in
             //     any order, so the rne(16256*t) seed of the AVX2 kernel is added afterwards.
@@ -592,9 +605,11 @@ static cudaError_t launch_tile(const SampleArgs &a, int n_sms, cudaStream_t s) {
   const size_t smem = make_layout(NS, MT, a.m.a_rec.n_chunks, a.m.b_in.n_chunks, a.m.b_rec.n_chunks).total;
   const bool dbg = a.trace || a.logits;
   const bool fix = a.m.a_rec.slots[2] != 0;
+  const bool ra = a.m.rcp_arith != 0;   // the trace/logit variants always use the table
   void (*kern)(const SampleArgs) =
-      dbg ? (fix ? sample_kernel<MT, VR, true, true> : sample_kernel<MT, VR, true, false>)
-          : (fix ? sample_kernel<MT, VR, false, true> : sample_kernel<MT, VR, false, false>);
+      dbg ? (fix ? sample_kernel<MT, VR, true, true, false> : sample_kernel<MT, VR, true, false, false>)
+      : ra ? (fix ? sample_kernel<MT, VR, false, true, true> : sample_kernel<MT, VR, false, false, true>)
+           : (fix ? sample_kernel<MT, VR, false, true, false> : sample_kernel<MT, VR, false, false, false>);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const int n_tiles = (a.n_streams + NS - 1) / NS;

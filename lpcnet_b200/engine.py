@@ -189,6 +189,14 @@ class Batch:
         return self.L.lpcnet_batch_nblocks(self.h, 1)
 
     @property
+    def rcp_arith(self):
+        return bool(self.L.lpcnet_batch_nblocks(self.h, 2))
+
+    @property
+    def fixed_slots(self):
+        return bool(self.L.lpcnet_batch_nblocks(self.h, 3))
+
+    @property
     def launch_count(self):
         return int(self.L.lpcnet_batch_launch_count(self.h))
 

@@ -34,8 +34,9 @@ def main():
                     bad = np.nonzero(tr[s] != ref[s][1])[0]
                     if len(bad):
                         print("  stream", s, "first diff step", bad[0], tr[s][bad[0]], ref[s][1][bad[0]]); break
+            flags = (bt.rcp_arith, bt.fixed_slots)
             bt.close()
-    print("PARITY", "OK" if allok else "FAILED", flush=True)
+    print("PARITY", "OK" if allok else "FAILED", " rcp_arith, fixed_slots =", flags, flush=True)
     if os.environ.get("QUICK_NO_TIMING"): return
     cfgs = [(1024, 8), (2048, 16), (4096, 32), (4736, 32), (9472, 64)]
     if len(sys.argv) > 1:
