@@ -125,7 +125,7 @@ LPCNET_B200_EXPORT int lpcnet_batch_reset(LPCNetBatch *b, int stream);
 LPCNET_B200_EXPORT int lpcnet_batch_set_seed(LPCNetBatch *b, int stream, const unsigned char *data, int n);
 /* Run on this cudaStream_t (as void*) instead of the batch's own stream. */
 LPCNET_B200_EXPORT int lpcnet_batch_set_cuda_stream(LPCNetBatch *b, void *cuda_stream);
-/* Streams per CTA tile: 0 = automatic (by n_streams), else one of 8, 16, 32, 64. */
+/* Streams per CTA tile: 0 = automatic (by n_streams), else one of 8, 16, 32. */
 LPCNET_B200_EXPORT int lpcnet_batch_set_tile(LPCNetBatch *b, int streams_per_cta);
 
 /* HOST buffers.  features: [n_streams][n_frames][feature_stride] floats (only [0,20) of
@@ -162,7 +162,8 @@ LPCNET_B200_EXPORT int lpcnet_batch_set_state(LPCNetBatch *b, int stream, const 
 LPCNET_B200_EXPORT int lpcnet_batch_sync(LPCNetBatch *b);
 /* Model facts.  which = 0 / 1: number of block-sparse 8x4 blocks in GRU-A / GRU-B input (for the op
  * counts); 2: 1 when the rcpps estimate is computed arithmetically (the table was verified equal on this
- * GPU), 0 when looked up; 3: 1 when GRU-A runs the unrolled fixed-slot path; 4: GRU-A chunks of 8 blocks. */
+ * GPU), 0 when looked up; 3: 1 when GRU-A runs the unrolled fixed-slot path; 4: GRU-A chunks of 8 blocks;
+ * 8 / 16 / 32: bytes of shared memory the sample kernel needs per CTA at that many streams per CTA. */
 LPCNET_B200_EXPORT int lpcnet_batch_nblocks(const LPCNetBatch *b, int which);
 /* Kernels launched by this batch so far (for bench.py's gpu_launches). */
 LPCNET_B200_EXPORT long long lpcnet_batch_launch_count(const LPCNetBatch *b);

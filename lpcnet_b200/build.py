@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "liblpcnet_b200.so")
-SOURCES = ["model.cu", "frame.cu", "sample.cu", "sample_t8.cu", "sample_t16.cu", "sample_t32.cu", "sample_t64.cu",
+SOURCES = ["model.cu", "frame.cu", "sample.cu", "sample_t8.cu", "sample_t16.cu", "sample_t32.cu",
            "api.cu", "probe.cu"]
 HEADERS = ["engine.h", "bitexact.cuh", "sample_kernel.cuh", os.path.join("..", "..", "include", "lpcnet_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -25,8 +25,12 @@ def _mtime(p):
     return os.path.getmtime(p) if os.path.exists(p) else 0.0
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, extra_flags=(), tag: str = "") -> str:
+    """tag/extra_flags: development variants (e.g. tag="_clk", extra_flags=["-DLPCB_PHASE_CLOCKS"]) built next to
+    the product library as liblpcnet_b200<tag>.so; the product build passes neither."""
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    OBJ = os.path.join(HERE, "build" + tag)
+    LIB = os.path.join(HERE, f"liblpcnet_b200{tag}.so")
     os.makedirs(OBJ, exist_ok=True)
     hdr_t = max([_mtime(os.path.join(CSRC, h)) for h in HEADERS] + [_mtime(os.path.abspath(__file__))])
     jobs = []
@@ -37,7 +41,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     def compile_one(job):
         src, obj = job
-        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj, os.path.join(CSRC, src)]
+        cmd = [nvcc] + NVCC_FLAGS + list(extra_flags) + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj, os.path.join(CSRC, src)]
         return src, subprocess.run(cmd, capture_output=True, text=True)
 
     with ThreadPoolExecutor(max_workers=min(8, max(1, len(jobs)))) as ex:
@@ -58,4 +62,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--phase-clocks" in sys.argv:
+        print(build(force="--force" in sys.argv, extra_flags=["-DLPCB_PHASE_CLOCKS"], tag="_clk"))
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -15,6 +15,9 @@ using namespace lpcb;
 
 namespace {
 
+#ifdef LPCB_PHASE_CLOCKS
+unsigned long long *g_phase_clk = nullptr;
+#endif
 thread_local std::string g_err;
 thread_local std::string g_err_ret;
 std::mutex g_cfg_mu;
@@ -64,7 +67,7 @@ struct LPCNetBatch {
   int n_streams = 0;
   int n_sms = 0;
   int tile = 0;  // 0 = auto
-  int max_tile = 64;
+  int max_tile = 32;
   Model model;
   DevState st{};
   void *st_alloc = nullptr;
@@ -188,6 +191,10 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
     sa.frame0 = f0; sa.total_frames = n_frames;
     sa.cond_a = b->fb.cond_a; sa.cond_b = b->fb.cond_b; sa.lpc = b->fb.lpc; sa.active = b->fb.active;
     sa.pcm = d_pcm; sa.forced = d_forced; sa.trace = d_trace; sa.logits = d_logits;
+#ifdef LPCB_PHASE_CLOCKS
+    if (!g_phase_clk) { CK(cudaMalloc(&g_phase_clk, 16 * 8)); CK(cudaMemset(g_phase_clk, 0, 16 * 8)); }
+    sa.phase_clk = g_phase_clk;
+#endif
     int nl = 0;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (b->profiling) { CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventRecord(e0, b->stream)); }
@@ -201,6 +208,17 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
 }  // namespace
 
 extern "C" {
+
+#ifdef LPCB_PHASE_CLOCKS
+// development build only (tools/phase_clocks.py): cycle sums per phase of the sample kernel's CTA 0, then cleared
+__attribute__((visibility("default"))) int lpcnet_b200_read_phase_clocks(unsigned long long *out) {
+  if (!g_phase_clk) return -1;
+  if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+  if (cudaMemcpy(out, g_phase_clk, 16 * 8, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+  cudaMemset(g_phase_clk, 0, 16 * 8);
+  return 0;
+}
+#endif
 
 const char *lpcnet_b200_last_error(void) {
   g_err_ret = g_err;
@@ -262,7 +280,7 @@ LPCNetBatch *lpcnet_batch_create(const unsigned char *blob, int len, int n_strea
   }
   // largest streams-per-CTA tile whose resident weights + per-stream buffers fit this GPU's shared memory
   b->max_tile = 0;
-  for (int t : {64, 32, 16, 8})
+  for (int t : {32, 16, 8})
     if (!b->max_tile && sample_kernel_smem(t, b->model.d) <= (size_t)prop.sharedMemPerBlockOptin) b->max_tile = t;
   if (!b->max_tile) {
     fail("model does not fit the shared-memory-resident kernel on this GPU");
@@ -300,6 +318,7 @@ int lpcnet_batch_nblocks(const LPCNetBatch *b, int which) {
     case 2: return b->model.d.rcp_arith;               // 1: reciprocal estimate computed, 0: table lookup
     case 3: return b->model.d.a_rec.slots[2] != 0;     // 1: GRU-A runs the unrolled fixed-slot path
     case 4: return b->model.d.a_rec.n_chunks;
+    case 8: case 16: case 32: return (int)sample_kernel_smem(which, b->model.d);   // bytes of shared memory per CTA
     default: return 0;
   }
 }
@@ -313,7 +332,7 @@ int lpcnet_batch_set_cuda_stream(LPCNetBatch *b, void *s) {
 
 int lpcnet_batch_set_tile(LPCNetBatch *b, int t) {
   if (!b) return fail("null batch");
-  if (t != 0 && t != 8 && t != 16 && t != 32 && t != 64) return fail("tile must be 0, 8, 16, 32 or 64");
+  if (t != 0 && t != 8 && t != 16 && t != 32) return fail("tile must be 0, 8, 16 or 32");
   if (t > b->max_tile) return fail("tile does not fit in shared memory for this model");
   b->tile = t;
   return 0;
@@ -535,6 +554,11 @@ int lpcnet_batch_get_state(LPCNetBatch *b, int s, LPCNetB200StreamState *o) {
 int lpcnet_batch_set_state(LPCNetBatch *b, int s, const LPCNetB200StreamState *in) {
   if (!b || !in) return fail("null argument");
   if (s < 0 || s >= b->n_streams) return fail("stream index out of range");
+  // a GRU state is a convex combination of values in [-1, 1]; the kernels' byte quantiser relies on it
+  for (int i = 0; i < kN; i++)
+    if (!(in->gru_a_state[i] >= -1.f && in->gru_a_state[i] <= 1.f)) return fail("gru_a_state outside [-1, 1]");
+  for (int i = 0; i < kNB; i++)
+    if (!(in->gru_b_state[i] >= -1.f && in->gru_b_state[i] <= 1.f)) return fail("gru_b_state outside [-1, 1]");
   CK(cudaSetDevice(b->device));
   CK(cudaStreamSynchronize(b->stream));
   const DevState &S = b->st;

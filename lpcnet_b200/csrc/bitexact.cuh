@@ -17,14 +17,21 @@ __device__ __forceinline__ float rcp_estimate(float x, const uint32_t *__restric
 
 // The default table without the lookup: entry i is 1/(mid-point of bucket i) rounded half-up to 12
 // mantissa bits, so MUFU.RCP of the mid-point (exponent kept) plus an integer rounding gives the same
-// bits whenever the hardware estimate lands on the right side of every rounding boundary -- which
-// model.cu checks exhaustively on the GPU at load before a kernel variant using this is chosen.
+// bits whenever the estimate lands on the right side of the rounding boundary.  One bucket cannot: for
+// i = 1984 (k = 8065) the exact quotient 2^25/k = 4160.49994 lies 0.13 binary32 ulp below its boundary,
+// so any binary32 reciprocal sits on the tie and rounds up; it is corrected explicitly.  The closest
+// other buckets are 0.59 and 1.05 ulp away, inside MUFU.RCP's error on paper -- so model.cu compares
+// this function with the table for every bucket and exponent on the GPU at load, and the kernel
+// variants built on it are used only when all of them agree.
 struct RcpArith {};
 __device__ __forceinline__ float rcp_estimate(float x, RcpArith) {
-  const float mid = __uint_as_float((__float_as_uint(x) & 0xfffff000u) | 0x800u);
+  const uint32_t b = __float_as_uint(x);
+  const float mid = __uint_as_float((b & 0xfffff000u) | 0x800u);
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(mid));
-  return __uint_as_float((__float_as_uint(r) + 0x400u) & 0xfffff800u);
+  uint32_t q = (__float_as_uint(r) + 0x400u) & 0xfffff800u;
+  if ((b & 0x007ff000u) == (1984u << 12)) q -= 0x800u;
+  return __uint_as_float(q);
 }
 
 // tanh8_approx (src/vec_avx.h:393-411)
@@ -124,6 +131,14 @@ __device__ __forceinline__ int32_t cvt_rne_fast(float x) {
 // convex combinations of values in [-1,1].
 __device__ __forceinline__ uint32_t quant_u8_fast(float x) {
   return (uint32_t)min(max(__float2int_rn(fmaf(x, 127.f, 127.f)), 0), 255);
+}
+
+// The same for a GRU-A state produced by the blend z*a + (1-z)*h with |a|, |h| <= 1 (so |x| <= 1 + a few
+// ulp and fma(x,127,127) lies in (-1e-4, 254.0001)): adding 1.5*2^23 rounds to the nearest-even integer
+// exactly like the conversion does, and the integer is the low byte.  No conversion instruction, no clamp.
+// (lpcnet_batch_set_state refuses GRU-A states outside [-1, 1], which zero-initialised streams never reach.)
+__device__ __forceinline__ uint32_t quant_u8_unit(float x) {
+  return __float_as_uint(fmaf(x, 127.f, 127.f) + 12582912.f) & 0xffu;
 }
 
 #define LPCB_SCALE (128.f * 127.f)

@@ -38,20 +38,23 @@ __host__ __device__ inline int gru_a_col_index(int col) {
 }
 
 // Block-sparse int8 matrix re-tiled for mma.sync.m16n8k32 B fragments.
-// A "chunk" is 8 blocks (K = 32) of one 8-row group.
+// A "chunk" is 8 blocks (K = 32) of one 8-row group; its 64 weight words are stored [lane][2] so that a
+// lane fetches both B registers with one 8-byte load.
 struct PackedSparse {
   int n_groups = 0;   // rows / 8
   int n_chunks = 0;
   int n_blocks = 0;   // real (un-padded) blocks
-  std::vector<uint32_t> chunk_start;  // [n_groups + 1]
+  std::vector<uint32_t> chunk_start;  // [n_groups + 1]   (slotted GRU-A: [unit groups + 1])
   std::vector<uint8_t> pos;           // [n_chunks][8]  column position / 4
-  std::vector<uint32_t> w;            // [n_chunks][2][32] words, fragment order
+  std::vector<uint32_t> w;            // [n_chunks][32 lanes][2] words, fragment order
   // GRU-A only ("slotted" layout): unit group ug owns the fixed chunks [ug*ST, (ug+1)*ST), ST = slots[0]+
   // slots[1]+slots[2], gate-major inside; blocks that do not fit go to overflow chunks after the fixed region,
-  // with chunk_start indexed by ug*3+gate.  off: per chunk, per lane%4, the two gather byte offsets packed
-  // lo | hi << 16.
+  // one list per unit group (chunk_start[ug] .. chunk_start[ug+1]) with the gate of each chunk in its offset words.
+  // off: per chunk, per lane%4, the two gather byte offsets and the gate: lo | hi << 16 | gate << 30.
+  // off_fixed: the same words of the fixed chunks regrouped [ug][lane%4][8] (ST <= 8 used) for 16-byte loads.
   int slots[3] = {0, 0, 0};
   std::vector<uint32_t> off;          // [n_chunks][4]
+  std::vector<uint32_t> off_fixed;    // [unit groups][4][8]
 };
 
 struct DevSparse {
@@ -59,7 +62,8 @@ struct DevSparse {
   const uint32_t *chunk_start;  // device
   const uint2 *pos;             // device, [n_chunks]
   const uint32_t *w;            // device, [n_chunks][64]
-  const uint32_t *off;          // device, [n_chunks][4] (slotted GRU-A layout only)
+  const uint32_t *off;          // device, [n_chunks][4] (GRU-A only)
+  const uint32_t *off_fixed;    // device, [unit groups][4][8] (GRU-A only)
   int slots[3];                 // fixed chunk slots per gate per unit group (0,0,0 = all chunks in the overflow lists)
 };
 
@@ -157,6 +161,7 @@ struct SampleArgs {
   const short *forced;       // nullable, same layout
   void *trace;               // nullable LPCNetB200Trace [B][total_frames*spf]
   float *logits;             // nullable [B][total_frames*spf][256]
+  unsigned long long *phase_clk;   // development builds (-DLPCB_PHASE_CLOCKS) only: per-phase cycle sums of CTA 0
 };
 
 cudaError_t launch_sample_kernel(const SampleArgs &a, int tile_streams, int n_sms, cudaStream_t s,

@@ -126,12 +126,12 @@ bool pack_sparse(PackedSparse &ps, const int32_t *idx, int idx_len, const int8_t
   auto emit = [&](int c, int slot, const Slot &sl) {
     ps.pos[(size_t)c * 8 + slot] = (uint8_t)(sl.pos / 4);
     if (!sl.w) return;
-    // B fragment of mma.m16n8k32: register slot/4, lane = row*4 + slot%4 holds the four input
-    // weights of output row `row` of block `slot`.
+    // B fragment of mma.m16n8k32: register slot/4 of lane = row*4 + slot%4 holds the four input
+    // weights of output row `row` of block `slot`; the two registers of a lane are adjacent.
     for (int r = 0; r < 8; r++) {
       uint32_t word;
       memcpy(&word, sl.w + r * 4, 4);
-      ps.w[(size_t)c * 64 + (slot / 4) * 32 + r * 4 + (slot % 4)] = word;
+      ps.w[(size_t)c * 64 + (r * 4 + (slot % 4)) * 2 + slot / 4] = word;
     }
   };
   if (!slotted) {
@@ -161,32 +161,41 @@ bool pack_sparse(PackedSparse &ps, const int32_t *idx, int idx_len, const int8_t
       ps.slots[0] = ps.slots[1] = ps.slots[2] = 0;
     const int ST = ps.slots[0] + ps.slots[1] + ps.slots[2];
     int nchunks = nug * ST;
-    ps.chunk_start.assign(nug * 3 + 1, 0);
-    for (int ug = 0; ug < nug; ug++)
+    ps.chunk_start.assign(nug + 1, 0);
+    for (int ug = 0; ug < nug; ug++) {
+      ps.chunk_start[ug] = nchunks;
       for (int gate = 0; gate < 3; gate++) {
-        ps.chunk_start[ug * 3 + gate] = nchunks;
-        const int over = (int)gpos[gate * nug + ug].size() - 8 * ps.slots[gate];
-        if (over > 0) nchunks += (over + 7) / 8;
+        const int over = (int)gslots[gate * nug + ug].size() - 8 * ps.slots[gate];
+        if (over > 0) nchunks += over / 8;
       }
-    ps.chunk_start[nug * 3] = nchunks;
+    }
+    ps.chunk_start[nug] = nchunks;
     ps.n_chunks = nchunks;
     ps.pos.assign((size_t)nchunks * 8, 0);
     ps.w.assign((size_t)nchunks * 64, 0);
+    std::vector<int> gate_of(nchunks, 0);
     for (int ug = 0; ug < nug; ug++) {
-      int slot0 = 0;
+      int slot0 = 0, oc = ps.chunk_start[ug];
       for (int gate = 0; gate < 3; gate++) {
         const int g = gate * nug + ug, cap = 8 * ps.slots[gate];
         for (int b = 0; b < (int)gslots[g].size(); b++) {
-          if (b < cap) emit(ug * ST + slot0 + b / 8, b % 8, gslots[g][b]);
-          else emit(ps.chunk_start[ug * 3 + gate] + (b - cap) / 8, (b - cap) % 8, gslots[g][b]);
+          const int c = b < cap ? ug * ST + slot0 + b / 8 : oc + (b - cap) / 8;
+          emit(c, b % 8, gslots[g][b]);
+          gate_of[c] = gate;
         }
+        if ((int)gslots[g].size() > cap) oc += ((int)gslots[g].size() - cap) / 8;
         slot0 += ps.slots[gate];
       }
     }
     ps.off.assign((size_t)nchunks * 4, 0);
     for (int c = 0; c < nchunks; c++)
       for (int t = 0; t < 4; t++)
-        ps.off[(size_t)c * 4 + t] = (uint32_t)ps.pos[(size_t)c * 8 + t] * 4u | ((uint32_t)ps.pos[(size_t)c * 8 + 4 + t] * 4u) << 16;
+        ps.off[(size_t)c * 4 + t] = (uint32_t)ps.pos[(size_t)c * 8 + t] * 4u | ((uint32_t)ps.pos[(size_t)c * 8 + 4 + t] * 4u) << 16 |
+                                    (uint32_t)gate_of[c] << 30;
+    ps.off_fixed.assign((size_t)nug * 32, 0);
+    for (int ug = 0; ug < nug; ug++)
+      for (int sl = 0; sl < ST; sl++)
+        for (int t = 0; t < 4; t++) ps.off_fixed[((size_t)ug * 4 + t) * 8 + sl] = ps.off[((size_t)ug * ST + sl) * 4 + t] & 0x3fffffffu;
   }
   return true;
 }
@@ -339,9 +348,10 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
     put(reinterpret_cast<const void **>(&ds.chunk_start), ps.chunk_start.data(), ps.chunk_start.size() * 4);
     put(reinterpret_cast<const void **>(&ds.pos), ps.pos.data(), ps.pos.size());
     put(reinterpret_cast<const void **>(&ds.w), ps.w.data(), ps.w.size() * 4);
-    ds.off = nullptr;
+    ds.off = ds.off_fixed = nullptr;
     for (int k = 0; k < 3; k++) ds.slots[k] = ps.slots[k];
     if (!ps.off.empty()) put(reinterpret_cast<const void **>(&ds.off), ps.off.data(), ps.off.size() * 4);
+    if (!ps.off_fixed.empty()) put(reinterpret_cast<const void **>(&ds.off_fixed), ps.off_fixed.data(), ps.off_fixed.size() * 4);
   };
   put_sparse(d.a_rec, pa);
   put_sparse(d.b_in, pb);

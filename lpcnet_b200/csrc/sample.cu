@@ -6,7 +6,6 @@ namespace lpcb {
 cudaError_t launch_sample_t8(const SampleArgs &a, int n_sms, cudaStream_t s);
 cudaError_t launch_sample_t16(const SampleArgs &a, int n_sms, cudaStream_t s);
 cudaError_t launch_sample_t32(const SampleArgs &a, int n_sms, cudaStream_t s);
-cudaError_t launch_sample_t64(const SampleArgs &a, int n_sms, cudaStream_t s);
 
 size_t sample_kernel_smem(int tile_streams, const DevModel &m) {
   const int VR = tile_streams == 8 ? 8 : 16;
@@ -20,7 +19,6 @@ cudaError_t launch_sample_kernel(const SampleArgs &a, int tile_streams, int n_sm
     case 8: e = launch_sample_t8(a, n_sms, s); break;
     case 16: e = launch_sample_t16(a, n_sms, s); break;
     case 32: e = launch_sample_t32(a, n_sms, s); break;
-    case 64: e = launch_sample_t64(a, n_sms, s); break;
     default: return cudaErrorInvalidValue;
   }
   if (e == cudaSuccess && n_launches) ++*n_launches;

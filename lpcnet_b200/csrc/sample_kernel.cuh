@@ -31,15 +31,15 @@ constexpr int kRGroupsB = kRowsB / 8;      // 6
 
 struct SmemLayout {
   // byte offsets
-  unsigned wA, posA, csA, wBi, posBi, csBi, wBr, posBr, csBr;
-  unsigned subA, diagA, subB, rcp, u2l, logit;
+  unsigned wA, posA, offF, csA, wBi, posBi, csBi, wBr, posBr, csBr;
+  unsigned sdA, subB, rcp, u2l, logit;
   unsigned xa, xb, bst, lsig, lpc, condb, part;
-  unsigned usig, upred, lexc, pred, deemph, rng, head, act;
+  unsigned usig, upred, lexc, pred, deemph, rng, head, act, ix;
   unsigned fcw, fcb;   // dual_fc weights (node stride kFcStride floats) and bias|factor, when resident
   unsigned total;
 };
 
-__host__ __device__ inline int b_parts(int MT) { return MT == 1 ? 4 : (MT == 2 ? 2 : 1); }
+constexpr int kPartsB = 2;   // K-split of the GRU-B input product (phase B1 jobs = 6 row groups x (kPartsB + 1))
 
 constexpr int kFcStride = 36;   // 32 weights per node padded so that 8 lanes' 16-byte reads hit disjoint banks
 __host__ __device__ inline bool fc_resident(int NS) { return NS <= 32; }
@@ -48,19 +48,19 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
   SmemLayout L;
   unsigned o = 0;
   auto take = [&](unsigned bytes) { unsigned r = o; o += (bytes + 15u) & ~15u; return r; };
-  L.wA = take(chA * 256); L.posA = take(chA * 16); L.csA = take((kRowsA / 8 + 1) * 4);
+  L.wA = take(chA * 256); L.posA = take(chA * 16); L.offF = take(kN / 8 * 32 * 4); L.csA = take((kN / 8 + 1) * 4);
   L.wBi = take(chBi * 256); L.posBi = take(chBi * 8); L.csBi = take((kRGroupsB + 1) * 4);
   L.wBr = take(chBr * 256); L.posBr = take(chBr * 8); L.csBr = take((kRGroupsB + 1) * 4);
-  L.subA = take(kRowsA * 4); L.diagA = take(kRowsA * 4); L.subB = take(2 * kRowsB * 4);
+  L.sdA = take(kRowsA * 8); L.subB = take(2 * kRowsB * 4);
   L.rcp = take(2048 * 4); L.u2l = take(256 * 4); L.logit = take(256 * 4);
   L.xa = take(2 * NS * kXaStride * 4);
   L.xb = take(NS * kXbStride * 4);
   L.bst = take(NS * 20 * 4);
   L.lsig = take(16 * NS * 4); L.lpc = take(16 * NS * 4);
   L.condb = take(NS * kRowsB * 4);
-  L.part = take(MT * (b_parts(MT) + 1) * kRGroupsB * 128 * 4);
+  L.part = take(MT * (kPartsB + 1) * kRGroupsB * 128 * 4);
   L.usig = take(NS * 4); L.upred = take(NS * 4); L.lexc = take(NS * 4); L.pred = take(NS * 4);
-  L.deemph = take(NS * 4); L.rng = take(4 * NS * 4); L.head = take(NS * 4); L.act = take(NS * 4);
+  L.deemph = take(NS * 4); L.rng = take(4 * NS * 4); L.head = take(NS * 4); L.act = take(NS * 4); L.ix = take(NS * 4);
   L.fcb = take(4 * 256 * 4);
   L.fcw = fc_resident(NS) ? take(256 * kFcStride * 4) : 0;
   L.total = o;
@@ -117,11 +117,17 @@ __device__ __forceinline__ uint32_t fnv1a_bytes(const unsigned char *p, int n) {
   return h;
 }
 
+// development builds: thread 0 of CTA 0 accumulates the cycles between phase marks
+#ifdef LPCB_PHASE_CLOCKS
+#define LPCB_MARK(k) do { if (blockIdx.x == 0 && threadIdx.x == 0) { const long long now_ = clock64(); clk_[k] += now_ - last_; last_ = now_; } } while (0)
+#else
+#define LPCB_MARK(k) do { } while (0)
+#endif
+
 template <int MT, int VR, bool DEBUG, bool FIX, bool RA>
 __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A) {
   constexpr int NS = MT * VR;
   constexpr int NV = (VR == 16) ? 4 : 2;   // accumulator registers in use per thread
-  constexpr int P = (MT == 1) ? 4 : (MT == 2 ? 2 : 1);
   constexpr bool CREG = (MT == 1 && VR == 8);   // frame conditioning of GRU-A held in registers (18 per thread)
   constexpr bool FCS = NS <= 32;            // dual_fc resident in shared memory (fc_resident)
   extern __shared__ __align__(16) unsigned char smem[];
@@ -130,15 +136,15 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
 
   uint32_t *s_wA = reinterpret_cast<uint32_t *>(smem + L.wA);
   uint32_t *s_offA = reinterpret_cast<uint32_t *>(smem + L.posA);   // [chunk][4] packed gather offsets
-  uint32_t *s_csA = reinterpret_cast<uint32_t *>(smem + L.csA);
+  uint32_t *s_offF = reinterpret_cast<uint32_t *>(smem + L.offF);   // [ug][lane%4][8] offsets of the fixed chunks
+  uint32_t *s_csA = reinterpret_cast<uint32_t *>(smem + L.csA);     // [ug + 1] overflow chunk lists
   uint32_t *s_wBi = reinterpret_cast<uint32_t *>(smem + L.wBi);
   uint2 *s_posBi = reinterpret_cast<uint2 *>(smem + L.posBi);
   uint32_t *s_csBi = reinterpret_cast<uint32_t *>(smem + L.csBi);
   uint32_t *s_wBr = reinterpret_cast<uint32_t *>(smem + L.wBr);
   uint2 *s_posBr = reinterpret_cast<uint2 *>(smem + L.posBr);
   uint32_t *s_csBr = reinterpret_cast<uint32_t *>(smem + L.csBr);
-  float *s_subA = reinterpret_cast<float *>(smem + L.subA);
-  float *s_diagA = reinterpret_cast<float *>(smem + L.diagA);
+  float *s_sdA = reinterpret_cast<float *>(smem + L.sdA);   // [gate][ug][lane%4][sub0 sub1 diag0 diag1]
   float *s_subB = reinterpret_cast<float *>(smem + L.subB);
   uint32_t *s_rcp_tab = reinterpret_cast<uint32_t *>(smem + L.rcp);
   const typename RcpSel<RA>::type s_rcp = RcpSel<RA>::make(s_rcp_tab);   // table in shared memory, or arithmetic
@@ -159,6 +165,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   uint32_t *s_rng = reinterpret_cast<uint32_t *>(smem + L.rng);
   int *s_head = reinterpret_cast<int *>(smem + L.head);
   int *s_act = reinterpret_cast<int *>(smem + L.act);
+  uint32_t *s_ix = reinterpret_cast<uint32_t *>(smem + L.ix);   // u_sig | u_pred << 8 | last_exc << 16 | active << 24
   // dual_fc weights: resident copy (padded node stride) or the blob array in global memory; bias|factor resident
   const float *fc_w = FCS ? reinterpret_cast<const float *>(smem + L.fcw) : M.fc_w;
   const int fc_stride = FCS ? kFcStride : 32;
@@ -176,15 +183,19 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
     };
     copy_words(s_wA, M.a_rec.w, M.a_rec.n_chunks * 64);
     copy_words(s_offA, M.a_rec.off, M.a_rec.n_chunks * 4);
-    copy_words(s_csA, M.a_rec.chunk_start, kRowsA / 8 + 1);
+    if (FIX) copy_words(s_offF, M.a_rec.off_fixed, kUGroups * 32);
+    copy_words(s_csA, M.a_rec.chunk_start, kUGroups + 1);
     copy_words(s_wBi, M.b_in.w, M.b_in.n_chunks * 64);
     copy_words(reinterpret_cast<uint32_t *>(s_posBi), reinterpret_cast<const uint32_t *>(M.b_in.pos), M.b_in.n_chunks * 2);
     copy_words(s_csBi, M.b_in.chunk_start, kRGroupsB + 1);
     copy_words(s_wBr, M.b_rec.w, M.b_rec.n_chunks * 64);
     copy_words(reinterpret_cast<uint32_t *>(s_posBr), reinterpret_cast<const uint32_t *>(M.b_rec.pos), M.b_rec.n_chunks * 2);
     copy_words(s_csBr, M.b_rec.chunk_start, kRGroupsB + 1);
-    copy_words(reinterpret_cast<uint32_t *>(s_subA), reinterpret_cast<const uint32_t *>(M.a_subias_rec), kRowsA);
-    copy_words(reinterpret_cast<uint32_t *>(s_diagA), reinterpret_cast<const uint32_t *>(M.a_diag), kRowsA);
+    for (int i = tid; i < kRowsA; i += kThreads) {
+      const int k = (i >> 3) * 16 + ((i & 7) >> 1) * 4 + (i & 1);   // [gate*48 + ug][lane%4][.]
+      s_sdA[k] = __ldg(M.a_subias_rec + i);
+      s_sdA[k + 2] = __ldg(M.a_diag + i);
+    }
     copy_words(reinterpret_cast<uint32_t *>(s_subB), reinterpret_cast<const uint32_t *>(M.b_subias), 2 * kRowsB);
     if (!RA) copy_words(s_rcp_tab, M.rcp_tab, 2048);
     copy_words(reinterpret_cast<uint32_t *>(s_u2l), reinterpret_cast<const uint32_t *>(M.ulaw2lin_tab), 256);
@@ -199,6 +210,9 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
     }
   }
 
+#ifdef LPCB_PHASE_CLOCKS
+  long long clk_[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, last_ = clock64();
+#endif
   const int n_tiles = (B + NS - 1) / NS;
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const int stream0 = tile * NS;
@@ -291,8 +305,10 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
 #pragma unroll
         for (int j = 0; j < 16; j++) pred = pred - s_lsig[((head + j) & 15) * NS + s] * s_lpc[j * NS + s];
         s_pred[s] = pred;
-        s_usig[s] = lin2ulaw_ref(s_lsig[head * NS + s]);
-        s_upred[s] = lin2ulaw_ref(pred);
+        const int us = lin2ulaw_ref(s_lsig[head * NS + s]), up = lin2ulaw_ref(pred);
+        s_usig[s] = us;
+        s_upred[s] = up;
+        s_ix[s] = (uint32_t)us | (uint32_t)up << 8 | (uint32_t)s_lexc[s] << 16 | (uint32_t)s_act[s] << 24;
       };
       if (tid < NS) predict(tid);
       __syncthreads();
@@ -306,31 +322,35 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
           ldg_zrh(condA_f + (size_t)gs * kRowsA, warp + u * kWarps, t, cond_reg[u][0], cond_reg[u][1], cond_reg[u][2]);
       }
 
+      LPCB_MARK(0);   // frame prologue and everything outside the step loop
       for (int step = 0; step < A.spf; step++) {
         uint32_t *xa_cur = s_xa + cur * NS * kXaStride;
         uint32_t *xa_new = s_xa + (cur ^ 1) * NS * kXaStride;
         // ================= phase A: GRU-A =================
+        // per-stream indices of this step (the same for the three unit groups of the warp)
+        uint32_t ixw[MT][NV / 2];
+#pragma unroll
+        for (int mt = 0; mt < MT; mt++)
+#pragma unroll
+          for (int h = 0; h < NV / 2; h++) ixw[mt][h] = s_ix[mt * VR + g + 8 * h];
 #pragma unroll
         for (int u = 0; u < 3; u++) {
           const int ug = warp + u * kWarps;
 #pragma unroll
           for (int mt = 0; mt < MT; mt++) {
             const int sA = mt * VR + g;
-            int ac[2];
             // (1) issue the gathers first: compute_gru_a_input (src/nnet.c:484-491) reads the frame
             //     conditioning and one row of each embedding table; none of it feeds the recurrent product
             float2 cv[3][NV / 2], e1[3][NV / 2], e2[3][NV / 2], e3[3][NV / 2];
 #pragma unroll
             for (int h = 0; h < NV / 2; h++) {
-              const int s = sA + 8 * h;
-              const int us = s_usig[s], up = s_upred[s], le = s_lexc[s];
-              ac[h] = s_act[s];
-              const int gs = min(stream0 + s, B - 1);
+              const int gs = min(stream0 + sA + 8 * h, B - 1);
               if (CREG) { cv[0][h] = cond_reg[u][0]; cv[1][h] = cond_reg[u][1]; cv[2][h] = cond_reg[u][2]; }
               else ldg_zrh(condA_f + (size_t)gs * kRowsA, ug, t, cv[0][h], cv[1][h], cv[2][h]);
-              ldg_zrh(M.e_sig + (size_t)us * kRowsA, ug, t, e1[0][h], e1[1][h], e1[2][h]);
-              ldg_zrh(M.e_pred + (size_t)up * kRowsA, ug, t, e2[0][h], e2[1][h], e2[2][h]);
-              ldg_zrh(M.e_exc + (size_t)le * kRowsA, ug, t, e3[0][h], e3[1][h], e3[2][h]);
+              const uint32_t w = ixw[mt][h];
+              ldg_zrh(M.e_sig + (w & 0xffu) * kRowsA, ug, t, e1[0][h], e1[1][h], e1[2][h]);
+              ldg_zrh(M.e_pred + ((w >> 8) & 0xffu) * kRowsA, ug, t, e2[0][h], e2[1][h], e2[2][h]);
+              ldg_zrh(M.e_exc + ((w >> 16) & 0xffu) * kRowsA, ug, t, e3[0][h], e3[1][h], e3[2][h]);
             }
             // (2) sparse_sgemv_accum8x4 (src/vec_avx.h:790-858) on tensor cores.  The int32 sum is exact in
             //     any order, so the rne(16256*t) seed of the AVX2 kernel is added afterwards.
@@ -338,8 +358,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
 #pragma unroll
             for (int gate = 0; gate < 3; gate++) acc[gate][0] = acc[gate][1] = acc[gate][2] = acc[gate][3] = 0;
             const unsigned char *xrowb = reinterpret_cast<const unsigned char *>(xa_cur + sA * kXaStride);
-            auto chunk = [&](int32_t (&d)[4], uint32_t pk, uint32_t b0, uint32_t b1) {
-              const uint32_t lo = pk & 0xffffu, hi = pk >> 16;
+            auto chunk = [&](int32_t (&d)[4], uint32_t lo, uint32_t hi, uint2 bw) {
               const uint32_t a0 = *reinterpret_cast<const uint32_t *>(xrowb + lo);
               const uint32_t a2 = *reinterpret_cast<const uint32_t *>(xrowb + hi);
               uint32_t a1 = 0, a3 = 0;
@@ -347,32 +366,39 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
                 a1 = *reinterpret_cast<const uint32_t *>(xrowb + 8 * kXaStride * 4 + lo);
                 a3 = *reinterpret_cast<const uint32_t *>(xrowb + 8 * kXaStride * 4 + hi);
               }
-              mma_u8s8(d, a0, a1, a2, a3, b0, b1);
+              mma_u8s8(d, a0, a1, a2, a3, bw.x, bw.y);
             };
             if (FIX) {
               // fixed slots of this unit group: 1 chunk for z, 1 for r, 3 for h -- fully unrolled
               constexpr int ST = 5;
-              const uint32_t *wq = s_wA + ug * ST * 64 + lane;
-              const uint32_t *oq = s_offA + ug * ST * 4 + t;
-              uint32_t pk[ST], b0[ST], b1[ST];
+              const uint2 *wq = reinterpret_cast<const uint2 *>(s_wA) + ug * ST * 32 + lane;
+              const uint4 o4 = *reinterpret_cast<const uint4 *>(s_offF + (ug * 4 + t) * 8);
+              const uint32_t pk[ST] = {o4.x, o4.y, o4.z, o4.w, s_offF[(ug * 4 + t) * 8 + 4]};
+              uint2 bw[ST];
 #pragma unroll
-              for (int sl = 0; sl < ST; sl++) { pk[sl] = oq[sl * 4]; b0[sl] = wq[sl * 64]; b1[sl] = wq[sl * 64 + 32]; }
+              for (int sl = 0; sl < ST; sl++) bw[sl] = wq[sl * 32];
 #pragma unroll
-              for (int sl = 0; sl < ST; sl++) chunk(acc[sl < 2 ? sl : 2], pk[sl], b0[sl], b1[sl]);
+              for (int sl = 0; sl < ST; sl++) chunk(acc[sl < 2 ? sl : 2], pk[sl] & 0xffffu, pk[sl] >> 16, bw[sl]);
             }
-            // overflow chunks (all chunks when the model does not fit the fixed slots)
-#pragma unroll
-            for (int gate = 0; gate < 3; gate++) {
-              const int c0 = s_csA[ug * 3 + gate], c1 = s_csA[ug * 3 + gate + 1];
-              for (int c = c0; c < c1; c++) chunk(acc[gate], s_offA[c * 4 + t], s_wA[c * 64 + lane], s_wA[c * 64 + 32 + lane]);
+            // overflow chunks (all chunks when the model does not fit the fixed slots); bits 30-31 of the
+            // offset word name the gate
+            {
+              const int c0 = s_csA[ug], c1 = s_csA[ug + 1];
+              for (int c = c0; c < c1; c++) {
+                const uint32_t pk = s_offA[c * 4 + t];
+                const uint2 bw = reinterpret_cast<const uint2 *>(s_wA)[c * 32 + lane];
+                const uint32_t lo = pk & 0xffffu, hi = (pk >> 16) & 0x3fffu, gate = pk >> 30;
+                if (gate == 0) chunk(acc[0], lo, hi, bw);
+                else if (gate == 1) chunk(acc[1], lo, hi, bw);
+                else chunk(acc[2], lo, hi, bw);
+              }
             }
             // (3) seeds and gates: compute_sparse_gru (src/nnet.c:431-447), two units per packed operation
             float2 gh[NV / 2];
 #pragma unroll
             for (int gate = 0; gate < 3; gate++) {
-              const int col = gate * kN + ug * 8 + 2 * t;
-              const float2 sub = *reinterpret_cast<const float2 *>(s_subA + col);
-              const float2 dg = *reinterpret_cast<const float2 *>(s_diagA + col);
+              const float4 sd4 = *reinterpret_cast<const float4 *>(s_sdA + ((gate * kUGroups + ug) * 4 + t) * 4);
+              const float2 sub = make_float2(sd4.x, sd4.y), dg = make_float2(sd4.z, sd4.w);
 #pragma unroll
               for (int h = 0; h < NV / 2; h++) {
                 const float2 gx = f2_add(f2_add(f2_add(cv[gate][h], e1[gate][h]), e2[gate][h]), e3[gate][h]);
@@ -398,9 +424,9 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               // z*state + (1-z)*h, scalar for the same reason
               const float2 a_nw = make_float2(z.x * a_old.x + (1.f - z.x) * hh.x, z.y * a_old.y + (1.f - z.y) * hh.y);
               unsigned short *dst = reinterpret_cast<unsigned short *>(xa_new) + (((sA + 8 * h) * kXaStride * 4 + ug * 8 + 2 * t) >> 1);
-              if (ac[h]) {
+              if (ixw[mt][h] >> 24) {
                 a_reg[u][mt][h] = a_nw;
-                *dst = (unsigned short)(quant_u8_fast(a_nw.x) | (quant_u8_fast(a_nw.y) << 8));
+                *dst = (unsigned short)(quant_u8_unit(a_nw.x) | (quant_u8_unit(a_nw.y) << 8));
               } else {
                 // an inactive stream keeps its state and the byte pair it already has
                 *dst = reinterpret_cast<const unsigned short *>(xa_cur)[((sA + 8 * h) * kXaStride * 4 + ug * 8 + 2 * t) >> 1];
@@ -408,46 +434,70 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             }
           }
         }
+        LPCB_MARK(1);   // phase A (this warp)
         __syncthreads();
+        LPCB_MARK(2);   // wait for the other warps
         // ================= phase B1: GRU-B products =================
+        // jobs: (row group, K half) of the input product on the new GRU-A state, then the recurrent product;
+        // every job covers all M tiles so the B fragments are fetched once.  Loads of UB chunks are issued
+        // before their MMAs.
         {
-          constexpr int JOBS_PER_MT = kRGroupsB * (P + 1);
-          for (int job = warp; job < MT * JOBS_PER_MT; job += kWarps) {
-            const int mt = job / JOBS_PER_MT, r = job % JOBS_PER_MT;
-            const int rg = r / (P + 1), kind = r % (P + 1);
-            const int sA = mt * VR + g;
-            int32_t acc[4] = {0, 0, 0, 0};
-            if (kind < P) {
+          constexpr int JOBS = kRGroupsB * (kPartsB + 1);
+          constexpr int UB = MT == 1 ? 3 : (MT == 2 ? 2 : 1);
+          for (int job = warp; job < JOBS; job += kWarps) {
+            const int kind = job / kRGroupsB, rg = job % kRGroupsB;
+            const bool inp = kind < kPartsB;
+            int lo, hi;
+            if (inp) {
               const int cs = s_csBi[rg], n = s_csBi[rg + 1] - cs;
-              const int lo = cs + (n * kind) / P, hi = cs + (n * (kind + 1)) / P;
-              const uint32_t *xrow = xa_new + sA * kXaStride;
-              for (int c = lo; c < hi; c++) {
-                const uint2 pp = s_posBi[c];
-                const uint32_t b0 = s_wBi[c * 64 + lane], b1 = s_wBi[c * 64 + 32 + lane];
-                const uint32_t plo = (pp.x >> (8 * t)) & 0xffu, phi = (pp.y >> (8 * t)) & 0xffu;
-                const uint32_t a0 = xrow[plo], a2 = xrow[phi];
-                uint32_t a1 = 0, a3 = 0;
-                if (VR == 16) { a1 = xrow[8 * kXaStride + plo]; a3 = xrow[8 * kXaStride + phi]; }
-                mma_u8s8(acc, a0, a1, a2, a3, b0, b1);
-              }
+              lo = cs + (n * kind) / kPartsB; hi = cs + (n * (kind + 1)) / kPartsB;
             } else {
-              const uint32_t *xrow = s_xb + sA * kXbStride;
-              for (int c = s_csBr[rg]; c < (int)s_csBr[rg + 1]; c++) {
-                const uint2 pp = s_posBr[c];
-                const uint32_t b0 = s_wBr[c * 64 + lane], b1 = s_wBr[c * 64 + 32 + lane];
-                const uint32_t plo = (pp.x >> (8 * t)) & 0xffu, phi = (pp.y >> (8 * t)) & 0xffu;
-                const uint32_t a0 = xrow[plo], a2 = xrow[phi];
-                uint32_t a1 = 0, a3 = 0;
-                if (VR == 16) { a1 = xrow[8 * kXbStride + plo]; a3 = xrow[8 * kXbStride + phi]; }
-                mma_u8s8(acc, a0, a1, a2, a3, b0, b1);
-              }
+              lo = s_csBr[rg]; hi = s_csBr[rg + 1];
             }
-            int32_t *dst = s_part + ((mt * (P + 1) + kind) * kRGroupsB + rg) * 128;
-            *reinterpret_cast<int2 *>(dst + g * 8 + 2 * t) = make_int2(acc[0], acc[1]);
-            if (VR == 16) *reinterpret_cast<int2 *>(dst + (g + 8) * 8 + 2 * t) = make_int2(acc[2], acc[3]);
+            const uint2 *wq = reinterpret_cast<const uint2 *>(inp ? s_wBi : s_wBr) + lane;
+            const uint2 *pq = inp ? s_posBi : s_posBr;
+            const uint32_t *xbase = (inp ? xa_new : s_xb) + g * (inp ? kXaStride : kXbStride);
+            const int tstride = VR * (inp ? kXaStride : kXbStride), hstride = 8 * (inp ? kXaStride : kXbStride);
+            int32_t acc[MT][4];
+#pragma unroll
+            for (int mt = 0; mt < MT; mt++) acc[mt][0] = acc[mt][1] = acc[mt][2] = acc[mt][3] = 0;
+            for (int c = lo; c < hi; c += UB) {
+              uint2 bw[UB];
+              uint32_t plo[UB], phi[UB], a[UB][MT][4];
+#pragma unroll
+              for (int k = 0; k < UB; k++) {
+                const bool on = c + k < hi;
+                const int cc = on ? c + k : c;
+                const uint2 pp = pq[cc];
+                bw[k] = wq[cc * 32];
+                if (!on) bw[k] = make_uint2(0u, 0u);
+                plo[k] = (pp.x >> (8 * t)) & 0xffu; phi[k] = (pp.y >> (8 * t)) & 0xffu;
+              }
+#pragma unroll
+              for (int k = 0; k < UB; k++)
+#pragma unroll
+                for (int mt = 0; mt < MT; mt++) {
+                  const uint32_t *xrow = xbase + mt * tstride;
+                  a[k][mt][0] = xrow[plo[k]]; a[k][mt][2] = xrow[phi[k]];
+                  a[k][mt][1] = a[k][mt][3] = 0;
+                  if (VR == 16) { a[k][mt][1] = xrow[hstride + plo[k]]; a[k][mt][3] = xrow[hstride + phi[k]]; }
+                }
+#pragma unroll
+              for (int k = 0; k < UB; k++)
+#pragma unroll
+                for (int mt = 0; mt < MT; mt++) mma_u8s8(acc[mt], a[k][mt][0], a[k][mt][1], a[k][mt][2], a[k][mt][3], bw[k].x, bw[k].y);
+            }
+#pragma unroll
+            for (int mt = 0; mt < MT; mt++) {
+              int32_t *dst = s_part + ((mt * (kPartsB + 1) + kind) * kRGroupsB + rg) * 128;
+              *reinterpret_cast<int2 *>(dst + g * 8 + 2 * t) = make_int2(acc[mt][0], acc[mt][1]);
+              if (VR == 16) *reinterpret_cast<int2 *>(dst + (g + 8) * 8 + 2 * t) = make_int2(acc[mt][2], acc[mt][3]);
+            }
           }
         }
+        LPCB_MARK(3);   // phase B1
         __syncthreads();
+        LPCB_MARK(4);
         // ================= phase B2 + T: GRU-B gates, sampling, signal update =================
         {
           const int l16 = tid & 15, grp = tid >> 4;
@@ -465,9 +515,9 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               const int e = row * 8 + (l16 & 7);
               int32_t ai = acc_seed(s_subB[i] + s_condb[s * kRowsB + i]);
 #pragma unroll
-              for (int kind = 0; kind < P; kind++) ai += s_part[((mt * (P + 1) + kind) * kRGroupsB + rg) * 128 + e];
+              for (int kind = 0; kind < kPartsB; kind++) ai += s_part[((mt * (kPartsB + 1) + kind) * kRGroupsB + rg) * 128 + e];
               zrh[gate] = acc_out(ai);
-              const int32_t ar = acc_seed(s_subB[kRowsB + i]) + s_part[((mt * (P + 1) + P) * kRGroupsB + rg) * 128 + e];
+              const int32_t ar = acc_seed(s_subB[kRowsB + i]) + s_part[((mt * (kPartsB + 1) + kPartsB) * kRGroupsB + rg) * 128 + e];
               rec[gate] = acc_out(ar);
             }
             const float z = sigmoid_ref(zrh[0] + rec[0], s_rcp);
@@ -481,6 +531,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               reinterpret_cast<unsigned char *>(s_xb)[s * kXbStride * 4 + l16] = (unsigned char)quant_u8_fast(b_new);
             }
             __syncwarp();
+            LPCB_MARK(5);   // GRU-B gates
             // sample_mdense (src/nnet.c:163-214)
             uint32_t r0 = 0, r1 = 0;
             if (l16 == 0) {
@@ -504,6 +555,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             int n = 1;
 #pragma unroll
             for (int lvl = 0; lvl < 4; lvl++) n = 2 * n + __shfl_sync(0xffffffffu, bit, gbase + n);
+            LPCB_MARK(6);   // sampler round 1
             // round 2: levels 4..7 below node n
             const int node = (n << d) | (m - (1 << d));
             bit = s_logit[(r1 >> (8 * d)) & 0xffu] < node_logit<FCS>(fc_w, fc_stride, fc_bf, node, bv, s_rcp);
@@ -518,6 +570,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
                 lg[nd] = (nd == 0 || !act) ? 0.f : node_logit<FCS>(fc_w, fc_stride, fc_bf, nd, bv, s_rcp);
               }
             }
+            LPCB_MARK(7);   // sampler round 2
             // signal update (src/lpcnet.c:256-269), one lane per stream
             if (l16 == 0 && stream0 + s < B) {
               const size_t oidx = (size_t)(stream0 + s) * row_len + out_base + step;
@@ -564,7 +617,9 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             }
           }
         }
+        LPCB_MARK(8);   // signal update
         __syncthreads();
+        LPCB_MARK(9);
         cur ^= 1;
       }  // step
     }    // frame
@@ -597,6 +652,10 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
       }
     }
   }  // tile
+#ifdef LPCB_PHASE_CLOCKS
+  if (blockIdx.x == 0 && threadIdx.x == 0 && A.phase_clk)
+    for (int k = 0; k < 10; k++) atomicAdd(A.phase_clk + k, (unsigned long long)clk_[k]);
+#endif
 }
 
 template <int MT, int VR>
@@ -605,10 +664,14 @@ static cudaError_t launch_tile(const SampleArgs &a, int n_sms, cudaStream_t s) {
   const size_t smem = make_layout(NS, MT, a.m.a_rec.n_chunks, a.m.b_in.n_chunks, a.m.b_rec.n_chunks).total;
   const bool dbg = a.trace || a.logits;
   const bool fix = a.m.a_rec.slots[2] != 0;
-  const bool ra = a.m.rcp_arith != 0;   // the trace/logit variants always use the table
+  // Arithmetic rcpps where the kernel is bound by the L1/shared-memory pipe (16+ streams per CTA: 4% faster
+  // at 32); the 8-stream kernel is issue/latency-bound and 3% faster with the table (both measured, B200).
+  // The trace/logit variants always use the table.
+  constexpr bool kArith = NS >= 16;
+  const bool ra = kArith && a.m.rcp_arith != 0;
   void (*kern)(const SampleArgs) =
       dbg ? (fix ? sample_kernel<MT, VR, true, true, false> : sample_kernel<MT, VR, true, false, false>)
-      : ra ? (fix ? sample_kernel<MT, VR, false, true, true> : sample_kernel<MT, VR, false, false, true>)
+      : ra ? (fix ? sample_kernel<MT, VR, false, true, kArith> : sample_kernel<MT, VR, false, false, kArith>)
            : (fix ? sample_kernel<MT, VR, false, true, false> : sample_kernel<MT, VR, false, false, false>);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
