@@ -321,8 +321,28 @@ def run_gpu(args):
         except Exception:
             l2_peak = None
         hbm_bytes_per_sample = 2.0 + (stride * 4 + (1152 + 48 + 16) * 4 * 2) / FRAME   # pcm + features + conditioning w/r
+        # DRAM bytes of one sample_kernel launch from the committed ncu --set full capture of this command
+        # (profiles/r1_traffic.json); null when the workload differs from the captured one.
+        traffic = None
+        tile_used = bt.tile
+        n_sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))["sample_kernel"]
+            frames_per_launch = active_frames * args.steps / max(1, n_sample)
+            if tj["streams"] == B and tj["tile_streams_per_cta"] == tile_used and abs(tj["frames_per_launch"] - frames_per_launch) < 2:
+                traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
+        except Exception:
+            traffic = None
+        # L1/shared-memory data pipe (128 B/clk/SM): bytes the algorithm moves through it per stream-sample --
+        # the four gathered input rows, the A fragments (4 B per block per stream), the B fragments (256 B per
+        # chunk, shared by the streams of a CTA) and the 30 dual-FC nodes the sampler evaluates
+        chunks = bt.chunks_a + bt.nblocks_b / 8.0 + 6
+        smem_bytes = gather_bytes + 32.0 * chunks + 256.0 * chunks / tile_used + 30 * 128
+        sm_clock = (clk or {}).get("sm_mhz") or 1965.0
+        smem_peak = 128.0 * n_sms * sm_clock * 1e6 / 1e9
+        smem_gbs = smem_bytes * samples_per_launch / kernel_s / 1e9
         roofline = {"bound": "tensor", "kernel": "sample_kernel", "achieved": int8_tops, "peak": int8_peak,
-                    "unit": "TFLOP/s", "frac": int8_tops / int8_peak, "traffic": None,
+                    "unit": "TFLOP/s", "frac": int8_tops / int8_peak, "traffic": traffic,
                     "peak_source": f"2 x bf16_tflops_sustained ({pk['src']})",
                     "ops_per_stream_sample": ops_per_sample, "avg_launch_ms": kernel_s * 1e3,
                     "launches": n_sample, "share_of_step": sample_ms / ms,
@@ -332,6 +352,9 @@ def run_gpu(args):
                    "frac": (gather_gbs / l2_peak) if l2_peak else None,
                    "bytes_per_stream_sample": gather_bytes,
                    "peak_source": "lpcnet_b200_measure_l2_gather (random 4608 B rows from a 3.5 MB L2-resident table)"}
+        roof_smem = {"bound": "l1_shared_data_pipe", "achieved": smem_gbs, "peak": smem_peak, "unit": "GB/s",
+                     "frac": smem_gbs / smem_peak, "bytes_per_stream_sample": smem_bytes,
+                     "peak_source": f"128 B/clk/SM x {n_sms} SMs x {sm_clock:.0f} MHz (SM clock sampled during the run)"}
         roof_hbm = {"bound": "hbm", "achieved": hbm_bytes_per_sample * value / world / 1e9, "peak": pk["hbm_gbs"],
                     "unit": "GB/s", "frac": hbm_bytes_per_sample * value / world / 1e9 / pk["hbm_gbs"]}
         # ---- CPU baseline: bounded sample of the same workload on the host cores ----
@@ -353,7 +376,7 @@ def run_gpu(args):
             "x_realtime": value / 16000.0,
             "step_latency_us": kernel_s * 1e6 / (active_frames * FRAME * args.steps / max(1, n_sample)),
             "config": {"workload": f"batched -synthesis, {B} streams x {args.seconds:g} s per GPU (BASELINE configs[1])",
-                       "streams_per_gpu": B, "seconds": args.seconds, "tile_streams_per_cta": args.tile or "auto",
+                       "streams_per_gpu": B, "seconds": args.seconds, "tile_streams_per_cta": bt.tile,
                        "model": "random-init, N=384 NB=16 density (0.05,0.05,0.2), reference blob layout",
                        "parallelism": f"streams sharded over {world} GPU(s), no collective",
                        "l2": f"inputs larger than L2 (features {h_feat.numel() * 4 / 2**20:.0f} MiB + pcm "
@@ -361,7 +384,7 @@ def run_gpu(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h_feat.numel() * 4 * world,
                     "d2h_bytes_per_step": h_pcm.numel() * 2 * world, "steps": k_e2e},
             "gpu_launches": launches, "clocks": clk,
-            "roofline": roofline, "roofline_l2": roof_l2, "roofline_hbm": roof_hbm,
+            "roofline": roofline, "roofline_smem": roof_smem, "roofline_l2": roof_l2, "roofline_hbm": roof_hbm,
             "frame_network_share_of_step": frame_ms / ms,
             "cpu_baseline": cpu,
         }

@@ -162,7 +162,7 @@ LPCNET_B200_EXPORT int lpcnet_batch_set_state(LPCNetBatch *b, int stream, const 
 LPCNET_B200_EXPORT int lpcnet_batch_sync(LPCNetBatch *b);
 /* Model facts.  which = 0 / 1: number of block-sparse 8x4 blocks in GRU-A / GRU-B input (for the op
  * counts); 2: 1 when the rcpps estimate is computed arithmetically (the table was verified equal on this
- * GPU), 0 when looked up; 3: 1 when GRU-A runs the unrolled fixed-slot path; 4: GRU-A chunks of 8 blocks;
+ * GPU), 0 when looked up; 3: 1 when GRU-A runs the unrolled fixed-slot path; 4: GRU-A chunks of 8 blocks; 5: streams per CTA in effect;
  * 8 / 16 / 32: bytes of shared memory the sample kernel needs per CTA at that many streams per CTA. */
 LPCNET_B200_EXPORT int lpcnet_batch_nblocks(const LPCNetBatch *b, int which);
 /* Kernels launched by this batch so far (for bench.py's gpu_launches). */

@@ -318,6 +318,7 @@ int lpcnet_batch_nblocks(const LPCNetBatch *b, int which) {
     case 2: return b->model.d.rcp_arith;               // 1: reciprocal estimate computed, 0: table lookup
     case 3: return b->model.d.a_rec.slots[2] != 0;     // 1: GRU-A runs the unrolled fixed-slot path
     case 4: return b->model.d.a_rec.n_chunks;
+    case 5: return auto_tile(b);                        // streams per CTA the next synthesize call will use
     case 8: case 16: case 32: return (int)sample_kernel_smem(which, b->model.d);   // bytes of shared memory per CTA
     default: return 0;
   }

@@ -28,6 +28,11 @@ constexpr int kRowsB = 3 * kNB;  // 48
 constexpr int kXaStride = kN / 4 + 4;    // words per stream (100)
 constexpr int kXbStride = kNB / 4;       // 4: eight streams x four words = 32 distinct banks
 
+// Phase B1 of the sample kernel: the GRU-B input product of a row group is split into kPartsB K ranges
+// (one warp job each); model.cu pads every range to a multiple of kPadB chunks (the unroll factors 3, 2, 1).
+constexpr int kPartsB = 2;
+constexpr int kPadB = 6;
+
 // Column order of the GRU-A input rows (embedding tables, frame conditioning) in device memory:
 // the z and r values a lane needs sit in one 16-byte piece, [ug][t][z0 z1 r0 r1], followed by the
 // candidate gate in natural order.  col = gate*384 + unit  ->  storage index.
@@ -62,7 +67,7 @@ struct DevSparse {
   const uint32_t *chunk_start;  // device
   const uint2 *pos;             // device, [n_chunks]
   const uint32_t *w;            // device, [n_chunks][64]
-  const uint32_t *off;          // device, [n_chunks][4] (GRU-A only)
+  const uint32_t *off;          // device, [n_chunks][4]
   const uint32_t *off_fixed;    // device, [unit groups][4][8] (GRU-A only)
   int slots[3];                 // fixed chunk slots per gate per unit group (0,0,0 = all chunks in the overflow lists)
 };

@@ -55,7 +55,7 @@ struct Builder {
 // find_idx_check (parse_lpcnet_weights.c:90-113) + re-tiling.  `idx` NULL means a dense
 // dotp-layout matrix [rows/8][cols/4][8][4] (dump_lpcnet.py:56-60).
 bool pack_sparse(PackedSparse &ps, const int32_t *idx, int idx_len, const int8_t *w, int w_bytes, int rows,
-                 int cols, std::string &err, const char *what, bool slotted = false) {
+                 int cols, std::string &err, const char *what, bool slotted = false, int parts = 1, int pad_to = 1) {
   ps.n_groups = rows / 8;
   ps.chunk_start.assign(ps.n_groups + 1, 0);
   std::vector<std::vector<int>> gpos(ps.n_groups);
@@ -135,17 +135,32 @@ bool pack_sparse(PackedSparse &ps, const int32_t *idx, int idx_len, const int8_t
     }
   };
   if (!slotted) {
+    // every row group's chunks split into `parts` K ranges (one kernel job each), each range padded with
+    // empty chunks to a multiple of `pad_to` so that the kernel's unrolled loops need no tail
     int nchunks = 0;
+    ps.chunk_start.assign((size_t)ps.n_groups * parts + 1, 0);
+    std::vector<int> first(ps.n_groups * parts), count(ps.n_groups * parts);
     for (int g = 0; g < ps.n_groups; g++) {
-      ps.chunk_start[g] = nchunks;
-      nchunks += ((int)gpos[g].size() + 7) / 8;
+      const int n = (int)gslots[g].size() / 8;
+      for (int p = 0; p < parts; p++) {
+        const int lo = n * p / parts, hi = n * (p + 1) / parts;
+        ps.chunk_start[g * parts + p] = nchunks;
+        first[g * parts + p] = lo; count[g * parts + p] = hi - lo;
+        nchunks += (hi - lo + pad_to - 1) / pad_to * pad_to;
+      }
     }
-    ps.chunk_start[ps.n_groups] = nchunks;
+    ps.chunk_start[(size_t)ps.n_groups * parts] = nchunks;
     ps.n_chunks = nchunks;
     ps.pos.assign((size_t)nchunks * 8, 0);
     ps.w.assign((size_t)nchunks * 64, 0);
     for (int g = 0; g < ps.n_groups; g++)
-      for (int b = 0; b < (int)gslots[g].size(); b++) emit(ps.chunk_start[g] + b / 8, b % 8, gslots[g][b]);
+      for (int p = 0; p < parts; p++)
+        for (int k = 0; k < count[g * parts + p] * 8; k++)
+          emit(ps.chunk_start[g * parts + p] + k / 8, k % 8, gslots[g][(size_t)first[g * parts + p] * 8 + k]);
+    ps.off.assign((size_t)nchunks * 4, 0);
+    for (int c = 0; c < nchunks; c++)
+      for (int t = 0; t < 4; t++)
+        ps.off[(size_t)c * 4 + t] = (uint32_t)ps.pos[(size_t)c * 8 + t] * 4u | ((uint32_t)ps.pos[(size_t)c * 8 + 4 + t] * 4u) << 16;
   } else {
     // rows are gate-major: group index = gate*(n_groups/3) + ug
     const int nug = ps.n_groups / 3;
@@ -333,7 +348,7 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
     auto ib = A.find("gru_b_weights_idx"), wb = A.find("gru_b_weights");
     if (ib == A.end() || wb == A.end()) { err = "missing GRU-B input arrays"; return false; }
     if (!pack_sparse(pb, reinterpret_cast<const int32_t *>(ib->second.data), ib->second.size / 4,
-                     reinterpret_cast<const int8_t *>(wb->second.data), wb->second.size, kRowsB, kN, err, "gru_b"))
+                     reinterpret_cast<const int8_t *>(wb->second.data), wb->second.size, kRowsB, kN, err, "gru_b", false, kPartsB, kPadB))
       return false;
     const unsigned char *wr = need("gru_b_recurrent_weights", kRowsB * kNB);
     if (!wr) return false;

@@ -39,7 +39,6 @@ struct SmemLayout {
   unsigned total;
 };
 
-constexpr int kPartsB = 2;   // K-split of the GRU-B input product (phase B1 jobs = 6 row groups x (kPartsB + 1))
 
 constexpr int kFcStride = 36;   // 32 weights per node padded so that 8 lanes' 16-byte reads hit disjoint banks
 __host__ __device__ inline bool fc_resident(int NS) { return NS <= 32; }
@@ -49,8 +48,8 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
   unsigned o = 0;
   auto take = [&](unsigned bytes) { unsigned r = o; o += (bytes + 15u) & ~15u; return r; };
   L.wA = take(chA * 256); L.posA = take(chA * 16); L.offF = take(kN / 8 * 32 * 4); L.csA = take((kN / 8 + 1) * 4);
-  L.wBi = take(chBi * 256); L.posBi = take(chBi * 8); L.csBi = take((kRGroupsB + 1) * 4);
-  L.wBr = take(chBr * 256); L.posBr = take(chBr * 8); L.csBr = take((kRGroupsB + 1) * 4);
+  L.wBi = take(chBi * 256); L.posBi = take(chBi * 16); L.csBi = take((kRGroupsB * kPartsB + 1) * 4);
+  L.wBr = take(chBr * 256); L.posBr = take(chBr * 16); L.csBr = take((kRGroupsB + 1) * 4);
   L.sdA = take(kRowsA * 8); L.subB = take(2 * kRowsB * 4);
   L.rcp = take(2048 * 4); L.u2l = take(256 * 4); L.logit = take(256 * 4);
   L.xa = take(2 * NS * kXaStride * 4);
@@ -139,10 +138,10 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   uint32_t *s_offF = reinterpret_cast<uint32_t *>(smem + L.offF);   // [ug][lane%4][8] offsets of the fixed chunks
   uint32_t *s_csA = reinterpret_cast<uint32_t *>(smem + L.csA);     // [ug + 1] overflow chunk lists
   uint32_t *s_wBi = reinterpret_cast<uint32_t *>(smem + L.wBi);
-  uint2 *s_posBi = reinterpret_cast<uint2 *>(smem + L.posBi);
+  uint32_t *s_offBi = reinterpret_cast<uint32_t *>(smem + L.posBi);   // [chunk][lane%4] packed gather offsets
   uint32_t *s_csBi = reinterpret_cast<uint32_t *>(smem + L.csBi);
   uint32_t *s_wBr = reinterpret_cast<uint32_t *>(smem + L.wBr);
-  uint2 *s_posBr = reinterpret_cast<uint2 *>(smem + L.posBr);
+  uint32_t *s_offBr = reinterpret_cast<uint32_t *>(smem + L.posBr);
   uint32_t *s_csBr = reinterpret_cast<uint32_t *>(smem + L.csBr);
   float *s_sdA = reinterpret_cast<float *>(smem + L.sdA);   // [gate][ug][lane%4][sub0 sub1 diag0 diag1]
   float *s_subB = reinterpret_cast<float *>(smem + L.subB);
@@ -186,10 +185,10 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
     if (FIX) copy_words(s_offF, M.a_rec.off_fixed, kUGroups * 32);
     copy_words(s_csA, M.a_rec.chunk_start, kUGroups + 1);
     copy_words(s_wBi, M.b_in.w, M.b_in.n_chunks * 64);
-    copy_words(reinterpret_cast<uint32_t *>(s_posBi), reinterpret_cast<const uint32_t *>(M.b_in.pos), M.b_in.n_chunks * 2);
-    copy_words(s_csBi, M.b_in.chunk_start, kRGroupsB + 1);
+    copy_words(s_offBi, M.b_in.off, M.b_in.n_chunks * 4);
+    copy_words(s_csBi, M.b_in.chunk_start, kRGroupsB * kPartsB + 1);
     copy_words(s_wBr, M.b_rec.w, M.b_rec.n_chunks * 64);
-    copy_words(reinterpret_cast<uint32_t *>(s_posBr), reinterpret_cast<const uint32_t *>(M.b_rec.pos), M.b_rec.n_chunks * 2);
+    copy_words(s_offBr, M.b_rec.off, M.b_rec.n_chunks * 4);
     copy_words(s_csBr, M.b_rec.chunk_start, kRGroupsB + 1);
     for (int i = tid; i < kRowsA; i += kThreads) {
       const int k = (i >> 3) * 16 + ((i & 7) >> 1) * 4 + (i & 1);   // [gate*48 + ug][lane%4][.]
@@ -438,58 +437,75 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
         __syncthreads();
         LPCB_MARK(2);   // wait for the other warps
         // ================= phase B1: GRU-B products =================
-        // jobs: (row group, K half) of the input product on the new GRU-A state, then the recurrent product;
-        // every job covers all M tiles so the B fragments are fetched once.  Loads of UB chunks are issued
-        // before their MMAs.
+        // jobs 0..11: (row group, K half) of the input product on the new GRU-A state, on warps 0..11; jobs
+        // 12..17: the recurrent product, on warps 12..15 and again 12, 13.  Every job covers all M tiles so
+        // the B fragments are fetched once; the input ranges are padded to whole unroll groups (model.cu),
+        // and the loads of a group are issued before its MMAs.
         {
-          constexpr int JOBS = kRGroupsB * (kPartsB + 1);
+          constexpr int NIN = kRGroupsB * kPartsB, JOBS = NIN + kRGroupsB;
           constexpr int UB = MT == 1 ? 3 : (MT == 2 ? 2 : 1);
-          for (int job = warp; job < JOBS; job += kWarps) {
-            const int kind = job / kRGroupsB, rg = job % kRGroupsB;
-            const bool inp = kind < kPartsB;
-            int lo, hi;
-            if (inp) {
-              const int cs = s_csBi[rg], n = s_csBi[rg + 1] - cs;
-              lo = cs + (n * kind) / kPartsB; hi = cs + (n * (kind + 1)) / kPartsB;
-            } else {
-              lo = s_csBr[rg]; hi = s_csBr[rg + 1];
-            }
-            const uint2 *wq = reinterpret_cast<const uint2 *>(inp ? s_wBi : s_wBr) + lane;
-            const uint2 *pq = inp ? s_posBi : s_posBr;
-            const uint32_t *xbase = (inp ? xa_new : s_xb) + g * (inp ? kXaStride : kXbStride);
-            const int tstride = VR * (inp ? kXaStride : kXbStride), hstride = 8 * (inp ? kXaStride : kXbStride);
+          static_assert(kPadB % UB == 0, "padding must cover the unroll factor");
+          for (int job = warp; job < JOBS; job = (job >= NIN && job + 4 < JOBS) ? job + 4 : JOBS) {
             int32_t acc[MT][4];
 #pragma unroll
             for (int mt = 0; mt < MT; mt++) acc[mt][0] = acc[mt][1] = acc[mt][2] = acc[mt][3] = 0;
-            for (int c = lo; c < hi; c += UB) {
-              uint2 bw[UB];
-              uint32_t plo[UB], phi[UB], a[UB][MT][4];
+            int slot;
+            if (job < NIN) {
+              const unsigned char *xb0 = reinterpret_cast<const unsigned char *>(xa_new + g * kXaStride);
+              const int hi = s_csBi[job + 1];
+              for (int c = s_csBi[job]; c < hi; c += UB) {
+                uint2 bw[UB];
+                uint32_t pk[UB], a[UB][MT][4];
 #pragma unroll
-              for (int k = 0; k < UB; k++) {
-                const bool on = c + k < hi;
-                const int cc = on ? c + k : c;
-                const uint2 pp = pq[cc];
-                bw[k] = wq[cc * 32];
-                if (!on) bw[k] = make_uint2(0u, 0u);
-                plo[k] = (pp.x >> (8 * t)) & 0xffu; phi[k] = (pp.y >> (8 * t)) & 0xffu;
-              }
-#pragma unroll
-              for (int k = 0; k < UB; k++)
-#pragma unroll
-                for (int mt = 0; mt < MT; mt++) {
-                  const uint32_t *xrow = xbase + mt * tstride;
-                  a[k][mt][0] = xrow[plo[k]]; a[k][mt][2] = xrow[phi[k]];
-                  a[k][mt][1] = a[k][mt][3] = 0;
-                  if (VR == 16) { a[k][mt][1] = xrow[hstride + plo[k]]; a[k][mt][3] = xrow[hstride + phi[k]]; }
+                for (int k = 0; k < UB; k++) {
+                  pk[k] = s_offBi[(c + k) * 4 + t];
+                  bw[k] = reinterpret_cast<const uint2 *>(s_wBi)[(c + k) * 32 + lane];
                 }
 #pragma unroll
-              for (int k = 0; k < UB; k++)
+                for (int k = 0; k < UB; k++)
 #pragma unroll
-                for (int mt = 0; mt < MT; mt++) mma_u8s8(acc[mt], a[k][mt][0], a[k][mt][1], a[k][mt][2], a[k][mt][3], bw[k].x, bw[k].y);
+                  for (int mt = 0; mt < MT; mt++) {
+                    const unsigned char *xr = xb0 + mt * VR * kXaStride * 4;
+                    const uint32_t lo = pk[k] & 0xffffu, hi2 = pk[k] >> 16;
+                    a[k][mt][0] = *reinterpret_cast<const uint32_t *>(xr + lo);
+                    a[k][mt][2] = *reinterpret_cast<const uint32_t *>(xr + hi2);
+                    a[k][mt][1] = a[k][mt][3] = 0;
+                    if (VR == 16) {
+                      a[k][mt][1] = *reinterpret_cast<const uint32_t *>(xr + 8 * kXaStride * 4 + lo);
+                      a[k][mt][3] = *reinterpret_cast<const uint32_t *>(xr + 8 * kXaStride * 4 + hi2);
+                    }
+                  }
+#pragma unroll
+                for (int k = 0; k < UB; k++)
+#pragma unroll
+                  for (int mt = 0; mt < MT; mt++) mma_u8s8(acc[mt], a[k][mt][0], a[k][mt][1], a[k][mt][2], a[k][mt][3], bw[k].x, bw[k].y);
+              }
+              // s_part index: [mt][kind][rg] with job = rg * kPartsB + kind
+              slot = (job % kPartsB) * kRGroupsB + job / kPartsB;
+            } else {
+              const int rg = job - NIN;
+              const unsigned char *xb0 = reinterpret_cast<const unsigned char *>(s_xb + g * kXbStride);
+              for (int c = s_csBr[rg]; c < (int)s_csBr[rg + 1]; c++) {
+                const uint32_t pk = s_offBr[c * 4 + t];
+                const uint2 bw = reinterpret_cast<const uint2 *>(s_wBr)[c * 32 + lane];
+                const uint32_t lo = pk & 0xffffu, hi2 = pk >> 16;
+#pragma unroll
+                for (int mt = 0; mt < MT; mt++) {
+                  const unsigned char *xr = xb0 + mt * VR * kXbStride * 4;
+                  const uint32_t a0 = *reinterpret_cast<const uint32_t *>(xr + lo), a2 = *reinterpret_cast<const uint32_t *>(xr + hi2);
+                  uint32_t a1 = 0, a3 = 0;
+                  if (VR == 16) {
+                    a1 = *reinterpret_cast<const uint32_t *>(xr + 8 * kXbStride * 4 + lo);
+                    a3 = *reinterpret_cast<const uint32_t *>(xr + 8 * kXbStride * 4 + hi2);
+                  }
+                  mma_u8s8(acc[mt], a0, a1, a2, a3, bw.x, bw.y);
+                }
+              }
+              slot = kPartsB * kRGroupsB + rg;
             }
 #pragma unroll
             for (int mt = 0; mt < MT; mt++) {
-              int32_t *dst = s_part + ((mt * (kPartsB + 1) + kind) * kRGroupsB + rg) * 128;
+              int32_t *dst = s_part + (mt * (kPartsB + 1) * kRGroupsB + slot) * 128;
               *reinterpret_cast<int2 *>(dst + g * 8 + 2 * t) = make_int2(acc[mt][0], acc[mt][1]);
               if (VR == 16) *reinterpret_cast<int2 *>(dst + (g + 8) * 8 + 2 * t) = make_int2(acc[mt][2], acc[mt][3]);
             }

@@ -189,6 +189,15 @@ class Batch:
         return self.L.lpcnet_batch_nblocks(self.h, 1)
 
     @property
+    def chunks_a(self):
+        return self.L.lpcnet_batch_nblocks(self.h, 4)
+
+    @property
+    def tile(self):
+        """streams per CTA the sample kernel runs with (set_tile, or the automatic choice)"""
+        return self.L.lpcnet_batch_nblocks(self.h, 5)
+
+    @property
     def rcp_arith(self):
         return bool(self.L.lpcnet_batch_nblocks(self.h, 2))
 
