@@ -383,7 +383,8 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             // offset word name the gate
             {
               const int c0 = s_csA[ug], c1 = s_csA[ug + 1];
-              for (int c = c0; c < c1; c++) {
+#pragma unroll 1
+              for (int c = c0; c < c1; c++) {   // rarely more than one trip: keep the code small (instruction cache)
                 const uint32_t pk = s_offA[c * 4 + t];
                 const uint2 bw = reinterpret_cast<const uint2 *>(s_wA)[c * 32 + lane];
                 const uint32_t lo = pk & 0xffffu, hi = (pk >> 16) & 0x3fffu, gate = pk >> 30;

@@ -285,3 +285,46 @@ def test_full_size_batch_invariance(eng, model_blob, orc_model):
         assert np.array_equal(pcm[s], ref), s
     assert (pcm[:, :320] == 0).all() and (pcm[:, 320:] != 0).any()
     bt.close()
+
+
+def test_full_size_decode_batch_invariance(eng, model_blob, golden_decode, codebooks, orc_model):
+    """BASELINE config 3 size (8192 streams, 32-streams-per-CTA regime): every stream decodes one of 16
+    packet sequences; equal inputs must give equal outputs whatever the slot, the first sequence must give
+    the reference's decoded features, and sampled streams must equal the oracle on their features."""
+    B, NP = 8192, 2
+    pk = golden_decode["packets"]                               # [24][8]
+    seqs = np.stack([np.roll(pk, -k, axis=0)[:NP] for k in range(16)])
+    packets = seqs[np.arange(B) % 16]
+    bt = eng.Batch(model_blob, B)
+    assert bt.tile == 32
+    bt.set_codebooks(codebooks)
+    pcm, feats = bt.decode(packets, want_features=True)
+    for k in range(16):
+        assert (pcm[k::16] == pcm[k]).all(), k
+        assert (bits(feats[k::16]) == bits(feats[k])).all(), k
+    assert np.array_equal(bits(feats[0]), bits(golden_decode["features"][:NP].reshape(4 * NP, 36)))
+    for s in (0, 5, 8191):
+        ref = orcpy.OrcStream(orc_model).run(feats[s])[0]
+        assert np.array_equal(pcm[s], ref), s
+    bt.close()
+
+
+def test_sweep_size_sharded_invariance(eng, model_blob, orc_model):
+    """BASELINE config 5 shape on one GPU: 16384 streams (several tiles per CTA), the shard a rank would own
+    under lpcnet_b200.sharding; outputs repeat with the 256-stream input period and match the oracle."""
+    from lpcnet_b200 import sharding
+    total, world = 65536, 4
+    lo, hi = sharding.shard_range(total, 1, world)
+    B, F = hi - lo, 4
+    assert B == 16384
+    base = np.stack([blob.synthetic_features(F, s) for s in range(256)])
+    feats = base[(lo + np.arange(B)) % 256]
+    bt = eng.Batch(model_blob, B)
+    for s in range(B):
+        bt.set_seed(s, blob.stream_seed((lo + s) % 256))
+    pcm, _, _ = bt.synthesize(feats)
+    assert (pcm.reshape(B // 256, 256, -1) == pcm[:256]).all()
+    for s in (0, 255):
+        ref = orcpy.OrcStream(orc_model, blob.stream_seed((lo + s) % 256)).run(feats[s])[0]
+        assert np.array_equal(pcm[s], ref), s
+    bt.close()
