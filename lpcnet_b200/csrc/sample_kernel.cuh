@@ -33,8 +33,8 @@ struct SmemLayout {
   // byte offsets
   unsigned wA, posA, offF, csA, wBi, posBi, csBi, wBr, posBr, csBr;
   unsigned sdA, subB, rcp, u2l, logit;
-  unsigned xa, xb, bst, lsig, lpc, condb, part;
-  unsigned usig, upred, lexc, pred, deemph, rng, head, act, ix;
+  unsigned xa, xb, bst, condb, part;
+  unsigned usig, upred, lexc, deemph, rng, act, ix, tst;
   unsigned fcw, fcb;   // dual_fc weights (node stride kFcStride floats) and bias|factor, when resident
   unsigned total;
 };
@@ -55,11 +55,11 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
   L.xa = take(2 * NS * kXaStride * 4);
   L.xb = take(NS * kXbStride * 4);
   L.bst = take(NS * 20 * 4);
-  L.lsig = take(16 * NS * 4); L.lpc = take(16 * NS * 4);
   L.condb = take(NS * kRowsB * 4);
   L.part = take(MT * (kPartsB + 1) * kRGroupsB * 128 * 4);
-  L.usig = take(NS * 4); L.upred = take(NS * 4); L.lexc = take(NS * 4); L.pred = take(NS * 4);
-  L.deemph = take(NS * 4); L.rng = take(4 * NS * 4); L.head = take(NS * 4); L.act = take(NS * 4); L.ix = take(NS * 4);
+  L.usig = take(NS * 4); L.upred = take(NS * 4); L.lexc = take(NS * 4);
+  L.deemph = take(NS * 4); L.rng = take(4 * NS * 4); L.act = take(NS * 4); L.ix = take(NS * 4);
+  L.tst = NS >= 32 ? take(3 * kThreads * 4) : 0;
   L.fcb = take(4 * 256 * 4);
   L.fcw = fc_resident(NS) ? take(256 * kFcStride * 4) : 0;
   L.total = o;
@@ -129,6 +129,9 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   constexpr int NV = (VR == 16) ? 4 : 2;   // accumulator registers in use per thread
   constexpr bool CREG = (MT == 1 && VR == 8);   // frame conditioning of GRU-A held in registers (18 per thread)
   constexpr bool FCS = NS <= 32;            // dual_fc resident in shared memory (fc_resident)
+  // 32 streams per CTA: phase A has no registers to spare, so the three phase-T values each thread carries
+  // from step to step wait in shared memory while phase A runs (measured +2 %; -2 % for the smaller tiles)
+  constexpr bool TST = NS >= 32;
   extern __shared__ __align__(16) unsigned char smem[];
   const DevModel &M = A.m;
   const SmemLayout L = make_layout(NS, MT, M.a_rec.n_chunks, M.b_in.n_chunks, M.b_rec.n_chunks);
@@ -152,19 +155,16 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   uint32_t *s_xa = reinterpret_cast<uint32_t *>(smem + L.xa);
   uint32_t *s_xb = reinterpret_cast<uint32_t *>(smem + L.xb);
   float *s_bst = reinterpret_cast<float *>(smem + L.bst);
-  float *s_lsig = reinterpret_cast<float *>(smem + L.lsig);
-  float *s_lpc = reinterpret_cast<float *>(smem + L.lpc);
   float *s_condb = reinterpret_cast<float *>(smem + L.condb);
   int32_t *s_part = reinterpret_cast<int32_t *>(smem + L.part);
   int *s_usig = reinterpret_cast<int *>(smem + L.usig);
   int *s_upred = reinterpret_cast<int *>(smem + L.upred);
   int *s_lexc = reinterpret_cast<int *>(smem + L.lexc);
-  float *s_pred = reinterpret_cast<float *>(smem + L.pred);
   float *s_deemph = reinterpret_cast<float *>(smem + L.deemph);
   uint32_t *s_rng = reinterpret_cast<uint32_t *>(smem + L.rng);
-  int *s_head = reinterpret_cast<int *>(smem + L.head);
   int *s_act = reinterpret_cast<int *>(smem + L.act);
-  uint32_t *s_ix = reinterpret_cast<uint32_t *>(smem + L.ix);   // u_sig | u_pred << 8 | last_exc << 16 | active << 24
+  uint32_t *s_ix = reinterpret_cast<uint32_t *>(smem + L.ix);
+  float *s_tst = reinterpret_cast<float *>(smem + L.tst);   // u_sig | u_pred << 8 | last_exc << 16 | active << 24
   // dual_fc weights: resident copy (padded node stride) or the blob array in global memory; bias|factor resident
   const float *fc_w = FCS ? reinterpret_cast<const float *>(smem + L.fcw) : M.fc_w;
   const int fc_stride = FCS ? kFcStride : 32;
@@ -242,13 +242,18 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
       float v = A.st.gru_b[(size_t)gs * kNB + j];
       s_bst[s * 20 + j] = v;
       reinterpret_cast<unsigned char *>(s_xb)[s * kXbStride * 4 + j] = (unsigned char)quant_u8_ref(v);
-      s_lsig[j * NS + s] = A.st.last_sig[(size_t)gs * 16 + j];
     }
+    // Phase T state of the 16-lane group that owns stream `grp` of the tile (NS <= 32 groups): lane j holds
+    // last_sig[j] (j = 0 newest) and lpc[j]; the LPC prediction is known to all 16 lanes.
+    const int l16 = tid & 15, grp = tid >> 4;
+    const unsigned gbase = lane & 16;
+    const bool twarp = 2 * warp < NS;                       // both 16-lane halves own a stream (NS is even)
+    const int tgs = min(stream0 + min(grp, NS - 1), B - 1);
+    float t_x = A.st.last_sig[(size_t)tgs * 16 + l16], t_lpc = 0.f, t_pred = 0.f;
     for (int s = tid; s < NS; s += kThreads) {
       const int gs = min(stream0 + s, B - 1);
       s_deemph[s] = A.st.deemph[gs];
       s_lexc[s] = A.st.last_exc[gs];
-      s_head[s] = 0;
 #pragma unroll
       for (int k = 0; k < 4; k++) s_rng[k * NS + s] = A.st.rng[(size_t)gs * 4 + k];
     }
@@ -256,11 +261,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
 
     for (int f = 0; f < A.n_frames; f++) {
       // ---- frame prologue: LPC, GRU-B conditioning, active flags ----
-      for (int i = tid; i < NS * 16; i += kThreads) {
-        const int s = i >> 4, j = i & 15;
-        const int gs = min(stream0 + s, B - 1);
-        s_lpc[j * NS + s] = A.lpc[((size_t)f * B + gs) * 16 + j];
-      }
+      t_lpc = A.lpc[((size_t)f * B + tgs) * 16 + l16];
       for (int i = tid; i < NS * kRowsB; i += kThreads) {
         const int s = i / kRowsB, j = i % kRowsB;
         const int gs = min(stream0 + s, B - 1);
@@ -297,19 +298,22 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
         }
         continue;
       }
-      // LPC prediction + mu-law indices for step 0 (src/lpcnet.c:252-254)
-      auto predict = [&](int s) {
-        const int head = s_head[s];
+      // LPC prediction + mu-law indices of the next step (src/lpcnet.c:252-254), by the 16 lanes of a stream:
+      // lane j forms last_sig[j]*lpc[j]; the sum runs in the reference's order j = 0..15 over shuffles.
+      auto predict = [&]() {
+        const float p = t_x * t_lpc;
         float pred = 0.f;
 #pragma unroll
-        for (int j = 0; j < 16; j++) pred = pred - s_lsig[((head + j) & 15) * NS + s] * s_lpc[j * NS + s];
-        s_pred[s] = pred;
-        const int us = lin2ulaw_ref(s_lsig[head * NS + s]), up = lin2ulaw_ref(pred);
-        s_usig[s] = us;
-        s_upred[s] = up;
-        s_ix[s] = (uint32_t)us | (uint32_t)up << 8 | (uint32_t)s_lexc[s] << 16 | (uint32_t)s_act[s] << 24;
+        for (int j = 0; j < 16; j++) pred = pred - __shfl_sync(0xffffffffu, p, gbase + j);
+        t_pred = pred;
+        const int us = lin2ulaw_ref(__shfl_sync(0xffffffffu, t_x, gbase)), up = lin2ulaw_ref(pred);
+        if (l16 == 0 && grp < NS) {
+          if (DEBUG) { s_usig[grp] = us; s_upred[grp] = up; }
+          s_ix[grp] = (uint32_t)us | (uint32_t)up << 8 | (uint32_t)s_lexc[grp] << 16 | (uint32_t)s_act[grp] << 24;
+        }
       };
-      if (tid < NS) predict(tid);
+      if (twarp) predict();
+      if (TST) { s_tst[tid] = t_x; s_tst[kThreads + tid] = t_lpc; s_tst[2 * kThreads + tid] = t_pred; }
       __syncthreads();
 
       const float *condA_f = A.cond_a + (size_t)f * B * kRowsA;
@@ -517,10 +521,10 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
         LPCB_MARK(4);
         // ================= phase B2 + T: GRU-B gates, sampling, signal update =================
         {
-          const int l16 = tid & 15, grp = tid >> 4;
-          const unsigned gbase = lane & 16;
-          for (int s = grp; s < ((NS + 1) & ~1); s += kThreads / 16) {
+          if (twarp) {
             // pairs of streams share a warp; NS is even so both halves are valid together
+            const int s = grp;
+            if (TST) { t_x = s_tst[tid]; t_lpc = s_tst[kThreads + tid]; t_pred = s_tst[2 * kThreads + tid]; }
             const int mt = s / VR, row = s % VR;
             const int act = s_act[s];
             // compute_gruB (src/nnet.c:326-372)
@@ -588,49 +592,53 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               }
             }
             LPCB_MARK(7);   // sampler round 2
-            // signal update (src/lpcnet.c:256-269), one lane per stream
-            if (l16 == 0 && stream0 + s < B) {
-              const size_t oidx = (size_t)(stream0 + s) * row_len + out_base + step;
-              if (!act) {
-                A.pcm[oidx] = 0;
+            // signal update (src/lpcnet.c:256-269): every lane of the stream follows the scalar recurrence (same
+            // values in all 16 lanes), the history shifts by one lane, lane 0 stores.  Shuffles stay outside the
+            // per-stream conditions: the two streams of a warp may differ in `act`.
+            {
+              const bool valid = stream0 + s < B;
+              const size_t oidx = (size_t)min(stream0 + s, B - 1) * row_len + out_base + step;
+              const float dm = s_deemph[s];
+              float pcm;
+              int forced_v = 0;
+              if (A.forced) {
+                forced_v = A.forced[oidx];
+                const float fo = (float)forced_v;
+                exc = lin2ulaw_ref(fo - 0.85f * dm - t_pred);
+                pcm = fo - 0.85f * dm;
+              } else {
+                pcm = t_pred + s_u2l[exc];
+              }
+              const float x_up = __shfl_up_sync(0xffffffffu, t_x, 1, 16);
+              if (act) t_x = l16 ? x_up : pcm;
+              float out = pcm + 0.85f * dm;
+              const float dm_new = out;
+              if (out < -32767.f) out = -32767.f;
+              if (out > 32767.f) out = 32767.f;
+              const int outv = A.forced ? forced_v : round_half_up_ref(out);
+              if (l16 == 0 && valid) {
+                if (act) {
+                  s_lexc[s] = exc;
+                  s_deemph[s] = dm_new;
+                  A.pcm[oidx] = (short)outv;
+                } else {
+                  A.pcm[oidx] = 0;
+                }
                 if (DEBUG && A.trace) {
                   LPCNetB200Trace tr = {0, 0, 0, 0, 0, 0, 0, 0};
+                  if (act) {
+                    tr.exc = exc; tr.u_sig = s_usig[s]; tr.u_pred = s_upred[s];
+                    tr.rng_z = s_rng[s]; tr.rng_w = s_rng[NS + s];
+                    tr.xa_hash = fnv1a_bytes(reinterpret_cast<const unsigned char *>(xa_new + s * kXaStride), kN);
+                    tr.xb_hash = fnv1a_bytes(reinterpret_cast<const unsigned char *>(s_xb + s * kXbStride), kNB);
+                    tr.pcm = outv;
+                  }
                   reinterpret_cast<LPCNetB200Trace *>(A.trace)[oidx] = tr;
                 }
-              } else {
-                const float pred = s_pred[s];
-                const float dm = s_deemph[s];
-                float pcm;
-                int outv;
-                if (A.forced) {
-                  const float fo = (float)A.forced[oidx];
-                  exc = lin2ulaw_ref(fo - 0.85f * dm - pred);
-                  pcm = fo - 0.85f * dm;
-                } else {
-                  pcm = pred + s_u2l[exc];
-                }
-                const int head = (s_head[s] + 15) & 15;
-                s_head[s] = head;
-                s_lsig[head * NS + s] = pcm;
-                s_lexc[s] = exc;
-                pcm = pcm + 0.85f * dm;
-                s_deemph[s] = pcm;
-                if (pcm < -32767.f) pcm = -32767.f;
-                if (pcm > 32767.f) pcm = 32767.f;
-                if (A.forced) outv = A.forced[oidx];
-                else outv = round_half_up_ref(pcm);
-                A.pcm[oidx] = (short)outv;
-                if (DEBUG && A.trace) {
-                  LPCNetB200Trace tr;
-                  tr.exc = exc; tr.u_sig = s_usig[s]; tr.u_pred = s_upred[s];
-                  tr.rng_z = s_rng[s]; tr.rng_w = s_rng[NS + s];
-                  tr.xa_hash = fnv1a_bytes(reinterpret_cast<const unsigned char *>(xa_new + s * kXaStride), kN);
-                  tr.xb_hash = fnv1a_bytes(reinterpret_cast<const unsigned char *>(s_xb + s * kXbStride), kNB);
-                  tr.pcm = outv;
-                  reinterpret_cast<LPCNetB200Trace *>(A.trace)[oidx] = tr;
-                }
-                if (step + 1 < A.spf) predict(s);
               }
+              __syncwarp();
+              if (step + 1 < A.spf) predict();
+              if (TST) { s_tst[tid] = t_x; s_tst[2 * kThreads + tid] = t_pred; }
             }
           }
         }
@@ -657,9 +665,9 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
       const int s = i >> 4, j = i & 15;
       if (stream0 + s < B) {
         A.st.gru_b[(size_t)(stream0 + s) * kNB + j] = s_bst[s * 20 + j];
-        A.st.last_sig[(size_t)(stream0 + s) * 16 + j] = s_lsig[((s_head[s] + j) & 15) * NS + s];
       }
     }
+    if (grp < NS && stream0 + grp < B) A.st.last_sig[(size_t)(stream0 + grp) * 16 + l16] = t_x;
     for (int s = tid; s < NS; s += kThreads) {
       if (stream0 + s < B) {
         A.st.deemph[stream0 + s] = s_deemph[s];

@@ -4,9 +4,12 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from lpcnet_b200 import blob, engine
 from oracle import orcpy
+if os.environ.get("LPCNET_B200_LIB"):       # A/B runs against another build of the library
+    engine.LIB_PATH = os.environ["LPCNET_B200_LIB"]
 
 def main():
     b = blob.write_blob(blob.random_model())
+    if os.environ.get("QUICK_NO_PARITY"): return main_timing(b)
     om = orcpy.OrcModel(orcpy.OrcLib(), b, 2, 1.0, None)
     B, F = 19, 4
     feats = np.stack([blob.synthetic_features(F, s) for s in range(B)])
@@ -42,6 +45,9 @@ def main():
             bt.close()
     print("PARITY", "OK" if allok else "FAILED", " rcp_arith, fixed_slots =", flags, flush=True)
     if os.environ.get("QUICK_NO_TIMING"): return
+    main_timing(b)
+
+def main_timing(b):
     cfgs = [(1024, 8), (2048, 16), (2368, 16), (4736, 32)]
     if len(sys.argv) > 1:
         cfgs = [tuple(int(x) for x in a.split(":")) for a in sys.argv[1:]]
