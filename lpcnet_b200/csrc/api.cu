@@ -7,6 +7,7 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "../../include/lpcnet_b200.h"
 #include "engine.h"
@@ -68,6 +69,7 @@ struct LPCNetBatch {
   int n_sms = 0;
   int tile = 0;  // 0 = auto
   int max_tile = 32;
+  bool st_cond_compact = false;   // column order of st.cond_a (that of the last frame-network run)
   Model model;
   DevState st{};
   void *st_alloc = nullptr;
@@ -104,7 +106,7 @@ int alloc_state(LPCNetBatch *b) {
   auto take = [&](size_t bytes) { size_t r = off; off += (bytes + 255) & ~size_t(255); return r; };
   const size_t o_c1 = take(B * 168 * 4), o_c2 = take(B * 256 * 4), o_a = take(B * kN * 4), o_b = take(B * kNB * 4);
   const size_t o_ls = take(B * 16 * 4), o_ol = take(B * kMaxDelay * 16 * 4), o_lpc = take(B * 16 * 4);
-  const size_t o_ca = take(B * kRowsA * 4), o_cb = take(B * kRowsB * 4), o_de = take(B * 4), o_le = take(B * 4);
+  const size_t o_ca = take(B * kRowsAP * 4), o_cb = take(B * kRowsB * 4), o_de = take(B * 4), o_le = take(B * 4);
   const size_t o_fc = take(B * 4), o_rng = take(B * 16), o_vq = take(B * 18 * 4);
   CK(cudaMalloc(&b->st_alloc, off));
   CK(cudaMemset(b->st_alloc, 0, off));
@@ -118,8 +120,8 @@ int alloc_state(LPCNetBatch *b) {
 }
 
 int chunk_frames(const LPCNetBatch *b, int n_frames) {
-  // conditioning is 4864 B per stream-frame; keep a chunk under ~256 MB and at most 32 frames
-  long long cap = (256ll << 20) / ((long long)b->n_streams * 4864);
+  // conditioning is 6400 B per stream-frame; keep a chunk under ~320 MB and at most 32 frames
+  long long cap = (320ll << 20) / ((long long)b->n_streams * 6400);
   if (cap < 1) cap = 1;
   if (cap > 32) cap = 32;
   return n_frames < cap ? n_frames : (int)cap;
@@ -133,7 +135,7 @@ int ensure_frame_buffers(LPCNetBatch *b, int F) {
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t r = off; off += (bytes + 255) & ~size_t(255); return r; };
   const size_t o_iv = take(B * (F + 2) * kConvIn * 4), o_c1 = take(B * (F + 2) * kC * 4);
-  const size_t o_ca = take((size_t)F * B * kRowsA * 4), o_cb = take((size_t)F * B * kRowsB * 4);
+  const size_t o_ca = take((size_t)F * B * kRowsAP * 4), o_cb = take((size_t)F * B * kRowsB * 4);
   const size_t o_lpc = take((size_t)F * B * 16 * 4), o_act = take((size_t)F * B);
   const size_t fft_threads = ((B * F + 63) / 64) * 64;
   const size_t o_fft = take(fft_threads * 640 * 4);
@@ -160,6 +162,8 @@ int run_frames(LPCNetBatch *b, const float *d_features, int stride, int f0, int 
   FrameArgs fa{};
   fa.m = b->model.d; fa.st = b->st; fa.fb = b->fb; fa.n_streams = b->n_streams; fa.n_frames = F;
   fa.features = d_features; fa.feature_stride = stride; fa.frame0 = f0; fa.total_frames = total_frames;
+  fa.cond_compact = gru_a_compact_order(auto_tile(b));
+  b->st_cond_compact = fa.cond_compact != 0;
   int nl = 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (b->profiling) { CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventRecord(e0, b->stream)); }
@@ -168,7 +172,7 @@ int run_frames(LPCNetBatch *b, const float *d_features, int stride, int f0, int 
   b->launches += nl;
   // keep the last frame's conditioning in the stream state (lpcnet_private.h:43-47)
   const size_t B = b->n_streams;
-  CK(cudaMemcpyAsync(b->st.cond_a, b->fb.cond_a + (size_t)(F - 1) * B * kRowsA, B * kRowsA * 4, cudaMemcpyDeviceToDevice, b->stream));
+  CK(cudaMemcpyAsync(b->st.cond_a, b->fb.cond_a + (size_t)(F - 1) * B * kRowsAP, B * kRowsAP * 4, cudaMemcpyDeviceToDevice, b->stream));
   CK(cudaMemcpyAsync(b->st.cond_b, b->fb.cond_b + (size_t)(F - 1) * B * kRowsB, B * kRowsB * 4, cudaMemcpyDeviceToDevice, b->stream));
   return 0;
 }
@@ -394,7 +398,7 @@ int lpcnet_batch_reset(LPCNetBatch *b, int stream) {
   CK(cudaMemset(S.last_sig + (size_t)s0 * 16, 0, (size_t)n * 16 * 4));
   CK(cudaMemset(S.old_lpc + (size_t)s0 * kMaxDelay * 16, 0, (size_t)n * kMaxDelay * 16 * 4));
   CK(cudaMemset(S.lpc + (size_t)s0 * 16, 0, (size_t)n * 16 * 4));
-  CK(cudaMemset(S.cond_a + (size_t)s0 * kRowsA, 0, (size_t)n * kRowsA * 4));
+  CK(cudaMemset(S.cond_a + (size_t)s0 * kRowsAP, 0, (size_t)n * kRowsAP * 4));
   CK(cudaMemset(S.cond_b + (size_t)s0 * kRowsB, 0, (size_t)n * kRowsB * 4));
   CK(cudaMemset(S.deemph + s0, 0, (size_t)n * 4));
   CK(cudaMemset(S.frame_count + s0, 0, (size_t)n * 4));
@@ -483,15 +487,16 @@ int lpcnet_batch_frame_network(LPCNetBatch *b, const float *features, int stride
                         (size_t)W * 4, B, cudaMemcpyDeviceToHost));
       return 0;
     };
-    if (fetch(ga, b->fb.cond_a, kRowsA) || fetch(gb, b->fb.cond_b, kRowsB) || fetch(lpc, b->fb.lpc, 16)) return -1;
+    if (fetch(gb, b->fb.cond_b, kRowsB) || fetch(lpc, b->fb.lpc, 16)) return -1;
     if (ga) {
-      // back to the reference's column order (the device rows are in gru_a_col_index order)
-      float tmp[kRowsA];
-      for (size_t s = 0; s < (size_t)B; s++)
-        for (int f = 0; f < F; f++) {
+      // device rows are [F][B][kRowsAP] in gru_a_col_index order; the caller gets the reference's column order
+      std::vector<float> tmp((size_t)F * B * kRowsAP);
+      CK(cudaMemcpy(tmp.data(), b->fb.cond_a, tmp.size() * 4, cudaMemcpyDeviceToHost));
+      for (int f = 0; f < F; f++)
+        for (size_t s = 0; s < (size_t)B; s++) {
+          const float *src = tmp.data() + ((size_t)f * B + s) * kRowsAP;
           float *row = ga + (s * n_frames + f0 + f) * kRowsA;
-          memcpy(tmp, row, sizeof(tmp));
-          for (int col = 0; col < kRowsA; col++) row[col] = tmp[gru_a_col_index(col)];
+          for (int col = 0; col < kRowsA; col++) row[col] = src[gru_a_col_index(col, b->st_cond_compact)];
         }
     }
   }
@@ -540,9 +545,9 @@ int lpcnet_batch_get_state(LPCNetBatch *b, int s, LPCNetB200StreamState *o) {
   CK(cudaMemcpy(o->lpc, S.lpc + (size_t)s * 16, 64, cudaMemcpyDeviceToHost));
   CK(cudaMemcpy(o->old_lpc, S.old_lpc + (size_t)s * kMaxDelay * 16, (size_t)b->model.d.features_delay * 64, cudaMemcpyDeviceToHost));
   {
-    float tmp[kRowsA];
-    CK(cudaMemcpy(tmp, S.cond_a + (size_t)s * kRowsA, kRowsA * 4, cudaMemcpyDeviceToHost));
-    for (int col = 0; col < kRowsA; col++) o->gru_a_condition[col] = tmp[gru_a_col_index(col)];
+    float tmp[kRowsAP];
+    CK(cudaMemcpy(tmp, S.cond_a + (size_t)s * kRowsAP, kRowsAP * 4, cudaMemcpyDeviceToHost));
+    for (int col = 0; col < kRowsA; col++) o->gru_a_condition[col] = tmp[gru_a_col_index(col, b->st_cond_compact)];
   }
   CK(cudaMemcpy(o->gru_b_condition, S.cond_b + (size_t)s * kRowsB, kRowsB * 4, cudaMemcpyDeviceToHost));
   CK(cudaMemcpy(&o->deemph_mem, S.deemph + s, 4, cudaMemcpyDeviceToHost));
@@ -571,9 +576,10 @@ int lpcnet_batch_set_state(LPCNetBatch *b, int s, const LPCNetB200StreamState *i
   CK(cudaMemcpy(S.lpc + (size_t)s * 16, in->lpc, 64, cudaMemcpyHostToDevice));
   CK(cudaMemcpy(S.old_lpc + (size_t)s * kMaxDelay * 16, in->old_lpc, (size_t)b->model.d.features_delay * 64, cudaMemcpyHostToDevice));
   {
-    float tmp[kRowsA];
-    for (int col = 0; col < kRowsA; col++) tmp[gru_a_col_index(col)] = in->gru_a_condition[col];
-    CK(cudaMemcpy(S.cond_a + (size_t)s * kRowsA, tmp, kRowsA * 4, cudaMemcpyHostToDevice));
+    float tmp[kRowsAP] = {0.f};
+    b->st_cond_compact = gru_a_compact_order(auto_tile(b));
+    for (int col = 0; col < kRowsA; col++) tmp[gru_a_col_index(col, b->st_cond_compact)] = in->gru_a_condition[col];
+    CK(cudaMemcpy(S.cond_a + (size_t)s * kRowsAP, tmp, kRowsAP * 4, cudaMemcpyHostToDevice));
   }
   CK(cudaMemcpy(S.cond_b + (size_t)s * kRowsB, in->gru_b_condition, kRowsB * 4, cudaMemcpyHostToDevice));
   CK(cudaMemcpy(S.deemph + s, &in->deemph_mem, 4, cudaMemcpyHostToDevice));

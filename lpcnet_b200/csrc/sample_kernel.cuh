@@ -68,9 +68,16 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
 
 __device__ __forceinline__ float2 ldg2(const float *p) { return __ldg(reinterpret_cast<const float2 *>(p)); }
 
-// the six GRU-A input values of lane t for one unit group from a row in gru_a_col_index order
-// (engine.h): one 16-byte piece [z0 z1 r0 r1] and one 8-byte piece [h0 h1]
-__device__ __forceinline__ void ldg_zrh(const float *row, int ug, int t, float2 &z, float2 &r, float2 &h) {
+// the six GRU-A input values of a lane for one unit group: p points at the lane's 32-byte sector
+// [z0 z1 r0 r1 h0 h1 - -] of a row in gru_a_col_index sector order (engine.h)
+__device__ __forceinline__ void ldg_zrh(const float *p, float2 &z, float2 &r, float2 &h) {
+  const float4 zr = __ldg(reinterpret_cast<const float4 *>(p));
+  h = ldg2(p + 4);
+  z = make_float2(zr.x, zr.y);
+  r = make_float2(zr.z, zr.w);
+}
+// the same from a row in compact order: one 16-byte piece [z0 z1 r0 r1] and one 8-byte piece [h0 h1]
+__device__ __forceinline__ void ldg_zrh_compact(const float *row, int ug, int t, float2 &z, float2 &r, float2 &h) {
   const float4 zr = __ldg(reinterpret_cast<const float4 *>(row + ug * 16 + t * 4));
   h = ldg2(row + 2 * kN + ug * 8 + 2 * t);
   z = make_float2(zr.x, zr.y);
@@ -316,13 +323,13 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
       if (TST) { s_tst[tid] = t_x; s_tst[kThreads + tid] = t_lpc; s_tst[2 * kThreads + tid] = t_pred; }
       __syncthreads();
 
-      const float *condA_f = A.cond_a + (size_t)f * B * kRowsA;
+      const float *condA_f = A.cond_a + (size_t)f * B * kRowsAP;
       float2 cond_reg[3][3];
       if (CREG) {
         const int gs = min(stream0 + g, B - 1);
 #pragma unroll
         for (int u = 0; u < 3; u++)
-          ldg_zrh(condA_f + (size_t)gs * kRowsA, warp + u * kWarps, t, cond_reg[u][0], cond_reg[u][1], cond_reg[u][2]);
+          ldg_zrh(condA_f + (size_t)gs * kRowsAP + ((warp + u * kWarps) * 4 + t) * 8, cond_reg[u][0], cond_reg[u][1], cond_reg[u][2]);
       }
 
       LPCB_MARK(0);   // frame prologue and everything outside the step loop
@@ -331,11 +338,24 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
         uint32_t *xa_new = s_xa + (cur ^ 1) * NS * kXaStride;
         // ================= phase A: GRU-A =================
         // per-stream indices of this step (the same for the three unit groups of the warp)
+        // rp: row pointers (this lane's sector of unit group `warp`) of the three embedding rows, held for the
+        // step when there are registers for them; a unit group further on is an immediate offset
+        constexpr bool PH = !gru_a_compact_order(NS);
+        const int lane_off = (warp * 4 + t) * 8;
         uint32_t ixw[MT][NV / 2];
+        const float *rp[PH ? MT : 1][PH ? NV / 2 : 1][3];
 #pragma unroll
         for (int mt = 0; mt < MT; mt++)
 #pragma unroll
-          for (int h = 0; h < NV / 2; h++) ixw[mt][h] = s_ix[mt * VR + g + 8 * h];
+          for (int h = 0; h < NV / 2; h++) {
+            const uint32_t w = s_ix[mt * VR + g + 8 * h];
+            ixw[mt][h] = w;
+            if (PH) {
+              rp[mt][h][0] = M.e_sig + (w & 0xffu) * kRowsAP + lane_off;
+              rp[mt][h][1] = M.e_pred + ((w >> 8) & 0xffu) * kRowsAP + lane_off;
+              rp[mt][h][2] = M.e_exc + ((w >> 16) & 0xffu) * kRowsAP + lane_off;
+            }
+          }
 #pragma unroll
         for (int u = 0; u < 3; u++) {
           const int ug = warp + u * kWarps;
@@ -349,11 +369,18 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             for (int h = 0; h < NV / 2; h++) {
               const int gs = min(stream0 + sA + 8 * h, B - 1);
               if (CREG) { cv[0][h] = cond_reg[u][0]; cv[1][h] = cond_reg[u][1]; cv[2][h] = cond_reg[u][2]; }
-              else ldg_zrh(condA_f + (size_t)gs * kRowsA, ug, t, cv[0][h], cv[1][h], cv[2][h]);
-              const uint32_t w = ixw[mt][h];
-              ldg_zrh(M.e_sig + (w & 0xffu) * kRowsA, ug, t, e1[0][h], e1[1][h], e1[2][h]);
-              ldg_zrh(M.e_pred + ((w >> 8) & 0xffu) * kRowsA, ug, t, e2[0][h], e2[1][h], e2[2][h]);
-              ldg_zrh(M.e_exc + ((w >> 16) & 0xffu) * kRowsA, ug, t, e3[0][h], e3[1][h], e3[2][h]);
+              else if (PH) ldg_zrh(condA_f + (size_t)gs * kRowsAP + lane_off + u * (kWarps * 32), cv[0][h], cv[1][h], cv[2][h]);
+              else ldg_zrh_compact(condA_f + (size_t)gs * kRowsAP, ug, t, cv[0][h], cv[1][h], cv[2][h]);
+              if (PH) {
+                ldg_zrh(rp[mt][h][0] + u * (kWarps * 32), e1[0][h], e1[1][h], e1[2][h]);
+                ldg_zrh(rp[mt][h][1] + u * (kWarps * 32), e2[0][h], e2[1][h], e2[2][h]);
+                ldg_zrh(rp[mt][h][2] + u * (kWarps * 32), e3[0][h], e3[1][h], e3[2][h]);
+              } else {
+                const uint32_t w = ixw[mt][h];
+                ldg_zrh_compact(M.e_sig_c + (w & 0xffu) * kRowsAP, ug, t, e1[0][h], e1[1][h], e1[2][h]);
+                ldg_zrh_compact(M.e_pred_c + ((w >> 8) & 0xffu) * kRowsAP, ug, t, e2[0][h], e2[1][h], e2[2][h]);
+                ldg_zrh_compact(M.e_exc_c + ((w >> 16) & 0xffu) * kRowsAP, ug, t, e3[0][h], e3[1][h], e3[2][h]);
+              }
             }
             // (2) sparse_sgemv_accum8x4 (src/vec_avx.h:790-858) on tensor cores.  The int32 sum is exact in
             //     any order, so the rne(16256*t) seed of the AVX2 kernel is added afterwards.
