@@ -34,7 +34,7 @@ struct SmemLayout {
   unsigned wA, posA, offF, csA, wBi, posBi, csBi, wBr, posBr, csBr;
   unsigned sdA, subB, rcp, u2l, logit;
   unsigned xa, xb, bst, condb, part;
-  unsigned usig, upred, lexc, deemph, rng, act, ix, tst;
+  unsigned usig, upred, lexc, deemph, rng, act, ix, tst, accx;
   unsigned fcw, fcb;   // dual_fc weights (node stride kFcStride floats) and bias|factor, when resident
   unsigned total;
 };
@@ -60,6 +60,7 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
   L.usig = take(NS * 4); L.upred = take(NS * 4); L.lexc = take(NS * 4);
   L.deemph = take(NS * 4); L.rng = take(4 * NS * 4); L.act = take(NS * 4); L.ix = take(NS * 4);
   L.tst = NS >= 32 ? take(3 * kThreads * 4) : 0;
+  L.accx = NS == 8 ? take(12 * 3 * 32 * 8) : 0;   // GRU-A sums computed ahead for the sampler warps' unit groups
   L.fcb = take(4 * 256 * 4);
   L.fcw = fc_resident(NS) ? take(256 * kFcStride * 4) : 0;
   L.total = o;
@@ -139,6 +140,10 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   // 32 streams per CTA: phase A has no registers to spare, so the three phase-T values each thread carries
   // from step to step wait in shared memory while phase A runs (measured +2 %; -2 % for the smaller tiles)
   constexpr bool TST = NS >= 32;
+  // 8 streams per CTA: while four warps run phase T of step i, the other twelve already form the recurrent GRU-A
+  // sums of step i+1 (they need only the state of step i): their own three unit groups into registers and one
+  // of the sampler warps' twelve into shared memory.  Phase A of step i+1 then starts at the gates.
+  constexpr bool OVL = (MT == 1 && VR == 8);
   extern __shared__ __align__(16) unsigned char smem[];
   const DevModel &M = A.m;
   const SmemLayout L = make_layout(NS, MT, M.a_rec.n_chunks, M.b_in.n_chunks, M.b_rec.n_chunks);
@@ -171,7 +176,8 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   uint32_t *s_rng = reinterpret_cast<uint32_t *>(smem + L.rng);
   int *s_act = reinterpret_cast<int *>(smem + L.act);
   uint32_t *s_ix = reinterpret_cast<uint32_t *>(smem + L.ix);
-  float *s_tst = reinterpret_cast<float *>(smem + L.tst);   // u_sig | u_pred << 8 | last_exc << 16 | active << 24
+  float *s_tst = reinterpret_cast<float *>(smem + L.tst);
+  int2 *s_accx = reinterpret_cast<int2 *>(smem + L.accx);   // [job of a sampler warp: u*4 + warp][gate][lane]   // u_sig | u_pred << 8 | last_exc << 16 | active << 24
   // dual_fc weights: resident copy (padded node stride) or the blob array in global memory; bias|factor resident
   const float *fc_w = FCS ? reinterpret_cast<const float *>(smem + L.fcw) : M.fc_w;
   const int fc_stride = FCS ? kFcStride : 32;
@@ -181,6 +187,49 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   const int g = lane >> 2, t = lane & 3;
   const int B = A.n_streams;
   const int row_len = A.total_frames * A.spf;
+
+  // sparse_sgemv_accum8x4 (src/vec_avx.h:790-858) of unit group ug for the M tile at xrow0 on tensor cores: the
+  // three gates' int32 sums without their seeds (the sum is exact in any order; the rne(16256*t) seed of the AVX2
+  // kernel is added afterwards).
+  auto gru_a_product = [&](int ug, const uint32_t *xrow0, int32_t (&acc)[3][4]) {
+#pragma unroll
+    for (int gate = 0; gate < 3; gate++) acc[gate][0] = acc[gate][1] = acc[gate][2] = acc[gate][3] = 0;
+    const unsigned char *xrowb = reinterpret_cast<const unsigned char *>(xrow0 + g * kXaStride);
+    auto chunk = [&](int32_t (&d)[4], uint32_t lo, uint32_t hi, uint2 bw) {
+      const uint32_t a0 = *reinterpret_cast<const uint32_t *>(xrowb + lo);
+      const uint32_t a2 = *reinterpret_cast<const uint32_t *>(xrowb + hi);
+      uint32_t a1 = 0, a3 = 0;
+      if (VR == 16) {
+        a1 = *reinterpret_cast<const uint32_t *>(xrowb + 8 * kXaStride * 4 + lo);
+        a3 = *reinterpret_cast<const uint32_t *>(xrowb + 8 * kXaStride * 4 + hi);
+      }
+      mma_u8s8(d, a0, a1, a2, a3, bw.x, bw.y);
+    };
+    if (FIX) {
+      // fixed slots of this unit group: 1 chunk for z, 1 for r, 3 for h -- fully unrolled
+      constexpr int ST = 5;
+      const uint2 *wq = reinterpret_cast<const uint2 *>(s_wA) + ug * ST * 32 + lane;
+      const uint4 o4 = *reinterpret_cast<const uint4 *>(s_offF + (ug * 4 + t) * 8);
+      const uint32_t pk[ST] = {o4.x, o4.y, o4.z, o4.w, s_offF[(ug * 4 + t) * 8 + 4]};
+      uint2 bw[ST];
+#pragma unroll
+      for (int sl = 0; sl < ST; sl++) bw[sl] = wq[sl * 32];
+#pragma unroll
+      for (int sl = 0; sl < ST; sl++) chunk(acc[sl < 2 ? sl : 2], pk[sl] & 0xffffu, pk[sl] >> 16, bw[sl]);
+    }
+    // overflow chunks (all chunks when the model does not fit the fixed slots); bits 30-31 of the
+    // offset word name the gate
+    const int c0 = s_csA[ug], c1 = s_csA[ug + 1];
+#pragma unroll 1
+    for (int c = c0; c < c1; c++) {   // rarely more than one trip: keep the code small (instruction cache)
+      const uint32_t pk = s_offA[c * 4 + t];
+      const uint2 bw = reinterpret_cast<const uint2 *>(s_wA)[c * 32 + lane];
+      const uint32_t lo = pk & 0xffffu, hi = (pk >> 16) & 0x3fffu, gate = pk >> 30;
+      if (gate == 0) chunk(acc[0], lo, hi, bw);
+      else if (gate == 1) chunk(acc[1], lo, hi, bw);
+      else chunk(acc[2], lo, hi, bw);
+    }
+  };
 
   // ---- one-time: weights, index lists and tables into shared memory ----
   {
@@ -252,11 +301,28 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
     }
     // Phase T state of the 16-lane group that owns stream `grp` of the tile (NS <= 32 groups): lane j holds
     // last_sig[j] (j = 0 newest) and lpc[j]; the LPC prediction is known to all 16 lanes.
-    const int l16 = tid & 15, grp = tid >> 4;
+    // Sampler warps: the first NS/2 warps (one per SM sub-partition when there are four; putting the four on one
+    // sub-partition, away from the product warps of OVL, measured 3 % slower).
+    const int tw = 2 * warp < NS ? warp : -1;
+    const bool twarp = tw >= 0;                             // both 16-lane halves own a stream (NS is even)
+    const int l16 = tid & 15, grp = twarp ? 2 * tw + (lane >> 4) : NS;
     const unsigned gbase = lane & 16;
-    const bool twarp = 2 * warp < NS;                       // both 16-lane halves own a stream (NS is even)
     const int tgs = min(stream0 + min(grp, NS - 1), B - 1);
     float t_x = A.st.last_sig[(size_t)tgs * 16 + l16], t_lpc = 0.f, t_pred = 0.f;
+    int32_t accp[OVL ? 3 : 1][3][2];
+    auto product_ahead = [&](const uint32_t *xa_buf) {   // the twelve non-sampler warps (OVL)
+      int32_t acc[3][4];
+#pragma unroll
+      for (int u = 0; u < 3; u++) {
+        gru_a_product(warp + u * kWarps, xa_buf, acc);
+#pragma unroll
+        for (int gate = 0; gate < 3; gate++) { accp[OVL ? u : 0][gate][0] = acc[gate][0]; accp[OVL ? u : 0][gate][1] = acc[gate][1]; }
+      }
+      const int e = warp - 4;                              // 0..11: job e / 4 of sampler warp e % 4
+      gru_a_product((e & 3) + kWarps * (e >> 2), xa_buf, acc);
+#pragma unroll
+      for (int gate = 0; gate < 3; gate++) s_accx[(e * 3 + gate) * 32 + lane] = make_int2(acc[gate][0], acc[gate][1]);
+    };
     for (int s = tid; s < NS; s += kThreads) {
       const int gs = min(stream0 + s, B - 1);
       s_deemph[s] = A.st.deemph[gs];
@@ -265,6 +331,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
       for (int k = 0; k < 4; k++) s_rng[k * NS + s] = A.st.rng[(size_t)gs * 4 + k];
     }
     __syncthreads();
+    if (OVL && !twarp) product_ahead(s_xa + cur * NS * kXaStride);   // sums for the tile's first step
 
     for (int f = 0; f < A.n_frames; f++) {
       // ---- frame prologue: LPC, GRU-B conditioning, active flags ----
@@ -382,46 +449,18 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
                 ldg_zrh_compact(M.e_exc_c + ((w >> 16) & 0xffu) * kRowsAP, ug, t, e3[0][h], e3[1][h], e3[2][h]);
               }
             }
-            // (2) sparse_sgemv_accum8x4 (src/vec_avx.h:790-858) on tensor cores.  The int32 sum is exact in
-            //     any order, so the rne(16256*t) seed of the AVX2 kernel is added afterwards.
+            // (2) the recurrent product: formed here, or already at hand from the previous step's phase T
             int32_t acc[3][4];
+            if (!OVL) {
+              gru_a_product(ug, xa_cur + mt * VR * kXaStride, acc);
+            } else if (!twarp) {
 #pragma unroll
-            for (int gate = 0; gate < 3; gate++) acc[gate][0] = acc[gate][1] = acc[gate][2] = acc[gate][3] = 0;
-            const unsigned char *xrowb = reinterpret_cast<const unsigned char *>(xa_cur + sA * kXaStride);
-            auto chunk = [&](int32_t (&d)[4], uint32_t lo, uint32_t hi, uint2 bw) {
-              const uint32_t a0 = *reinterpret_cast<const uint32_t *>(xrowb + lo);
-              const uint32_t a2 = *reinterpret_cast<const uint32_t *>(xrowb + hi);
-              uint32_t a1 = 0, a3 = 0;
-              if (VR == 16) {
-                a1 = *reinterpret_cast<const uint32_t *>(xrowb + 8 * kXaStride * 4 + lo);
-                a3 = *reinterpret_cast<const uint32_t *>(xrowb + 8 * kXaStride * 4 + hi);
-              }
-              mma_u8s8(d, a0, a1, a2, a3, bw.x, bw.y);
-            };
-            if (FIX) {
-              // fixed slots of this unit group: 1 chunk for z, 1 for r, 3 for h -- fully unrolled
-              constexpr int ST = 5;
-              const uint2 *wq = reinterpret_cast<const uint2 *>(s_wA) + ug * ST * 32 + lane;
-              const uint4 o4 = *reinterpret_cast<const uint4 *>(s_offF + (ug * 4 + t) * 8);
-              const uint32_t pk[ST] = {o4.x, o4.y, o4.z, o4.w, s_offF[(ug * 4 + t) * 8 + 4]};
-              uint2 bw[ST];
+              for (int gate = 0; gate < 3; gate++) { acc[gate][0] = accp[u][gate][0]; acc[gate][1] = accp[u][gate][1]; acc[gate][2] = acc[gate][3] = 0; }
+            } else {
 #pragma unroll
-              for (int sl = 0; sl < ST; sl++) bw[sl] = wq[sl * 32];
-#pragma unroll
-              for (int sl = 0; sl < ST; sl++) chunk(acc[sl < 2 ? sl : 2], pk[sl] & 0xffffu, pk[sl] >> 16, bw[sl]);
-            }
-            // overflow chunks (all chunks when the model does not fit the fixed slots); bits 30-31 of the
-            // offset word name the gate
-            {
-              const int c0 = s_csA[ug], c1 = s_csA[ug + 1];
-#pragma unroll 1
-              for (int c = c0; c < c1; c++) {   // rarely more than one trip: keep the code small (instruction cache)
-                const uint32_t pk = s_offA[c * 4 + t];
-                const uint2 bw = reinterpret_cast<const uint2 *>(s_wA)[c * 32 + lane];
-                const uint32_t lo = pk & 0xffffu, hi = (pk >> 16) & 0x3fffu, gate = pk >> 30;
-                if (gate == 0) chunk(acc[0], lo, hi, bw);
-                else if (gate == 1) chunk(acc[1], lo, hi, bw);
-                else chunk(acc[2], lo, hi, bw);
+              for (int gate = 0; gate < 3; gate++) {
+                const int2 v = s_accx[((u * 4 + tw) * 3 + gate) * 32 + lane];
+                acc[gate][0] = v.x; acc[gate][1] = v.y; acc[gate][2] = acc[gate][3] = 0;
               }
             }
             // (3) seeds and gates: compute_sparse_gru (src/nnet.c:431-447), two units per packed operation
@@ -667,6 +706,8 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               if (step + 1 < A.spf) predict();
               if (TST) { s_tst[tid] = t_x; s_tst[2 * kThreads + tid] = t_pred; }
             }
+          } else if (OVL) {
+            product_ahead(xa_new);   // the next step's recurrent sums, while warps 0-3 sample
           }
         }
         LPCB_MARK(8);   // signal update
