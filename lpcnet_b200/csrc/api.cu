@@ -69,7 +69,6 @@ struct LPCNetBatch {
   int n_sms = 0;
   int tile = 0;  // 0 = auto
   int max_tile = 32;
-  bool st_cond_compact = false;   // column order of st.cond_a (that of the last frame-network run)
   Model model;
   DevState st{};
   void *st_alloc = nullptr;
@@ -151,9 +150,10 @@ int ensure_frame_buffers(LPCNetBatch *b, int F) {
 int auto_tile(const LPCNetBatch *b) {
   if (b->tile) return b->tile;
   const int B = b->n_streams, sms = b->n_sms;
-  int t = 32;   // 32 streams per CTA is the throughput optimum (measured); smaller batches spread over all SMs
+  // 16 streams per CTA is the throughput optimum (2.97e8 samples/s at 2368+ streams against 2.91e8 for 32 and
+  // 2.45e8 for 8, measured); batches that fit one 8-stream tile per SM get the lowest step latency from 8
+  int t = 16;
   if (B <= 8 * sms) t = 8;
-  else if (B <= 16 * sms) t = 16;
   return t < b->max_tile ? t : b->max_tile;
 }
 
@@ -162,8 +162,6 @@ int run_frames(LPCNetBatch *b, const float *d_features, int stride, int f0, int 
   FrameArgs fa{};
   fa.m = b->model.d; fa.st = b->st; fa.fb = b->fb; fa.n_streams = b->n_streams; fa.n_frames = F;
   fa.features = d_features; fa.feature_stride = stride; fa.frame0 = f0; fa.total_frames = total_frames;
-  fa.cond_compact = gru_a_compact_order(auto_tile(b));
-  b->st_cond_compact = fa.cond_compact != 0;
   int nl = 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (b->profiling) { CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventRecord(e0, b->stream)); }
@@ -496,7 +494,7 @@ int lpcnet_batch_frame_network(LPCNetBatch *b, const float *features, int stride
         for (size_t s = 0; s < (size_t)B; s++) {
           const float *src = tmp.data() + ((size_t)f * B + s) * kRowsAP;
           float *row = ga + (s * n_frames + f0 + f) * kRowsA;
-          for (int col = 0; col < kRowsA; col++) row[col] = src[gru_a_col_index(col, b->st_cond_compact)];
+          for (int col = 0; col < kRowsA; col++) row[col] = src[gru_a_col_index(col)];
         }
     }
   }
@@ -547,7 +545,7 @@ int lpcnet_batch_get_state(LPCNetBatch *b, int s, LPCNetB200StreamState *o) {
   {
     float tmp[kRowsAP];
     CK(cudaMemcpy(tmp, S.cond_a + (size_t)s * kRowsAP, kRowsAP * 4, cudaMemcpyDeviceToHost));
-    for (int col = 0; col < kRowsA; col++) o->gru_a_condition[col] = tmp[gru_a_col_index(col, b->st_cond_compact)];
+    for (int col = 0; col < kRowsA; col++) o->gru_a_condition[col] = tmp[gru_a_col_index(col)];
   }
   CK(cudaMemcpy(o->gru_b_condition, S.cond_b + (size_t)s * kRowsB, kRowsB * 4, cudaMemcpyDeviceToHost));
   CK(cudaMemcpy(&o->deemph_mem, S.deemph + s, 4, cudaMemcpyDeviceToHost));
@@ -577,8 +575,7 @@ int lpcnet_batch_set_state(LPCNetBatch *b, int s, const LPCNetB200StreamState *i
   CK(cudaMemcpy(S.old_lpc + (size_t)s * kMaxDelay * 16, in->old_lpc, (size_t)b->model.d.features_delay * 64, cudaMemcpyHostToDevice));
   {
     float tmp[kRowsAP] = {0.f};
-    b->st_cond_compact = gru_a_compact_order(auto_tile(b));
-    for (int col = 0; col < kRowsA; col++) tmp[gru_a_col_index(col, b->st_cond_compact)] = in->gru_a_condition[col];
+    for (int col = 0; col < kRowsA; col++) tmp[gru_a_col_index(col)] = in->gru_a_condition[col];
     CK(cudaMemcpy(S.cond_a + (size_t)s * kRowsAP, tmp, kRowsAP * 4, cudaMemcpyHostToDevice));
   }
   CK(cudaMemcpy(S.cond_b + (size_t)s * kRowsB, in->gru_b_condition, kRowsB * 4, cudaMemcpyHostToDevice));

@@ -33,20 +33,16 @@ constexpr int kXbStride = kNB / 4;       // 4: eight streams x four words = 32 d
 constexpr int kPartsB = 2;
 constexpr int kPadB = 6;
 
-// Column order of the GRU-A input rows (embedding tables, frame conditioning) in device memory; rows are
-// kRowsAP floats apart in both orders.  col = gate*384 + unit  ->  storage index.
-//  * sector order (kernels with 8 or 16 streams per CTA, instruction/latency bound): the six values lane t of
-//    a quad needs for unit group ug share one 32-byte sector, [ug][t][z0 z1 r0 r1 h0 h1 - -], so one row
-//    pointer per table, held in registers for the step, and two loads at immediate offsets fetch them;
-//  * compact order (32 streams per CTA, bound by the L1 tag/data stages): [ug][t][z0 z1 r0 r1] then the
-//    candidate gate in natural order -- 3 sectors per (row, unit group) instead of 4 half-used ones.
+// Column order of the GRU-A input rows (embedding tables, frame conditioning) in device memory: the six
+// values lane t of a quad needs for unit group ug share one 32-byte sector, [ug][t][z0 z1 r0 r1 h0 h1 - -]:
+// one 256-bit load per lane fetches them, a warp request covers exactly one 128-byte line per stream, and a
+// row pointer per table serves all unit groups at immediate offsets.  Rows are kRowsAP floats.
+// col = gate*384 + unit  ->  storage index.
 constexpr int kRowsAP = kN / 8 * 32;   // 1536
-__host__ __device__ inline int gru_a_col_index(int col, bool compact) {
+__host__ __device__ inline int gru_a_col_index(int col) {
   const int gate = col / kN, unit = col % kN;
-  if (compact) return gate == 2 ? col : (unit >> 3) * 16 + ((unit & 7) >> 1) * 4 + gate * 2 + (unit & 1);
   return ((unit >> 3) * 4 + ((unit & 7) >> 1)) * 8 + gate * 2 + (unit & 1);
 }
-__host__ __device__ constexpr bool gru_a_compact_order(int tile_streams) { return tile_streams >= 32; }
 
 // Block-sparse int8 matrix re-tiled for mma.sync.m16n8k32 B fragments.
 // A "chunk" is 8 blocks (K = 32) of one 8-row group; its 64 weight words are stored [lane][2] so that a
@@ -88,8 +84,7 @@ struct DevModel {
   const float *a_feat_w, *a_feat_b;         // [128][1152], [1152]
   const float *b_feat_w, *b_feat_b;         // [128][48], [48]
   // 16 kHz sample network
-  const float *e_sig, *e_pred, *e_exc;      // [256][kRowsAP], columns in gru_a_col_index sector order
-  const float *e_sig_c, *e_pred_c, *e_exc_c;   // the same tables in compact order
+  const float *e_sig, *e_pred, *e_exc;      // [256][kRowsAP], columns in gru_a_col_index order
   const float *a_subias_rec;                // [1152] = &sparse_gru_a_subias[3N]
   const float *a_diag;                      // [1152]
   DevSparse a_rec;                          // 1152 x 384 block-sparse
@@ -185,7 +180,6 @@ struct FrameArgs {
   DevState st;
   FrameBuffers fb;
   int n_streams, n_frames;
-  int cond_compact;          // column order of the cond_a rows to write (gru_a_col_index)
   const float *features;     // device [B][total_frames][stride]
   int feature_stride;
   int frame0, total_frames;

@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(kFT) cond_kernel(FrameArgs A) {
       if (blockIdx.x * R + r >= total) break;
       float *dst = isA ? A.fb.cond_a + ((size_t)row_f[r] * B + row_s[r]) * kRowsAP
                        : A.fb.cond_b + ((size_t)row_f[r] * B + row_s[r]) * kRowsB;
-      dst[isA ? gru_a_col_index(col, A.cond_compact != 0) : col] = acc[r];   // GRU-A conditioning in the sample kernel's gather order
+      dst[isA ? gru_a_col_index(col) : col] = acc[r];   // GRU-A conditioning in the sample kernel's gather order
     }
   }
 }

@@ -270,19 +270,19 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
   DevModel &d = m.d;
   bool ok = true;
   // embedding rows are stored in the column order the sample kernel's 16-byte gathers want
-  auto put_embed = [&](const float **dst, const char *name, bool compact) -> bool {
+  auto put_embed = [&](const float **dst, const char *name) -> bool {
     const unsigned char *p = need(name, 256 * kRowsA * 4);
     if (!p) return false;
     std::vector<float> t((size_t)256 * kRowsAP, 0.f);
     for (int v = 0; v < 256; v++)
       for (int col = 0; col < kRowsA; col++)
-        memcpy(&t[(size_t)v * kRowsAP + gru_a_col_index(col, compact)], p + ((size_t)v * kRowsA + col) * 4, 4);
+        memcpy(&t[(size_t)v * kRowsAP + gru_a_col_index(col)], p + ((size_t)v * kRowsA + col) * 4, 4);
     put(reinterpret_cast<const void **>(dst), t.data(), t.size() * 4);
     return true;
   };
-  ok &= put_embed(&d.e_sig, "gru_a_embed_sig_weights", false) && put_embed(&d.e_sig_c, "gru_a_embed_sig_weights", true);
-  ok &= put_embed(&d.e_pred, "gru_a_embed_pred_weights", false) && put_embed(&d.e_pred_c, "gru_a_embed_pred_weights", true);
-  ok &= put_embed(&d.e_exc, "gru_a_embed_exc_weights", false) && put_embed(&d.e_exc_c, "gru_a_embed_exc_weights", true);
+  ok &= put_embed(&d.e_sig, "gru_a_embed_sig_weights");
+  ok &= put_embed(&d.e_pred, "gru_a_embed_pred_weights");
+  ok &= put_embed(&d.e_exc, "gru_a_embed_exc_weights");
   ok &= put_f(&d.a_feat_b, "gru_a_dense_feature_bias", kRowsA);
   ok &= put_f(&d.a_feat_w, "gru_a_dense_feature_weights", kC * kRowsA);
   ok &= put_f(&d.b_feat_b, "gru_b_dense_feature_bias", kRowsB);

@@ -72,19 +72,12 @@ __device__ __forceinline__ float2 ldg2(const float *p) { return __ldg(reinterpre
 // the six GRU-A input values of a lane for one unit group: p points at the lane's 32-byte sector
 // [z0 z1 r0 r1 h0 h1 - -] of a row in gru_a_col_index sector order (engine.h)
 __device__ __forceinline__ void ldg_zrh(const float *p, float2 &z, float2 &r, float2 &h) {
-  const float4 zr = __ldg(reinterpret_cast<const float4 *>(p));
-  h = ldg2(p + 4);
-  z = make_float2(zr.x, zr.y);
-  r = make_float2(zr.z, zr.w);
+  // one 256-bit load (sm_100: LDG.E.256): a warp request then covers exactly one 128-byte line per stream,
+  // 8 L1 wavefronts for all six values instead of 8 + 8 with a 16-byte and an 8-byte load
+  float pad0, pad1;
+  asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=f"(z.x), "=f"(z.y), "=f"(r.x), "=f"(r.y), "=f"(h.x), "=f"(h.y), "=f"(pad0), "=f"(pad1) : "l"(p));
 }
-// the same from a row in compact order: one 16-byte piece [z0 z1 r0 r1] and one 8-byte piece [h0 h1]
-__device__ __forceinline__ void ldg_zrh_compact(const float *row, int ug, int t, float2 &z, float2 &r, float2 &h) {
-  const float4 zr = __ldg(reinterpret_cast<const float4 *>(row + ug * 16 + t * 4));
-  h = ldg2(row + 2 * kN + ug * 8 + 2 * t);
-  z = make_float2(zr.x, zr.y);
-  r = make_float2(zr.z, zr.w);
-}
-
 template <bool ARITH> struct RcpSel {
   typedef const uint32_t *type;
   static __device__ __forceinline__ type make(const uint32_t *tab) { return tab; }
@@ -407,7 +400,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
         // per-stream indices of this step (the same for the three unit groups of the warp)
         // rp: row pointers (this lane's sector of unit group `warp`) of the three embedding rows, held for the
         // step when there are registers for them; a unit group further on is an immediate offset
-        constexpr bool PH = !gru_a_compact_order(NS);
+        constexpr bool PH = MT * (NV / 2) <= 2;
         const int lane_off = (warp * 4 + t) * 8;
         uint32_t ixw[MT][NV / 2];
         const float *rp[PH ? MT : 1][PH ? NV / 2 : 1][3];
@@ -436,17 +429,17 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             for (int h = 0; h < NV / 2; h++) {
               const int gs = min(stream0 + sA + 8 * h, B - 1);
               if (CREG) { cv[0][h] = cond_reg[u][0]; cv[1][h] = cond_reg[u][1]; cv[2][h] = cond_reg[u][2]; }
-              else if (PH) ldg_zrh(condA_f + (size_t)gs * kRowsAP + lane_off + u * (kWarps * 32), cv[0][h], cv[1][h], cv[2][h]);
-              else ldg_zrh_compact(condA_f + (size_t)gs * kRowsAP, ug, t, cv[0][h], cv[1][h], cv[2][h]);
+              else ldg_zrh(condA_f + (size_t)gs * kRowsAP + lane_off + u * (kWarps * 32), cv[0][h], cv[1][h], cv[2][h]);
               if (PH) {
                 ldg_zrh(rp[mt][h][0] + u * (kWarps * 32), e1[0][h], e1[1][h], e1[2][h]);
                 ldg_zrh(rp[mt][h][1] + u * (kWarps * 32), e2[0][h], e2[1][h], e2[2][h]);
                 ldg_zrh(rp[mt][h][2] + u * (kWarps * 32), e3[0][h], e3[1][h], e3[2][h]);
               } else {
                 const uint32_t w = ixw[mt][h];
-                ldg_zrh_compact(M.e_sig_c + (w & 0xffu) * kRowsAP, ug, t, e1[0][h], e1[1][h], e1[2][h]);
-                ldg_zrh_compact(M.e_pred_c + ((w >> 8) & 0xffu) * kRowsAP, ug, t, e2[0][h], e2[1][h], e2[2][h]);
-                ldg_zrh_compact(M.e_exc_c + ((w >> 16) & 0xffu) * kRowsAP, ug, t, e3[0][h], e3[1][h], e3[2][h]);
+                const int off = lane_off + u * (kWarps * 32);
+                ldg_zrh(M.e_sig + (w & 0xffu) * kRowsAP + off, e1[0][h], e1[1][h], e1[2][h]);
+                ldg_zrh(M.e_pred + ((w >> 8) & 0xffu) * kRowsAP + off, e2[0][h], e2[1][h], e2[2][h]);
+                ldg_zrh(M.e_exc + ((w >> 16) & 0xffu) * kRowsAP + off, e3[0][h], e3[1][h], e3[2][h]);
               }
             }
             // (2) the recurrent product: formed here, or already at hand from the previous step's phase T
