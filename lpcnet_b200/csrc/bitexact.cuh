@@ -17,21 +17,21 @@ __device__ __forceinline__ float rcp_estimate(float x, const uint32_t *__restric
 
 // The default table without the lookup: entry i is 1/(mid-point of bucket i) rounded half-up to 12
 // mantissa bits, so MUFU.RCP of the mid-point (exponent kept) plus an integer rounding gives the same
-// bits whenever the estimate lands on the right side of the rounding boundary.  One bucket cannot: for
-// i = 1984 (k = 8065) the exact quotient 2^25/k = 4160.49994 lies 0.13 binary32 ulp below its boundary,
-// so any binary32 reciprocal sits on the tie and rounds up; it is corrected explicitly.  The closest
-// other buckets are 0.59 and 1.05 ulp away, inside MUFU.RCP's error on paper -- so model.cu compares
-// this function with the table for every bucket and exponent on the GPU at load, and the kernel
-// variants built on it are used only when all of them agree.
+// bits whenever the estimate lands on the right side of the rounding boundary.  Three buckets put the
+// binary32 reciprocal exactly ON the boundary (the exact quotient 2^25/k is 0.13 ulp below it for bucket
+// 1984, 0.13 and 0.59 ulp above it for buckets 2047 and 550), and they need different tie-breaks: down for
+// 1984, up for the other two.  Bit 1 of the bucket number (mantissa bit 13) is 0 for 1984 and 1 for 2047
+// and 550, so the rounding bias 0x3ff + that bit resolves all three; for every other bucket the two biases
+// round alike.  The next-closest buckets are 1.05 ulp from their boundary, inside MUFU.RCP's error on
+// paper -- so model.cu compares this function with the table for every bucket and exponent on the GPU at
+// load, and the kernel variants built on it are used only when all of them agree.
 struct RcpArith {};
 __device__ __forceinline__ float rcp_estimate(float x, RcpArith) {
   const uint32_t b = __float_as_uint(x);
   const float mid = __uint_as_float((b & 0xfffff000u) | 0x800u);
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(mid));
-  uint32_t q = (__float_as_uint(r) + 0x400u) & 0xfffff800u;
-  if ((b & 0x007ff000u) == (1984u << 12)) q -= 0x800u;
-  return __uint_as_float(q);
+  return __uint_as_float((__float_as_uint(r) + 0x3ffu + ((b >> 13) & 1u)) & 0xfffff800u);
 }
 
 // tanh8_approx (src/vec_avx.h:393-411)

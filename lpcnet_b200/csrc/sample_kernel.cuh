@@ -750,14 +750,12 @@ static cudaError_t launch_tile(const SampleArgs &a, int n_sms, cudaStream_t s) {
   const size_t smem = make_layout(NS, MT, a.m.a_rec.n_chunks, a.m.b_in.n_chunks, a.m.b_rec.n_chunks).total;
   const bool dbg = a.trace || a.logits;
   const bool fix = a.m.a_rec.slots[2] != 0;
-  // Arithmetic rcpps where the kernel is bound by the L1/shared-memory pipe (16+ streams per CTA: 4% faster
-  // at 32); the 8-stream kernel is issue/latency-bound and 3% faster with the table (both measured, B200).
-  // The trace/logit variants always use the table.
-  constexpr bool kArith = NS >= 16;
-  const bool ra = kArith && a.m.rcp_arith != 0;
+  // Arithmetic rcpps when it was verified against the table on this GPU (model.cu): no shared-memory lookups,
+  // 2-4 % faster at every tile size (measured).  The trace/logit variants always use the table.
+  const bool ra = a.m.rcp_arith != 0;
   void (*kern)(const SampleArgs) =
       dbg ? (fix ? sample_kernel<MT, VR, true, true, false> : sample_kernel<MT, VR, true, false, false>)
-      : ra ? (fix ? sample_kernel<MT, VR, false, true, kArith> : sample_kernel<MT, VR, false, false, kArith>)
+      : ra ? (fix ? sample_kernel<MT, VR, false, true, true> : sample_kernel<MT, VR, false, false, true>)
            : (fix ? sample_kernel<MT, VR, false, true, false> : sample_kernel<MT, VR, false, false, false>);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;

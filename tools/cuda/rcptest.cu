@@ -21,15 +21,19 @@ __global__ void k(int *cnt, int *ex) {
     if (b != want) atomicAdd(&cnt[1], 1);
     if (c != want) atomicAdd(&cnt[2], 1);
     if (__float_as_uint(lpcb::rcp_estimate(mid, lpcb::RcpArith{})) != want) atomicAdd(&cnt[5], 1);
+    if (((__float_as_uint(r0) + 0x3ffu) & 0xfffff800u) != want) { int n = atomicAdd(&cnt[6], 1); if (n < 4) { ex[24 + 2 * n] = i; ex[25 + 2 * n] = e; } }
     if (e == 127 && a != want) atomicAdd(&cnt[3], 1);
     if (e == 127 && b != want) atomicAdd(&cnt[4], 1);
   }
 }
 int main() {
-  int *cnt, *ex; cudaMallocManaged(&cnt, 64); cudaMallocManaged(&ex, 4 * 24);
+  int *cnt, *ex; cudaMallocManaged(&cnt, 64); cudaMallocManaged(&ex, 4 * 40);
   for (int i = 0; i < 16; i++) cnt[i] = 0;
   k<<<8, 256>>>(cnt, ex); cudaDeviceSynchronize();
   printf("mismatches of 2048*239: mufu %d  newton %d  frcp_rn %d ; at e=127: mufu %d newton %d ; library form %d\n", cnt[0], cnt[1], cnt[2], cnt[3], cnt[4], cnt[5]);
+  printf("bias 0x3ff without special case: %d mismatches", cnt[6]);
+  for (int n = 0; n < 4 && n < cnt[6]; n++) printf("  (bucket %d e %d)", ex[24 + 2 * n], ex[25 + 2 * n]);
+  printf("\n");
   for (int n = 0; n < 8 && n < cnt[0]; n++) printf("  bucket %d e %d  mufu-rn ulps %d\n", ex[3 * n], ex[3 * n + 1], ex[3 * n + 2]);
   return 0;
 }
