@@ -49,26 +49,32 @@ __global__ void frame_inputs_kernel(FrameArgs A) {
 }
 
 // out[r][i] = act(bias[i] + sum_j W[j*N+i] * x[r][j]), j ascending, fmaf: sgemv_accum16 order.
-template <int R>
+// The R input rows are interleaved in shared memory, xt[j][r], so one weight load meets the R activations
+// of its input with two 16-byte broadcast loads (R = 8).  OUT_T: write the result interleaved too (it feeds
+// the next layer), else as rows with stride out_stride.
+template <int R, bool OUT_T>
 __device__ __forceinline__ void dense_rows(const float *__restrict__ W, const float *__restrict__ bias, int K, int N,
-                                           const float *x /*smem [R][K]*/, float *out /*[R][N] smem or global rows*/,
-                                           int out_stride, bool do_tanh, const uint32_t *rcp, int tid, int nthreads,
-                                           const bool *zero_row) {
+                                           const float *xt /*smem [K][R]*/, float *out, int out_stride, bool do_tanh,
+                                           const uint32_t *rcp, int tid, int nthreads, const bool *zero_row) {
+  static_assert(R == 8, "two float4 per input");
   for (int i = tid; i < N; i += nthreads) {
     float acc[R];
     const float b = __ldg(bias + i);
 #pragma unroll
     for (int r = 0; r < R; r++) acc[r] = b;
+#pragma unroll 4
     for (int j = 0; j < K; j++) {
       const float w = __ldg(W + (size_t)j * N + i);
-#pragma unroll
-      for (int r = 0; r < R; r++) acc[r] = fmaf(w, x[r * K + j], acc[r]);
+      const float4 x0 = *reinterpret_cast<const float4 *>(xt + j * R), x1 = *reinterpret_cast<const float4 *>(xt + j * R + 4);
+      acc[0] = fmaf(w, x0.x, acc[0]); acc[1] = fmaf(w, x0.y, acc[1]); acc[2] = fmaf(w, x0.z, acc[2]); acc[3] = fmaf(w, x0.w, acc[3]);
+      acc[4] = fmaf(w, x1.x, acc[4]); acc[5] = fmaf(w, x1.y, acc[5]); acc[6] = fmaf(w, x1.z, acc[6]); acc[7] = fmaf(w, x1.w, acc[7]);
     }
 #pragma unroll
     for (int r = 0; r < R; r++) {
       float v = do_tanh ? tanh_ref(acc[r], rcp) : acc[r];
       if (zero_row && zero_row[r]) v = 0.f;
-      out[(size_t)r * out_stride + i] = v;
+      if (OUT_T) out[i * R + r] = v;
+      else out[(size_t)r * out_stride + i] = v;
     }
   }
 }
@@ -76,7 +82,7 @@ __device__ __forceinline__ void dense_rows(const float *__restrict__ W, const fl
 // K1: conv1 for R rows per block.
 __global__ void __launch_bounds__(kFT) conv1_kernel(FrameArgs A) {
   constexpr int R = kRowsPerBlock;
-  __shared__ float x[R][3 * kConvIn];
+  __shared__ __align__(16) float xt[3 * kConvIn][R];
   __shared__ float y[R][kC];
   __shared__ bool zero[R];
   __shared__ uint32_t rcp[2048];
@@ -87,11 +93,11 @@ __global__ void __launch_bounds__(kFT) conv1_kernel(FrameArgs A) {
     const int row = min(blockIdx.x * R + r, total - 1);
     const int s = row / F, f = row % F;
     const float *src = A.fb.in_vec + ((size_t)s * (F + 2) + f) * kConvIn;  // rows f, f+1, f+2 are contiguous
-    for (int i = tid; i < 3 * kConvIn; i += kFT) x[r][i] = src[i];
+    for (int i = tid; i < 3 * kConvIn; i += kFT) xt[i][r] = src[i];
     if (tid == 0) zero[r] = frame_count_at(A.st.frame_count[s], f) < 1;  // FEATURE_CONV1_DELAY (src/lpcnet.c:99)
   }
   __syncthreads();
-  dense_rows<R>(A.m.conv1_w, A.m.conv1_b, 3 * kConvIn, kC, &x[0][0], &y[0][0], kC, true, rcp, tid, kFT, zero);
+  dense_rows<R, false>(A.m.conv1_w, A.m.conv1_b, 3 * kConvIn, kC, &xt[0][0], &y[0][0], kC, true, rcp, tid, kFT, zero);
   __syncthreads();
   for (int r = 0; r < R; r++) {
     const int row = blockIdx.x * R + r;
@@ -104,9 +110,9 @@ __global__ void __launch_bounds__(kFT) conv1_kernel(FrameArgs A) {
 // K2: conv2 -> dense1 -> dense2 -> gru_a/gru_b conditioning for R rows per block.
 __global__ void __launch_bounds__(kFT) cond_kernel(FrameArgs A) {
   constexpr int R = kRowsPerBlock;
-  __shared__ float x[R][3 * kC];
-  __shared__ float y[R][kC];
-  __shared__ float z[R][kC];
+  __shared__ __align__(16) float xt[3 * kC][R];
+  __shared__ __align__(16) float yt[kC][R];
+  __shared__ __align__(16) float zt[kC][R];
   __shared__ bool zero[R];
   __shared__ int row_s[R], row_f[R];
   __shared__ uint32_t rcp[2048];
@@ -117,39 +123,53 @@ __global__ void __launch_bounds__(kFT) cond_kernel(FrameArgs A) {
     const int row = min(blockIdx.x * R + r, total - 1);
     const int s = row / F, f = row % F;
     const float *src = A.fb.c1 + ((size_t)s * (F + 2) + f) * kC;
-    for (int i = tid; i < 3 * kC; i += kFT) x[r][i] = src[i];
+    for (int i = tid; i < 3 * kC; i += kFT) xt[i][r] = src[i];
     if (tid == 0) {
       zero[r] = frame_count_at(A.st.frame_count[s], f) < A.m.features_delay;  // src/lpcnet.c:101
       row_s[r] = s; row_f[r] = f;
     }
   }
   __syncthreads();
-  dense_rows<R>(A.m.conv2_w, A.m.conv2_b, 3 * kC, kC, &x[0][0], &y[0][0], kC, true, rcp, tid, kFT, zero);
+  dense_rows<R, true>(A.m.conv2_w, A.m.conv2_b, 3 * kC, kC, &xt[0][0], &yt[0][0], 0, true, rcp, tid, kFT, zero);
   __syncthreads();
-  dense_rows<R>(A.m.dense1_w, A.m.dense1_b, kC, kC, &y[0][0], &z[0][0], kC, true, rcp, tid, kFT, nullptr);
+  dense_rows<R, true>(A.m.dense1_w, A.m.dense1_b, kC, kC, &yt[0][0], &zt[0][0], 0, true, rcp, tid, kFT, nullptr);
   __syncthreads();
-  dense_rows<R>(A.m.dense2_w, A.m.dense2_b, kC, kC, &z[0][0], &y[0][0], kC, true, rcp, tid, kFT, nullptr);
+  dense_rows<R, true>(A.m.dense2_w, A.m.dense2_b, kC, kC, &zt[0][0], &yt[0][0], 0, true, rcp, tid, kFT, nullptr);
   __syncthreads();
-  // linear heads, written straight to [F][B][*]
-  for (int i = tid; i < kRowsA + kRowsB; i += kFT) {
-    const bool isA = i < kRowsA;
-    const int col = isA ? i : i - kRowsA, N = isA ? kRowsA : kRowsB;
-    const float *W = isA ? A.m.a_feat_w : A.m.b_feat_w;
-    float acc[R];
-    const float b = __ldg((isA ? A.m.a_feat_b : A.m.b_feat_b) + col);
+  // linear heads, written straight to [F][B][*]; two output columns per thread share the activation loads
+  constexpr int NH = kRowsA + kRowsB;
+  for (int i0 = tid; i0 < NH; i0 += 2 * kFT) {
+    const int i1 = i0 + kFT < NH ? i0 + kFT : i0;   // the last pass may have one column only (computed twice, stored once)
+    const float *Wc[2]; int colc[2], Nc[2]; float acc[2][R];
 #pragma unroll
-    for (int r = 0; r < R; r++) acc[r] = b;
+    for (int c = 0; c < 2; c++) {
+      const int i = c ? i1 : i0;
+      const bool isA = i < kRowsA;
+      colc[c] = isA ? i : i - kRowsA; Nc[c] = isA ? kRowsA : kRowsB;
+      Wc[c] = (isA ? A.m.a_feat_w : A.m.b_feat_w) + colc[c];
+      const float b = __ldg((isA ? A.m.a_feat_b : A.m.b_feat_b) + colc[c]);
+#pragma unroll
+      for (int r = 0; r < R; r++) acc[c][r] = b;
+    }
+#pragma unroll 4
     for (int j = 0; j < kC; j++) {
-      const float w = __ldg(W + (size_t)j * N + col);
+      const float w0 = __ldg(Wc[0] + (size_t)j * Nc[0]), w1 = __ldg(Wc[1] + (size_t)j * Nc[1]);
+      const float4 x0 = *reinterpret_cast<const float4 *>(&yt[j][0]), x1 = *reinterpret_cast<const float4 *>(&yt[j][4]);
+      const float xr[R] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
 #pragma unroll
-      for (int r = 0; r < R; r++) acc[r] = fmaf(w, y[r][j], acc[r]);
+      for (int r = 0; r < R; r++) { acc[0][r] = fmaf(w0, xr[r], acc[0][r]); acc[1][r] = fmaf(w1, xr[r], acc[1][r]); }
     }
 #pragma unroll
-    for (int r = 0; r < R; r++) {
-      if (blockIdx.x * R + r >= total) break;
-      float *dst = isA ? A.fb.cond_a + ((size_t)row_f[r] * B + row_s[r]) * kRowsAP
-                       : A.fb.cond_b + ((size_t)row_f[r] * B + row_s[r]) * kRowsB;
-      dst[isA ? gru_a_col_index(col) : col] = acc[r];   // GRU-A conditioning in the sample kernel's gather order
+    for (int c = 0; c < 2; c++) {
+      if (c == 1 && i1 == i0) break;
+      const bool isA = Nc[c] == kRowsA;
+#pragma unroll
+      for (int r = 0; r < R; r++) {
+        if (blockIdx.x * R + r >= total) break;
+        float *dst = isA ? A.fb.cond_a + ((size_t)row_f[r] * B + row_s[r]) * kRowsAP
+                         : A.fb.cond_b + ((size_t)row_f[r] * B + row_s[r]) * kRowsB;
+        dst[isA ? gru_a_col_index(colc[c]) : colc[c]] = acc[c][r];   // GRU-A conditioning in the sample kernel's gather order
+      }
     }
   }
 }
