@@ -507,7 +507,8 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
         // and the loads of a group are issued before its MMAs.
         {
           constexpr int NIN = kRGroupsB * kPartsB, JOBS = NIN + kRGroupsB;
-          constexpr int UB = MT == 1 ? 3 : (MT == 2 ? 2 : 1);
+          constexpr int UB = NS == 8 ? 6 : (MT == 1 ? 3 : (MT == 2 ? 2 : 1));   // chunks in flight
+          constexpr int NA = NS == 8 ? 3 : 1;                                   // independent accumulators
           static_assert(kPadB % UB == 0, "padding must cover the unroll factor");
           for (int job = warp; job < JOBS; job = (job >= NIN && job + 4 < JOBS) ? job + 4 : JOBS) {
             int32_t acc[MT][4];
@@ -515,6 +516,11 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             for (int mt = 0; mt < MT; mt++) acc[mt][0] = acc[mt][1] = acc[mt][2] = acc[mt][3] = 0;
             int slot;
             if (job < NIN) {
+              int32_t accn[NA][MT][4];
+#pragma unroll
+              for (int n = 0; n < NA; n++)
+#pragma unroll
+                for (int mt = 0; mt < MT; mt++) accn[n][mt][0] = accn[n][mt][1] = accn[n][mt][2] = accn[n][mt][3] = 0;
               const unsigned char *xb0 = reinterpret_cast<const unsigned char *>(xa_new + g * kXaStride);
               const int hi = s_csBi[job + 1];
               for (int c = s_csBi[job]; c < hi; c += UB) {
@@ -542,8 +548,14 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
 #pragma unroll
                 for (int k = 0; k < UB; k++)
 #pragma unroll
-                  for (int mt = 0; mt < MT; mt++) mma_u8s8(acc[mt], a[k][mt][0], a[k][mt][1], a[k][mt][2], a[k][mt][3], bw[k].x, bw[k].y);
+                  for (int mt = 0; mt < MT; mt++) mma_u8s8(accn[k % NA][mt], a[k][mt][0], a[k][mt][1], a[k][mt][2], a[k][mt][3], bw[k].x, bw[k].y);
               }
+#pragma unroll
+              for (int n = 0; n < NA; n++)
+#pragma unroll
+                for (int mt = 0; mt < MT; mt++)
+#pragma unroll
+                  for (int q = 0; q < 4; q++) acc[mt][q] += accn[n][mt][q];
               // s_part index: [mt][kind][rg] with job = rg * kPartsB + kind
               slot = (job % kPartsB) * kRGroupsB + job / kPartsB;
             } else {
@@ -586,6 +598,16 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             if (TST) { t_x = s_tst[tid]; t_lpc = s_tst[kThreads + tid]; t_pred = s_tst[2 * kThreads + tid]; }
             const int mt = s / VR, row = s % VR;
             const int act = s_act[s];
+            // the step's two kiss99 draws, by every lane of the stream from broadcast loads (no branch, no shuffle;
+            // the integer work fills the latency of the loads below)
+            uint32_t r0, r1;
+            {
+              uint32_t zz = s_rng[s], ww = s_rng[NS + s], js = s_rng[2 * NS + s], jc = s_rng[3 * NS + s];
+              r0 = kiss99_next(zz, ww, js, jc);
+              r1 = kiss99_next(zz, ww, js, jc);
+              __syncwarp();
+              if (l16 == 0 && act) { s_rng[s] = zz; s_rng[NS + s] = ww; s_rng[2 * NS + s] = js; s_rng[3 * NS + s] = jc; }
+            }
             // compute_gruB (src/nnet.c:326-372)
             float zrh[3], rec[3];
 #pragma unroll
@@ -613,15 +635,6 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             __syncwarp();
             LPCB_MARK(5);   // GRU-B gates
             // sample_mdense (src/nnet.c:163-214)
-            uint32_t r0 = 0, r1 = 0;
-            if (l16 == 0) {
-              uint32_t zz = s_rng[s], ww = s_rng[NS + s], js = s_rng[2 * NS + s], jc = s_rng[3 * NS + s];
-              r0 = kiss99_next(zz, ww, js, jc);
-              r1 = kiss99_next(zz, ww, js, jc);
-              if (act) { s_rng[s] = zz; s_rng[NS + s] = ww; s_rng[2 * NS + s] = js; s_rng[3 * NS + s] = jc; }
-            }
-            r0 = __shfl_sync(0xffffffffu, r0, gbase);
-            r1 = __shfl_sync(0xffffffffu, r1, gbase);
             float bv[16];
 #pragma unroll
             for (int k = 0; k < 4; k++) {
