@@ -201,6 +201,16 @@ def run_reference(args):
         ref.close()
 
 
+def step_latency_percentiles(launch_ms, launch_steps):
+    """Per-sample step latency of one resident stream tile, per sample-kernel launch (launch duration / steps in
+    the launch; the two warm-up frames of a call run no steps and are excluded): [median, p99] in microseconds."""
+    lat = [1e3 * float(m) / int(n) for m, n in zip(launch_ms, launch_steps) if int(n) >= 160 * 4]
+    if not lat:
+        return None
+    lat.sort()
+    return [lat[len(lat) // 2], lat[min(len(lat) - 1, int(0.99 * len(lat)))]]
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -277,6 +287,7 @@ def run_gpu(args):
     ms = e0.elapsed_time(e1)
     launches = bt.launch_count - l0
     sample_ms, n_sample, frame_ms, n_frame = bt.read_profile()
+    launch_ms, launch_steps = bt.profile_launches()
     bt.set_profiling(False)
     clk = clocks.stop() if rank == 0 else None
     nonzero = int((d_pcm[:, 320:] != 0).sum().item())
@@ -375,6 +386,7 @@ def run_gpu(args):
             "vs_baseline": None, "dtype": "u8*s8->s32 + f32", "data": "synthetic",
             "x_realtime": value / 16000.0,
             "step_latency_us": kernel_s * 1e6 / (active_frames * FRAME * args.steps / max(1, n_sample)),
+            "step_latency_us_p50_p99": step_latency_percentiles(launch_ms, launch_steps),
             "config": {"workload": f"batched -synthesis, {B} streams x {args.seconds:g} s per GPU (BASELINE configs[1])",
                        "streams_per_gpu": B, "seconds": args.seconds, "tile_streams_per_cta": bt.tile,
                        "model": "random-init, N=384 NB=16 density (0.05,0.05,0.2), reference blob layout",

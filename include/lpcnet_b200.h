@@ -172,6 +172,9 @@ LPCNET_B200_EXPORT long long lpcnet_batch_launch_count(const LPCNetBatch *b);
  * launch group on the batch's stream; read_profile synchronises, returns the summed
  * durations and counts since the last read, and clears them. */
 LPCNET_B200_EXPORT int lpcnet_batch_set_profiling(LPCNetBatch *b, int on);
+/* After read_profile: duration (ms) and number of sample steps of each sample-kernel launch it summed.
+ * Returns the number of launches; fills at most `max` entries (either array may be NULL). */
+LPCNET_B200_EXPORT int lpcnet_batch_profile_launches(LPCNetBatch *b, float *ms, int *steps, int max);
 LPCNET_B200_EXPORT int lpcnet_batch_read_profile(LPCNetBatch *b, double *sample_ms, int *sample_launches,
                                                  double *frame_ms, int *frame_groups);
 /* Micro-benchmark used for the on-chip roofline: GB/s achieved by all SMs gathering random

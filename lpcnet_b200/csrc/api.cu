@@ -79,6 +79,8 @@ struct LPCNetBatch {
   long long launches = 0;
   bool profiling = false;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_sample, ev_frame;
+  std::vector<int> ev_sample_steps, last_launch_steps;   // sample steps of every profiled sample-kernel launch
+  std::vector<float> last_launch_ms;                     // their durations, as of the last read_profile
   // grow-only staging for the host-buffer entry points
   void *d_feat = nullptr; size_t d_feat_bytes = 0;
   void *d_pcm = nullptr; size_t d_pcm_bytes = 0;
@@ -201,7 +203,7 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (b->profiling) { CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventRecord(e0, b->stream)); }
     CK(launch_sample_kernel(sa, tile, b->n_sms, b->stream, &nl));
-    if (b->profiling) { CK(cudaEventRecord(e1, b->stream)); b->ev_sample.emplace_back(e0, e1); }
+    if (b->profiling) { CK(cudaEventRecord(e1, b->stream)); b->ev_sample.emplace_back(e0, e1); b->ev_sample_steps.push_back(F * spf); }
     b->launches += nl;
   }
   return 0;
@@ -354,12 +356,16 @@ int lpcnet_batch_read_profile(LPCNetBatch *b, double *sample_ms, int *sample_lau
   if (!b) return fail("null batch");
   CK(cudaSetDevice(b->device));
   CK(cudaStreamSynchronize(b->stream));
+  b->last_launch_ms.clear();
+  b->last_launch_steps.swap(b->ev_sample_steps);
+  b->ev_sample_steps.clear();
   auto drain = [&](std::vector<std::pair<cudaEvent_t, cudaEvent_t>> &v, double *ms, int *n) -> int {
     double tot = 0;
     for (auto &p : v) {
       float t = 0;
       CK(cudaEventElapsedTime(&t, p.first, p.second));
       tot += t;
+      if (&v == &b->ev_sample) b->last_launch_ms.push_back(t);
       cudaEventDestroy(p.first); cudaEventDestroy(p.second);
     }
     if (ms) *ms = tot;
@@ -370,6 +376,16 @@ int lpcnet_batch_read_profile(LPCNetBatch *b, double *sample_ms, int *sample_lau
   if (drain(b->ev_sample, sample_ms, sample_launches)) return -1;
   if (drain(b->ev_frame, frame_ms, frame_groups)) return -1;
   return 0;
+}
+
+int lpcnet_batch_profile_launches(LPCNetBatch *b, float *ms, int *steps, int max) {
+  if (!b) return fail("null batch");
+  const int n = (int)b->last_launch_ms.size();
+  for (int i = 0; i < n && i < max; i++) {
+    if (ms) ms[i] = b->last_launch_ms[i];
+    if (steps) steps[i] = i < (int)b->last_launch_steps.size() ? b->last_launch_steps[i] : 0;
+  }
+  return n;
 }
 
 int lpcnet_batch_sync(LPCNetBatch *b) {

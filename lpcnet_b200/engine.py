@@ -41,7 +41,7 @@ EXPORTED_SYMBOLS = [
     "lpcnet_batch_synthesize", "lpcnet_batch_synthesize_device", "lpcnet_batch_frame_network",
     "lpcnet_batch_decode", "lpcnet_batch_set_codebooks", "lpcnet_batch_get_state",
     "lpcnet_batch_set_state", "lpcnet_batch_sync", "lpcnet_batch_nblocks", "lpcnet_batch_launch_count",
-    "lpcnet_batch_set_profiling", "lpcnet_batch_read_profile", "lpcnet_b200_measure_l2_gather",
+    "lpcnet_batch_set_profiling", "lpcnet_batch_read_profile", "lpcnet_batch_profile_launches", "lpcnet_b200_measure_l2_gather",
     "lpcnet_b200_set_rcp_table", "lpcnet_b200_default_rcp_table", "lpcnet_b200_set_model_constants",
     "lpcnet_b200_last_error", "lpcnet_b200_device_count",
 ]
@@ -89,6 +89,7 @@ def load_library() -> C.CDLL:
     L.lpcnet_batch_launch_count.argtypes = [vp]
     L.lpcnet_batch_set_profiling.argtypes = [vp, ci]
     L.lpcnet_batch_read_profile.argtypes = [vp, vp, vp, vp, vp]
+    L.lpcnet_batch_profile_launches.argtypes = [vp, vp, vp, ci]
     L.lpcnet_b200_measure_l2_gather.argtypes = [ci, vp]
     L.lpcnet_b200_set_rcp_table.argtypes = [vp]
     L.lpcnet_b200_default_rcp_table.argtypes = [vp]
@@ -211,6 +212,14 @@ class Batch:
 
     def set_profiling(self, on: bool):
         _check(self.L.lpcnet_batch_set_profiling(self.h, int(on)), "lpcnet_batch_set_profiling")
+
+    def profile_launches(self):
+        """(ms, steps) arrays of the sample-kernel launches summed by the last read_profile()."""
+        n = self.L.lpcnet_batch_profile_launches(self.h, None, None, 0)
+        ms = np.zeros(max(n, 1), np.float32)
+        steps = np.zeros(max(n, 1), np.int32)
+        self.L.lpcnet_batch_profile_launches(self.h, _p(ms), _p(steps), n)
+        return ms[:n], steps[:n]
 
     def read_profile(self):
         """(sample_kernel_ms, n_sample_launches, frame_network_ms, n_frame_groups) since the last read."""
