@@ -468,7 +468,8 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
                 // bias + diag*state: a multiply feeding an add stays scalar -- ptxas contracts
                 // mul.rn.f32x2 + add.rn.f32x2 into FFMA2 (it never contracts the scalar .rn forms)
                 const float2 a2 = a_reg[u][mt][h];
-                float2 tx = make_float2(sub.x + dg.x * a2.x, sub.y + dg.y * a2.y);
+                const float2 da = f2_mul(dg, a2);                         // packed product, scalar sums (see above)
+                float2 tx = make_float2(sub.x + da.x, sub.y + da.y);
                 if (gate < 2) tx = f2_add(tx, gx);                        // (+ input for z, r)
                 else gh[h] = gx;
                 const float2 sd = f2_mul(tx, f2_set(LPCB_SCALE));
@@ -482,10 +483,12 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               const float2 z = sigmoid2_ref(f2_mul(make_float2((float)acc[0][2 * h], (float)acc[0][2 * h + 1]), k1), s_rcp);
               const float2 r = sigmoid2_ref(f2_mul(make_float2((float)acc[1][2 * h], (float)acc[1][2 * h + 1]), k1), s_rcp);
               float2 hh = f2_mul(make_float2((float)acc[2][2 * h], (float)acc[2][2 * h + 1]), k1);
-              hh = tanh2_ref(make_float2(hh.x * r.x + gh[h].x, hh.y * r.y + gh[h].y), s_rcp);   // scalar mul+add (see above)
+              const float2 hr = f2_mul(hh, r);
+              hh = tanh2_ref(make_float2(hr.x + gh[h].x, hr.y + gh[h].y), s_rcp);   // packed product, scalar sums
               const float2 a_old = a_reg[u][mt][h];
               // z*state + (1-z)*h, scalar for the same reason
-              const float2 a_nw = make_float2(z.x * a_old.x + (1.f - z.x) * hh.x, z.y * a_old.y + (1.f - z.y) * hh.y);
+              const float2 za = f2_mul(z, a_old), zh = f2_mul(f2_add(f2_set(1.f), make_float2(-z.x, -z.y)), hh);
+              const float2 a_nw = make_float2(za.x + zh.x, za.y + zh.y);
               unsigned short *dst = reinterpret_cast<unsigned short *>(xa_new) + (((sA + 8 * h) * kXaStride * 4 + ug * 8 + 2 * t) >> 1);
               if (ixw[mt][h] >> 24) {
                 a_reg[u][mt][h] = a_nw;
