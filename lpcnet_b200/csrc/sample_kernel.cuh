@@ -101,10 +101,13 @@ __device__ __forceinline__ float node_logit(const float *__restrict__ wbase, int
   }
   float sum1 = bf[i], sum2 = bf[256 + i];       // bias|factor are always resident
   const float f1 = bf[512 + i], f2 = bf[768 + i];
+  // products two at a time (FMUL2), sums in the reference's order: each product is rounded before its add
 #pragma unroll
-  for (int j = 0; j < 16; j++) {
-    sum1 = sum1 + w[j] * bv[j];
-    sum2 = sum2 + w[16 + j] * bv[j];
+  for (int j = 0; j < 16; j += 2) {
+    const float2 b2 = make_float2(bv[j], bv[j + 1]);
+    const float2 p1 = f2_mul(make_float2(w[j], w[j + 1]), b2), p2 = f2_mul(make_float2(w[16 + j], w[17 + j]), b2);
+    sum1 = sum1 + p1.x; sum2 = sum2 + p2.x;
+    sum1 = sum1 + p1.y; sum2 = sum2 + p2.y;
   }
   sum1 = f1 * tanh_ref(sum1, rcp);
   sum2 = f2 * tanh_ref(sum2, rcp);
