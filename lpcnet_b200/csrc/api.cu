@@ -72,8 +72,12 @@ struct LPCNetBatch {
   Model model;
   DevState st{};
   void *st_alloc = nullptr;
-  FrameBuffers fb;
+  FrameBuffers fb;                // frame-network outputs of one chunk ...
   void *fb_alloc = nullptr;
+  FrameBuffers fb2;               // ... and of the next one: the frame network of chunk k+1 runs on its own stream
+  void *fb2_alloc = nullptr;      //     beside the sample kernel of chunk k (it depends only on frame-rate state)
+  cudaStream_t fstream = nullptr;
+  cudaEvent_t ev_entry = nullptr, ev_frames[2] = {nullptr, nullptr}, ev_samples[2] = {nullptr, nullptr};
   cudaStream_t own_stream = nullptr;
   cudaStream_t stream = nullptr;
   long long launches = 0;
@@ -128,10 +132,12 @@ int chunk_frames(const LPCNetBatch *b, int n_frames) {
   return n_frames < cap ? n_frames : (int)cap;
 }
 
-int ensure_frame_buffers(LPCNetBatch *b, int F) {
-  if (b->fb.cap_frames >= F) return 0;
-  if (b->fb_alloc) cudaFree(b->fb_alloc);
-  b->fb_alloc = nullptr; b->fb.cap_frames = 0;
+int ensure_frame_buffers(LPCNetBatch *b, int F, bool second = false) {
+  FrameBuffers &fb = second ? b->fb2 : b->fb;
+  void *&alloc = second ? b->fb2_alloc : b->fb_alloc;
+  if (fb.cap_frames >= F) return 0;
+  if (alloc) cudaFree(alloc);
+  alloc = nullptr; fb.cap_frames = 0;
   const size_t B = b->n_streams;
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t r = off; off += (bytes + 255) & ~size_t(255); return r; };
@@ -140,12 +146,12 @@ int ensure_frame_buffers(LPCNetBatch *b, int F) {
   const size_t o_lpc = take((size_t)F * B * 16 * 4), o_act = take((size_t)F * B);
   const size_t fft_threads = ((B * F + 63) / 64) * 64;
   const size_t o_fft = take(fft_threads * 640 * 4);
-  CK(cudaMalloc(&b->fb_alloc, off));
-  char *p = static_cast<char *>(b->fb_alloc);
-  b->fb.in_vec = (float *)(p + o_iv); b->fb.c1 = (float *)(p + o_c1); b->fb.cond_a = (float *)(p + o_ca);
-  b->fb.cond_b = (float *)(p + o_cb); b->fb.lpc = (float *)(p + o_lpc); b->fb.active = (uint8_t *)(p + o_act);
-  b->fb.fft_scratch = (float *)(p + o_fft);
-  b->fb.cap_frames = F;
+  CK(cudaMalloc(&alloc, off));
+  char *p = static_cast<char *>(alloc);
+  fb.in_vec = (float *)(p + o_iv); fb.c1 = (float *)(p + o_c1); fb.cond_a = (float *)(p + o_ca);
+  fb.cond_b = (float *)(p + o_cb); fb.lpc = (float *)(p + o_lpc); fb.active = (uint8_t *)(p + o_act);
+  fb.fft_scratch = (float *)(p + o_fft);
+  fb.cap_frames = F;
   return 0;
 }
 
@@ -159,22 +165,26 @@ int auto_tile(const LPCNetBatch *b) {
   return t < b->max_tile ? t : b->max_tile;
 }
 
-// frame network for frames [f0, f0+F) of the call, results left in b->fb
-int run_frames(LPCNetBatch *b, const float *d_features, int stride, int f0, int F, int total_frames) {
+// frame network for frames [f0, f0+F) of the call on stream st, results left in fb
+int run_frames(LPCNetBatch *b, const float *d_features, int stride, int f0, int F, int total_frames,
+               const FrameBuffers &fb, cudaStream_t st) {
   FrameArgs fa{};
-  fa.m = b->model.d; fa.st = b->st; fa.fb = b->fb; fa.n_streams = b->n_streams; fa.n_frames = F;
+  fa.m = b->model.d; fa.st = b->st; fa.fb = fb; fa.n_streams = b->n_streams; fa.n_frames = F;
   fa.features = d_features; fa.feature_stride = stride; fa.frame0 = f0; fa.total_frames = total_frames;
   int nl = 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
-  if (b->profiling) { CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventRecord(e0, b->stream)); }
-  CK(launch_frame_network(fa, b->stream, &nl));
-  if (b->profiling) { CK(cudaEventRecord(e1, b->stream)); b->ev_frame.emplace_back(e0, e1); }
+  if (b->profiling) { CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventRecord(e0, st)); }
+  CK(launch_frame_network(fa, st, &nl));
+  if (b->profiling) { CK(cudaEventRecord(e1, st)); b->ev_frame.emplace_back(e0, e1); }
   b->launches += nl;
   // keep the last frame's conditioning in the stream state (lpcnet_private.h:43-47)
   const size_t B = b->n_streams;
-  CK(cudaMemcpyAsync(b->st.cond_a, b->fb.cond_a + (size_t)(F - 1) * B * kRowsAP, B * kRowsAP * 4, cudaMemcpyDeviceToDevice, b->stream));
-  CK(cudaMemcpyAsync(b->st.cond_b, b->fb.cond_b + (size_t)(F - 1) * B * kRowsB, B * kRowsB * 4, cudaMemcpyDeviceToDevice, b->stream));
+  CK(cudaMemcpyAsync(b->st.cond_a, fb.cond_a + (size_t)(F - 1) * B * kRowsAP, B * kRowsAP * 4, cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemcpyAsync(b->st.cond_b, fb.cond_b + (size_t)(F - 1) * B * kRowsB, B * kRowsB * 4, cudaMemcpyDeviceToDevice, st));
   return 0;
+}
+int run_frames(LPCNetBatch *b, const float *d_features, int stride, int f0, int F, int total_frames) {
+  return run_frames(b, d_features, stride, f0, F, total_frames, b->fb, b->stream);
 }
 
 int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_frames, int spf, short *d_pcm,
@@ -187,13 +197,41 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
   const int Fc = chunk_frames(b, n_frames);
   if (ensure_frame_buffers(b, Fc)) return -1;
   const int tile = auto_tile(b);
-  for (int f0 = 0; f0 < n_frames; f0 += Fc) {
+  // Several chunks: the frame network of chunk k+1 runs on a second stream while the sample kernel works on
+  // chunk k (two buffer sets).  It touches only frame-rate state (conv histories, frame counter, LPC delay
+  // line); the sample kernel only sample-rate state.  Everything is ordered after the caller's stream at
+  // entry, and the caller's stream ends after all of it.
+  const bool pipe = n_frames > Fc && !getenv("LPCNET_B200_NO_PIPELINE");
+  if (pipe) {
+    if (ensure_frame_buffers(b, Fc, true)) return -1;
+    if (!b->fstream) {
+      CK(cudaStreamCreateWithFlags(&b->fstream, cudaStreamNonBlocking));
+      CK(cudaEventCreateWithFlags(&b->ev_entry, cudaEventDisableTiming));
+      for (int k = 0; k < 2; k++) {
+        CK(cudaEventCreateWithFlags(&b->ev_frames[k], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&b->ev_samples[k], cudaEventDisableTiming));
+      }
+    }
+    CK(cudaEventRecord(b->ev_entry, b->stream));
+    CK(cudaStreamWaitEvent(b->fstream, b->ev_entry, 0));
+  }
+  int chunk = 0;
+  for (int f0 = 0; f0 < n_frames; f0 += Fc, chunk++) {
     const int F = (n_frames - f0) < Fc ? (n_frames - f0) : Fc;
-    if (run_frames(b, d_features, stride, f0, F, n_frames)) return -1;
+    const int buf = pipe ? (chunk & 1) : 0;
+    const FrameBuffers &fbk = buf ? b->fb2 : b->fb;
+    if (pipe) {
+      if (chunk >= 2) CK(cudaStreamWaitEvent(b->fstream, b->ev_samples[buf], 0));   // the buffers are free again
+      if (run_frames(b, d_features, stride, f0, F, n_frames, fbk, b->fstream)) return -1;
+      CK(cudaEventRecord(b->ev_frames[buf], b->fstream));
+      CK(cudaStreamWaitEvent(b->stream, b->ev_frames[buf], 0));
+    } else if (run_frames(b, d_features, stride, f0, F, n_frames)) {
+      return -1;
+    }
     SampleArgs sa{};
     sa.m = b->model.d; sa.st = b->st; sa.n_streams = b->n_streams; sa.n_frames = F; sa.spf = spf;
     sa.frame0 = f0; sa.total_frames = n_frames;
-    sa.cond_a = b->fb.cond_a; sa.cond_b = b->fb.cond_b; sa.lpc = b->fb.lpc; sa.active = b->fb.active;
+    sa.cond_a = fbk.cond_a; sa.cond_b = fbk.cond_b; sa.lpc = fbk.lpc; sa.active = fbk.active;
     sa.pcm = d_pcm; sa.forced = d_forced; sa.trace = d_trace; sa.logits = d_logits;
 #ifdef LPCB_PHASE_CLOCKS
     if (!g_phase_clk) { CK(cudaMalloc(&g_phase_clk, 16 * 8)); CK(cudaMemset(g_phase_clk, 0, 16 * 8)); }
@@ -204,6 +242,7 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
     if (b->profiling) { CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventRecord(e0, b->stream)); }
     CK(launch_sample_kernel(sa, tile, b->n_sms, b->stream, &nl));
     if (b->profiling) { CK(cudaEventRecord(e1, b->stream)); b->ev_sample.emplace_back(e0, e1); b->ev_sample_steps.push_back(F * spf); }
+    if (pipe) CK(cudaEventRecord(b->ev_samples[buf], b->stream));
     b->launches += nl;
   }
   return 0;
@@ -307,7 +346,13 @@ void lpcnet_batch_destroy(LPCNetBatch *b) {
   cudaSetDevice(b->device);
   if (b->stream) cudaStreamSynchronize(b->stream);
   free_model(b->model);
-  void *ptrs[] = {b->st_alloc, b->fb_alloc, b->d_feat, b->d_pcm, b->d_forced, b->d_trace, b->d_logits, b->d_packets};
+  if (b->fstream) {
+    cudaStreamSynchronize(b->fstream);
+    cudaStreamDestroy(b->fstream);
+    cudaEventDestroy(b->ev_entry);
+    for (int k = 0; k < 2; k++) { cudaEventDestroy(b->ev_frames[k]); cudaEventDestroy(b->ev_samples[k]); }
+  }
+  void *ptrs[] = {b->st_alloc, b->fb_alloc, b->fb2_alloc, b->d_feat, b->d_pcm, b->d_forced, b->d_trace, b->d_logits, b->d_packets};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (b->own_stream) cudaStreamDestroy(b->own_stream);
   delete b;
