@@ -181,6 +181,41 @@ LPCNET_B200_EXPORT int lpcnet_batch_read_profile(LPCNetBatch *b, double *sample_
  * 4608-byte rows (one embedding row) from an L2-resident 3.5 MB table with 128-bit loads. */
 LPCNET_B200_EXPORT int lpcnet_b200_measure_l2_gather(int device, double *gbytes_per_s);
 
+/* ------------------------------------------------------------------------------------
+ * 3. Feature analysis (the step before the synthesis path)
+ * ------------------------------------------------------------------------------------ */
+/* The reference's per-frame analysis entry points (include/lpcnet.h:98-158, src/lpcnet_enc.c:467-486, 913-933):
+ * 160 samples of 16 kHz PCM -> NB_TOTAL_FEATURES (36) floats = 18 cepstral coefficients, pitch period,
+ * pitch correlation, 16 LPC coefficients.  One stream; the state lives on the GPU (device 0). */
+typedef struct LPCNetEncState LPCNetEncState;
+LPCNET_B200_EXPORT int lpcnet_encoder_get_size(void);
+LPCNET_B200_EXPORT int lpcnet_encoder_init(LPCNetEncState *st);
+LPCNET_B200_EXPORT LPCNetEncState *lpcnet_encoder_create(void);
+LPCNET_B200_EXPORT void lpcnet_encoder_destroy(LPCNetEncState *st);
+LPCNET_B200_EXPORT int lpcnet_compute_single_frame_features(LPCNetEncState *st, const short *pcm, float *features);
+LPCNET_B200_EXPORT int lpcnet_compute_single_frame_features_float(LPCNetEncState *st, const float *pcm,
+                                                                  float *features);
+
+/* Batched form: n_streams independent analysis states, any number of frames per call (the state carries over,
+ * so one call of n frames equals n calls of one frame).  pcm: [n_streams][n_frames*160]; features:
+ * [n_streams][n_frames][36].  Returns 0, or -1 with lpcnet_b200_last_error() set.  No CPU fallback. */
+typedef struct LPCNetFeatureBatch LPCNetFeatureBatch;
+LPCNET_B200_EXPORT LPCNetFeatureBatch *lpcnet_feature_batch_create(int n_streams, int device);
+LPCNET_B200_EXPORT void lpcnet_feature_batch_destroy(LPCNetFeatureBatch *b);
+LPCNET_B200_EXPORT int lpcnet_feature_batch_n_streams(const LPCNetFeatureBatch *b);
+LPCNET_B200_EXPORT long long lpcnet_feature_batch_launch_count(const LPCNetFeatureBatch *b);
+/* lpcnet_encoder_init for one stream, or for all of them (stream = -1). */
+LPCNET_B200_EXPORT int lpcnet_feature_batch_reset(LPCNetFeatureBatch *b, int stream);
+LPCNET_B200_EXPORT int lpcnet_feature_batch_compute(LPCNetFeatureBatch *b, const short *pcm, int n_frames,
+                                                    float *features);
+LPCNET_B200_EXPORT int lpcnet_feature_batch_compute_float(LPCNetFeatureBatch *b, const float *pcm, int n_frames,
+                                                          float *features);
+/* Device pointers (exactly one of d_pcm16 / d_pcmf non-NULL); enqueued on cuda_stream (a cudaStream_t, NULL = the
+ * batch's own stream) without synchronising. */
+LPCNET_B200_EXPORT int lpcnet_feature_batch_compute_device(LPCNetFeatureBatch *b, const short *d_pcm16,
+                                                           const float *d_pcmf, int n_frames, float *d_features,
+                                                           void *cuda_stream);
+
 /* The reference's tanh/sigmoid multiply by `rcpps` (src/vec_avx.h:408,437), a CPU
  * hardware estimate that is exactly a 2048-entry table over the top 11 mantissa bits.
  * Default: the Intel table model (oracle/orc_prim.c).  A process-wide override takes the

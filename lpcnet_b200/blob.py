@@ -207,3 +207,18 @@ def stream_seed(stream: int) -> bytes:
     """Per-stream kiss99 seed string; stream 0 is the reference default "LPCNet"
     (lpcnet.c:176-181)."""
     return b"LPCNet" if stream == 0 else b"LPCNet" + str(stream).encode()
+
+
+def synthetic_pcm(n_frames: int, stream: int = 0) -> np.ndarray:
+    """Synthetic 16 kHz input for the analysis side (band-limited noise + a sinusoid with a
+    moving fundamental, slow amplitude envelope): int16 [n_frames*160]."""
+    rng = np.random.default_rng(5000 + stream)
+    n = n_frames * 160
+    t = np.arange(n)
+    f0 = 80 + 200 * rng.random()
+    ph = 2 * np.pi * f0 / 16000 * t + 3 * np.sin(2 * np.pi * (1 + 2 * rng.random()) / 16000 * t)
+    x = 4000 * np.sin(ph) + 1500 * np.sin(2.01 * ph) + 700 * np.sin(3.02 * ph)
+    noise = rng.standard_normal(n + 8)
+    x += 600 * np.convolve(noise, np.ones(8) / 8, mode="valid")[:n] + 100 * noise[:n]
+    env = 0.55 + 0.45 * np.sin(2 * np.pi * 1.3 / 16000 * t + 6 * rng.random())
+    return np.clip(np.round(x * env), -32768, 32767).astype(np.int16)

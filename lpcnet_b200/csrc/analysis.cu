@@ -1,0 +1,533 @@
+// Per-frame feature analysis for many streams at once: the reference's
+// lpcnet_compute_single_frame_features = preemphasis + compute_frame_features + process_single_frame
+// (src/lpcnet_enc.c:872-880, 498-577, 814-870, 913-933) -- the step before the synthesis path ("-features"
+// per frame) and an inner step of the PLC (src/lpcnet_plc.c:252-254, 424-432).
+//
+// What is sequential in the reference and what is not:
+//  * pre-emphasis, the analysis window, the LPC residual (an FIR over the 80-sample-delayed signal) and its
+//    one-tap smoothing are feed-forward: every sample / frame of a call is computed in parallel from the
+//    signal and a 160-sample history (P), with the frame's own LPC;
+//  * the pitch search is a Viterbi pass over half-frames: one block per stream walks the frames in order,
+//    256 threads = 256 lags (cross-correlation, 3x interpolation, octave penalty, path update, argmax);
+//  * the running energy under the correlation window is a double-precision recurrence over the lags
+//    (lpcnet_enc.c:539-546): one thread walks it so that every addition rounds as in the reference.
+// Every float operation is a separate IEEE operation in the reference's order (-fmad=false), so the features
+// are bit-identical to the reference's parity build; log10() is evaluated in double as there.
+#include <math.h>
+
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/lpcnet_b200.h"
+#include "dsp.cuh"
+#include "engine.h"
+
+namespace lpcb {
+
+namespace {
+
+constexpr int kWin = 320, kOverlap = 160, kTOff = 80, kPMax = 256, kPMin = 32, kBands = 18, kNF = 36;
+
+struct EncState {        // per stream, device
+  float *p_hist;         // [B][160]  analysis_mem: the last 160 pre-emphasised samples
+  float *mem_preemph;    // [B]
+  float *s_last;         // [B]       pitch_filt: the LPC residual of the last sample
+  float *e_hist;         // [B][256]  exc_buf[160..416): the last 256 smoothed residual samples
+  float *path;           // [B][256]  pitch_max_path[0]
+  float *path_all;       // [B]
+  int *best_i;           // [B]
+};
+
+struct AnalysisArgs {
+  EncState st;
+  DspTables tab;
+  const float *half_window;   // [160]
+  int n_streams, n_frames;    // frames in this chunk
+  int frame0, total_frames;   // position of the chunk in the call (pcm / feature row strides)
+  const short *pcm16;         // device [B][total_frames*160], or NULL
+  const float *pcmf;          // device [B][total_frames*160], or NULL
+  float *features;            // device [B][total_frames][36]
+  float *P;                   // [B][160 + 160F]  history | pre-emphasised signal
+  float *S;                   // [B][1 + 160F]    previous residual | LPC residual
+  float *fft_scratch;         // [320][2][B*F]
+};
+
+__device__ __forceinline__ float pcm_at(const AnalysisArgs &A, int s, int n) {
+  const size_t i = (size_t)s * A.total_frames * kFrame + (size_t)A.frame0 * kFrame + n;
+  return A.pcm16 ? (float)A.pcm16[i] : A.pcmf[i];
+}
+
+// preemphasis (lpcnet_enc.c:872-880): y[n] = x[n] + mem, mem = -0.85f * x[n]
+__global__ void preemph_kernel(AnalysisArgs A) {
+  const int L = kOverlap + A.n_frames * kFrame;
+  const size_t total = (size_t)A.n_streams * L;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int s = (int)(i / L), k = (int)(i % L);
+    float v;
+    if (k < kOverlap) {
+      v = A.st.p_hist[(size_t)s * kOverlap + k];
+    } else {
+      const int n = k - kOverlap;
+      const float mem = n == 0 ? A.st.mem_preemph[s] : -0.85f * pcm_at(A, s, n - 1);
+      v = pcm_at(A, s, n) + mem;
+    }
+    A.P[i] = v;
+  }
+}
+
+// frame_analysis + the spectral half of compute_frame_features (lpcnet_enc.c:488-527): window, forward FFT,
+// band energies, log smoothing, DCT, LPC from the cepstrum.  One thread per (stream, frame).
+__global__ void spectral_kernel(AnalysisArgs A) {
+  const int B = A.n_streams, F = A.n_frames;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t nthreads = (size_t)gridDim.x * blockDim.x;
+  if (idx >= B * F) return;
+  const int s = idx / F, f = idx % F;
+  Scratch S{A.fft_scratch + idx, nthreads};
+  const float *x = A.P + (size_t)s * (kOverlap + F * kFrame) + (size_t)f * kFrame;   // [analysis_mem | frame]
+  // apply_window (freq.c:322-328) and opus_fft_c's scaled bit-reversed copy (kiss_fft.c:566-585)
+  const float scale = 1.f / 320;
+  for (int k = 0; k < kWin; k++) {
+    const float w = __ldg(A.half_window + (k < kOverlap ? k : kWin - 1 - k));
+    Cpx c;
+    c.r = scale * (x[k] * w); c.i = scale * 0.f;
+    S.st(__ldg(A.tab.fft_bitrev + k), c);
+  }
+  fft320_butterflies(S, A.tab.fft_tw);
+  // lpcn_compute_band_energy (freq.c:128-150)
+  float sum[kBands];
+  for (int i = 0; i < kBands; i++) sum[i] = 0;
+  for (int i = 0; i < kBands - 1; i++) {
+    const int band_size = (c_eband5ms[i + 1] - c_eband5ms[i]) * 4;
+    for (int j = 0; j < band_size; j++) {
+      const float frac = (float)j / (float)band_size;
+      const Cpx X = S.ld(c_eband5ms[i] * 4 + j);
+      float tmp = X.r * X.r;
+      tmp += X.i * X.i;
+      sum[i] += (1.f - frac) * tmp;
+      sum[i + 1] += frac * tmp;
+    }
+  }
+  sum[0] *= 2;
+  sum[kBands - 1] *= 2;
+  // lpcnet_enc.c:514-522
+  float Ly[kBands], logMax = -2, follow = -2;
+  for (int i = 0; i < kBands; i++) {
+    float l = (float)log10(1e-2 + (double)sum[i]);
+    l = fmaxf(logMax - 8, fmaxf(follow - 2.5f, l));
+    Ly[i] = l;
+    logMax = fmaxf(logMax, l);
+    follow = fmaxf(follow - 2.5f, l);
+  }
+  // dct (freq.c:218-228)
+  float ceps[kBands];
+  for (int i = 0; i < kBands; i++) {
+    float acc = 0;
+    for (int j = 0; j < kBands; j++) acc += Ly[j] * __ldg(A.tab.dct + j * kBands + i);
+    ceps[i] = (float)((double)acc * sqrt(2. / kBands));
+  }
+  ceps[0] -= 4;
+  float lpc[16];
+  lpc_from_cepstrum_dev(A.tab, ceps, lpc, S);
+  float *out = A.features + ((size_t)s * A.total_frames + A.frame0 + f) * kNF;
+  for (int i = 0; i < kBands; i++) out[i] = ceps[i];
+  for (int i = 0; i < 16; i++) out[kBands + 2 + i] = lpc[i];
+}
+
+// The LPC residual of the 80-sample-delayed signal (lpcnet_enc.c:528-539): an FIR, so every sample is independent.
+// S[s][1 + n] = a[n] + sum_j lpc[j] * a[n-1-j], a[n] = P[80 + n]; S[s][0] = the previous call's last value.
+__global__ void residual_kernel(AnalysisArgs A) {
+  const int F = A.n_frames, L = F * kFrame;
+  const size_t total = (size_t)A.n_streams * L;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int s = (int)(i / L), n = (int)(i % L), f = n / kFrame;
+    const float *a = A.P + (size_t)s * (kOverlap + L) + kTOff + n;
+    const float *lpc = A.features + ((size_t)s * A.total_frames + A.frame0 + f) * kNF + kBands + 2;
+    float sum = a[0];
+    for (int j = 0; j < 16; j++) sum += lpc[j] * a[-1 - j];
+    A.S[(size_t)s * (L + 1) + 1 + n] = sum;
+    if (n == 0) A.S[(size_t)s * (L + 1)] = A.st.s_last[s];
+  }
+}
+
+// The pitch half of compute_frame_features (lpcnet_enc.c:540-576) and process_single_frame (814-870); one block
+// per stream, thread t = lag t.
+constexpr int kPT = 256;
+__global__ void __launch_bounds__(kPT) pitch_kernel(AnalysisArgs A) {
+  extern __shared__ float sm[];
+  const int s = blockIdx.x, t = threadIdx.x, F = A.n_frames, L = F * kFrame;
+  float *ebuf = sm;                         // [256 + L]
+  float *xc = ebuf + kPMax + L;             // [2][256]
+  float *path0 = xc + 2 * kPMax;            // [256]
+  float *path1 = path0 + kPMax;             // [256]
+  double *ener1 = reinterpret_cast<double *>(path1 + kPMax);   // [256]
+  int *prev = reinterpret_cast<int *>(ener1 + kPMax);          // [2][256]
+  float *redv = reinterpret_cast<float *>(prev + 2 * kPMax);   // [8]
+  int *redi = reinterpret_cast<int *>(redv + 8);               // [8]
+  __shared__ float ener0_s[2];
+  __shared__ float path_all_s;
+  __shared__ int best_i_s;
+
+  const float *Ss = A.S + (size_t)s * (L + 1);
+  ebuf[t] = A.st.e_hist[(size_t)s * kPMax + t];
+  for (int n = t; n < L; n += kPT) ebuf[kPMax + n] = Ss[n + 1] + .7f * Ss[n];
+  path0[t] = A.st.path[(size_t)s * kPMax + t];
+  path1[t] = 0.f;
+  if (t == 0) { path_all_s = A.st.path_all[s]; best_i_s = A.st.best_i[s]; }
+  __syncthreads();
+
+  for (int f = 0; f < F; f++) {
+    for (int sub = 0; sub < 2; sub++) {
+      const float *ys = ebuf + f * kFrame + sub * (kFrame / 2), *xs = ys + kPMax;
+      // celt_pitch_xcorr (pitch.c:43-83, pitch.h:42-105): every lag is a j-ascending sum from zero
+      float acc = 0;
+      for (int j = 0; j < kFrame / 2; j++) acc = acc + xs[j] * ys[t + j];
+      if (t == 0) {
+        // ener1 (double) walks the lags: += y[i+79]^2 before lag i, -= y[i]^2 after it (lpcnet_enc.c:542-551)
+        float e1f = 0;
+        for (int j = 0; j < kFrame / 2 - 1; j++) e1f = e1f + ys[j] * ys[j];
+        double e1 = e1f;
+        for (int i = 0; i < kPMax; i++) {
+          e1 += (double)(ys[i + kFrame / 2 - 1] * ys[i + kFrame / 2 - 1]);
+          ener1[i] = e1;
+          e1 -= (double)(ys[i] * ys[i]);
+        }
+      } else if (t == 32) {
+        float e0 = 0;
+        for (int j = 0; j < kFrame / 2; j++) e0 = e0 + xs[j] * xs[j];
+        ener0_s[sub] = e0;
+      }
+      __syncthreads();
+      const float ener = (float)((double)(1 + ener0_s[sub]) + ener1[t]);
+      xc[sub * kPMax + t] = 2 * acc / ener;
+      __syncthreads();
+      // 3x upsampled correlation, keep the max (lpcnet_enc.c:552-569)
+      float up = 0.f;
+      if (t >= 4 && t < kPMax - 4) {
+        const float interp[7] = {0.026184f, -0.098339f, 0.369938f, 0.837891f, -0.184969f, 0.070242f, -0.020947f};
+        const float *c = xc + sub * kPMax;
+        float v1 = 0, v2 = 0;
+#pragma unroll
+        for (int j = 0; j < 7; j++) {
+          v1 += c[t - 3 + j] * interp[j];
+          v2 += c[t + 3 - j] * interp[j];
+        }
+        up = fmaxf(c[t], fmaxf(v1, v2));
+      }
+      __syncthreads();
+      if (t >= 4 && t < kPMax - 4) xc[sub * kPMax + t] = up;
+    }
+    __syncthreads();
+    // process_single_frame (lpcnet_enc.c:814-870)
+    float fws = 1e-15f;
+    fws += ener0_s[0];
+    fws += ener0_s[1];
+    const float fw[2] = {ener0_s[0] * (2.f / fws), ener0_s[1] * (2.f / fws)};
+    for (int sub = 0; sub < 2; sub++) {
+      float *c = xc + sub * kPMax;
+      // octave penalty: the values it compares against sit at higher lags than the one it scales
+      float cv = c[t];
+      if (t < kPMax - 2 * kPMin) {
+        const float half = fmaxf(fmaxf(c[(kPMax + t) / 2], c[(kPMax + t + 2) / 2]), c[(kPMax + t - 1) / 2]);
+        if (cv < half * 1.1f) cv *= .8f;
+      }
+      __syncthreads();
+      c[t] = cv;
+      float v = -3.0e38f;
+      if (t < kPMax - kPMin) {
+        float max_prev = path_all_s - 6.f;
+        int pp = best_i_s;
+        for (int j = (t < 4 ? -t : -4); j <= 4 && t + j < kPMax - kPMin; j++) {
+          const int aj = j < 0 ? -j : j;
+          const float cand = path0[t + j] - .02f * (float)aj * (float)aj;
+          if (cand > max_prev) { max_prev = cand; pp = t + j; }
+        }
+        prev[sub * kPMax + t] = pp;
+        v = max_prev + fw[sub] * cv;
+        path1[t] = v;
+      }
+      // first maximum over the lags (strict '>' in lag order, starting from -1e15 / lag 0)
+      int bi = t;
+#pragma unroll
+      for (int o = 16; o; o >>= 1) {
+        const float ov = __shfl_down_sync(0xffffffffu, v, o);
+        const int oi = __shfl_down_sync(0xffffffffu, bi, o);
+        if (ov > v || (ov == v && oi < bi)) { v = ov; bi = oi; }
+      }
+      if ((t & 31) == 0) { redv[t >> 5] = v; redi[t >> 5] = bi; }
+      __syncthreads();
+      if (t == 0) {
+        float mv = -1e15f;
+        int mi = 0;
+        for (int w = 0; w < kPT / 32; w++)
+          if (redv[w] > mv) { mv = redv[w]; mi = redi[w]; }
+        path_all_s = mv; best_i_s = mi;
+      }
+      __syncthreads();
+      if (t < kPMax - kPMin) path1[t] -= path_all_s;
+      path0[t] = path1[t];
+      __syncthreads();
+    }
+    if (t == 0) {
+      int bi = best_i_s, best[2];
+      float frame_corr = 0;
+      for (int sub = 1; sub >= 0; sub--) {
+        best[sub] = kPMax - bi;
+        frame_corr += fw[sub] * xc[sub * kPMax + bi];
+        bi = prev[sub * kPMax + bi];
+      }
+      frame_corr /= 2;
+      float *out = A.features + ((size_t)s * A.total_frames + A.frame0 + f) * kNF;
+      out[kBands] = .01f * (float)(max(66, min(510, best[0] + best[1])) - 200);
+      out[kBands + 1] = frame_corr - .5f;
+    }
+    __syncthreads();
+  }
+  // carry the stream state to the next call
+  A.st.e_hist[(size_t)s * kPMax + t] = ebuf[L + t];
+  A.st.path[(size_t)s * kPMax + t] = path0[t];
+  if (t < kOverlap) A.st.p_hist[(size_t)s * kOverlap + t] = A.P[(size_t)s * (kOverlap + L) + L + t];
+  if (t == 0) {
+    A.st.path_all[s] = path_all_s;
+    A.st.best_i[s] = best_i_s;
+    A.st.s_last[s] = Ss[L];
+    A.st.mem_preemph[s] = -0.85f * pcm_at(A, s, L - 1);
+  }
+}
+
+size_t pitch_smem(int F) {
+  return (size_t)(kPMax + F * kFrame + 2 * kPMax + 2 * kPMax) * 4 + kPMax * 8 + 2 * kPMax * 4 + 64;
+}
+
+}  // namespace
+
+}  // namespace lpcb
+
+using namespace lpcb;
+
+// ---- host side: the batched handle and the reference's encoder-state entry points -------------------------
+struct LPCNetFeatureBatch {
+  int device = 0, n_streams = 0;
+  EncState st{};
+  void *st_alloc = nullptr;
+  size_t st_bytes = 0;
+  void *tab_alloc = nullptr;
+  DspTables tab{};
+  const float *half_window = nullptr;
+  cudaStream_t stream = nullptr;
+  void *work = nullptr; size_t work_bytes = 0;
+  void *d_pcm = nullptr; size_t d_pcm_bytes = 0;
+  void *d_feat = nullptr; size_t d_feat_bytes = 0;
+  long long launches = 0;
+};
+
+namespace {
+
+#define CKA(call)                                                                                      \
+  do {                                                                                                 \
+    cudaError_t e_ = (call);                                                                           \
+    if (e_ != cudaSuccess) return set_last_error(std::string(#call) + ": " + cudaGetErrorString(e_));  \
+  } while (0)
+
+int grow_buf(void **p, size_t *have, size_t want) {
+  if (*have >= want) return 0;
+  if (*p) cudaFree(*p);
+  *p = nullptr; *have = 0;
+  CKA(cudaMalloc(p, want));
+  *have = want;
+  return 0;
+}
+
+int feature_chunk_frames(int B, int n_frames) {
+  int F = 32768 / (B > 0 ? B : 1);
+  F = F < 1 ? 1 : (F > 32 ? 32 : F);
+  return F < n_frames ? F : n_frames;
+}
+
+int analysis_device(LPCNetFeatureBatch *b, const short *d16, const float *df, int n_frames, float *d_features) {
+  const int B = b->n_streams;
+  CKA(cudaSetDevice(b->device));
+  const int Fc = feature_chunk_frames(B, n_frames);
+  const size_t nP = (size_t)B * (kOverlap + Fc * kFrame), nS = (size_t)B * (1 + Fc * kFrame);
+  const int lpc_threads = 64;
+  const size_t n_fft_threads = (size_t)((B * Fc + lpc_threads - 1) / lpc_threads) * lpc_threads;
+  const size_t want = (nP + nS + n_fft_threads * 640) * 4 + 1024;
+  if (grow_buf(&b->work, &b->work_bytes, want)) return -1;
+  for (int f0 = 0; f0 < n_frames; f0 += Fc) {
+    const int F = n_frames - f0 < Fc ? n_frames - f0 : Fc;
+    AnalysisArgs A{};
+    A.st = b->st; A.tab = b->tab; A.half_window = b->half_window;
+    A.n_streams = B; A.n_frames = F; A.frame0 = f0; A.total_frames = n_frames;
+    A.pcm16 = d16; A.pcmf = df; A.features = d_features;
+    A.P = static_cast<float *>(b->work);
+    A.S = A.P + (((size_t)B * (kOverlap + F * kFrame) + 63) & ~size_t(63));
+    A.fft_scratch = A.S + (((size_t)B * (1 + F * kFrame) + 63) & ~size_t(63));
+    const size_t np = (size_t)B * (kOverlap + F * kFrame);
+    preemph_kernel<<<(unsigned)((np + 255) / 256 > 65535 * 16 ? 65535 * 16 : (np + 255) / 256), 256, 0, b->stream>>>(A);
+    spectral_kernel<<<(B * F + lpc_threads - 1) / lpc_threads, lpc_threads, 0, b->stream>>>(A);
+    const size_t nr = (size_t)B * F * kFrame;
+    residual_kernel<<<(unsigned)((nr + 255) / 256 > 65535 * 16 ? 65535 * 16 : (nr + 255) / 256), 256, 0, b->stream>>>(A);
+    pitch_kernel<<<B, kPT, pitch_smem(F), b->stream>>>(A);
+    b->launches += 4;
+    CKA(cudaGetLastError());
+  }
+  return 0;
+}
+
+int analysis_host(LPCNetFeatureBatch *b, const short *p16, const float *pf, int n_frames, float *features) {
+  if (!b || (!p16 && !pf) || !features || n_frames < 0) return set_last_error("lpcnet_feature_batch_compute: bad arguments");
+  if (n_frames == 0) return 0;
+  const size_t ns = (size_t)b->n_streams * n_frames * kFrame, nf = (size_t)b->n_streams * n_frames * kNF;
+  CKA(cudaSetDevice(b->device));
+  if (grow_buf(&b->d_pcm, &b->d_pcm_bytes, ns * (p16 ? 2 : 4))) return -1;
+  if (grow_buf(&b->d_feat, &b->d_feat_bytes, nf * 4)) return -1;
+  CKA(cudaMemcpyAsync(b->d_pcm, p16 ? (const void *)p16 : (const void *)pf, ns * (p16 ? 2 : 4), cudaMemcpyHostToDevice, b->stream));
+  CKA(cudaMemsetAsync(b->d_feat, 0, nf * 4, b->stream));
+  if (analysis_device(b, p16 ? static_cast<const short *>(b->d_pcm) : nullptr,
+                      p16 ? nullptr : static_cast<const float *>(b->d_pcm), n_frames, static_cast<float *>(b->d_feat)))
+    return -1;
+  CKA(cudaMemcpyAsync(features, b->d_feat, nf * 4, cudaMemcpyDeviceToHost, b->stream));
+  CKA(cudaStreamSynchronize(b->stream));
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+LPCNetFeatureBatch *lpcnet_feature_batch_create(int n_streams, int device) {
+  if (n_streams <= 0) { set_last_error("lpcnet_feature_batch_create: n_streams must be positive"); return nullptr; }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+    set_last_error("lpcnet_feature_batch_create: no such CUDA device (there is no CPU fallback)");
+    return nullptr;
+  }
+  LPCNetFeatureBatch *b = new (std::nothrow) LPCNetFeatureBatch();
+  if (!b) return nullptr;
+  b->device = device; b->n_streams = n_streams;
+  auto bail = [&](const char *what, cudaError_t e) -> LPCNetFeatureBatch * {
+    set_last_error(std::string(what) + ": " + cudaGetErrorString(e));
+    lpcnet_feature_batch_destroy(b);
+    return nullptr;
+  };
+  cudaError_t e;
+  if ((e = cudaSetDevice(device)) != cudaSuccess) return bail("cudaSetDevice", e);
+  if ((e = cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+  // tables: kiss_fft twiddles / bit reversal, DCT, and the analysis half-window (dump_lpcnet_tables.c:83-84)
+  std::vector<float> tw, dct, hw(kOverlap);
+  std::vector<int16_t> br;
+  host_dsp_tables(tw, br, dct);
+  for (int i = 0; i < kOverlap; i++)
+    hw[i] = (float)sin(.5 * M_PI * sin(.5 * M_PI * (i + .5) / kOverlap) * sin(.5 * M_PI * (i + .5) / kOverlap));
+  const size_t o_tw = 0, o_dct = o_tw + tw.size() * 4, o_hw = o_dct + dct.size() * 4, o_br = o_hw + hw.size() * 4;
+  if ((e = cudaMalloc(&b->tab_alloc, o_br + br.size() * 2)) != cudaSuccess) return bail("cudaMalloc(tables)", e);
+  char *tp = static_cast<char *>(b->tab_alloc);
+  cudaMemcpy(tp + o_tw, tw.data(), tw.size() * 4, cudaMemcpyHostToDevice);
+  cudaMemcpy(tp + o_dct, dct.data(), dct.size() * 4, cudaMemcpyHostToDevice);
+  cudaMemcpy(tp + o_hw, hw.data(), hw.size() * 4, cudaMemcpyHostToDevice);
+  if ((e = cudaMemcpy(tp + o_br, br.data(), br.size() * 2, cudaMemcpyHostToDevice)) != cudaSuccess) return bail("cudaMemcpy(tables)", e);
+  b->tab = DspTables{(const float *)(tp + o_tw), (const int16_t *)(tp + o_br), (const float *)(tp + o_dct)};
+  b->half_window = (const float *)(tp + o_hw);
+  // stream state, zero = lpcnet_encoder_init (lpcnet_enc.c:471-475; exc_mem is encoder-only)
+  const size_t B = n_streams;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t r = off; off += (bytes + 255) & ~size_t(255); return r; };
+  const size_t o_p = take(B * kOverlap * 4), o_m = take(B * 4), o_s = take(B * 4), o_e = take(B * kPMax * 4),
+               o_pa = take(B * kPMax * 4), o_al = take(B * 4), o_bi = take(B * 4);
+  if ((e = cudaMalloc(&b->st_alloc, off)) != cudaSuccess) return bail("cudaMalloc(state)", e);
+  b->st_bytes = off;
+  if ((e = cudaMemset(b->st_alloc, 0, off)) != cudaSuccess) return bail("cudaMemset(state)", e);
+  char *p = static_cast<char *>(b->st_alloc);
+  b->st.p_hist = (float *)(p + o_p); b->st.mem_preemph = (float *)(p + o_m); b->st.s_last = (float *)(p + o_s);
+  b->st.e_hist = (float *)(p + o_e); b->st.path = (float *)(p + o_pa); b->st.path_all = (float *)(p + o_al);
+  b->st.best_i = (int *)(p + o_bi);
+  return b;
+}
+
+void lpcnet_feature_batch_destroy(LPCNetFeatureBatch *b) {
+  if (!b) return;
+  cudaSetDevice(b->device);
+  if (b->stream) { cudaStreamSynchronize(b->stream); cudaStreamDestroy(b->stream); }
+  cudaFree(b->st_alloc); cudaFree(b->tab_alloc); cudaFree(b->work); cudaFree(b->d_pcm); cudaFree(b->d_feat);
+  delete b;
+}
+
+int lpcnet_feature_batch_n_streams(const LPCNetFeatureBatch *b) { return b ? b->n_streams : 0; }
+long long lpcnet_feature_batch_launch_count(const LPCNetFeatureBatch *b) { return b ? b->launches : 0; }
+
+int lpcnet_feature_batch_reset(LPCNetFeatureBatch *b, int stream) {
+  if (!b || stream < -1 || stream >= b->n_streams) return set_last_error("lpcnet_feature_batch_reset: bad arguments");
+  CKA(cudaSetDevice(b->device));
+  if (stream < 0) {
+    CKA(cudaMemsetAsync(b->st_alloc, 0, b->st_bytes, b->stream));
+  } else {
+    const size_t s = stream;
+    CKA(cudaMemsetAsync(b->st.p_hist + s * kOverlap, 0, kOverlap * 4, b->stream));
+    CKA(cudaMemsetAsync(b->st.mem_preemph + s, 0, 4, b->stream));
+    CKA(cudaMemsetAsync(b->st.s_last + s, 0, 4, b->stream));
+    CKA(cudaMemsetAsync(b->st.e_hist + s * kPMax, 0, kPMax * 4, b->stream));
+    CKA(cudaMemsetAsync(b->st.path + s * kPMax, 0, kPMax * 4, b->stream));
+    CKA(cudaMemsetAsync(b->st.path_all + s, 0, 4, b->stream));
+    CKA(cudaMemsetAsync(b->st.best_i + s, 0, 4, b->stream));
+  }
+  CKA(cudaStreamSynchronize(b->stream));
+  return 0;
+}
+
+int lpcnet_feature_batch_compute(LPCNetFeatureBatch *b, const short *pcm, int n_frames, float *features) {
+  return analysis_host(b, pcm, nullptr, n_frames, features);
+}
+int lpcnet_feature_batch_compute_float(LPCNetFeatureBatch *b, const float *pcm, int n_frames, float *features) {
+  return analysis_host(b, nullptr, pcm, n_frames, features);
+}
+int lpcnet_feature_batch_compute_device(LPCNetFeatureBatch *b, const short *d_pcm16, const float *d_pcmf, int n_frames,
+                                        float *d_features, void *cuda_stream) {
+  if (!b || (!d_pcm16 && !d_pcmf) || !d_features || n_frames < 0)
+    return set_last_error("lpcnet_feature_batch_compute_device: bad arguments");
+  cudaStream_t keep = b->stream;
+  if (cuda_stream) b->stream = static_cast<cudaStream_t>(cuda_stream);
+  const int r = n_frames ? analysis_device(b, d_pcm16, d_pcmf, n_frames, d_features) : 0;
+  b->stream = keep;
+  return r;
+}
+
+// ---- the reference's encoder-state API for this path (include/lpcnet.h:98-158), one stream -----------------
+struct LPCNetEncState {
+  uint32_t magic;
+  LPCNetFeatureBatch *batch;
+};
+static const uint32_t kEncMagic = 0x4C50454Eu;
+
+int lpcnet_encoder_get_size(void) { return (int)sizeof(LPCNetEncState); }
+
+int lpcnet_encoder_init(LPCNetEncState *st) {
+  if (!st) return -1;
+  st->magic = kEncMagic;
+  st->batch = lpcnet_feature_batch_create(1, 0);
+  return st->batch ? 0 : -1;
+}
+
+LPCNetEncState *lpcnet_encoder_create(void) {
+  LPCNetEncState *st = static_cast<LPCNetEncState *>(calloc(1, sizeof(LPCNetEncState)));
+  if (st) lpcnet_encoder_init(st);
+  return st;
+}
+
+void lpcnet_encoder_destroy(LPCNetEncState *st) {
+  if (!st) return;
+  if (st->magic == kEncMagic) lpcnet_feature_batch_destroy(st->batch);
+  free(st);
+}
+
+int lpcnet_compute_single_frame_features(LPCNetEncState *st, const short *pcm, float *features) {
+  if (!st || st->magic != kEncMagic || !st->batch) return set_last_error("lpcnet_compute_single_frame_features: state not initialised");
+  return lpcnet_feature_batch_compute(st->batch, pcm, 1, features);
+}
+
+int lpcnet_compute_single_frame_features_float(LPCNetEncState *st, const float *pcm, float *features) {
+  if (!st || st->magic != kEncMagic || !st->batch) return set_last_error("lpcnet_compute_single_frame_features_float: state not initialised");
+  return lpcnet_feature_batch_compute_float(st->batch, pcm, 1, features);
+}
+
+}  // extern "C"

@@ -15,11 +15,18 @@
 using namespace lpcb;
 
 namespace {
+thread_local std::string g_err;
+}
+int lpcb::set_last_error(const std::string &msg) {
+  g_err = msg;
+  return -1;
+}
+
+namespace {
 
 #ifdef LPCB_PHASE_CLOCKS
 unsigned long long *g_phase_clk = nullptr;
 #endif
-thread_local std::string g_err;
 thread_local std::string g_err_ret;
 std::mutex g_cfg_mu;
 bool g_have_rcp = false;
@@ -27,10 +34,7 @@ uint32_t g_rcp[2048];
 int g_default_delay = 2;
 float g_default_gamma = 1.0f;
 
-int fail(const std::string &msg) {
-  g_err = msg;
-  return -1;
-}
+int fail(const std::string &msg) { return lpcb::set_last_error(msg); }
 int fail_cuda(const char *what, cudaError_t e) { return fail(std::string(what) + ": " + cudaGetErrorString(e)); }
 
 #define CK(call)                                        \

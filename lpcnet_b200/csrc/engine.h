@@ -138,7 +138,11 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
 void free_model(Model &m);
 bool install_codebooks(Model &m, const float *cb, int n, std::string &err);
 
+// Latches the thread's error text (lpcnet_b200_last_error) and returns -1.
+int set_last_error(const std::string &msg);
+
 void default_rcp_table(uint32_t *tab);
+void host_dsp_tables(std::vector<float> &tw, std::vector<int16_t> &br, std::vector<float> &dct);
 
 // Per-chunk scratch: conditioning for F frames.
 struct FrameBuffers {

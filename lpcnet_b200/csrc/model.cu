@@ -244,6 +244,38 @@ void free_model(Model &m) {
   m.dev_blob = nullptr;
 }
 
+// kiss_fft tables for nfft = 320 (src/kiss_fft.c:409-424, 312-345; factors {5,64,4,16,4,4,4,1}
+// src/lpcnet_tables.c:197-205) and the 18x18 DCT (src/dump_lpcnet_tables.c:83-99).
+void host_dsp_tables(std::vector<float> &tw, std::vector<int16_t> &br, std::vector<float> &dct) {
+  tw.assign(640, 0.f);
+  for (int i = 0; i < 320; i++) {
+    const double pi = 3.14159265358979323846264338327;
+    double phase = (-2 * pi / 320) * i;
+    tw[2 * i] = (float)cos(phase);
+    tw[2 * i + 1] = (float)sin(phase);
+  }
+  static const int factors[8] = {5, 64, 4, 16, 4, 4, 4, 1};
+  br.assign(320, 0);
+  struct Rec {
+    static void go(int Fout, int16_t *f, int fstride, const int *fac) {
+      int p = *fac++, mm = *fac++;
+      if (mm == 1) {
+        for (int j = 0; j < p; j++) { *f = (int16_t)(Fout + j); f += fstride; }
+      } else {
+        for (int j = 0; j < p; j++) { go(Fout, f, fstride * p, fac); f += fstride; Fout += mm; }
+      }
+    }
+  };
+  Rec::go(0, br.data(), 1, factors);
+  dct.assign(18 * 18, 0.f);
+  for (int i = 0; i < 18; i++)
+    for (int j = 0; j < 18; j++) {
+      float v = (float)cos((i + .5) * j * M_PI / 18);
+      if (j == 0) v = (float)((double)v * sqrt(.5));
+      dct[i * 18 + j] = v;
+    }
+}
+
 bool load_model(Model &m, const unsigned char *blob, int len, int features_delay, float lpc_gamma,
                 const uint32_t *rcp_tab, std::string &err) {
   if (features_delay < 0 || features_delay > kMaxDelay) { err = "features_delay must be 0..2"; return false; }
@@ -391,38 +423,12 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
   }
   put(reinterpret_cast<const void **>(&d.ulaw2lin_tab), u2l, sizeof(u2l));
   put(reinterpret_cast<const void **>(&d.logit_tab), logit, sizeof(logit));
-  // kiss_fft tables for nfft = 320 (src/kiss_fft.c:409-424, 312-345; factors {5,64,4,16,4,4,4,1}
-  // src/lpcnet_tables.c:197-205) and the 18x18 DCT (src/dump_lpcnet_tables.c:83-99).
   {
-    std::vector<float> tw(640);
-    for (int i = 0; i < 320; i++) {
-      const double pi = 3.14159265358979323846264338327;
-      double phase = (-2 * pi / 320) * i;
-      tw[2 * i] = (float)cos(phase);
-      tw[2 * i + 1] = (float)sin(phase);
-    }
+    std::vector<float> tw, dct;
+    std::vector<int16_t> br;
+    host_dsp_tables(tw, br, dct);
     put(reinterpret_cast<const void **>(&d.fft_tw), tw.data(), tw.size() * 4);
-    static const int factors[8] = {5, 64, 4, 16, 4, 4, 4, 1};
-    std::vector<int16_t> br(320);
-    struct Rec {
-      static void go(int Fout, int16_t *f, int fstride, const int *fac) {
-        int p = *fac++, mm = *fac++;
-        if (mm == 1) {
-          for (int j = 0; j < p; j++) { *f = (int16_t)(Fout + j); f += fstride; }
-        } else {
-          for (int j = 0; j < p; j++) { go(Fout, f, fstride * p, fac); f += fstride; Fout += mm; }
-        }
-      }
-    };
-    Rec::go(0, br.data(), 1, factors);
     put(reinterpret_cast<const void **>(&d.fft_bitrev), br.data(), br.size() * 2);
-    std::vector<float> dct(18 * 18);
-    for (int i = 0; i < 18; i++)
-      for (int j = 0; j < 18; j++) {
-        float v = (float)cos((i + .5) * j * M_PI / 18);
-        if (j == 0) v = (float)((double)v * sqrt(.5));
-        dct[i * 18 + j] = v;
-      }
     put(reinterpret_cast<const void **>(&d.dct), dct.data(), dct.size() * 4);
   }
   // optional VQ codebooks carried in the blob under their C names (src/lpcnet_private.h:109-112)

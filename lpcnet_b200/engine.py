@@ -44,6 +44,11 @@ EXPORTED_SYMBOLS = [
     "lpcnet_batch_set_profiling", "lpcnet_batch_read_profile", "lpcnet_batch_profile_launches", "lpcnet_b200_measure_l2_gather",
     "lpcnet_b200_set_rcp_table", "lpcnet_b200_default_rcp_table", "lpcnet_b200_set_model_constants",
     "lpcnet_b200_last_error", "lpcnet_b200_device_count",
+    "lpcnet_encoder_get_size", "lpcnet_encoder_init", "lpcnet_encoder_create", "lpcnet_encoder_destroy",
+    "lpcnet_compute_single_frame_features", "lpcnet_compute_single_frame_features_float",
+    "lpcnet_feature_batch_create", "lpcnet_feature_batch_destroy", "lpcnet_feature_batch_n_streams",
+    "lpcnet_feature_batch_launch_count", "lpcnet_feature_batch_reset", "lpcnet_feature_batch_compute",
+    "lpcnet_feature_batch_compute_float", "lpcnet_feature_batch_compute_device",
 ]
 
 _lib = None
@@ -104,6 +109,20 @@ def load_library() -> C.CDLL:
     L.lpcnet_decoder_destroy.argtypes = [vp]
     L.lpcnet_decoder_load_model.argtypes = [vp, vp, ci]
     L.lpcnet_decode.argtypes = [vp, vp, vp]
+    L.lpcnet_encoder_create.restype = vp
+    L.lpcnet_encoder_destroy.argtypes = [vp]
+    L.lpcnet_compute_single_frame_features.argtypes = [vp, vp, vp]
+    L.lpcnet_compute_single_frame_features_float.argtypes = [vp, vp, vp]
+    L.lpcnet_feature_batch_create.restype = vp
+    L.lpcnet_feature_batch_create.argtypes = [ci, ci]
+    L.lpcnet_feature_batch_destroy.argtypes = [vp]
+    L.lpcnet_feature_batch_n_streams.argtypes = [vp]
+    L.lpcnet_feature_batch_launch_count.restype = C.c_longlong
+    L.lpcnet_feature_batch_launch_count.argtypes = [vp]
+    L.lpcnet_feature_batch_reset.argtypes = [vp, ci]
+    L.lpcnet_feature_batch_compute.argtypes = [vp, vp, ci, vp]
+    L.lpcnet_feature_batch_compute_float.argtypes = [vp, vp, ci, vp]
+    L.lpcnet_feature_batch_compute_device.argtypes = [vp, vp, vp, ci, vp, vp]
     _lib = L
     return L
 
@@ -351,3 +370,81 @@ class Decoder:
         buf = np.frombuffer(packet, np.uint8)
         _check(self.L.lpcnet_decode(self.h, _p(buf), _p(pcm)), "lpcnet_decode")
         return pcm
+
+
+class FeatureBatch:
+    """Batched per-frame feature analysis (lpcnet_compute_single_frame_features for n_streams states at once)."""
+
+    def __init__(self, n_streams: int, device: int = 0):
+        self.L = load_library()
+        self.n_streams = n_streams
+        self.h = self.L.lpcnet_feature_batch_create(n_streams, device)
+        if not self.h:
+            raise LPCNetError(f"lpcnet_feature_batch_create: {last_error()}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.lpcnet_feature_batch_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def reset(self, stream: int = -1):
+        _check(self.L.lpcnet_feature_batch_reset(self.h, stream), "lpcnet_feature_batch_reset")
+
+    @property
+    def launch_count(self):
+        return int(self.L.lpcnet_feature_batch_launch_count(self.h))
+
+    def compute(self, pcm):
+        """pcm: [n_streams][n_frames*160] int16 or float32 -> features [n_streams][n_frames][36] float32."""
+        pcm = np.asarray(pcm)
+        assert pcm.ndim == 2 and pcm.shape[0] == self.n_streams and pcm.shape[1] % FRAME_SIZE == 0
+        n_frames = pcm.shape[1] // FRAME_SIZE
+        out = np.zeros((self.n_streams, n_frames, NB_TOTAL_FEATURES), np.float32)
+        if pcm.dtype == np.int16:
+            x = np.ascontiguousarray(pcm)
+            _check(self.L.lpcnet_feature_batch_compute(self.h, _p(x), n_frames, _p(out)), "lpcnet_feature_batch_compute")
+        else:
+            x = np.ascontiguousarray(pcm, np.float32)
+            _check(self.L.lpcnet_feature_batch_compute_float(self.h, _p(x), n_frames, _p(out)),
+                   "lpcnet_feature_batch_compute_float")
+        return out
+
+    def compute_device(self, d_pcm16: int, d_pcmf: int, n_frames: int, d_features: int, cuda_stream: int = 0):
+        _check(self.L.lpcnet_feature_batch_compute_device(self.h, d_pcm16 or None, d_pcmf or None, n_frames,
+                                                          d_features, cuda_stream or None),
+               "lpcnet_feature_batch_compute_device")
+
+
+class Encoder:
+    """lpcnet_encoder_create + lpcnet_compute_single_frame_features[_float] (include/lpcnet.h:98-158)."""
+
+    def __init__(self):
+        self.L = load_library()
+        self.h = self.L.lpcnet_encoder_create()
+        if not self.h:
+            raise LPCNetError("lpcnet_encoder_create failed")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.lpcnet_encoder_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def single_frame_features(self, pcm):
+        pcm = np.asarray(pcm)
+        assert pcm.size == FRAME_SIZE
+        out = np.zeros(NB_TOTAL_FEATURES, np.float32)
+        if pcm.dtype == np.int16:
+            x = np.ascontiguousarray(pcm)
+            _check(self.L.lpcnet_compute_single_frame_features(self.h, _p(x), _p(out)),
+                   "lpcnet_compute_single_frame_features")
+        else:
+            x = np.ascontiguousarray(pcm, np.float32)
+            _check(self.L.lpcnet_compute_single_frame_features_float(self.h, _p(x), _p(out)),
+                   "lpcnet_compute_single_frame_features_float")
+        return out

@@ -99,6 +99,13 @@ void orc_fft_tables(float *twiddles /*[320][2]*/, int16_t *bitrev /*[320]*/, flo
 void orc_decode_packet(float *features /*[4][36]*/, float *vq_mem /*[18]*/, const unsigned char *buf,
                        const float *codebooks /*cb1|cb2|cb3|diff4*/);
 
+/* Feature analysis (lpcnet_compute_single_frame_features, src/lpcnet_enc.c:913-933): 160 samples -> 36 features */
+typedef struct OrcEncState OrcEncState;
+OrcEncState *orc_enc_new(void);
+void orc_enc_free(OrcEncState *s);
+void orc_enc_single_frame(OrcEncState *s, const float *pcm /*[160]*/, float *features /*[36]*/);
+const float *orc_half_window(void);   /* [160] */
+
 #ifdef __cplusplus
 }
 #endif

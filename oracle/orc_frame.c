@@ -36,7 +36,7 @@ void orc_conv1d(const OrcConv *l, float *out, float *mem, const float *in) {
  * Tables as dump_lpcnet_tables.c:58-99 generates them (lpcnet_tables.c stores them with
  * %#0.9g, which round-trips binary32): twiddles from kiss_fft.c:409-424, bit-reversal
  * from kiss_fft.c:312-345, factors {5,64, 4,16, 4,4, 4,1} from kf_factor (351-405). */
-typedef struct { float r, i; } cpx;
+typedef OrcCpx cpx;
 static cpx g_tw[320];
 static int16_t g_bitrev[320];
 static float g_dct[18 * 18];
@@ -70,6 +70,8 @@ static void init_tables(void) {
     }
   g_tables = 1;
 }
+
+const float *orc_dct_table(void) { init_tables(); return g_dct; }
 
 void orc_fft_tables(float *tw, int16_t *br, float *dct) {
   init_tables();
@@ -168,7 +170,7 @@ static void bfly5(cpx *Fout, int fstride, int m, int N, int mm) {
 }
 
 /* opus_fft_c + opus_fft_impl (kiss_fft.c:518-585) for the fixed factorisation */
-static void fft320(const cpx *fin, cpx *fout) {
+void orc_fft320(const cpx *fin, cpx *fout) {
   int fstride[5], i, L = 4, m, m2;
   const float scale = 1.f / 320;
   init_tables();
@@ -188,7 +190,7 @@ static void fft320(const cpx *fin, cpx *fout) {
 }
 
 /* lpcn_lpc (freq.c:86-127), float build: MULT32_32_Q31 = *, SHR32/SHL32 = identity */
-static void levinson(float *lpc, const float *ac, int p) {
+void orc_levinson(float *lpc, const float *ac, int p) {
   int i, j;
   float r, error = ac[0];
   memset(lpc, 0, p * sizeof(float));
@@ -240,12 +242,12 @@ void orc_lpc_from_cepstrum(float *lpc, const float *cepstrum) {
   Xr[160] = 0;
   for (i = 0; i < 161; i++) { x[i].r = Xr[i]; x[i].i = 0; }
   for (; i < 320; i++) { x[i].r = x[320 - i].r; x[i].i = -x[320 - i].i; }
-  fft320(x, y);
+  orc_fft320(x, y);
   ac[0] = (float)320 * y[0].r;
   for (i = 1; i < 17; i++) ac[i] = (float)320 * y[320 - i].r;
   ac[0] = (float)((double)ac[0] + ((double)ac[0] * 1e-4 + 320 / 12 / 38.));
   for (i = 1; i < 17; i++) ac[i] = (float)((double)ac[i] * (1 - 6e-5 * i * i));
-  levinson(lpc, ac, 16);
+  orc_levinson(lpc, ac, 16);
 }
 
 /* run_frame_network (lpcnet.c:82-120) */

@@ -43,6 +43,10 @@ struct OrcState {
   float lpc[ORC_LPC_ORDER];
 };
 
+typedef struct { float r, i; } OrcCpx;
+void orc_fft320(const OrcCpx *fin, OrcCpx *fout);            /* opus_fft_c, nfft = 320, scale 1/320 */
+void orc_levinson(float *lpc, const float *ac, int p);
+const float *orc_dct_table(void);
 void orc_vec_act(float *y, const float *x, int n, int act);
 void orc_dense(const OrcDense *l, float *out, const float *in);
 void orc_conv1d(const OrcConv *l, float *out, float *mem, const float *in);

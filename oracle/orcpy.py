@@ -184,3 +184,33 @@ class OrcStream:
         s = np.zeros(1, SNAP_DTYPE)
         s[0] = snap
         self.L.lib.orc_set(self.h, _p(s))
+
+
+class OrcEncoder:
+    """Feature analysis oracle (orc_analysis.c): lpcnet_compute_single_frame_features of one stream."""
+
+    def __init__(self, lib: OrcLib):
+        self.L = lib
+        lib.lib.orc_enc_new.restype = C.c_void_p
+        lib.lib.orc_enc_free.argtypes = [C.c_void_p]
+        lib.lib.orc_enc_single_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        self.h = lib.lib.orc_enc_new()
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.lib.orc_enc_free(self.h)
+            self.h = None
+
+    def run(self, pcm):
+        """pcm: [n_frames*160] (int16 or float) -> [n_frames][36]"""
+        x = np.ascontiguousarray(pcm, np.float32)
+        n = x.size // 160
+        out = np.zeros((n, 36), np.float32)
+        for f in range(n):
+            self.L.lib.orc_enc_single_frame(self.h, _p(x[f * 160:(f + 1) * 160]), _p(out[f]))
+        return out
+
+
+def half_window(lib: OrcLib):
+    lib.lib.orc_half_window.restype = C.POINTER(C.c_float)
+    return np.ctypeslib.as_array(lib.lib.orc_half_window(), (160,)).copy()

@@ -169,3 +169,38 @@ class RefStream:
         t = np.zeros(256, np.float32)
         self.L.lib.ref_sampling_logit_table(self.h, _p(t))
         return t
+
+
+class RefEncoder:
+    """The reference's own LPCNetEncState (lpcnet_encoder_create, lpcnet_compute_single_frame_features[_float])."""
+
+    def __init__(self, lib: RefLib):
+        self.L = lib
+        L = lib.lib
+        L.lpcnet_encoder_create.restype = C.c_void_p
+        L.lpcnet_encoder_destroy.argtypes = [C.c_void_p]
+        L.lpcnet_compute_single_frame_features.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.lpcnet_compute_single_frame_features_float.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        self.h = L.lpcnet_encoder_create()
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.lib.lpcnet_encoder_destroy(self.h)
+            self.h = None
+
+    def run(self, pcm):
+        pcm = np.asarray(pcm)
+        n = pcm.size // 160
+        out = np.zeros((n, 36), np.float32)
+        for f in range(n):
+            if pcm.dtype == np.int16:
+                x = np.ascontiguousarray(pcm[f * 160:(f + 1) * 160])
+                self.L.lib.lpcnet_compute_single_frame_features(self.h, _p(x), _p(out[f]))
+            else:
+                x = np.ascontiguousarray(pcm[f * 160:(f + 1) * 160], np.float32)
+                self.L.lib.lpcnet_compute_single_frame_features_float(self.h, _p(x), _p(out[f]))
+        return out
+
+
+def ref_half_window(lib: RefLib):
+    return np.ctypeslib.as_array((C.c_float * 160).in_dll(lib.lib, "half_window")).copy()

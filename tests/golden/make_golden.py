@@ -119,10 +119,28 @@ def decode(R):
     np.savez_compressed(os.path.join(OUT, "decode.npz"), packets=pk, features=np.stack(feats))
 
 
+def analysis_signals():
+    """The inputs of analysis.npz (tests/test_analysis_oracle.py rebuilds and compares them)."""
+    sig = [blob.synthetic_pcm(40, s) for s in range(4)]
+    sig.append(np.zeros(40 * 160, np.int16))                                       # silence
+    sig.append(np.random.default_rng(9).integers(-32768, 32767, 40 * 160).astype(np.int16))   # full-scale noise
+    x = blob.synthetic_pcm(40, 7).copy()
+    x[1600:3200] = 0                                                               # a gap: the energy floor path
+    sig.append(x)
+    return sig
+
+
+def analysis(R):
+    """lpcnet_compute_single_frame_features of the reference on 7 signals x 40 frames."""
+    sig = analysis_signals()
+    feats = [refpy.RefEncoder(R).run(x) for x in sig]
+    np.savez_compressed(os.path.join(OUT, "analysis.npz"), pcm=np.stack(sig), features=np.stack(feats))
+
+
 if __name__ == "__main__":
     R = refpy.RefLib(2)
-    prims(R)
-    synth(R)
-    decode(R)
+    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis"]
+    for name in which:
+        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis}[name](R)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
