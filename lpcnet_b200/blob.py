@@ -185,6 +185,43 @@ def random_model(seed: int = 1234, N: int = 384, NB: int = 16, C: int = 128,
     return A
 
 
+def random_plc_model(seed: int = 4321, cond: int = 128, units: int = 256, sigma: float = 0.1,
+                     qmax_in: int = 12, qmax_rec: int = 8) -> "OrderedDict[str, np.ndarray]":
+    """Random-init PLC predictor in the reference's array layout (training_tf2/dump_plc.py:160-208, 331-368;
+    src/lpcnet_plc.c:135-145): dense 57 -> cond (tanh), GRU cond -> units, GRU units -> units (both int8, the
+    input matrix in the block-sparse stream format with every block present, the recurrent one in the dense
+    8x4 layout), dense units -> 20 (linear).  Append to a model dict before write_blob: lpcnet_plc_load_model
+    reads both models from one blob (src/lpcnet_plc.c:88-98)."""
+    rng = np.random.default_rng(seed)
+    f32 = np.float32
+    A: "OrderedDict[str, np.ndarray]" = OrderedDict()
+
+    def normal(shape, s=sigma):
+        return (rng.standard_normal(shape) * s).astype(f32)
+
+    A["plc_dense1_weights"] = normal((57, cond))
+    A["plc_dense1_bias"] = normal((cond,))
+    for name, nin in (("plc_gru1", cond), ("plc_gru2", units)):
+        q = rng.integers(-qmax_in, qmax_in + 1, size=(nin, 3 * units)).astype(np.int32)
+        mask = np.ones((nin // 4, 3 * units // 8), bool)
+        wq, idx = block_sparse_encode(q, mask)
+        A[f"{name}_weights"] = wq
+        A[f"{name}_weights_idx"] = idx
+        q2 = rng.integers(-qmax_rec, qmax_rec + 1, size=(units, 3 * units)).astype(np.int32)
+        A[f"{name}_recurrent_weights"] = dotp_layout(q2)
+        bias = normal((2, 3 * units))
+        A[f"{name}_bias"] = bias.reshape(-1)
+        sub = bias.astype(np.float64).copy()
+        sub[0] -= q.sum(axis=0) * (1.0 / 128.0)
+        sub[1] -= q2.sum(axis=0) * (1.0 / 128.0)
+        A[f"{name}_subias"] = sub.astype(f32).reshape(-1)
+    A["plc_out_weights"] = normal((units, 20), 0.05)
+    A["plc_out_bias"] = np.concatenate([[1.0], np.zeros(17), [0.3, 0.0]]).astype(f32) + normal((20,), 0.02)
+    for k in list(A.keys()):
+        A[k] = np.ascontiguousarray(A[k]).reshape(-1)
+    return A
+
+
 def saturation_free(wq: np.ndarray) -> bool:
     """True if no adjacent input pair of any block row can saturate vpmaddubsw's s16:
     255*(|q0|+|q1|) <= 32767, i.e. |q0|+|q1| <= 128."""
@@ -222,3 +259,16 @@ def synthetic_pcm(n_frames: int, stream: int = 0) -> np.ndarray:
     x += 600 * np.convolve(noise, np.ones(8) / 8, mode="valid")[:n] + 100 * noise[:n]
     env = 0.55 + 0.45 * np.sin(2 * np.pi * 1.3 / 16000 * t + 6 * rng.random())
     return np.clip(np.round(x * env), -32768, 32767).astype(np.int16)
+
+
+def synthetic_loss_pattern(n_frames: int, stream: int = 0, p_stay: float = 0.6, p_enter: float = 0.1) -> np.ndarray:
+    """Two-state Gilbert loss pattern per 10 ms frame, seed 7 + stream; the first three
+    frames are always received.  bool [n_frames]."""
+    rng = np.random.default_rng(7 + stream)
+    lost = np.zeros(n_frames, bool)
+    state = False
+    for f in range(n_frames):
+        state = bool(rng.random() < (p_stay if state else p_enter))
+        lost[f] = state
+    lost[:3] = False
+    return lost

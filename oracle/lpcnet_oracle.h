@@ -105,6 +105,19 @@ OrcEncState *orc_enc_new(void);
 void orc_enc_free(OrcEncState *s);
 void orc_enc_single_frame(OrcEncState *s, const float *pcm /*[160]*/, float *features /*[36]*/);
 const float *orc_half_window(void);   /* [160] */
+/* burg_cepstral_analysis (src/freq.c:188-199): 160 samples -> 2 x 18 Burg cepstra (mean, difference) */
+void orc_burg_cepstral_analysis(float *ceps /*[36]*/, const float *x /*[160]*/);
+
+/* Packet-loss concealment, non-causal mode (src/lpcnet_plc.c:349-491); the model must carry the plc_* arrays and
+ * be loaded with features_delay 0.  options: 1 (LPCNET_PLC_NONCAUSAL) | 4 (LPCNET_PLC_DC_FILTER). */
+typedef struct OrcPLC OrcPLC;
+OrcPLC *orc_plc_new(const OrcModel *m, int options);
+void orc_plc_free(OrcPLC *p);
+void orc_plc_seed(OrcPLC *p, const unsigned char *data, int n);
+int orc_plc_update(OrcPLC *p, int16_t *pcm /*[160] in/out*/);
+int orc_plc_conceal(OrcPLC *p, int16_t *pcm /*[160] out*/);
+void orc_plc_pred(const OrcModel *m, float *gru1 /*[256]*/, float *gru2 /*[256]*/, float *out /*[20]*/, const float *in /*[57]*/);
+void orc_plc_peek(const OrcPLC *p, float *features20, float *gru1, float *gru2, int *loss_count, double *dc /*[2]*/);
 
 #ifdef __cplusplus
 }

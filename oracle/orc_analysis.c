@@ -18,20 +18,6 @@
 
 static const int16_t eband5ms[NBANDS] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 10, 12, 14, 16, 20, 24, 28, 34, 40};
 
-struct OrcEncState {
-  float analysis_mem[OVERLAP];
-  float mem_preemph;
-  float pitch_mem[ORC_LPC_ORDER];
-  float pitch_filt;
-  float xc[2][PMAX + 1];            /* rows 2, 3 of the reference's xc[10]: pcount stays 0 in single-frame mode */
-  float frame_weight[2];
-  float exc_buf[PMAX + 320];
-  float pitch_max_path[2][PMAX];
-  float pitch_max_path_all;
-  int best_i;
-  float lpc[ORC_LPC_ORDER];
-  float features[36];
-};
 
 static float g_half_window[OVERLAP];
 static int g_hw = 0;
@@ -235,4 +221,149 @@ void orc_enc_single_frame(OrcEncState *st, const float *pcm, float *features) {
   frame_features(st, x);
   single_frame_pitch(st);
   memcpy(features, st->features, sizeof(st->features));
+}
+
+/* ---- burg_cepstral_analysis (freq.c:152-199) over silk_burg_analysis (burg.c:97-245) ------------------------ */
+
+/* silk_energy_FLP / silk_inner_product_FLP (burg.c:41-92): 4-way grouped double sums */
+static double inner_flp(const float *a, const float *b, int n) {
+  double r = 0.0;
+  int i;
+  for (i = 0; i < n - 3; i += 4)
+    r += a[i + 0] * (double)b[i + 0] + a[i + 1] * (double)b[i + 1] + a[i + 2] * (double)b[i + 2] + a[i + 3] * (double)b[i + 3];
+  for (; i < n; i++) r += a[i] * (double)b[i];
+  return r;
+}
+
+/* silk_burg_analysis with nb_subfr = 1 (the only use, freq.c:168) */
+static float burg_analysis(float *A, const float *x, float minInvGain, int len, int D) {
+  double C0, invGain, num, nrg_f, nrg_b, rc, Atmp, tmp1, tmp2;
+  double Cf[16], Cl[16], CAf[17], CAb[17], Af[16];
+  int k, n, reached = 0;
+  C0 = inner_flp(x, x, len);
+  memset(Cf, 0, sizeof(Cf));
+  for (n = 1; n < D + 1; n++) Cf[n - 1] += inner_flp(x, x + n, len - n);
+  memcpy(Cl, Cf, sizeof(Cf));
+  CAb[0] = CAf[0] = C0 + 1e-5f * C0 + 1e-9f;
+  invGain = 1.0f;
+  for (n = 0; n < D; n++) {
+    tmp1 = x[n];
+    tmp2 = x[len - n - 1];
+    for (k = 0; k < n; k++) {
+      Cf[k] -= x[n] * x[n - k - 1];                     /* float product */
+      Cl[k] -= x[len - n - 1] * x[len - n + k];
+      Atmp = Af[k];
+      tmp1 += x[n - k - 1] * Atmp;
+      tmp2 += x[len - n + k] * Atmp;
+    }
+    for (k = 0; k <= n; k++) {
+      CAf[k] -= tmp1 * x[n - k];
+      CAb[k] -= tmp2 * x[len - n + k - 1];
+    }
+    tmp1 = Cf[n];
+    tmp2 = Cl[n];
+    for (k = 0; k < n; k++) {
+      Atmp = Af[k];
+      tmp1 += Cl[n - k - 1] * Atmp;
+      tmp2 += Cf[n - k - 1] * Atmp;
+    }
+    CAf[n + 1] = tmp1;
+    CAb[n + 1] = tmp2;
+    num = CAb[n + 1];
+    nrg_b = CAb[0];
+    nrg_f = CAf[0];
+    for (k = 0; k < n; k++) {
+      Atmp = Af[k];
+      num += CAb[n - k] * Atmp;
+      nrg_b += CAb[k + 1] * Atmp;
+      nrg_f += CAf[k + 1] * Atmp;
+    }
+    rc = -2.0 * num / (nrg_f + nrg_b);
+    tmp1 = invGain * (1.0 - rc * rc);
+    if (tmp1 <= minInvGain) {
+      rc = sqrt(1.0 - minInvGain / invGain);
+      if (num > 0) rc = -rc;
+      invGain = minInvGain;
+      reached = 1;
+    } else {
+      invGain = tmp1;
+    }
+    for (k = 0; k < (n + 1) >> 1; k++) {
+      tmp1 = Af[k];
+      tmp2 = Af[n - k - 1];
+      Af[k] = tmp1 + rc * tmp2;
+      Af[n - k - 1] = tmp2 + rc * tmp1;
+    }
+    Af[n] = rc;
+    if (reached) {
+      for (k = n + 1; k < D; k++) Af[k] = 0.0;
+      break;
+    }
+    for (k = 0; k <= n + 1; k++) {
+      tmp1 = CAf[k];
+      CAf[k] += rc * CAb[n - k + 1];
+      CAb[n - k + 1] += rc * tmp1;
+    }
+  }
+  if (reached) {
+    for (k = 0; k < D; k++) A[k] = (float)(-Af[k]);
+    C0 -= inner_flp(x, x, D);
+    nrg_f = C0 * invGain;
+  } else {
+    nrg_f = CAf[0];
+    tmp1 = 1.0;
+    for (k = 0; k < D; k++) {
+      Atmp = Af[k];
+      nrg_f += CAf[k + 1] * Atmp;
+      tmp1 += Atmp * Atmp;
+      A[k] = (float)(-Atmp);
+    }
+    nrg_f -= 1e-5f * C0 * tmp1;
+  }
+  return (float)nrg_f;
+}
+
+/* compute_burg_cepstrum (freq.c:152-186) for len = 80, order = 16 */
+static void burg_cepstrum(const float *pcm, float *out) {
+  float burg_in[FRAME], burg_lpc[ORC_LPC_ORDER], x[WINDOW], Eburg[NBANDS], Ly[NBANDS], sum[NBANDS] = {0}, g;
+  OrcCpx X[WINDOW / 2 + 1];
+  const int len = FRAME / 2, order = ORC_LPC_ORDER;
+  int i, j;
+  for (i = 0; i < len - 1; i++) burg_in[i] = pcm[i + 1] - 0.85f * pcm[i];
+  g = burg_analysis(burg_lpc, burg_in, 1e-3, len - 1, order);
+  g /= len - 2 * (order - 1);
+  memset(x, 0, sizeof(x));
+  x[0] = 1;
+  for (i = 0; i < order; i++) x[i + 1] = (float)(-burg_lpc[i] * pow(.995, i + 1));
+  forward_transform(X, x);
+  /* compute_band_energy_inverse (freq.c:59-84) */
+  for (i = 0; i < NBANDS - 1; i++) {
+    int band_size = (eband5ms[i + 1] - eband5ms[i]) * 4;
+    for (j = 0; j < band_size; j++) {
+      float frac = (float)j / band_size;
+      float tmp = X[eband5ms[i] * 4 + j].r * X[eband5ms[i] * 4 + j].r;
+      tmp += X[eband5ms[i] * 4 + j].i * X[eband5ms[i] * 4 + j].i;
+      tmp = (float)(1.f / (tmp + 1e-9));
+      sum[i] += (1 - frac) * tmp;
+      sum[i + 1] += frac * tmp;
+    }
+  }
+  sum[0] *= 2;
+  sum[NBANDS - 1] *= 2;
+  for (i = 0; i < NBANDS; i++) Eburg[i] = (float)(sum[i] * (.45 * g * (1.f / ((float)WINDOW * WINDOW * WINDOW))));
+  log_bands(Ly, Eburg, 0);
+  dct18(out, Ly);
+  out[0] += -4;
+}
+
+/* burg_cepstral_analysis (freq.c:188-199): mean and difference of the two half-frame cepstra */
+void orc_burg_cepstral_analysis(float *ceps /*[36]*/, const float *x /*[160]*/) {
+  int i;
+  burg_cepstrum(x, &ceps[0]);
+  burg_cepstrum(&x[FRAME / 2], &ceps[NBANDS]);
+  for (i = 0; i < NBANDS; i++) {
+    float c0 = ceps[i], c1 = ceps[NBANDS + i];
+    ceps[i] = (float)(.5 * (c0 + c1));
+    ceps[NBANDS + i] = (c0 - c1);
+  }
 }

@@ -27,7 +27,31 @@ struct OrcModel {
   OrcSparseGRU gru_a;
   OrcMDense dual_fc;
   float logit_table[256];
+  /* PLC predictor (plc_data.c stand-in, training_tf2/dump_plc.py), present when the blob carries plc_* arrays */
+  int has_plc;
+  OrcDense plc_dense1, plc_out;
+  OrcGRU plc_gru1, plc_gru2;
 };
+
+/* LPCNetEncState (lpcnet_private.h:55-75), the fields single-frame analysis uses */
+#define PMAX 256
+#define OVERLAP 160
+struct OrcEncState {
+  float analysis_mem[OVERLAP];
+  float mem_preemph;
+  float pitch_mem[ORC_LPC_ORDER];
+  float pitch_filt;
+  float xc[2][PMAX + 1];            /* rows 2, 3 of the reference's xc[10]: pcount stays 0 in single-frame mode */
+  float frame_weight[2];
+  float exc_buf[PMAX + 320];
+  float pitch_max_path[2][PMAX];
+  float pitch_max_path_all;
+  int best_i;
+  float lpc[ORC_LPC_ORDER];
+  float features[36];
+};
+#undef PMAX
+#undef OVERLAP
 
 struct OrcState {
   const OrcModel *m;
@@ -50,6 +74,7 @@ const float *orc_dct_table(void);
 void orc_vec_act(float *y, const float *x, int n, int act);
 void orc_dense(const OrcDense *l, float *out, const float *in);
 void orc_conv1d(const OrcConv *l, float *out, float *mem, const float *in);
+void orc_gru_b(const OrcGRU *g, const float *cond, float *state, const float *input);   /* compute_gruB */
 void orc_sample_tail(const OrcModel *m, OrcState *s, int16_t *out, int N, int preload);
 int orc_sample_network(const OrcModel *m, OrcState *s, int last_exc, int u_sig, int u_pred);
 void orc_all_node_logits(const OrcModel *m, const OrcState *s, float *logits);

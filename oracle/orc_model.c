@@ -70,14 +70,14 @@ static int embed(OrcEmbed *l, const Arr *a, int n, const char *w, int rows, int 
 OrcModel *orc_model_load(const unsigned char *blob, int len, int features_delay, float lpc_gamma,
                          const uint32_t *rcp_table) {
   enum { N = 384, NB = 16, C = 128 };
-  Arr arr[128];
+  Arr arr[192];
   int n, i, bad = 0;
   OrcModel *m;
   if (features_delay < 0 || features_delay > ORC_MAX_DELAY) return NULL;
   m = calloc(1, sizeof(*m));
   m->blob = malloc(len); memcpy(m->blob, blob, len); m->len = len;
   m->features_delay = features_delay; m->lpc_gamma = lpc_gamma;
-  n = parse(m->blob, len, arr, 128);
+  n = parse(m->blob, len, arr, 192);
   if (n < 0) { orc_model_free(m); return NULL; }
   bad |= embed(&m->e_sig, arr, n, "gru_a_embed_sig_weights", 256, 3 * N);
   bad |= embed(&m->e_pred, arr, n, "gru_a_embed_pred_weights", 256, 3 * N);
@@ -112,6 +112,28 @@ OrcModel *orc_model_load(const unsigned char *blob, int len, int features_delay,
   m->gru_a.n = N;
   bad |= !m->gru_a.bias || !m->gru_a.subias || !m->gru_a.diag || !m->gru_a.idx || !m->gru_a.w;
   if (bad) { orc_model_free(m); return NULL; }
+  /* init_plc_model (plc_data.c stand-in, oracle/gen/plc_data.c): optional */
+  if (find(arr, n, "plc_dense1_bias", 128 * 4)) {
+    OrcGRU *gs[2] = {&m->plc_gru1, &m->plc_gru2};
+    const char *nm[2][5] = {{"plc_gru1_bias", "plc_gru1_subias", "plc_gru1_weights_idx", "plc_gru1_weights", "plc_gru1_recurrent_weights"},
+                            {"plc_gru2_bias", "plc_gru2_subias", "plc_gru2_weights_idx", "plc_gru2_weights", "plc_gru2_recurrent_weights"}};
+    const int nin[2] = {128, 256};
+    int k, pbad = 0;
+    pbad |= dense(&m->plc_dense1, arr, n, "plc_dense1_bias", "plc_dense1_weights", 57, 128, ORC_TANH);
+    pbad |= dense(&m->plc_out, arr, n, "plc_out_bias", "plc_out_weights", 256, 20, ORC_LINEAR);
+    for (k = 0; k < 2; k++) {
+      OrcGRU *g = gs[k];
+      g->bias = find(arr, n, nm[k][0], 6 * 256 * 4);
+      g->subias = find(arr, n, nm[k][1], 6 * 256 * 4);
+      g->idx_in = find_idx(arr, n, nm[k][2], nin[k], 3 * 256, &g->nblocks);
+      g->w_in = find(arr, n, nm[k][3], 32 * g->nblocks);
+      g->w_rec = find(arr, n, nm[k][4], 3 * 256 * 256);
+      g->nin = nin[k]; g->n = 256;
+      pbad |= !g->bias || !g->subias || !g->idx_in || !g->w_in || !g->w_rec;
+    }
+    if (pbad) { orc_model_free(m); return NULL; }
+    m->has_plc = 1;
+  }
   /* sampling_logit_table (lpcnet.c:188-191): float prob, double log */
   for (i = 0; i < 256; i++) {
     float prob = .025f + .95f * (float)i / 255.f;

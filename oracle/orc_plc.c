@@ -1,0 +1,203 @@
+/* Oracle: packet-loss concealment, the non-causal mode (LPCNET_PLC_NONCAUSAL, with or without the DC filter):
+ * lpcnet_plc_update_non_causal / lpcnet_plc_conceal_non_causal / process_queued_update / compute_plc_pred /
+ * clear_state (src/lpcnet_plc.c:349-491, 342-347, 135-145, 175-181), for a model built with FEATURES_DELAY 0
+ * (lpcnet_plc.c:357-361).  The FEC queue is left empty (lpcnet_demo -plc_file never fills it), so every
+ * prediction is compute_plc_pred.  TEST INFRASTRUCTURE ONLY.  Compile with -ffp-contract=off. */
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+#include "orc_internal.h"
+
+#define FRAME 160
+#define TOFF 80
+#define NBANDS 18
+#define PLC_IN (2 * NBANDS + ORC_NB_FEATURES + 1)   /* 57 */
+#define DC_CONST 0.003
+
+struct OrcPLC {
+  const OrcModel *m;
+  OrcState lp;
+  OrcEncState enc;
+  int remove_dc;
+  int16_t pcm[TOFF + FRAME];
+  float features[36];
+  int loss_count;
+  float gru1[256], gru2[256];
+  double dc_mem, syn_dc;
+  int16_t dc_buf[TOFF];
+  int queued_update;
+  int16_t queued_samples[FRAME];
+};
+
+
+/* lpcnet_plc_create(options) + lpcnet_plc_load_model: options = 1 (non-causal) | 4 (DC filter) */
+OrcPLC *orc_plc_new(const OrcModel *m, int options) {
+  OrcPLC *p;
+  if (!m->has_plc || (options & 3) != 1 || m->features_delay != 0) return NULL;
+  p = calloc(1, sizeof(*p));
+  p->m = m;
+  p->lp.m = m;
+  orc_state_reset(&p->lp);
+  p->remove_dc = !!(options & 4);
+  return p;
+}
+void orc_plc_free(OrcPLC *p) { free(p); }
+void orc_plc_seed(OrcPLC *p, const unsigned char *d, int n) { orc_kiss99_srand(p->lp.rng, d, n); }
+
+/* compute_plc_pred (lpcnet_plc.c:135-145) */
+void orc_plc_pred(const OrcModel *m, float *gru1, float *gru2, float *out, const float *in) {
+  float zeros[3 * 256] = {0};
+  float dense_out[128];
+  orc_dense(&m->plc_dense1, dense_out, in);
+  orc_gru_b(&m->plc_gru1, zeros, gru1, dense_out);
+  orc_gru_b(&m->plc_gru2, zeros, gru2, gru1);
+  orc_dense(&m->plc_out, out, gru2);
+  out[19] = (.5f < out[19] + .1f) ? .5f : out[19] + .1f;
+}
+
+static void analysis(OrcPLC *p, const int16_t *pcm) {
+  float x[FRAME], f[36];
+  int i;
+  for (i = 0; i < FRAME; i++) x[i] = pcm[i];
+  orc_enc_single_frame(&p->enc, x, f);
+}
+
+static void process_queued_update(OrcPLC *p) {
+  if (p->queued_update) {
+    orc_synthesize(p->m, &p->lp, p->features, p->queued_samples, FRAME, FRAME);
+    p->queued_update = 0;
+  }
+}
+
+static const float att_table[10] = {0, 0, -.2, -.2, -.4, -.4, -.8, -.8, -1.6, -1.6};
+
+static void attenuate(OrcPLC *p) {
+  float v;
+  if (p->loss_count >= 10) v = p->features[0] + att_table[9] - 2 * (p->loss_count - 9);
+  else v = p->features[0] + att_table[p->loss_count];
+  p->features[0] = -10 > v ? -10 : v;
+}
+
+/* lpcnet_plc_update_non_causal (lpcnet_plc.c:349-447) */
+int orc_plc_update(OrcPLC *p, int16_t *pcm) {
+  float x[FRAME], plc_features[PLC_IN];
+  int16_t pcm_save[FRAME], lp[FRAME] = {0};
+  double mem_bak = 0;
+  int delta = (int)p->syn_dc;
+  int i;
+  process_queued_update(p);
+  if (p->remove_dc) {
+    p->dc_mem += p->syn_dc;
+    p->syn_dc = 0;
+    mem_bak = p->dc_mem;
+    for (i = 0; i < FRAME; i++) {
+      lp[i] = (int16_t)(int)floor(.5 + p->dc_mem);
+      p->dc_mem += DC_CONST * (pcm[i] - p->dc_mem);
+      pcm[i] -= lp[i];
+    }
+  }
+  memcpy(pcm_save, pcm, sizeof(pcm_save));
+  for (i = 0; i < FRAME; i++) x[i] = pcm[i];
+  orc_burg_cepstral_analysis(plc_features, x);
+  if (p->loss_count > 0) {
+    OrcState copy;
+    float zeros[PLC_IN] = {0};
+    int16_t rev[FRAME];
+    memcpy(zeros, plc_features, 2 * NBANDS * sizeof(float));
+    zeros[2 * NBANDS + ORC_NB_FEATURES] = 1;
+    orc_plc_pred(p->m, p->gru1, p->gru2, p->features, zeros);
+    copy = p->lp;
+    orc_synthesize(p->m, &p->lp, p->features, &p->pcm[FRAME - TOFF], TOFF, 0);
+    if (p->remove_dc) {
+      for (i = 0; i < FRAME; i++) pcm[i] += lp[i];
+      p->dc_mem = mem_bak;
+      for (i = 0; i < TOFF; i++) p->syn_dc += DC_CONST * (p->pcm[FRAME - TOFF + i] - p->syn_dc);
+      p->dc_mem += p->syn_dc;
+      delta += p->syn_dc;                 /* int += double: converts the sum back to int */
+      p->syn_dc = 0;
+      for (i = 0; i < FRAME; i++) {
+        lp[i] = (int16_t)(int)floor(.5 + p->dc_mem);
+        p->dc_mem += DC_CONST * (pcm[i] - p->dc_mem);
+        pcm[i] -= lp[i];
+      }
+      memcpy(pcm_save, pcm, sizeof(pcm_save));
+    }
+    for (i = 0; i < FRAME; i++) rev[i] = pcm[FRAME - i - 1];
+    /* clear_state (lpcnet_plc.c:175-181) */
+    memset(p->lp.last_sig, 0, sizeof(p->lp.last_sig));
+    p->lp.last_exc = orc_lin2ulaw(0.f);
+    p->lp.deemph_mem = 0;
+    memset(p->lp.gru_a_state, 0, sizeof(p->lp.gru_a_state));
+    memset(p->lp.gru_b_state, 0, sizeof(p->lp.gru_b_state));
+    orc_synthesize(p->m, &p->lp, p->features, rev, FRAME, FRAME);
+    orc_sample_tail(p->m, &p->lp, rev, TOFF, 0);
+    for (i = 0; i < TOFF; i++) {
+      float w = (float)(.5 - .5 * cos(M_PI * i / (TOFF)));
+      p->pcm[FRAME - 1 - i] = (int16_t)(int)floor(.5 + w * p->pcm[FRAME - 1 - i] + (1 - w) * (rev[i] + delta));
+    }
+    p->lp = copy;
+    p->queued_update = 1;
+    memcpy(&p->queued_samples[0], &p->pcm[FRAME - TOFF], TOFF * sizeof(int16_t));
+    memcpy(&p->queued_samples[TOFF], pcm, (FRAME - TOFF) * sizeof(int16_t));
+    analysis(p, p->pcm);
+  }
+  analysis(p, pcm);
+  if (p->loss_count == 0) {
+    memcpy(&plc_features[2 * NBANDS], p->enc.features, ORC_NB_FEATURES * sizeof(float));
+    plc_features[2 * NBANDS + ORC_NB_FEATURES] = 1;
+    orc_plc_pred(p->m, p->gru1, p->gru2, p->features, plc_features);
+    orc_synthesize(p->m, &p->lp, p->enc.features, &p->pcm[FRAME - TOFF], TOFF, TOFF);
+    orc_sample_tail(p->m, &p->lp, pcm, FRAME - TOFF, FRAME - TOFF);
+  }
+  memcpy(&pcm[FRAME - TOFF], pcm, TOFF * sizeof(int16_t));
+  memcpy(pcm, &p->pcm[TOFF], (FRAME - TOFF) * sizeof(int16_t));
+  memcpy(p->pcm, pcm_save, FRAME * sizeof(int16_t));
+  p->loss_count = 0;
+  if (p->remove_dc) {
+    for (i = 0; i < TOFF; i++) pcm[i] += p->dc_buf[i];
+    for (; i < FRAME; i++) pcm[i] += lp[i - TOFF];
+    for (i = 0; i < TOFF; i++) p->dc_buf[i] = lp[FRAME - TOFF + i];
+  }
+  return 0;
+}
+
+/* lpcnet_plc_conceal_non_causal (lpcnet_plc.c:449-491) */
+int orc_plc_conceal(OrcPLC *p, int16_t *pcm) {
+  float zeros[PLC_IN] = {0};
+  int i;
+  process_queued_update(p);
+  orc_plc_pred(p->m, p->gru1, p->gru2, p->features, zeros);
+  attenuate(p);
+  if (p->loss_count == 0) {
+    memcpy(pcm, &p->pcm[FRAME - TOFF], TOFF * sizeof(int16_t));
+    orc_synthesize(p->m, &p->lp, p->features, &p->pcm[FRAME - TOFF], TOFF, TOFF);
+    orc_sample_tail(p->m, &p->lp, &pcm[TOFF], FRAME - TOFF, 0);
+  } else {
+    orc_synthesize(p->m, &p->lp, p->features, pcm, TOFF, 0);
+    orc_sample_tail(p->m, &p->lp, &pcm[TOFF], FRAME - TOFF, 0);
+    memcpy(&p->pcm[FRAME - TOFF], pcm, TOFF * sizeof(int16_t));
+    analysis(p, p->pcm);
+  }
+  memcpy(p->pcm, &pcm[TOFF], (FRAME - TOFF) * sizeof(int16_t));
+  if (p->remove_dc) {
+    int dc = (int)floor(.5 + p->dc_mem);
+    if (p->loss_count == 0) {
+      for (i = TOFF; i < FRAME; i++) p->syn_dc += DC_CONST * (pcm[i] - p->syn_dc);
+    } else {
+      for (i = 0; i < FRAME; i++) p->syn_dc += DC_CONST * (pcm[i] - p->syn_dc);
+    }
+    for (i = 0; i < TOFF; i++) pcm[i] += p->dc_buf[i];
+    for (; i < FRAME; i++) pcm[i] += dc;
+    for (i = 0; i < TOFF; i++) p->dc_buf[i] = (int16_t)dc;
+  }
+  p->loss_count++;
+  return 0;
+}
+
+void orc_plc_peek(const OrcPLC *p, float *features20, float *gru1, float *gru2, int *loss_count, double *dc) {
+  memcpy(features20, p->features, 20 * sizeof(float));
+  memcpy(gru1, p->gru1, sizeof(p->gru1));
+  memcpy(gru2, p->gru2, sizeof(p->gru2));
+  *loss_count = p->loss_count;
+  dc[0] = p->dc_mem; dc[1] = p->syn_dc;
+}

@@ -25,11 +25,10 @@ static void sparse_gru_a(const OrcModel *m, float *state, const float *input) {
   for (i = 0; i < N; i++) state[i] = z[i] * state[i] + ((float)1 - z[i]) * h[i];
 }
 
-/* compute_gruB (nnet.c:326-372), USE_SU_BIAS build */
-static void gru_b(const OrcModel *m, const float *cond, float *state, const float *input) {
-  const OrcGRU *g = &m->gru_b;
-  enum { N = 16 };
-  float zrh[3 * N], recur[3 * N];
+/* compute_gruB (nnet.c:326-372), USE_SU_BIAS build; any size up to 256 units (GRU-B: 16, PLC GRUs: 256) */
+void orc_gru_b(const OrcGRU *g, const float *cond, float *state, const float *input) {
+  const int N = g->n;
+  float zrh[3 * 256], recur[3 * 256];
   float *z = zrh, *r = zrh + N, *h = zrh + 2 * N;
   int i;
   for (i = 0; i < 3 * N; i++) zrh[i] = g->subias[i] + cond[i];
@@ -93,7 +92,7 @@ int orc_sample_network(const OrcModel *m, OrcState *s, int last_exc, int u_sig, 
   const float *e3 = &m->e_exc.w[last_exc * 3 * N];
   for (i = 0; i < 3 * N; i++) gru_a_input[i] = s->gru_a_condition[i] + e1[i] + e2[i] + e3[i];
   sparse_gru_a(m, s->gru_a_state, gru_a_input);
-  gru_b(m, s->gru_b_condition, s->gru_b_state, s->gru_a_state);
+  orc_gru_b(&m->gru_b, s->gru_b_condition, s->gru_b_state, s->gru_a_state);
   return sample_tree(m, s);
 }
 

@@ -214,3 +214,56 @@ class OrcEncoder:
 def half_window(lib: OrcLib):
     lib.lib.orc_half_window.restype = C.POINTER(C.c_float)
     return np.ctypeslib.as_array(lib.lib.orc_half_window(), (160,)).copy()
+
+
+def burg_cepstral_analysis(lib: OrcLib, x):
+    x = np.ascontiguousarray(x, np.float32)
+    out = np.zeros(36, np.float32)
+    lib.lib.orc_burg_cepstral_analysis(_p(out), _p(x))
+    return out
+
+
+def plc_pred(model: OrcModel, gru1, gru2, x):
+    """compute_plc_pred: updates gru1/gru2 (float32[256]) in place, returns the 20 predicted features."""
+    out = np.zeros(20, np.float32)
+    model.L.lib.orc_plc_pred.argtypes = [C.c_void_p] * 5
+    model.L.lib.orc_plc_pred(model.h, _p(gru1), _p(gru2), _p(out), _p(np.ascontiguousarray(x, np.float32)))
+    return out
+
+
+class OrcPLC:
+    """Non-causal packet-loss concealment of one stream (orc_plc.c); model loaded with features_delay=0."""
+
+    def __init__(self, model: OrcModel, options: int = 1, seed: bytes | None = None):
+        self.m = model
+        L = model.L.lib
+        L.orc_plc_new.restype = C.c_void_p
+        L.orc_plc_new.argtypes = [C.c_void_p, C.c_int]
+        L.orc_plc_free.argtypes = [C.c_void_p]
+        L.orc_plc_seed.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+        L.orc_plc_update.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_plc_conceal.argtypes = [C.c_void_p, C.c_void_p]
+        self.h = L.orc_plc_new(model.h, options)
+        if not self.h:
+            raise RuntimeError("orc_plc_new: needs plc_* arrays, features_delay 0 and the non-causal mode")
+        if seed is not None:
+            L.orc_plc_seed(self.h, seed, len(seed))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.m.L.lib.orc_plc_free(self.h)
+            self.h = None
+
+    def run(self, pcm, lost):
+        """pcm int16 [n_frames*160], lost bool [n_frames] -> concealed output int16 [n_frames*160]
+        (the non-causal mode delays the signal by 80 samples)."""
+        out = np.ascontiguousarray(pcm, np.int16).copy()
+        L = self.m.L.lib
+        for f, l in enumerate(lost):
+            fr = out[f * 160:(f + 1) * 160]
+            if l:
+                fr[:] = 0
+                L.orc_plc_conceal(self.h, _p(fr))
+            else:
+                L.orc_plc_update(self.h, _p(fr))
+        return out

@@ -248,3 +248,57 @@ void ref_frame_network(void *hp, const float *features, float *ga, float *gb, fl
 void ref_decode_packet(float *features /*[4][36]*/, float *vq_mem, const unsigned char *buf) {
   decode_packet((float(*)[NB_TOTAL_FEATURES])features, vq_mem, buf);
 }
+
+/* ---- feature analysis / PLC (lpcnet_enc.c, lpcnet_plc.c): thin handles over the reference's own API ---------- */
+#include "lpcnet.h"
+#include "plc_data.h"
+#include "freq.h"
+
+void ref_burg_cepstral_analysis(float *ceps, const float *x) { burg_cepstral_analysis(ceps, x); }
+
+typedef struct {
+  LPCNetPLCState *st;
+  unsigned char *blob;
+} RefPLC;
+
+/* lpcnet_plc_create + lpcnet_plc_load_model (lpcnet_plc.c:100-109, 88-98); the blob is borrowed, so keep a copy */
+void *ref_plc_new(const unsigned char *blob, int len, int options) {
+  RefPLC *h = calloc(1, sizeof(*h));
+  h->blob = malloc(len);
+  memcpy(h->blob, blob, len);
+  h->st = lpcnet_plc_create(options);
+  if (!h->st || lpcnet_plc_load_model(h->st, h->blob, len) != 0) {
+    if (h->st) lpcnet_plc_destroy(h->st);
+    free(h->blob); free(h);
+    return NULL;
+  }
+  return h;
+}
+void ref_plc_free(void *hp) {
+  RefPLC *h = hp;
+  if (!h) return;
+  lpcnet_plc_destroy(h->st); free(h->blob); free(h);
+}
+void ref_plc_seed(void *hp, const unsigned char *data, int n) { kiss99_srand(&((RefPLC *)hp)->st->lpcnet.rng, data, n); }
+int ref_plc_update(void *hp, short *pcm) { return lpcnet_plc_update(((RefPLC *)hp)->st, pcm); }
+int ref_plc_conceal(void *hp, short *pcm) { return lpcnet_plc_conceal(((RefPLC *)hp)->st, pcm); }
+/* observable PLC state for step-by-step comparison */
+void ref_plc_peek(void *hp, float *features20, float *gru1, float *gru2, int *loss_count, double *dc /*[2]*/) {
+  LPCNetPLCState *st = ((RefPLC *)hp)->st;
+  memcpy(features20, st->features, 20 * sizeof(float));
+  memcpy(gru1, st->plc_net.plc_gru1_state, sizeof(st->plc_net.plc_gru1_state));
+  memcpy(gru2, st->plc_net.plc_gru2_state, sizeof(st->plc_net.plc_gru2_state));
+  *loss_count = st->loss_count;
+  dc[0] = st->dc_mem; dc[1] = st->syn_dc;
+}
+/* compute_plc_pred (lpcnet_plc.c:135-145) is static there: the same five calls on the reference's layers */
+void ref_plc_pred(void *hp, float *gru1, float *gru2, float *out, const float *in) {
+  LPCNetPLCState *st = ((RefPLC *)hp)->st;
+  float zeros[3 * PLC_MAX_RNN_NEURONS] = {0};
+  float dense_out[PLC_DENSE1_OUT_SIZE];
+  _lpcnet_compute_dense(&st->model.plc_dense1, dense_out, in);
+  compute_gruB(&st->model.plc_gru1, zeros, gru1, dense_out);
+  compute_gruB(&st->model.plc_gru2, zeros, gru2, gru1);
+  _lpcnet_compute_dense(&st->model.plc_out, out, gru2);
+  out[19] = MIN16(.5f, out[19] + .1f);
+}

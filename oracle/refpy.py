@@ -204,3 +204,52 @@ class RefEncoder:
 
 def ref_half_window(lib: RefLib):
     return np.ctypeslib.as_array((C.c_float * 160).in_dll(lib.lib, "half_window")).copy()
+
+
+def ref_burg_cepstral_analysis(lib: RefLib, x):
+    x = np.ascontiguousarray(x, np.float32)
+    out = np.zeros(36, np.float32)
+    lib.lib.ref_burg_cepstral_analysis(_p(out), _p(x))
+    return out
+
+
+class RefPLC:
+    """The reference's LPCNetPLCState (lpcnet_plc_create / _load_model / _update / _conceal); use RefLib(0)
+    for the non-causal mode (it needs a FEATURES_DELAY 0 build, src/lpcnet_plc.c:357-361)."""
+
+    def __init__(self, lib: RefLib, blob: bytes, options: int = 1, seed: bytes | None = None):
+        self.L = lib
+        L = lib.lib
+        L.ref_plc_new.restype = C.c_void_p
+        L.ref_plc_new.argtypes = [C.c_char_p, C.c_int, C.c_int]
+        L.ref_plc_free.argtypes = [C.c_void_p]
+        L.ref_plc_seed.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+        L.ref_plc_update.argtypes = [C.c_void_p, C.c_void_p]
+        L.ref_plc_conceal.argtypes = [C.c_void_p, C.c_void_p]
+        L.ref_plc_pred.argtypes = [C.c_void_p] * 5
+        self.h = L.ref_plc_new(blob, len(blob), options)
+        if not self.h:
+            raise RuntimeError("reference rejected the PLC blob / options")
+        if seed is not None:
+            L.ref_plc_seed(self.h, seed, len(seed))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.lib.ref_plc_free(self.h)
+            self.h = None
+
+    def run(self, pcm, lost):
+        out = np.ascontiguousarray(pcm, np.int16).copy()
+        for f, l in enumerate(lost):
+            fr = out[f * 160:(f + 1) * 160]
+            if l:
+                fr[:] = 0
+                self.L.lib.ref_plc_conceal(self.h, _p(fr))
+            else:
+                self.L.lib.ref_plc_update(self.h, _p(fr))
+        return out
+
+    def pred(self, gru1, gru2, x):
+        out = np.zeros(20, np.float32)
+        self.L.lib.ref_plc_pred(self.h, _p(gru1), _p(gru2), _p(out), _p(np.ascontiguousarray(x, np.float32)))
+        return out

@@ -137,10 +137,46 @@ def analysis(R):
     np.savez_compressed(os.path.join(OUT, "analysis.npz"), pcm=np.stack(sig), features=np.stack(feats))
 
 
+def plc_model_blob():
+    A = blob.random_model()
+    A.update(blob.random_plc_model())
+    return blob.write_blob(A)
+
+
+def plc(R):
+    """lpcnet_plc_update / lpcnet_plc_conceal of the reference's FEATURES_DELAY 0 build (libref_d0.so), non-causal
+    mode without and with the DC filter, 3 streams x 40 frames under Gilbert loss; plus burg_cepstral_analysis and
+    the predictor network on its own."""
+    R0 = refpy.RefLib(0)
+    b = plc_model_blob()
+    d = {"blob_sha256": np.frombuffer(hashlib.sha256(b).digest(), np.uint8)}
+    F = 40
+    for opt in (1, 5):
+        for s in range(3):
+            x = blob.synthetic_pcm(F, s)
+            if opt == 5:
+                x = np.clip(x.astype(np.int32) + 700, -32768, 32767).astype(np.int16)   # a DC offset to remove
+            lost = blob.synthetic_loss_pattern(F, s)
+            d[f"in_{opt}_{s}"], d[f"lost_{opt}_{s}"] = x, lost
+            d[f"out_{opt}_{s}"] = refpy.RefPLC(R0, b, opt, blob.stream_seed(s)).run(x, lost)
+    x = blob.synthetic_pcm(12, 5).astype(np.float32)
+    d["burg_in"] = x
+    d["burg_out"] = np.stack([refpy.ref_burg_cepstral_analysis(R0, x[f * 160:(f + 1) * 160]) for f in range(12)])
+    rp = refpy.RefPLC(R0, b, 1)
+    rng = np.random.default_rng(11)
+    g1 = np.zeros(256, np.float32); g2 = np.zeros(256, np.float32)
+    pin = (rng.standard_normal((16, 57)) * 0.7).astype(np.float32)
+    pin[::4] = 0
+    d["pred_in"] = pin
+    d["pred_out"] = np.stack([rp.pred(g1, g2, v) for v in pin])
+    d["pred_gru1"], d["pred_gru2"] = g1.copy(), g2.copy()
+    np.savez_compressed(os.path.join(OUT, "plc.npz"), **d)
+
+
 if __name__ == "__main__":
     R = refpy.RefLib(2)
-    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis"]
+    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc"]
     for name in which:
-        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis}[name](R)
+        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc}[name](R)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
