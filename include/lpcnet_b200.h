@@ -216,6 +216,41 @@ LPCNET_B200_EXPORT int lpcnet_feature_batch_compute_device(LPCNetFeatureBatch *b
                                                            const float *d_pcmf, int n_frames, float *d_features,
                                                            void *cuda_stream);
 
+/* ------------------------------------------------------------------------------------
+ * 4. Packet-loss concealment, non-causal mode (BASELINE config 4)
+ * ------------------------------------------------------------------------------------ */
+/* The reference's PLC entry points (include/lpcnet.h:190-215, src/lpcnet_plc.c:44-109, 493-503) for
+ * options = LPCNET_PLC_NONCAUSAL (1), optionally | LPCNET_PLC_DC_FILTER (4); other modes return -1.  The blob
+ * must carry the plc_* arrays next to the LPCNet model, and the model is run with FEATURES_DELAY 0 as
+ * src/lpcnet_plc.c:357-361 demands.  pcm: 160 samples in (update) / out (both); the output lags the input by 80
+ * samples.  The FEC queue (lpcnet_plc_fec_add) is not built. */
+typedef struct LPCNetPLCState LPCNetPLCState;
+LPCNET_B200_EXPORT int lpcnet_plc_get_size(void);
+LPCNET_B200_EXPORT int lpcnet_plc_init(LPCNetPLCState *st, int options);
+LPCNET_B200_EXPORT LPCNetPLCState *lpcnet_plc_create(int options);
+LPCNET_B200_EXPORT void lpcnet_plc_destroy(LPCNetPLCState *st);
+LPCNET_B200_EXPORT int lpcnet_plc_load_model(LPCNetPLCState *st, const unsigned char *data, int len);
+LPCNET_B200_EXPORT int lpcnet_plc_update(LPCNetPLCState *st, short *pcm);
+LPCNET_B200_EXPORT int lpcnet_plc_conceal(LPCNetPLCState *st, short *pcm);
+
+/* Batched form: n_streams independent PLC states, each with its own loss pattern.  lost: [n_streams][n_frames]
+ * (non-zero = the 10 ms frame is lost -> lpcnet_plc_conceal, else lpcnet_plc_update); pcm: [n_streams][n_frames*160]
+ * in/out.  Streams are seeded like lpcnet_batch_set_seed. */
+typedef struct LPCNetPLCBatch LPCNetPLCBatch;
+LPCNET_B200_EXPORT LPCNetPLCBatch *lpcnet_plc_batch_create(const unsigned char *blob, int len, int n_streams, int device,
+                                                           int options, float lpc_gamma);
+LPCNET_B200_EXPORT void lpcnet_plc_batch_destroy(LPCNetPLCBatch *b);
+LPCNET_B200_EXPORT int lpcnet_plc_batch_n_streams(const LPCNetPLCBatch *b);
+LPCNET_B200_EXPORT int lpcnet_plc_batch_set_seed(LPCNetPLCBatch *b, int stream, const unsigned char *data, int n);
+LPCNET_B200_EXPORT long long lpcnet_plc_batch_launch_count(const LPCNetPLCBatch *b);
+LPCNET_B200_EXPORT int lpcnet_plc_batch_process(LPCNetPLCBatch *b, const unsigned char *lost, short *pcm, int n_frames);
+/* Frame-rate state of one stream for step-by-step checks: st->features[0..20), the predictor's two GRU states
+ * (256 each), {dc_mem, syn_dc}; any pointer may be NULL. */
+LPCNET_B200_EXPORT int lpcnet_plc_batch_peek(LPCNetPLCBatch *b, int stream, float *features20, float *gru1, float *gru2,
+                                             double *dc2);
+/* The last processed frame's burg_cepstral_analysis output and analysis features of one stream (good frames). */
+LPCNET_B200_EXPORT int lpcnet_plc_batch_peek_frame(LPCNetPLCBatch *b, int stream, float *burg36, float *enc36);
+
 /* The reference's tanh/sigmoid multiply by `rcpps` (src/vec_avx.h:408,437), a CPU
  * hardware estimate that is exactly a 2048-entry table over the top 11 mantissa bits.
  * Default: the Intel table model (oracle/orc_prim.c).  A process-wide override takes the

@@ -51,6 +51,7 @@ struct AnalysisArgs {
   float *P;                   // [B][160 + 160F]  history | pre-emphasised signal
   float *S;                   // [B][1 + 160F]    previous residual | LPC residual
   float *fft_scratch;         // [320][2][B*F]
+  const uint8_t *stream_mask; // nullable [B]: streams with 0 keep their state and their feature rows
 };
 
 __device__ __forceinline__ float pcm_at(const AnalysisArgs &A, int s, int n) {
@@ -84,6 +85,7 @@ __global__ void spectral_kernel(AnalysisArgs A) {
   const size_t nthreads = (size_t)gridDim.x * blockDim.x;
   if (idx >= B * F) return;
   const int s = idx / F, f = idx % F;
+  if (A.stream_mask && !A.stream_mask[s]) return;
   Scratch S{A.fft_scratch + idx, nthreads};
   const float *x = A.P + (size_t)s * (kOverlap + F * kFrame) + (size_t)f * kFrame;   // [analysis_mem | frame]
   // apply_window (freq.c:322-328) and opus_fft_c's scaled bit-reversed copy (kiss_fft.c:566-585)
@@ -157,6 +159,7 @@ constexpr int kPT = 256;
 __global__ void __launch_bounds__(kPT) pitch_kernel(AnalysisArgs A) {
   extern __shared__ float sm[];
   const int s = blockIdx.x, t = threadIdx.x, F = A.n_frames, L = F * kFrame;
+  if (A.stream_mask && !A.stream_mask[s]) return;
   float *ebuf = sm;                         // [256 + L]
   float *xc = ebuf + kPMax + L;             // [2][256]
   float *path0 = xc + 2 * kPMax;            // [256]
@@ -345,7 +348,8 @@ int feature_chunk_frames(int B, int n_frames) {
   return F < n_frames ? F : n_frames;
 }
 
-int analysis_device(LPCNetFeatureBatch *b, const short *d16, const float *df, int n_frames, float *d_features) {
+int analysis_device(LPCNetFeatureBatch *b, const short *d16, const float *df, int n_frames, float *d_features,
+                    const uint8_t *d_mask = nullptr) {
   const int B = b->n_streams;
   CKA(cudaSetDevice(b->device));
   const int Fc = feature_chunk_frames(B, n_frames);
@@ -359,7 +363,7 @@ int analysis_device(LPCNetFeatureBatch *b, const short *d16, const float *df, in
     AnalysisArgs A{};
     A.st = b->st; A.tab = b->tab; A.half_window = b->half_window;
     A.n_streams = B; A.n_frames = F; A.frame0 = f0; A.total_frames = n_frames;
-    A.pcm16 = d16; A.pcmf = df; A.features = d_features;
+    A.pcm16 = d16; A.pcmf = df; A.features = d_features; A.stream_mask = d_mask;
     A.P = static_cast<float *>(b->work);
     A.S = A.P + (((size_t)B * (kOverlap + F * kFrame) + 63) & ~size_t(63));
     A.fft_scratch = A.S + (((size_t)B * (1 + F * kFrame) + 63) & ~size_t(63));
@@ -393,6 +397,15 @@ int analysis_host(LPCNetFeatureBatch *b, const short *p16, const float *pf, int 
 }
 
 }  // namespace
+
+int lpcb::feature_batch_frame_masked(LPCNetFeatureBatch *b, const short *d_pcm16, const uint8_t *d_mask, float *d_features,
+                                     cudaStream_t stream) {
+  cudaStream_t keep = b->stream;
+  b->stream = stream;
+  const int r = analysis_device(b, d_pcm16, nullptr, 1, d_features, d_mask);
+  b->stream = keep;
+  return r;
+}
 
 extern "C" {
 

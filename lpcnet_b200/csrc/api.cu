@@ -254,6 +254,36 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
 
 }  // namespace
 
+// ---- hooks for the PLC driver (plc.cu) ----
+BatchView lpcb::batch_view(LPCNetBatch *b) { return BatchView{b->st, &b->model, b->stream, b->n_streams, b->device}; }
+
+int lpcb::batch_frame_network_masked(LPCNetBatch *b, const float *d_features, int stride, const uint8_t *d_mask) {
+  CK(cudaSetDevice(b->device));
+  if (ensure_frame_buffers(b, 1)) return -1;
+  FrameArgs fa{};
+  fa.m = b->model.d; fa.st = b->st; fa.fb = b->fb; fa.n_streams = b->n_streams; fa.n_frames = 1;
+  fa.features = d_features; fa.feature_stride = stride; fa.frame0 = 0; fa.total_frames = 1;
+  fa.stream_mask = d_mask;
+  int nl = 0;
+  CK(launch_frame_network(fa, b->stream, &nl));
+  b->launches += nl;
+  return 0;
+}
+
+int lpcb::batch_sample_segment(LPCNetBatch *b, int n, const uint8_t *d_flags, const short *d_forced, short *d_out) {
+  if (n <= 0 || n > kFrame) return fail("sample segment must be 1..160 steps");
+  CK(cudaSetDevice(b->device));
+  SampleArgs sa{};
+  sa.m = b->model.d; sa.st = b->st; sa.n_streams = b->n_streams; sa.n_frames = 1; sa.spf = n;
+  sa.frame0 = 0; sa.total_frames = 1;
+  sa.cond_a = b->fb.cond_a; sa.cond_b = b->fb.cond_b; sa.lpc = b->fb.lpc; sa.active = d_flags;
+  sa.pcm = d_out; sa.forced = d_forced; sa.forced_by_flag = 1;
+  int nl = 0;
+  CK(launch_sample_kernel(sa, auto_tile(b), b->n_sms, b->stream, &nl));
+  b->launches += nl;
+  return 0;
+}
+
 extern "C" {
 
 #ifdef LPCB_PHASE_CLOCKS

@@ -74,6 +74,17 @@ struct DevSparse {
   int slots[3];                 // fixed chunk slots per gate per unit group (0,0,0 = all chunks in the overflow lists)
 };
 
+// PLC predictor (src/lpcnet_plc.c:135-145; plc_data.c): dense 57->128, two int8 GRUs of 256 units, dense 256->20.
+// GRU matrices re-tiled as words of four consecutive inputs, [input/4][3*256 rows]: thread = row, coalesced.
+constexpr int kPlcIn = 57, kPlcCond = 128, kPlcUnits = 256, kPlcRows = 3 * kPlcUnits;
+struct DevPlc {
+  const float *dense1_w, *dense1_b;     // [57][128], [128]
+  const float *out_w, *out_b;           // [256][20], [20]
+  const uint32_t *g1_in, *g1_rec;       // [128/4][768], [256/4][768]
+  const uint32_t *g2_in, *g2_rec;       // [256/4][768], [256/4][768]
+  const float *g1_subias, *g2_subias;   // [2][768]
+};
+
 // Device-side model: pointers into one device allocation.
 struct DevModel {
   // 100 Hz frame network (fp32, blob layout)
@@ -103,6 +114,7 @@ struct DevModel {
   const float *codebooks;                   // cb1|cb2|cb3|diff4 or NULL
   int features_delay;
   float lpc_gamma;
+  DevPlc plc;                               // valid when Model::has_plc
 };
 
 // Per-stream mutable state, structure-of-arrays in HBM ([field][stream] where noted).
@@ -129,6 +141,7 @@ struct Model {
   size_t dev_bytes = 0;
   int nblocks_a = 0, nblocks_b = 0;
   bool has_codebooks = false;
+  bool has_plc = false;   // the blob carried the plc_* arrays
 };
 
 // Loads and validates a DNNw blob (src/parse_lpcnet_weights.c) and builds the device model.
@@ -170,6 +183,8 @@ struct SampleArgs {
   const uint8_t *active;     // [F][B]
   short *pcm;                // [B][total_frames*spf]
   const short *forced;       // nullable, same layout
+  int forced_by_flag;        // 0: `forced` (if given) teacher-forces every active stream; 1: only streams whose
+                             //    active flag has bit 1 set (PLC: forced and free-running streams in one launch)
   void *trace;               // nullable LPCNetB200Trace [B][total_frames*spf]
   float *logits;             // nullable [B][total_frames*spf][256]
   unsigned long long *phase_clk;   // development builds (-DLPCB_PHASE_CLOCKS) only: per-phase cycle sums of CTA 0
@@ -187,6 +202,7 @@ struct FrameArgs {
   const float *features;     // device [B][total_frames][stride]
   int feature_stride;
   int frame0, total_frames;
+  const uint8_t *stream_mask;  // nullable [B]: streams with 0 keep their frame-rate state (their outputs are unused)
 };
 cudaError_t launch_frame_network(const FrameArgs &a, cudaStream_t s, int *n_launches);
 
@@ -198,5 +214,28 @@ struct DecodeArgs {
   float *features;               // device [B][n_packets*4][36]
 };
 cudaError_t launch_decode_packets(const DecodeArgs &a, cudaStream_t s, int *n_launches);
+
+}  // namespace lpcb
+
+// Hooks the PLC driver (plc.cu) uses on the batched engine (api.cu) and the feature analysis (analysis.cu).
+struct LPCNetBatch;
+struct LPCNetFeatureBatch;
+namespace lpcb {
+struct BatchView {
+  DevState st;
+  const Model *model;
+  cudaStream_t stream;
+  int n_streams, device;
+};
+BatchView batch_view(LPCNetBatch *b);
+// run_frame_network for one frame of the streams with mask != 0 (features: device [B][stride]); the conditioning
+// stays in the batch's frame buffers for the sample segments that follow.
+int batch_frame_network_masked(LPCNetBatch *b, const float *d_features, int stride, const uint8_t *d_mask);
+// n sample steps (lpcnet_synthesize_tail_impl) on the conditioning of the last frame network.  flags [B]: 0 the
+// stream does not move, 1 free-running, 3 teacher-forced on d_forced [B][n]; d_out [B][n].
+int batch_sample_segment(LPCNetBatch *b, int n, const uint8_t *d_flags, const short *d_forced, short *d_out);
+// one frame of analysis for the streams with mask != 0: d_pcm16 [B][160] -> d_features [B][36] (others untouched)
+int feature_batch_frame_masked(LPCNetFeatureBatch *b, const short *d_pcm16, const uint8_t *d_mask, float *d_features,
+                               cudaStream_t stream);
 
 }  // namespace lpcb

@@ -45,7 +45,8 @@ __global__ void frame_inputs_kernel(FrameArgs A) {
   if (tid == 0) {
     const int fc0 = A.st.frame_count[s];
     // lpcnet_synthesize_tail_impl runs after frame_count++ (src/lpcnet.c:119, 239)
-    A.fb.active[(size_t)f * B + s] = (frame_count_at(fc0, f + 1) > A.m.features_delay) ? 1 : 0;
+    const bool on = !A.stream_mask || A.stream_mask[s];
+    A.fb.active[(size_t)f * B + s] = (on && frame_count_at(fc0, f + 1) > A.m.features_delay) ? 1 : 0;
   }
 }
 
@@ -197,6 +198,7 @@ __global__ void frame_finalize_kernel(FrameArgs A) {
   const int B = A.n_streams, F = A.n_frames, D = A.m.features_delay;
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= B) return;
+  if (A.stream_mask && !A.stream_mask[s]) return;   // this stream did not run a frame network
   if (D > 0) {
     float newest[kMaxDelay][16];   // new_lpc[F-1-k]
     for (int k = 0; k < D; k++)

@@ -447,6 +447,64 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
       m.has_codebooks = true;
     }
   }
+  // optional PLC predictor arrays (init_plc_model, training_tf2/dump_plc.py:319-330): all or none
+  if (A.find("plc_dense1_bias") != A.end()) {
+    DevPlc &P = d.plc;
+    bool pk = true;
+    pk &= put_f(&P.dense1_b, "plc_dense1_bias", kPlcCond);
+    pk &= put_f(&P.dense1_w, "plc_dense1_weights", kPlcIn * kPlcCond);
+    pk &= put_f(&P.out_b, "plc_out_bias", 20);
+    pk &= put_f(&P.out_w, "plc_out_weights", kPlcUnits * 20);
+    pk &= put_f(&P.g1_subias, "plc_gru1_subias", 2 * kPlcRows);
+    pk &= put_f(&P.g2_subias, "plc_gru2_subias", 2 * kPlcRows);
+    pk &= need("plc_gru1_bias", 2 * kPlcRows * 4) != nullptr;
+    pk &= need("plc_gru2_bias", 2 * kPlcRows * 4) != nullptr;
+    // [input/4][row] words from the block-sparse stream (absent blocks = 0) or the dense 8x4 layout
+    auto retile = [&](const uint32_t **dst, const char *wname, const char *iname, int cols) -> bool {
+      auto wi = A.find(wname);
+      if (wi == A.end()) { if (err.empty()) err = std::string("missing array ") + wname; return false; }
+      const int8_t *w = reinterpret_cast<const int8_t *>(wi->second.data);
+      const int wb = wi->second.size;
+      for (int i = 0; i + 1 < wb; i += 2)
+        if (255 * (abs((int)w[i]) + abs((int)w[i + 1])) > 32767) {
+          err = std::string(wname) + ": int8 pair would saturate vpmaddubsw; not representable bit-exactly";
+          return false;
+        }
+      std::vector<uint32_t> t((size_t)(cols / 4) * kPlcRows, 0u);
+      auto place = [&](int grp, int pos, const int8_t *blk) {
+        for (int r = 0; r < 8; r++) memcpy(&t[(size_t)(pos / 4) * kPlcRows + grp * 8 + r], blk + 4 * r, 4);
+      };
+      if (iname) {
+        auto ii = A.find(iname);
+        if (ii == A.end() || (ii->second.size & 3)) { if (err.empty()) err = std::string("missing array ") + iname; return false; }
+        const int32_t *p = reinterpret_cast<const int32_t *>(ii->second.data);
+        int remain = ii->second.size / 4, grp = 0, total = 0;
+        while (remain > 0) {
+          const int nb = *p++;
+          if (nb < 0 || remain < nb + 1 || grp >= kPlcRows / 8 || (total + nb) * 32 > wb) { err = std::string(iname) + ": bad block index stream"; return false; }
+          for (int k = 0; k < nb; k++) {
+            const int pos = *p++;
+            if (pos < 0 || (pos & 3) || pos + 3 >= cols) { err = std::string(iname) + ": bad block position"; return false; }
+            place(grp, pos, w + (size_t)(total + k) * 32);
+          }
+          remain -= nb + 1; total += nb; grp++;
+        }
+        if (grp != kPlcRows / 8 || total * 32 != wb) { err = std::string(iname) + ": block index stream does not match the weights"; return false; }
+      } else {
+        if (wb != kPlcRows * cols) { err = std::string("wrong size for array ") + wname; return false; }
+        for (int grp = 0; grp < kPlcRows / 8; grp++)
+          for (int pos = 0; pos < cols; pos += 4) place(grp, pos, w + ((size_t)grp * (cols / 4) + pos / 4) * 32);
+      }
+      put(reinterpret_cast<const void **>(dst), t.data(), t.size() * 4);
+      return true;
+    };
+    pk = pk && retile(&P.g1_in, "plc_gru1_weights", "plc_gru1_weights_idx", kPlcCond);
+    pk = pk && retile(&P.g1_rec, "plc_gru1_recurrent_weights", nullptr, kPlcUnits);
+    pk = pk && retile(&P.g2_in, "plc_gru2_weights", "plc_gru2_weights_idx", kPlcUnits);
+    pk = pk && retile(&P.g2_rec, "plc_gru2_recurrent_weights", nullptr, kPlcUnits);
+    if (!pk) return false;
+    m.has_plc = true;
+  }
   d.features_delay = features_delay;
   d.lpc_gamma = lpc_gamma;
 

@@ -1,0 +1,870 @@
+// Packet-loss concealment for many streams at once: the reference's non-causal mode
+// (lpcnet_plc_update_non_causal / lpcnet_plc_conceal_non_causal / process_queued_update / compute_plc_pred /
+// clear_state, src/lpcnet_plc.c:349-491, 342-347, 135-145, 175-181), LPCNET_PLC_NONCAUSAL with or without
+// LPCNET_PLC_DC_FILTER, for a model built with FEATURES_DELAY 0 (lpcnet_plc.c:357-361).
+//
+// Every stream follows its own loss pattern, so in one 10 ms frame the streams of a batch are in different
+// branches of the reference's state machine.  The branch a stream takes depends only on the loss flags (lost now,
+// lost before, an update queued), which the host knows: it sorts the streams of every frame into classes and
+// uploads one byte mask per stage; all streams then walk the same sequence of stages, and a stage moves only
+// the streams of its class:
+//   Q   queued update            frame network + 160 teacher-forced samples
+//   FG  first good frame after a loss: prediction, 80 free samples, the backward pass on the reversed frame
+//       (clear_state, frame network, 160 forced + 80 free samples), cross-fade, state restore, analysis
+//   M   good frame (2 x 80 forced samples) or lost frame (80 forced-or-free + 80 free samples)
+// The sample steps are the synthesis engine's persistent kernel (sample_kernel.cuh) with per-stream flags:
+// inactive / free-running / teacher-forced.  Frame-rate arithmetic (DC filter in double, Burg cepstrum, the
+// int8 predictor GRUs, cross-fade) follows the reference operation by operation; -fmad=false.
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/lpcnet_b200.h"
+#include "bitexact.cuh"
+#include "dsp.cuh"
+#include "engine.h"
+
+namespace lpcb {
+namespace {
+
+constexpr int kTOff = 80, kBands = 18;
+
+// stream classes of one frame (host side) and the per-stage byte masks derived from them
+enum Cls : uint8_t { kG0 = 0, kFG = 1, kL0 = 2, kL1 = 3 };   // good, first good after loss, first lost, lost again
+enum Mask { mQ = 0, mUpd, mFG, mMain, mL1, fQ, fFgFree, fFgForced, fA, fB, mCls, kNMasks };
+
+struct PlcState {        // per stream, device
+  short *pcm;            // [B][160]  st->pcm[0..160)
+  float *features;       // [B][20]   st->features
+  float *gru1, *gru2;    // [B][256]  plc_net
+  double *dc_mem, *syn_dc;   // [B]
+  short *dc_buf;         // [B][80]
+  short *queued;         // [B][160]  queued_samples
+};
+
+struct PlcWork {         // per frame scratch, device
+  short *in;             // [B][160]  the frame after DC removal
+  short *save;           // [B][160]  pcm_save
+  short *lp;             // [B][160]
+  double *mem_bak;       // [B]
+  int *delta;            // [B]
+  float *burg;           // [B][36]
+  float *encf;           // [B][36]   analysis of the input frame
+  float *encf2;          // [B][36]   analysis of the concealment buffer (state update only)
+  float *fnfeat;         // [B][20]   frame-network input
+  short *segf;           // [B][160]  teacher-forcing input of a sample segment
+  short *sego, *sego2;   // [B][160]  sample segment outputs
+  short *out;            // [B][160]  the frame's output
+};
+
+struct PlcArgs {
+  PlcState st;
+  PlcWork w;
+  DevState lp;           // the synthesis state (LPCNetState) and its snapshot
+  DevState lp_copy;
+  DevPlc net;
+  const uint32_t *rcp_tab;
+  DspTables tab;
+  float *fft_scratch;    // [320][2][B]
+  const float *fade;     // [80] cross-fade weights
+  const uint8_t *masks;  // [kNMasks][B] of this frame
+  const uint16_t *lossc; // [B] loss_count before this frame
+  short *pcm_io;         // [B][total_frames*160]
+  int n_streams, frame, total_frames, remove_dc;
+};
+
+#define DC_CONST 0.003
+
+// ---- update streams: DC removal (lpcnet_plc.c:361-371), pcm_save ----
+__global__ void plc_pre_kernel(PlcArgs A) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= A.n_streams || !A.masks[mUpd * A.n_streams + s]) return;
+  const short *x = A.pcm_io + ((size_t)s * A.total_frames + A.frame) * kFrame;
+  short *in = A.w.in + (size_t)s * kFrame, *save = A.w.save + (size_t)s * kFrame, *lp = A.w.lp + (size_t)s * kFrame;
+  A.w.delta[s] = (int)A.st.syn_dc[s];
+  if (A.remove_dc) {
+    double dc = A.st.dc_mem[s] + A.st.syn_dc[s];
+    A.st.syn_dc[s] = 0;
+    A.w.mem_bak[s] = dc;
+    for (int i = 0; i < kFrame; i++) {
+      const short l = (short)(int)floor(.5 + dc);
+      dc += DC_CONST * ((double)x[i] - dc);
+      lp[i] = l;
+      in[i] = (short)(x[i] - l);
+    }
+    A.st.dc_mem[s] = dc;
+  } else {
+    for (int i = 0; i < kFrame; i++) { lp[i] = 0; in[i] = x[i]; }
+  }
+  for (int i = 0; i < kFrame; i++) save[i] = in[i];
+}
+
+// ---- burg_cepstral_analysis (freq.c:152-199, burg.c:97-245), one thread per update stream ----
+__device__ double inner_flp(const float *a, const float *b, int n) {
+  double r = 0.0;
+  int i;
+  for (i = 0; i < n - 3; i += 4)
+    r += (double)a[i + 0] * (double)b[i + 0] + (double)a[i + 1] * (double)b[i + 1] + (double)a[i + 2] * (double)b[i + 2] +
+         (double)a[i + 3] * (double)b[i + 3];
+  for (; i < n; i++) r += (double)a[i] * (double)b[i];
+  return r;
+}
+
+__device__ float burg_analysis(float *Aout, const float *x, float minInvGain, int len, int D) {
+  double C0, invGain, num, nrg_f, nrg_b, rc, Atmp, tmp1, tmp2;
+  double Cf[16], Cl[16], CAf[17], CAb[17], Af[16];
+  bool reached = false;
+  C0 = inner_flp(x, x, len);
+  for (int n = 0; n < 16; n++) Cf[n] = 0;
+  for (int n = 1; n < D + 1; n++) Cf[n - 1] += inner_flp(x, x + n, len - n);
+  for (int n = 0; n < 16; n++) Cl[n] = Cf[n];
+  CAb[0] = CAf[0] = C0 + (double)1e-5f * C0 + (double)1e-9f;
+  invGain = 1.0;
+  for (int n = 0; n < D; n++) {
+    tmp1 = x[n];
+    tmp2 = x[len - n - 1];
+    for (int k = 0; k < n; k++) {
+      Cf[k] -= (double)(x[n] * x[n - k - 1]);
+      Cl[k] -= (double)(x[len - n - 1] * x[len - n + k]);
+      Atmp = Af[k];
+      tmp1 += (double)x[n - k - 1] * Atmp;
+      tmp2 += (double)x[len - n + k] * Atmp;
+    }
+    for (int k = 0; k <= n; k++) {
+      CAf[k] -= tmp1 * (double)x[n - k];
+      CAb[k] -= tmp2 * (double)x[len - n + k - 1];
+    }
+    tmp1 = Cf[n];
+    tmp2 = Cl[n];
+    for (int k = 0; k < n; k++) {
+      Atmp = Af[k];
+      tmp1 += Cl[n - k - 1] * Atmp;
+      tmp2 += Cf[n - k - 1] * Atmp;
+    }
+    CAf[n + 1] = tmp1;
+    CAb[n + 1] = tmp2;
+    num = CAb[n + 1];
+    nrg_b = CAb[0];
+    nrg_f = CAf[0];
+    for (int k = 0; k < n; k++) {
+      Atmp = Af[k];
+      num += CAb[n - k] * Atmp;
+      nrg_b += CAb[k + 1] * Atmp;
+      nrg_f += CAf[k + 1] * Atmp;
+    }
+    rc = -2.0 * num / (nrg_f + nrg_b);
+    tmp1 = invGain * (1.0 - rc * rc);
+    if (tmp1 <= (double)minInvGain) {
+      rc = sqrt(1.0 - (double)minInvGain / invGain);
+      if (num > 0) rc = -rc;
+      invGain = minInvGain;
+      reached = true;
+    } else {
+      invGain = tmp1;
+    }
+    for (int k = 0; k < (n + 1) >> 1; k++) {
+      tmp1 = Af[k];
+      tmp2 = Af[n - k - 1];
+      Af[k] = tmp1 + rc * tmp2;
+      Af[n - k - 1] = tmp2 + rc * tmp1;
+    }
+    Af[n] = rc;
+    if (reached) {
+      for (int k = n + 1; k < D; k++) Af[k] = 0.0;
+      break;
+    }
+    for (int k = 0; k <= n + 1; k++) {
+      tmp1 = CAf[k];
+      CAf[k] += rc * CAb[n - k + 1];
+      CAb[n - k + 1] += rc * tmp1;
+    }
+  }
+  if (reached) {
+    for (int k = 0; k < D; k++) Aout[k] = (float)(-Af[k]);
+    C0 -= inner_flp(x, x, D);
+    nrg_f = C0 * invGain;
+  } else {
+    nrg_f = CAf[0];
+    tmp1 = 1.0;
+    for (int k = 0; k < D; k++) {
+      Atmp = Af[k];
+      nrg_f += CAf[k + 1] * Atmp;
+      tmp1 += Atmp * Atmp;
+      Aout[k] = (float)(-Atmp);
+    }
+    nrg_f -= (double)1e-5f * C0 * tmp1;
+  }
+  return (float)nrg_f;
+}
+
+__constant__ double c_pow995[16];   // pow(.995, i+1), filled by the host's libm at start-up
+
+__device__ void burg_cepstrum(const PlcArgs &A, const short *pcm, float *out, const Scratch &S) {
+  float bin[kTOff], blpc[16];
+  for (int i = 0; i < kTOff - 1; i++) bin[i] = (float)pcm[i + 1] - 0.85f * (float)pcm[i];
+  float g = burg_analysis(blpc, bin, (float)1e-3, kTOff - 1, 16);
+  g /= (float)(kTOff - 2 * (16 - 1));
+  // forward_transform of [1, -lpc[i]*.995^(i+1), 0...]: opus_fft_c's scaled bit-reversed copy
+  const float scale = 1.f / 320;
+  for (int k = 0; k < 320; k++) {
+    float v = 0.f;
+    if (k == 0) v = 1.f;
+    else if (k <= 16) v = (float)((double)(-blpc[k - 1]) * c_pow995[k - 1]);
+    Cpx c;
+    c.r = scale * v; c.i = scale * 0.f;
+    S.st(__ldg(A.tab.fft_bitrev + k), c);
+  }
+  fft320_butterflies(S, A.tab.fft_tw);
+  // compute_band_energy_inverse (freq.c:59-84)
+  float sum[kBands];
+  for (int i = 0; i < kBands; i++) sum[i] = 0;
+  for (int i = 0; i < kBands - 1; i++) {
+    const int band_size = (c_eband5ms[i + 1] - c_eband5ms[i]) * 4;
+    for (int j = 0; j < band_size; j++) {
+      const float frac = (float)j / (float)band_size;
+      const Cpx X = S.ld(c_eband5ms[i] * 4 + j);
+      float tmp = X.r * X.r;
+      tmp += X.i * X.i;
+      tmp = (float)((double)1.f / ((double)tmp + 1e-9));
+      sum[i] += (1.f - frac) * tmp;
+      sum[i + 1] += frac * tmp;
+    }
+  }
+  sum[0] *= 2;
+  sum[kBands - 1] *= 2;
+  const double gain = (.45 * (double)g) * (double)(1.f / ((float)320 * 320 * 320));
+  float Ly[kBands], logMax = -2, follow = -2;
+  for (int i = 0; i < kBands; i++) {
+    const float E = (float)((double)sum[i] * gain);
+    float l = (float)log10(1e-2 + (double)E);
+    // freq.c:180-183: the constant 2.5 is a double there, so these comparisons run in double
+    const double f25 = (double)follow - 2.5;
+    const double inner = f25 > (double)l ? f25 : (double)l;
+    const float lm8 = logMax - 8;
+    l = (float)((double)lm8 > inner ? (double)lm8 : inner);
+    Ly[i] = l;
+    logMax = fmaxf(logMax, l);
+    follow = (float)(f25 > (double)l ? f25 : (double)l);
+  }
+  for (int i = 0; i < kBands; i++) {
+    float acc = 0;
+    for (int j = 0; j < kBands; j++) acc += Ly[j] * __ldg(A.tab.dct + j * kBands + i);
+    out[i] = (float)((double)acc * sqrt(2. / kBands));
+  }
+  out[0] += -4;
+}
+
+// one thread per (update stream, half frame); the two cepstra go to encf2 (free at this point of the frame) and
+// are combined into mean / difference (freq.c:188-199) by plc_burg_combine_kernel
+__global__ void plc_burg_kernel(PlcArgs A) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t nthreads = (size_t)gridDim.x * blockDim.x;
+  const int s = idx >> 1, half = idx & 1;
+  if (s >= A.n_streams || !A.masks[mUpd * A.n_streams + s]) return;
+  Scratch S{A.fft_scratch + idx, nthreads};
+  burg_cepstrum(A, A.w.in + (size_t)s * kFrame + half * kTOff, A.w.encf2 + (size_t)s * 36 + half * kBands, S);
+}
+
+__global__ void plc_burg_combine_kernel(PlcArgs A) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= A.n_streams * kBands) return;
+  const int s = i / kBands, k = i % kBands;
+  if (!A.masks[mUpd * A.n_streams + s]) return;
+  const float c0 = A.w.encf2[(size_t)s * 36 + k], c1 = A.w.encf2[(size_t)s * 36 + kBands + k];
+  A.w.burg[(size_t)s * 36 + k] = (float)(.5 * (double)(c0 + c1));
+  A.w.burg[(size_t)s * 36 + kBands + k] = c0 - c1;
+}
+
+// ---- compute_plc_pred (lpcnet_plc.c:135-145): one block of 256 threads per stream ----
+// mode per stream from its class: FG pass -> [burg | 0 | 1]; main pass, good -> [burg | features | 1]; main
+// pass, lost -> zeros, then the loss attenuation of features[0] (lpcnet_plc.c:457-458).
+// u8 x s8 dot product of four byte pairs on an int32 accumulator (vpmaddubsw + vpmaddwd without the s16 saturation,
+// which the loader has excluded)
+__device__ __forceinline__ int32_t dp4a_u8s8(uint32_t a, uint32_t b, int32_t c) {
+  int32_t d;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+
+__device__ __forceinline__ float plc_gru_row(const uint32_t *__restrict__ w_in, const uint32_t *xq_in, int nin4,
+                                              const uint32_t *__restrict__ w_rec, const uint32_t *xq_st, float bias_in,
+                                              float bias_rec, int row, float &recur_out) {
+  // compute_gruB (nnet.c:326-372): zrh = subias[row] + 0 -> int8 dot products on int32 accumulators seeded
+  // with cvtps2dq(16256*t), back to float by * 1/16256 (vec_avx.h:690-755, 790-860)
+  int32_t acc = cvt_rne_ref((bias_in + 0.f) * LPCB_SCALE);
+  for (int k = 0; k < nin4; k++) acc = dp4a_u8s8(xq_in[k], __ldg(w_in + (size_t)k * kPlcRows + row), acc);
+  int32_t acr = cvt_rne_ref(bias_rec * LPCB_SCALE);
+  for (int k = 0; k < kPlcUnits / 4; k++) acr = dp4a_u8s8(xq_st[k], __ldg(w_rec + (size_t)k * kPlcRows + row), acr);
+  recur_out = (float)acr * LPCB_SCALE_1;
+  return (float)acc * LPCB_SCALE_1;
+}
+
+__device__ void plc_gru(const uint32_t *w_in, const uint32_t *w_rec, const float *subias, const float *x_in, int nin,
+                        float *state /*global [256]*/, uint32_t *xq_in, uint32_t *xq_st, float *s_state,
+                        const uint32_t *rcp, int t) {
+  // vector_ps_to_epi8 of the input and of the state
+  unsigned char *qi = reinterpret_cast<unsigned char *>(xq_in), *qs = reinterpret_cast<unsigned char *>(xq_st);
+  if (t < nin) qi[t] = (unsigned char)quant_u8_ref(x_in[t]);
+  const float st = state[t];
+  qs[t] = (unsigned char)quant_u8_ref(st);
+  __syncthreads();
+  float rz, rr, rh;
+  float z = plc_gru_row(w_in, xq_in, nin / 4, w_rec, xq_st, subias[t], subias[kPlcRows + t], t, rz);
+  float r = plc_gru_row(w_in, xq_in, nin / 4, w_rec, xq_st, subias[kPlcUnits + t], subias[kPlcRows + kPlcUnits + t],
+                        kPlcUnits + t, rr);
+  float h = plc_gru_row(w_in, xq_in, nin / 4, w_rec, xq_st, subias[2 * kPlcUnits + t],
+                        subias[kPlcRows + 2 * kPlcUnits + t], 2 * kPlcUnits + t, rh);
+  z = sigmoid_ref(z + rz, rcp);
+  r = sigmoid_ref(r + rr, rcp);
+  h = tanh_ref(h + rh * r, rcp);
+  const float nv = z * st + (1.f - z) * h;
+  __syncthreads();
+  state[t] = nv;
+  s_state[t] = nv;
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(256) plc_pred_kernel(PlcArgs A, int fg_pass) {
+  const int s = blockIdx.x, t = threadIdx.x, B = A.n_streams;
+  const uint8_t cls = A.masks[mCls * B + s];
+  int mode;   // 1 zeros, 2 burg only, 3 burg + features
+  if (fg_pass) {
+    if (cls != kFG) return;
+    mode = 2;
+  } else {
+    if (cls == kFG) return;
+    mode = cls == kG0 ? 3 : 1;
+  }
+  __shared__ float s_in[kPlcIn + 3], s_d1[kPlcCond], s_g1[kPlcUnits], s_g2[kPlcUnits];
+  __shared__ uint32_t xq_in[kPlcUnits / 4], xq_st[kPlcUnits / 4];
+  if (t < kPlcIn) {
+    float v = 0.f;
+    if (mode >= 2 && t < 2 * kBands) v = A.w.burg[(size_t)s * 2 * kBands + t];
+    else if (mode == 3 && t < 2 * kBands + 20) v = A.w.encf[(size_t)s * 36 + t - 2 * kBands];
+    else if (mode >= 2 && t == kPlcIn - 1) v = 1.f;
+    s_in[t] = v;
+  }
+  __syncthreads();
+  // _lpcnet_compute_dense, 57 -> 128, tanh: sgemv_accum16 = fmaf in input order from the bias
+  if (t < kPlcCond) {
+    float acc = __ldg(A.net.dense1_b + t);
+    for (int j = 0; j < kPlcIn; j++) acc = fmaf(__ldg(A.net.dense1_w + j * kPlcCond + t), s_in[j], acc);
+    s_d1[t] = tanh_ref(acc, A.rcp_tab);
+  }
+  __syncthreads();
+  plc_gru(A.net.g1_in, A.net.g1_rec, A.net.g1_subias, s_d1, kPlcCond, A.st.gru1 + (size_t)s * kPlcUnits, xq_in, xq_st,
+          s_g1, A.rcp_tab, t);
+  plc_gru(A.net.g2_in, A.net.g2_rec, A.net.g2_subias, s_g1, kPlcUnits, A.st.gru2 + (size_t)s * kPlcUnits, xq_in, xq_st,
+          s_g2, A.rcp_tab, t);
+  // plc_out, 256 -> 20, linear: 20 rows is not a multiple of 16, so the reference takes sgemv_accum's scalar
+  // loop (vec_avx.h:73-86 of nnet.c) -- separate multiply and add
+  if (t < 20) {
+    float acc = __ldg(A.net.out_b + t);
+    for (int j = 0; j < kPlcUnits; j++) acc += __ldg(A.net.out_w + j * 20 + t) * s_g2[j];
+    if (t == 19) acc = fminf(.5f, acc + .1f);
+    if (t == 0 && mode == 1) {
+      const int lc = A.lossc[s];
+      const float att[10] = {0, 0, -.2f, -.2f, -.4f, -.4f, -.8f, -.8f, -1.6f, -1.6f};
+      float v;
+      if (lc >= 10) v = acc + att[9] - (float)(2 * (lc - 9));
+      else v = acc + att[lc];
+      acc = fmaxf(-10.f, v);
+    }
+    A.st.features[(size_t)s * 20 + t] = acc;
+  }
+}
+
+// ---- small per-stream moves ----
+// frame-network input rows: `from_enc` streams take the analysis features, the others st->features
+__global__ void plc_gather_feat_kernel(PlcArgs A, int mask_row, int main_pass) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= A.n_streams * 20) return;
+  const int s = i / 20, k = i % 20;
+  if (!A.masks[mask_row * A.n_streams + s]) return;
+  const bool enc = main_pass && A.masks[mCls * A.n_streams + s] == kG0;
+  A.w.fnfeat[i] = enc ? A.w.encf[(size_t)s * 36 + k] : A.st.features[i];
+}
+
+// copies n shorts per stream for the streams of a mask row (optionally only those of one class)
+__global__ void plc_copy_kernel(const uint8_t *mask, const uint8_t *cls, int want_cls, int B, int n, short *dst,
+                                int dst_stride, int dst_off, const short *src, int src_stride, int src_off, int reverse) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * n) return;
+  const int s = i / n, k = i % n;
+  if (mask && !mask[s]) return;
+  if (cls && cls[s] != want_cls) return;
+  dst[(size_t)s * dst_stride + dst_off + k] = src[(size_t)s * src_stride + src_off + (reverse ? n - 1 - k : k)];
+}
+
+// snapshot / restore of the synthesis state (`copy = st->lpcnet`, `st->lpcnet = copy`), and clear_state
+__global__ void plc_state_copy_kernel(DevState dst, DevState src, const uint8_t *mask, int B) {
+  const int s = blockIdx.x, t = threadIdx.x;
+  if (!mask[s]) return;
+  for (int i = t; i < 2 * kConvIn; i += blockDim.x) dst.conv1_state[(size_t)s * 2 * kConvIn + i] = src.conv1_state[(size_t)s * 2 * kConvIn + i];
+  for (int i = t; i < 2 * kC; i += blockDim.x) dst.conv2_state[(size_t)s * 2 * kC + i] = src.conv2_state[(size_t)s * 2 * kC + i];
+  for (int i = t; i < kN; i += blockDim.x) dst.gru_a[(size_t)s * kN + i] = src.gru_a[(size_t)s * kN + i];
+  if (t < kNB) dst.gru_b[(size_t)s * kNB + t] = src.gru_b[(size_t)s * kNB + t];
+  if (t < 16) {
+    dst.last_sig[(size_t)s * 16 + t] = src.last_sig[(size_t)s * 16 + t];
+    dst.lpc[(size_t)s * 16 + t] = src.lpc[(size_t)s * 16 + t];
+  }
+  if (t < 4) dst.rng[(size_t)s * 4 + t] = src.rng[(size_t)s * 4 + t];
+  if (t == 0) {
+    dst.deemph[s] = src.deemph[s];
+    dst.last_exc[s] = src.last_exc[s];
+    dst.frame_count[s] = src.frame_count[s];
+  }
+}
+
+__global__ void plc_clear_state_kernel(DevState st, const uint8_t *mask, int B) {
+  const int s = blockIdx.x, t = threadIdx.x;
+  if (!mask[s]) return;
+  for (int i = t; i < kN; i += blockDim.x) st.gru_a[(size_t)s * kN + i] = 0.f;
+  if (t < kNB) st.gru_b[(size_t)s * kNB + t] = 0.f;
+  if (t < 16) st.last_sig[(size_t)s * 16 + t] = 0.f;
+  if (t == 0) { st.deemph[s] = 0.f; st.last_exc[s] = 128; }   // lin2ulaw(0.f)
+}
+
+// FG: after the 80 free samples (lpcnet_plc.c:385-402): keep them, redo the DC removal so that it accounts for
+// the synthesised 5 ms, and lay out the reversed frame for the backward pass
+__global__ void plc_fg_mid_kernel(PlcArgs A) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= A.n_streams || !A.masks[mFG * A.n_streams + s]) return;
+  short *pcm = A.st.pcm + (size_t)s * kFrame, *in = A.w.in + (size_t)s * kFrame, *lp = A.w.lp + (size_t)s * kFrame;
+  const short *syn = A.w.sego + (size_t)s * kTOff;   // an 80-sample segment: rows of 80
+  for (int i = 0; i < kTOff; i++) pcm[kFrame - kTOff + i] = syn[i];
+  if (A.remove_dc) {
+    double dc = A.w.mem_bak[s], sd = A.st.syn_dc[s];
+    for (int i = 0; i < kTOff; i++) sd += DC_CONST * ((double)pcm[kFrame - kTOff + i] - sd);
+    dc += sd;
+    A.w.delta[s] = (int)((double)A.w.delta[s] + sd);
+    A.st.syn_dc[s] = 0;
+    for (int i = 0; i < kFrame; i++) {
+      const short x = (short)(in[i] + lp[i]);
+      const short l = (short)(int)floor(.5 + dc);
+      dc += DC_CONST * ((double)x - dc);
+      lp[i] = l;
+      in[i] = (short)(x - l);
+    }
+    A.st.dc_mem[s] = dc;
+    for (int i = 0; i < kFrame; i++) A.w.save[(size_t)s * kFrame + i] = in[i];
+  }
+  for (int i = 0; i < kFrame; i++) A.w.segf[(size_t)s * kFrame + i] = in[kFrame - 1 - i];
+}
+
+// FG: cross-fade of the forward and the backward synthesis, and the queued update (lpcnet_plc.c:403-419)
+__global__ void plc_fg_end_kernel(PlcArgs A) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= A.n_streams || !A.masks[mFG * A.n_streams + s]) return;
+  short *pcm = A.st.pcm + (size_t)s * kFrame;
+  const short *rev = A.w.sego2 + (size_t)s * kTOff, *in = A.w.in + (size_t)s * kFrame;
+  const int delta = A.w.delta[s];
+  for (int i = 0; i < kTOff; i++) {
+    const float w = A.fade[i];
+    const float a = w * (float)pcm[kFrame - 1 - i];
+    const float b = (1.f - w) * (float)(rev[i] + delta);
+    pcm[kFrame - 1 - i] = (short)(int)floor((.5 + (double)a) + (double)b);
+  }
+  short *q = A.st.queued + (size_t)s * kFrame;
+  for (int i = 0; i < kTOff; i++) q[i] = pcm[kFrame - kTOff + i];
+  for (int i = 0; i < kFrame - kTOff; i++) q[kTOff + i] = in[i];
+}
+
+// main pass, the teacher-forcing input of the two 80-sample segments
+__global__ void plc_seg_prep_kernel(PlcArgs A, int second) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= A.n_streams * kTOff) return;
+  const int s = i / kTOff, k = i % kTOff;
+  const uint8_t cls = A.masks[mCls * A.n_streams + s];
+  short v = 0;
+  if (!second) { if (cls == kG0 || cls == kL0) v = A.st.pcm[(size_t)s * kFrame + kTOff + k]; }
+  else if (cls == kG0) v = A.w.in[(size_t)s * kFrame + k];
+  A.w.segf[(size_t)s * kTOff + k] = v;
+}
+
+// lost streams after the two segments, before the analysis (lpcnet_plc.c:460-471)
+__global__ void plc_lost_mid_kernel(PlcArgs A) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= A.n_streams) return;
+  const uint8_t cls = A.masks[mCls * A.n_streams + s];
+  if (cls != kL0 && cls != kL1) return;
+  short *pcm = A.st.pcm + (size_t)s * kFrame, *out = A.w.out + (size_t)s * kFrame;
+  const short *a = A.w.sego + (size_t)s * kTOff, *b = A.w.sego2 + (size_t)s * kTOff;
+  for (int i = 0; i < kTOff; i++) out[i] = cls == kL0 ? pcm[kTOff + i] : a[i];
+  for (int i = 0; i < kTOff; i++) out[kTOff + i] = b[i];
+  if (cls == kL1) for (int i = 0; i < kTOff; i++) pcm[kTOff + i] = out[i];
+}
+
+// end of the frame for every stream: outputs, buffers, DC (lpcnet_plc.c:436-446, 473-489)
+__global__ void plc_finish_kernel(PlcArgs A) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= A.n_streams) return;
+  const uint8_t cls = A.masks[mCls * A.n_streams + s];
+  short *pcm = A.st.pcm + (size_t)s * kFrame, *out = A.w.out + (size_t)s * kFrame;
+  short *dcb = A.st.dc_buf + (size_t)s * kTOff;
+  short *io = A.pcm_io + ((size_t)s * A.total_frames + A.frame) * kFrame;
+  if (cls == kG0 || cls == kFG) {
+    const short *in = A.w.in + (size_t)s * kFrame, *save = A.w.save + (size_t)s * kFrame, *lp = A.w.lp + (size_t)s * kFrame;
+    for (int i = 0; i < kTOff; i++) { out[kTOff + i] = in[i]; out[i] = pcm[kTOff + i]; }
+    for (int i = 0; i < kFrame; i++) pcm[i] = save[i];
+    if (A.remove_dc) {
+      for (int i = 0; i < kTOff; i++) out[i] = (short)(out[i] + dcb[i]);
+      for (int i = kTOff; i < kFrame; i++) out[i] = (short)(out[i] + lp[i - kTOff]);
+      for (int i = 0; i < kTOff; i++) dcb[i] = lp[kFrame - kTOff + i];
+    }
+  } else {
+    for (int i = 0; i < kTOff; i++) pcm[i] = out[kTOff + i];
+    if (A.remove_dc) {
+      const int dc = (int)floor(.5 + A.st.dc_mem[s]);
+      double sd = A.st.syn_dc[s];
+      for (int i = (cls == kL0 ? kTOff : 0); i < kFrame; i++) sd += DC_CONST * ((double)out[i] - sd);
+      A.st.syn_dc[s] = sd;
+      for (int i = 0; i < kTOff; i++) out[i] = (short)(out[i] + dcb[i]);
+      for (int i = kTOff; i < kFrame; i++) out[i] = (short)(out[i] + dc);
+      for (int i = 0; i < kTOff; i++) dcb[i] = (short)dc;
+    }
+  }
+  for (int i = 0; i < kFrame; i++) io[i] = out[i];
+}
+
+}  // namespace
+}  // namespace lpcb
+
+using namespace lpcb;
+
+// ---- host side ------------------------------------------------------------------------------------------------
+struct LPCNetPLCBatch {
+  int device = 0, n_streams = 0, options = 0, remove_dc = 0;
+  LPCNetBatch *syn = nullptr;           // synthesis engine: model, LPCNetState of every stream, sample kernel
+  LPCNetFeatureBatch *ana = nullptr;    // LPCNetEncState of every stream
+  void *alloc = nullptr;                // PLC state + per-frame scratch + state snapshot
+  PlcState st{};
+  PlcWork w{};
+  DevState snap{};
+  float *fft_scratch = nullptr;
+  float *fade = nullptr;
+  void *tab_alloc = nullptr;
+  DspTables tab{};
+  std::vector<int> loss_count;          // host mirrors of the control state (functions of the loss pattern only)
+  std::vector<uint8_t> queued;
+  void *d_io = nullptr; size_t d_io_bytes = 0;
+  void *d_ctl = nullptr; size_t d_ctl_bytes = 0;
+  long long frames_done = 0;
+};
+
+namespace {
+
+#define CKP(call)                                                                                      \
+  do {                                                                                                 \
+    cudaError_t e_ = (call);                                                                           \
+    if (e_ != cudaSuccess) return set_last_error(std::string(#call) + ": " + cudaGetErrorString(e_));  \
+  } while (0)
+
+int grow_dev(void **p, size_t *have, size_t want) {
+  if (*have >= want) return 0;
+  if (*p) cudaFree(*p);
+  *p = nullptr; *have = 0;
+  CKP(cudaMalloc(p, want));
+  *have = want;
+  return 0;
+}
+
+int plc_alloc(LPCNetPLCBatch *p) {
+  const size_t B = p->n_streams;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t r = off; off += (bytes + 255) & ~size_t(255); return r; };
+  const size_t o_pcm = take(B * kFrame * 2), o_feat = take(B * 20 * 4), o_g1 = take(B * kPlcUnits * 4),
+               o_g2 = take(B * kPlcUnits * 4), o_dc = take(B * 8), o_sd = take(B * 8), o_dcb = take(B * kTOff * 2),
+               o_q = take(B * kFrame * 2);
+  const size_t o_in = take(B * kFrame * 2), o_save = take(B * kFrame * 2), o_lp = take(B * kFrame * 2),
+               o_mb = take(B * 8), o_de = take(B * 4), o_burg = take(B * 36 * 4), o_e1 = take(B * 36 * 4),
+               o_e2 = take(B * 36 * 4), o_fn = take(B * 20 * 4), o_sf = take(B * kFrame * 2), o_so = take(B * kFrame * 2),
+               o_so2 = take(B * kFrame * 2), o_out = take(B * kFrame * 2);
+  const size_t o_c1 = take(B * 2 * kConvIn * 4), o_c2 = take(B * 2 * kC * 4), o_ga = take(B * kN * 4), o_gb = take(B * kNB * 4),
+               o_ls = take(B * 16 * 4), o_lpc = take(B * 16 * 4), o_rng = take(B * 16), o_dm = take(B * 4),
+               o_le = take(B * 4), o_fc = take(B * 4);
+  const size_t n_fft = ((2 * B + 63) / 64) * 64;   // one transform per (stream, half frame)
+  const size_t o_fft = take(n_fft * 640 * 4), o_fade = take(kTOff * 4);
+  CKP(cudaMalloc(&p->alloc, off));
+  CKP(cudaMemset(p->alloc, 0, off));
+  char *b = static_cast<char *>(p->alloc);
+  p->st.pcm = (short *)(b + o_pcm); p->st.features = (float *)(b + o_feat); p->st.gru1 = (float *)(b + o_g1);
+  p->st.gru2 = (float *)(b + o_g2); p->st.dc_mem = (double *)(b + o_dc); p->st.syn_dc = (double *)(b + o_sd);
+  p->st.dc_buf = (short *)(b + o_dcb); p->st.queued = (short *)(b + o_q);
+  p->w.in = (short *)(b + o_in); p->w.save = (short *)(b + o_save); p->w.lp = (short *)(b + o_lp);
+  p->w.mem_bak = (double *)(b + o_mb); p->w.delta = (int *)(b + o_de); p->w.burg = (float *)(b + o_burg);
+  p->w.encf = (float *)(b + o_e1); p->w.encf2 = (float *)(b + o_e2); p->w.fnfeat = (float *)(b + o_fn);
+  p->w.segf = (short *)(b + o_sf); p->w.sego = (short *)(b + o_so); p->w.sego2 = (short *)(b + o_so2);
+  p->w.out = (short *)(b + o_out);
+  p->snap.conv1_state = (float *)(b + o_c1); p->snap.conv2_state = (float *)(b + o_c2); p->snap.gru_a = (float *)(b + o_ga);
+  p->snap.gru_b = (float *)(b + o_gb); p->snap.last_sig = (float *)(b + o_ls); p->snap.lpc = (float *)(b + o_lpc);
+  p->snap.rng = (uint32_t *)(b + o_rng); p->snap.deemph = (float *)(b + o_dm); p->snap.last_exc = (int *)(b + o_le);
+  p->snap.frame_count = (int *)(b + o_fc);
+  p->fft_scratch = (float *)(b + o_fft);
+  p->fade = (float *)(b + o_fade);
+  // cross-fade weights, w = .5 - .5*cos(M_PI*i/TRAINING_OFFSET) as a float (lpcnet_plc.c:406), by the host's libm
+  float fade[kTOff];
+  for (int i = 0; i < kTOff; i++) fade[i] = (float)(.5 - .5 * cos(M_PI * i / (kTOff)));
+  CKP(cudaMemcpy(p->fade, fade, sizeof(fade), cudaMemcpyHostToDevice));
+  double pw[16];
+  for (int i = 0; i < 16; i++) pw[i] = pow(.995, i + 1);
+  CKP(cudaMemcpyToSymbol(c_pow995, pw, sizeof(pw)));
+  // DSP tables (the model's copy lives inside the engine; a private copy keeps this file independent)
+  std::vector<float> tw, dct;
+  std::vector<int16_t> br;
+  host_dsp_tables(tw, br, dct);
+  const size_t t_tw = 0, t_dct = tw.size() * 4, t_br = t_dct + dct.size() * 4;
+  CKP(cudaMalloc(&p->tab_alloc, t_br + br.size() * 2));
+  char *tp = static_cast<char *>(p->tab_alloc);
+  CKP(cudaMemcpy(tp + t_tw, tw.data(), tw.size() * 4, cudaMemcpyHostToDevice));
+  CKP(cudaMemcpy(tp + t_dct, dct.data(), dct.size() * 4, cudaMemcpyHostToDevice));
+  CKP(cudaMemcpy(tp + t_br, br.data(), br.size() * 2, cudaMemcpyHostToDevice));
+  p->tab = DspTables{(const float *)(tp + t_tw), (const int16_t *)(tp + t_br), (const float *)(tp + t_dct)};
+  return 0;
+}
+
+// One call: n_frames frames of every stream, in lock step.  lost: [B][n_frames]; d_io: device [B][n_frames*160].
+int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int n_frames) {
+  const int B = p->n_streams;
+  BatchView V = batch_view(p->syn);
+  cudaStream_t cs = V.stream;
+  // classes, masks and loss counters of every frame (they depend on the loss pattern only)
+  const size_t lc_off = ((size_t)kNMasks * B + 15) & ~size_t(15);           // the uint16 counters sit aligned
+  const size_t per_frame = (lc_off + (size_t)B * 2 + 15) & ~size_t(15);
+  std::vector<uint8_t> ctl(per_frame * n_frames);
+  struct Any { bool q, upd, fg, main_, l1; };
+  std::vector<Any> any(n_frames);
+  for (int f = 0; f < n_frames; f++) {
+    uint8_t *m = ctl.data() + per_frame * f;
+    uint16_t *lc = reinterpret_cast<uint16_t *>(m + lc_off);
+    Any a{false, false, false, false, false};
+    for (int s = 0; s < B; s++) {
+      const bool is_lost = lost[(size_t)s * n_frames + f] != 0;
+      const int c = p->loss_count[s];
+      const uint8_t cls = is_lost ? (c == 0 ? kL0 : kL1) : (c == 0 ? kG0 : kFG);
+      const bool q = p->queued[s] != 0;
+      m[mCls * B + s] = cls;
+      m[mQ * B + s] = q;
+      m[fQ * B + s] = q ? 3 : 0;
+      m[mUpd * B + s] = !is_lost;
+      m[mFG * B + s] = cls == kFG;
+      m[fFgFree * B + s] = cls == kFG ? 1 : 0;
+      m[fFgForced * B + s] = cls == kFG ? 3 : 0;
+      m[mMain * B + s] = cls != kFG;
+      m[mL1 * B + s] = cls == kL1;
+      m[fA * B + s] = cls == kG0 || cls == kL0 ? 3 : (cls == kL1 ? 1 : 0);
+      m[fB * B + s] = cls == kG0 ? 3 : (cls == kFG ? 0 : 1);
+      lc[s] = (uint16_t)(c > 60000 ? 60000 : c);
+      a.q |= q; a.upd |= !is_lost; a.fg |= cls == kFG; a.main_ |= cls != kFG; a.l1 |= cls == kL1;
+      // process_queued_update runs at the start of both entry points; only the FG branch queues a new one
+      p->queued[s] = cls == kFG;
+      p->loss_count[s] = is_lost ? c + 1 : 0;
+    }
+    any[f] = a;
+  }
+  if (grow_dev(&p->d_ctl, &p->d_ctl_bytes, ctl.size())) return -1;
+  CKP(cudaMemcpyAsync(p->d_ctl, ctl.data(), ctl.size(), cudaMemcpyHostToDevice, cs));
+
+  PlcArgs A{};
+  A.st = p->st; A.w = p->w; A.lp = V.st; A.lp_copy = p->snap; A.net = V.model->d.plc; A.rcp_tab = V.model->d.rcp_tab;
+  A.tab = p->tab; A.fft_scratch = p->fft_scratch; A.fade = p->fade;
+  A.pcm_io = static_cast<short *>(p->d_io); A.n_streams = B; A.total_frames = n_frames; A.remove_dc = p->remove_dc;
+  const int tb = 128, gs = (B + tb - 1) / tb;
+  for (int f = 0; f < n_frames; f++) {
+    const uint8_t *M = static_cast<const uint8_t *>(p->d_ctl) + per_frame * f;
+    A.masks = M;
+    A.lossc = reinterpret_cast<const uint16_t *>(M + lc_off);
+    A.frame = f;
+    const Any a = any[f];
+    // Q: process_queued_update (lpcnet_plc.c:342-347)
+    if (a.q) {
+      plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, cs>>>(A, mQ, 0);
+      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mQ * B)) return -1;
+      if (batch_sample_segment(p->syn, kFrame, M + (size_t)fQ * B, p->st.queued, p->w.sego)) return -1;
+    }
+    if (a.upd) {
+      plc_pre_kernel<<<gs, tb, 0, cs>>>(A);
+      plc_burg_kernel<<<(2 * B + 63) / 64, 64, 0, cs>>>(A);
+      plc_burg_combine_kernel<<<(B * kBands + 255) / 256, 256, 0, cs>>>(A);
+    }
+    if (a.fg) {
+      plc_pred_kernel<<<B, 256, 0, cs>>>(A, 1);
+      plc_state_copy_kernel<<<B, 128, 0, cs>>>(p->snap, V.st, M + (size_t)mFG * B, B);
+      plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, cs>>>(A, mFG, 0);
+      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B)) return -1;
+      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fFgFree * B, nullptr, p->w.sego)) return -1;
+      plc_fg_mid_kernel<<<gs, tb, 0, cs>>>(A);
+      plc_clear_state_kernel<<<B, 128, 0, cs>>>(V.st, M + (size_t)mFG * B, B);
+      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B)) return -1;
+      if (batch_sample_segment(p->syn, kFrame, M + (size_t)fFgForced * B, p->w.segf, p->w.sego)) return -1;
+      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fFgFree * B, nullptr, p->w.sego2)) return -1;
+      plc_fg_end_kernel<<<gs, tb, 0, cs>>>(A);
+      plc_state_copy_kernel<<<B, 128, 0, cs>>>(V.st, p->snap, M + (size_t)mFG * B, B);
+      if (feature_batch_frame_masked(p->ana, p->st.pcm, M + (size_t)mFG * B, p->w.encf2, cs)) return -1;
+    }
+    if (a.upd && feature_batch_frame_masked(p->ana, p->w.in, M + (size_t)mUpd * B, p->w.encf, cs)) return -1;
+    if (a.main_) {
+      plc_pred_kernel<<<B, 256, 0, cs>>>(A, 0);
+      plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, cs>>>(A, mMain, 1);
+      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mMain * B)) return -1;
+      plc_seg_prep_kernel<<<(B * kTOff + 255) / 256, 256, 0, cs>>>(A, 0);
+      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fA * B, p->w.segf, p->w.sego)) return -1;
+      plc_seg_prep_kernel<<<(B * kTOff + 255) / 256, 256, 0, cs>>>(A, 1);
+      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fB * B, p->w.segf, p->w.sego2)) return -1;
+      plc_lost_mid_kernel<<<gs, tb, 0, cs>>>(A);
+      if (a.l1 && feature_batch_frame_masked(p->ana, p->st.pcm, M + (size_t)mL1 * B, p->w.encf2, cs)) return -1;
+    }
+    plc_finish_kernel<<<gs, tb, 0, cs>>>(A);
+    CKP(cudaGetLastError());
+    p->frames_done++;
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+LPCNetPLCBatch *lpcnet_plc_batch_create(const unsigned char *blob, int len, int n_streams, int device, int options,
+                                        float lpc_gamma) {
+  if ((options & 3) != 1) {
+    set_last_error("lpcnet_plc_batch_create: only LPCNET_PLC_NONCAUSAL (1), optionally | LPCNET_PLC_DC_FILTER (4), is built");
+    return nullptr;
+  }
+  LPCNetPLCBatch *p = new (std::nothrow) LPCNetPLCBatch();
+  if (!p) return nullptr;
+  p->n_streams = n_streams; p->options = options; p->remove_dc = !!(options & 4);
+  // the non-causal mode needs a no-lookahead model: FEATURES_DELAY 0 (lpcnet_plc.c:357-361)
+  p->syn = lpcnet_batch_create(blob, len, n_streams, device, 0, lpc_gamma);
+  if (!p->syn) { delete p; return nullptr; }
+  BatchView V = batch_view(p->syn);
+  p->device = V.device;
+  if (!V.model->has_plc) {
+    set_last_error("lpcnet_plc_batch_create: the blob has no plc_* arrays (lpcnet_plc_load_model would fail too)");
+    lpcnet_plc_batch_destroy(p);
+    return nullptr;
+  }
+  p->ana = lpcnet_feature_batch_create(n_streams, p->device);
+  if (!p->ana || plc_alloc(p)) { lpcnet_plc_batch_destroy(p); return nullptr; }
+  p->loss_count.assign(n_streams, 0);
+  p->queued.assign(n_streams, 0);
+  return p;
+}
+
+void lpcnet_plc_batch_destroy(LPCNetPLCBatch *p) {
+  if (!p) return;
+  if (p->syn) lpcnet_batch_sync(p->syn);
+  cudaFree(p->alloc); cudaFree(p->tab_alloc); cudaFree(p->d_io); cudaFree(p->d_ctl);
+  if (p->ana) lpcnet_feature_batch_destroy(p->ana);
+  if (p->syn) lpcnet_batch_destroy(p->syn);
+  delete p;
+}
+
+int lpcnet_plc_batch_n_streams(const LPCNetPLCBatch *p) { return p ? p->n_streams : 0; }
+
+int lpcnet_plc_batch_set_seed(LPCNetPLCBatch *p, int stream, const unsigned char *data, int n) {
+  if (!p) return set_last_error("null PLC batch");
+  return lpcnet_batch_set_seed(p->syn, stream, data, n);
+}
+
+long long lpcnet_plc_batch_launch_count(const LPCNetPLCBatch *p) {
+  return p ? lpcnet_batch_launch_count(p->syn) + lpcnet_feature_batch_launch_count(p->ana) + 12 * p->frames_done : 0;
+}
+
+int lpcnet_plc_batch_process(LPCNetPLCBatch *p, const unsigned char *lost, short *pcm, int n_frames) {
+  if (!p || !lost || !pcm || n_frames < 0) return set_last_error("lpcnet_plc_batch_process: bad arguments");
+  if (n_frames == 0) return 0;
+  CKP(cudaSetDevice(p->device));
+  const size_t bytes = (size_t)p->n_streams * n_frames * kFrame * 2;
+  if (grow_dev(&p->d_io, &p->d_io_bytes, bytes)) return -1;
+  cudaStream_t cs = batch_view(p->syn).stream;
+  CKP(cudaMemcpyAsync(p->d_io, pcm, bytes, cudaMemcpyHostToDevice, cs));
+  if (plc_run(p, lost, n_frames)) return -1;
+  CKP(cudaMemcpyAsync(pcm, p->d_io, bytes, cudaMemcpyDeviceToHost, cs));
+  CKP(cudaStreamSynchronize(cs));
+  return 0;
+}
+
+// observable frame-rate state of one stream (tests): st->features[0..20), the predictor's GRU states, dc_mem, syn_dc
+int lpcnet_plc_batch_peek(LPCNetPLCBatch *p, int stream, float *features20, float *gru1, float *gru2, double *dc2) {
+  if (!p || stream < 0 || stream >= p->n_streams) return set_last_error("lpcnet_plc_batch_peek: bad arguments");
+  CKP(cudaSetDevice(p->device));
+  CKP(cudaStreamSynchronize(batch_view(p->syn).stream));
+  const size_t s = stream;
+  if (features20) CKP(cudaMemcpy(features20, p->st.features + s * 20, 20 * 4, cudaMemcpyDeviceToHost));
+  if (gru1) CKP(cudaMemcpy(gru1, p->st.gru1 + s * kPlcUnits, kPlcUnits * 4, cudaMemcpyDeviceToHost));
+  if (gru2) CKP(cudaMemcpy(gru2, p->st.gru2 + s * kPlcUnits, kPlcUnits * 4, cudaMemcpyDeviceToHost));
+  if (dc2) {
+    CKP(cudaMemcpy(dc2, p->st.dc_mem + s, 8, cudaMemcpyDeviceToHost));
+    CKP(cudaMemcpy(dc2 + 1, p->st.syn_dc + s, 8, cudaMemcpyDeviceToHost));
+  }
+  return 0;
+}
+
+// the last frame's Burg cepstrum and analysis features of one stream (tests)
+int lpcnet_plc_batch_peek_frame(LPCNetPLCBatch *p, int stream, float *burg36, float *enc36) {
+  if (!p || stream < 0 || stream >= p->n_streams) return set_last_error("lpcnet_plc_batch_peek_frame: bad arguments");
+  CKP(cudaSetDevice(p->device));
+  CKP(cudaStreamSynchronize(batch_view(p->syn).stream));
+  const size_t s = stream;
+  if (burg36) CKP(cudaMemcpy(burg36, p->w.burg + s * 36, 36 * 4, cudaMemcpyDeviceToHost));
+  if (enc36) CKP(cudaMemcpy(enc36, p->w.encf + s * 36, 36 * 4, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+// ---- the reference's single-stream PLC API (include/lpcnet.h:190-215), non-causal mode ----
+struct LPCNetPLCState {
+  uint32_t magic;
+  int options;
+  LPCNetPLCBatch *batch;
+};
+static const uint32_t kPlcMagic = 0x4C50504Cu;
+
+int lpcnet_plc_get_size(void) { return (int)sizeof(LPCNetPLCState); }
+
+int lpcnet_plc_init(LPCNetPLCState *st, int options) {
+  if (!st) return -1;
+  st->magic = kPlcMagic; st->options = options; st->batch = nullptr;
+  if ((options & 3) != 1) {
+    set_last_error("lpcnet_plc_init: only LPCNET_PLC_NONCAUSAL (1), optionally | LPCNET_PLC_DC_FILTER (4), is built");
+    return -1;
+  }
+  return 0;
+}
+
+LPCNetPLCState *lpcnet_plc_create(int options) {
+  LPCNetPLCState *st = static_cast<LPCNetPLCState *>(calloc(1, sizeof(LPCNetPLCState)));
+  if (st) lpcnet_plc_init(st, options);
+  return st;
+}
+
+void lpcnet_plc_destroy(LPCNetPLCState *st) {
+  if (!st) return;
+  if (st->magic == kPlcMagic && st->batch) lpcnet_plc_batch_destroy(st->batch);
+  free(st);
+}
+
+int lpcnet_plc_load_model(LPCNetPLCState *st, const unsigned char *data, int len) {
+  if (!st || st->magic != kPlcMagic) return set_last_error("lpcnet_plc_load_model: state not initialised");
+  if (st->batch) { lpcnet_plc_batch_destroy(st->batch); st->batch = nullptr; }
+  st->batch = lpcnet_plc_batch_create(data, len, 1, 0, st->options, 1.0f);
+  return st->batch ? 0 : -1;
+}
+
+int lpcnet_plc_update(LPCNetPLCState *st, short *pcm) {
+  if (!st || st->magic != kPlcMagic || !st->batch) return set_last_error("lpcnet_plc_update: no model loaded");
+  const unsigned char lost = 0;
+  return lpcnet_plc_batch_process(st->batch, &lost, pcm, 1);
+}
+
+int lpcnet_plc_conceal(LPCNetPLCState *st, short *pcm) {
+  if (!st || st->magic != kPlcMagic || !st->batch) return set_last_error("lpcnet_plc_conceal: no model loaded");
+  const unsigned char lost = 1;
+  return lpcnet_plc_batch_process(st->batch, &lost, pcm, 1);
+}
+
+}  // extern "C"

@@ -679,7 +679,8 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               const float dm = s_deemph[s];
               float pcm;
               int forced_v = 0;
-              if (A.forced) {
+              const bool teach = A.forced && (!A.forced_by_flag || (act & 2));
+              if (teach) {
                 forced_v = A.forced[oidx];
                 const float fo = (float)forced_v;
                 exc = lin2ulaw_ref(fo - 0.85f * dm - t_pred);
@@ -693,7 +694,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               const float dm_new = out;
               if (out < -32767.f) out = -32767.f;
               if (out > 32767.f) out = 32767.f;
-              const int outv = A.forced ? forced_v : round_half_up_ref(out);
+              const int outv = teach ? forced_v : round_half_up_ref(out);
               if (l16 == 0 && valid) {
                 if (act) {
                   s_lexc[s] = exc;

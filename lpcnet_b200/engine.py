@@ -49,6 +49,10 @@ EXPORTED_SYMBOLS = [
     "lpcnet_feature_batch_create", "lpcnet_feature_batch_destroy", "lpcnet_feature_batch_n_streams",
     "lpcnet_feature_batch_launch_count", "lpcnet_feature_batch_reset", "lpcnet_feature_batch_compute",
     "lpcnet_feature_batch_compute_float", "lpcnet_feature_batch_compute_device",
+    "lpcnet_plc_get_size", "lpcnet_plc_init", "lpcnet_plc_create", "lpcnet_plc_destroy", "lpcnet_plc_load_model",
+    "lpcnet_plc_update", "lpcnet_plc_conceal", "lpcnet_plc_batch_create", "lpcnet_plc_batch_destroy",
+    "lpcnet_plc_batch_n_streams", "lpcnet_plc_batch_set_seed", "lpcnet_plc_batch_launch_count",
+    "lpcnet_plc_batch_process", "lpcnet_plc_batch_peek", "lpcnet_plc_batch_peek_frame",
 ]
 
 _lib = None
@@ -123,6 +127,22 @@ def load_library() -> C.CDLL:
     L.lpcnet_feature_batch_compute.argtypes = [vp, vp, ci, vp]
     L.lpcnet_feature_batch_compute_float.argtypes = [vp, vp, ci, vp]
     L.lpcnet_feature_batch_compute_device.argtypes = [vp, vp, vp, ci, vp, vp]
+    L.lpcnet_plc_create.restype = vp
+    L.lpcnet_plc_create.argtypes = [ci]
+    L.lpcnet_plc_destroy.argtypes = [vp]
+    L.lpcnet_plc_load_model.argtypes = [vp, vp, ci]
+    L.lpcnet_plc_update.argtypes = [vp, vp]
+    L.lpcnet_plc_conceal.argtypes = [vp, vp]
+    L.lpcnet_plc_batch_create.restype = vp
+    L.lpcnet_plc_batch_create.argtypes = [vp, ci, ci, ci, ci, cf]
+    L.lpcnet_plc_batch_destroy.argtypes = [vp]
+    L.lpcnet_plc_batch_n_streams.argtypes = [vp]
+    L.lpcnet_plc_batch_set_seed.argtypes = [vp, ci, C.c_char_p, ci]
+    L.lpcnet_plc_batch_launch_count.restype = C.c_longlong
+    L.lpcnet_plc_batch_launch_count.argtypes = [vp]
+    L.lpcnet_plc_batch_process.argtypes = [vp, vp, vp, ci]
+    L.lpcnet_plc_batch_peek.argtypes = [vp, ci, vp, vp, vp, vp]
+    L.lpcnet_plc_batch_peek_frame.argtypes = [vp, ci, vp, vp]
     _lib = L
     return L
 
@@ -448,3 +468,90 @@ class Encoder:
             _check(self.L.lpcnet_compute_single_frame_features_float(self.h, _p(x), _p(out)),
                    "lpcnet_compute_single_frame_features_float")
         return out
+
+
+PLC_NONCAUSAL = 1
+PLC_DC_FILTER = 4
+
+
+class PLCBatch:
+    """Batched packet-loss concealment (non-causal mode): n_streams PLC states, each with its own loss pattern."""
+
+    def __init__(self, blob: bytes, n_streams: int, options: int = PLC_NONCAUSAL, device: int = 0,
+                 lpc_gamma: float = 1.0):
+        self.L = load_library()
+        self.n_streams = n_streams
+        self._blob = np.frombuffer(blob, np.uint8)
+        self.h = self.L.lpcnet_plc_batch_create(_p(self._blob), len(blob), n_streams, device, options, lpc_gamma)
+        if not self.h:
+            raise LPCNetError(f"lpcnet_plc_batch_create: {last_error()}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.lpcnet_plc_batch_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def set_seed(self, stream: int, seed: bytes):
+        _check(self.L.lpcnet_plc_batch_set_seed(self.h, stream, seed, len(seed)), "lpcnet_plc_batch_set_seed")
+
+    @property
+    def launch_count(self):
+        return int(self.L.lpcnet_plc_batch_launch_count(self.h))
+
+    def peek(self, stream: int):
+        """(features[20], gru1[256], gru2[256], [dc_mem, syn_dc]) of one stream."""
+        f = np.zeros(20, np.float32); g1 = np.zeros(256, np.float32); g2 = np.zeros(256, np.float32)
+        dc = np.zeros(2, np.float64)
+        _check(self.L.lpcnet_plc_batch_peek(self.h, stream, _p(f), _p(g1), _p(g2), _p(dc)), "lpcnet_plc_batch_peek")
+        return f, g1, g2, dc
+
+    def peek_frame(self, stream: int):
+        burg = np.zeros(36, np.float32); enc = np.zeros(36, np.float32)
+        _check(self.L.lpcnet_plc_batch_peek_frame(self.h, stream, _p(burg), _p(enc)), "lpcnet_plc_batch_peek_frame")
+        return burg, enc
+
+    def process(self, pcm, lost):
+        """pcm int16 [n_streams][n_frames*160], lost [n_streams][n_frames] -> concealed int16, same shape."""
+        out = np.ascontiguousarray(pcm, np.int16).copy()
+        lost = np.ascontiguousarray(lost, np.uint8)
+        assert out.shape[0] == self.n_streams and lost.shape[0] == self.n_streams
+        n_frames = lost.shape[1]
+        assert out.shape[1] == n_frames * FRAME_SIZE
+        out.reshape(self.n_streams, n_frames, FRAME_SIZE)[lost != 0] = 0     # a lost frame carries no input
+        _check(self.L.lpcnet_plc_batch_process(self.h, _p(lost), _p(out), n_frames), "lpcnet_plc_batch_process")
+        return out
+
+
+class PLC:
+    """lpcnet_plc_create + lpcnet_plc_load_model + lpcnet_plc_update / lpcnet_plc_conceal (include/lpcnet.h:190-215)."""
+
+    def __init__(self, blob: bytes, options: int = PLC_NONCAUSAL):
+        self.L = load_library()
+        self.h = self.L.lpcnet_plc_create(options)
+        self._blob = np.frombuffer(blob, np.uint8)
+        if self.L.lpcnet_plc_load_model(self.h, _p(self._blob), len(blob)) != 0:
+            err = last_error()
+            self.L.lpcnet_plc_destroy(self.h)
+            self.h = None
+            raise LPCNetError(f"lpcnet_plc_load_model: {err}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.lpcnet_plc_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def update(self, pcm):
+        x = np.ascontiguousarray(pcm, np.int16).copy()
+        _check(self.L.lpcnet_plc_update(self.h, _p(x)), "lpcnet_plc_update")
+        return x
+
+    def conceal(self):
+        x = np.zeros(FRAME_SIZE, np.int16)
+        _check(self.L.lpcnet_plc_conceal(self.h, _p(x)), "lpcnet_plc_conceal")
+        return x

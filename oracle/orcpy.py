@@ -254,6 +254,14 @@ class OrcPLC:
             self.m.L.lib.orc_plc_free(self.h)
             self.h = None
 
+    def peek(self):
+        L = self.m.L.lib
+        L.orc_plc_peek.argtypes = [C.c_void_p] * 6
+        f = np.zeros(20, np.float32); g1 = np.zeros(256, np.float32); g2 = np.zeros(256, np.float32)
+        lc = np.zeros(1, np.int32); dc = np.zeros(2, np.float64)
+        L.orc_plc_peek(self.h, _p(f), _p(g1), _p(g2), _p(lc), _p(dc))
+        return f, g1, g2, dc
+
     def run(self, pcm, lost):
         """pcm int16 [n_frames*160], lost bool [n_frames] -> concealed output int16 [n_frames*160]
         (the non-causal mode delays the signal by 80 samples)."""

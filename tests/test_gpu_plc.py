@@ -1,0 +1,102 @@
+"""Parity of the CUDA packet-loss concealment (lpcnet_plc_batch_*, lpcnet_plc_update / _conceal; through the C-ABI)
+against the golden vectors of the unmodified reference (tests/golden/plc.npz, FEATURES_DELAY 0 build) and the CPU
+oracle.  The output is PCM (int16): the bar is bit-exact, streams under different loss patterns side by side."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+from lpcnet_b200 import blob, engine
+from oracle import orcpy
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.fixture(scope="module")
+def eng(engine_lib):
+    assert engine.device_count() > 0, "no CUDA device: the gpu tests cannot run (there is no CPU fallback)"
+    return engine
+
+
+@pytest.fixture(scope="module")
+def plc_blob():
+    A = blob.random_model()
+    A.update(blob.random_plc_model())
+    return blob.write_blob(A)
+
+
+@pytest.fixture(scope="module")
+def plc_model(plc_blob):
+    return orcpy.OrcModel(orcpy.OrcLib(), plc_blob, 0, 1.0, None)
+
+
+def first_diff(got, want):
+    d = np.nonzero(got != want)
+    return None if d[0].size == 0 else tuple(int(v[0]) for v in d)
+
+
+@pytest.mark.parametrize("opt", [1, 5])
+def test_golden_vectors_of_the_reference(eng, plc_blob, opt):
+    g = np.load(os.path.join(HERE, "golden", "plc.npz"))
+    assert hashlib.sha256(plc_blob).digest() == g["blob_sha256"].tobytes()
+    pcm = np.stack([g[f"in_{opt}_{s}"] for s in range(3)])
+    lost = np.stack([g[f"lost_{opt}_{s}"] for s in range(3)])
+    want = np.stack([g[f"out_{opt}_{s}"] for s in range(3)])
+    pb = eng.PLCBatch(plc_blob, 3, opt)
+    for s in range(3):
+        pb.set_seed(s, blob.stream_seed(s))
+    got = pb.process(pcm, lost)
+    assert pb.launch_count > 0
+    pb.close()
+    assert first_diff(got, want) is None, ("first difference (stream, sample)", first_diff(got, want))
+
+
+def test_call_splitting_and_single_stream_api(eng, plc_blob):
+    g = np.load(os.path.join(HERE, "golden", "plc.npz"))
+    x, lost, want = g["in_1_0"], g["lost_1_0"], g["out_1_0"]
+    # frame by frame through the reference's own entry points (stream 0 = the default "LPCNet" seed)
+    plc = eng.PLC(plc_blob, 1)
+    out = []
+    for f in range(len(lost)):
+        out.append(plc.conceal() if lost[f] else plc.update(x[f * 160:(f + 1) * 160]))
+    plc.close()
+    assert first_diff(np.concatenate(out), want) is None
+    # the same in three batched calls of 7 + 1 + 32 frames
+    pb = eng.PLCBatch(plc_blob, 1, 1)
+    parts = [pb.process(x[None, a * 160:b * 160], lost[None, a:b]) for a, b in ((0, 7), (7, 8), (8, 40))]
+    pb.close()
+    assert first_diff(np.concatenate(parts, axis=1)[0], want) is None
+
+
+def test_many_streams_against_the_oracle(eng, plc_blob, plc_model):
+    """96 streams x 30 frames with the DC filter, every stream under its own Gilbert loss pattern (long bursts for
+    some): a sample of streams against the oracle, and batch invariance for the rest."""
+    B, F, opt = 96, 30, 5
+    pcm = np.stack([np.clip(blob.synthetic_pcm(F, 100 + s).astype(np.int32) + 300 * (s % 5), -32768, 32767).astype(np.int16)
+                    for s in range(B)])
+    lost = np.stack([blob.synthetic_loss_pattern(F, s, 0.6 + 0.3 * (s % 3 == 0), 0.12) for s in range(B)])
+    assert lost.sum() > B
+    pb = eng.PLCBatch(plc_blob, B, opt)
+    for s in range(B):
+        pb.set_seed(s, blob.stream_seed(s))
+    got = pb.process(pcm, lost)
+    pb.close()
+    for s in (0, 1, 17, 48, 95):
+        want = orcpy.OrcPLC(plc_model, opt, blob.stream_seed(s)).run(pcm[s], lost[s])
+        assert first_diff(got[s], want) is None, (s, first_diff(got[s], want))
+    pick = [3, 50, 77]
+    small = eng.PLCBatch(plc_blob, len(pick), opt)
+    for i, s in enumerate(pick):
+        small.set_seed(i, blob.stream_seed(s))
+    again = small.process(pcm[pick], lost[pick])
+    small.close()
+    assert first_diff(again, got[pick]) is None
+
+
+def test_unsupported_modes_and_models_are_errors(eng, plc_blob, model_blob):
+    with pytest.raises(engine.LPCNetError):
+        eng.PLCBatch(plc_blob, 2, 0)            # causal mode is not built
+    with pytest.raises(engine.LPCNetError):
+        eng.PLCBatch(model_blob, 2, 1)          # no plc_* arrays in the blob
