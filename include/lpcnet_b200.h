@@ -216,6 +216,25 @@ LPCNET_B200_EXPORT int lpcnet_feature_batch_compute_device(LPCNetFeatureBatch *b
                                                            const float *d_pcmf, int n_frames, float *d_features,
                                                            void *cuda_stream);
 
+/* 1.6 kb/s encoder, the wire format's other half.  The reference's entry points
+ * (include/lpcnet.h:98-131, src/lpcnet_enc.c:882-911): 640 samples -> LPCNET_COMPRESSED_SIZE (8) bytes
+ * (lpcnet_encode), or -> 4 x 36 unquantised features with the superframe pitch tracker (lpcnet_compute_features;
+ * features = float[4][36]).  The reference links its VQ tables (ceps_codebooks.c) into the library; here they are
+ * given once per process (lpcnet_b200_set_codebooks: ceps_codebook1|2|3 [1024][17] then ceps_codebook_diff4
+ * [4096][18], 125952 floats, copied; encoder states created afterwards use them) or per batch. */
+LPCNET_B200_EXPORT int lpcnet_b200_set_codebooks(const float *codebooks, int n_floats);
+LPCNET_B200_EXPORT int lpcnet_encode(LPCNetEncState *st, const short *pcm, unsigned char *buf);
+LPCNET_B200_EXPORT int lpcnet_compute_features(LPCNetEncState *st, const short *pcm, float *features);
+/* Batched: pcm [n_streams][n_packets*640] -> packets [n_streams][n_packets][8]; quantised_features (nullable)
+ * [n_streams][n_packets*4][36] receives the encoder's quantised rows, entries [0..20) (= what lpcnet_decode's
+ * decode_packet rebuilds from the packet; entries [20..36) hold the LPC of the unquantised cepstrum). */
+LPCNET_B200_EXPORT int lpcnet_feature_batch_set_codebooks(LPCNetFeatureBatch *b, const float *codebooks, int n_floats);
+LPCNET_B200_EXPORT int lpcnet_feature_batch_encode(LPCNetFeatureBatch *b, const short *pcm, int n_packets,
+                                                   unsigned char *packets, float *quantised_features);
+/* lpcnet_compute_features batched: features [n_streams][n_packets*4][36]. */
+LPCNET_B200_EXPORT int lpcnet_feature_batch_compute_features(LPCNetFeatureBatch *b, const short *pcm, int n_packets,
+                                                             float *features);
+
 /* ------------------------------------------------------------------------------------
  * 4. Packet-loss concealment, non-causal mode (BASELINE config 4)
  * ------------------------------------------------------------------------------------ */

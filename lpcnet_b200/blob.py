@@ -272,3 +272,13 @@ def synthetic_loss_pattern(n_frames: int, stream: int = 0, p_stay: float = 0.6, 
         lost[f] = state
     lost[:3] = False
     return lost
+
+
+def synthetic_codebooks(seed: int = 99) -> np.ndarray:
+    """Synthetic VQ codebooks for the 1.6 kb/s codec (the real ceps_codebooks.c ships in the model tarball, which is
+    not available offline): ceps_codebook1/2/3 [1024][17] and ceps_codebook_diff4 [4096][18] (lpcnet_private.h:109-112),
+    N(0, 0.3^2), concatenated -- the same values oracle/gen_codebooks.py compiles into the reference build."""
+    rng = np.random.default_rng(seed)
+    cb = [rng.standard_normal(1024 * 17) * 0.3 for _ in range(3)]
+    cb.append(rng.standard_normal(4096 * 18) * 0.3)
+    return np.concatenate([c.astype(np.float32) for c in cb])

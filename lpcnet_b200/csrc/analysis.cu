@@ -15,6 +15,7 @@
 // are bit-identical to the reference's parity build; log10() is evaluated in double as there.
 #include <math.h>
 
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -37,6 +38,7 @@ struct EncState {        // per stream, device
   float *path;           // [B][256]  pitch_max_path[0]
   float *path_all;       // [B]
   int *best_i;           // [B]
+  float *vq_mem;         // [B][18]   the encoder's vq_mem (superframe quantisation only)
 };
 
 struct AnalysisArgs {
@@ -52,7 +54,18 @@ struct AnalysisArgs {
   float *S;                   // [B][1 + 160F]    previous residual | LPC residual
   float *fft_scratch;         // [320][2][B*F]
   const uint8_t *stream_mask; // nullable [B]: streams with 0 keep their state and their feature rows
+  // superframe modes (lpcnet_encode / lpcnet_compute_features, lpcnet_enc.c:882-911): frames come in packets of four
+  int quantize;               // 1: process_superframe(encode = quantize = 1), 0: (0, 0)
+  int *ids;                   // [B][total_frames/4][kIds] bit-field values of the packet (quantize mode)
+  const float *pitch_pow;     // [64] (float)(pow(2.f, main_pitch/21.)*PITCH_MIN_PERIOD), by the host's libm
 };
+
+constexpr int kIds = 10;      // c0_id+64, main_pitch, modulation field, corr_id, vq_end[3], vq_mid, interp_id, (spare)
+
+// (int)x of the reference build for a double that may be NaN or out of range: x86 cvttsd2si gives INT_MIN
+__device__ __forceinline__ int cvt_x86(double v) {
+  return (v != v || v >= 2147483648.0 || v <= -2147483649.0) ? (int)0x80000000 : (int)v;
+}
 
 __device__ __forceinline__ float pcm_at(const AnalysisArgs &A, int s, int n) {
   const size_t i = (size_t)s * A.total_frames * kFrame + (size_t)A.frame0 * kFrame + n;
@@ -153,22 +166,26 @@ __global__ void residual_kernel(AnalysisArgs A) {
   }
 }
 
-// The pitch half of compute_frame_features (lpcnet_enc.c:540-576) and process_single_frame (814-870); one block
-// per stream, thread t = lag t.
+// The pitch half of compute_frame_features (lpcnet_enc.c:540-576) and the Viterbi pass over half-frames; one block
+// per stream, thread t = lag t.  SUPER = false: process_single_frame (814-870), two half-frames per frame.
+// SUPER = true: process_superframe (579-743), eight half-frames per packet of four frames, then the pitch contour
+// regression and -- in quantize mode -- the pitch / correlation fields of the packet.
 constexpr int kPT = 256;
+template <bool SUPER>
 __global__ void __launch_bounds__(kPT) pitch_kernel(AnalysisArgs A) {
+  constexpr int NR = SUPER ? 8 : 2;         // correlation rows (half-frames) per Viterbi pass
   extern __shared__ float sm[];
   const int s = blockIdx.x, t = threadIdx.x, F = A.n_frames, L = F * kFrame;
   if (A.stream_mask && !A.stream_mask[s]) return;
   float *ebuf = sm;                         // [256 + L]
-  float *xc = ebuf + kPMax + L;             // [2][256]
-  float *path0 = xc + 2 * kPMax;            // [256]
+  float *xc = ebuf + kPMax + L;             // [NR][256]
+  float *path0 = xc + NR * kPMax;           // [256]
   float *path1 = path0 + kPMax;             // [256]
   double *ener1 = reinterpret_cast<double *>(path1 + kPMax);   // [256]
-  int *prev = reinterpret_cast<int *>(ener1 + kPMax);          // [2][256]
-  float *redv = reinterpret_cast<float *>(prev + 2 * kPMax);   // [8]
+  int *prev = reinterpret_cast<int *>(ener1 + kPMax);          // [NR][256]
+  float *redv = reinterpret_cast<float *>(prev + NR * kPMax);  // [8]
   int *redi = reinterpret_cast<int *>(redv + 8);               // [8]
-  __shared__ float ener0_s[2];
+  __shared__ float ener0_s[NR];
   __shared__ float path_all_s;
   __shared__ int best_i_s;
 
@@ -181,7 +198,9 @@ __global__ void __launch_bounds__(kPT) pitch_kernel(AnalysisArgs A) {
   __syncthreads();
 
   for (int f = 0; f < F; f++) {
+    const int r0 = SUPER ? 2 * (f & 3) : 0;   // rows 2+2*pcount+sub of the reference's xc / frame_weight
     for (int sub = 0; sub < 2; sub++) {
+      const int row = r0 + sub;
       const float *ys = ebuf + f * kFrame + sub * (kFrame / 2), *xs = ys + kPMax;
       // celt_pitch_xcorr (pitch.c:43-83, pitch.h:42-105): every lag is a j-ascending sum from zero
       float acc = 0;
@@ -199,17 +218,17 @@ __global__ void __launch_bounds__(kPT) pitch_kernel(AnalysisArgs A) {
       } else if (t == 32) {
         float e0 = 0;
         for (int j = 0; j < kFrame / 2; j++) e0 = e0 + xs[j] * xs[j];
-        ener0_s[sub] = e0;
+        ener0_s[row] = e0;
       }
       __syncthreads();
-      const float ener = (float)((double)(1 + ener0_s[sub]) + ener1[t]);
-      xc[sub * kPMax + t] = 2 * acc / ener;
+      const float ener = (float)((double)(1 + ener0_s[row]) + ener1[t]);
+      xc[row * kPMax + t] = 2 * acc / ener;
       __syncthreads();
       // 3x upsampled correlation, keep the max (lpcnet_enc.c:552-569)
       float up = 0.f;
       if (t >= 4 && t < kPMax - 4) {
         const float interp[7] = {0.026184f, -0.098339f, 0.369938f, 0.837891f, -0.184969f, 0.070242f, -0.020947f};
-        const float *c = xc + sub * kPMax;
+        const float *c = xc + row * kPMax;
         float v1 = 0, v2 = 0;
 #pragma unroll
         for (int j = 0; j < 7; j++) {
@@ -219,15 +238,19 @@ __global__ void __launch_bounds__(kPT) pitch_kernel(AnalysisArgs A) {
         up = fmaxf(c[t], fmaxf(v1, v2));
       }
       __syncthreads();
-      if (t >= 4 && t < kPMax - 4) xc[sub * kPMax + t] = up;
+      if (t >= 4 && t < kPMax - 4) xc[row * kPMax + t] = up;
     }
     __syncthreads();
-    // process_single_frame (lpcnet_enc.c:814-870)
+    if (SUPER && (f & 3) != 3) continue;      // the superframe pass runs after the packet's fourth frame
+    // process_single_frame (lpcnet_enc.c:814-870) / process_superframe (579-630): the same pass over 2 / 8 rows
     float fws = 1e-15f;
-    fws += ener0_s[0];
-    fws += ener0_s[1];
-    const float fw[2] = {ener0_s[0] * (2.f / fws), ener0_s[1] * (2.f / fws)};
-    for (int sub = 0; sub < 2; sub++) {
+#pragma unroll
+    for (int r = 0; r < NR; r++) fws += ener0_s[r];
+    float fw[NR];
+#pragma unroll
+    for (int r = 0; r < NR; r++) fw[r] = ener0_s[r] * ((float)NR / fws);
+#pragma unroll
+    for (int sub = 0; sub < NR; sub++) {
       float *c = xc + sub * kPMax;
       // octave penalty: the values it compares against sit at higher lags than the one it scales
       float cv = c[t];
@@ -273,17 +296,75 @@ __global__ void __launch_bounds__(kPT) pitch_kernel(AnalysisArgs A) {
       __syncthreads();
     }
     if (t == 0) {
-      int bi = best_i_s, best[2];
+      int bi = best_i_s, best[NR];
       float frame_corr = 0;
-      for (int sub = 1; sub >= 0; sub--) {
+#pragma unroll
+      for (int sub = NR - 1; sub >= 0; sub--) {
         best[sub] = kPMax - bi;
         frame_corr += fw[sub] * xc[sub * kPMax + bi];
         bi = prev[sub * kPMax + bi];
       }
-      frame_corr /= 2;
-      float *out = A.features + ((size_t)s * A.total_frames + A.frame0 + f) * kNF;
-      out[kBands] = .01f * (float)(max(66, min(510, best[0] + best[1])) - 200);
-      out[kBands + 1] = frame_corr - .5f;
+      frame_corr /= (float)NR;
+      if (!SUPER) {
+        float *out = A.features + ((size_t)s * A.total_frames + A.frame0 + f) * kNF;
+        out[kBands] = .01f * (float)(max(66, min(510, best[0] + best[1])) - 200);
+        out[kBands + 1] = frame_corr - .5f;
+      } else {
+        // lpcnet_enc.c:640-699: weighted linear regression of the pitch contour, then its quantisation
+        const int quantize = A.quantize;
+        if (quantize && frame_corr < 0) frame_corr = 0;
+        float sx = 0, sxx = 0, sxy = 0, sy = 0, sw = 0;
+#pragma unroll
+        for (int sub = 2; sub < 10; sub++) {
+          const float w = fw[sub - 2];
+          sw += w;
+          sx += w * (float)sub;
+          sxx += w * (float)sub * (float)sub;
+          sxy += w * (float)sub * (float)best[sub - 2];
+          sy += w * (float)best[sub - 2];
+        }
+        const int voiced = (double)frame_corr >= .3;
+        float best_a = (sw * sxy - sx * sy) / (sw * sxx - sx * sx);
+        int corr_id;
+        if (voiced) {
+          const float mean_pitch = sy / sw;
+          const float max_a = mean_pitch / 32.f;
+          const float lo = -max_a > best_a ? -max_a : best_a;
+          best_a = max_a < lo ? max_a : lo;
+          corr_id = cvt_x86(floor((double)((frame_corr - .3f) / .175f)));
+          if (quantize) frame_corr = 0.3875f + .175f * (float)corr_id;
+        } else {
+          best_a = 0;
+          corr_id = cvt_x86(floor((double)(frame_corr / .075f)));
+          if (quantize) frame_corr = 0.0375f + .075f * (float)corr_id;
+        }
+        const float best_b = (sy - best_a * sx) / sw;
+        const float center_pitch = best_b + 5.5f * best_a;
+        int main_pitch = cvt_x86(floor(.5 + 21. * 1.442695041 * log((double)(center_pitch / 32.f))));
+        main_pitch = max(0, min(63, main_pitch));
+        int modulation = cvt_x86(floor(.5 + (double)(112.f * best_a / center_pitch)));
+        modulation = max(-3, min(3, modulation));
+        const int fr0 = A.frame0 + f - 3;
+        for (int sub = 0; sub < 4; sub++) {
+          float *out = A.features + ((size_t)s * A.total_frames + fr0 + sub) * kNF;
+          if (quantize) {
+            float p = __ldg(A.pitch_pow + main_pitch);
+            p *= 1.f + (float)modulation / 16.f / 7.f * (float)(2 * sub - 3);
+            const float lo = 33.f > p ? 33.f : p;
+            p = 255.f < lo ? 255.f : lo;
+            out[kBands] = .02f * (p - 100.f);
+          } else {
+            out[kBands] = .01f * (float)(max(66, min(510, best[2 * sub] + best[2 * sub + 1])) - 200);
+          }
+          out[kBands + 1] = frame_corr - .5f;
+        }
+        if (quantize) {
+          int *id = A.ids + ((size_t)s * (A.total_frames / 4) + fr0 / 4) * kIds;
+          id[1] = main_pitch;
+          id[2] = voiced ? modulation + 4 : 0;
+          id[3] = corr_id;
+        }
+      }
     }
     __syncthreads();
   }
@@ -299,9 +380,11 @@ __global__ void __launch_bounds__(kPT) pitch_kernel(AnalysisArgs A) {
   }
 }
 
-size_t pitch_smem(int F) {
-  return (size_t)(kPMax + F * kFrame + 2 * kPMax + 2 * kPMax) * 4 + kPMax * 8 + 2 * kPMax * 4 + 64;
+size_t pitch_smem(int F, int rows) {
+  return (size_t)(kPMax + F * kFrame + rows * kPMax + 2 * kPMax) * 4 + kPMax * 8 + (size_t)rows * kPMax * 4 + 64;
 }
+
+#include "vq.cuh"
 
 }  // namespace
 
@@ -322,6 +405,12 @@ struct LPCNetFeatureBatch {
   void *work = nullptr; size_t work_bytes = 0;
   void *d_pcm = nullptr; size_t d_pcm_bytes = 0;
   void *d_feat = nullptr; size_t d_feat_bytes = 0;
+  // 1.6 kb/s encoder (lpcnet_encode): codebooks, per-packet field values, packets
+  float *d_cb = nullptr;
+  const float *pitch_pow = nullptr;
+  void *d_ids = nullptr; size_t d_ids_bytes = 0;
+  void *d_left0 = nullptr; size_t d_left0_bytes = 0;
+  void *d_packets = nullptr; size_t d_packets_bytes = 0;
   long long launches = 0;
 };
 
@@ -342,17 +431,20 @@ int grow_buf(void **p, size_t *have, size_t want) {
   return 0;
 }
 
-int feature_chunk_frames(int B, int n_frames) {
+int feature_chunk_frames(int B, int n_frames, bool super) {
   int F = 32768 / (B > 0 ? B : 1);
   F = F < 1 ? 1 : (F > 32 ? 32 : F);
+  if (super) F = F < 4 ? 4 : (F & ~3);     // whole packets of four frames
   return F < n_frames ? F : n_frames;
 }
 
+// mode 0: single-frame analysis; 1: superframes (n_frames a multiple of 4), unquantised (lpcnet_compute_features);
+// 2: superframes with the pitch / correlation fields quantised into b->d_ids (lpcnet_encode)
 int analysis_device(LPCNetFeatureBatch *b, const short *d16, const float *df, int n_frames, float *d_features,
-                    const uint8_t *d_mask = nullptr) {
+                    const uint8_t *d_mask = nullptr, int mode = 0) {
   const int B = b->n_streams;
   CKA(cudaSetDevice(b->device));
-  const int Fc = feature_chunk_frames(B, n_frames);
+  const int Fc = feature_chunk_frames(B, n_frames, mode != 0);
   const size_t nP = (size_t)B * (kOverlap + Fc * kFrame), nS = (size_t)B * (1 + Fc * kFrame);
   const int lpc_threads = 64;
   const size_t n_fft_threads = (size_t)((B * Fc + lpc_threads - 1) / lpc_threads) * lpc_threads;
@@ -364,6 +456,7 @@ int analysis_device(LPCNetFeatureBatch *b, const short *d16, const float *df, in
     A.st = b->st; A.tab = b->tab; A.half_window = b->half_window;
     A.n_streams = B; A.n_frames = F; A.frame0 = f0; A.total_frames = n_frames;
     A.pcm16 = d16; A.pcmf = df; A.features = d_features; A.stream_mask = d_mask;
+    A.quantize = mode == 2; A.ids = static_cast<int *>(b->d_ids); A.pitch_pow = b->pitch_pow;
     A.P = static_cast<float *>(b->work);
     A.S = A.P + (((size_t)B * (kOverlap + F * kFrame) + 63) & ~size_t(63));
     A.fft_scratch = A.S + (((size_t)B * (1 + F * kFrame) + 63) & ~size_t(63));
@@ -372,7 +465,8 @@ int analysis_device(LPCNetFeatureBatch *b, const short *d16, const float *df, in
     spectral_kernel<<<(B * F + lpc_threads - 1) / lpc_threads, lpc_threads, 0, b->stream>>>(A);
     const size_t nr = (size_t)B * F * kFrame;
     residual_kernel<<<(unsigned)((nr + 255) / 256 > 65535 * 16 ? 65535 * 16 : (nr + 255) / 256), 256, 0, b->stream>>>(A);
-    pitch_kernel<<<B, kPT, pitch_smem(F), b->stream>>>(A);
+    if (mode) pitch_kernel<true><<<B, kPT, pitch_smem(F, 8), b->stream>>>(A);
+    else pitch_kernel<false><<<B, kPT, pitch_smem(F, 2), b->stream>>>(A);
     b->launches += 4;
     CKA(cudaGetLastError());
   }
@@ -395,6 +489,57 @@ int analysis_host(LPCNetFeatureBatch *b, const short *p16, const float *pf, int 
   CKA(cudaStreamSynchronize(b->stream));
   return 0;
 }
+
+// lpcnet_encode / lpcnet_compute_features for every stream: n_packets packets of 640 samples (lpcnet_enc.c:882-911)
+int superframe_host(LPCNetFeatureBatch *b, const short *pcm, int n_packets, unsigned char *packets, float *features) {
+  const bool quantize = packets != nullptr;
+  if (!b || !pcm || n_packets < 0 || (!packets && !features)) return set_last_error("lpcnet_feature_batch_encode: bad arguments");
+  if (quantize && !b->d_cb)
+    return set_last_error("lpcnet_feature_batch_encode: no codebooks (lpcnet_feature_batch_set_codebooks / lpcnet_b200_set_codebooks)");
+  if (n_packets == 0) return 0;
+  const int B = b->n_streams, n_frames = 4 * n_packets;
+  const size_t ns = (size_t)B * n_frames * kFrame, nf = (size_t)B * n_frames * kNF;
+  CKA(cudaSetDevice(b->device));
+  if (grow_buf(&b->d_pcm, &b->d_pcm_bytes, ns * 2)) return -1;
+  if (grow_buf(&b->d_feat, &b->d_feat_bytes, nf * 4)) return -1;
+  if (quantize) {
+    if (grow_buf(&b->d_ids, &b->d_ids_bytes, (size_t)B * n_packets * kIds * 4)) return -1;
+    if (grow_buf(&b->d_left0, &b->d_left0_bytes, (size_t)B * kBands * 4)) return -1;
+    if (grow_buf(&b->d_packets, &b->d_packets_bytes, (size_t)B * n_packets * 8)) return -1;
+  }
+  CKA(cudaMemcpyAsync(b->d_pcm, pcm, ns * 2, cudaMemcpyHostToDevice, b->stream));
+  CKA(cudaMemsetAsync(b->d_feat, 0, nf * 4, b->stream));
+  float *d_feat = static_cast<float *>(b->d_feat);
+  if (analysis_device(b, static_cast<const short *>(b->d_pcm), nullptr, n_frames, d_feat, nullptr, quantize ? 2 : 1)) return -1;
+  if (quantize) {
+    VqArgs V{};
+    V.cb = b->d_cb; V.features = d_feat; V.ids = static_cast<int *>(b->d_ids); V.vq_mem = b->st.vq_mem;
+    V.left0 = static_cast<float *>(b->d_left0); V.packets = static_cast<unsigned char *>(b->d_packets);
+    V.n_streams = B; V.n_packets = n_packets;
+    const unsigned grid = (unsigned)(((size_t)B * n_packets + kVqWarps - 1) / kVqWarps);
+    vq_end_kernel<<<grid, kVqThreads, kVqEndSmem, b->stream>>>(V);
+    vq_mid_kernel<<<grid, kVqThreads, kVqMidSmem, b->stream>>>(V);
+    b->launches += 2;
+    CKA(cudaGetLastError());
+    CKA(cudaMemcpyAsync(packets, b->d_packets, (size_t)B * n_packets * 8, cudaMemcpyDeviceToHost, b->stream));
+  }
+  if (features) CKA(cudaMemcpyAsync(features, b->d_feat, nf * 4, cudaMemcpyDeviceToHost, b->stream));
+  CKA(cudaStreamSynchronize(b->stream));
+  return 0;
+}
+
+int upload_codebooks(LPCNetFeatureBatch *b, const float *codebooks, int n_floats) {
+  const int want = 3 * kCbN * kNb1 + 4096 * kBands;
+  if (!b || !codebooks || n_floats != want)
+    return set_last_error("codebooks: expected ceps_codebook1|2|3 [1024][17] + ceps_codebook_diff4 [4096][18] = 125952 floats");
+  CKA(cudaSetDevice(b->device));
+  if (!b->d_cb) CKA(cudaMalloc(&b->d_cb, (size_t)want * 4));
+  CKA(cudaMemcpy(b->d_cb, codebooks, (size_t)want * 4, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+std::mutex g_cb_mu;
+std::vector<float> g_codebooks;     // process-wide default (the reference links ceps_codebooks.c into the library)
 
 }  // namespace
 
@@ -433,9 +578,18 @@ LPCNetFeatureBatch *lpcnet_feature_batch_create(int n_streams, int device) {
   host_dsp_tables(tw, br, dct);
   for (int i = 0; i < kOverlap; i++)
     hw[i] = (float)sin(.5 * M_PI * sin(.5 * M_PI * (i + .5) / kOverlap) * sin(.5 * M_PI * (i + .5) / kOverlap));
-  const size_t o_tw = 0, o_dct = o_tw + tw.size() * 4, o_hw = o_dct + dct.size() * 4, o_br = o_hw + hw.size() * 4;
+  // (float)(pow(2.f, main_pitch/21.)*PITCH_MIN_PERIOD) (lpcnet_enc.c:687), by the host's libm as in the reference
+  std::vector<float> pp(64);
+  for (int i = 0; i < 64; i++) pp[i] = (float)(pow(2.f, i / 21.) * kPMin);
+  const size_t o_tw = 0, o_dct = o_tw + tw.size() * 4, o_hw = o_dct + dct.size() * 4, o_pp = o_hw + hw.size() * 4,
+               o_br = o_pp + pp.size() * 4;
   if ((e = cudaMalloc(&b->tab_alloc, o_br + br.size() * 2)) != cudaSuccess) return bail("cudaMalloc(tables)", e);
   char *tp = static_cast<char *>(b->tab_alloc);
+  cudaMemcpy(tp + o_pp, pp.data(), pp.size() * 4, cudaMemcpyHostToDevice);
+  b->pitch_pow = (const float *)(tp + o_pp);
+  if ((e = cudaFuncSetAttribute(vq_end_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kVqEndSmem)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(vq_mid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kVqMidSmem)) != cudaSuccess)
+    return bail("cudaFuncSetAttribute(vq kernels)", e);
   cudaMemcpy(tp + o_tw, tw.data(), tw.size() * 4, cudaMemcpyHostToDevice);
   cudaMemcpy(tp + o_dct, dct.data(), dct.size() * 4, cudaMemcpyHostToDevice);
   cudaMemcpy(tp + o_hw, hw.data(), hw.size() * 4, cudaMemcpyHostToDevice);
@@ -447,14 +601,21 @@ LPCNetFeatureBatch *lpcnet_feature_batch_create(int n_streams, int device) {
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t r = off; off += (bytes + 255) & ~size_t(255); return r; };
   const size_t o_p = take(B * kOverlap * 4), o_m = take(B * 4), o_s = take(B * 4), o_e = take(B * kPMax * 4),
-               o_pa = take(B * kPMax * 4), o_al = take(B * 4), o_bi = take(B * 4);
+               o_pa = take(B * kPMax * 4), o_al = take(B * 4), o_bi = take(B * 4), o_vq = take(B * kBands * 4);
   if ((e = cudaMalloc(&b->st_alloc, off)) != cudaSuccess) return bail("cudaMalloc(state)", e);
   b->st_bytes = off;
   if ((e = cudaMemset(b->st_alloc, 0, off)) != cudaSuccess) return bail("cudaMemset(state)", e);
   char *p = static_cast<char *>(b->st_alloc);
   b->st.p_hist = (float *)(p + o_p); b->st.mem_preemph = (float *)(p + o_m); b->st.s_last = (float *)(p + o_s);
   b->st.e_hist = (float *)(p + o_e); b->st.path = (float *)(p + o_pa); b->st.path_all = (float *)(p + o_al);
-  b->st.best_i = (int *)(p + o_bi);
+  b->st.best_i = (int *)(p + o_bi); b->st.vq_mem = (float *)(p + o_vq);
+  {
+    std::lock_guard<std::mutex> lk(g_cb_mu);
+    if (!g_codebooks.empty() && upload_codebooks(b, g_codebooks.data(), (int)g_codebooks.size())) {
+      lpcnet_feature_batch_destroy(b);
+      return nullptr;
+    }
+  }
   return b;
 }
 
@@ -463,6 +624,7 @@ void lpcnet_feature_batch_destroy(LPCNetFeatureBatch *b) {
   cudaSetDevice(b->device);
   if (b->stream) { cudaStreamSynchronize(b->stream); cudaStreamDestroy(b->stream); }
   cudaFree(b->st_alloc); cudaFree(b->tab_alloc); cudaFree(b->work); cudaFree(b->d_pcm); cudaFree(b->d_feat);
+  cudaFree(b->d_cb); cudaFree(b->d_ids); cudaFree(b->d_left0); cudaFree(b->d_packets);
   delete b;
 }
 
@@ -483,6 +645,7 @@ int lpcnet_feature_batch_reset(LPCNetFeatureBatch *b, int stream) {
     CKA(cudaMemsetAsync(b->st.path + s * kPMax, 0, kPMax * 4, b->stream));
     CKA(cudaMemsetAsync(b->st.path_all + s, 0, 4, b->stream));
     CKA(cudaMemsetAsync(b->st.best_i + s, 0, 4, b->stream));
+    CKA(cudaMemsetAsync(b->st.vq_mem + s * kBands, 0, kBands * 4, b->stream));
   }
   CKA(cudaStreamSynchronize(b->stream));
   return 0;
@@ -503,6 +666,29 @@ int lpcnet_feature_batch_compute_device(LPCNetFeatureBatch *b, const short *d_pc
   const int r = n_frames ? analysis_device(b, d_pcm16, d_pcmf, n_frames, d_features) : 0;
   b->stream = keep;
   return r;
+}
+
+int lpcnet_feature_batch_set_codebooks(LPCNetFeatureBatch *b, const float *codebooks, int n_floats) {
+  return upload_codebooks(b, codebooks, n_floats);
+}
+
+int lpcnet_feature_batch_encode(LPCNetFeatureBatch *b, const short *pcm, int n_packets, unsigned char *packets,
+                                float *quantised_features) {
+  if (!packets) return set_last_error("lpcnet_feature_batch_encode: packets must not be NULL");
+  return superframe_host(b, pcm, n_packets, packets, quantised_features);
+}
+
+int lpcnet_feature_batch_compute_features(LPCNetFeatureBatch *b, const short *pcm, int n_packets, float *features) {
+  if (!features) return set_last_error("lpcnet_feature_batch_compute_features: features must not be NULL");
+  return superframe_host(b, pcm, n_packets, nullptr, features);
+}
+
+int lpcnet_b200_set_codebooks(const float *codebooks, int n_floats) {
+  std::lock_guard<std::mutex> lk(g_cb_mu);
+  if (!codebooks) { g_codebooks.clear(); return 0; }
+  if (n_floats != 3 * kCbN * kNb1 + 4096 * kBands) return set_last_error("lpcnet_b200_set_codebooks: expected 125952 floats");
+  g_codebooks.assign(codebooks, codebooks + n_floats);
+  return 0;
 }
 
 // ---- the reference's encoder-state API for this path (include/lpcnet.h:98-158), one stream -----------------
@@ -541,6 +727,16 @@ int lpcnet_compute_single_frame_features(LPCNetEncState *st, const short *pcm, f
 int lpcnet_compute_single_frame_features_float(LPCNetEncState *st, const float *pcm, float *features) {
   if (!st || st->magic != kEncMagic || !st->batch) return set_last_error("lpcnet_compute_single_frame_features_float: state not initialised");
   return lpcnet_feature_batch_compute_float(st->batch, pcm, 1, features);
+}
+
+int lpcnet_encode(LPCNetEncState *st, const short *pcm, unsigned char *buf) {
+  if (!st || st->magic != kEncMagic || !st->batch) return set_last_error("lpcnet_encode: state not initialised");
+  return lpcnet_feature_batch_encode(st->batch, pcm, 1, buf, nullptr);
+}
+
+int lpcnet_compute_features(LPCNetEncState *st, const short *pcm, float *features) {
+  if (!st || st->magic != kEncMagic || !st->batch) return set_last_error("lpcnet_compute_features: state not initialised");
+  return lpcnet_feature_batch_compute_features(st->batch, pcm, 1, features);
 }
 
 }  // extern "C"

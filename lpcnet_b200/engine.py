@@ -49,6 +49,8 @@ EXPORTED_SYMBOLS = [
     "lpcnet_feature_batch_create", "lpcnet_feature_batch_destroy", "lpcnet_feature_batch_n_streams",
     "lpcnet_feature_batch_launch_count", "lpcnet_feature_batch_reset", "lpcnet_feature_batch_compute",
     "lpcnet_feature_batch_compute_float", "lpcnet_feature_batch_compute_device",
+    "lpcnet_b200_set_codebooks", "lpcnet_encode", "lpcnet_compute_features", "lpcnet_feature_batch_set_codebooks",
+    "lpcnet_feature_batch_encode", "lpcnet_feature_batch_compute_features",
     "lpcnet_plc_get_size", "lpcnet_plc_init", "lpcnet_plc_create", "lpcnet_plc_destroy", "lpcnet_plc_load_model",
     "lpcnet_plc_update", "lpcnet_plc_conceal", "lpcnet_plc_batch_create", "lpcnet_plc_batch_destroy",
     "lpcnet_plc_batch_n_streams", "lpcnet_plc_batch_set_seed", "lpcnet_plc_batch_launch_count",
@@ -56,6 +58,9 @@ EXPORTED_SYMBOLS = [
 ]
 
 _lib = None
+
+
+PACKET_SAMPLES = 640         # LPCNET_PACKET_SAMPLES (include/lpcnet.h)
 
 
 class LPCNetError(RuntimeError):
@@ -127,6 +132,12 @@ def load_library() -> C.CDLL:
     L.lpcnet_feature_batch_compute.argtypes = [vp, vp, ci, vp]
     L.lpcnet_feature_batch_compute_float.argtypes = [vp, vp, ci, vp]
     L.lpcnet_feature_batch_compute_device.argtypes = [vp, vp, vp, ci, vp, vp]
+    L.lpcnet_b200_set_codebooks.argtypes = [vp, ci]
+    L.lpcnet_encode.argtypes = [vp, vp, vp]
+    L.lpcnet_compute_features.argtypes = [vp, vp, vp]
+    L.lpcnet_feature_batch_set_codebooks.argtypes = [vp, vp, ci]
+    L.lpcnet_feature_batch_encode.argtypes = [vp, vp, ci, vp, vp]
+    L.lpcnet_feature_batch_compute_features.argtypes = [vp, vp, ci, vp]
     L.lpcnet_plc_create.restype = vp
     L.lpcnet_plc_create.argtypes = [ci]
     L.lpcnet_plc_destroy.argtypes = [vp]
@@ -432,6 +443,31 @@ class FeatureBatch:
                    "lpcnet_feature_batch_compute_float")
         return out
 
+    def set_codebooks(self, codebooks):
+        cb = np.ascontiguousarray(codebooks, np.float32).reshape(-1)
+        _check(self.L.lpcnet_feature_batch_set_codebooks(self.h, _p(cb), cb.size), "lpcnet_feature_batch_set_codebooks")
+
+    def encode(self, pcm, want_features=False):
+        """lpcnet_encode for every stream: pcm [n_streams][n_packets*640] int16 -> packets [n_streams][n_packets][8]
+        uint8 (and the encoder's quantised feature rows [n_streams][n_packets*4][36] if asked)."""
+        x = np.ascontiguousarray(pcm, np.int16)
+        assert x.ndim == 2 and x.shape[0] == self.n_streams and x.shape[1] % PACKET_SAMPLES == 0
+        n = x.shape[1] // PACKET_SAMPLES
+        pk = np.zeros((self.n_streams, n, 8), np.uint8)
+        ft = np.zeros((self.n_streams, n * 4, NB_TOTAL_FEATURES), np.float32) if want_features else None
+        _check(self.L.lpcnet_feature_batch_encode(self.h, _p(x), n, _p(pk), _p(ft) if want_features else None),
+               "lpcnet_feature_batch_encode")
+        return (pk, ft) if want_features else pk
+
+    def compute_features(self, pcm):
+        """lpcnet_compute_features for every stream: pcm [n_streams][n_packets*640] int16 -> [n_streams][n_packets*4][36]."""
+        x = np.ascontiguousarray(pcm, np.int16)
+        assert x.ndim == 2 and x.shape[0] == self.n_streams and x.shape[1] % PACKET_SAMPLES == 0
+        n = x.shape[1] // PACKET_SAMPLES
+        ft = np.zeros((self.n_streams, n * 4, NB_TOTAL_FEATURES), np.float32)
+        _check(self.L.lpcnet_feature_batch_compute_features(self.h, _p(x), n, _p(ft)), "lpcnet_feature_batch_compute_features")
+        return ft
+
     def compute_device(self, d_pcm16: int, d_pcmf: int, n_frames: int, d_features: int, cuda_stream: int = 0):
         _check(self.L.lpcnet_feature_batch_compute_device(self.h, d_pcm16 or None, d_pcmf or None, n_frames,
                                                           d_features, cuda_stream or None),
@@ -468,6 +504,33 @@ class Encoder:
             _check(self.L.lpcnet_compute_single_frame_features_float(self.h, _p(x), _p(out)),
                    "lpcnet_compute_single_frame_features_float")
         return out
+
+
+    def encode(self, pcm):
+        """lpcnet_encode (include/lpcnet.h:113-120): 640 int16 samples -> 8 bytes"""
+        x = np.ascontiguousarray(pcm, np.int16)
+        assert x.size == PACKET_SAMPLES
+        buf = np.zeros(8, np.uint8)
+        _check(self.L.lpcnet_encode(self.h, _p(x), _p(buf)), "lpcnet_encode")
+        return buf
+
+    def compute_features(self, pcm):
+        """lpcnet_compute_features (include/lpcnet.h:122-131): 640 int16 samples -> [4][36]"""
+        x = np.ascontiguousarray(pcm, np.int16)
+        assert x.size == PACKET_SAMPLES
+        out = np.zeros((4, NB_TOTAL_FEATURES), np.float32)
+        _check(self.L.lpcnet_compute_features(self.h, _p(x), _p(out)), "lpcnet_compute_features")
+        return out
+
+
+def set_codebooks(codebooks) -> None:
+    """Process-wide VQ tables for encoder states created afterwards (lpcnet_b200_set_codebooks); None clears them."""
+    L = load_library()
+    if codebooks is None:
+        _check(L.lpcnet_b200_set_codebooks(None, 0), "lpcnet_b200_set_codebooks")
+        return
+    cb = np.ascontiguousarray(codebooks, np.float32).reshape(-1)
+    _check(L.lpcnet_b200_set_codebooks(_p(cb), cb.size), "lpcnet_b200_set_codebooks")
 
 
 PLC_NONCAUSAL = 1

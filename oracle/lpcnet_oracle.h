@@ -104,6 +104,10 @@ typedef struct OrcEncState OrcEncState;
 OrcEncState *orc_enc_new(void);
 void orc_enc_free(OrcEncState *s);
 void orc_enc_single_frame(OrcEncState *s, const float *pcm /*[160]*/, float *features /*[36]*/);
+/* lpcnet_encode (quantize 1: 640 samples -> 8 bytes, features = the quantised rows) and lpcnet_compute_features
+ * (quantize 0, buf unused) (src/lpcnet_enc.c:882-911); codebooks = cb1|cb2|cb3|diff4 as for orc_decode_packet */
+void orc_enc_superframe(OrcEncState *s, const float *pcm /*[640]*/, unsigned char *buf /*[8]*/, float *features /*[4][36]*/,
+                        int quantize, const float *codebooks);
 const float *orc_half_window(void);   /* [160] */
 /* burg_cepstral_analysis (src/freq.c:188-199): 160 samples -> 2 x 18 Burg cepstra (mean, difference) */
 void orc_burg_cepstral_analysis(float *ceps /*[36]*/, const float *x /*[160]*/);

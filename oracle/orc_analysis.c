@@ -97,8 +97,9 @@ static void log_bands(float *Ly, const float *Ex, int float_consts) {
   }
 }
 
-/* compute_frame_features (lpcnet_enc.c:498-577) with pcount = 0 */
-static void frame_features(OrcEncState *st, const float *in) {
+/* compute_frame_features (lpcnet_enc.c:498-577); writes rows 0, 1 of st->xc / st->frame_weight and st->features
+ * (the reference's rows 2+2*pcount+sub and features[pcount]: the superframe encoder copies them out, orc_encode.c) */
+void orc_enc_frame_features(OrcEncState *st, const float *in) {
   const float *hw = orc_half_window();
   float aligned_in[FRAME], x[WINDOW], Ex[NBANDS], Ly[NBANDS], xcorr[PMAX];
   OrcCpx X[WINDOW / 2 + 1];
@@ -218,7 +219,7 @@ void orc_enc_single_frame(OrcEncState *st, const float *pcm, float *features) {
     st->mem_preemph = -0.85f * pcm[i];
     x[i] = yi;
   }
-  frame_features(st, x);
+  orc_enc_frame_features(st, x);
   single_frame_pitch(st);
   memcpy(features, st->features, sizeof(st->features));
 }

@@ -49,7 +49,9 @@ struct OrcEncState {
   int best_i;
   float lpc[ORC_LPC_ORDER];
   float features[36];
+  float vq_mem[18];                 /* superframe encoder only (orc_encode.c) */
 };
+void orc_enc_frame_features(struct OrcEncState *st, const float *in /*[160], pre-emphasised*/);
 #undef PMAX
 #undef OVERLAP
 

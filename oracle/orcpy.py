@@ -211,6 +211,29 @@ class OrcEncoder:
         return out
 
 
+    def encode(self, pcm, codebooks):
+        """lpcnet_encode over [n_packets*640] samples -> (packets [n][8] uint8, quantised features [n][4][36])"""
+        x = np.ascontiguousarray(pcm, np.float32)
+        cb = np.ascontiguousarray(codebooks, np.float32)
+        n = x.size // 640
+        pk = np.zeros((n, 8), np.uint8)
+        ft = np.zeros((n, 4, 36), np.float32)
+        self.L.lib.orc_enc_superframe.argtypes = [C.c_void_p] * 4 + [C.c_int, C.c_void_p]
+        for k in range(n):
+            self.L.lib.orc_enc_superframe(self.h, _p(x[k * 640:(k + 1) * 640]), _p(pk[k]), _p(ft[k]), 1, _p(cb))
+        return pk, ft
+
+    def compute_features(self, pcm):
+        """lpcnet_compute_features over [n_packets*640] samples -> [n*4][36]"""
+        x = np.ascontiguousarray(pcm, np.float32)
+        n = x.size // 640
+        ft = np.zeros((n, 4, 36), np.float32)
+        self.L.lib.orc_enc_superframe.argtypes = [C.c_void_p] * 4 + [C.c_int, C.c_void_p]
+        for k in range(n):
+            self.L.lib.orc_enc_superframe(self.h, _p(x[k * 640:(k + 1) * 640]), None, _p(ft[k]), 0, None)
+        return ft.reshape(n * 4, 36)
+
+
 def half_window(lib: OrcLib):
     lib.lib.orc_half_window.restype = C.POINTER(C.c_float)
     return np.ctypeslib.as_array(lib.lib.orc_half_window(), (160,)).copy()

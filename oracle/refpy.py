@@ -202,6 +202,27 @@ class RefEncoder:
         return out
 
 
+    def encode(self, pcm):
+        """the reference's lpcnet_encode (lpcnet_enc.c:882-893) over [n_packets*640] int16 -> packets [n][8]"""
+        x = np.ascontiguousarray(pcm, np.int16)
+        n = x.size // 640
+        pk = np.zeros((n, 8), np.uint8)
+        self.L.lib.lpcnet_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        for k in range(n):
+            self.L.lib.lpcnet_encode(self.h, _p(x[k * 640:(k + 1) * 640]), _p(pk[k]))
+        return pk
+
+    def compute_features(self, pcm):
+        """the reference's lpcnet_compute_features (lpcnet_enc.c:895-911) -> [n_packets*4][36]"""
+        x = np.ascontiguousarray(pcm, np.int16)
+        n = x.size // 640
+        ft = np.zeros((n, 4, 36), np.float32)
+        self.L.lib.lpcnet_compute_features.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        for k in range(n):
+            self.L.lib.lpcnet_compute_features(self.h, _p(x[k * 640:(k + 1) * 640]), _p(ft[k]))
+        return ft.reshape(n * 4, 36)
+
+
 def ref_half_window(lib: RefLib):
     return np.ctypeslib.as_array((C.c_float * 160).in_dll(lib.lib, "half_window")).copy()
 

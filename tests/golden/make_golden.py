@@ -137,6 +137,27 @@ def analysis(R):
     np.savez_compressed(os.path.join(OUT, "analysis.npz"), pcm=np.stack(sig), features=np.stack(feats))
 
 
+def encode_signals():
+    """The inputs of encode.npz: 7 signals x 24 packets (tests/test_encode_oracle.py rebuilds and compares them)."""
+    n = 24 * 4
+    sig = [blob.synthetic_pcm(n, 300 + s) for s in range(4)]
+    x = blob.synthetic_pcm(n, 304).copy()
+    x[640 * 6:640 * 14] = 0                                                        # digital silence: NaN pitch contour
+    sig.append(x)
+    sig.append(np.clip(blob.synthetic_pcm(n, 305).astype(np.int32) * 6, -32768, 32767).astype(np.int16))   # clipping
+    sig.append(np.random.default_rng(19).integers(-3000, 3000, n * 160).astype(np.int16))                # unvoiced
+    return sig
+
+
+def encode(R):
+    """lpcnet_encode and lpcnet_compute_features of the reference (lpcnet_enc.c:882-911) with the synthetic
+    codebooks of oracle/gen_codebooks.py linked in."""
+    sig = encode_signals()
+    pk = [refpy.RefEncoder(R).encode(x) for x in sig]
+    ft = [refpy.RefEncoder(R).compute_features(x) for x in sig]
+    np.savez_compressed(os.path.join(OUT, "encode.npz"), pcm=np.stack(sig), packets=np.stack(pk), features=np.stack(ft))
+
+
 def plc_model_blob():
     A = blob.random_model()
     A.update(blob.random_plc_model())
@@ -175,8 +196,8 @@ def plc(R):
 
 if __name__ == "__main__":
     R = refpy.RefLib(2)
-    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc"]
+    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc", "encode"]
     for name in which:
-        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc}[name](R)
+        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc, "encode": encode}[name](R)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
