@@ -96,9 +96,48 @@ struct LPCNetBatch {
   void *d_trace = nullptr; size_t d_trace_bytes = 0;
   void *d_logits = nullptr; size_t d_logits_bytes = 0;
   void *d_packets = nullptr; size_t d_packets_bytes = 0;
+  // compact copy of the streams one PLC sample segment moves (batch_sample_segment with a stream list)
+  void *d_compact = nullptr; size_t d_compact_bytes = 0;
 };
 
 namespace {
+
+// One PLC sample segment usually moves a small part of the batch (the streams that come out of a loss burst).  The
+// sample kernel walks whole tiles in lock step, so those streams are gathered into a dense batch of their own
+// (state, conditioning, flags, teacher-forcing samples), advanced there, and scattered back.
+struct CompactView {
+  DevState st;            // gru_a, gru_b, last_sig, deemph, last_exc, rng of the listed streams
+  float *cond_a, *cond_b, *lpc;
+  uint8_t *flags;
+  short *forced, *out;    // [n_act][n]
+};
+
+__global__ void compact_gather_kernel(CompactView c, DevState st, const float *cond_a, const float *cond_b, const float *lpc,
+                                      const uint8_t *flags, const short *forced, const int *perm, int n) {
+  const int j = blockIdx.x, t = threadIdx.x, s = perm[j];
+  for (int i = t; i < kRowsAP / 4; i += blockDim.x)
+    reinterpret_cast<float4 *>(c.cond_a + (size_t)j * kRowsAP)[i] = reinterpret_cast<const float4 *>(cond_a + (size_t)s * kRowsAP)[i];
+  for (int i = t; i < kN; i += blockDim.x) c.st.gru_a[(size_t)j * kN + i] = st.gru_a[(size_t)s * kN + i];
+  if (t < kRowsB) c.cond_b[(size_t)j * kRowsB + t] = cond_b[(size_t)s * kRowsB + t];
+  if (t < kNB) c.st.gru_b[(size_t)j * kNB + t] = st.gru_b[(size_t)s * kNB + t];
+  if (t < 16) {
+    c.st.last_sig[(size_t)j * 16 + t] = st.last_sig[(size_t)s * 16 + t];
+    c.lpc[(size_t)j * 16 + t] = lpc[(size_t)s * 16 + t];
+  }
+  if (t < 4) c.st.rng[(size_t)j * 4 + t] = st.rng[(size_t)s * 4 + t];
+  if (t == 0) { c.st.deemph[j] = st.deemph[s]; c.st.last_exc[j] = st.last_exc[s]; c.flags[j] = flags[s]; }
+  if (forced) for (int i = t; i < n; i += blockDim.x) c.forced[(size_t)j * n + i] = forced[(size_t)s * n + i];
+}
+
+__global__ void compact_scatter_kernel(CompactView c, DevState st, short *out, const int *perm, int n) {
+  const int j = blockIdx.x, t = threadIdx.x, s = perm[j];
+  for (int i = t; i < kN; i += blockDim.x) st.gru_a[(size_t)s * kN + i] = c.st.gru_a[(size_t)j * kN + i];
+  if (t < kNB) st.gru_b[(size_t)s * kNB + t] = c.st.gru_b[(size_t)j * kNB + t];
+  if (t < 16) st.last_sig[(size_t)s * 16 + t] = c.st.last_sig[(size_t)j * 16 + t];
+  if (t < 4) st.rng[(size_t)s * 4 + t] = c.st.rng[(size_t)j * 4 + t];
+  if (t == 0) { st.deemph[s] = c.st.deemph[j]; st.last_exc[s] = c.st.last_exc[j]; }
+  for (int i = t; i < n; i += blockDim.x) out[(size_t)s * n + i] = c.out[(size_t)j * n + i];
+}
 
 int grow(void **p, size_t *have, size_t want) {
   if (*have >= want) return 0;
@@ -270,9 +309,40 @@ int lpcb::batch_frame_network_masked(LPCNetBatch *b, const float *d_features, in
   return 0;
 }
 
-int lpcb::batch_sample_segment(LPCNetBatch *b, int n, const uint8_t *d_flags, const short *d_forced, short *d_out) {
+int lpcb::batch_sample_segment(LPCNetBatch *b, int n, const uint8_t *d_flags, const short *d_forced, short *d_out,
+                               const int *d_perm, int n_act) {
   if (n <= 0 || n > kFrame) return fail("sample segment must be 1..160 steps");
   CK(cudaSetDevice(b->device));
+  if (d_perm && n_act == 0) return 0;
+  if (d_perm && 2 * n_act <= b->n_streams && !getenv("LPCNET_B200_NO_COMPACT")) {
+    const size_t A = n_act;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t r = off; off += (bytes + 255) & ~size_t(255); return r; };
+    const size_t o_ca = take(A * kRowsAP * 4), o_ga = take(A * kN * 4), o_cb = take(A * kRowsB * 4), o_gb = take(A * kNB * 4),
+                 o_ls = take(A * 16 * 4), o_lpc = take(A * 16 * 4), o_rng = take(A * 16), o_de = take(A * 4), o_le = take(A * 4),
+                 o_fl = take(A), o_fo = take(A * kFrame * 2), o_out = take(A * kFrame * 2);
+    if (grow(&b->d_compact, &b->d_compact_bytes, off)) return -1;
+    char *p = static_cast<char *>(b->d_compact);
+    CompactView c{};
+    c.cond_a = (float *)(p + o_ca); c.st.gru_a = (float *)(p + o_ga); c.cond_b = (float *)(p + o_cb); c.st.gru_b = (float *)(p + o_gb);
+    c.st.last_sig = (float *)(p + o_ls); c.lpc = (float *)(p + o_lpc); c.st.rng = (uint32_t *)(p + o_rng);
+    c.st.deemph = (float *)(p + o_de); c.st.last_exc = (int *)(p + o_le); c.flags = (uint8_t *)(p + o_fl);
+    c.forced = (short *)(p + o_fo); c.out = (short *)(p + o_out);
+    compact_gather_kernel<<<n_act, 128, 0, b->stream>>>(c, b->st, b->fb.cond_a, b->fb.cond_b, b->fb.lpc, d_flags, d_forced, d_perm, n);
+    SampleArgs sa{};
+    sa.m = b->model.d; sa.st = c.st; sa.n_streams = n_act; sa.n_frames = 1; sa.spf = n;
+    sa.frame0 = 0; sa.total_frames = 1;
+    sa.cond_a = c.cond_a; sa.cond_b = c.cond_b; sa.lpc = c.lpc; sa.active = c.flags;
+    sa.pcm = c.out; sa.forced = d_forced ? c.forced : nullptr; sa.forced_by_flag = 1;
+    int nl = 0;
+    int tile = b->tile ? b->tile : (n_act <= 8 * b->n_sms ? 8 : 16);
+    tile = tile < b->max_tile ? tile : b->max_tile;
+    CK(launch_sample_kernel(sa, tile, b->n_sms, b->stream, &nl));
+    compact_scatter_kernel<<<n_act, 128, 0, b->stream>>>(c, b->st, d_out, d_perm, n);
+    CK(cudaGetLastError());
+    b->launches += nl + 2;
+    return 0;
+  }
   SampleArgs sa{};
   sa.m = b->model.d; sa.st = b->st; sa.n_streams = b->n_streams; sa.n_frames = 1; sa.spf = n;
   sa.frame0 = 0; sa.total_frames = 1;
@@ -386,7 +456,7 @@ void lpcnet_batch_destroy(LPCNetBatch *b) {
     cudaEventDestroy(b->ev_entry);
     for (int k = 0; k < 2; k++) { cudaEventDestroy(b->ev_frames[k]); cudaEventDestroy(b->ev_samples[k]); }
   }
-  void *ptrs[] = {b->st_alloc, b->fb_alloc, b->fb2_alloc, b->d_feat, b->d_pcm, b->d_forced, b->d_trace, b->d_logits, b->d_packets};
+  void *ptrs[] = {b->st_alloc, b->fb_alloc, b->fb2_alloc, b->d_feat, b->d_pcm, b->d_forced, b->d_trace, b->d_logits, b->d_packets, b->d_compact};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (b->own_stream) cudaStreamDestroy(b->own_stream);
   delete b;

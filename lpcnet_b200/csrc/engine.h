@@ -233,7 +233,10 @@ BatchView batch_view(LPCNetBatch *b);
 int batch_frame_network_masked(LPCNetBatch *b, const float *d_features, int stride, const uint8_t *d_mask);
 // n sample steps (lpcnet_synthesize_tail_impl) on the conditioning of the last frame network.  flags [B]: 0 the
 // stream does not move, 1 free-running, 3 teacher-forced on d_forced [B][n]; d_out [B][n].
-int batch_sample_segment(LPCNetBatch *b, int n, const uint8_t *d_flags, const short *d_forced, short *d_out);
+// d_perm (nullable): device list of the n_act streams whose flag is not 0, ascending; when they are at most half of
+// the batch they are advanced as a dense batch of their own (gather, sample kernel, scatter).
+int batch_sample_segment(LPCNetBatch *b, int n, const uint8_t *d_flags, const short *d_forced, short *d_out,
+                         const int *d_perm = nullptr, int n_act = 0);
 // one frame of analysis for the streams with mask != 0: d_pcm16 [B][160] -> d_features [B][36] (others untouched)
 int feature_batch_frame_masked(LPCNetFeatureBatch *b, const short *d_pcm16, const uint8_t *d_mask, float *d_features,
                                cudaStream_t stream);

@@ -634,14 +634,17 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int n_frames) {
   cudaStream_t cs = V.stream;
   // classes, masks and loss counters of every frame (they depend on the loss pattern only)
   const size_t lc_off = ((size_t)kNMasks * B + 15) & ~size_t(15);           // the uint16 counters sit aligned
-  const size_t per_frame = (lc_off + (size_t)B * 2 + 15) & ~size_t(15);
+  // stream lists of the three sample-segment groups (queued update, first good frame, main), for the compact path
+  const size_t perm_off = (lc_off + (size_t)B * 2 + 15) & ~size_t(15);
+  const size_t per_frame = (perm_off + (size_t)3 * B * 4 + 15) & ~size_t(15);
   std::vector<uint8_t> ctl(per_frame * n_frames);
-  struct Any { bool q, upd, fg, main_, l1; };
+  struct Any { bool q, upd, fg, main_, l1; int nq, nfg, nmain; };
   std::vector<Any> any(n_frames);
   for (int f = 0; f < n_frames; f++) {
     uint8_t *m = ctl.data() + per_frame * f;
     uint16_t *lc = reinterpret_cast<uint16_t *>(m + lc_off);
-    Any a{false, false, false, false, false};
+    int *perm = reinterpret_cast<int *>(m + perm_off);
+    Any a{false, false, false, false, false, 0, 0, 0};
     for (int s = 0; s < B; s++) {
       const bool is_lost = lost[(size_t)s * n_frames + f] != 0;
       const int c = p->loss_count[s];
@@ -660,6 +663,8 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int n_frames) {
       m[fB * B + s] = cls == kG0 ? 3 : (cls == kFG ? 0 : 1);
       lc[s] = (uint16_t)(c > 60000 ? 60000 : c);
       a.q |= q; a.upd |= !is_lost; a.fg |= cls == kFG; a.main_ |= cls != kFG; a.l1 |= cls == kL1;
+      if (q) perm[a.nq++] = s;
+      if (cls == kFG) perm[B + a.nfg++] = s; else perm[2 * B + a.nmain++] = s;
       // process_queued_update runs at the start of both entry points; only the FG branch queues a new one
       p->queued[s] = cls == kFG;
       p->loss_count[s] = is_lost ? c + 1 : 0;
@@ -680,11 +685,12 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int n_frames) {
     A.lossc = reinterpret_cast<const uint16_t *>(M + lc_off);
     A.frame = f;
     const Any a = any[f];
+    const int *permQ = reinterpret_cast<const int *>(M + perm_off), *permFG = permQ + B, *permMain = permQ + 2 * B;
     // Q: process_queued_update (lpcnet_plc.c:342-347)
     if (a.q) {
       plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, cs>>>(A, mQ, 0);
       if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mQ * B)) return -1;
-      if (batch_sample_segment(p->syn, kFrame, M + (size_t)fQ * B, p->st.queued, p->w.sego)) return -1;
+      if (batch_sample_segment(p->syn, kFrame, M + (size_t)fQ * B, p->st.queued, p->w.sego, permQ, a.nq)) return -1;
     }
     if (a.upd) {
       plc_pre_kernel<<<gs, tb, 0, cs>>>(A);
@@ -696,12 +702,12 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int n_frames) {
       plc_state_copy_kernel<<<B, 128, 0, cs>>>(p->snap, V.st, M + (size_t)mFG * B, B);
       plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, cs>>>(A, mFG, 0);
       if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B)) return -1;
-      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fFgFree * B, nullptr, p->w.sego)) return -1;
+      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fFgFree * B, nullptr, p->w.sego, permFG, a.nfg)) return -1;
       plc_fg_mid_kernel<<<gs, tb, 0, cs>>>(A);
       plc_clear_state_kernel<<<B, 128, 0, cs>>>(V.st, M + (size_t)mFG * B, B);
       if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B)) return -1;
-      if (batch_sample_segment(p->syn, kFrame, M + (size_t)fFgForced * B, p->w.segf, p->w.sego)) return -1;
-      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fFgFree * B, nullptr, p->w.sego2)) return -1;
+      if (batch_sample_segment(p->syn, kFrame, M + (size_t)fFgForced * B, p->w.segf, p->w.sego, permFG, a.nfg)) return -1;
+      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fFgFree * B, nullptr, p->w.sego2, permFG, a.nfg)) return -1;
       plc_fg_end_kernel<<<gs, tb, 0, cs>>>(A);
       plc_state_copy_kernel<<<B, 128, 0, cs>>>(V.st, p->snap, M + (size_t)mFG * B, B);
       if (feature_batch_frame_masked(p->ana, p->st.pcm, M + (size_t)mFG * B, p->w.encf2, cs)) return -1;
@@ -712,9 +718,9 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int n_frames) {
       plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, cs>>>(A, mMain, 1);
       if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mMain * B)) return -1;
       plc_seg_prep_kernel<<<(B * kTOff + 255) / 256, 256, 0, cs>>>(A, 0);
-      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fA * B, p->w.segf, p->w.sego)) return -1;
+      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fA * B, p->w.segf, p->w.sego, permMain, a.nmain)) return -1;
       plc_seg_prep_kernel<<<(B * kTOff + 255) / 256, 256, 0, cs>>>(A, 1);
-      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fB * B, p->w.segf, p->w.sego2)) return -1;
+      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fB * B, p->w.segf, p->w.sego2, permMain, a.nmain)) return -1;
       plc_lost_mid_kernel<<<gs, tb, 0, cs>>>(A);
       if (a.l1 && feature_batch_frame_masked(p->ana, p->st.pcm, M + (size_t)mL1 * B, p->w.encf2, cs)) return -1;
     }
