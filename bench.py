@@ -370,7 +370,7 @@ def run_gpu(args):
                     "unit": "GB/s", "frac": hbm_bytes_per_sample * value / world / 1e9 / pk["hbm_gbs"]}
         # ---- CPU baseline: bounded sample of the same workload on the host cores ----
         cpu = None
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:     # the reported baseline is an N=1 figure
             ref = CpuReference(model_blob, n_frames)
             try:
                 ref.run_once()

@@ -542,6 +542,7 @@ struct LPCNetPLCBatch {
   LPCNetBatch *syn = nullptr;           // synthesis engine: model, LPCNetState of every stream, sample kernel
   LPCNetFeatureBatch *ana = nullptr;    // LPCNetEncState of every stream
   void *alloc = nullptr;                // PLC state + per-frame scratch + state snapshot
+  size_t state_bytes = 0;               // leading part of `alloc` that lpcnet_plc_reset clears
   PlcState st{};
   PlcWork w{};
   DevState snap{};
@@ -591,6 +592,7 @@ int plc_alloc(LPCNetPLCBatch *p) {
   const size_t o_fft = take(n_fft * 640 * 4), o_fade = take(kTOff * 4);
   CKP(cudaMalloc(&p->alloc, off));
   CKP(cudaMemset(p->alloc, 0, off));
+  p->state_bytes = o_fft;
   char *b = static_cast<char *>(p->alloc);
   p->st.pcm = (short *)(b + o_pcm); p->st.features = (float *)(b + o_feat); p->st.gru1 = (float *)(b + o_g1);
   p->st.gru2 = (float *)(b + o_g2); p->st.dc_mem = (double *)(b + o_dc); p->st.syn_dc = (double *)(b + o_sd);
@@ -781,6 +783,17 @@ long long lpcnet_plc_batch_launch_count(const LPCNetPLCBatch *p) {
   return p ? lpcnet_batch_launch_count(p->syn) + lpcnet_feature_batch_launch_count(p->ana) + 12 * p->frames_done : 0;
 }
 
+// lpcnet_plc_reset (lpcnet_plc.c:46-60) for every stream: lpcnet_reset, lpcnet_encoder_init, PLC state cleared
+int lpcnet_plc_batch_reset(LPCNetPLCBatch *p) {
+  if (!p) return set_last_error("lpcnet_plc_batch_reset: null batch");
+  if (lpcnet_batch_reset(p->syn, -1) || lpcnet_feature_batch_reset(p->ana, -1)) return -1;
+  CKP(cudaSetDevice(p->device));
+  CKP(cudaMemset(p->alloc, 0, p->state_bytes));
+  p->loss_count.assign(p->n_streams, 0);
+  p->queued.assign(p->n_streams, 0);
+  return 0;
+}
+
 int lpcnet_plc_batch_process(LPCNetPLCBatch *p, const unsigned char *lost, short *pcm, int n_frames) {
   if (!p || !lost || !pcm || n_frames < 0) return set_last_error("lpcnet_plc_batch_process: bad arguments");
   if (n_frames == 0) return 0;
@@ -860,6 +873,16 @@ int lpcnet_plc_load_model(LPCNetPLCState *st, const unsigned char *data, int len
   st->batch = lpcnet_plc_batch_create(data, len, 1, 0, st->options, 1.0f);
   return st->batch ? 0 : -1;
 }
+
+void lpcnet_plc_reset(LPCNetPLCState *st) {
+  if (st && st->magic == kPlcMagic && st->batch) lpcnet_plc_batch_reset(st->batch);
+}
+
+// The FEC queue (lpcnet_plc.c:111-132) feeds get_fec_or_pred, which only the causal entry points call
+// (lpcnet_plc.c:316, 325); the non-causal mode built here never reads it, so -- as in the reference -- features
+// added in this mode have no effect on the output.  The calls are accepted so that callers need no special case.
+void lpcnet_plc_fec_add(LPCNetPLCState *st, const float *features) { (void)st; (void)features; }
+void lpcnet_plc_fec_clear(LPCNetPLCState *st) { (void)st; }
 
 int lpcnet_plc_update(LPCNetPLCState *st, short *pcm) {
   if (!st || st->magic != kPlcMagic || !st->batch) return set_last_error("lpcnet_plc_update: no model loaded");

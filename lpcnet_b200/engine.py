@@ -52,7 +52,8 @@ EXPORTED_SYMBOLS = [
     "lpcnet_b200_set_codebooks", "lpcnet_encode", "lpcnet_compute_features", "lpcnet_feature_batch_set_codebooks",
     "lpcnet_feature_batch_encode", "lpcnet_feature_batch_compute_features",
     "lpcnet_plc_get_size", "lpcnet_plc_init", "lpcnet_plc_create", "lpcnet_plc_destroy", "lpcnet_plc_load_model",
-    "lpcnet_plc_update", "lpcnet_plc_conceal", "lpcnet_plc_batch_create", "lpcnet_plc_batch_destroy",
+    "lpcnet_plc_update", "lpcnet_plc_conceal", "lpcnet_plc_reset", "lpcnet_plc_fec_add", "lpcnet_plc_fec_clear",
+    "lpcnet_plc_batch_reset", "lpcnet_plc_batch_create", "lpcnet_plc_batch_destroy",
     "lpcnet_plc_batch_n_streams", "lpcnet_plc_batch_set_seed", "lpcnet_plc_batch_launch_count",
     "lpcnet_plc_batch_process", "lpcnet_plc_batch_peek", "lpcnet_plc_batch_peek_frame",
 ]
@@ -143,6 +144,13 @@ def load_library() -> C.CDLL:
     L.lpcnet_plc_destroy.argtypes = [vp]
     L.lpcnet_plc_load_model.argtypes = [vp, vp, ci]
     L.lpcnet_plc_update.argtypes = [vp, vp]
+    L.lpcnet_plc_reset.argtypes = [vp]
+    L.lpcnet_plc_reset.restype = None
+    L.lpcnet_plc_fec_add.argtypes = [vp, vp]
+    L.lpcnet_plc_fec_add.restype = None
+    L.lpcnet_plc_fec_clear.argtypes = [vp]
+    L.lpcnet_plc_fec_clear.restype = None
+    L.lpcnet_plc_batch_reset.argtypes = [vp]
     L.lpcnet_plc_conceal.argtypes = [vp, vp]
     L.lpcnet_plc_batch_create.restype = vp
     L.lpcnet_plc_batch_create.argtypes = [vp, ci, ci, ci, ci, cf]
@@ -564,6 +572,10 @@ class PLCBatch:
     def launch_count(self):
         return int(self.L.lpcnet_plc_batch_launch_count(self.h))
 
+    def reset(self):
+        """lpcnet_plc_reset for every stream (seeds return to the default "LPCNet")."""
+        _check(self.L.lpcnet_plc_batch_reset(self.h), "lpcnet_plc_batch_reset")
+
     def peek(self, stream: int):
         """(features[20], gru1[256], gru2[256], [dc_mem, syn_dc]) of one stream."""
         f = np.zeros(20, np.float32); g1 = np.zeros(256, np.float32); g2 = np.zeros(256, np.float32)
@@ -608,6 +620,17 @@ class PLC:
 
     def __del__(self):
         self.close()
+
+    def reset(self):
+        self.L.lpcnet_plc_reset(self.h)
+
+    def fec_add(self, features):
+        """lpcnet_plc_fec_add: accepted; the non-causal mode never reads the queue (as in the reference)."""
+        f = None if features is None else np.ascontiguousarray(features, np.float32)
+        self.L.lpcnet_plc_fec_add(self.h, None if f is None else _p(f))
+
+    def fec_clear(self):
+        self.L.lpcnet_plc_fec_clear(self.h)
 
     def update(self, pcm):
         x = np.ascontiguousarray(pcm, np.int16).copy()

@@ -70,6 +70,25 @@ def test_call_splitting_and_single_stream_api(eng, plc_blob):
     assert first_diff(np.concatenate(parts, axis=1)[0], want) is None
 
 
+def test_reset_and_fec_calls(eng, plc_blob):
+    """lpcnet_plc_reset returns a used state to its initial one; FEC features are accepted and -- as in the
+    reference's non-causal mode, which never reads the queue -- leave the output unchanged."""
+    g = np.load(os.path.join(HERE, "golden", "plc.npz"))
+    x, lost, want = g["in_1_0"], g["lost_1_0"], g["out_1_0"]
+    plc = eng.PLC(plc_blob, 1)
+    for f in range(9):
+        plc.conceal() if lost[f] else plc.update(x[f * 160:(f + 1) * 160])
+    plc.reset()
+    out = []
+    for f in range(len(lost)):
+        plc.fec_add(np.full(20, 0.25, np.float32) if f % 3 else None)
+        out.append(plc.conceal() if lost[f] else plc.update(x[f * 160:(f + 1) * 160]))
+        if f % 5 == 4:
+            plc.fec_clear()
+    plc.close()
+    assert first_diff(np.concatenate(out), want) is None
+
+
 def test_many_streams_against_the_oracle(eng, plc_blob, plc_model):
     """96 streams x 30 frames with the DC filter, every stream under its own Gilbert loss pattern (long bursts for
     some): a sample of streams against the oracle, and batch invariance for the rest."""
