@@ -239,7 +239,8 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
   CK(cudaSetDevice(b->device));
   const int Fc = chunk_frames(b, n_frames);
   if (ensure_frame_buffers(b, Fc)) return -1;
-  const int tile = auto_tile(b);
+  // no explicit tile: whole waves of 16-stream tiles, the remainder in 8-stream tiles when that is faster (0 = mixed)
+  const int tile = (b->tile == 0 && b->max_tile >= 16 && !getenv("LPCNET_B200_NO_MIX")) ? 0 : auto_tile(b);
   // Several chunks: the frame network of chunk k+1 runs on a second stream while the sample kernel works on
   // chunk k (two buffer sets).  It touches only frame-rate state (conv histories, frame counter, LPC delay
   // line); the sample kernel only sample-rate state.  Everything is ordered after the caller's stream at

@@ -173,6 +173,8 @@ struct SampleArgs {
   DevModel m;
   DevState st;
   int n_streams;
+  int stream_begin = 0;      // the launch advances streams [stream_begin, stream_end); stream_end 0 = n_streams
+  int stream_end = 0;
   int n_frames;              // frames in this chunk
   int spf;                   // samples per frame (<=160)
   int frame0;                // index of the chunk's first frame within the call
@@ -190,6 +192,8 @@ struct SampleArgs {
   unsigned long long *phase_clk;   // development builds (-DLPCB_PHASE_CLOCKS) only: per-phase cycle sums of CTA 0
 };
 
+// tile_streams 8 / 16 / 32, or 0: 16-stream tiles in whole waves of one tile per SM, and the remainder in 8-stream
+// tiles when it fits one per SM (lower step latency than a part-filled wave of 16-stream tiles), else in 16s.
 cudaError_t launch_sample_kernel(const SampleArgs &a, int tile_streams, int n_sms, cudaStream_t s,
                                  int *n_launches);
 size_t sample_kernel_smem(int tile_streams, const DevModel &m);

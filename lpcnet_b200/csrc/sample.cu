@@ -15,6 +15,16 @@ size_t sample_kernel_smem(int tile_streams, const DevModel &m) {
 
 cudaError_t launch_sample_kernel(const SampleArgs &a, int tile_streams, int n_sms, cudaStream_t s, int *n_launches) {
   cudaError_t e;
+  if (tile_streams == 0) {
+    const int B = a.n_streams, full = B / (16 * n_sms) * (16 * n_sms), rest = B - full;
+    if (full == 0) return launch_sample_kernel(a, rest <= 8 * n_sms ? 8 : 16, n_sms, s, n_launches);
+    if (rest == 0 || rest > 8 * n_sms || a.trace || a.logits) return launch_sample_kernel(a, 16, n_sms, s, n_launches);
+    SampleArgs head = a, tail = a;
+    head.stream_end = full;
+    tail.stream_begin = full;
+    if ((e = launch_sample_kernel(head, 16, n_sms, s, n_launches)) != cudaSuccess) return e;
+    return launch_sample_kernel(tail, 8, n_sms, s, n_launches);
+  }
   switch (tile_streams) {
     case 8: e = launch_sample_t8(a, n_sms, s); break;
     case 16: e = launch_sample_t16(a, n_sms, s); break;

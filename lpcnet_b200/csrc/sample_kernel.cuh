@@ -127,7 +127,10 @@ __device__ __forceinline__ uint32_t fnv1a_bytes(const unsigned char *p, int n) {
 #define LPCB_MARK(k) do { } while (0)
 #endif
 
-template <int MT, int VR, bool DEBUG, bool FIX, bool RA>
+// SUB: the launch advances a sub-range of the batch (SampleArgs::stream_begin / stream_end).  A template parameter
+// because carrying the two bounds in the whole-batch kernel cost 3.5 % at 8 streams per CTA (4.18 -> 4.33 us per
+// step, A/B on one B200): the whole-batch instantiation keeps the constants.
+template <int MT, int VR, bool DEBUG, bool FIX, bool RA, bool SUB = false>
 __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A) {
   constexpr int NS = MT * VR;
   constexpr int NV = (VR == 16) ? 4 : 2;   // accumulator registers in use per thread
@@ -181,7 +184,9 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2, t = lane & 3;
-  const int B = A.n_streams;
+  const int B = A.n_streams;                                   // row stride of the per-frame arrays
+  const int Bend = SUB && A.stream_end ? A.stream_end : B;      // this launch advances streams [sbegin, Bend)
+  const int sbegin = SUB ? A.stream_begin : 0;
   const int row_len = A.total_frames * A.spf;
 
   // sparse_sgemv_accum8x4 (src/vec_avx.h:790-858) of unit group ug for the M tile at xrow0 on tensor cores: the
@@ -264,9 +269,9 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
 #ifdef LPCB_PHASE_CLOCKS
   long long clk_[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, last_ = clock64();
 #endif
-  const int n_tiles = (B + NS - 1) / NS;
+  const int n_tiles = (Bend - sbegin + NS - 1) / NS;
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const int stream0 = tile * NS;
+    const int stream0 = sbegin + tile * NS;
     __syncthreads();
     // ---- load the tile's stream state ----
     float2 a_reg[3][MT][NV / 2];
@@ -279,7 +284,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
 #pragma unroll
         for (int h = 0; h < NV / 2; h++) {
           const int s = mt * VR + g + h * 8;
-          const int gs = min(stream0 + s, B - 1);
+          const int gs = min(stream0 + s, Bend - 1);
           const int unit = ug * 8 + 2 * t;
           const float2 v = *reinterpret_cast<const float2 *>(A.st.gru_a + (size_t)gs * kN + unit);
           a_reg[u][mt][h] = v;
@@ -290,7 +295,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
     }
     for (int i = tid; i < NS * 16; i += kThreads) {
       const int s = i >> 4, j = i & 15;
-      const int gs = min(stream0 + s, B - 1);
+      const int gs = min(stream0 + s, Bend - 1);
       float v = A.st.gru_b[(size_t)gs * kNB + j];
       s_bst[s * 20 + j] = v;
       reinterpret_cast<unsigned char *>(s_xb)[s * kXbStride * 4 + j] = (unsigned char)quant_u8_ref(v);
@@ -303,7 +308,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
     const bool twarp = tw >= 0;                             // both 16-lane halves own a stream (NS is even)
     const int l16 = tid & 15, grp = twarp ? 2 * tw + (lane >> 4) : NS;
     const unsigned gbase = lane & 16;
-    const int tgs = min(stream0 + min(grp, NS - 1), B - 1);
+    const int tgs = min(stream0 + min(grp, NS - 1), Bend - 1);
     float t_x = A.st.last_sig[(size_t)tgs * 16 + l16], t_lpc = 0.f, t_pred = 0.f;
     int32_t accp[OVL ? 3 : 1][3][2];
     auto product_ahead = [&](const uint32_t *xa_buf) {   // the twelve non-sampler warps (OVL)
@@ -320,7 +325,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
       for (int gate = 0; gate < 3; gate++) s_accx[(e * 3 + gate) * 32 + lane] = make_int2(acc[gate][0], acc[gate][1]);
     };
     for (int s = tid; s < NS; s += kThreads) {
-      const int gs = min(stream0 + s, B - 1);
+      const int gs = min(stream0 + s, Bend - 1);
       s_deemph[s] = A.st.deemph[gs];
       s_lexc[s] = A.st.last_exc[gs];
 #pragma unroll
@@ -334,13 +339,13 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
       t_lpc = A.lpc[((size_t)f * B + tgs) * 16 + l16];
       for (int i = tid; i < NS * kRowsB; i += kThreads) {
         const int s = i / kRowsB, j = i % kRowsB;
-        const int gs = min(stream0 + s, B - 1);
+        const int gs = min(stream0 + s, Bend - 1);
         s_condb[i] = A.cond_b[((size_t)f * B + gs) * kRowsB + j];
       }
       int my_act = 0;
       if (tid < NS) {
         const int gs = stream0 + tid;
-        my_act = (gs < B) ? (int)A.active[(size_t)f * B + gs] : 0;
+        my_act = (gs < Bend) ? (int)A.active[(size_t)f * B + gs] : 0;
         s_act[tid] = my_act;
       }
       const int any_act = __syncthreads_or(my_act);
@@ -350,7 +355,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
         if (!A.forced || true) {
           for (int i = tid; i < NS * A.spf; i += kThreads) {
             const int s = i / A.spf, k = i % A.spf;
-            if (stream0 + s < B) {
+            if (stream0 + s < Bend) {
               A.pcm[(size_t)(stream0 + s) * row_len + out_base + k] = 0;
               if (DEBUG && A.trace) {
                 LPCNetB200Trace tr = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -362,7 +367,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             for (size_t i = tid; i < (size_t)NS * A.spf * 256; i += kThreads) {
               const int s = (int)(i / ((size_t)A.spf * 256));
               const size_t r = i % ((size_t)A.spf * 256);
-              if (stream0 + s < B) A.logits[((size_t)(stream0 + s) * row_len + out_base) * 256 + r] = 0.f;
+              if (stream0 + s < Bend) A.logits[((size_t)(stream0 + s) * row_len + out_base) * 256 + r] = 0.f;
             }
           }
         }
@@ -389,7 +394,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
       const float *condA_f = A.cond_a + (size_t)f * B * kRowsAP;
       float2 cond_reg[3][3];
       if (CREG) {
-        const int gs = min(stream0 + g, B - 1);
+        const int gs = min(stream0 + g, Bend - 1);
 #pragma unroll
         for (int u = 0; u < 3; u++)
           ldg_zrh(condA_f + (size_t)gs * kRowsAP + ((warp + u * kWarps) * 4 + t) * 8, cond_reg[u][0], cond_reg[u][1], cond_reg[u][2]);
@@ -430,7 +435,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             float2 cv[3][NV / 2], e1[3][NV / 2], e2[3][NV / 2], e3[3][NV / 2];
 #pragma unroll
             for (int h = 0; h < NV / 2; h++) {
-              const int gs = min(stream0 + sA + 8 * h, B - 1);
+              const int gs = min(stream0 + sA + 8 * h, Bend - 1);
               if (CREG) { cv[0][h] = cond_reg[u][0]; cv[1][h] = cond_reg[u][1]; cv[2][h] = cond_reg[u][2]; }
               else ldg_zrh(condA_f + (size_t)gs * kRowsAP + lane_off + u * (kWarps * 32), cv[0][h], cv[1][h], cv[2][h]);
               if (PH) {
@@ -662,7 +667,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
 #pragma unroll
             for (int lvl = 0; lvl < 4; lvl++) mm = 2 * mm + __shfl_sync(0xffffffffu, bit, gbase + mm);
             int exc = ((n - 16) << 4) | (mm - 16);
-            if (DEBUG && A.logits && stream0 + s < B) {
+            if (DEBUG && A.logits && stream0 + s < Bend) {
               float *lg = A.logits + ((size_t)(stream0 + s) * row_len + out_base + step) * 256;
               for (int k = 0; k < 16; k++) {
                 const int nd = k * 16 + l16;
@@ -674,8 +679,8 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             // values in all 16 lanes), the history shifts by one lane, lane 0 stores.  Shuffles stay outside the
             // per-stream conditions: the two streams of a warp may differ in `act`.
             {
-              const bool valid = stream0 + s < B;
-              const size_t oidx = (size_t)min(stream0 + s, B - 1) * row_len + out_base + step;
+              const bool valid = stream0 + s < Bend;
+              const size_t oidx = (size_t)min(stream0 + s, Bend - 1) * row_len + out_base + step;
               const float dm = s_deemph[s];
               float pcm;
               int forced_v = 0;
@@ -739,18 +744,18 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
 #pragma unroll
         for (int h = 0; h < NV / 2; h++) {
           const int s = mt * VR + g + h * 8;
-          if (stream0 + s < B) *reinterpret_cast<float2 *>(A.st.gru_a + (size_t)(stream0 + s) * kN + ug * 8 + 2 * t) = a_reg[u][mt][h];
+          if (stream0 + s < Bend) *reinterpret_cast<float2 *>(A.st.gru_a + (size_t)(stream0 + s) * kN + ug * 8 + 2 * t) = a_reg[u][mt][h];
         }
     }
     for (int i = tid; i < NS * 16; i += kThreads) {
       const int s = i >> 4, j = i & 15;
-      if (stream0 + s < B) {
+      if (stream0 + s < Bend) {
         A.st.gru_b[(size_t)(stream0 + s) * kNB + j] = s_bst[s * 20 + j];
       }
     }
-    if (grp < NS && stream0 + grp < B) A.st.last_sig[(size_t)(stream0 + grp) * 16 + l16] = t_x;
+    if (grp < NS && stream0 + grp < Bend) A.st.last_sig[(size_t)(stream0 + grp) * 16 + l16] = t_x;
     for (int s = tid; s < NS; s += kThreads) {
-      if (stream0 + s < B) {
+      if (stream0 + s < Bend) {
         A.st.deemph[stream0 + s] = s_deemph[s];
         A.st.last_exc[stream0 + s] = s_lexc[s];
 #pragma unroll
@@ -773,13 +778,17 @@ static cudaError_t launch_tile(const SampleArgs &a, int n_sms, cudaStream_t s) {
   // Arithmetic rcpps when it was verified against the table on this GPU (model.cu): no shared-memory lookups,
   // 2-4 % faster at every tile size (measured).  The trace/logit variants always use the table.
   const bool ra = a.m.rcp_arith != 0;
+  const bool sub = a.stream_begin != 0 || a.stream_end != 0;
+  if (sub && dbg) return cudaErrorInvalidValue;     // the trace / logit builds advance whole batches only
   void (*kern)(const SampleArgs) =
       dbg ? (fix ? sample_kernel<MT, VR, true, true, false> : sample_kernel<MT, VR, true, false, false>)
+      : sub ? (ra ? (fix ? sample_kernel<MT, VR, false, true, true, true> : sample_kernel<MT, VR, false, false, true, true>)
+                  : (fix ? sample_kernel<MT, VR, false, true, false, true> : sample_kernel<MT, VR, false, false, false, true>))
       : ra ? (fix ? sample_kernel<MT, VR, false, true, true> : sample_kernel<MT, VR, false, false, true>)
            : (fix ? sample_kernel<MT, VR, false, true, false> : sample_kernel<MT, VR, false, false, false>);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  const int n_tiles = (a.n_streams + NS - 1) / NS;
+  const int n_tiles = ((a.stream_end ? a.stream_end : a.n_streams) - a.stream_begin + NS - 1) / NS;
   const int grid = n_tiles < n_sms ? n_tiles : n_sms;
   kern<<<grid, kThreads, smem, s>>>(a);
   return cudaGetLastError();

@@ -330,3 +330,24 @@ def test_sweep_size_sharded_invariance(eng, model_blob, orc_model, tile):
         ref = orcpy.OrcStream(orc_model, blob.stream_seed((lo + s) % 256)).run(feats[s])[0]
         assert np.array_equal(pcm[s], ref), s
     bt.close()
+
+
+def test_mixed_tile_schedule_is_invisible(eng, model_blob, orc_model):
+    """One wave of 16-stream tiles plus a remainder in 8-stream tiles (the automatic schedule on a 148-SM part for
+    2368 < B <= 3552) gives the PCM of the plain 16-stream schedule, and the last streams match the oracle."""
+    B, F = 16 * 148 + 75, 3
+    base = np.stack([blob.synthetic_features(F, s) for s in range(64)])
+    feats = base[np.arange(B) % 64]
+    out = []
+    for tile in (0, 16):
+        bt = eng.Batch(model_blob, B)
+        bt.set_tile(tile)
+        for s in range(B):
+            bt.set_seed(s, blob.stream_seed(s % 64))
+        out.append(bt.synthesize(feats)[0])
+        assert bt.launch_count > 0
+        bt.close()
+    assert np.array_equal(out[0], out[1])
+    for s in (0, 2367, 2368, B - 1):
+        ref = orcpy.OrcStream(orc_model, blob.stream_seed(s % 64)).run(feats[s])[0]
+        assert np.array_equal(out[0][s], ref), s

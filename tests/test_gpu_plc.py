@@ -114,6 +114,36 @@ def test_many_streams_against_the_oracle(eng, plc_blob, plc_model):
     assert first_diff(again, got[pick]) is None
 
 
+def test_full_size_config4_compaction_is_invisible(eng, plc_blob, plc_model):
+    """BASELINE config 4 size: 4096 streams, noncausal_dc, Gilbert losses.  The gathered (compact) sample segments
+    and the in-place ones give the same PCM for every stream, and sampled streams match the oracle."""
+    B, F, opt = 4096, 14, 5
+    base = [blob.synthetic_pcm(F, 100 + s) for s in range(32)]
+    pcm = np.stack([base[s % 32] for s in range(B)])
+    lost = np.stack([blob.synthetic_loss_pattern(F, 7 + s, 0.6, 0.1) for s in range(B)])
+    assert 0.05 < lost.mean() < 0.4
+
+    def run():
+        pb = eng.PLCBatch(plc_blob, B, opt)
+        for s in range(0, B, 7):
+            pb.set_seed(s, blob.stream_seed(s))
+        out = pb.process(pcm, lost)
+        pb.close()
+        return out
+
+    got = run()
+    os.environ["LPCNET_B200_NO_COMPACT"] = "1"
+    try:
+        plain = run()
+    finally:
+        del os.environ["LPCNET_B200_NO_COMPACT"]
+    assert first_diff(got, plain) is None
+    for s in (0, 7, 2051, 4095):
+        seed = blob.stream_seed(s) if s % 7 == 0 else b"LPCNet"
+        want = orcpy.OrcPLC(plc_model, opt, seed).run(pcm[s], lost[s])
+        assert first_diff(got[s], want) is None, (s, first_diff(got[s], want))
+
+
 def test_unsupported_modes_and_models_are_errors(eng, plc_blob, model_blob):
     with pytest.raises(engine.LPCNetError):
         eng.PLCBatch(plc_blob, 2, 0)            # causal mode is not built
