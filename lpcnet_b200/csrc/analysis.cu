@@ -167,210 +167,255 @@ __global__ void residual_kernel(AnalysisArgs A) {
 }
 
 // The pitch half of compute_frame_features (lpcnet_enc.c:540-576) and the Viterbi pass over half-frames; one block
-// per stream, thread t = lag t.  SUPER = false: process_single_frame (814-870), two half-frames per frame.
-// SUPER = true: process_superframe (579-743), eight half-frames per packet of four frames, then the pitch contour
-// regression and -- in quantize mode -- the pitch / correlation fields of the packet.
-constexpr int kPT = 256;
+// per stream.  SUPER = false: process_single_frame (814-870), two half-frames per frame.  SUPER = true:
+// process_superframe (579-743), eight half-frames per packet of four frames, then the pitch contour regression and
+// -- in quantize mode -- the pitch / correlation fields of the packet.
+//
+// Only the Viterbi pass is sequential over the frames.  The cross-correlations and the energy recurrences of the
+// chunk's half-frames ("rows") depend on the residual alone, so a group of up to 16 frames is prepared at once:
+//  * warps 0-7, thread t = lag t: the 80-term correlation of every row of the group as a j-ascending float sum
+//    (celt_pitch_xcorr's order), the frame's samples read as broadcast 16-byte loads;
+//  * warp 8, lane r = row r: the row's energies -- the double-precision recurrence over the 256 lags
+//    (lpcnet_enc.c:542-551) is a serial chain, so the 32 rows walk it side by side instead of one after the other
+//    (one thread per block did that before: 72 % of the kernel's stall samples sat at the barrier behind it).
+//    Rows are 80 floats apart, i.e. 16 banks: lanes run skewed by lane/2 steps so that a warp load touches 32 banks.
+// Then the frames of the group follow in order: normalisation, 3x interpolation, octave penalty, path update.
+constexpr int kPT = 256 + 32, kGroup = 16;
 template <bool SUPER>
 __global__ void __launch_bounds__(kPT) pitch_kernel(AnalysisArgs A) {
   constexpr int NR = SUPER ? 8 : 2;         // correlation rows (half-frames) per Viterbi pass
   extern __shared__ float sm[];
   const int s = blockIdx.x, t = threadIdx.x, F = A.n_frames, L = F * kFrame;
   if (A.stream_mask && !A.stream_mask[s]) return;
+  const int GR = F < kGroup ? F : kGroup;   // frames per group
+  const bool lagthr = t < kPMax;
   float *ebuf = sm;                         // [256 + L]
-  float *xc = ebuf + kPMax + L;             // [NR][256]
-  float *path0 = xc + NR * kPMax;           // [256]
+  float *xcg = ebuf + kPMax + L;            // [2*GR][256] correlations, then the normalised / interpolated rows
+  float *enr = xcg + 2 * GR * kPMax;        // [2*GR][256] 1 + ener0 + ener1 of every lag, as the reference's float
+  float *path0 = enr + 2 * GR * kPMax;      // [256]
   float *path1 = path0 + kPMax;             // [256]
-  double *ener1 = reinterpret_cast<double *>(path1 + kPMax);   // [256]
-  int *prev = reinterpret_cast<int *>(ener1 + kPMax);          // [NR][256]
+  int *prev = reinterpret_cast<int *>(path1 + kPMax);          // [NR][256]
   float *redv = reinterpret_cast<float *>(prev + NR * kPMax);  // [8]
   int *redi = reinterpret_cast<int *>(redv + 8);               // [8]
-  __shared__ float ener0_s[NR];
+  float *e0s = reinterpret_cast<float *>(redi + 8);            // [2*GR] frame_weight before normalisation
   __shared__ float path_all_s;
   __shared__ int best_i_s;
 
   const float *Ss = A.S + (size_t)s * (L + 1);
-  ebuf[t] = A.st.e_hist[(size_t)s * kPMax + t];
+  if (lagthr) {
+    ebuf[t] = A.st.e_hist[(size_t)s * kPMax + t];
+    path0[t] = A.st.path[(size_t)s * kPMax + t];
+    path1[t] = 0.f;
+  }
   for (int n = t; n < L; n += kPT) ebuf[kPMax + n] = Ss[n + 1] + .7f * Ss[n];
-  path0[t] = A.st.path[(size_t)s * kPMax + t];
-  path1[t] = 0.f;
   if (t == 0) { path_all_s = A.st.path_all[s]; best_i_s = A.st.best_i[s]; }
   __syncthreads();
 
-  for (int f = 0; f < F; f++) {
-    const int r0 = SUPER ? 2 * (f & 3) : 0;   // rows 2+2*pcount+sub of the reference's xc / frame_weight
-    for (int sub = 0; sub < 2; sub++) {
-      const int row = r0 + sub;
-      const float *ys = ebuf + f * kFrame + sub * (kFrame / 2), *xs = ys + kPMax;
+  for (int g0 = 0; g0 < F; g0 += GR) {
+    const int gf = F - g0 < GR ? F - g0 : GR, rows = 2 * gf;
+    if (lagthr) {
       // celt_pitch_xcorr (pitch.c:43-83, pitch.h:42-105): every lag is a j-ascending sum from zero
-      float acc = 0;
-      for (int j = 0; j < kFrame / 2; j++) acc = acc + xs[j] * ys[t + j];
-      if (t == 0) {
-        // ener1 (double) walks the lags: += y[i+79]^2 before lag i, -= y[i]^2 after it (lpcnet_enc.c:542-551)
-        float e1f = 0;
-        for (int j = 0; j < kFrame / 2 - 1; j++) e1f = e1f + ys[j] * ys[j];
-        double e1 = e1f;
-        for (int i = 0; i < kPMax; i++) {
-          e1 += (double)(ys[i + kFrame / 2 - 1] * ys[i + kFrame / 2 - 1]);
-          ener1[i] = e1;
-          e1 -= (double)(ys[i] * ys[i]);
+      for (int r = 0; r < rows; r++) {
+        const float *ys = ebuf + g0 * kFrame + r * (kFrame / 2), *xs = ys + kPMax;
+        float acc = 0;
+#pragma unroll 5
+        for (int j = 0; j < kFrame / 2; j += 4) {
+          const float4 x4 = *reinterpret_cast<const float4 *>(xs + j);
+          acc = acc + x4.x * ys[t + j];
+          acc = acc + x4.y * ys[t + j + 1];
+          acc = acc + x4.z * ys[t + j + 2];
+          acc = acc + x4.w * ys[t + j + 3];
         }
-      } else if (t == 32) {
-        float e0 = 0;
-        for (int j = 0; j < kFrame / 2; j++) e0 = e0 + xs[j] * xs[j];
-        ener0_s[row] = e0;
+        xcg[r * kPMax + t] = acc;
       }
-      __syncthreads();
-      const float ener = (float)((double)(1 + ener0_s[row]) + ener1[t]);
-      xc[row * kPMax + t] = 2 * acc / ener;
-      __syncthreads();
-      // 3x upsampled correlation, keep the max (lpcnet_enc.c:552-569)
-      float up = 0.f;
-      if (t >= 4 && t < kPMax - 4) {
-        const float interp[7] = {0.026184f, -0.098339f, 0.369938f, 0.837891f, -0.184969f, 0.070242f, -0.020947f};
-        const float *c = xc + row * kPMax;
-        float v1 = 0, v2 = 0;
-#pragma unroll
-        for (int j = 0; j < 7; j++) {
-          v1 += c[t - 3 + j] * interp[j];
-          v2 += c[t + 3 - j] * interp[j];
+    } else {
+      const int r = t - kPMax, skew = r >> 1;
+      const bool on = r < rows;
+      const float *ys = ebuf + g0 * kFrame + (on ? r : 0) * (kFrame / 2), *xs = ys + kPMax;
+      // ener0 = celt_inner_prod(x, x, 80), ener1 = celt_inner_prod(y, y, 79) (lpcnet_enc.c:540-541): float sums
+      float e0 = 0, e1f = 0;
+      for (int st = 0; st < kFrame / 2 + 16; st++) {
+        const int j = st - skew;
+        if (on && j >= 0 && j < kFrame / 2) {
+          e0 = e0 + xs[j] * xs[j];
+          if (j < kFrame / 2 - 1) e1f = e1f + ys[j] * ys[j];
         }
-        up = fmaxf(c[t], fmaxf(v1, v2));
       }
-      __syncthreads();
-      if (t >= 4 && t < kPMax - 4) xc[row * kPMax + t] = up;
+      // ener1 (double) walks the lags: += y[i+79]^2 before lag i, -= y[i]^2 after it (lpcnet_enc.c:542-551)
+      double e1 = e1f;
+      float *out = enr + (on ? r : 0) * kPMax;
+      for (int st = 0; st < kPMax + 16; st++) {
+        const int i = st - skew;
+        if (on && i >= 0 && i < kPMax) {
+          const float a = ys[i + kFrame / 2 - 1], b = ys[i];
+          e1 += (double)(a * a);
+          out[i] = (float)((double)(1 + e0) + e1);
+          e1 -= (double)(b * b);
+        }
+      }
+      if (on) e0s[r] = e0;
     }
     __syncthreads();
-    if (SUPER && (f & 3) != 3) continue;      // the superframe pass runs after the packet's fourth frame
-    // process_single_frame (lpcnet_enc.c:814-870) / process_superframe (579-630): the same pass over 2 / 8 rows
-    float fws = 1e-15f;
+    for (int fl = 0; fl < gf; fl++) {
+      const int f = g0 + fl;
+      // rows 2+2*pcount+sub of the reference's xc / frame_weight: the packet's (SUPER) or the frame's rows
+      const int pr0 = SUPER ? 2 * (fl & ~3) : 2 * fl;
+      float *xc = xcg + pr0 * kPMax;
+      const float *ener0_s = e0s + pr0;
+      for (int sub = 0; sub < 2; sub++) {
+        const int row = 2 * fl + sub;
+        float *c = xcg + row * kPMax;
+        if (lagthr) c[t] = 2 * c[t] / enr[row * kPMax + t];
+        __syncthreads();
+        // 3x upsampled correlation, keep the max (lpcnet_enc.c:552-569)
+        float up = 0.f;
+        if (t >= 4 && t < kPMax - 4) {
+          const float interp[7] = {0.026184f, -0.098339f, 0.369938f, 0.837891f, -0.184969f, 0.070242f, -0.020947f};
+          float v1 = 0, v2 = 0;
 #pragma unroll
-    for (int r = 0; r < NR; r++) fws += ener0_s[r];
-    float fw[NR];
-#pragma unroll
-    for (int r = 0; r < NR; r++) fw[r] = ener0_s[r] * ((float)NR / fws);
-#pragma unroll
-    for (int sub = 0; sub < NR; sub++) {
-      float *c = xc + sub * kPMax;
-      // octave penalty: the values it compares against sit at higher lags than the one it scales
-      float cv = c[t];
-      if (t < kPMax - 2 * kPMin) {
-        const float half = fmaxf(fmaxf(c[(kPMax + t) / 2], c[(kPMax + t + 2) / 2]), c[(kPMax + t - 1) / 2]);
-        if (cv < half * 1.1f) cv *= .8f;
-      }
-      __syncthreads();
-      c[t] = cv;
-      float v = -3.0e38f;
-      if (t < kPMax - kPMin) {
-        float max_prev = path_all_s - 6.f;
-        int pp = best_i_s;
-        for (int j = (t < 4 ? -t : -4); j <= 4 && t + j < kPMax - kPMin; j++) {
-          const int aj = j < 0 ? -j : j;
-          const float cand = path0[t + j] - .02f * (float)aj * (float)aj;
-          if (cand > max_prev) { max_prev = cand; pp = t + j; }
-        }
-        prev[sub * kPMax + t] = pp;
-        v = max_prev + fw[sub] * cv;
-        path1[t] = v;
-      }
-      // first maximum over the lags (strict '>' in lag order, starting from -1e15 / lag 0)
-      int bi = t;
-#pragma unroll
-      for (int o = 16; o; o >>= 1) {
-        const float ov = __shfl_down_sync(0xffffffffu, v, o);
-        const int oi = __shfl_down_sync(0xffffffffu, bi, o);
-        if (ov > v || (ov == v && oi < bi)) { v = ov; bi = oi; }
-      }
-      if ((t & 31) == 0) { redv[t >> 5] = v; redi[t >> 5] = bi; }
-      __syncthreads();
-      if (t == 0) {
-        float mv = -1e15f;
-        int mi = 0;
-        for (int w = 0; w < kPT / 32; w++)
-          if (redv[w] > mv) { mv = redv[w]; mi = redi[w]; }
-        path_all_s = mv; best_i_s = mi;
-      }
-      __syncthreads();
-      if (t < kPMax - kPMin) path1[t] -= path_all_s;
-      path0[t] = path1[t];
-      __syncthreads();
-    }
-    if (t == 0) {
-      int bi = best_i_s, best[NR];
-      float frame_corr = 0;
-#pragma unroll
-      for (int sub = NR - 1; sub >= 0; sub--) {
-        best[sub] = kPMax - bi;
-        frame_corr += fw[sub] * xc[sub * kPMax + bi];
-        bi = prev[sub * kPMax + bi];
-      }
-      frame_corr /= (float)NR;
-      if (!SUPER) {
-        float *out = A.features + ((size_t)s * A.total_frames + A.frame0 + f) * kNF;
-        out[kBands] = .01f * (float)(max(66, min(510, best[0] + best[1])) - 200);
-        out[kBands + 1] = frame_corr - .5f;
-      } else {
-        // lpcnet_enc.c:640-699: weighted linear regression of the pitch contour, then its quantisation
-        const int quantize = A.quantize;
-        if (quantize && frame_corr < 0) frame_corr = 0;
-        float sx = 0, sxx = 0, sxy = 0, sy = 0, sw = 0;
-#pragma unroll
-        for (int sub = 2; sub < 10; sub++) {
-          const float w = fw[sub - 2];
-          sw += w;
-          sx += w * (float)sub;
-          sxx += w * (float)sub * (float)sub;
-          sxy += w * (float)sub * (float)best[sub - 2];
-          sy += w * (float)best[sub - 2];
-        }
-        const int voiced = (double)frame_corr >= .3;
-        float best_a = (sw * sxy - sx * sy) / (sw * sxx - sx * sx);
-        int corr_id;
-        if (voiced) {
-          const float mean_pitch = sy / sw;
-          const float max_a = mean_pitch / 32.f;
-          const float lo = -max_a > best_a ? -max_a : best_a;
-          best_a = max_a < lo ? max_a : lo;
-          corr_id = cvt_x86(floor((double)((frame_corr - .3f) / .175f)));
-          if (quantize) frame_corr = 0.3875f + .175f * (float)corr_id;
-        } else {
-          best_a = 0;
-          corr_id = cvt_x86(floor((double)(frame_corr / .075f)));
-          if (quantize) frame_corr = 0.0375f + .075f * (float)corr_id;
-        }
-        const float best_b = (sy - best_a * sx) / sw;
-        const float center_pitch = best_b + 5.5f * best_a;
-        int main_pitch = cvt_x86(floor(.5 + 21. * 1.442695041 * log((double)(center_pitch / 32.f))));
-        main_pitch = max(0, min(63, main_pitch));
-        int modulation = cvt_x86(floor(.5 + (double)(112.f * best_a / center_pitch)));
-        modulation = max(-3, min(3, modulation));
-        const int fr0 = A.frame0 + f - 3;
-        for (int sub = 0; sub < 4; sub++) {
-          float *out = A.features + ((size_t)s * A.total_frames + fr0 + sub) * kNF;
-          if (quantize) {
-            float p = __ldg(A.pitch_pow + main_pitch);
-            p *= 1.f + (float)modulation / 16.f / 7.f * (float)(2 * sub - 3);
-            const float lo = 33.f > p ? 33.f : p;
-            p = 255.f < lo ? 255.f : lo;
-            out[kBands] = .02f * (p - 100.f);
-          } else {
-            out[kBands] = .01f * (float)(max(66, min(510, best[2 * sub] + best[2 * sub + 1])) - 200);
+          for (int j = 0; j < 7; j++) {
+            v1 += c[t - 3 + j] * interp[j];
+            v2 += c[t + 3 - j] * interp[j];
           }
-          out[kBands + 1] = frame_corr - .5f;
+          up = fmaxf(c[t], fmaxf(v1, v2));
         }
-        if (quantize) {
-          int *id = A.ids + ((size_t)s * (A.total_frames / 4) + fr0 / 4) * kIds;
-          id[1] = main_pitch;
-          id[2] = voiced ? modulation + 4 : 0;
-          id[3] = corr_id;
+        __syncthreads();
+        if (t >= 4 && t < kPMax - 4) c[t] = up;
+      }
+      __syncthreads();
+      if (SUPER && (fl & 3) != 3) continue;     // the superframe pass runs after the packet's fourth frame
+      // process_single_frame (lpcnet_enc.c:814-870) / process_superframe (579-630): the same pass over 2 / 8 rows
+      float fws = 1e-15f;
+#pragma unroll
+      for (int r = 0; r < NR; r++) fws += ener0_s[r];
+      float fw[NR];
+#pragma unroll
+      for (int r = 0; r < NR; r++) fw[r] = ener0_s[r] * ((float)NR / fws);
+#pragma unroll
+      for (int sub = 0; sub < NR; sub++) {
+        float *c = xc + sub * kPMax;
+        // octave penalty: the values it compares against sit at higher lags than the one it scales
+        float cv = lagthr ? c[t] : 0.f;
+        if (t < kPMax - 2 * kPMin) {
+          const float half = fmaxf(fmaxf(c[(kPMax + t) / 2], c[(kPMax + t + 2) / 2]), c[(kPMax + t - 1) / 2]);
+          if (cv < half * 1.1f) cv *= .8f;
+        }
+        __syncthreads();
+        if (lagthr) c[t] = cv;
+        float v = -3.0e38f;
+        if (t < kPMax - kPMin) {
+          float max_prev = path_all_s - 6.f;
+          int pp = best_i_s;
+          for (int j = (t < 4 ? -t : -4); j <= 4 && t + j < kPMax - kPMin; j++) {
+            const int aj = j < 0 ? -j : j;
+            const float cand = path0[t + j] - .02f * (float)aj * (float)aj;
+            if (cand > max_prev) { max_prev = cand; pp = t + j; }
+          }
+          prev[sub * kPMax + t] = pp;
+          v = max_prev + fw[sub] * cv;
+          path1[t] = v;
+        }
+        // first maximum over the lags (strict '>' in lag order, starting from -1e15 / lag 0)
+        int bi = t;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+          const float ov = __shfl_down_sync(0xffffffffu, v, o);
+          const int oi = __shfl_down_sync(0xffffffffu, bi, o);
+          if (ov > v || (ov == v && oi < bi)) { v = ov; bi = oi; }
+        }
+        if (lagthr && (t & 31) == 0) { redv[t >> 5] = v; redi[t >> 5] = bi; }
+        __syncthreads();
+        if (t == 0) {
+          float mv = -1e15f;
+          int mi = 0;
+          for (int w = 0; w < kPMax / 32; w++)
+            if (redv[w] > mv) { mv = redv[w]; mi = redi[w]; }
+          path_all_s = mv; best_i_s = mi;
+        }
+        __syncthreads();
+        if (t < kPMax - kPMin) path1[t] -= path_all_s;
+        if (lagthr) path0[t] = path1[t];
+        __syncthreads();
+      }
+      if (t == 0) {
+        int bi = best_i_s, best[NR];
+        float frame_corr = 0;
+#pragma unroll
+        for (int sub = NR - 1; sub >= 0; sub--) {
+          best[sub] = kPMax - bi;
+          frame_corr += fw[sub] * xc[sub * kPMax + bi];
+          bi = prev[sub * kPMax + bi];
+        }
+        frame_corr /= (float)NR;
+        if (!SUPER) {
+          float *out = A.features + ((size_t)s * A.total_frames + A.frame0 + f) * kNF;
+          out[kBands] = .01f * (float)(max(66, min(510, best[0] + best[1])) - 200);
+          out[kBands + 1] = frame_corr - .5f;
+        } else {
+          // lpcnet_enc.c:640-699: weighted linear regression of the pitch contour, then its quantisation
+          const int quantize = A.quantize;
+          if (quantize && frame_corr < 0) frame_corr = 0;
+          float sx = 0, sxx = 0, sxy = 0, sy = 0, sw = 0;
+#pragma unroll
+          for (int sub = 2; sub < 10; sub++) {
+            const float w = fw[sub - 2];
+            sw += w;
+            sx += w * (float)sub;
+            sxx += w * (float)sub * (float)sub;
+            sxy += w * (float)sub * (float)best[sub - 2];
+            sy += w * (float)best[sub - 2];
+          }
+          const int voiced = (double)frame_corr >= .3;
+          float best_a = (sw * sxy - sx * sy) / (sw * sxx - sx * sx);
+          int corr_id;
+          if (voiced) {
+            const float mean_pitch = sy / sw;
+            const float max_a = mean_pitch / 32.f;
+            const float lo = -max_a > best_a ? -max_a : best_a;
+            best_a = max_a < lo ? max_a : lo;
+            corr_id = cvt_x86(floor((double)((frame_corr - .3f) / .175f)));
+            if (quantize) frame_corr = 0.3875f + .175f * (float)corr_id;
+          } else {
+            best_a = 0;
+            corr_id = cvt_x86(floor((double)(frame_corr / .075f)));
+            if (quantize) frame_corr = 0.0375f + .075f * (float)corr_id;
+          }
+          const float best_b = (sy - best_a * sx) / sw;
+          const float center_pitch = best_b + 5.5f * best_a;
+          int main_pitch = cvt_x86(floor(.5 + 21. * 1.442695041 * log((double)(center_pitch / 32.f))));
+          main_pitch = max(0, min(63, main_pitch));
+          int modulation = cvt_x86(floor(.5 + (double)(112.f * best_a / center_pitch)));
+          modulation = max(-3, min(3, modulation));
+          const int fr0 = A.frame0 + f - 3;
+          for (int sub = 0; sub < 4; sub++) {
+            float *out = A.features + ((size_t)s * A.total_frames + fr0 + sub) * kNF;
+            if (quantize) {
+              float p = __ldg(A.pitch_pow + main_pitch);
+              p *= 1.f + (float)modulation / 16.f / 7.f * (float)(2 * sub - 3);
+              const float lo = 33.f > p ? 33.f : p;
+              p = 255.f < lo ? 255.f : lo;
+              out[kBands] = .02f * (p - 100.f);
+            } else {
+              out[kBands] = .01f * (float)(max(66, min(510, best[2 * sub] + best[2 * sub + 1])) - 200);
+            }
+            out[kBands + 1] = frame_corr - .5f;
+          }
+          if (quantize) {
+            int *id = A.ids + ((size_t)s * (A.total_frames / 4) + fr0 / 4) * kIds;
+            id[1] = main_pitch;
+            id[2] = voiced ? modulation + 4 : 0;
+            id[3] = corr_id;
+          }
         }
       }
+      __syncthreads();
     }
-    __syncthreads();
   }
   // carry the stream state to the next call
-  A.st.e_hist[(size_t)s * kPMax + t] = ebuf[L + t];
-  A.st.path[(size_t)s * kPMax + t] = path0[t];
+  if (lagthr) {
+    A.st.e_hist[(size_t)s * kPMax + t] = ebuf[L + t];
+    A.st.path[(size_t)s * kPMax + t] = path0[t];
+  }
   if (t < kOverlap) A.st.p_hist[(size_t)s * kOverlap + t] = A.P[(size_t)s * (kOverlap + L) + L + t];
   if (t == 0) {
     A.st.path_all[s] = path_all_s;
@@ -381,7 +426,8 @@ __global__ void __launch_bounds__(kPT) pitch_kernel(AnalysisArgs A) {
 }
 
 size_t pitch_smem(int F, int rows) {
-  return (size_t)(kPMax + F * kFrame + rows * kPMax + 2 * kPMax) * 4 + kPMax * 8 + (size_t)rows * kPMax * 4 + 64;
+  const int GR = F < kGroup ? F : kGroup;
+  return (size_t)(kPMax + F * kFrame + 2 * (2 * GR * kPMax) + 2 * kPMax + rows * kPMax + 16 + 2 * GR) * 4 + 64;
 }
 
 #include "vq.cuh"
@@ -466,7 +512,7 @@ int analysis_device(LPCNetFeatureBatch *b, const short *d16, const float *df, in
     const size_t nr = (size_t)B * F * kFrame;
     residual_kernel<<<(unsigned)((nr + 255) / 256 > 65535 * 16 ? 65535 * 16 : (nr + 255) / 256), 256, 0, b->stream>>>(A);
     if (mode) pitch_kernel<true><<<B, kPT, pitch_smem(F, 8), b->stream>>>(A);
-    else pitch_kernel<false><<<B, kPT, pitch_smem(F, 2), b->stream>>>(A);
+    else pitch_kernel<false><<<B, kPT, pitch_smem(F, 2), b->stream>>>(A);    // (> 48 KB: opted in at create)
     b->launches += 4;
     CKA(cudaGetLastError());
   }
@@ -587,6 +633,9 @@ LPCNetFeatureBatch *lpcnet_feature_batch_create(int n_streams, int device) {
   char *tp = static_cast<char *>(b->tab_alloc);
   cudaMemcpy(tp + o_pp, pp.data(), pp.size() * 4, cudaMemcpyHostToDevice);
   b->pitch_pow = (const float *)(tp + o_pp);
+  if ((e = cudaFuncSetAttribute(pitch_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pitch_smem(32, 8))) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(pitch_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pitch_smem(32, 2))) != cudaSuccess)
+    return bail("cudaFuncSetAttribute(pitch kernels)", e);
   if ((e = cudaFuncSetAttribute(vq_end_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kVqEndSmem)) != cudaSuccess ||
       (e = cudaFuncSetAttribute(vq_mid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kVqMidSmem)) != cudaSuccess)
     return bail("cudaFuncSetAttribute(vq kernels)", e);
