@@ -120,6 +120,9 @@ void orc_plc_free(OrcPLC *p);
 void orc_plc_seed(OrcPLC *p, const unsigned char *data, int n);
 int orc_plc_update(OrcPLC *p, int16_t *pcm /*[160] in/out*/);
 int orc_plc_conceal(OrcPLC *p, int16_t *pcm /*[160] out*/);
+/* lpcnet_plc_fec_add (features NULL = skip one) / lpcnet_plc_fec_clear: read by the causal and codec modes only */
+void orc_plc_fec_add(OrcPLC *p, const float *features /*[20] or NULL*/);
+void orc_plc_fec_clear(OrcPLC *p);
 void orc_plc_pred(const OrcModel *m, float *gru1 /*[256]*/, float *gru2 /*[256]*/, float *out /*[20]*/, const float *in /*[57]*/);
 void orc_plc_peek(const OrcPLC *p, float *features20, float *gru1, float *gru2, int *loss_count, double *dc /*[2]*/);
 

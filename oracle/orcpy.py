@@ -285,12 +285,15 @@ class OrcPLC:
         L.orc_plc_peek(self.h, _p(f), _p(g1), _p(g2), _p(lc), _p(dc))
         return f, g1, g2, dc
 
-    def run(self, pcm, lost):
+    def run(self, pcm, lost, fec=None):
         """pcm int16 [n_frames*160], lost bool [n_frames] -> concealed output int16 [n_frames*160]
         (the non-causal mode delays the signal by 80 samples)."""
         out = np.ascontiguousarray(pcm, np.int16).copy()
         L = self.m.L.lib
+        L.orc_plc_fec_add.argtypes = [C.c_void_p, C.c_void_p]
         for f, l in enumerate(lost):
+            for v in (fec or {}).get(f, []):
+                L.orc_plc_fec_add(self.h, None if v is None else _p(np.ascontiguousarray(v, np.float32)))
             fr = out[f * 160:(f + 1) * 160]
             if l:
                 fr[:] = 0

@@ -282,6 +282,8 @@ void ref_plc_free(void *hp) {
 void ref_plc_seed(void *hp, const unsigned char *data, int n) { kiss99_srand(&((RefPLC *)hp)->st->lpcnet.rng, data, n); }
 int ref_plc_update(void *hp, short *pcm) { return lpcnet_plc_update(((RefPLC *)hp)->st, pcm); }
 int ref_plc_conceal(void *hp, short *pcm) { return lpcnet_plc_conceal(((RefPLC *)hp)->st, pcm); }
+void ref_plc_fec_add(void *hp, const float *features) { lpcnet_plc_fec_add(((RefPLC *)hp)->st, features); }
+void ref_plc_fec_clear(void *hp) { lpcnet_plc_fec_clear(((RefPLC *)hp)->st); }
 /* observable PLC state for step-by-step comparison */
 void ref_plc_peek(void *hp, float *features20, float *gru1, float *gru2, int *loss_count, double *dc /*[2]*/) {
   LPCNetPLCState *st = ((RefPLC *)hp)->st;

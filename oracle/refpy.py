@@ -259,9 +259,13 @@ class RefPLC:
             self.L.lib.ref_plc_free(self.h)
             self.h = None
 
-    def run(self, pcm, lost):
+    def run(self, pcm, lost, fec=None):
+        """fec: {frame: [features20 | None, ...]} handed to lpcnet_plc_fec_add before that frame is processed"""
         out = np.ascontiguousarray(pcm, np.int16).copy()
+        self.L.lib.ref_plc_fec_add.argtypes = [C.c_void_p, C.c_void_p]
         for f, l in enumerate(lost):
+            for v in (fec or {}).get(f, []):
+                self.L.lib.ref_plc_fec_add(self.h, None if v is None else _p(np.ascontiguousarray(v, np.float32)))
             fr = out[f * 160:(f + 1) * 160]
             if l:
                 fr[:] = 0
