@@ -251,8 +251,8 @@ LPCNET_B200_EXPORT void lpcnet_plc_destroy(LPCNetPLCState *st);
 LPCNET_B200_EXPORT int lpcnet_plc_load_model(LPCNetPLCState *st, const unsigned char *data, int len);
 /* lpcnet_plc_reset (src/lpcnet_plc.c:46-60): back to the state after lpcnet_plc_init + lpcnet_plc_load_model. */
 LPCNET_B200_EXPORT void lpcnet_plc_reset(LPCNetPLCState *st);
-/* The FEC queue (include/lpcnet.h:213-215, src/lpcnet_plc.c:111-132) is read by the causal entry points only; in the
- * non-causal mode built here the calls are accepted and -- as in the reference -- do not change the output. */
+/* The FEC queue (include/lpcnet.h:213-215, src/lpcnet_plc.c:111-132): read by the causal and codec modes
+ * (get_fec_or_pred); in the non-causal mode -- as in the reference -- it does not change the output. */
 LPCNET_B200_EXPORT void lpcnet_plc_fec_add(LPCNetPLCState *st, const float *features);
 LPCNET_B200_EXPORT void lpcnet_plc_fec_clear(LPCNetPLCState *st);
 LPCNET_B200_EXPORT int lpcnet_plc_update(LPCNetPLCState *st, short *pcm);
@@ -269,6 +269,10 @@ LPCNET_B200_EXPORT int lpcnet_plc_batch_n_streams(const LPCNetPLCBatch *b);
 LPCNET_B200_EXPORT int lpcnet_plc_batch_set_seed(LPCNetPLCBatch *b, int stream, const unsigned char *data, int n);
 LPCNET_B200_EXPORT long long lpcnet_plc_batch_launch_count(const LPCNetPLCBatch *b);
 LPCNET_B200_EXPORT int lpcnet_plc_batch_reset(LPCNetPLCBatch *b);
+/* lpcnet_plc_fec_add / _fec_clear for one stream of the batch (features: 20 floats, NULL = "skip one"); the vectors
+ * a call of lpcnet_plc_batch_process consumes must have been added before it. */
+LPCNET_B200_EXPORT int lpcnet_plc_batch_fec_add(LPCNetPLCBatch *b, int stream, const float *features);
+LPCNET_B200_EXPORT int lpcnet_plc_batch_fec_clear(LPCNetPLCBatch *b, int stream);
 LPCNET_B200_EXPORT int lpcnet_plc_batch_process(LPCNetPLCBatch *b, const unsigned char *lost, short *pcm, int n_frames);
 /* Frame-rate state of one stream for step-by-step checks: st->features[0..20), the predictor's two GRU states
  * (256 each), {dc_mem, syn_dc}; any pointer may be NULL. */

@@ -282,3 +282,13 @@ def synthetic_codebooks(seed: int = 99) -> np.ndarray:
     cb = [rng.standard_normal(1024 * 17) * 0.3 for _ in range(3)]
     cb.append(rng.standard_normal(4096 * 18) * 0.3)
     return np.concatenate([c.astype(np.float32) for c in cb])
+
+
+def synthetic_fec(n_frames: int, stream: int) -> dict:
+    """Synthetic FEC feature vectors for the causal PLC tests: {frame: [20 floats | None, ...]} handed to
+    lpcnet_plc_fec_add before that frame (None = "skip one"); none for stream 0.  Seed 50 + stream."""
+    if stream == 0:
+        return {}
+    rng = np.random.default_rng(50 + stream)
+    return {f: [None if rng.random() < 0.2 else (rng.standard_normal(20) * 0.5).astype(np.float32)
+                for _ in range(int(rng.integers(0, 3)))] for f in range(n_frames)}

@@ -295,13 +295,20 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
 }  // namespace
 
 // ---- hooks for the PLC driver (plc.cu) ----
+int lpcb::default_features_delay() {
+  std::lock_guard<std::mutex> lk(g_cfg_mu);
+  return g_default_delay;
+}
+
 BatchView lpcb::batch_view(LPCNetBatch *b) { return BatchView{b->st, &b->model, b->stream, b->n_streams, b->device}; }
 
-int lpcb::batch_frame_network_masked(LPCNetBatch *b, const float *d_features, int stride, const uint8_t *d_mask) {
+int lpcb::batch_frame_network_masked(LPCNetBatch *b, const float *d_features, int stride, const uint8_t *d_mask,
+                                     bool state_only) {
   CK(cudaSetDevice(b->device));
-  if (ensure_frame_buffers(b, 1)) return -1;
+  if (ensure_frame_buffers(b, 1) || (state_only && ensure_frame_buffers(b, 1, true))) return -1;
   FrameArgs fa{};
-  fa.m = b->model.d; fa.st = b->st; fa.fb = b->fb; fa.n_streams = b->n_streams; fa.n_frames = 1;
+  fa.m = b->model.d; fa.st = b->st; fa.fb = state_only ? b->fb2 : b->fb; fa.n_streams = b->n_streams; fa.n_frames = 1;
+  fa.state_only = state_only ? 1 : 0;
   fa.features = d_features; fa.feature_stride = stride; fa.frame0 = 0; fa.total_frames = 1;
   fa.stream_mask = d_mask;
   int nl = 0;

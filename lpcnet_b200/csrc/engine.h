@@ -206,7 +206,8 @@ struct FrameArgs {
   const float *features;     // device [B][total_frames][stride]
   int feature_stride;
   int frame0, total_frames;
-  const uint8_t *stream_mask;  // nullable [B]: streams with 0 keep their frame-rate state (their outputs are unused)
+  const uint8_t *stream_mask;  // nullable [B]: streams with 0 keep their frame-rate state and their conditioning rows
+  int state_only = 0;          // run_frame_network_flush (lpcnet.c:134-144): only the frame-rate state moves
 };
 cudaError_t launch_frame_network(const FrameArgs &a, cudaStream_t s, int *n_launches);
 
@@ -232,9 +233,12 @@ struct BatchView {
   int n_streams, device;
 };
 BatchView batch_view(LPCNetBatch *b);
+int default_features_delay();   // lpcnet_b200_set_model_constants (default 2)
 // run_frame_network for one frame of the streams with mask != 0 (features: device [B][stride]); the conditioning
 // stays in the batch's frame buffers for the sample segments that follow.
-int batch_frame_network_masked(LPCNetBatch *b, const float *d_features, int stride, const uint8_t *d_mask);
+// state_only: run_frame_network_flush -- the outputs go to a scratch set, the streams' conditioning stays.
+int batch_frame_network_masked(LPCNetBatch *b, const float *d_features, int stride, const uint8_t *d_mask,
+                               bool state_only = false);
 // n sample steps (lpcnet_synthesize_tail_impl) on the conditioning of the last frame network.  flags [B]: 0 the
 // stream does not move, 1 free-running, 3 teacher-forced on d_forced [B][n]; d_out [B][n].
 // d_perm (nullable): device list of the n_act streams whose flag is not 0, ascending; when they are at most half of

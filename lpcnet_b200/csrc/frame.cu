@@ -82,6 +82,18 @@ __device__ __forceinline__ void dense_rows(const float *__restrict__ W, const fl
 }
 
 // K1: conv1 for R rows per block.
+
+// true when every row of this block belongs to a stream the mask leaves out (nothing to compute or store)
+__device__ __forceinline__ bool block_masked_out(const FrameArgs &A, int R) {
+  if (!A.stream_mask) return false;
+  const int F = A.n_frames, total = A.n_streams * F;
+  for (int r = 0; r < R; r++) {
+    const int row = blockIdx.x * R + r;
+    if (row < total && A.stream_mask[row / F]) return false;
+  }
+  return true;
+}
+
 __global__ void __launch_bounds__(kFT) conv1_kernel(FrameArgs A) {
   constexpr int R = kRowsPerBlock;
   __shared__ __align__(16) float xt[3 * kConvIn][R];
@@ -90,6 +102,7 @@ __global__ void __launch_bounds__(kFT) conv1_kernel(FrameArgs A) {
   __shared__ uint32_t rcp[2048];
   const int F = A.n_frames, total = A.n_streams * F;
   const int tid = threadIdx.x;
+  if (block_masked_out(A, R)) return;
   for (int i = tid; i < 2048; i += kFT) rcp[i] = A.m.rcp_tab[i];
   for (int r = 0; r < R; r++) {
     const int row = min(blockIdx.x * R + r, total - 1);
@@ -120,6 +133,7 @@ __global__ void __launch_bounds__(kFT) cond_kernel(FrameArgs A) {
   __shared__ uint32_t rcp[2048];
   const int F = A.n_frames, B = A.n_streams, total = B * F;
   const int tid = threadIdx.x;
+  if (block_masked_out(A, R)) return;
   for (int i = tid; i < 2048; i += kFT) rcp[i] = A.m.rcp_tab[i];
   for (int r = 0; r < R; r++) {
     const int row = min(blockIdx.x * R + r, total - 1);
@@ -168,6 +182,9 @@ __global__ void __launch_bounds__(kFT) cond_kernel(FrameArgs A) {
 #pragma unroll
       for (int r = 0; r < R; r++) {
         if (blockIdx.x * R + r >= total) break;
+        // a stream the mask leaves out keeps the conditioning of its own last frame network (the sample segments
+        // of the PLC run on it later: lpcnet_synthesize_tail_impl reads lpcnet->gru_a_condition)
+        if (A.stream_mask && !A.stream_mask[row_s[r]]) continue;
         float *dst = isA ? A.fb.cond_a + ((size_t)row_f[r] * B + row_s[r]) * kRowsAP
                          : A.fb.cond_b + ((size_t)row_f[r] * B + row_s[r]) * kRowsB;
         dst[isA ? gru_a_col_index(colc[c]) : colc[c]] = acc[c][r];   // GRU-A conditioning in the sample kernel's gather order
@@ -183,6 +200,7 @@ __global__ void lpc_kernel(FrameArgs A) {
   const size_t nthreads = (size_t)gridDim.x * blockDim.x;
   if (idx >= B * F) return;
   const int s = idx / F, f = idx % F;
+  if (A.stream_mask && !A.stream_mask[s]) return;      // keeps its LPC (see cond_kernel)
   Scratch S{A.fb.fft_scratch + idx, nthreads};
   const float *feat = A.features + ((size_t)s * A.total_frames + A.frame0 + f) * A.feature_stride;
   float lpc[16];
@@ -229,7 +247,8 @@ __global__ void frame_finalize_kernel(FrameArgs A) {
     for (int i = 0; i < kC; i++) A.st.conv2_state[(size_t)s * 2 * kC + r * kC + i] = cv[i];
   }
   // current-frame conditioning kept in the stream state like the reference (lpcnet_private.h:43-47)
-  for (int i = 0; i < 16; i++) A.st.lpc[(size_t)s * 16 + i] = A.fb.lpc[((size_t)(F - 1) * B + s) * 16 + i];
+  if (!A.state_only)
+    for (int i = 0; i < 16; i++) A.st.lpc[(size_t)s * 16 + i] = A.fb.lpc[((size_t)(F - 1) * B + s) * 16 + i];
   A.st.frame_count[s] = frame_count_at(A.st.frame_count[s], F);
 }
 

@@ -19,6 +19,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <new>
 #include <string>
 #include <vector>
@@ -413,6 +414,8 @@ __global__ void plc_state_copy_kernel(DevState dst, DevState src, const uint8_t 
     dst.lpc[(size_t)s * 16 + t] = src.lpc[(size_t)s * 16 + t];
   }
   if (t < 4) dst.rng[(size_t)s * 4 + t] = src.rng[(size_t)s * 4 + t];
+  if (t < kMaxDelay * 16 && dst.old_lpc && src.old_lpc)       // the FEATURES_DELAY line (causal modes)
+    dst.old_lpc[(size_t)s * kMaxDelay * 16 + t] = src.old_lpc[(size_t)s * kMaxDelay * 16 + t];
   if (t == 0) {
     dst.deemph[s] = src.deemph[s];
     dst.last_exc[s] = src.last_exc[s];
@@ -531,6 +534,8 @@ __global__ void plc_finish_kernel(PlcArgs A) {
   for (int i = 0; i < kFrame; i++) io[i] = out[i];
 }
 
+#include "plc_causal.cuh"
+
 }  // namespace
 }  // namespace lpcb
 
@@ -555,6 +560,17 @@ struct LPCNetPLCBatch {
   void *d_io = nullptr; size_t d_io_bytes = 0;
   void *d_ctl = nullptr; size_t d_ctl_bytes = 0;
   long long frames_done = 0;
+  // causal / codec modes (lpcnet_plc.c:185-340): device buffers and the host's copy of the control state
+  bool causal = false;
+  int enable_blending = 1, delay = 0;
+  CausalState cst{};
+  void *causal_alloc = nullptr; size_t causal_bytes = 0;
+  struct Ctl {
+    int blend = 0, skip = 0, pcm_fill = 0, fbfill = 0;
+    int fec_keep = 0, fec_read = 0, fec_fill = 0, fec_skip = 0;
+    std::vector<float> fec;             // [fec_fill][20]
+  };
+  std::vector<Ctl> ctl;
 };
 
 namespace {
@@ -587,7 +603,7 @@ int plc_alloc(LPCNetPLCBatch *p) {
                o_so2 = take(B * kFrame * 2), o_out = take(B * kFrame * 2);
   const size_t o_c1 = take(B * 2 * kConvIn * 4), o_c2 = take(B * 2 * kC * 4), o_ga = take(B * kN * 4), o_gb = take(B * kNB * 4),
                o_ls = take(B * 16 * 4), o_lpc = take(B * 16 * 4), o_rng = take(B * 16), o_dm = take(B * 4),
-               o_le = take(B * 4), o_fc = take(B * 4);
+               o_le = take(B * 4), o_fc = take(B * 4), o_ol = take(B * kMaxDelay * 16 * 4);
   const size_t n_fft = ((2 * B + 63) / 64) * 64;   // one transform per (stream, half frame)
   const size_t o_fft = take(n_fft * 640 * 4), o_fade = take(kTOff * 4);
   CKP(cudaMalloc(&p->alloc, off));
@@ -605,7 +621,7 @@ int plc_alloc(LPCNetPLCBatch *p) {
   p->snap.conv1_state = (float *)(b + o_c1); p->snap.conv2_state = (float *)(b + o_c2); p->snap.gru_a = (float *)(b + o_ga);
   p->snap.gru_b = (float *)(b + o_gb); p->snap.last_sig = (float *)(b + o_ls); p->snap.lpc = (float *)(b + o_lpc);
   p->snap.rng = (uint32_t *)(b + o_rng); p->snap.deemph = (float *)(b + o_dm); p->snap.last_exc = (int *)(b + o_le);
-  p->snap.frame_count = (int *)(b + o_fc);
+  p->snap.frame_count = (int *)(b + o_fc); p->snap.old_lpc = (float *)(b + o_ol);
   p->fft_scratch = (float *)(b + o_fft);
   p->fade = (float *)(b + o_fade);
   // cross-fade weights, w = .5 - .5*cos(M_PI*i/TRAINING_OFFSET) as a float (lpcnet_plc.c:406), by the host's libm
@@ -733,21 +749,239 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int n_frames) {
   return 0;
 }
 
+
+// ---- causal / codec modes -----------------------------------------------------------------------------------------
+// control rows of one frame, [row][B] bytes (cU sits at mUpd's index so that the Burg kernels serve both drivers)
+enum CRow { cC = 0, cU = 1, cSB, cSnB, cNS, cFl0, cFl1, cFl2, cFl3, cA0, cA1, cA2, pmA0, pmA1, pmA2, pmC, pmSB, pmNB,
+            fA0, fA1, fA2, fSBfree, fSBforced, fC, pushSB0, pushSB1, pushEnc, kCRows };
+static_assert(cU == mUpd, "plc_burg_kernel reads the update mask at mUpd");
+
+int plc_alloc_causal(LPCNetPLCBatch *p) {
+  const size_t B = p->n_streams;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t r = off; off += (bytes + 255) & ~size_t(255); return r; };
+  const size_t o_pcm = take(B * kCpcm * 2), o_cp = take(3 * B * 512 * 4), o_fb = take(B * 80 * 4), o_fe = take(4 * B * 20 * 4);
+  CKP(cudaMalloc(&p->causal_alloc, off));
+  CKP(cudaMemset(p->causal_alloc, 0, off));
+  p->causal_bytes = off;
+  char *b = static_cast<char *>(p->causal_alloc);
+  p->cst.cpcm = (short *)(b + o_pcm); p->cst.pcopy = (float *)(b + o_cp); p->cst.fbuf = (float *)(b + o_fb);
+  p->cst.fecst = (float *)(b + o_fe);
+  return 0;
+}
+
+void plc_reset_causal_ctl(LPCNetPLCBatch *p) {
+  p->ctl.assign(p->n_streams, LPCNetPLCBatch::Ctl());
+  for (auto &c : p->ctl) c.pcm_fill = p->delay * kFrame + kTOff;      // lpcnet_plc_reset: PLC_BUF_SIZE
+}
+
+// One call of the causal / codec modes: the host walks the reference's control flow for every stream and frame
+// (no signal data is involved), the device follows the resulting rows.
+int plc_run_causal(LPCNetPLCBatch *p, const unsigned char *lost, int n_frames) {
+  const int B = p->n_streams, D = p->delay, BUF = D * kFrame + kTOff;
+  BatchView V = batch_view(p->syn);
+  cudaStream_t cs = V.stream;
+  const size_t u16_off = ((size_t)kCRows * B + 15) & ~size_t(15);          // appendOff[B], lossc[B]
+  const size_t perm_off = (u16_off + (size_t)2 * B * 2 + 15) & ~size_t(15); // 5 stream lists: A0 A1 A2 SB C
+  const size_t per_frame = (perm_off + (size_t)5 * B * 4 + 15) & ~size_t(15);
+  std::vector<uint8_t> ctl(per_frame * n_frames, 0);
+  struct Any { int fl[4], a[3], nA[3], nSB, nC, u, sb, snb, ns, nb, pushsb[2], pushenc, fec[4]; };
+  std::vector<Any> any(n_frames);
+  struct FecUse { int frame, slot, stream; float v[20]; };
+  std::vector<FecUse> fec_use;
+  auto push_code = [](LPCNetPLCBatch::Ctl &c) -> uint8_t {     // run_frame_network_deferred (lpcnet.c:122-133)
+    if (c.fbfill == 4) return (uint8_t)(4 | 8);
+    c.fbfill++;
+    return (uint8_t)c.fbfill;
+  };
+  for (int f = 0; f < n_frames; f++) {
+    uint8_t *m = ctl.data() + per_frame * f;
+    uint16_t *append_off = reinterpret_cast<uint16_t *>(m + u16_off), *lossc = append_off + B;
+    int *perm = reinterpret_cast<int *>(m + perm_off);
+    Any a{};
+    for (int s = 0; s < B; s++) {
+      LPCNetPLCBatch::Ctl &c = p->ctl[s];
+      int &lc = p->loss_count[s];
+      // get_fec_or_pred (lpcnet_plc.c:147-166): mode 4 with the vector staged for `slot`, or mode 1
+      auto fec_or_pred = [&](int slot) -> bool {
+        if (c.fec_read != c.fec_fill && c.fec_skip == 0) {
+          FecUse u; u.frame = f; u.slot = slot; u.stream = s;
+          memcpy(u.v, &c.fec[(size_t)c.fec_read * 20], sizeof(u.v));
+          fec_use.push_back(u);
+          a.fec[slot] = 1;
+          c.fec_read++;
+          c.fec_keep = std::max(0, std::max(c.fec_keep, c.fec_read - D - 1));
+          return true;
+        }
+        if (c.fec_skip > 0) c.fec_skip--;
+        return false;
+      };
+      if (lost[(size_t)s * n_frames + f]) {
+        m[cC * B + s] = 1; m[fC * B + s] = 1;
+        for (int k = 0; k < c.fbfill; k++) { m[(cFl0 + k) * B + s] = 1; a.fl[k] = 1; }
+        c.fbfill = 0;
+        const int n_iter = (c.pcm_fill + kFrame - 1) / kFrame;
+        for (int it = 0; it < n_iter; it++) {
+          const int j = 3 - n_iter + it;
+          m[(cA0 + j) * B + s] = 1; m[(fA0 + j) * B + s] = 3;
+          m[(pmA0 + j) * B + s] = fec_or_pred(j) ? 4 : 1;
+          perm[j * B + a.nA[j]++] = s;
+          a.a[j] = 1;
+          c.skip++;
+        }
+        c.pcm_fill = 0;
+        const bool used = fec_or_pred(3);
+        lc = used ? 0 : lc + 1;
+        m[pmC * B + s] = (uint8_t)((used ? 4 : 1) | 8);
+        lossc[s] = (uint16_t)(lc > 60000 ? 60000 : lc);
+        perm[4 * B + a.nC++] = s;
+        c.blend = 1;
+      } else {
+        m[cU * B + s] = 1; a.u = 1;
+        if (c.skip) {
+          if (c.blend) {
+            m[cSB * B + s] = 1; a.sb = 1;
+            if (p->enable_blending) {
+              m[pmSB * B + s] = 2; m[fSBfree * B + s] = 1; m[fSBforced * B + s] = 3;
+              for (int i = 0; i < D; i++) { m[(pushSB0 + i) * B + s] = push_code(c); a.pushsb[i] = 1; }
+              perm[3 * B + a.nSB++] = s;
+            } else {
+              c.fec_read -= D;                                    // fec_rewind (lpcnet_plc.c:168-173)
+              if (c.fec_read < c.fec_keep) c.fec_read = c.fec_keep;
+            }
+            c.pcm_fill = kTOff;
+          } else {
+            m[cSnB * B + s] = 1; a.snb = 1;
+            append_off[s] = (uint16_t)c.pcm_fill;
+            c.pcm_fill += kFrame;
+          }
+        }
+        if (!c.blend) {
+          m[pmNB * B + s] = 3; a.nb = 1;
+          if (c.fec_skip) c.fec_skip--;
+          else if (c.fec_read < c.fec_fill) c.fec_read++;
+          c.fec_keep = std::max(0, std::max(c.fec_keep, c.fec_read - D - 1));
+        }
+        if (c.skip) {
+          if (p->enable_blending) { m[pushEnc * B + s] = push_code(c); a.pushenc = 1; }
+          c.skip--;
+        } else {
+          m[cNS * B + s] = 1; a.ns = 1;
+          m[pushEnc * B + s] = push_code(c); a.pushenc = 1;
+        }
+        lc = 0;
+        c.blend = 0;
+      }
+    }
+    any[f] = a;
+  }
+  if (grow_dev(&p->d_ctl, &p->d_ctl_bytes, ctl.size())) return -1;
+  CKP(cudaMemcpyAsync(p->d_ctl, ctl.data(), ctl.size(), cudaMemcpyHostToDevice, cs));
+
+  PlcArgs A{};
+  A.st = p->st; A.w = p->w; A.lp = V.st; A.lp_copy = p->snap; A.net = V.model->d.plc; A.rcp_tab = V.model->d.rcp_tab;
+  A.tab = p->tab; A.fft_scratch = p->fft_scratch; A.fade = p->fade;
+  A.pcm_io = static_cast<short *>(p->d_io); A.n_streams = B; A.total_frames = n_frames; A.remove_dc = p->remove_dc;
+  const int tb = 128, gs = (B + tb - 1) / tb, g20 = (B * 20 + 255) / 256;
+  const CausalState C = p->cst;
+  std::vector<float> stage((size_t)4 * B * 20);
+  size_t fu = 0;
+  for (int f = 0; f < n_frames; f++) {
+    const uint8_t *M = static_cast<const uint8_t *>(p->d_ctl) + per_frame * f;
+    auto row = [&](int r) { return M + (size_t)r * B; };
+    const uint16_t *append_off = reinterpret_cast<const uint16_t *>(M + u16_off);
+    const int *perm = reinterpret_cast<const int *>(M + perm_off);
+    A.masks = M; A.lossc = append_off + B; A.frame = f;
+    const Any a = any[f];
+    if (fu < fec_use.size() && fec_use[fu].frame == f) {        // the FEC vectors this frame consumes
+      for (; fu < fec_use.size() && fec_use[fu].frame == f; fu++)
+        memcpy(&stage[((size_t)fec_use[fu].slot * B + fec_use[fu].stream) * 20], fec_use[fu].v, 80);
+      CKP(cudaMemcpyAsync(C.fecst, stage.data(), stage.size() * 4, cudaMemcpyHostToDevice, cs));
+      CKP(cudaStreamSynchronize(cs));                           // `stage` is reused by the next frame
+    }
+    // ---- concealed frames (lpcnet_plc_conceal_causal) ----
+    for (int k = 0; k < 4; k++)                                 // run_frame_network_flush
+      if (a.fl[k] && batch_frame_network_masked(p->syn, C.fbuf + k * 20, 80, row(cFl0 + k), true)) return -1;
+    for (int j = 0; j < 3; j++) {                               // catch up on the buffered samples
+      if (!a.a[j]) continue;
+      const int n = j < 2 ? kFrame : kTOff;
+      c_push_copy_kernel<<<B, 128, 0, cs>>>(A.st, C, row(cA0 + j), B, D);
+      c_pred_kernel<<<B, 256, 0, cs>>>(A, row(pmA0 + j), C.fecst + (size_t)j * B * 20);
+      c_feat_kernel<<<g20, 256, 0, cs>>>(A, row(cA0 + j));
+      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, row(cA0 + j))) return -1;
+      c_pcm_load_kernel<<<B, 64, 0, cs>>>(C, row(cA0 + j), p->w.segf, n);
+      if (batch_sample_segment(p->syn, n, row(fA0 + j), p->w.segf, p->w.sego, perm + (size_t)j * B, a.nA[j])) return -1;
+      c_pcm_shift_kernel<<<B, 128, 0, cs>>>(C, row(cA0 + j), BUF);
+    }
+    if (a.nC) {
+      c_push_copy_kernel<<<B, 128, 0, cs>>>(A.st, C, row(cC), B, D);
+      if (batch_sample_segment(p->syn, kTOff, row(fC), nullptr, p->w.sego, perm + (size_t)4 * B, a.nC)) return -1;
+      c_pred_kernel<<<B, 256, 0, cs>>>(A, row(pmC), C.fecst + (size_t)3 * B * 20);
+      c_feat_kernel<<<g20, 256, 0, cs>>>(A, row(cC));
+      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, row(cC))) return -1;
+      if (batch_sample_segment(p->syn, kTOff, row(fC), nullptr, p->w.sego2, perm + (size_t)4 * B, a.nC)) return -1;
+      c_finish_kernel<<<gs, tb, 0, cs>>>(A, row(cU), row(cC), 0);
+    }
+    // ---- received frames (lpcnet_plc_update_causal) ----
+    if (a.u) {
+      c_pre_kernel<<<gs, tb, 0, cs>>>(A, row(cU));
+      plc_burg_kernel<<<(2 * B + 63) / 64, 64, 0, cs>>>(A);
+      plc_burg_combine_kernel<<<(B * kBands + 255) / 256, 256, 0, cs>>>(A);
+    }
+    if (a.sb) {
+      if (p->enable_blending) {
+        c_set_net_kernel<<<B, 128, 0, cs>>>(A.st, C, row(cSB), B, D);
+        c_pred_kernel<<<B, 256, 0, cs>>>(A, row(pmSB), nullptr);
+        for (int i = 0; i < D; i++)
+          if (a.pushsb[i]) c_fb_push_kernel<<<g20, 256, 0, cs>>>(C, row(pushSB0 + i), A.st.features, 20, B);
+        plc_state_copy_kernel<<<B, 128, 0, cs>>>(p->snap, V.st, row(cSB), B);
+        c_feat_kernel<<<g20, 256, 0, cs>>>(A, row(cSB));
+        if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, row(cSB))) return -1;
+        if (batch_sample_segment(p->syn, kTOff, row(fSBfree), nullptr, p->w.sego, perm + (size_t)3 * B, a.nSB)) return -1;
+        c_crossfade_kernel<<<(B * kTOff + 255) / 256, 256, 0, cs>>>(A, row(cSB));
+        plc_state_copy_kernel<<<B, 128, 0, cs>>>(V.st, p->snap, row(cSB), B);
+        if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, row(cSB))) return -1;
+        if (batch_sample_segment(p->syn, kTOff, row(fSBforced), p->w.segf, p->w.sego, perm + (size_t)3 * B, a.nSB)) return -1;
+      } else {
+        if (D > 0) c_set_net_kernel<<<B, 128, 0, cs>>>(A.st, C, row(cSB), B, D - 1);
+        plc_clear_state_kernel<<<B, 128, 0, cs>>>(V.st, row(cSB), B);      // lpcnet_reset_signal (lpcnet.c:226-233)
+      }
+      c_pcm_store_kernel<<<B, 64, 0, cs>>>(C, row(cSB), nullptr, 0, p->w.in, kFrame, kFrame - kTOff, kTOff);
+    }
+    if (a.snb) c_pcm_store_kernel<<<B, 64, 0, cs>>>(C, row(cSnB), append_off, 0, p->w.in, kFrame, 0, kFrame);
+    // the analysis of every stream's frame (w.in: the received frame, or the concealment just synthesised)
+    if (feature_batch_frame_masked(p->ana, p->w.in, nullptr, p->w.encf, cs)) return -1;
+    if (a.nb) c_pred_kernel<<<B, 256, 0, cs>>>(A, row(pmNB), nullptr);
+    if (a.pushenc) c_fb_push_kernel<<<g20, 256, 0, cs>>>(C, row(pushEnc), p->w.encf, 36, B);
+    if (a.ns) {
+      c_pcm_store_kernel<<<B, 64, 0, cs>>>(C, row(cNS), nullptr, BUF, p->w.in, kFrame, 0, kFrame);
+      c_pcm_shift_kernel<<<B, 128, 0, cs>>>(C, row(cNS), BUF);
+    }
+    if (a.u) c_finish_kernel<<<gs, tb, 0, cs>>>(A, row(cU), row(cC), 1);
+    CKP(cudaGetLastError());
+    p->frames_done++;
+  }
+  return 0;
+}
+
 }  // namespace
 
 extern "C" {
 
 LPCNetPLCBatch *lpcnet_plc_batch_create(const unsigned char *blob, int len, int n_streams, int device, int options,
                                         float lpc_gamma) {
-  if ((options & 3) != 1) {
-    set_last_error("lpcnet_plc_batch_create: only LPCNET_PLC_NONCAUSAL (1), optionally | LPCNET_PLC_DC_FILTER (4), is built");
+  if ((options & 3) == 3 || (options & ~7)) {
+    set_last_error("lpcnet_plc_batch_create: options must be LPCNET_PLC_CAUSAL (0), _NONCAUSAL (1) or _CODEC (2), optionally | LPCNET_PLC_DC_FILTER (4)");
     return nullptr;
   }
   LPCNetPLCBatch *p = new (std::nothrow) LPCNetPLCBatch();
   if (!p) return nullptr;
   p->n_streams = n_streams; p->options = options; p->remove_dc = !!(options & 4);
-  // the non-causal mode needs a no-lookahead model: FEATURES_DELAY 0 (lpcnet_plc.c:357-361)
-  p->syn = lpcnet_batch_create(blob, len, n_streams, device, 0, lpc_gamma);
+  p->causal = (options & 3) != 1; p->enable_blending = (options & 3) != 2;
+  // the non-causal mode needs a no-lookahead model: FEATURES_DELAY 0 (lpcnet_plc.c:357-361); the causal and codec
+  // modes run on the model's own delay (lpcnet_b200_set_model_constants, default 2)
+  p->delay = p->causal ? default_features_delay() : 0;
+  p->syn = lpcnet_batch_create(blob, len, n_streams, device, p->delay, lpc_gamma);
   if (!p->syn) { delete p; return nullptr; }
   BatchView V = batch_view(p->syn);
   p->device = V.device;
@@ -757,7 +991,8 @@ LPCNetPLCBatch *lpcnet_plc_batch_create(const unsigned char *blob, int len, int 
     return nullptr;
   }
   p->ana = lpcnet_feature_batch_create(n_streams, p->device);
-  if (!p->ana || plc_alloc(p)) { lpcnet_plc_batch_destroy(p); return nullptr; }
+  if (!p->ana || plc_alloc(p) || (p->causal && plc_alloc_causal(p))) { lpcnet_plc_batch_destroy(p); return nullptr; }
+  if (p->causal) plc_reset_causal_ctl(p);
   p->loss_count.assign(n_streams, 0);
   p->queued.assign(n_streams, 0);
   return p;
@@ -766,7 +1001,7 @@ LPCNetPLCBatch *lpcnet_plc_batch_create(const unsigned char *blob, int len, int 
 void lpcnet_plc_batch_destroy(LPCNetPLCBatch *p) {
   if (!p) return;
   if (p->syn) lpcnet_batch_sync(p->syn);
-  cudaFree(p->alloc); cudaFree(p->tab_alloc); cudaFree(p->d_io); cudaFree(p->d_ctl);
+  cudaFree(p->alloc); cudaFree(p->tab_alloc); cudaFree(p->d_io); cudaFree(p->d_ctl); cudaFree(p->causal_alloc);
   if (p->ana) lpcnet_feature_batch_destroy(p->ana);
   if (p->syn) lpcnet_batch_destroy(p->syn);
   delete p;
@@ -791,6 +1026,40 @@ int lpcnet_plc_batch_reset(LPCNetPLCBatch *p) {
   CKP(cudaMemset(p->alloc, 0, p->state_bytes));
   p->loss_count.assign(p->n_streams, 0);
   p->queued.assign(p->n_streams, 0);
+  if (p->causal) {
+    CKP(cudaMemset(p->causal_alloc, 0, p->causal_bytes));
+    plc_reset_causal_ctl(p);
+  }
+  return 0;
+}
+
+// lpcnet_plc_fec_add / lpcnet_plc_fec_clear (lpcnet_plc.c:111-132) for one stream of the batch; features NULL means
+// "skip one".  The queue lives on the host (its positions are control state); the non-causal mode never reads it.
+int lpcnet_plc_batch_fec_add(LPCNetPLCBatch *p, int stream, const float *features) {
+  if (!p || stream < 0 || stream >= p->n_streams) return set_last_error("lpcnet_plc_batch_fec_add: bad arguments");
+  if (!p->causal) return 0;
+  LPCNetPLCBatch::Ctl &c = p->ctl[stream];
+  if (!features) { c.fec_skip++; return 0; }
+  const int kMaxFec = 100;                      // PLC_MAX_FEC
+  if (c.fec_fill == kMaxFec) {
+    if (c.fec_keep == 0) return 0;              // "FEC buffer full": the reference drops the vector too
+    c.fec.erase(c.fec.begin(), c.fec.begin() + (size_t)c.fec_keep * 20);
+    c.fec_fill -= c.fec_keep;
+    c.fec_read -= c.fec_keep;
+    c.fec_keep = 0;
+  }
+  c.fec.resize((size_t)(c.fec_fill + 1) * 20);
+  memcpy(&c.fec[(size_t)c.fec_fill * 20], features, 80);
+  c.fec_fill++;
+  return 0;
+}
+
+int lpcnet_plc_batch_fec_clear(LPCNetPLCBatch *p, int stream) {
+  if (!p || stream < 0 || stream >= p->n_streams) return set_last_error("lpcnet_plc_batch_fec_clear: bad arguments");
+  if (!p->causal) return 0;
+  LPCNetPLCBatch::Ctl &c = p->ctl[stream];
+  c.fec_keep = c.fec_read = c.fec_fill = c.fec_skip = 0;
+  c.fec.clear();
   return 0;
 }
 
@@ -802,7 +1071,7 @@ int lpcnet_plc_batch_process(LPCNetPLCBatch *p, const unsigned char *lost, short
   if (grow_dev(&p->d_io, &p->d_io_bytes, bytes)) return -1;
   cudaStream_t cs = batch_view(p->syn).stream;
   CKP(cudaMemcpyAsync(p->d_io, pcm, bytes, cudaMemcpyHostToDevice, cs));
-  if (plc_run(p, lost, n_frames)) return -1;
+  if (p->causal ? plc_run_causal(p, lost, n_frames) : plc_run(p, lost, n_frames)) return -1;
   CKP(cudaMemcpyAsync(pcm, p->d_io, bytes, cudaMemcpyDeviceToHost, cs));
   CKP(cudaStreamSynchronize(cs));
   return 0;
@@ -848,8 +1117,8 @@ int lpcnet_plc_get_size(void) { return (int)sizeof(LPCNetPLCState); }
 int lpcnet_plc_init(LPCNetPLCState *st, int options) {
   if (!st) return -1;
   st->magic = kPlcMagic; st->options = options; st->batch = nullptr;
-  if ((options & 3) != 1) {
-    set_last_error("lpcnet_plc_init: only LPCNET_PLC_NONCAUSAL (1), optionally | LPCNET_PLC_DC_FILTER (4), is built");
+  if ((options & 3) == 3) {                    // lpcnet_plc.c:64-76
+    set_last_error("lpcnet_plc_init: options must be LPCNET_PLC_CAUSAL, _NONCAUSAL or _CODEC, optionally | LPCNET_PLC_DC_FILTER");
     return -1;
   }
   return 0;
@@ -879,10 +1148,14 @@ void lpcnet_plc_reset(LPCNetPLCState *st) {
 }
 
 // The FEC queue (lpcnet_plc.c:111-132) feeds get_fec_or_pred, which only the causal entry points call
-// (lpcnet_plc.c:316, 325); the non-causal mode built here never reads it, so -- as in the reference -- features
-// added in this mode have no effect on the output.  The calls are accepted so that callers need no special case.
-void lpcnet_plc_fec_add(LPCNetPLCState *st, const float *features) { (void)st; (void)features; }
-void lpcnet_plc_fec_clear(LPCNetPLCState *st) { (void)st; }
+// (lpcnet_plc.c:316, 325); the non-causal mode never reads it, so -- as in the reference -- features added in that
+// mode have no effect on the output.
+void lpcnet_plc_fec_add(LPCNetPLCState *st, const float *features) {
+  if (st && st->magic == kPlcMagic && st->batch) lpcnet_plc_batch_fec_add(st->batch, 0, features);
+}
+void lpcnet_plc_fec_clear(LPCNetPLCState *st) {
+  if (st && st->magic == kPlcMagic && st->batch) lpcnet_plc_batch_fec_clear(st->batch, 0);
+}
 
 int lpcnet_plc_update(LPCNetPLCState *st, short *pcm) {
   if (!st || st->magic != kPlcMagic || !st->batch) return set_last_error("lpcnet_plc_update: no model loaded");

@@ -53,7 +53,7 @@ EXPORTED_SYMBOLS = [
     "lpcnet_feature_batch_encode", "lpcnet_feature_batch_compute_features",
     "lpcnet_plc_get_size", "lpcnet_plc_init", "lpcnet_plc_create", "lpcnet_plc_destroy", "lpcnet_plc_load_model",
     "lpcnet_plc_update", "lpcnet_plc_conceal", "lpcnet_plc_reset", "lpcnet_plc_fec_add", "lpcnet_plc_fec_clear",
-    "lpcnet_plc_batch_reset", "lpcnet_plc_batch_create", "lpcnet_plc_batch_destroy",
+    "lpcnet_plc_batch_reset", "lpcnet_plc_batch_fec_add", "lpcnet_plc_batch_fec_clear", "lpcnet_plc_batch_create", "lpcnet_plc_batch_destroy",
     "lpcnet_plc_batch_n_streams", "lpcnet_plc_batch_set_seed", "lpcnet_plc_batch_launch_count",
     "lpcnet_plc_batch_process", "lpcnet_plc_batch_peek", "lpcnet_plc_batch_peek_frame",
 ]
@@ -151,6 +151,8 @@ def load_library() -> C.CDLL:
     L.lpcnet_plc_fec_clear.argtypes = [vp]
     L.lpcnet_plc_fec_clear.restype = None
     L.lpcnet_plc_batch_reset.argtypes = [vp]
+    L.lpcnet_plc_batch_fec_add.argtypes = [vp, ci, vp]
+    L.lpcnet_plc_batch_fec_clear.argtypes = [vp, ci]
     L.lpcnet_plc_conceal.argtypes = [vp, vp]
     L.lpcnet_plc_batch_create.restype = vp
     L.lpcnet_plc_batch_create.argtypes = [vp, ci, ci, ci, ci, cf]
@@ -541,7 +543,9 @@ def set_codebooks(codebooks) -> None:
     _check(L.lpcnet_b200_set_codebooks(_p(cb), cb.size), "lpcnet_b200_set_codebooks")
 
 
+PLC_CAUSAL = 0
 PLC_NONCAUSAL = 1
+PLC_CODEC = 2
 PLC_DC_FILTER = 4
 
 
@@ -571,6 +575,14 @@ class PLCBatch:
     @property
     def launch_count(self):
         return int(self.L.lpcnet_plc_batch_launch_count(self.h))
+
+    def fec_add(self, stream: int, features):
+        """lpcnet_plc_fec_add for one stream (features: 20 floats, or None = skip one)."""
+        f = None if features is None else np.ascontiguousarray(features, np.float32)
+        _check(self.L.lpcnet_plc_batch_fec_add(self.h, stream, None if f is None else _p(f)), "lpcnet_plc_batch_fec_add")
+
+    def fec_clear(self, stream: int):
+        _check(self.L.lpcnet_plc_batch_fec_clear(self.h, stream), "lpcnet_plc_batch_fec_clear")
 
     def reset(self):
         """lpcnet_plc_reset for every stream (seeds return to the default "LPCNet")."""

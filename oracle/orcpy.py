@@ -255,7 +255,8 @@ def plc_pred(model: OrcModel, gru1, gru2, x):
 
 
 class OrcPLC:
-    """Non-causal packet-loss concealment of one stream (orc_plc.c); model loaded with features_delay=0."""
+    """Packet-loss concealment of one stream (orc_plc.c): options 1 | 4 need a model loaded with features_delay=0, the
+    causal (0) and codec (2) modes take any delay up to 2."""
 
     def __init__(self, model: OrcModel, options: int = 1, seed: bytes | None = None):
         self.m = model
@@ -268,7 +269,7 @@ class OrcPLC:
         L.orc_plc_conceal.argtypes = [C.c_void_p, C.c_void_p]
         self.h = L.orc_plc_new(model.h, options)
         if not self.h:
-            raise RuntimeError("orc_plc_new: needs plc_* arrays, features_delay 0 and the non-causal mode")
+            raise RuntimeError("orc_plc_new: needs plc_* arrays, a mode in {0, 1, 2}, and features_delay 0 for the non-causal mode")
         if seed is not None:
             L.orc_plc_seed(self.h, seed, len(seed))
 

@@ -137,6 +137,33 @@ def analysis(R):
     np.savez_compressed(os.path.join(OUT, "analysis.npz"), pcm=np.stack(sig), features=np.stack(feats))
 
 
+def plc_causal_fec(F, s):
+    """FEC features handed to lpcnet_plc_fec_add before frame f (None = skip one); none for stream 0."""
+    if s == 0:
+        return {}
+    rng = np.random.default_rng(50 + s)
+    return {f: [None if rng.random() < 0.2 else (rng.standard_normal(20) * 0.5).astype(np.float32)
+                for _ in range(int(rng.integers(0, 3)))] for f in range(F)}
+
+
+def plc_causal(R):
+    """lpcnet_plc_update / lpcnet_plc_conceal of the reference's FEATURES_DELAY 2 build (libref_d2.so) in the causal
+    and codec modes, without and with the DC filter: 3 streams x 40 frames under Gilbert loss, streams 1 and 2 with FEC
+    features in the queue."""
+    b = plc_model_blob()
+    d = {"blob_sha256": np.frombuffer(hashlib.sha256(b).digest(), np.uint8)}
+    F = 40
+    for opt in (0, 4, 2, 6):
+        for s in range(3):
+            x = blob.synthetic_pcm(F, s)
+            if opt & 4:
+                x = np.clip(x.astype(np.int32) + 700, -32768, 32767).astype(np.int16)
+            lost = blob.synthetic_loss_pattern(F, s, 0.6 + 0.25 * (s == 2), 0.15)
+            d[f"in_{opt}_{s}"], d[f"lost_{opt}_{s}"] = x, lost
+            d[f"out_{opt}_{s}"] = refpy.RefPLC(R, b, opt, blob.stream_seed(s)).run(x, lost, plc_causal_fec(F, s))
+    np.savez_compressed(os.path.join(OUT, "plc_causal.npz"), **d)
+
+
 def encode_signals():
     """The inputs of encode.npz: 7 signals x 24 packets (tests/test_encode_oracle.py rebuilds and compares them)."""
     n = 24 * 4
@@ -196,8 +223,8 @@ def plc(R):
 
 if __name__ == "__main__":
     R = refpy.RefLib(2)
-    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc", "encode"]
+    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc", "encode", "plc_causal"]
     for name in which:
-        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc, "encode": encode}[name](R)
+        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc, "encode": encode, "plc_causal": plc_causal}[name](R)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))

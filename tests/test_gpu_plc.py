@@ -144,8 +144,71 @@ def test_full_size_config4_compaction_is_invisible(eng, plc_blob, plc_model):
         assert first_diff(got[s], want) is None, (s, first_diff(got[s], want))
 
 
+def run_with_fec(pb, pcm, lost, fec):
+    """frame by frame, handing each stream's FEC vectors to the queue before the frame they precede"""
+    B, F = lost.shape
+    out = []
+    for f in range(F):
+        for s in range(B):
+            for v in fec[s].get(f, []):
+                pb.fec_add(s, v)
+        out.append(pb.process(pcm[:, f * 160:(f + 1) * 160], lost[:, f:f + 1]))
+    return np.concatenate(out, axis=1)
+
+
+@pytest.mark.parametrize("opt", [0, 4, 2, 6])
+def test_causal_and_codec_modes_golden_vectors(eng, plc_blob, opt):
+    """lpcnet_plc_update_causal / _conceal_causal with the FEC queue (FEATURES_DELAY 2 build of the reference)"""
+    g = np.load(os.path.join(HERE, "golden", "plc_causal.npz"))
+    assert hashlib.sha256(plc_blob).digest() == g["blob_sha256"].tobytes()
+    pcm = np.stack([g[f"in_{opt}_{s}"] for s in range(3)])
+    lost = np.stack([g[f"lost_{opt}_{s}"] for s in range(3)])
+    want = np.stack([g[f"out_{opt}_{s}"] for s in range(3)])
+    pb = eng.PLCBatch(plc_blob, 3, opt)
+    for s in range(3):
+        pb.set_seed(s, blob.stream_seed(s))
+    got = run_with_fec(pb, pcm, lost, [blob.synthetic_fec(lost.shape[1], s) for s in range(3)])
+    pb.close()
+    assert first_diff(got, want) is None, ("first difference (stream, sample)", first_diff(got, want))
+
+
+def test_causal_mode_many_streams_in_one_call(eng, plc_blob):
+    """64 streams x 24 frames in a single batched call (no FEC), the causal mode with the DC filter: sampled streams
+    against the oracle, batch invariance for the rest; and the single-stream entry points with FEC."""
+    B, F, opt = 64, 24, 4
+    model = orcpy.OrcModel(orcpy.OrcLib(), plc_blob, 2, 1.0, None)
+    pcm = np.stack([np.clip(blob.synthetic_pcm(F, 200 + s).astype(np.int32) + 250 * (s % 4), -32768, 32767).astype(np.int16)
+                    for s in range(B)])
+    lost = np.stack([blob.synthetic_loss_pattern(F, s, 0.55 + 0.3 * (s % 3 == 0), 0.15) for s in range(B)])
+    pb = eng.PLCBatch(plc_blob, B, opt)
+    for s in range(B):
+        pb.set_seed(s, blob.stream_seed(s))
+    got = pb.process(pcm, lost)
+    pb.close()
+    for s in (0, 3, 31, 63):
+        want = orcpy.OrcPLC(model, opt, blob.stream_seed(s)).run(pcm[s], lost[s])
+        assert first_diff(got[s], want) is None, (s, first_diff(got[s], want))
+    pick = [5, 40]
+    small = eng.PLCBatch(plc_blob, len(pick), opt)
+    for i, s in enumerate(pick):
+        small.set_seed(i, blob.stream_seed(s))
+    assert first_diff(small.process(pcm[pick], lost[pick]), got[pick]) is None
+    small.close()
+    # lpcnet_plc_create(LPCNET_PLC_CODEC) + fec_add / update / conceal, one stream
+    s, fec = 2, blob.synthetic_fec(F, 2)
+    plc = eng.PLC(plc_blob, 2)
+    out = []
+    for f in range(F):
+        for v in fec.get(f, []):
+            plc.fec_add(v)
+        out.append(plc.conceal() if lost[s, f] else plc.update(pcm[s, f * 160:(f + 1) * 160]))
+    plc.close()
+    want = orcpy.OrcPLC(model, 2, b"LPCNet").run(pcm[s], lost[s], fec)
+    assert first_diff(np.concatenate(out), want) is None
+
+
 def test_unsupported_modes_and_models_are_errors(eng, plc_blob, model_blob):
     with pytest.raises(engine.LPCNetError):
-        eng.PLCBatch(plc_blob, 2, 0)            # causal mode is not built
+        eng.PLCBatch(plc_blob, 2, 3)            # 3 is not a mode (lpcnet_plc.c:64-76)
     with pytest.raises(engine.LPCNetError):
         eng.PLCBatch(model_blob, 2, 1)          # no plc_* arrays in the blob
