@@ -236,7 +236,7 @@ LPCNET_B200_EXPORT int lpcnet_feature_batch_compute_features(LPCNetFeatureBatch 
                                                              float *features);
 
 /* ------------------------------------------------------------------------------------
- * 4. Packet-loss concealment, non-causal mode (BASELINE config 4)
+ * 4. Packet-loss concealment: non-causal, causal and codec modes (BASELINE config 4)
  * ------------------------------------------------------------------------------------ */
 /* The reference's PLC entry points (include/lpcnet.h:190-215, src/lpcnet_plc.c:44-109, 493-503) for
  * options = LPCNET_PLC_NONCAUSAL (1), optionally | LPCNET_PLC_DC_FILTER (4); other modes return -1.  The blob

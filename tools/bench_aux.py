@@ -28,21 +28,21 @@ def timed(fn, reps):
     return float(np.median(best)), float(min(best))
 
 
-def bench_plc(B, F, reps):
+def bench_plc(B, F, reps, options=5):
     A = blob.random_model()
     A.update(blob.random_plc_model())
     bl = blob.write_blob(A)
     base = [blob.synthetic_pcm(F, 100 + s) for s in range(64)]
     pcm = np.stack([base[s % 64] for s in range(B)])
     lost = np.stack([blob.synthetic_loss_pattern(F, 7 + s, 0.6, 0.1) for s in range(B)])
-    pb = engine.PLCBatch(bl, B, 5)
+    pb = engine.PLCBatch(bl, B, options)
     for s in range(B):
         pb.set_seed(s, blob.stream_seed(s))
     n0 = pb.launch_count
     med, mn = timed(lambda: pb.process(pcm, lost), reps)
     launches = (pb.launch_count - n0) // (reps + 1)
     pb.close()
-    return {"workload": "plc noncausal_dc", "streams": B, "frames": F, "loss_rate": float(lost.mean()),
+    return {"workload": {5: "plc noncausal_dc", 4: "plc causal_dc", 6: "plc codec_dc"}.get(options, f"plc options {options}"), "streams": B, "frames": F, "loss_rate": float(lost.mean()),
             "samples_per_s": B * F * 160 / med, "x_realtime": B * F * 160 / med / 16000, "ms_per_frame": med / F * 1e3,
             "best_s": mn, "median_s": med, "launches_per_call": int(launches)}
 
@@ -98,6 +98,8 @@ def main():
     for w in a.what:
         if w == "plc":
             r = bench_plc(a.streams, a.frames, a.reps)
+        elif w == "plc_causal":
+            r = bench_plc(a.streams, a.frames, a.reps, 4)
         elif w == "features":
             r = bench_features(a.streams, a.frames, a.reps)
         elif w == "decode":
