@@ -238,11 +238,12 @@ LPCNET_B200_EXPORT int lpcnet_feature_batch_compute_features(LPCNetFeatureBatch 
 /* ------------------------------------------------------------------------------------
  * 4. Packet-loss concealment: non-causal, causal and codec modes (BASELINE config 4)
  * ------------------------------------------------------------------------------------ */
-/* The reference's PLC entry points (include/lpcnet.h:190-215, src/lpcnet_plc.c:44-109, 493-503) for
- * options = LPCNET_PLC_NONCAUSAL (1), optionally | LPCNET_PLC_DC_FILTER (4); other modes return -1.  The blob
- * must carry the plc_* arrays next to the LPCNet model, and the model is run with FEATURES_DELAY 0 as
- * src/lpcnet_plc.c:357-361 demands.  pcm: 160 samples in (update) / out (both); the output lags the input by 80
- * samples.  The FEC queue (lpcnet_plc_fec_add) is not built. */
+/* The reference's PLC entry points (include/lpcnet.h:190-215, src/lpcnet_plc.c:44-109, 493-503).  options =
+ * LPCNET_PLC_CAUSAL (0), LPCNET_PLC_NONCAUSAL (1) or LPCNET_PLC_CODEC (2), optionally | LPCNET_PLC_DC_FILTER (4); 3
+ * returns -1.  The blob must carry the plc_* arrays next to the LPCNet model.  The non-causal mode runs the model with
+ * FEATURES_DELAY 0, as src/lpcnet_plc.c:357-361 demands, and its output lags the input by 80 samples; the causal and
+ * codec modes run it with the delay of lpcnet_b200_set_model_constants (default 2).  pcm: 160 samples in (update) /
+ * out (both). */
 typedef struct LPCNetPLCState LPCNetPLCState;
 LPCNET_B200_EXPORT int lpcnet_plc_get_size(void);
 LPCNET_B200_EXPORT int lpcnet_plc_init(LPCNetPLCState *st, int options);
