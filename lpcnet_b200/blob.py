@@ -292,3 +292,47 @@ def synthetic_fec(n_frames: int, stream: int) -> dict:
     rng = np.random.default_rng(50 + stream)
     return {f: [None if rng.random() < 0.2 else (rng.standard_normal(20) * 0.5).astype(np.float32)
                 for _ in range(int(rng.integers(0, 3)))] for f in range(n_frames)}
+
+
+def random_dred_decoder_model(seed: int = 8765, cond: int = 256, latent: int = 80, state: int = 24, sigma: float = 0.1,
+                              qmax_in: int = 10, qmax_rec: int = 8) -> "OrderedDict[str, np.ndarray]":
+    """Random-init RDOVAE decoder (DRED) in the reference's array layout (torch/rdovae/export_rdovae_weights.py:178-222
+    over CoreDecoder, torch/rdovae/rdovae/rdovae.py:342-413; consumed by src/dred_rdovae_dec.c): state1..3 state -> cond
+    (tanh), dec_dense1 latent -> cond, three int8 GRUs cond -> cond (dec_dense2/4/6) with dense layers between them
+    (dec_dense3/5/7/8), dec_final 8*cond -> 4*20 (linear).  Append to a model dict before write_blob: the reference's
+    write_lpcnet_weights.c puts every model into one blob too."""
+    rng = np.random.default_rng(seed)
+    f32 = np.float32
+    A: "OrderedDict[str, np.ndarray]" = OrderedDict()
+
+    def normal(shape, s=sigma):
+        return (rng.standard_normal(shape) * s).astype(f32)
+
+    for k in (1, 2, 3):
+        A[f"state{k}_weights"] = normal((state, cond), 0.3)
+        A[f"state{k}_bias"] = normal((cond,))
+    A["dec_dense1_weights"] = normal((latent, cond))
+    A["dec_dense1_bias"] = normal((cond,))
+    for name in ("dec_dense3", "dec_dense5", "dec_dense7", "dec_dense8"):
+        A[f"{name}_weights"] = normal((cond, cond), 0.08)
+        A[f"{name}_bias"] = normal((cond,))
+    A["dec_final_weights"] = normal((8 * cond, 80), 0.03)
+    A["dec_final_bias"] = normal((80,), 0.2)
+    for name in ("dec_dense2", "dec_dense4", "dec_dense6"):
+        q = rng.integers(-qmax_in, qmax_in + 1, size=(cond, 3 * cond)).astype(np.int32)
+        mask = rng.random((cond // 4, 3 * cond // 8)) < 0.5            # input_sparse: half of the 8x4 blocks present
+        q = q * np.repeat(np.repeat(mask, 4, axis=0), 8, axis=1)
+        wq, idx = block_sparse_encode(q, mask)
+        A[f"{name}_weights"] = wq
+        A[f"{name}_weights_idx"] = idx
+        q2 = rng.integers(-qmax_rec, qmax_rec + 1, size=(cond, 3 * cond)).astype(np.int32)
+        A[f"{name}_recurrent_weights"] = dotp_layout(q2)
+        bias = normal((2, 3 * cond))
+        A[f"{name}_bias"] = bias.reshape(-1)
+        sub = bias.astype(np.float64).copy()
+        sub[0] -= q.sum(axis=0) * (1.0 / 128.0)
+        sub[1] -= q2.sum(axis=0) * (1.0 / 128.0)
+        A[f"{name}_subias"] = sub.astype(f32).reshape(-1)
+    for k in list(A.keys()):
+        A[k] = np.ascontiguousarray(A[k]).reshape(-1)
+    return A

@@ -112,6 +112,9 @@ const float *orc_half_window(void);   /* [160] */
 /* burg_cepstral_analysis (src/freq.c:188-199): 160 samples -> 2 x 18 Burg cepstra (mean, difference) */
 void orc_burg_cepstral_analysis(float *ceps /*[36]*/, const float *x /*[160]*/);
 
+/* RDOVAE decoder of DRED (src/dred_rdovae.c:37-51): features [nb_latents][80], state [24], latents [nb_latents][80] */
+int orc_dred_decode_all(const OrcModel *m, float *features, const float *state, const float *latents, int nb_latents);
+
 /* Packet-loss concealment, non-causal mode (src/lpcnet_plc.c:349-491); the model must carry the plc_* arrays and
  * be loaded with features_delay 0.  options: 1 (LPCNET_PLC_NONCAUSAL) | 4 (LPCNET_PLC_DC_FILTER). */
 typedef struct OrcPLC OrcPLC;

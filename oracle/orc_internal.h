@@ -31,6 +31,10 @@ struct OrcModel {
   int has_plc;
   OrcDense plc_dense1, plc_out;
   OrcGRU plc_gru1, plc_gru2;
+  /* RDOVAE decoder of DRED (dred_rdovae_dec_data.c stand-in), present when the blob carries the dec_* arrays */
+  int has_dred;
+  OrcDense dred_state[3], dred_dense[5], dred_final;   /* state1..3; dec_dense1,3,5,7,8; dec_final */
+  OrcGRU dred_gru[3];                                   /* dec_dense2,4,6 */
 };
 
 /* LPCNetEncState (lpcnet_private.h:55-75), the fields single-frame analysis uses */

@@ -2,6 +2,7 @@
  * Follows src/parse_lpcnet_weights.c:36-221 (record validation, lookup by name and
  * exact size, idx stream validation) and the init call list of the generated
  * nnet_data.c (training_tf2/dump_lpcnet.py). */
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 #include <math.h>
@@ -133,6 +134,34 @@ OrcModel *orc_model_load(const unsigned char *blob, int len, int features_delay,
     }
     if (pbad) { orc_model_free(m); return NULL; }
     m->has_plc = 1;
+  }
+  /* init_rdovaedec (dred_rdovae_dec_data.c stand-in, oracle/gen/dred_rdovae_dec_data.c): optional */
+  if (find(arr, n, "dec_dense1_bias", 256 * 4)) {
+    static const char *dn[5] = {"dec_dense1", "dec_dense3", "dec_dense5", "dec_dense7", "dec_dense8"};
+    static const char *gn[3] = {"dec_dense2", "dec_dense4", "dec_dense6"};
+    char a[64], b[64];
+    int k, dbad = 0;
+    for (k = 0; k < 3; k++) {
+      snprintf(a, sizeof(a), "state%d_bias", k + 1); snprintf(b, sizeof(b), "state%d_weights", k + 1);
+      dbad |= dense(&m->dred_state[k], arr, n, a, b, 24, 256, ORC_TANH);
+    }
+    for (k = 0; k < 5; k++) {
+      snprintf(a, sizeof(a), "%s_bias", dn[k]); snprintf(b, sizeof(b), "%s_weights", dn[k]);
+      dbad |= dense(&m->dred_dense[k], arr, n, a, b, k == 0 ? 80 : 256, 256, ORC_TANH);
+    }
+    dbad |= dense(&m->dred_final, arr, n, "dec_final_bias", "dec_final_weights", 2048, 80, ORC_LINEAR);
+    for (k = 0; k < 3; k++) {
+      OrcGRU *g = &m->dred_gru[k];
+      snprintf(a, sizeof(a), "%s_bias", gn[k]); g->bias = find(arr, n, a, 6 * 256 * 4);
+      snprintf(a, sizeof(a), "%s_subias", gn[k]); g->subias = find(arr, n, a, 6 * 256 * 4);
+      snprintf(a, sizeof(a), "%s_weights_idx", gn[k]); g->idx_in = find_idx(arr, n, a, 256, 3 * 256, &g->nblocks);
+      snprintf(a, sizeof(a), "%s_weights", gn[k]); g->w_in = find(arr, n, a, 32 * g->nblocks);
+      snprintf(a, sizeof(a), "%s_recurrent_weights", gn[k]); g->w_rec = find(arr, n, a, 3 * 256 * 256);
+      g->nin = 256; g->n = 256;
+      dbad |= !g->bias || !g->subias || !g->idx_in || !g->w_in || !g->w_rec;
+    }
+    if (dbad) { orc_model_free(m); return NULL; }
+    m->has_dred = 1;
   }
   /* sampling_logit_table (lpcnet.c:188-191): float prob, double log */
   for (i = 0; i < 256; i++) {

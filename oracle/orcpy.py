@@ -302,3 +302,15 @@ class OrcPLC:
             else:
                 L.orc_plc_update(self.h, _p(fr))
         return out
+
+
+def dred_decode_all(model: "OrcModel", state, latents):
+    """DRED_rdovae_decode_all (orc_dred.c): state [24], latents [n][80] -> features [n][80]"""
+    z = np.ascontiguousarray(latents, np.float32)
+    st = np.ascontiguousarray(state, np.float32)
+    out = np.zeros((z.shape[0], 80), np.float32)
+    L = model.L.lib
+    L.orc_dred_decode_all.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    if L.orc_dred_decode_all(model.h, _p(out), _p(st), _p(z), z.shape[0]) != 0:
+        raise RuntimeError("orc_dred_decode_all: the model has no RDOVAE decoder arrays")
+    return out

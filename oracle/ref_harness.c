@@ -304,3 +304,24 @@ void ref_plc_pred(void *hp, float *gru1, float *gru2, float *out, const float *i
   _lpcnet_compute_dense(&st->model.plc_out, out, gru2);
   out[19] = MIN16(.5f, out[19] + .1f);
 }
+
+/* ---- DRED: the RDOVAE decoder (dred_rdovae_dec.c) on a model parsed from the blob ------------------------------- */
+#include "dred_rdovae_dec.h"
+
+/* DRED_rdovae_decode_all (dred_rdovae.c:37-51) over the reference's dred_rdovae_dec_init_states /
+ * dred_rdovae_decode_qframe: features [nb_latents][4*20]; returns 0, or -1 if the blob lacks the decoder arrays */
+int ref_dred_decode_all(const unsigned char *blob, int len, float *features, const float *state, const float *latents,
+                        int nb_latents) {
+  WeightArray *list;
+  RDOVAEDec model;
+  RDOVAEDecState dec;
+  int i;
+  parse_weights(&list, blob, len);
+  if (!list || init_rdovaedec(&model, list) != 0) { free(list); return -1; }
+  memset(&dec, 0, sizeof(dec));
+  dred_rdovae_dec_init_states(&dec, &model, state);
+  for (i = 0; i < 2 * nb_latents; i += 2)
+    dred_rdovae_decode_qframe(&dec, &model, &features[2 * i * DRED_NUM_FEATURES], &latents[(i / 2) * DRED_LATENT_DIM]);
+  free(list);
+  return 0;
+}

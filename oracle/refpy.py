@@ -278,3 +278,15 @@ class RefPLC:
         out = np.zeros(20, np.float32)
         self.L.lib.ref_plc_pred(self.h, _p(gru1), _p(gru2), _p(out), _p(np.ascontiguousarray(x, np.float32)))
         return out
+
+
+def ref_dred_decode_all(lib: RefLib, blob: bytes, state, latents):
+    """the reference's dred_rdovae_dec_init_states + dred_rdovae_decode_qframe (src/dred_rdovae_dec.c) over a model
+    parsed from `blob`: state [24], latents [n][80] -> features [n][80]"""
+    z = np.ascontiguousarray(latents, np.float32)
+    st = np.ascontiguousarray(state, np.float32)
+    out = np.zeros((z.shape[0], 80), np.float32)
+    lib.lib.ref_dred_decode_all.argtypes = [C.c_char_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    if lib.lib.ref_dred_decode_all(blob, len(blob), _p(out), _p(st), _p(z), z.shape[0]) != 0:
+        raise RuntimeError("reference rejected the RDOVAE decoder arrays")
+    return out
