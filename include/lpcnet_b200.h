@@ -282,6 +282,25 @@ LPCNET_B200_EXPORT int lpcnet_plc_batch_peek(LPCNetPLCBatch *b, int stream, floa
 /* The last processed frame's burg_cepstral_analysis output and analysis features of one stream (good frames). */
 LPCNET_B200_EXPORT int lpcnet_plc_batch_peek_frame(LPCNetPLCBatch *b, int stream, float *burg36, float *enc36);
 
+/* ------------------------------------------------------------------------------------
+ * 5. DRED: the RDOVAE decoder that turns received latent vectors into FEC features
+ * ------------------------------------------------------------------------------------ */
+/* DRED_rdovae_decode_all (include/dred_rdovae.h:40, src/dred_rdovae.c:37-51 over src/dred_rdovae_dec.c:37-98): the
+ * 24-value initial state and nb_latents latent vectors of 80 floats -> nb_latents x 4 feature vectors of 20 floats
+ * (each group of four in the reference's reverse order), ready for lpcnet_plc_fec_add.  The reference's RDOVAEDec model
+ * struct is replaced by a handle created from a weights blob that carries the decoder arrays (dec_dense1..8, dec_final,
+ * state1..3 in the layout of torch/rdovae/export_rdovae_weights.py; write_lpcnet_weights.c writes them into the same
+ * blob as the LPCNet model).  Sizes are those of the reference's default export: cond_size 256, latent 80, state 24. */
+typedef struct LPCNetDredDecoder LPCNetDredDecoder;
+LPCNET_B200_EXPORT LPCNetDredDecoder *lpcnet_dred_decoder_create(const unsigned char *blob, int len, int device);
+LPCNET_B200_EXPORT void lpcnet_dred_decoder_destroy(LPCNetDredDecoder *d);
+LPCNET_B200_EXPORT long long lpcnet_dred_decoder_launch_count(const LPCNetDredDecoder *d);
+LPCNET_B200_EXPORT int lpcnet_dred_decode_all(LPCNetDredDecoder *d, float *features, const float *state,
+                                              const float *latents, int nb_latents);
+/* n_streams independent packets per call: states [n][24], latents [n][nb_latents][80] -> features [n][nb_latents][80] */
+LPCNET_B200_EXPORT int lpcnet_dred_decode_batch(LPCNetDredDecoder *d, int n_streams, float *features, const float *states,
+                                                const float *latents, int nb_latents);
+
 /* The reference's tanh/sigmoid multiply by `rcpps` (src/vec_avx.h:408,437), a CPU
  * hardware estimate that is exactly a 2048-entry table over the top 11 mantissa bits.
  * Default: the Intel table model (oracle/orc_prim.c).  A process-wide override takes the

@@ -85,6 +85,16 @@ struct DevPlc {
   const float *g1_subias, *g2_subias;   // [2][768]
 };
 
+// RDOVAE decoder of DRED (src/dred_rdovae_dec.c): cond_size = cond_size2 = 256, i.e. the PLC predictor's GRU geometry
+constexpr int kDredLatent = 80, kDredState = 24, kDredOut = 80;
+struct DevDred {
+  const float *state_w[3], *state_b[3];     // state1..3: [24][256], [256]
+  const float *dense_w[5], *dense_b[5];     // dec_dense1 [80][256]; dec_dense3/5/7/8 [256][256]
+  const float *final_w, *final_b;           // dec_final [2048][80], [80]
+  const uint32_t *g_in[3], *g_rec[3];       // dec_dense2/4/6: [256/4][768] words each
+  const float *g_subias[3];                 // [2][768]
+};
+
 // Device-side model: pointers into one device allocation.
 struct DevModel {
   // 100 Hz frame network (fp32, blob layout)
@@ -115,6 +125,7 @@ struct DevModel {
   int features_delay;
   float lpc_gamma;
   DevPlc plc;                               // valid when Model::has_plc
+  DevDred dred;                             // valid when Model::has_dred
 };
 
 // Per-stream mutable state, structure-of-arrays in HBM ([field][stream] where noted).
@@ -142,6 +153,7 @@ struct Model {
   int nblocks_a = 0, nblocks_b = 0;
   bool has_codebooks = false;
   bool has_plc = false;   // the blob carried the plc_* arrays
+  bool has_dred = false;  // ... the RDOVAE decoder arrays (dec_*, state1..3)
 };
 
 // Loads and validates a DNNw blob (src/parse_lpcnet_weights.c) and builds the device model.

@@ -447,6 +447,45 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
       m.has_codebooks = true;
     }
   }
+  // [input/4][row] words from the block-sparse stream (absent blocks = 0) or the dense 8x4 layout
+  auto retile = [&](const uint32_t **dst, const char *wname, const char *iname, int cols) -> bool {
+    auto wi = A.find(wname);
+    if (wi == A.end()) { if (err.empty()) err = std::string("missing array ") + wname; return false; }
+    const int8_t *w = reinterpret_cast<const int8_t *>(wi->second.data);
+    const int wb = wi->second.size;
+    for (int i = 0; i + 1 < wb; i += 2)
+      if (255 * (abs((int)w[i]) + abs((int)w[i + 1])) > 32767) {
+        err = std::string(wname) + ": int8 pair would saturate vpmaddubsw; not representable bit-exactly";
+        return false;
+      }
+    std::vector<uint32_t> t((size_t)(cols / 4) * kPlcRows, 0u);
+    auto place = [&](int grp, int pos, const int8_t *blk) {
+      for (int r = 0; r < 8; r++) memcpy(&t[(size_t)(pos / 4) * kPlcRows + grp * 8 + r], blk + 4 * r, 4);
+    };
+    if (iname) {
+      auto ii = A.find(iname);
+      if (ii == A.end() || (ii->second.size & 3)) { if (err.empty()) err = std::string("missing array ") + iname; return false; }
+      const int32_t *p = reinterpret_cast<const int32_t *>(ii->second.data);
+      int remain = ii->second.size / 4, grp = 0, total = 0;
+      while (remain > 0) {
+        const int nb = *p++;
+        if (nb < 0 || remain < nb + 1 || grp >= kPlcRows / 8 || (total + nb) * 32 > wb) { err = std::string(iname) + ": bad block index stream"; return false; }
+        for (int k = 0; k < nb; k++) {
+          const int pos = *p++;
+          if (pos < 0 || (pos & 3) || pos + 3 >= cols) { err = std::string(iname) + ": bad block position"; return false; }
+          place(grp, pos, w + (size_t)(total + k) * 32);
+        }
+        remain -= nb + 1; total += nb; grp++;
+      }
+      if (grp != kPlcRows / 8 || total * 32 != wb) { err = std::string(iname) + ": block index stream does not match the weights"; return false; }
+    } else {
+      if (wb != kPlcRows * cols) { err = std::string("wrong size for array ") + wname; return false; }
+      for (int grp = 0; grp < kPlcRows / 8; grp++)
+        for (int pos = 0; pos < cols; pos += 4) place(grp, pos, w + ((size_t)grp * (cols / 4) + pos / 4) * 32);
+    }
+    put(reinterpret_cast<const void **>(dst), t.data(), t.size() * 4);
+    return true;
+  };
   // optional PLC predictor arrays (init_plc_model, training_tf2/dump_plc.py:319-330): all or none
   if (A.find("plc_dense1_bias") != A.end()) {
     DevPlc &P = d.plc;
@@ -459,51 +498,39 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
     pk &= put_f(&P.g2_subias, "plc_gru2_subias", 2 * kPlcRows);
     pk &= need("plc_gru1_bias", 2 * kPlcRows * 4) != nullptr;
     pk &= need("plc_gru2_bias", 2 * kPlcRows * 4) != nullptr;
-    // [input/4][row] words from the block-sparse stream (absent blocks = 0) or the dense 8x4 layout
-    auto retile = [&](const uint32_t **dst, const char *wname, const char *iname, int cols) -> bool {
-      auto wi = A.find(wname);
-      if (wi == A.end()) { if (err.empty()) err = std::string("missing array ") + wname; return false; }
-      const int8_t *w = reinterpret_cast<const int8_t *>(wi->second.data);
-      const int wb = wi->second.size;
-      for (int i = 0; i + 1 < wb; i += 2)
-        if (255 * (abs((int)w[i]) + abs((int)w[i + 1])) > 32767) {
-          err = std::string(wname) + ": int8 pair would saturate vpmaddubsw; not representable bit-exactly";
-          return false;
-        }
-      std::vector<uint32_t> t((size_t)(cols / 4) * kPlcRows, 0u);
-      auto place = [&](int grp, int pos, const int8_t *blk) {
-        for (int r = 0; r < 8; r++) memcpy(&t[(size_t)(pos / 4) * kPlcRows + grp * 8 + r], blk + 4 * r, 4);
-      };
-      if (iname) {
-        auto ii = A.find(iname);
-        if (ii == A.end() || (ii->second.size & 3)) { if (err.empty()) err = std::string("missing array ") + iname; return false; }
-        const int32_t *p = reinterpret_cast<const int32_t *>(ii->second.data);
-        int remain = ii->second.size / 4, grp = 0, total = 0;
-        while (remain > 0) {
-          const int nb = *p++;
-          if (nb < 0 || remain < nb + 1 || grp >= kPlcRows / 8 || (total + nb) * 32 > wb) { err = std::string(iname) + ": bad block index stream"; return false; }
-          for (int k = 0; k < nb; k++) {
-            const int pos = *p++;
-            if (pos < 0 || (pos & 3) || pos + 3 >= cols) { err = std::string(iname) + ": bad block position"; return false; }
-            place(grp, pos, w + (size_t)(total + k) * 32);
-          }
-          remain -= nb + 1; total += nb; grp++;
-        }
-        if (grp != kPlcRows / 8 || total * 32 != wb) { err = std::string(iname) + ": block index stream does not match the weights"; return false; }
-      } else {
-        if (wb != kPlcRows * cols) { err = std::string("wrong size for array ") + wname; return false; }
-        for (int grp = 0; grp < kPlcRows / 8; grp++)
-          for (int pos = 0; pos < cols; pos += 4) place(grp, pos, w + ((size_t)grp * (cols / 4) + pos / 4) * 32);
-      }
-      put(reinterpret_cast<const void **>(dst), t.data(), t.size() * 4);
-      return true;
-    };
     pk = pk && retile(&P.g1_in, "plc_gru1_weights", "plc_gru1_weights_idx", kPlcCond);
     pk = pk && retile(&P.g1_rec, "plc_gru1_recurrent_weights", nullptr, kPlcUnits);
     pk = pk && retile(&P.g2_in, "plc_gru2_weights", "plc_gru2_weights_idx", kPlcUnits);
     pk = pk && retile(&P.g2_rec, "plc_gru2_recurrent_weights", nullptr, kPlcUnits);
     if (!pk) return false;
     m.has_plc = true;
+  }
+  // optional RDOVAE decoder of DRED (init_rdovaedec, torch/rdovae/export_rdovae_weights.py:178-222): all or none
+  if (A.find("dec_dense1_bias") != A.end()) {
+    DevDred &R = d.dred;
+    bool pk = true;
+    static const char *dn[5] = {"dec_dense1", "dec_dense3", "dec_dense5", "dec_dense7", "dec_dense8"};
+    static const char *gn[3] = {"dec_dense2", "dec_dense4", "dec_dense6"};
+    for (int k = 0; k < 3; k++) {
+      const std::string n = "state" + std::to_string(k + 1);
+      pk &= put_f(&R.state_b[k], (n + "_bias").c_str(), kPlcUnits);
+      pk &= put_f(&R.state_w[k], (n + "_weights").c_str(), kDredState * kPlcUnits);
+    }
+    for (int k = 0; k < 5; k++) {
+      pk &= put_f(&R.dense_b[k], (std::string(dn[k]) + "_bias").c_str(), kPlcUnits);
+      pk &= put_f(&R.dense_w[k], (std::string(dn[k]) + "_weights").c_str(), (k == 0 ? kDredLatent : kPlcUnits) * kPlcUnits);
+    }
+    pk &= put_f(&R.final_b, "dec_final_bias", kDredOut);
+    pk &= put_f(&R.final_w, "dec_final_weights", 8 * kPlcUnits * kDredOut);
+    for (int k = 0; k < 3 && pk; k++) {
+      const std::string n = gn[k];
+      pk &= put_f(&R.g_subias[k], (n + "_subias").c_str(), 2 * kPlcRows);
+      pk &= need((n + "_bias").c_str(), 2 * kPlcRows * 4) != nullptr;
+      pk = pk && retile(&R.g_in[k], (n + "_weights").c_str(), (n + "_weights_idx").c_str(), kPlcUnits);
+      pk = pk && retile(&R.g_rec[k], (n + "_recurrent_weights").c_str(), nullptr, kPlcUnits);
+    }
+    if (!pk) return false;
+    m.has_dred = true;
   }
   d.features_delay = features_delay;
   d.lpc_gamma = lpc_gamma;

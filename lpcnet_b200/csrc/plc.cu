@@ -535,6 +535,7 @@ __global__ void plc_finish_kernel(PlcArgs A) {
 }
 
 #include "plc_causal.cuh"
+#include "dred.cuh"
 
 }  // namespace
 }  // namespace lpcb
@@ -1167,6 +1168,68 @@ int lpcnet_plc_conceal(LPCNetPLCState *st, short *pcm) {
   if (!st || st->magic != kPlcMagic || !st->batch) return set_last_error("lpcnet_plc_conceal: no model loaded");
   const unsigned char lost = 1;
   return lpcnet_plc_batch_process(st->batch, &lost, pcm, 1);
+}
+
+// ---- DRED: the RDOVAE decoder (src/dred_rdovae.c:37-51, src/dred_rdovae_dec.c) -------------------------------------
+struct LPCNetDredDecoder {
+  LPCNetBatch *host = nullptr;     // owns the device model (the blob carries every model, as write_lpcnet_weights.c writes it)
+  void *d_buf = nullptr; size_t d_bytes = 0;
+  long long launches = 0;
+};
+
+LPCNetDredDecoder *lpcnet_dred_decoder_create(const unsigned char *blob, int len, int device) {
+  LPCNetDredDecoder *d = new (std::nothrow) LPCNetDredDecoder();
+  if (!d) return nullptr;
+  d->host = lpcnet_batch_create(blob, len, 1, device, default_features_delay(), 1.0f);
+  if (!d->host) { delete d; return nullptr; }
+  if (!batch_view(d->host).model->has_dred) {
+    set_last_error("lpcnet_dred_decoder_create: the blob has no RDOVAE decoder arrays (dec_dense*, dec_final, state1..3)");
+    lpcnet_dred_decoder_destroy(d);
+    return nullptr;
+  }
+  return d;
+}
+
+void lpcnet_dred_decoder_destroy(LPCNetDredDecoder *d) {
+  if (!d) return;
+  if (d->host) {
+    lpcnet_batch_sync(d->host);
+    cudaSetDevice(batch_view(d->host).device);
+    cudaFree(d->d_buf);
+    lpcnet_batch_destroy(d->host);
+  }
+  delete d;
+}
+
+long long lpcnet_dred_decoder_launch_count(const LPCNetDredDecoder *d) { return d ? d->launches : 0; }
+
+int lpcnet_dred_decode_batch(LPCNetDredDecoder *d, int n_streams, float *features, const float *states, const float *latents,
+                             int nb_latents) {
+  if (!d || n_streams <= 0 || nb_latents < 0 || !features || !states || !latents)
+    return set_last_error("lpcnet_dred_decode_batch: bad arguments");
+  if (nb_latents == 0) return 0;
+  BatchView V = batch_view(d->host);
+  CKP(cudaSetDevice(V.device));
+  const size_t n_st = (size_t)n_streams * kDredState, n_z = (size_t)n_streams * nb_latents * kDredLatent,
+               n_f = (size_t)n_streams * nb_latents * kDredOut;
+  if (grow_dev(&d->d_buf, &d->d_bytes, (n_st + n_z + n_f) * 4)) return -1;
+  float *d_st = static_cast<float *>(d->d_buf), *d_z = d_st + n_st, *d_f = d_z + n_z;
+  CKP(cudaMemcpyAsync(d_st, states, n_st * 4, cudaMemcpyHostToDevice, V.stream));
+  CKP(cudaMemcpyAsync(d_z, latents, n_z * 4, cudaMemcpyHostToDevice, V.stream));
+  DredArgs A{};
+  A.net = V.model->d.dred; A.rcp_tab = V.model->d.rcp_tab; A.states = d_st; A.latents = d_z; A.features = d_f;
+  A.n_latents = nb_latents;
+  dred_decode_kernel<<<n_streams, 256, 0, V.stream>>>(A);
+  CKP(cudaGetLastError());
+  d->launches++;
+  CKP(cudaMemcpyAsync(features, d_f, n_f * 4, cudaMemcpyDeviceToHost, V.stream));
+  CKP(cudaStreamSynchronize(V.stream));
+  return 0;
+}
+
+// DRED_rdovae_decode_all (include/dred_rdovae.h:40): one stream
+int lpcnet_dred_decode_all(LPCNetDredDecoder *d, float *features, const float *state, const float *latents, int nb_latents) {
+  return lpcnet_dred_decode_batch(d, 1, features, state, latents, nb_latents);
 }
 
 }  // extern "C"

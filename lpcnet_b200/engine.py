@@ -53,7 +53,9 @@ EXPORTED_SYMBOLS = [
     "lpcnet_feature_batch_encode", "lpcnet_feature_batch_compute_features",
     "lpcnet_plc_get_size", "lpcnet_plc_init", "lpcnet_plc_create", "lpcnet_plc_destroy", "lpcnet_plc_load_model",
     "lpcnet_plc_update", "lpcnet_plc_conceal", "lpcnet_plc_reset", "lpcnet_plc_fec_add", "lpcnet_plc_fec_clear",
-    "lpcnet_plc_batch_reset", "lpcnet_plc_batch_fec_add", "lpcnet_plc_batch_fec_clear", "lpcnet_plc_batch_create", "lpcnet_plc_batch_destroy",
+    "lpcnet_plc_batch_reset", "lpcnet_plc_batch_fec_add", "lpcnet_plc_batch_fec_clear",
+    "lpcnet_dred_decoder_create", "lpcnet_dred_decoder_destroy", "lpcnet_dred_decoder_launch_count",
+    "lpcnet_dred_decode_all", "lpcnet_dred_decode_batch", "lpcnet_plc_batch_create", "lpcnet_plc_batch_destroy",
     "lpcnet_plc_batch_n_streams", "lpcnet_plc_batch_set_seed", "lpcnet_plc_batch_launch_count",
     "lpcnet_plc_batch_process", "lpcnet_plc_batch_peek", "lpcnet_plc_batch_peek_frame",
 ]
@@ -153,6 +155,13 @@ def load_library() -> C.CDLL:
     L.lpcnet_plc_batch_reset.argtypes = [vp]
     L.lpcnet_plc_batch_fec_add.argtypes = [vp, ci, vp]
     L.lpcnet_plc_batch_fec_clear.argtypes = [vp, ci]
+    L.lpcnet_dred_decoder_create.restype = vp
+    L.lpcnet_dred_decoder_create.argtypes = [vp, ci, ci]
+    L.lpcnet_dred_decoder_destroy.argtypes = [vp]
+    L.lpcnet_dred_decoder_launch_count.restype = C.c_longlong
+    L.lpcnet_dred_decoder_launch_count.argtypes = [vp]
+    L.lpcnet_dred_decode_all.argtypes = [vp, vp, vp, vp, ci]
+    L.lpcnet_dred_decode_batch.argtypes = [vp, ci, vp, vp, vp, ci]
     L.lpcnet_plc_conceal.argtypes = [vp, vp]
     L.lpcnet_plc_batch_create.restype = vp
     L.lpcnet_plc_batch_create.argtypes = [vp, ci, ci, ci, ci, cf]
@@ -653,3 +662,44 @@ class PLC:
         x = np.zeros(FRAME_SIZE, np.int16)
         _check(self.L.lpcnet_plc_conceal(self.h, _p(x)), "lpcnet_plc_conceal")
         return x
+
+
+class DredDecoder:
+    """RDOVAE decoder of DRED (DRED_rdovae_decode_all): latent vectors -> FEC feature vectors."""
+
+    def __init__(self, blob: bytes, device: int = 0):
+        self.L = load_library()
+        self._blob = np.frombuffer(blob, np.uint8)
+        self.h = self.L.lpcnet_dred_decoder_create(_p(self._blob), len(blob), device)
+        if not self.h:
+            raise LPCNetError(f"lpcnet_dred_decoder_create: {last_error()}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.lpcnet_dred_decoder_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    @property
+    def launch_count(self):
+        return int(self.L.lpcnet_dred_decoder_launch_count(self.h))
+
+    def decode_all(self, state, latents):
+        """state [24], latents [n][80] -> features [n][80] (four 20-float vectors per latent, reverse order)"""
+        z = np.ascontiguousarray(latents, np.float32)
+        st = np.ascontiguousarray(state, np.float32)
+        assert st.size == 24 and z.ndim == 2 and z.shape[1] == 80
+        out = np.zeros((z.shape[0], 80), np.float32)
+        _check(self.L.lpcnet_dred_decode_all(self.h, _p(out), _p(st), _p(z), z.shape[0]), "lpcnet_dred_decode_all")
+        return out
+
+    def decode_batch(self, states, latents):
+        """states [B][24], latents [B][n][80] -> features [B][n][80]"""
+        z = np.ascontiguousarray(latents, np.float32)
+        st = np.ascontiguousarray(states, np.float32)
+        assert z.ndim == 3 and z.shape[2] == 80 and st.shape == (z.shape[0], 24)
+        out = np.zeros(z.shape[:2] + (80,), np.float32)
+        _check(self.L.lpcnet_dred_decode_batch(self.h, z.shape[0], _p(out), _p(st), _p(z), z.shape[1]), "lpcnet_dred_decode_batch")
+        return out

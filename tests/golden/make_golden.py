@@ -164,6 +164,30 @@ def plc_causal(R):
     np.savez_compressed(os.path.join(OUT, "plc_causal.npz"), **d)
 
 
+def dred_inputs():
+    """The inputs of dred.npz: 3 packets (initial state + latent vectors) of 1, 9 and 26 latents."""
+    rng = np.random.default_rng(31)
+    return [((rng.standard_normal(24) * 0.8).astype(np.float32), (rng.standard_normal((n, 80)) * (0.5 + 0.5 * k)).astype(np.float32))
+            for k, n in enumerate((1, 9, 26))]
+
+
+def dred_model_blob():
+    A = blob.random_model()
+    A.update(blob.random_dred_decoder_model())
+    return blob.write_blob(A)
+
+
+def dred(R):
+    """The reference's RDOVAE decoder (dred_rdovae_dec_init_states + dred_rdovae_decode_qframe, src/dred_rdovae_dec.c)
+    on the random-init decoder of blob.random_dred_decoder_model()."""
+    b = dred_model_blob()
+    d = {"blob_sha256": np.frombuffer(hashlib.sha256(b).digest(), np.uint8)}
+    for k, (st, z) in enumerate(dred_inputs()):
+        d[f"state_{k}"], d[f"latents_{k}"] = st, z
+        d[f"features_{k}"] = refpy.ref_dred_decode_all(R, b, st, z)
+    np.savez_compressed(os.path.join(OUT, "dred.npz"), **d)
+
+
 def encode_signals():
     """The inputs of encode.npz: 7 signals x 24 packets (tests/test_encode_oracle.py rebuilds and compares them)."""
     n = 24 * 4
@@ -223,8 +247,8 @@ def plc(R):
 
 if __name__ == "__main__":
     R = refpy.RefLib(2)
-    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc", "encode", "plc_causal"]
+    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc", "encode", "plc_causal", "dred"]
     for name in which:
-        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc, "encode": encode, "plc_causal": plc_causal}[name](R)
+        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc, "encode": encode, "plc_causal": plc_causal, "dred": dred}[name](R)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))

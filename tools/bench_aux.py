@@ -86,6 +86,20 @@ def bench_encode(B, P, reps):
             "launches_per_call": int(launches)}
 
 
+def bench_dred(B, n, reps):
+    A = blob.random_model()
+    A.update(blob.random_dred_decoder_model())
+    bl = blob.write_blob(A)
+    rng = np.random.default_rng(3)
+    states = rng.standard_normal((B, 24)).astype(np.float32)
+    latents = rng.standard_normal((B, n, 80)).astype(np.float32)
+    dec = engine.DredDecoder(bl)
+    med, mn = timed(lambda: dec.decode_batch(states, latents), reps)
+    dec.close()
+    return {"workload": "dred rdovae decode", "packets": B, "latents_per_packet": n, "feature_vectors_per_s": B * n * 4 / med,
+            "x_realtime": B * n * 4 / med / 100, "best_s": mn, "median_s": med}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("what", nargs="*", default=["plc", "features", "encode"])
@@ -104,6 +118,8 @@ def main():
             r = bench_features(a.streams, a.frames, a.reps)
         elif w == "decode":
             r = bench_decode(a.streams, max(1, a.frames // 4), a.reps)
+        elif w == "dred":
+            r = bench_dred(a.streams, 26, a.reps)
         elif w == "encode":
             r = bench_encode(a.streams, max(1, a.frames // 4), a.reps)
         else:
