@@ -647,7 +647,8 @@ int plc_alloc(LPCNetPLCBatch *p) {
 }
 
 // One call: n_frames frames of every stream, in lock step.  lost: [B][n_frames]; d_io: device [B][n_frames*160].
-int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int n_frames) {
+// frames [f0, f0 + n_frames) of a call of total_frames frames (the control rows of a long call are built in pieces)
+int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, int total_frames) {
   const int B = p->n_streams;
   BatchView V = batch_view(p->syn);
   cudaStream_t cs = V.stream;
@@ -665,7 +666,7 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int n_frames) {
     int *perm = reinterpret_cast<int *>(m + perm_off);
     Any a{false, false, false, false, false, 0, 0, 0};
     for (int s = 0; s < B; s++) {
-      const bool is_lost = lost[(size_t)s * n_frames + f] != 0;
+      const bool is_lost = lost[(size_t)s * total_frames + f0 + f] != 0;
       const int c = p->loss_count[s];
       const uint8_t cls = is_lost ? (c == 0 ? kL0 : kL1) : (c == 0 ? kG0 : kFG);
       const bool q = p->queued[s] != 0;
@@ -696,13 +697,13 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int n_frames) {
   PlcArgs A{};
   A.st = p->st; A.w = p->w; A.lp = V.st; A.lp_copy = p->snap; A.net = V.model->d.plc; A.rcp_tab = V.model->d.rcp_tab;
   A.tab = p->tab; A.fft_scratch = p->fft_scratch; A.fade = p->fade;
-  A.pcm_io = static_cast<short *>(p->d_io); A.n_streams = B; A.total_frames = n_frames; A.remove_dc = p->remove_dc;
+  A.pcm_io = static_cast<short *>(p->d_io); A.n_streams = B; A.total_frames = total_frames; A.remove_dc = p->remove_dc;
   const int tb = 128, gs = (B + tb - 1) / tb;
   for (int f = 0; f < n_frames; f++) {
     const uint8_t *M = static_cast<const uint8_t *>(p->d_ctl) + per_frame * f;
     A.masks = M;
     A.lossc = reinterpret_cast<const uint16_t *>(M + lc_off);
-    A.frame = f;
+    A.frame = f0 + f;
     const Any a = any[f];
     const int *permQ = reinterpret_cast<const int *>(M + perm_off), *permFG = permQ + B, *permMain = permQ + 2 * B;
     // Q: process_queued_update (lpcnet_plc.c:342-347)
@@ -778,7 +779,7 @@ void plc_reset_causal_ctl(LPCNetPLCBatch *p) {
 
 // One call of the causal / codec modes: the host walks the reference's control flow for every stream and frame
 // (no signal data is involved), the device follows the resulting rows.
-int plc_run_causal(LPCNetPLCBatch *p, const unsigned char *lost, int n_frames) {
+int plc_run_causal(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, int total_frames) {
   const int B = p->n_streams, D = p->delay, BUF = D * kFrame + kTOff;
   BatchView V = batch_view(p->syn);
   cudaStream_t cs = V.stream;
@@ -817,7 +818,7 @@ int plc_run_causal(LPCNetPLCBatch *p, const unsigned char *lost, int n_frames) {
         if (c.fec_skip > 0) c.fec_skip--;
         return false;
       };
-      if (lost[(size_t)s * n_frames + f]) {
+      if (lost[(size_t)s * total_frames + f0 + f]) {
         m[cC * B + s] = 1; m[fC * B + s] = 1;
         for (int k = 0; k < c.fbfill; k++) { m[(cFl0 + k) * B + s] = 1; a.fl[k] = 1; }
         c.fbfill = 0;
@@ -882,7 +883,7 @@ int plc_run_causal(LPCNetPLCBatch *p, const unsigned char *lost, int n_frames) {
   PlcArgs A{};
   A.st = p->st; A.w = p->w; A.lp = V.st; A.lp_copy = p->snap; A.net = V.model->d.plc; A.rcp_tab = V.model->d.rcp_tab;
   A.tab = p->tab; A.fft_scratch = p->fft_scratch; A.fade = p->fade;
-  A.pcm_io = static_cast<short *>(p->d_io); A.n_streams = B; A.total_frames = n_frames; A.remove_dc = p->remove_dc;
+  A.pcm_io = static_cast<short *>(p->d_io); A.n_streams = B; A.total_frames = total_frames; A.remove_dc = p->remove_dc;
   const int tb = 128, gs = (B + tb - 1) / tb, g20 = (B * 20 + 255) / 256;
   const CausalState C = p->cst;
   std::vector<float> stage((size_t)4 * B * 20);
@@ -892,7 +893,7 @@ int plc_run_causal(LPCNetPLCBatch *p, const unsigned char *lost, int n_frames) {
     auto row = [&](int r) { return M + (size_t)r * B; };
     const uint16_t *append_off = reinterpret_cast<const uint16_t *>(M + u16_off);
     const int *perm = reinterpret_cast<const int *>(M + perm_off);
-    A.masks = M; A.lossc = append_off + B; A.frame = f;
+    A.masks = M; A.lossc = append_off + B; A.frame = f0 + f;
     const Any a = any[f];
     if (fu < fec_use.size() && fec_use[fu].frame == f) {        // the FEC vectors this frame consumes
       for (; fu < fec_use.size() && fec_use[fu].frame == f; fu++)
@@ -1072,7 +1073,13 @@ int lpcnet_plc_batch_process(LPCNetPLCBatch *p, const unsigned char *lost, short
   if (grow_dev(&p->d_io, &p->d_io_bytes, bytes)) return -1;
   cudaStream_t cs = batch_view(p->syn).stream;
   CKP(cudaMemcpyAsync(p->d_io, pcm, bytes, cudaMemcpyHostToDevice, cs));
-  if (p->causal ? plc_run_causal(p, lost, n_frames) : plc_run(p, lost, n_frames)) return -1;
+  // the per-frame control rows cost ~50 bytes per stream: build them for at most 32 MiB worth of frames at a time
+  int step = std::max(1, (int)std::min<long long>(n_frames, (32ll << 20) / (64ll * p->n_streams)));
+  if (const char *e = getenv("LPCNET_B200_PLC_CTL_FRAMES")) step = std::max(1, atoi(e));      // tests: force small pieces
+  for (int f0 = 0; f0 < n_frames; f0 += step) {
+    const int nf = std::min(step, n_frames - f0);
+    if (p->causal ? plc_run_causal(p, lost, f0, nf, n_frames) : plc_run(p, lost, f0, nf, n_frames)) return -1;
+  }
   CKP(cudaMemcpyAsync(pcm, p->d_io, bytes, cudaMemcpyDeviceToHost, cs));
   CKP(cudaStreamSynchronize(cs));
   return 0;

@@ -194,6 +194,16 @@ def test_causal_mode_many_streams_in_one_call(eng, plc_blob):
         small.set_seed(i, blob.stream_seed(s))
     assert first_diff(small.process(pcm[pick], lost[pick]), got[pick]) is None
     small.close()
+    # a long call builds its control rows in pieces: forced to 5 frames per piece here
+    os.environ["LPCNET_B200_PLC_CTL_FRAMES"] = "5"
+    try:
+        pb = eng.PLCBatch(plc_blob, B, opt)
+        for s in range(B):
+            pb.set_seed(s, blob.stream_seed(s))
+        assert first_diff(pb.process(pcm, lost), got) is None
+        pb.close()
+    finally:
+        del os.environ["LPCNET_B200_PLC_CTL_FRAMES"]
     # lpcnet_plc_create(LPCNET_PLC_CODEC) + fec_add / update / conceal, one stream
     s, fec = 2, blob.synthetic_fec(F, 2)
     plc = eng.PLC(plc_blob, 2)
