@@ -568,6 +568,7 @@ struct LPCNetPLCBatch {
   void *causal_alloc = nullptr; size_t causal_bytes = 0;
   struct Ctl {
     int blend = 0, skip = 0, pcm_fill = 0, fbfill = 0;
+    int fcount = 0;                     // the synthesiser's frame_count (lpcnet.c:119): frames it has conditioned on
     int fec_keep = 0, fec_read = 0, fec_fill = 0, fec_skip = 0;
     std::vector<float> fec;             // [fec_fill][20]
   };
@@ -755,7 +756,7 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
 // ---- causal / codec modes -----------------------------------------------------------------------------------------
 // control rows of one frame, [row][B] bytes (cU sits at mUpd's index so that the Burg kernels serve both drivers)
 enum CRow { cC = 0, cU = 1, cSB, cSnB, cNS, cFl0, cFl1, cFl2, cFl3, cA0, cA1, cA2, pmA0, pmA1, pmA2, pmC, pmSB, pmNB,
-            fA0, fA1, fA2, fSBfree, fSBforced, fC, pushSB0, pushSB1, pushEnc, kCRows };
+            fA0, fA1, fA2, fSBfree, fSBforced, fC, fC2, pushSB0, pushSB1, pushEnc, kCRows };
 static_assert(cU == mUpd, "plc_burg_kernel reads the update mask at mUpd");
 
 int plc_alloc_causal(LPCNetPLCBatch *p) {
@@ -818,21 +819,30 @@ int plc_run_causal(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_f
         if (c.fec_skip > 0) c.fec_skip--;
         return false;
       };
+      // lpcnet_synthesize_tail_impl writes zeros and leaves the state alone until the synthesiser has run more than
+      // FEATURES_DELAY frame networks (lpcnet.c:239-243): a loss in the first frames of a stream
+      auto ran_network = [&]() { if (c.fcount < 1000) c.fcount++; };
+      auto warm = [&]() -> uint8_t { return c.fcount > D ? 1 : 0; };
       if (lost[(size_t)s * total_frames + f0 + f]) {
-        m[cC * B + s] = 1; m[fC * B + s] = 1;
-        for (int k = 0; k < c.fbfill; k++) { m[(cFl0 + k) * B + s] = 1; a.fl[k] = 1; }
+        m[cC * B + s] = 1;
+        for (int k = 0; k < c.fbfill; k++) { m[(cFl0 + k) * B + s] = 1; a.fl[k] = 1; ran_network(); }
         c.fbfill = 0;
         const int n_iter = (c.pcm_fill + kFrame - 1) / kFrame;
         for (int it = 0; it < n_iter; it++) {
           const int j = 3 - n_iter + it;
-          m[(cA0 + j) * B + s] = 1; m[(fA0 + j) * B + s] = 3;
+          m[(cA0 + j) * B + s] = 1;
           m[(pmA0 + j) * B + s] = fec_or_pred(j) ? 4 : 1;
+          ran_network();
+          m[(fA0 + j) * B + s] = (uint8_t)(3 * warm());
           perm[j * B + a.nA[j]++] = s;
           a.a[j] = 1;
           c.skip++;
         }
         c.pcm_fill = 0;
+        m[fC * B + s] = warm();
         const bool used = fec_or_pred(3);
+        ran_network();
+        m[fC2 * B + s] = warm();
         lc = used ? 0 : lc + 1;
         m[pmC * B + s] = (uint8_t)((used ? 4 : 1) | 8);
         lossc[s] = (uint16_t)(lc > 60000 ? 60000 : lc);
@@ -844,7 +854,8 @@ int plc_run_causal(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_f
           if (c.blend) {
             m[cSB * B + s] = 1; a.sb = 1;
             if (p->enable_blending) {
-              m[pmSB * B + s] = 2; m[fSBfree * B + s] = 1; m[fSBforced * B + s] = 3;
+              ran_network();               // twice in the reference, the first on a copy that is thrown away
+              m[pmSB * B + s] = 2; m[fSBfree * B + s] = warm(); m[fSBforced * B + s] = (uint8_t)(3 * warm());
               for (int i = 0; i < D; i++) { m[(pushSB0 + i) * B + s] = push_code(c); a.pushsb[i] = 1; }
               perm[3 * B + a.nSB++] = s;
             } else {
@@ -921,7 +932,7 @@ int plc_run_causal(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_f
       c_pred_kernel<<<B, 256, 0, cs>>>(A, row(pmC), C.fecst + (size_t)3 * B * 20);
       c_feat_kernel<<<g20, 256, 0, cs>>>(A, row(cC));
       if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, row(cC))) return -1;
-      if (batch_sample_segment(p->syn, kTOff, row(fC), nullptr, p->w.sego2, perm + (size_t)4 * B, a.nC)) return -1;
+      if (batch_sample_segment(p->syn, kTOff, row(fC2), nullptr, p->w.sego2, perm + (size_t)4 * B, a.nC)) return -1;
       c_finish_kernel<<<gs, tb, 0, cs>>>(A, row(cU), row(cC), 0);
     }
     // ---- received frames (lpcnet_plc_update_causal) ----

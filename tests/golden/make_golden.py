@@ -215,6 +215,35 @@ def plc_model_blob():
     return blob.write_blob(A)
 
 
+def plc_edges(R):
+    """Losses where the concealment has the least to stand on, through the reference (FEATURES_DELAY 0 build for the
+    non-causal mode, 2 for the causal and codec modes): stream 0 loses every frame, 1 none, 2 the very first frame,
+    3 everything but the first, 4 every other frame starting with the first; inputs are silence, full-scale square
+    waves, a click and a ramp (the synthesiser is still in its FEATURES_DELAY warm-up when the early losses arrive,
+    src/lpcnet.c:239-243)."""
+    b = plc_model_blob()
+    F = 14
+    T = F * 160
+    t = np.arange(T)
+    x = np.stack([blob.synthetic_pcm(F, 9),
+                  np.where((t // 40) % 2 == 0, 32767, -32768).astype(np.int16),
+                  np.zeros(T, np.int16),
+                  np.where(t % 2 == 0, 32767, -32768).astype(np.int16),
+                  np.linspace(-32768, 32767, T).astype(np.int16)])
+    x[2, T // 2] = 32767
+    lost = np.zeros((5, F), np.uint8)
+    lost[0, :] = 1
+    lost[2, 0] = 1
+    lost[3, 1:] = 1
+    lost[4, ::2] = 1
+    d = {"blob_sha256": np.frombuffer(hashlib.sha256(b).digest(), np.uint8), "in": x, "lost": lost}
+    R0 = refpy.RefLib(0)
+    for opt in (5, 0, 4, 2):
+        lib = R0 if opt & 1 else R
+        d[f"out_{opt}"] = np.stack([refpy.RefPLC(lib, b, opt, blob.stream_seed(s)).run(x[s], lost[s]) for s in range(5)])
+    np.savez_compressed(os.path.join(OUT, "plc_edges.npz"), **d)
+
+
 def plc(R):
     """lpcnet_plc_update / lpcnet_plc_conceal of the reference's FEATURES_DELAY 0 build (libref_d0.so), non-causal
     mode without and with the DC filter, 3 streams x 40 frames under Gilbert loss; plus burg_cepstral_analysis and
@@ -247,8 +276,8 @@ def plc(R):
 
 if __name__ == "__main__":
     R = refpy.RefLib(2)
-    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc", "encode", "plc_causal", "dred"]
+    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc", "encode", "plc_causal", "dred", "plc_edges"]
     for name in which:
-        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc, "encode": encode, "plc_causal": plc_causal, "dred": dred}[name](R)
+        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc, "encode": encode, "plc_causal": plc_causal, "dred": dred, "plc_edges": plc_edges}[name](R)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))

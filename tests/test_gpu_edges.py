@@ -1,0 +1,198 @@
+"""Edge cases of the C-ABI on the GPU: empty calls, bad arguments, extreme inputs (silence, full-scale square waves,
+all-ones / all-zero packets, a stream that loses every frame beside one that loses none, a loss on the very first
+frame).  Where there is output it is compared bit for bit with the CPU oracle."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+from lpcnet_b200 import blob, engine
+from oracle import orcpy
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+@pytest.fixture(scope="module")
+def eng(engine_lib):
+    assert engine.device_count() > 0, "no CUDA device: the gpu tests cannot run (there is no CPU fallback)"
+    return engine
+
+
+@pytest.fixture(scope="module")
+def plc_blob():
+    A = blob.random_model()
+    A.update(blob.random_plc_model())
+    return blob.write_blob(A)
+
+
+def extreme_pcm(n_frames):
+    """silence | full-scale square wave | one click | alternating +-32768/32767 | a ramp through the int16 range"""
+    T = n_frames * 160
+    t = np.arange(T)
+    rows = [np.zeros(T, np.int16),
+            np.where((t // 40) % 2 == 0, 32767, -32768).astype(np.int16),
+            np.zeros(T, np.int16),
+            np.where(t % 2 == 0, 32767, -32768).astype(np.int16),
+            np.linspace(-32768, 32767, T).astype(np.int16)]
+    rows[2][T // 2] = 32767
+    return np.stack(rows)
+
+
+def test_empty_calls_change_nothing(eng, model_blob, orc_model, codebooks, orclib, plc_blob):
+    B, F = 3, 3
+    feats = np.stack([blob.synthetic_features(F, s) for s in range(B)])
+    seeds = [blob.stream_seed(s) for s in range(B)]
+    bt = eng.Batch(model_blob, B)
+    bt.set_codebooks(codebooks)
+    for s in range(B):
+        bt.set_seed(s, seeds[s])
+    n0 = bt.launch_count
+    pcm, _, _ = bt.synthesize(feats[:, :0])
+    assert pcm.shape == (B, 0)
+    pcm, ft = bt.decode(np.zeros((B, 0, 8), np.uint8), want_features=True)
+    assert pcm.shape == (B, 0) and ft.shape == (B, 0, 36)
+    assert bt.launch_count == n0                     # nothing ran
+    pcm, _, _ = bt.synthesize(feats)
+    for s in range(B):
+        assert np.array_equal(pcm[s], orcpy.OrcStream(orc_model, seeds[s]).run(feats[s])[0])
+    bt.close()
+
+    x = np.stack([blob.synthetic_pcm(8, 40 + s) for s in range(B)])
+    fb = eng.FeatureBatch(B)
+    fb.set_codebooks(codebooks)
+    n0 = fb.launch_count
+    assert fb.compute(x[:, :0]).shape == (B, 0, 36)
+    pk = fb.encode(x[:, :0])
+    assert pk.shape == (B, 0, 8)
+    assert fb.launch_count == n0
+    pk = fb.encode(x)
+    for s in range(B):
+        want, _ = orcpy.OrcEncoder(orclib).encode(x[s], codebooks)
+        assert np.array_equal(pk[s], want)
+    fb.close()
+
+    pb = eng.PLCBatch(plc_blob, B, 5)
+    n0 = pb.launch_count
+    out = pb.process(x[:, :0], np.zeros((B, 0), np.uint8))
+    assert out.shape == (B, 0) and pb.launch_count == n0
+    pb.close()
+
+
+def test_bad_arguments_are_errors_with_a_message(eng, model_blob):
+    L = eng.load_library()
+    bt = eng.Batch(model_blob, 2)
+    f = np.zeros((2, 1, 36), np.float32)
+    pcm = np.zeros((2, 160), np.int16)
+    P = eng._p
+    assert L.lpcnet_batch_synthesize(bt.h, P(f), 36, 1, None, None, None, None) != 0          # no output buffer
+    assert L.lpcnet_b200_last_error()
+    assert L.lpcnet_batch_synthesize(bt.h, None, 36, 1, P(pcm), None, None, None) != 0         # no features
+    assert L.lpcnet_batch_synthesize(bt.h, P(f), 19, 1, P(pcm), None, None, None) != 0         # stride < NB_FEATURES
+    assert L.lpcnet_batch_synthesize(None, P(f), 36, 1, P(pcm), None, None, None) != 0         # no batch
+    with pytest.raises(eng.LPCNetError):
+        bt.set_seed(2, b"x")                                                                    # stream out of range
+    with pytest.raises(eng.LPCNetError):
+        bt.set_tile(12)
+    with pytest.raises(eng.LPCNetError):
+        bt.get_state(-1)
+    with pytest.raises(eng.LPCNetError):
+        bt.decode(np.zeros((2, 1, 8), np.uint8))                                                # no codebooks yet
+    with pytest.raises(eng.LPCNetError):
+        bt.set_codebooks(np.zeros(100, np.float32))                                             # wrong size
+    # the batch is still usable after the refused calls
+    got, _, _ = bt.synthesize(np.zeros((2, 2, 36), np.float32))
+    assert got.shape == (2, 320)
+    bt.close()
+    with pytest.raises(eng.LPCNetError):
+        eng.Batch(model_blob, 0)
+    with pytest.raises(eng.LPCNetError):
+        eng.Batch(model_blob[:1000], 1)                                                         # truncated blob
+    with pytest.raises(eng.LPCNetError):
+        eng.FeatureBatch(0)
+
+
+def test_extreme_packets_decode_like_the_oracle(eng, model_blob, codebooks, orc_model, orclib):
+    """All-zero, all-ones and alternating packets: every index field at its smallest / largest value (pitch index
+    63, interpolation id 7, the forbidden-interpolation remap)."""
+    pats = [bytes(8), b"\xff" * 8, b"\xaa" * 8, b"\x55" * 8, bytes(range(0, 256, 32))]
+    packets = np.stack([np.frombuffer(p * 1, np.uint8).reshape(1, 8).repeat(3, 0) for p in pats])
+    packets[4, 1] = 255 - packets[4, 1]
+    bt = eng.Batch(model_blob, len(pats))
+    bt.set_codebooks(codebooks)
+    pcm, feats = bt.decode(packets, want_features=True)
+    bt.close()
+    for s in range(len(pats)):
+        vq_mem = np.zeros(18, np.float32)
+        want = np.stack([orclib.decode_packet(vq_mem, packets[s, k].tobytes(), codebooks) for k in range(3)])
+        assert np.array_equal(bits(feats[s]), bits(want.reshape(12, 36))), s
+        assert np.array_equal(pcm[s], orcpy.OrcStream(orc_model).run(feats[s])[0]), s
+
+
+def test_extreme_signals_through_analysis_and_encoder(eng, codebooks, orclib):
+    x = extreme_pcm(12)
+    B = x.shape[0]
+    fb = eng.FeatureBatch(B)
+    fb.set_codebooks(codebooks)
+    got = fb.compute(x)
+    fb.reset()
+    pk, qf = fb.encode(x, want_features=True)
+    fb.close()
+    for s in range(B):
+        want = orcpy.OrcEncoder(orclib).run(x[s])
+        assert np.array_equal(bits(got[s]), bits(want)), ("features", s)
+        wpk, wqf = orcpy.OrcEncoder(orclib).encode(x[s], codebooks)
+        assert np.array_equal(pk[s], wpk), ("packets", s)
+        # the LPC entries [20, 36) of the encoder's quantised rows never leave lpcnet_encode
+        assert np.array_equal(bits(qf[s][:, :20]), bits(wqf.reshape(-1, 36)[:, :20])), ("quantised features", s)
+
+
+@pytest.mark.parametrize("opt", [5, 0, 4, 2])
+def test_plc_all_lost_none_lost_and_first_frame_lost(eng, plc_blob, opt):
+    """tests/golden/plc_edges.npz (the unmodified reference): stream 0 loses every frame, 1 none, 2 the very first
+    frame, 3 everything but the first, 4 alternates from the first; silence, full-scale square waves, a click, a ramp.
+    In the causal and codec modes the early losses meet a synthesiser that is still inside its FEATURES_DELAY warm-up
+    (src/lpcnet.c:239-243: zeros out, state untouched)."""
+    g = np.load(os.path.join(HERE, "golden", "plc_edges.npz"))
+    assert hashlib.sha256(plc_blob).digest() == g["blob_sha256"].tobytes()
+    x, lost, want = g["in"], g["lost"], g[f"out_{opt}"]
+    B = x.shape[0]
+    pb = eng.PLCBatch(plc_blob, B, opt)
+    for s in range(B):
+        pb.set_seed(s, blob.stream_seed(s))
+    got = pb.process(x, lost)
+    pb.close()
+    for s in range(B):
+        d = np.nonzero(got[s] != want[s])[0]
+        assert d.size == 0, ("stream, first differing sample", s, int(d[0]))
+    # frame by frame through lpcnet_plc_update / lpcnet_plc_conceal, the stream that loses its first frame
+    s = 2
+    plc = eng.PLC(plc_blob, opt)
+    out = [plc.conceal() if lost[s, f] else plc.update(x[s, f * 160:(f + 1) * 160]) for f in range(lost.shape[1])]
+    plc.close()
+    # the single-stream state is seeded "LPCNet" like the reference's; the fixture used stream seeds, so compare with
+    # the oracle on the default seed
+    model = orcpy.OrcModel(orcpy.OrcLib(), plc_blob, 0 if opt & 1 else 2, 1.0, None)
+    ref = orcpy.OrcPLC(model, opt, b"LPCNet").run(x[s], lost[s])
+    assert np.array_equal(np.concatenate(out), ref)
+
+
+def test_silence_and_full_scale_features_synthesize_like_the_oracle(eng, model_blob, orc_model):
+    """Feature rows of zeros, of large magnitude (saturating the pitch index clamp) and with NaN-free extremes."""
+    F = 4
+    base = blob.synthetic_features(F, 0)
+    rows = [np.zeros_like(base), base * 8.0, -base * 8.0, base.copy()]
+    rows[3][:, 18] = 5.0          # pitch feature far above the range: the index clamps (src/lpcnet.c:109-111)
+    feats = np.stack(rows)
+    bt = eng.Batch(model_blob, len(rows))
+    pcm, tr, _ = bt.synthesize(feats, trace=True)
+    bt.close()
+    for s in range(len(rows)):
+        ref = orcpy.OrcStream(orc_model).run(feats[s], trace=True)
+        assert np.array_equal(pcm[s], ref[0]), s
+        assert np.array_equal(tr[s], ref[1]), s
