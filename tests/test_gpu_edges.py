@@ -196,3 +196,121 @@ def test_silence_and_full_scale_features_synthesize_like_the_oracle(eng, model_b
         ref = orcpy.OrcStream(orc_model).run(feats[s], trace=True)
         assert np.array_equal(pcm[s], ref[0]), s
         assert np.array_equal(tr[s], ref[1]), s
+
+
+def overflow_fec(F):
+    """more vectors than PLC_MAX_FEC (100) in one go, steady arrivals afterwards, a few "skip one" markers"""
+    rng = np.random.default_rng(77)
+    fec = {f: [(rng.standard_normal(20) * 0.5).astype(np.float32) for _ in range(3)] for f in range(F)}
+    fec[0] = [(rng.standard_normal(20) * 0.5).astype(np.float32) for _ in range(120)]
+    fec[5] = [None] * 4 + fec[5]
+    return fec
+
+
+@pytest.mark.parametrize("opt", [0, 2])
+def test_fec_queue_overflow_and_compaction(eng, plc_blob, opt):
+    """lpcnet_plc_fec_add past PLC_MAX_FEC: the reference drops vectors while nothing has been consumed, then moves
+    the kept tail to the front (lpcnet_plc.c:111-127)."""
+    F = 40
+    x = blob.synthetic_pcm(F, 3)
+    lost = blob.synthetic_loss_pattern(F, 1, 0.6, 0.2)
+    assert lost.sum() > 5
+    fec = overflow_fec(F)
+    model = orcpy.OrcModel(orcpy.OrcLib(), plc_blob, 2, 1.0, None)
+    want = orcpy.OrcPLC(model, opt, b"LPCNet").run(x, lost, fec)
+    plc = eng.PLC(plc_blob, opt)
+    out = []
+    for f in range(F):
+        for v in fec.get(f, []):
+            plc.fec_add(v)
+        out.append(plc.conceal() if lost[f] else plc.update(x[f * 160:(f + 1) * 160]))
+    plc.close()
+    d = np.nonzero(np.concatenate(out) != want)[0]
+    assert d.size == 0, int(d[0])
+    # the same through the batch entry points, the stream beside one without FEC
+    pb = eng.PLCBatch(plc_blob, 2, opt)
+    pb.set_seed(0, b"LPCNet")
+    pb.set_seed(1, b"LPCNet")
+    got = []
+    for f in range(F):
+        for v in fec.get(f, []):
+            pb.fec_add(0, v)
+        got.append(pb.process(np.stack([x, x])[:, f * 160:(f + 1) * 160], np.stack([lost, lost])[:, f:f + 1]))
+    pb.close()
+    got = np.concatenate(got, axis=1)
+    assert np.array_equal(got[0], want)
+    assert np.array_equal(got[1], orcpy.OrcPLC(model, opt, b"LPCNet").run(x, lost))
+
+
+@pytest.mark.parametrize("opt", [4, 6, 5])
+def test_plc_calls_of_any_length_agree(eng, plc_blob, opt):
+    """one call of 30 frames == calls of 1, 7, 2 and 20 frames (state carried across calls), all modes"""
+    B, F = 6, 30
+    x = np.stack([blob.synthetic_pcm(F, 60 + s) for s in range(B)])
+    lost = np.stack([blob.synthetic_loss_pattern(F, 20 + s, 0.6, 0.2) for s in range(B)])
+    lost[1, :3] = 1
+    outs = []
+    for cuts in ((0, 30), (0, 1, 8, 10, 30)):
+        pb = eng.PLCBatch(plc_blob, B, opt)
+        for s in range(B):
+            pb.set_seed(s, blob.stream_seed(s))
+        outs.append(np.concatenate([pb.process(x[:, a * 160:b * 160], lost[:, a:b]) for a, b in zip(cuts[:-1], cuts[1:])], axis=1))
+        pb.close()
+    assert np.array_equal(outs[0], outs[1])
+    model = orcpy.OrcModel(orcpy.OrcLib(), plc_blob, 0 if opt & 1 else 2, 1.0, None)
+    for s in (1, 4):
+        assert np.array_equal(outs[0][s], orcpy.OrcPLC(model, opt, blob.stream_seed(s)).run(x[s], lost[s])), s
+
+
+def test_reset_of_one_stream_and_two_batches_side_by_side(eng, model_blob, orc_model, codebooks):
+    """lpcnet_batch_reset(stream) in the middle of a run restarts that stream only; a second batch (other size, other
+    tile, with codebooks) used in between leaves the first untouched (no process-wide scratch)."""
+    B, F = 5, 6
+    feats = np.stack([blob.synthetic_features(F, s) for s in range(B)])
+    seeds = [blob.stream_seed(s) for s in range(B)]
+    b1 = eng.Batch(model_blob, B)
+    b2 = eng.Batch(model_blob, 19)
+    b2.set_tile(16)
+    b2.set_codebooks(codebooks)
+    for s in range(B):
+        b1.set_seed(s, seeds[s])
+    first, _, _ = b1.synthesize(feats[:, :3])
+    other, _, _ = b2.synthesize(np.stack([blob.synthetic_features(4, 30 + s) for s in range(19)]))
+    b2.decode(np.zeros((19, 1, 8), np.uint8))
+    b1.reset(2)
+    b1.set_seed(2, seeds[2])
+    second, _, _ = b1.synthesize(feats[:, 3:])
+    for s in range(B):
+        st = orcpy.OrcStream(orc_model, seeds[s])
+        want = st.run(feats[s])[0]
+        if s == 2:
+            want = np.concatenate([want[:480], orcpy.OrcStream(orc_model, seeds[s]).run(feats[s, 3:])[0]])
+        assert np.array_equal(np.concatenate([first[s], second[s]]), want), s
+    assert np.array_equal(other[7], orcpy.OrcStream(orc_model).run(blob.synthetic_features(4, 37))[0])
+    b1.close()
+    b2.close()
+
+
+def test_dred_decoder_edges(eng):
+    """no latents, one latent, the reference's maximum of 26 per packet (DRED_NUM_REDUNDANCY_FRAMES / 2), saturating
+    and zero inputs"""
+    A = blob.random_model()
+    A.update(blob.random_dred_decoder_model())
+    b = blob.write_blob(A)
+    m = orcpy.OrcModel(orcpy.OrcLib(), b, 2, 1.0, None)
+    dec = eng.DredDecoder(b)
+    n0 = dec.launch_count
+    assert dec.decode_all(np.zeros(24, np.float32), np.zeros((0, 80), np.float32)).shape == (0, 80)
+    assert dec.launch_count == n0
+    rng = np.random.default_rng(2)
+    cases = [(np.zeros(24, np.float32), np.zeros((1, 80), np.float32)),
+             (np.full(24, 50.0, np.float32), np.full((26, 80), -50.0, np.float32)),
+             ((rng.standard_normal(24) * 1e4).astype(np.float32), (rng.standard_normal((26, 80)) * 1e4).astype(np.float32)),
+             ((rng.standard_normal(24) * 1e-30).astype(np.float32), (rng.standard_normal((3, 80)) * 1e-30).astype(np.float32))]
+    for k, (st, z) in enumerate(cases):
+        got = dec.decode_all(st, z)
+        want = orcpy.dred_decode_all(m, st, z)
+        assert np.array_equal(bits(got), bits(want)), k
+    dec.close()
+    with pytest.raises(eng.LPCNetError):
+        eng.DredDecoder(blob.write_blob(blob.random_model()))        # no dred_rdovae_dec_* arrays
