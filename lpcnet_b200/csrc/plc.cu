@@ -81,27 +81,43 @@ struct PlcArgs {
 #define DC_CONST 0.003
 
 // ---- update streams: DC removal (lpcnet_plc.c:361-371), pcm_save ----
-__global__ void plc_pre_kernel(PlcArgs A) {
-  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+// One warp per stream (4 streams per block of 128): the frame moves in coalesced 64-byte rows, the DC filter's
+// recurrence (sequential in double precision) runs on lane 0 out of shared memory.
+constexpr int kWpsThreads = 128;
+__device__ __forceinline__ int wps_stream(int &lane, int &w) {
+  lane = threadIdx.x & 31; w = threadIdx.x >> 5;
+  return blockIdx.x * (kWpsThreads / 32) + w;
+}
+inline int wps_grid(int n_streams) { return (n_streams + kWpsThreads / 32 - 1) / (kWpsThreads / 32); }
+
+__global__ void __launch_bounds__(kWpsThreads) plc_pre_kernel(PlcArgs A) {
+  __shared__ short xs[kWpsThreads / 32][kFrame], ls[kWpsThreads / 32][kFrame];
+  int lane, w;
+  const int s = wps_stream(lane, w);
   if (s >= A.n_streams || !A.masks[mUpd * A.n_streams + s]) return;
   const short *x = A.pcm_io + ((size_t)s * A.total_frames + A.frame) * kFrame;
   short *in = A.w.in + (size_t)s * kFrame, *save = A.w.save + (size_t)s * kFrame, *lp = A.w.lp + (size_t)s * kFrame;
-  A.w.delta[s] = (int)A.st.syn_dc[s];
-  if (A.remove_dc) {
-    double dc = A.st.dc_mem[s] + A.st.syn_dc[s];
-    A.st.syn_dc[s] = 0;
-    A.w.mem_bak[s] = dc;
-    for (int i = 0; i < kFrame; i++) {
-      const short l = (short)(int)floor(.5 + dc);
-      dc += DC_CONST * ((double)x[i] - dc);
-      lp[i] = l;
-      in[i] = (short)(x[i] - l);
+  for (int i = lane; i < kFrame; i += 32) xs[w][i] = x[i];
+  __syncwarp();
+  if (lane == 0) {
+    A.w.delta[s] = (int)A.st.syn_dc[s];
+    if (A.remove_dc) {
+      double dc = A.st.dc_mem[s] + A.st.syn_dc[s];
+      A.st.syn_dc[s] = 0;
+      A.w.mem_bak[s] = dc;
+      for (int i = 0; i < kFrame; i++) {
+        ls[w][i] = (short)(int)floor(.5 + dc);
+        dc += DC_CONST * ((double)xs[w][i] - dc);
+      }
+      A.st.dc_mem[s] = dc;
     }
-    A.st.dc_mem[s] = dc;
-  } else {
-    for (int i = 0; i < kFrame; i++) { lp[i] = 0; in[i] = x[i]; }
   }
-  for (int i = 0; i < kFrame; i++) save[i] = in[i];
+  __syncwarp();
+  for (int i = lane; i < kFrame; i += 32) {
+    const short l = A.remove_dc ? ls[w][i] : (short)0;
+    const short v = (short)(xs[w][i] - l);
+    lp[i] = l; in[i] = v; save[i] = v;
+  }
 }
 
 // ---- burg_cepstral_analysis (freq.c:152-199, burg.c:97-245), one thread per update stream ----
@@ -434,29 +450,40 @@ __global__ void plc_clear_state_kernel(DevState st, const uint8_t *mask, int B) 
 
 // FG: after the 80 free samples (lpcnet_plc.c:385-402): keep them, redo the DC removal so that it accounts for
 // the synthesised 5 ms, and lay out the reversed frame for the backward pass
-__global__ void plc_fg_mid_kernel(PlcArgs A) {
-  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(kWpsThreads) plc_fg_mid_kernel(PlcArgs A) {
+  __shared__ short xs[kWpsThreads / 32][kFrame], ls[kWpsThreads / 32][kFrame], ys[kWpsThreads / 32][kTOff];
+  int lane, w;
+  const int s = wps_stream(lane, w);
   if (s >= A.n_streams || !A.masks[mFG * A.n_streams + s]) return;
   short *pcm = A.st.pcm + (size_t)s * kFrame, *in = A.w.in + (size_t)s * kFrame, *lp = A.w.lp + (size_t)s * kFrame;
   const short *syn = A.w.sego + (size_t)s * kTOff;   // an 80-sample segment: rows of 80
-  for (int i = 0; i < kTOff; i++) pcm[kFrame - kTOff + i] = syn[i];
+  for (int i = lane; i < kTOff; i += 32) { const short v = syn[i]; ys[w][i] = v; pcm[kFrame - kTOff + i] = v; }
+  for (int i = lane; i < kFrame; i += 32) xs[w][i] = (short)(in[i] + lp[i]);
+  __syncwarp();
   if (A.remove_dc) {
-    double dc = A.w.mem_bak[s], sd = A.st.syn_dc[s];
-    for (int i = 0; i < kTOff; i++) sd += DC_CONST * ((double)pcm[kFrame - kTOff + i] - sd);
-    dc += sd;
-    A.w.delta[s] = (int)((double)A.w.delta[s] + sd);
-    A.st.syn_dc[s] = 0;
-    for (int i = 0; i < kFrame; i++) {
-      const short x = (short)(in[i] + lp[i]);
-      const short l = (short)(int)floor(.5 + dc);
-      dc += DC_CONST * ((double)x - dc);
-      lp[i] = l;
-      in[i] = (short)(x - l);
+    if (lane == 0) {
+      double dc = A.w.mem_bak[s], sd = A.st.syn_dc[s];
+      for (int i = 0; i < kTOff; i++) sd += DC_CONST * ((double)ys[w][i] - sd);
+      dc += sd;
+      A.w.delta[s] = (int)((double)A.w.delta[s] + sd);
+      A.st.syn_dc[s] = 0;
+      for (int i = 0; i < kFrame; i++) {
+        ls[w][i] = (short)(int)floor(.5 + dc);
+        dc += DC_CONST * ((double)xs[w][i] - dc);
+      }
+      A.st.dc_mem[s] = dc;
     }
-    A.st.dc_mem[s] = dc;
-    for (int i = 0; i < kFrame; i++) A.w.save[(size_t)s * kFrame + i] = in[i];
+    __syncwarp();
+    for (int i = lane; i < kFrame; i += 32) {
+      const short l = ls[w][i], v = (short)(xs[w][i] - l);
+      lp[i] = l; in[i] = v; A.w.save[(size_t)s * kFrame + i] = v;
+      xs[w][i] = v;
+    }
+  } else {
+    for (int i = lane; i < kFrame; i += 32) xs[w][i] = in[i];
   }
-  for (int i = 0; i < kFrame; i++) A.w.segf[(size_t)s * kFrame + i] = in[kFrame - 1 - i];
+  __syncwarp();
+  for (int i = lane; i < kFrame; i += 32) A.w.segf[(size_t)s * kFrame + i] = xs[w][kFrame - 1 - i];
 }
 
 // FG: cross-fade of the forward and the backward synthesis, and the queued update (lpcnet_plc.c:403-419)
@@ -503,35 +530,62 @@ __global__ void plc_lost_mid_kernel(PlcArgs A) {
 }
 
 // end of the frame for every stream: outputs, buffers, DC (lpcnet_plc.c:436-446, 473-489)
-__global__ void plc_finish_kernel(PlcArgs A) {
-  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(kWpsThreads) plc_finish_kernel(PlcArgs A) {
+  __shared__ short os[kWpsThreads / 32][kFrame];
+  int lane, w;
+  const int s = wps_stream(lane, w);
   if (s >= A.n_streams) return;
   const uint8_t cls = A.masks[mCls * A.n_streams + s];
   short *pcm = A.st.pcm + (size_t)s * kFrame, *out = A.w.out + (size_t)s * kFrame;
   short *dcb = A.st.dc_buf + (size_t)s * kTOff;
   short *io = A.pcm_io + ((size_t)s * A.total_frames + A.frame) * kFrame;
+  constexpr int NI = kFrame / 32;                     // 5 samples per lane: i = lane + 32 k
+  short o[NI];
   if (cls == kG0 || cls == kFG) {
     const short *in = A.w.in + (size_t)s * kFrame, *save = A.w.save + (size_t)s * kFrame, *lp = A.w.lp + (size_t)s * kFrame;
-    for (int i = 0; i < kTOff; i++) { out[kTOff + i] = in[i]; out[i] = pcm[kTOff + i]; }
-    for (int i = 0; i < kFrame; i++) pcm[i] = save[i];
-    if (A.remove_dc) {
-      for (int i = 0; i < kTOff; i++) out[i] = (short)(out[i] + dcb[i]);
-      for (int i = kTOff; i < kFrame; i++) out[i] = (short)(out[i] + lp[i - kTOff]);
-      for (int i = 0; i < kTOff; i++) dcb[i] = lp[kFrame - kTOff + i];
+    short nd[NI];
+#pragma unroll
+    for (int k = 0; k < NI; k++) {
+      const int i = lane + 32 * k;
+      o[k] = i < kTOff ? pcm[kTOff + i] : in[i - kTOff];
+      nd[k] = 0;
+      if (A.remove_dc) {
+        o[k] = (short)(o[k] + (i < kTOff ? dcb[i] : lp[i - kTOff]));
+        if (i < kTOff) nd[k] = lp[kFrame - kTOff + i];
+      }
+    }
+    __syncwarp();                                     // every read of pcm / dc_buf is done
+#pragma unroll
+    for (int k = 0; k < NI; k++) {
+      const int i = lane + 32 * k;
+      pcm[i] = save[i];
+      if (A.remove_dc && i < kTOff) dcb[i] = nd[k];
     }
   } else {
-    for (int i = 0; i < kTOff; i++) pcm[i] = out[kTOff + i];
+#pragma unroll
+    for (int k = 0; k < NI; k++) { const int i = lane + 32 * k; o[k] = out[i]; os[w][i] = o[k]; }
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < NI; k++) { const int i = lane + 32 * k; if (i < kTOff) pcm[i] = os[w][kTOff + i]; }
     if (A.remove_dc) {
       const int dc = (int)floor(.5 + A.st.dc_mem[s]);
-      double sd = A.st.syn_dc[s];
-      for (int i = (cls == kL0 ? kTOff : 0); i < kFrame; i++) sd += DC_CONST * ((double)out[i] - sd);
-      A.st.syn_dc[s] = sd;
-      for (int i = 0; i < kTOff; i++) out[i] = (short)(out[i] + dcb[i]);
-      for (int i = kTOff; i < kFrame; i++) out[i] = (short)(out[i] + dc);
-      for (int i = 0; i < kTOff; i++) dcb[i] = (short)dc;
+      if (lane == 0) {
+        double sd = A.st.syn_dc[s];
+        for (int i = (cls == kL0 ? kTOff : 0); i < kFrame; i++) sd += DC_CONST * ((double)os[w][i] - sd);
+        A.st.syn_dc[s] = sd;
+      }
+#pragma unroll
+      for (int k = 0; k < NI; k++) {
+        const int i = lane + 32 * k;
+        o[k] = (short)(o[k] + (i < kTOff ? dcb[i] : (short)dc));
+      }
+      __syncwarp();
+#pragma unroll
+      for (int k = 0; k < NI; k++) { const int i = lane + 32 * k; if (i < kTOff) dcb[i] = (short)dc; }
     }
   }
-  for (int i = 0; i < kFrame; i++) io[i] = out[i];
+#pragma unroll
+  for (int k = 0; k < NI; k++) { const int i = lane + 32 * k; out[i] = o[k]; io[i] = o[k]; }
 }
 
 #include "plc_causal.cuh"
@@ -714,7 +768,7 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
       if (batch_sample_segment(p->syn, kFrame, M + (size_t)fQ * B, p->st.queued, p->w.sego, permQ, a.nq)) return -1;
     }
     if (a.upd) {
-      plc_pre_kernel<<<gs, tb, 0, cs>>>(A);
+      plc_pre_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A);
       plc_burg_kernel<<<(2 * B + 63) / 64, 64, 0, cs>>>(A);
       plc_burg_combine_kernel<<<(B * kBands + 255) / 256, 256, 0, cs>>>(A);
     }
@@ -724,7 +778,7 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
       plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, cs>>>(A, mFG, 0);
       if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B)) return -1;
       if (batch_sample_segment(p->syn, kTOff, M + (size_t)fFgFree * B, nullptr, p->w.sego, permFG, a.nfg)) return -1;
-      plc_fg_mid_kernel<<<gs, tb, 0, cs>>>(A);
+      plc_fg_mid_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A);
       plc_clear_state_kernel<<<B, 128, 0, cs>>>(V.st, M + (size_t)mFG * B, B);
       if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B)) return -1;
       if (batch_sample_segment(p->syn, kFrame, M + (size_t)fFgForced * B, p->w.segf, p->w.sego, permFG, a.nfg)) return -1;
@@ -745,7 +799,7 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
       plc_lost_mid_kernel<<<gs, tb, 0, cs>>>(A);
       if (a.l1 && feature_batch_frame_masked(p->ana, p->st.pcm, M + (size_t)mL1 * B, p->w.encf2, cs)) return -1;
     }
-    plc_finish_kernel<<<gs, tb, 0, cs>>>(A);
+    plc_finish_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A);
     CKP(cudaGetLastError());
     p->frames_done++;
   }
@@ -933,11 +987,11 @@ int plc_run_causal(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_f
       c_feat_kernel<<<g20, 256, 0, cs>>>(A, row(cC));
       if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, row(cC))) return -1;
       if (batch_sample_segment(p->syn, kTOff, row(fC2), nullptr, p->w.sego2, perm + (size_t)4 * B, a.nC)) return -1;
-      c_finish_kernel<<<gs, tb, 0, cs>>>(A, row(cU), row(cC), 0);
+      c_finish_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A, row(cU), row(cC), 0);
     }
     // ---- received frames (lpcnet_plc_update_causal) ----
     if (a.u) {
-      c_pre_kernel<<<gs, tb, 0, cs>>>(A, row(cU));
+      c_pre_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A, row(cU));
       plc_burg_kernel<<<(2 * B + 63) / 64, 64, 0, cs>>>(A);
       plc_burg_combine_kernel<<<(B * kBands + 255) / 256, 256, 0, cs>>>(A);
     }
@@ -970,7 +1024,7 @@ int plc_run_causal(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_f
       c_pcm_store_kernel<<<B, 64, 0, cs>>>(C, row(cNS), nullptr, BUF, p->w.in, kFrame, 0, kFrame);
       c_pcm_shift_kernel<<<B, 128, 0, cs>>>(C, row(cNS), BUF);
     }
-    if (a.u) c_finish_kernel<<<gs, tb, 0, cs>>>(A, row(cU), row(cC), 1);
+    if (a.u) c_finish_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A, row(cU), row(cC), 1);
     CKP(cudaGetLastError());
     p->frames_done++;
   }

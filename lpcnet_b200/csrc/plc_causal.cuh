@@ -131,25 +131,32 @@ __global__ void c_feat_kernel(PlcArgs A, const uint8_t *mask) {
 }
 
 // update streams, causal DC removal (lpcnet_plc.c:192-204): the frame -> w.in, the removed offset -> w.lp, delta
-__global__ void c_pre_kernel(PlcArgs A, const uint8_t *mask) {
-  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(kWpsThreads) c_pre_kernel(PlcArgs A, const uint8_t *mask) {
+  __shared__ short xs[kWpsThreads / 32][kFrame], ls[kWpsThreads / 32][kFrame];
+  int lane, w;
+  const int s = wps_stream(lane, w);                 // one warp per stream, see plc_pre_kernel
   if (s >= A.n_streams || !mask[s]) return;
   const short *x = A.pcm_io + ((size_t)s * A.total_frames + A.frame) * kFrame;
   short *in = A.w.in + (size_t)s * kFrame, *lp = A.w.lp + (size_t)s * kFrame;
-  A.w.delta[s] = 0;
-  if (A.remove_dc) {
-    double dc = A.st.dc_mem[s] + A.st.syn_dc[s];
-    A.w.delta[s] = (int)A.st.syn_dc[s];
-    A.st.syn_dc[s] = 0;
-    for (int i = 0; i < kFrame; i++) {
-      const short l = (short)(int)floor(.5 + dc);
-      dc += DC_CONST * ((double)x[i] - dc);
-      lp[i] = l;
-      in[i] = (short)(x[i] - l);
+  for (int i = lane; i < kFrame; i += 32) xs[w][i] = x[i];
+  __syncwarp();
+  if (lane == 0) {
+    A.w.delta[s] = 0;
+    if (A.remove_dc) {
+      double dc = A.st.dc_mem[s] + A.st.syn_dc[s];
+      A.w.delta[s] = (int)A.st.syn_dc[s];
+      A.st.syn_dc[s] = 0;
+      for (int i = 0; i < kFrame; i++) {
+        ls[w][i] = (short)(int)floor(.5 + dc);
+        dc += DC_CONST * ((double)xs[w][i] - dc);
+      }
+      A.st.dc_mem[s] = dc;
     }
-    A.st.dc_mem[s] = dc;
-  } else {
-    for (int i = 0; i < kFrame; i++) { lp[i] = 0; in[i] = x[i]; }
+  }
+  __syncwarp();
+  for (int i = lane; i < kFrame; i += 32) {
+    const short l = A.remove_dc ? ls[w][i] : (short)0;
+    lp[i] = l; in[i] = (short)(xs[w][i] - l);
   }
 }
 
@@ -170,28 +177,33 @@ __global__ void c_crossfade_kernel(PlcArgs A, const uint8_t *mask) {
 
 // end of a frame: update streams restore the DC offset (lpcnet_plc.c:281-285); conceal streams assemble the two
 // 80-sample segments, hand them to the analysis (w.in) and add the DC estimate (lpcnet_plc.c:332-338)
-__global__ void c_finish_kernel(PlcArgs A, const uint8_t *upd, const uint8_t *con, int stage) {
-  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(kWpsThreads) c_finish_kernel(PlcArgs A, const uint8_t *upd, const uint8_t *con, int stage) {
+  __shared__ short xs[kWpsThreads / 32][kFrame];
+  int lane, w;
+  const int s = wps_stream(lane, w);
   if (s >= A.n_streams) return;
   short *io = A.pcm_io + ((size_t)s * A.total_frames + A.frame) * kFrame;
   short *in = A.w.in + (size_t)s * kFrame;
   if (stage == 0) {                       // conceal: before the analysis
     if (!con[s]) return;
-    for (int i = 0; i < kTOff; i++) { in[i] = A.w.sego[(size_t)s * kTOff + i]; in[kTOff + i] = A.w.sego2[(size_t)s * kTOff + i]; }
-    if (A.remove_dc) {
-      double sd = A.st.syn_dc[s];
-      const int dc = (int)floor(.5 + A.st.dc_mem[s]);
-      for (int i = 0; i < kFrame; i++) {
-        sd += DC_CONST * ((double)in[i] - sd);
-        io[i] = (short)(in[i] + dc);
-      }
-      A.st.syn_dc[s] = sd;
-    } else {
-      for (int i = 0; i < kFrame; i++) io[i] = in[i];
+    for (int i = lane; i < kFrame; i += 32) {
+      const short v = i < kTOff ? A.w.sego[(size_t)s * kTOff + i] : A.w.sego2[(size_t)s * kTOff + i - kTOff];
+      in[i] = v; xs[w][i] = v;
     }
+    __syncwarp();
+    int dc = 0;
+    if (A.remove_dc) {
+      dc = (int)floor(.5 + A.st.dc_mem[s]);
+      if (lane == 0) {
+        double sd = A.st.syn_dc[s];
+        for (int i = 0; i < kFrame; i++) sd += DC_CONST * ((double)xs[w][i] - sd);
+        A.st.syn_dc[s] = sd;
+      }
+    }
+    for (int i = lane; i < kFrame; i += 32) io[i] = (short)(xs[w][i] + dc);
   } else {                                // update: after everything
     if (!upd[s]) return;
     const short *lp = A.w.lp + (size_t)s * kFrame;
-    for (int i = 0; i < kFrame; i++) io[i] = (short)(in[i] + lp[i]);
+    for (int i = lane; i < kFrame; i += 32) io[i] = (short)(in[i] + lp[i]);
   }
 }
