@@ -17,6 +17,7 @@ namespace {
 
 constexpr int kRowsPerBlock = 8;
 constexpr int kFT = 128;  // threads per block of the dense kernels
+constexpr int kPrefetch = 16;   // weight loads in flight per thread in the dense loops
 
 __device__ __forceinline__ int frame_count_at(int fc0, int f) { return min(fc0 + f, 1000); }
 
@@ -64,13 +65,22 @@ __device__ __forceinline__ void dense_rows(const float *__restrict__ W, const fl
     const float b = __ldg(bias + i);
 #pragma unroll
     for (int r = 0; r < R; r++) acc[r] = b;
-#pragma unroll 4
-    for (int j = 0; j < K; j++) {
-      const float w = __ldg(W + (size_t)j * N + i);
+    // The weights come from L2 and a block is alone on its rows, so the loop is bound by the load round trip:
+    // kPrefetch weights are in flight per thread while the fmaf chain keeps the reference's order j = 0..K-1.
+    auto step = [&](float w, int j) {
       const float4 x0 = *reinterpret_cast<const float4 *>(xt + j * R), x1 = *reinterpret_cast<const float4 *>(xt + j * R + 4);
       acc[0] = fmaf(w, x0.x, acc[0]); acc[1] = fmaf(w, x0.y, acc[1]); acc[2] = fmaf(w, x0.z, acc[2]); acc[3] = fmaf(w, x0.w, acc[3]);
       acc[4] = fmaf(w, x1.x, acc[4]); acc[5] = fmaf(w, x1.y, acc[5]); acc[6] = fmaf(w, x1.z, acc[6]); acc[7] = fmaf(w, x1.w, acc[7]);
+    };
+    int j = 0;
+    for (; j + kPrefetch <= K; j += kPrefetch) {
+      float w[kPrefetch];
+#pragma unroll
+      for (int u = 0; u < kPrefetch; u++) w[u] = __ldg(W + (size_t)(j + u) * N + i);
+#pragma unroll
+      for (int u = 0; u < kPrefetch; u++) step(w[u], j + u);
     }
+    for (; j < K; j++) step(__ldg(W + (size_t)j * N + i), j);
 #pragma unroll
     for (int r = 0; r < R; r++) {
       float v = do_tanh ? tanh_ref(acc[r], rcp) : acc[r];
@@ -167,13 +177,22 @@ __global__ void __launch_bounds__(kFT) cond_kernel(FrameArgs A) {
 #pragma unroll
       for (int r = 0; r < R; r++) acc[c][r] = b;
     }
-#pragma unroll 4
-    for (int j = 0; j < kC; j++) {
-      const float w0 = __ldg(Wc[0] + (size_t)j * Nc[0]), w1 = __ldg(Wc[1] + (size_t)j * Nc[1]);
-      const float4 x0 = *reinterpret_cast<const float4 *>(&yt[j][0]), x1 = *reinterpret_cast<const float4 *>(&yt[j][4]);
-      const float xr[R] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+    static_assert(kC % kPrefetch == 0, "prefetch depth must divide the layer width");
+    for (int j0 = 0; j0 < kC; j0 += kPrefetch) {
+      float w0[kPrefetch], w1[kPrefetch];
 #pragma unroll
-      for (int r = 0; r < R; r++) { acc[0][r] = fmaf(w0, xr[r], acc[0][r]); acc[1][r] = fmaf(w1, xr[r], acc[1][r]); }
+      for (int u = 0; u < kPrefetch; u++) {
+        w0[u] = __ldg(Wc[0] + (size_t)(j0 + u) * Nc[0]);
+        w1[u] = __ldg(Wc[1] + (size_t)(j0 + u) * Nc[1]);
+      }
+#pragma unroll
+      for (int u = 0; u < kPrefetch; u++) {
+        const int j = j0 + u;
+        const float4 x0 = *reinterpret_cast<const float4 *>(&yt[j][0]), x1 = *reinterpret_cast<const float4 *>(&yt[j][4]);
+        const float xr[R] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+#pragma unroll
+        for (int r = 0; r < R; r++) { acc[0][r] = fmaf(w0[u], xr[r], acc[0][r]); acc[1][r] = fmaf(w1[u], xr[r], acc[1][r]); }
+      }
     }
 #pragma unroll
     for (int c = 0; c < 2; c++) {
