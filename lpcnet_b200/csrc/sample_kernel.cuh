@@ -352,7 +352,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
       const size_t out_base = (size_t)(A.frame0 + f) * A.spf;
       if (!any_act) {
         // warm-up frames: N zeros, nothing else moves (src/lpcnet.c:239-243)
-        if (!A.forced || true) {
+        {
           for (int i = tid; i < NS * A.spf; i += kThreads) {
             const int s = i / A.spf, k = i % A.spf;
             if (stream0 + s < Bend) {
