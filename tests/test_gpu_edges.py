@@ -314,3 +314,79 @@ def test_dred_decoder_edges(eng):
     dec.close()
     with pytest.raises(eng.LPCNetError):
         eng.DredDecoder(blob.write_blob(blob.random_model()))        # no dred_rdovae_dec_* arrays
+
+
+def test_states_on_different_threads_do_not_interfere(eng, model_blob, plc_blob, codebooks, orc_model):
+    """SURVEY 8(b) threading: the reference is re-entrant per state.  Four host threads, each with its own handles
+    (batches of different sizes and tiles, a single-stream LPCNetState, an encoder batch, a PLC batch), call the
+    library at the same time (ctypes drops the GIL in the calls); every thread's output equals the one it produces
+    alone."""
+    import threading
+
+    F = 5
+    def work_synth(n, tile, reps, out):
+        feats = np.stack([blob.synthetic_features(F, (3 * n + s) % 16) for s in range(n)])
+        bt = eng.Batch(model_blob, n)
+        if tile:
+            bt.set_tile(tile)
+        for _ in range(reps):
+            bt.reset()
+            for s in range(n):
+                bt.set_seed(s, blob.stream_seed(s))
+            out.append(bt.synthesize(feats)[0].copy())
+        bt.close()
+
+    def work_single(reps, out):
+        f = blob.synthetic_features(F, 2)
+        syn = eng.Synth(model_blob)
+        for _ in range(reps):
+            syn.reset()
+            out.append(np.concatenate([syn.synthesize(f[k]) for k in range(F)]))
+        syn.close()
+
+    def work_encode(reps, out):
+        x = np.stack([blob.synthetic_pcm(8, 70 + s) for s in range(40)])
+        fb = eng.FeatureBatch(40)
+        fb.set_codebooks(codebooks)
+        for _ in range(reps):
+            fb.reset()
+            out.append(fb.encode(x).copy())
+        fb.close()
+
+    def work_plc(reps, out):
+        x = np.stack([blob.synthetic_pcm(10, 80 + s) for s in range(12)])
+        lost = np.stack([blob.synthetic_loss_pattern(10, 30 + s, 0.6, 0.25) for s in range(12)])
+        for _ in range(reps):
+            pb = eng.PLCBatch(plc_blob, 12, 4)
+            for s in range(12):
+                pb.set_seed(s, blob.stream_seed(s))
+            out.append(pb.process(x, lost).copy())
+            pb.close()
+
+    jobs = [(work_synth, (19, 16, 4)), (work_synth, (150, 0, 3)), (work_single, (3,)), (work_encode, (6,)), (work_plc, (3,))]
+    alone = []
+    for fn, args in jobs:                       # each job on its own first
+        out = []
+        fn(*args[:-1], 1, out) if len(args) > 1 else fn(1, out)
+        alone.append(out[0])
+    results = [[] for _ in jobs]
+    errors = []
+
+    def guarded(fn, args, out):
+        try:
+            fn(*args, out)
+        except Exception as e:                  # surfaced below: an exception in a thread must fail the test
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=guarded, args=(fn, args, results[k])) for k, (fn, args) in enumerate(jobs)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    for k, (fn, args) in enumerate(jobs):
+        assert len(results[k]) == args[-1]
+        for r in results[k]:
+            assert np.array_equal(r, alone[k]), (k, fn.__name__)
+    # and the single-stream thread is what the oracle gives
+    assert np.array_equal(alone[2], orcpy.OrcStream(orc_model).run(blob.synthetic_features(F, 2))[0])
