@@ -387,7 +387,8 @@ def run_gpu(args):
             "x_realtime": value / 16000.0,
             "step_latency_us": kernel_s * 1e6 / (active_frames * FRAME * args.steps / max(1, n_sample)),
             "step_latency_us_p50_p99": step_latency_percentiles(launch_ms, launch_steps),
-            "config": {"workload": f"batched -synthesis, {B} streams x {args.seconds:g} s per GPU (BASELINE configs[1])",
+            "config": {"workload": f"batched -synthesis, {B} streams x {args.seconds:g} s per GPU "
+                                   + ("(BASELINE configs[1])" if B == 1024 else "(BASELINE configs[4]: throughput sweep point)"),
                        "streams_per_gpu": B, "seconds": args.seconds, "tile_streams_per_cta": bt.tile,
                        "model": "random-init, N=384 NB=16 density (0.05,0.05,0.2), reference blob layout",
                        "parallelism": f"streams sharded over {world} GPU(s), no collective",
