@@ -61,16 +61,17 @@ __device__ __forceinline__ void dense_rows(const float *__restrict__ W, const fl
                                            const uint32_t *rcp, int tid, int nthreads, const bool *zero_row) {
   static_assert(R == 8, "two float4 per input");
   for (int i = tid; i < N; i += nthreads) {
-    float acc[R];
+    float2 acc2[R / 2];                       // rows (2k, 2k+1): packed fmaf, each half the same IEEE operation
     const float b = __ldg(bias + i);
 #pragma unroll
-    for (int r = 0; r < R; r++) acc[r] = b;
+    for (int r = 0; r < R / 2; r++) acc2[r] = make_float2(b, b);
     // The weights come from L2 and a block is alone on its rows, so the loop is bound by the load round trip:
     // kPrefetch weights are in flight per thread while the fmaf chain keeps the reference's order j = 0..K-1.
     auto step = [&](float w, int j) {
       const float4 x0 = *reinterpret_cast<const float4 *>(xt + j * R), x1 = *reinterpret_cast<const float4 *>(xt + j * R + 4);
-      acc[0] = fmaf(w, x0.x, acc[0]); acc[1] = fmaf(w, x0.y, acc[1]); acc[2] = fmaf(w, x0.z, acc[2]); acc[3] = fmaf(w, x0.w, acc[3]);
-      acc[4] = fmaf(w, x1.x, acc[4]); acc[5] = fmaf(w, x1.y, acc[5]); acc[6] = fmaf(w, x1.z, acc[6]); acc[7] = fmaf(w, x1.w, acc[7]);
+      const float2 w2 = make_float2(w, w);
+      acc2[0] = f2_fma(w2, make_float2(x0.x, x0.y), acc2[0]); acc2[1] = f2_fma(w2, make_float2(x0.z, x0.w), acc2[1]);
+      acc2[2] = f2_fma(w2, make_float2(x1.x, x1.y), acc2[2]); acc2[3] = f2_fma(w2, make_float2(x1.z, x1.w), acc2[3]);
     };
     int j = 0;
     for (; j + kPrefetch <= K; j += kPrefetch) {
@@ -81,6 +82,7 @@ __device__ __forceinline__ void dense_rows(const float *__restrict__ W, const fl
       for (int u = 0; u < kPrefetch; u++) step(w[u], j + u);
     }
     for (; j < K; j++) step(__ldg(W + (size_t)j * N + i), j);
+    const float acc[R] = {acc2[0].x, acc2[0].y, acc2[1].x, acc2[1].y, acc2[2].x, acc2[2].y, acc2[3].x, acc2[3].y};
 #pragma unroll
     for (int r = 0; r < R; r++) {
       float v = do_tanh ? tanh_ref(acc[r], rcp) : acc[r];
@@ -166,7 +168,7 @@ __global__ void __launch_bounds__(kFT) cond_kernel(FrameArgs A) {
   constexpr int NH = kRowsA + kRowsB;
   for (int i0 = tid; i0 < NH; i0 += 2 * kFT) {
     const int i1 = i0 + kFT < NH ? i0 + kFT : i0;   // the last pass may have one column only (computed twice, stored once)
-    const float *Wc[2]; int colc[2], Nc[2]; float acc[2][R];
+    const float *Wc[2]; int colc[2], Nc[2]; float2 acc2[2][R / 2];
 #pragma unroll
     for (int c = 0; c < 2; c++) {
       const int i = c ? i1 : i0;
@@ -175,7 +177,7 @@ __global__ void __launch_bounds__(kFT) cond_kernel(FrameArgs A) {
       Wc[c] = (isA ? A.m.a_feat_w : A.m.b_feat_w) + colc[c];
       const float b = __ldg((isA ? A.m.a_feat_b : A.m.b_feat_b) + colc[c]);
 #pragma unroll
-      for (int r = 0; r < R; r++) acc[c][r] = b;
+      for (int r = 0; r < R / 2; r++) acc2[c][r] = make_float2(b, b);
     }
     static_assert(kC % kPrefetch == 0, "prefetch depth must divide the layer width");
     for (int j0 = 0; j0 < kC; j0 += kPrefetch) {
@@ -189,9 +191,10 @@ __global__ void __launch_bounds__(kFT) cond_kernel(FrameArgs A) {
       for (int u = 0; u < kPrefetch; u++) {
         const int j = j0 + u;
         const float4 x0 = *reinterpret_cast<const float4 *>(&yt[j][0]), x1 = *reinterpret_cast<const float4 *>(&yt[j][4]);
-        const float xr[R] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+        const float2 xp[R / 2] = {make_float2(x0.x, x0.y), make_float2(x0.z, x0.w), make_float2(x1.x, x1.y), make_float2(x1.z, x1.w)};
+        const float2 wa = make_float2(w0[u], w0[u]), wb = make_float2(w1[u], w1[u]);
 #pragma unroll
-        for (int r = 0; r < R; r++) { acc[0][r] = fmaf(w0[u], xr[r], acc[0][r]); acc[1][r] = fmaf(w1[u], xr[r], acc[1][r]); }
+        for (int r = 0; r < R / 2; r++) { acc2[0][r] = f2_fma(wa, xp[r], acc2[0][r]); acc2[1][r] = f2_fma(wb, xp[r], acc2[1][r]); }
       }
     }
 #pragma unroll
@@ -206,7 +209,7 @@ __global__ void __launch_bounds__(kFT) cond_kernel(FrameArgs A) {
         if (A.stream_mask && !A.stream_mask[row_s[r]]) continue;
         float *dst = isA ? A.fb.cond_a + ((size_t)row_f[r] * B + row_s[r]) * kRowsAP
                          : A.fb.cond_b + ((size_t)row_f[r] * B + row_s[r]) * kRowsB;
-        dst[isA ? gru_a_col_index(colc[c]) : colc[c]] = acc[c][r];   // GRU-A conditioning in the sample kernel's gather order
+        dst[isA ? gru_a_col_index(colc[c]) : colc[c]] = (r & 1) ? acc2[c][r >> 1].y : acc2[c][r >> 1].x;   // GRU-A conditioning in the sample kernel's gather order
       }
     }
   }
