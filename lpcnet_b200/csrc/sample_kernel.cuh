@@ -47,6 +47,33 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
   SmemLayout L;
   unsigned o = 0;
   auto take = [&](unsigned bytes) { unsigned r = o; o += (bytes + 15u) & ~15u; return r; };
+  if (NS == 8) {
+    // 8 streams per CTA: the arrays whose size depends on the tile shape only come first, so their offsets fold to
+    // constants (immediate operands instead of live registers or re-computed sums); the model-sized weight and
+    // offset lists follow: 4.17 -> 4.13 us per step.  The larger tiles measured 2 % slower in this order
+    // (register allocation) and keep the lists in front.
+    L.offF = take(kN / 8 * 32 * 4); L.csA = take((kN / 8 + 1) * 4);
+    L.csBi = take((kRGroupsB * kPartsB + 1) * 4);
+    L.csBr = take((kRGroupsB + 1) * 4);
+    L.sdA = take(kRowsA * 8); L.subB = take(2 * kRowsB * 4);
+    L.rcp = take(2048 * 4); L.u2l = take(256 * 4); L.logit = take(256 * 4);
+    L.xa = take(2 * NS * kXaStride * 4);
+    L.xb = take(NS * kXbStride * 4);
+    L.bst = take(NS * 20 * 4);
+    L.condb = take(NS * kRowsB * 4);
+    L.part = take(MT * (kPartsB + 1) * kRGroupsB * 128 * 4);
+    L.usig = take(NS * 4); L.upred = take(NS * 4); L.lexc = take(NS * 4);
+    L.deemph = take(NS * 4); L.rng = take(4 * NS * 4); L.act = take(NS * 4); L.ix = take(NS * 4);
+    L.tst = 0;
+    L.accx = take(12 * 3 * 32 * 8);   // GRU-A sums computed ahead for the sampler warps' unit groups
+    L.fcb = take(4 * 256 * 4);
+    L.fcw = take(256 * kFcStride * 4);
+    L.wA = take(chA * 256); L.posA = take(chA * 16);
+    L.wBi = take(chBi * 256); L.posBi = take(chBi * 16);
+    L.wBr = take(chBr * 256); L.posBr = take(chBr * 16);
+    L.total = o;
+    return L;
+  }
   L.wA = take(chA * 256); L.posA = take(chA * 16); L.offF = take(kN / 8 * 32 * 4); L.csA = take((kN / 8 + 1) * 4);
   L.wBi = take(chBi * 256); L.posBi = take(chBi * 16); L.csBi = take((kRGroupsB * kPartsB + 1) * 4);
   L.wBr = take(chBr * 256); L.posBr = take(chBr * 16); L.csBr = take((kRGroupsB + 1) * 4);
