@@ -81,6 +81,8 @@ struct LPCNetBatch {
   FrameBuffers fb2;               // ... and of the next one: the frame network of chunk k+1 runs on its own stream
   void *fb2_alloc = nullptr;      //     beside the sample kernel of chunk k (it depends only on frame-rate state)
   cudaStream_t fstream = nullptr;
+  cudaStream_t cstream = nullptr;                       // device->host copies of finished chunks (pinned destination)
+  cudaEvent_t ev_chunk = nullptr, ev_copied = nullptr;
   cudaEvent_t ev_entry = nullptr, ev_frames[2] = {nullptr, nullptr}, ev_samples[2] = {nullptr, nullptr};
   cudaStream_t own_stream = nullptr;
   cudaStream_t stream = nullptr;
@@ -230,8 +232,10 @@ int run_frames(LPCNetBatch *b, const float *d_features, int stride, int f0, int 
   return run_frames(b, d_features, stride, f0, F, total_frames, b->fb, b->stream);
 }
 
+// h_pcm (optional, pinned host memory [B][n_frames * spf]): every chunk's samples are copied out on a third stream
+// as soon as its sample kernel is done, beside the next chunk's kernel; the caller's stream ends after the last copy.
 int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_frames, int spf, short *d_pcm,
-                 const short *d_forced, LPCNetB200Trace *d_trace, float *d_logits) {
+                 const short *d_forced, LPCNetB200Trace *d_trace, float *d_logits, short *h_pcm = nullptr) {
   if (!b) return fail("null batch");
   if (n_frames <= 0) return 0;
   if (spf <= 0 || spf > kFrame) return fail("samples_per_frame must be 1..160");
@@ -288,6 +292,22 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
     if (b->profiling) { CK(cudaEventRecord(e1, b->stream)); b->ev_sample.emplace_back(e0, e1); b->ev_sample_steps.push_back(F * spf); }
     if (pipe) CK(cudaEventRecord(b->ev_samples[buf], b->stream));
     b->launches += nl;
+    if (h_pcm) {
+      if (!b->cstream) {
+        CK(cudaStreamCreateWithFlags(&b->cstream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&b->ev_chunk, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&b->ev_copied, cudaEventDisableTiming));
+      }
+      const size_t row = (size_t)n_frames * spf * sizeof(short), off = (size_t)f0 * spf;
+      CK(cudaEventRecord(b->ev_chunk, b->stream));
+      CK(cudaStreamWaitEvent(b->cstream, b->ev_chunk, 0));
+      CK(cudaMemcpy2DAsync(h_pcm + off, row, d_pcm + off, row, (size_t)F * spf * sizeof(short), b->n_streams,
+                           cudaMemcpyDeviceToHost, b->cstream));
+    }
+  }
+  if (h_pcm) {
+    CK(cudaEventRecord(b->ev_copied, b->cstream));
+    CK(cudaStreamWaitEvent(b->stream, b->ev_copied, 0));
   }
   return 0;
 }
@@ -466,6 +486,7 @@ void lpcnet_batch_destroy(LPCNetBatch *b) {
   }
   void *ptrs[] = {b->st_alloc, b->fb_alloc, b->fb2_alloc, b->d_feat, b->d_pcm, b->d_forced, b->d_trace, b->d_logits, b->d_packets, b->d_compact};
   for (void *p : ptrs) if (p) cudaFree(p);
+  if (b->cstream) { cudaStreamSynchronize(b->cstream); cudaStreamDestroy(b->cstream); cudaEventDestroy(b->ev_chunk); cudaEventDestroy(b->ev_copied); }
   if (b->own_stream) cudaStreamDestroy(b->own_stream);
   delete b;
 }
@@ -621,13 +642,21 @@ int lpcnet_batch_synthesize(LPCNetBatch *b, const float *features, int stride, i
     CK(cudaMemcpyAsync(b->d_forced, forced, pbytes, cudaMemcpyHostToDevice, b->stream));
   }
   if (trace && grow(&b->d_trace, &b->d_trace_bytes, B * T * sizeof(LPCNetB200Trace))) return -1;
+  // a pinned destination takes the finished chunks while the next ones are computed (pageable memory would make the
+  // "asynchronous" copy block the host inside the chunk loop)
+  bool pinned = false;
+  {
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, pcm) == cudaSuccess) pinned = at.type == cudaMemoryTypeHost;
+    else cudaGetLastError();
+  }
   if (logits && grow(&b->d_logits, &b->d_logits_bytes, B * T * 256 * 4)) return -1;
   if (synth_device(b, static_cast<const float *>(b->d_feat), stride, n_frames, kFrame, static_cast<short *>(b->d_pcm),
                    forced ? static_cast<const short *>(b->d_forced) : nullptr,
                    trace ? static_cast<LPCNetB200Trace *>(b->d_trace) : nullptr,
-                   logits ? static_cast<float *>(b->d_logits) : nullptr))
+                   logits ? static_cast<float *>(b->d_logits) : nullptr, pinned ? pcm : nullptr))
     return -1;
-  CK(cudaMemcpyAsync(pcm, b->d_pcm, pbytes, cudaMemcpyDeviceToHost, b->stream));
+  if (!pinned) CK(cudaMemcpyAsync(pcm, b->d_pcm, pbytes, cudaMemcpyDeviceToHost, b->stream));
   if (trace) CK(cudaMemcpyAsync(trace, b->d_trace, B * T * sizeof(LPCNetB200Trace), cudaMemcpyDeviceToHost, b->stream));
   if (logits) CK(cudaMemcpyAsync(logits, b->d_logits, B * T * 256 * 4, cudaMemcpyDeviceToHost, b->stream));
   CK(cudaStreamSynchronize(b->stream));

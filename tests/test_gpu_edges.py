@@ -390,3 +390,29 @@ def test_states_on_different_threads_do_not_interfere(eng, model_blob, plc_blob,
             assert np.array_equal(r, alone[k]), (k, fn.__name__)
     # and the single-stream thread is what the oracle gives
     assert np.array_equal(alone[2], orcpy.OrcStream(orc_model).run(blob.synthetic_features(F, 2))[0])
+
+
+def test_pinned_destination_takes_chunks_as_they_finish(eng, model_blob):
+    """lpcnet_batch_synthesize into pinned host memory copies every 32-frame chunk out on its own stream beside the
+    next chunk's kernel; into pageable memory it copies once at the end.  Same samples either way."""
+    import torch
+    B, F = 21, 70                                  # three chunks, a ragged last tile
+    feats = np.stack([blob.synthetic_features(F, s % 16) for s in range(B)])
+    outs = []
+    for pinned in (False, True):
+        bt = eng.Batch(model_blob, B)
+        for s in range(B):
+            bt.set_seed(s, blob.stream_seed(s))
+        buf = None
+        if pinned:
+            hold = torch.empty((B, F * 160), dtype=torch.int16, pin_memory=True)
+            hold.fill_(-1)
+            buf = hold.numpy()
+        pcm, _, _ = bt.synthesize(feats, pcm_out=buf)
+        outs.append(np.array(pcm))
+        # a second call continues the streams: the copies of the first are complete and ordered
+        pcm2, _, _ = bt.synthesize(feats[:, :3], pcm_out=buf[:, :480].copy() if pinned else None)
+        outs.append(np.array(pcm2))
+        bt.close()
+    assert np.array_equal(outs[0], outs[2]) and np.array_equal(outs[1], outs[3])
+    assert np.abs(outs[0]).max() > 0
