@@ -232,6 +232,13 @@ int run_frames(LPCNetBatch *b, const float *d_features, int stride, int f0, int 
   return run_frames(b, d_features, stride, f0, F, total_frames, b->fb, b->stream);
 }
 
+bool is_pinned_host(const void *p) {
+  cudaPointerAttributes at{};
+  if (p && cudaPointerGetAttributes(&at, p) == cudaSuccess) return at.type == cudaMemoryTypeHost;
+  cudaGetLastError();
+  return false;
+}
+
 // h_pcm (optional, pinned host memory [B][n_frames * spf]): every chunk's samples are copied out on a third stream
 // as soon as its sample kernel is done, beside the next chunk's kernel; the caller's stream ends after the last copy.
 int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_frames, int spf, short *d_pcm,
@@ -644,12 +651,7 @@ int lpcnet_batch_synthesize(LPCNetBatch *b, const float *features, int stride, i
   if (trace && grow(&b->d_trace, &b->d_trace_bytes, B * T * sizeof(LPCNetB200Trace))) return -1;
   // a pinned destination takes the finished chunks while the next ones are computed (pageable memory would make the
   // "asynchronous" copy block the host inside the chunk loop)
-  bool pinned = false;
-  {
-    cudaPointerAttributes at{};
-    if (cudaPointerGetAttributes(&at, pcm) == cudaSuccess) pinned = at.type == cudaMemoryTypeHost;
-    else cudaGetLastError();
-  }
+  const bool pinned = is_pinned_host(pcm);
   if (logits && grow(&b->d_logits, &b->d_logits_bytes, B * T * 256 * 4)) return -1;
   if (synth_device(b, static_cast<const float *>(b->d_feat), stride, n_frames, kFrame, static_cast<short *>(b->d_pcm),
                    forced ? static_cast<const short *>(b->d_forced) : nullptr,
@@ -721,10 +723,11 @@ int lpcnet_batch_decode(LPCNetBatch *b, const unsigned char *packets, int n_pack
   int nl = 0;
   CK(launch_decode_packets(da, b->stream, &nl));
   b->launches += nl;
+  const bool pinned = is_pinned_host(pcm);     // finished chunks leave beside the next chunk's kernel
   if (synth_device(b, static_cast<const float *>(b->d_feat), 36, n_frames, kFrame, static_cast<short *>(b->d_pcm), nullptr,
-                   nullptr, nullptr))
+                   nullptr, nullptr, pinned ? pcm : nullptr))
     return -1;
-  if (pcm) CK(cudaMemcpyAsync(pcm, b->d_pcm, pbytes, cudaMemcpyDeviceToHost, b->stream));
+  if (pcm && !pinned) CK(cudaMemcpyAsync(pcm, b->d_pcm, pbytes, cudaMemcpyDeviceToHost, b->stream));
   if (features_out) CK(cudaMemcpyAsync(features_out, b->d_feat, fbytes, cudaMemcpyDeviceToHost, b->stream));
   CK(cudaStreamSynchronize(b->stream));
   return 0;

@@ -337,12 +337,14 @@ class Batch:
         cb = np.ascontiguousarray(codebooks, np.float32).reshape(-1)
         _check(self.L.lpcnet_batch_set_codebooks(self.h, _p(cb), cb.size), "lpcnet_batch_set_codebooks")
 
-    def decode(self, packets, want_features=False):
-        """packets: [n_streams][n_packets][8] uint8.  Returns (pcm [n][n_packets*640], features)."""
+    def decode(self, packets, want_features=False, pcm_out=None):
+        """packets: [n_streams][n_packets][8] uint8.  Returns (pcm [n][n_packets*640], features).  pcm_out: a
+        caller's buffer of that shape (pinned memory receives the chunks while the next ones are computed)."""
         pk = np.ascontiguousarray(packets, np.uint8)
         assert pk.ndim == 3 and pk.shape[0] == self.n_streams and pk.shape[2] == 8
         n_packets = pk.shape[1]
-        pcm = np.zeros((self.n_streams, n_packets * 640), np.int16)
+        pcm = pcm_out if pcm_out is not None else np.zeros((self.n_streams, n_packets * 640), np.int16)
+        assert pcm.shape == (self.n_streams, n_packets * 640) and pcm.dtype == np.int16 and pcm.flags.c_contiguous
         feats = np.zeros((self.n_streams, n_packets * 4, 36), np.float32) if want_features else None
         _check(self.L.lpcnet_batch_decode(self.h, _p(pk), n_packets, _p(pcm), _p(feats)), "lpcnet_batch_decode")
         return pcm, feats

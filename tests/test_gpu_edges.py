@@ -416,3 +416,18 @@ def test_pinned_destination_takes_chunks_as_they_finish(eng, model_blob):
         bt.close()
     assert np.array_equal(outs[0], outs[2]) and np.array_equal(outs[1], outs[3])
     assert np.abs(outs[0]).max() > 0
+
+
+def test_decode_into_pinned_memory(eng, model_blob, codebooks):
+    import torch
+    rng = np.random.default_rng(12)
+    packets = rng.integers(0, 256, size=(9, 20, 8), dtype=np.uint8)      # 80 frames: three chunks
+    outs = []
+    for pinned in (False, True):
+        bt = eng.Batch(model_blob, 9)
+        bt.set_codebooks(codebooks)
+        hold = torch.empty((9, 20 * 640), dtype=torch.int16, pin_memory=True) if pinned else None
+        pcm, _ = bt.decode(packets, pcm_out=hold.numpy() if pinned else None)
+        outs.append(np.array(pcm))
+        bt.close()
+    assert np.array_equal(outs[0], outs[1]) and np.abs(outs[0]).max() > 0
