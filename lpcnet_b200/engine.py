@@ -622,6 +622,14 @@ class PLCBatch:
         _check(self.L.lpcnet_plc_batch_process(self.h, _p(lost), _p(out), n_frames), "lpcnet_plc_batch_process")
         return out
 
+    def process_inplace(self, pcm, lost):
+        """lpcnet_plc_batch_process as the C-ABI has it: pcm int16 [n_streams][n_frames*160] is read and overwritten
+        (lost frames are not read).  A pinned buffer avoids the staging copies of pageable memory."""
+        lost = np.ascontiguousarray(lost, np.uint8)
+        assert pcm.dtype == np.int16 and pcm.flags.c_contiguous and pcm.shape == (self.n_streams, lost.shape[1] * FRAME_SIZE)
+        _check(self.L.lpcnet_plc_batch_process(self.h, _p(lost), _p(pcm), lost.shape[1]), "lpcnet_plc_batch_process")
+        return pcm
+
 
 class PLC:
     """lpcnet_plc_create + lpcnet_plc_load_model + lpcnet_plc_update / lpcnet_plc_conceal (include/lpcnet.h:190-215)."""

@@ -431,3 +431,26 @@ def test_decode_into_pinned_memory(eng, model_blob, codebooks):
         outs.append(np.array(pcm))
         bt.close()
     assert np.array_equal(outs[0], outs[1]) and np.abs(outs[0]).max() > 0
+
+
+@pytest.mark.parametrize("opt", [5, 4])
+def test_plc_in_place_ignores_the_content_of_lost_frames(eng, plc_blob, opt):
+    """lpcnet_plc_batch_process works in place like lpcnet_plc_update / _conceal; what the buffer holds in a lost
+    frame is never read (the reference's lpcnet_plc_conceal only writes)."""
+    B, F = 4, 12
+    x = np.stack([blob.synthetic_pcm(F, 90 + s) for s in range(B)])
+    lost = np.stack([blob.synthetic_loss_pattern(F, 40 + s, 0.6, 0.25) for s in range(B)])
+    assert lost.sum() > 0
+    outs = []
+    for junk in (False, True):
+        pb = eng.PLCBatch(plc_blob, B, opt)
+        for s in range(B):
+            pb.set_seed(s, blob.stream_seed(s))
+        if junk:
+            buf = x.copy()
+            buf.reshape(B, F, 160)[lost != 0] = 12345
+            outs.append(pb.process_inplace(buf, lost).copy())
+        else:
+            outs.append(pb.process(x, lost))
+        pb.close()
+    assert np.array_equal(outs[0], outs[1])
