@@ -274,10 +274,45 @@ def plc(R):
     np.savez_compressed(os.path.join(OUT, "plc.npz"), **d)
 
 
+BENCH_STEPS = 26
+BENCH_STREAMS = [0, 7, 8, 63, 64, 511, 1016, 1023]   # first / last tile of bench.py's 1024 streams, first / last slot
+
+
+def bench_hashes(R):
+    """bench.py's workload (BASELINE configs[1]: stream s = feature track s % 64, seed "LPCNet<s>", 1000 frames)
+    through the UNMODIFIED reference for a few fixed streams: SHA-256 of every second of PCM (little-endian int16),
+    so that bench.py and tests/test_gpu_long.py can check the timed kernel's output without the reference at hand
+    and name the first second that differs ("streams": the first call on fresh states); "steps": SHA-256 of the whole
+    PCM of call k = 0..BENCH_STEPS-1 on the same states, i.e. of every warm-up and timed step of a bench run."""
+    import json
+    from concurrent.futures import ThreadPoolExecutor
+    b = blob.write_blob(blob.random_model())
+    F = 1000
+
+    def one(s):
+        rs = refpy.RefStream(R, b, blob.stream_seed(s))
+        f = blob.synthetic_features(F, s % 64)
+        first, steps = None, []
+        for k in range(BENCH_STEPS):          # bench.py calls the engine again and again on the same states
+            pcm = rs.run(f)[0]
+            if k == 0:
+                first = [hashlib.sha256(pcm[j * 16000:(j + 1) * 16000].astype("<i2").tobytes()).hexdigest() for j in range(F // 100)]
+            steps.append(hashlib.sha256(pcm.astype("<i2").tobytes()).hexdigest())
+        return first, steps
+
+    with ThreadPoolExecutor(8) as ex:
+        hs = list(ex.map(one, BENCH_STREAMS))
+    d = {"blob_sha256": hashlib.sha256(b).hexdigest(), "frames": F, "block_samples": 16000,
+         "source": "oracle/_ref/libref_d2.so (the unmodified reference, -O2 -mavx2 -mfma -ffp-contract=off)",
+         "streams": {str(s): h[0] for s, h in zip(BENCH_STREAMS, hs)},
+         "steps": {str(s): h[1] for s, h in zip(BENCH_STREAMS, hs)}}
+    json.dump(d, open(os.path.join(OUT, "bench_pcm_hashes.json"), "w"), indent=1)
+
+
 if __name__ == "__main__":
     R = refpy.RefLib(2)
-    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc", "encode", "plc_causal", "dred", "plc_edges"]
+    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc", "encode", "plc_causal", "dred", "plc_edges", "bench"]
     for name in which:
-        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc, "encode": encode, "plc_causal": plc_causal, "dred": dred, "plc_edges": plc_edges}[name](R)
+        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc, "encode": encode, "plc_causal": plc_causal, "dred": dred, "plc_edges": plc_edges, "bench": bench_hashes}[name](R)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))

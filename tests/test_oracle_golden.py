@@ -131,3 +131,17 @@ def test_live_against_reference(orclib, model_blob):
         a = refpy.RefStream(R, model_blob, blob.stream_seed(s)).run(f, trace=True, logits=True)
         b = orcpy.OrcStream(om, blob.stream_seed(s)).run(f, trace=True, logits=True)
         assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(bits(a[2]), bits(b[2]))
+
+
+def test_oracle_against_reference_over_10s(orc_model, model_blob):
+    """bench.py's workload over its full length (1000 frames): the oracle's PCM hashes to what the unmodified
+    reference produced (tests/golden/bench_pcm_hashes.json, written by make_golden.py bench)."""
+    import json
+    import os
+    g = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "bench_pcm_hashes.json")))
+    assert g["blob_sha256"] == hashlib.sha256(model_blob).hexdigest()
+    for s in (7, 1016):
+        pcm = orcpy.OrcStream(orc_model, blob.stream_seed(s)).run(blob.synthetic_features(g["frames"], s % 64))[0]
+        n = g["block_samples"]
+        got = [hashlib.sha256(pcm[k * n:(k + 1) * n].astype("<i2").tobytes()).hexdigest() for k in range(len(pcm) // n)]
+        assert got == g["streams"][str(s)], s
