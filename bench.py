@@ -19,6 +19,7 @@ the unmodified sources built with the README's -Ofast flags) on all host cores.
 from __future__ import annotations
 
 import argparse
+import hashlib
 import json
 import os
 import shutil
@@ -48,75 +49,39 @@ def peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "src": "fallback"}
 
 
-# ------------------------------------------------------------------------------------------
-# CPU reference arm: the reference's own lpcnet_demo -synthesis, one process per host core
-# ------------------------------------------------------------------------------------------
-class CpuReference:
-    def __init__(self, blob_bytes: bytes, n_frames: int):
-        from lpcnet_b200 import blob
-        self.dir = tempfile.mkdtemp(prefix="lpcnet_ref_")
-        with open(os.path.join(self.dir, "weights_blob.bin"), "wb") as f:
-            f.write(blob_bytes)       # lpcnet_demo (USE_WEIGHTS_FILE) reads ./weights_blob.bin (lpcnet_demo.c:113)
-        self.cores = sorted(os.sched_getaffinity(0))
-        self.n_frames = n_frames
-        for i, _ in enumerate(self.cores):
-            blob.synthetic_features(n_frames, i).tofile(os.path.join(self.dir, f"feat{i}.f32"))
-        self.binary, self.kind = self._pick_binary()
-        self.blob_bytes = blob_bytes
-
-    def _pick_binary(self):
-        for name in ("lpcnet_demo_fast_native", "lpcnet_demo_fast_v3"):
-            p = os.path.join(ROOT, "oracle", "_ref", name)
-            if os.path.exists(p):
-                # -march=native was resolved on the build container; fall back if this host lacks the ISA
-                r = subprocess.run([p, "-synthesis", "feat0.f32", "probe.pcm"], cwd=self.dir,
-                                   stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
-                if r.returncode == 0 and os.path.getsize(os.path.join(self.dir, "probe.pcm")) == self.n_frames * FRAME * 2:
-                    return p, "reference"
-        return None, "port"
-
-    def run_once(self) -> float:
-        """All cores at once, one 10 s stream each.  Returns aggregate samples/s."""
-        n = len(self.cores)
-        t0 = time.perf_counter()
-        if self.binary:
-            procs = []
-            for i, core in enumerate(self.cores):
-                cmd = [self.binary, "-synthesis", f"feat{i}.f32", f"out{i}.pcm"]
-                if shutil.which("taskset"):
-                    cmd = ["taskset", "-c", str(core)] + cmd
-                procs.append(subprocess.Popen(cmd, cwd=self.dir, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL))
-            for p in procs:
-                if p.wait() != 0:
-                    raise RuntimeError("reference lpcnet_demo failed")
-        else:
-            # the oracle port, single thread (only when oracle/_ref did not travel)
-            from lpcnet_b200 import blob
-            from oracle import orcpy
-            n = 1
-            om = orcpy.OrcModel(orcpy.OrcLib(), self.blob_bytes, 2, 1.0, None)
-            orcpy.OrcStream(om).run(blob.synthetic_features(self.n_frames, 0))
-        dt = time.perf_counter() - t0
-        return n * self.n_frames * FRAME / dt
-
-    def describe(self, n_runs):
-        n = len(self.cores) if self.binary else 1
-        what = os.path.basename(self.binary) if self.binary else "oracle port (liblpcnet_oracle.so)"
-        return (f"{n_runs} x ({n} concurrent processes, one per host core, each lpcnet_demo -synthesis of one "
-                f"{self.n_frames / 100:.0f} s stream) with {what}")
-
-    def close(self):
-        shutil.rmtree(self.dir, ignore_errors=True)
+from tools.cpu_baseline import CpuReference, cpu_model  # noqa: E402  (the reference's lpcnet_demo on the host cores)
 
 
-def cpu_model():
+def measure_int8_peak(dev):
+    """Dense int8 tensor throughput of this GPU (SURVEY.md 8d asks for a measurement, not the datasheet): an
+    8192^3 s8 x s8 -> s32 GEMM through cuBLASLt (torch._int_mm), best of 10, CUDA events.  None if unavailable."""
+    import torch
     try:
-        for line in open("/proc/cpuinfo"):
-            if line.startswith("model name"):
-                return line.split(":", 1)[1].strip()
+        n = 8192
+        a = torch.randint(-127, 127, (n, n), dtype=torch.int8, device=dev)
+        b = torch.randint(-127, 127, (n, n), dtype=torch.int8, device=dev)
+        for _ in range(3):
+            torch._int_mm(a, b)
+        best = 1e9
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            torch._int_mm(a, b)
+            e1.record()
+            e1.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+    except Exception:
+        return None
+
+
+def golden_hashes():
+    """SHA-256 of the unmodified reference's PCM for fixed streams of this workload, per call on the same states
+    (tests/golden/bench_pcm_hashes.json, written by tests/golden/make_golden.py bench from oracle/_ref)."""
+    try:
+        return json.load(open(os.path.join(ROOT, "tests", "golden", "bench_pcm_hashes.json")))
     except OSError:
-        pass
-    return "unknown"
+        return None
 
 
 # ------------------------------------------------------------------------------------------
@@ -174,15 +139,17 @@ def run_reference(args):
     from lpcnet_b200 import blob
     b = blob.write_blob(blob.random_model())
     n_frames = int(round(args.seconds * 100))
-    ref = CpuReference(b, n_frames)
+    ref = CpuReference("synthesis", n_frames, b)
     try:
         for _ in range(args.warmup):
             ref.run_once()
         t0 = time.perf_counter()
-        vals = [ref.run_once() for _ in range(args.steps)]
+        runs = [ref.run_once() for _ in range(args.steps)]
         dt = time.perf_counter() - t0
-        value = statistics.mean(vals)
+        value = statistics.mean(r[0] for r in runs)
+        per_core = [v for r in runs for v in r[1]]
         cores = len(ref.cores) if ref.binary else 1
+        what = os.path.basename(ref.binary) if ref.binary else "oracle port (liblpcnet_oracle.so)"
         line = {
             "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
@@ -193,7 +160,9 @@ def run_reference(args):
                        "model": "random-init, N=384 NB=16 density (0.05,0.05,0.2), reference blob layout",
                        "cpu": cpu_model()},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": ref.kind,
-                             "sample": ref.describe(args.steps)},
+                             "per_core_min": min(per_core), "per_core_median": statistics.median(per_core),
+                             "sample": f"{args.steps} x ({cores} concurrent processes, one per host core, each lpcnet_demo "
+                                       f"-synthesis of one {args.seconds:g} s stream) with {what}", "cpu": cpu_model()},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         }
         print(json.dumps(line), flush=True)
@@ -209,6 +178,109 @@ def step_latency_percentiles(launch_ms, launch_steps):
         return None
     lat.sort()
     return [lat[len(lat) // 2], lat[min(len(lat) - 1, int(0.99 * len(lat)))]]
+
+
+def run_aux(args, dev, local_rank, model_blob):
+    """BASELINE configs[2], [3] and a configs[4] point, measured in this process with the same clock sampling and each
+    beside the reference's own CPU run of that mode (tools/cpu_baseline.py).  Short by design (a few seconds each):
+    the headline's step count is untouched.  Host-buffer C-ABI calls (copies inside the timed region) throughout."""
+    import torch
+    from lpcnet_b200 import blob, engine
+    out = []
+
+    def pinned(shape, dtype):
+        t = torch.empty(shape, dtype=dtype, pin_memory=True)
+        return t, t.numpy()
+
+    def timed(fn, reps):
+        fn()
+        torch.cuda.synchronize()
+        ts = []
+        clocks = ClockSampler(local_rank)
+        clocks.start()
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            fn()                                   # every call ends with a stream synchronise inside the library
+            ts.append(time.perf_counter() - t0)
+        return statistics.median(ts), clocks.stop()
+
+    def cpu(mode, n_frames, blob_bytes=None):
+        if args.no_cpu_baseline:
+            return None
+        ref = CpuReference(mode, n_frames, blob_bytes)
+        try:
+            return ref.measure(1) if ref.binary else None
+        finally:
+            ref.close()
+
+    # ---- configs[2]: batched -decode, 8192 streams (1.6 kb/s packets -> lpcnet_dec + synthesis) ----
+    B, P = 8192, 25
+    bt = engine.Batch(model_blob, B, device=local_rank)
+    bt.set_codebooks(blob.synthetic_codebooks())
+    packets = np.random.default_rng(5).integers(0, 256, size=(B, P, 8), dtype=np.uint8)
+    hold, pcm = pinned((B, P * 640), torch.int16)
+    l0 = bt.launch_count
+    med, clk = timed(lambda: bt.decode(packets, pcm_out=pcm), 3)
+    v = B * P * 640 / med
+    out.append({"config": "configs[2]: batched -decode from synthetic 1.6 kb/s bitstreams, 8192 streams x 1 s",
+                "metric": METRIC, "unit": UNIT, "value": v, "value_is_e2e": True, "x_realtime": v / 16000.0,
+                "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": int(packets.nbytes), "d2h_bytes_per_step": int(pcm.nbytes)},
+                "ms_per_call": med * 1e3, "gpu_launches": (bt.launch_count - l0) // 4, "clocks": clk,
+                "cpu_baseline": cpu("decode", 1000)})
+    bt.close()
+    del hold
+
+    # ---- configs[3]: PLC noncausal_dc, 4096 streams, Gilbert losses ----
+    B, F = 4096, 100
+    A = blob.random_model()
+    A.update(blob.random_plc_model())
+    pb = engine.PLCBatch(blob.write_blob(A), B, engine.PLC_NONCAUSAL | engine.PLC_DC_FILTER, device=local_rank)
+    for s in range(B):
+        pb.set_seed(s, blob.stream_seed(s))
+    base = [blob.synthetic_pcm(F, 100 + s) for s in range(64)]
+    lost = np.stack([blob.synthetic_loss_pattern(F, 7 + s, 0.6, 0.1) for s in range(B)])
+    hold, buf = pinned((B, F * FRAME), torch.int16)
+    for s in range(B):
+        buf[s] = base[s % 64]
+    l0 = pb.launch_count
+    med, clk = timed(lambda: pb.process_inplace(buf, lost), 2)      # in place, as the C-ABI works
+    v = B * F * FRAME / med
+    out.append({"config": "configs[3]: PLC noncausal_dc batched with synthetic loss patterns, 4096 streams x 1 s",
+                "metric": METRIC, "unit": UNIT, "value": v, "value_is_e2e": True, "x_realtime": v / 16000.0,
+                "ms_per_10ms_frame": med / F * 1e3, "loss_rate": float(lost.mean()),
+                "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": int(buf.nbytes + lost.nbytes), "d2h_bytes_per_step": int(buf.nbytes)},
+                "ms_per_call": med * 1e3, "gpu_launches": (pb.launch_count - l0) // 3, "clocks": clk,
+                "cpu_baseline": cpu("plc", 1000)})
+    pb.close()
+    del hold
+
+    # ---- configs[4] point: 65536 streams on this GPU, free-running synthesis ----
+    B, F = 65536, 100
+    tracks = np.stack([blob.synthetic_features(F, k) for k in range(64)])
+    hold_f, hf = pinned((B, F, 36), torch.float32)
+    hf[...] = tracks[np.arange(B) % 64]
+    hold_p, hp = pinned((B, F * FRAME), torch.int16)
+    bt = engine.Batch(model_blob, B, device=local_rank)
+    for s in range(0, B, 997):
+        bt.set_seed(s, blob.stream_seed(s))
+    d_feat = hold_f.to(dev)
+    d_pcm = torch.zeros((B, F * FRAME), dtype=torch.int16, device=dev)
+    l0 = bt.launch_count
+
+    def dev_step():
+        bt.synthesize_device(d_feat.data_ptr(), 36, F, d_pcm.data_ptr())
+        bt.sync()
+    med_d, clk = timed(dev_step, 2)
+    launches = (bt.launch_count - l0) // 3
+    med_h, _ = timed(lambda: bt.synthesize(hf, pcm_out=hp), 1)
+    v, e = B * F * FRAME / med_d, B * F * FRAME / med_h
+    out.append({"config": "configs[4] point: throughput sweep, 65536 streams x 1 s on one B200",
+                "metric": METRIC, "unit": UNIT, "value": v, "x_realtime": v / 16000.0, "tile_streams_per_cta": bt.tile,
+                "e2e": {"value": e, "unit": UNIT, "h2d_bytes_per_step": int(hf.nbytes), "d2h_bytes_per_step": int(hp.nbytes)},
+                "ms_per_call": med_d * 1e3, "gpu_launches": launches, "clocks": clk,
+                "cpu_baseline": "the headline's cpu_baseline (same mode: lpcnet_demo -synthesis per core)"})
+    bt.close()
+    return out
 
 
 def run_gpu(args):
@@ -265,9 +337,31 @@ def run_gpu(args):
     def step_host():
         bt.synthesize(hf, pcm_out=h_pcm.numpy())
 
+    # ---- parity of the timed run itself: SHA-256 of fixed streams' PCM against the unmodified reference's ----
+    gold = golden_hashes() if (rank == 0 and n_frames == 1000 and not args.tile) else None
+    parity = {"streams": 0, "ok": None, "checked_steps": [], "note": "no golden hashes for this workload"}
+    if gold and gold["blob_sha256"] == hashlib.sha256(model_blob).hexdigest():
+        gstreams = [int(k) for k in gold["steps"] if int(k) < B]
+        parity = {"streams": len(gstreams), "ok": True, "checked_steps": [], "mismatches": [],
+                  "against": "tests/golden/bench_pcm_hashes.json: " + gold["source"]}
+
+    def check_parity(call_index, src):
+        """call_index: how many engine calls these stream states have seen before this one"""
+        if parity["ok"] is None or call_index >= len(next(iter(gold["steps"].values()))):
+            return
+        rows = src[gstreams].cpu().numpy() if hasattr(src, "cpu") else src[gstreams]
+        for k, s_ in enumerate(gstreams):
+            if hashlib.sha256(rows[k].astype("<i2").tobytes()).hexdigest() != gold["steps"][str(s_)][call_index]:
+                parity["ok"] = False
+                parity["mismatches"].append({"stream": s_, "call": call_index})
+        parity["checked_steps"].append(call_index)
+
     # ---- warm-up ----
-    for _ in range(args.warmup):
+    for k in range(args.warmup):
         step_device()
+        if k == 0:
+            barrier()
+            check_parity(0, d_pcm)
     barrier()
 
     # ---- timed: HBM-resident ----
@@ -293,10 +387,12 @@ def run_gpu(args):
     nonzero = int((d_pcm[:, 320:] != 0).sum().item())
     if nonzero == 0:
         raise SystemExit("bench.py: output is all zeros -- the kernel did not run")
+    check_parity(args.warmup + args.steps - 1, d_pcm)     # the output of the LAST TIMED step
 
     # ---- timed: end to end through the host-buffer C-ABI call ----
     step_host()
     barrier()
+    check_parity(args.warmup + args.steps, h_pcm.numpy())  # the host-buffer path, first call
     k_e2e = max(1, min(args.steps, 2))
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record(stream)
@@ -323,7 +419,8 @@ def run_gpu(args):
         kernel_s = sample_ms * 1e-3 / max(1, n_sample)
         samples_per_launch = B * active_frames * FRAME * args.steps / max(1, n_sample)
         int8_tops = ops_per_sample * samples_per_launch / kernel_s / 1e12
-        int8_peak = 2.0 * pk["bf16_tflops_sustained"]        # dense int8 = 2 x dense bf16 on B200
+        int8_meas = measure_int8_peak(dev)                   # cuBLASLt s8 x s8 -> s32, 8192^3, on this GPU
+        int8_peak = int8_meas if int8_meas else 2.0 * pk["bf16_tflops_sustained"]
         # on-chip bytes the algorithm must move per stream-sample: 3 embedding rows + the conditioning row
         gather_bytes = 4 * 1152 * 4
         gather_gbs = gather_bytes * samples_per_launch / kernel_s / 1e9
@@ -333,12 +430,12 @@ def run_gpu(args):
             l2_peak = None
         hbm_bytes_per_sample = 2.0 + (stride * 4 + (1152 + 48 + 16) * 4 * 2) / FRAME   # pcm + features + conditioning w/r
         # DRAM bytes of one sample_kernel launch from the committed ncu --set full capture of this command
-        # (profiles/r1_traffic.json); null when the workload differs from the captured one.
+        # (profiles/traffic.json, refreshed with every committed capture); null when the workload differs from it.
         traffic = None
         tile_used = bt.tile
         n_sms = torch.cuda.get_device_properties(dev).multi_processor_count
         try:
-            tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))["sample_kernel"]
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["sample_kernel"]
             frames_per_launch = active_frames * args.steps / max(1, n_sample)
             if tj["streams"] == B and tj["tile_streams_per_cta"] == tile_used and abs(tj["frames_per_launch"] - frames_per_launch) < 2:
                 traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
@@ -354,7 +451,8 @@ def run_gpu(args):
         smem_gbs = smem_bytes * samples_per_launch / kernel_s / 1e9
         roofline = {"bound": "tensor", "kernel": "sample_kernel", "achieved": int8_tops, "peak": int8_peak,
                     "unit": "TFLOP/s", "frac": int8_tops / int8_peak, "traffic": traffic,
-                    "peak_source": f"2 x bf16_tflops_sustained ({pk['src']})",
+                    "peak_source": ("torch._int_mm 8192^3 s8*s8->s32 measured in this run" if int8_meas
+                                    else f"2 x bf16_tflops_sustained ({pk['src']})"),
                     "ops_per_stream_sample": ops_per_sample, "avg_launch_ms": kernel_s * 1e3,
                     "launches": n_sample, "share_of_step": sample_ms / ms,
                     "note": "int8 u8*s8->s32 tensor ops; the kernel is bound by on-chip gather bandwidth and issue "
@@ -366,20 +464,29 @@ def run_gpu(args):
         roof_smem = {"bound": "l1_shared_data_pipe", "achieved": smem_gbs, "peak": smem_peak, "unit": "GB/s",
                      "frac": smem_gbs / smem_peak, "bytes_per_stream_sample": smem_bytes,
                      "peak_source": f"128 B/clk/SM x {n_sms} SMs x {sm_clock:.0f} MHz (SM clock sampled during the run)"}
+        # SURVEY.md 8(d)'s algorithmic on-chip bytes per stream-sample (each datum once: 3 embedding rows, one 4-byte
+        # activation word per block, state read+write, conditioning amortised over the frame) against the same pipe:
+        # a roofline fraction, where roofline_smem above counts what THIS implementation moves (pipe utilisation)
+        algo_bytes = 3 * 1152 * 4 + 4 * (bt.nblocks_a + bt.nblocks_b + 24) + 2 * (384 + 16) * 4 + (1152 + 48 + 16) * 4 / FRAME
+        roof_onchip = {"bound": "on_chip_bytes_algorithmic", "achieved": algo_bytes * samples_per_launch / kernel_s / 1e9,
+                       "peak": smem_peak, "unit": "GB/s", "frac": algo_bytes * samples_per_launch / kernel_s / 1e9 / smem_peak,
+                       "bytes_per_stream_sample": algo_bytes}
         roof_hbm = {"bound": "hbm", "achieved": hbm_bytes_per_sample * value / world / 1e9, "peak": pk["hbm_gbs"],
                     "unit": "GB/s", "frac": hbm_bytes_per_sample * value / world / 1e9 / pk["hbm_gbs"]}
         # ---- CPU baseline: bounded sample of the same workload on the host cores ----
         cpu = None
         if not args.no_cpu_baseline and world == 1:     # the reported baseline is an N=1 figure
-            ref = CpuReference(model_blob, n_frames)
+            ref = CpuReference("synthesis", n_frames, model_blob)
             try:
-                ref.run_once()
-                runs = 3
-                vals = [ref.run_once() for _ in range(runs)]
-                cpu = {"value": statistics.mean(vals), "unit": UNIT, "cores": len(ref.cores) if ref.binary else 1,
-                       "kind": ref.kind, "sample": ref.describe(runs), "cpu": cpu_model()}
+                cpu = ref.measure(3)
             finally:
                 ref.close()
+        aux = None
+        if world == 1 and not args.no_aux and B == 1024:
+            try:
+                aux = run_aux(args, dev, local_rank, model_blob)
+            except Exception as e:      # the headline stands on its own; say why the side measurements are missing
+                aux = [{"error": f"{type(e).__name__}: {e}"}]
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -397,17 +504,22 @@ def run_gpu(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h_feat.numel() * 4 * world,
                     "d2h_bytes_per_step": h_pcm.numel() * 2 * world, "steps": k_e2e},
             "gpu_launches": launches, "clocks": clk,
-            "roofline": roofline, "roofline_smem": roof_smem, "roofline_l2": roof_l2, "roofline_hbm": roof_hbm,
+            "parity_check": parity,
+            "roofline": roofline, "roofline_onchip": roof_onchip, "roofline_smem": roof_smem, "roofline_l2": roof_l2,
+            "roofline_hbm": roof_hbm,
             # the frame network of chunk k+1 runs on a second stream beside the sample kernel of chunk k: its time
             # (here as a fraction of the step) is concurrent with the sample kernel, not additive
             "frame_network_share_of_step": frame_ms / ms, "frame_network_overlapped": True,
             "cpu_baseline": cpu,
+            "aux": aux,
         }
         print(json.dumps(line), flush=True)
     bt.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if parity["ok"] is False:
+        raise SystemExit(f"bench.py: the timed run's PCM differs from the reference's: {parity['mismatches']}")
 
 
 def main():
@@ -420,6 +532,7 @@ def main():
     ap.add_argument("--seconds", type=float, default=10.0, help="audio per stream per step")
     ap.add_argument("--tile", type=int, default=0, help="streams per CTA (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-aux", action="store_true", help="skip the configs[2]/[3]/[4] side measurements")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3

@@ -80,6 +80,7 @@ struct LPCNetBatch {
   void *fb_alloc = nullptr;
   FrameBuffers fb2;               // ... and of the next one: the frame network of chunk k+1 runs on its own stream
   void *fb2_alloc = nullptr;      //     beside the sample kernel of chunk k (it depends only on frame-rate state)
+  size_t fb_rows = 0, fb2_rows = 0;   // stream-frames the two buffer sets hold
   cudaStream_t fstream = nullptr;
   cudaStream_t cstream = nullptr;                       // device->host copies of finished chunks (pinned destination)
   cudaEvent_t ev_chunk = nullptr, ev_copied = nullptr;
@@ -169,21 +170,50 @@ int alloc_state(LPCNetBatch *b) {
   return 0;
 }
 
+// A call is walked in chunks of at most 32 frames (the sample kernel keeps a tile's state in registers / shared
+// memory for a whole chunk, the frame network evaluates the chunk's frames side by side).  The conditioning of a
+// chunk is 6400 B per stream-frame; instead of shrinking the chunk when the batch is large (1 frame per launch at
+// 65 536 streams: the tile state went through HBM every 160 steps and the frame network was never batched over
+// frames), the batch is walked in GROUPS of streams that each get full 32-frame chunks: a group is a whole number
+// of 16-stream-tile waves (n_sms * 16 streams) and its chunk buffer stays under kChunkBytes.
+constexpr long long kChunkBytes = 1ll << 30;
+constexpr int kChunkFrames = 32;
+
 int chunk_frames(const LPCNetBatch *b, int n_frames) {
-  // conditioning is 6400 B per stream-frame; keep a chunk under ~320 MB and at most 32 frames
-  long long cap = (320ll << 20) / ((long long)b->n_streams * 6400);
-  if (cap < 1) cap = 1;
-  if (cap > 32) cap = 32;
-  return n_frames < cap ? n_frames : (int)cap;
+  (void)b;
+  return n_frames < kChunkFrames ? n_frames : kChunkFrames;
 }
 
-int ensure_frame_buffers(LPCNetBatch *b, int F, bool second = false) {
+// streams per group for a call of n_frames frames (n_streams = no grouping)
+int group_streams(const LPCNetBatch *b, int n_frames) {
+  const int Fc = chunk_frames(b, n_frames);
+  const long long cap = kChunkBytes / ((long long)Fc * 6400);
+  if (cap >= b->n_streams) return b->n_streams;
+  const int wave = b->n_sms * 16;
+  long long g = cap / wave * wave;
+  if (g < wave) g = wave;
+  return (int)g;
+}
+
+// the stream state of streams [s0, ...) as a batch of its own: every array is [stream][field]
+DevState state_view(const DevState &S, size_t s0) {
+  DevState v = S;
+  v.conv1_state += s0 * 168; v.conv2_state += s0 * 256; v.gru_a += s0 * kN; v.gru_b += s0 * kNB;
+  v.last_sig += s0 * 16; v.old_lpc += s0 * kMaxDelay * 16; v.lpc += s0 * 16; v.cond_a += s0 * kRowsAP;
+  v.cond_b += s0 * kRowsB; v.deemph += s0; v.last_exc += s0; v.frame_count += s0; v.rng += s0 * 4; v.vq_mem += s0 * 18;
+  return v;
+}
+
+// buffers for F frames of `streams` streams (0 = the whole batch); they only grow
+int ensure_frame_buffers(LPCNetBatch *b, int F, bool second = false, int streams = 0) {
   FrameBuffers &fb = second ? b->fb2 : b->fb;
   void *&alloc = second ? b->fb2_alloc : b->fb_alloc;
-  if (fb.cap_frames >= F) return 0;
+  size_t &have = second ? b->fb2_rows : b->fb_rows;
+  const size_t B = streams > 0 ? streams : b->n_streams;
+  // every array is a product of the stream count with F or F + 2: both products bound all of them
+  if (have >= B * (size_t)F && (size_t)fb.cap_streams * (fb.cap_frames + 2) >= B * (size_t)(F + 2)) return 0;
   if (alloc) cudaFree(alloc);
-  alloc = nullptr; fb.cap_frames = 0;
-  const size_t B = b->n_streams;
+  alloc = nullptr; fb.cap_frames = 0; fb.cap_streams = 0; have = 0;
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t r = off; off += (bytes + 255) & ~size_t(255); return r; };
   const size_t o_iv = take(B * (F + 2) * kConvIn * 4), o_c1 = take(B * (F + 2) * kC * 4);
@@ -196,7 +226,7 @@ int ensure_frame_buffers(LPCNetBatch *b, int F, bool second = false) {
   fb.in_vec = (float *)(p + o_iv); fb.c1 = (float *)(p + o_c1); fb.cond_a = (float *)(p + o_ca);
   fb.cond_b = (float *)(p + o_cb); fb.lpc = (float *)(p + o_lpc); fb.active = (uint8_t *)(p + o_act);
   fb.fft_scratch = (float *)(p + o_fft);
-  fb.cap_frames = F;
+  fb.cap_frames = F; fb.cap_streams = (int)B; have = B * (size_t)F;
   return 0;
 }
 

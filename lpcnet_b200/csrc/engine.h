@@ -172,6 +172,7 @@ void host_dsp_tables(std::vector<float> &tw, std::vector<int16_t> &br, std::vect
 // Per-chunk scratch: conditioning for F frames.
 struct FrameBuffers {
   int cap_frames = 0;
+  int cap_streams = 0;       // the arrays below are laid out for batches of at most this many streams
   float *in_vec = nullptr;   // [B][F+2][84]   frame-network input rows incl. 2 history rows
   float *c1 = nullptr;       // [B][F+2][128]  conv1 outputs incl. 2 history rows
   float *cond_a = nullptr;   // [F][B][kRowsAP], gru_a_col_index order
