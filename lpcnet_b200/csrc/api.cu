@@ -187,7 +187,9 @@ int chunk_frames(const LPCNetBatch *b, int n_frames) {
 // streams per group for a call of n_frames frames (n_streams = no grouping)
 int group_streams(const LPCNetBatch *b, int n_frames) {
   const int Fc = chunk_frames(b, n_frames);
-  const long long cap = kChunkBytes / ((long long)Fc * 6400);
+  long long bytes = kChunkBytes;
+  if (const char *e = getenv("LPCNET_B200_CHUNK_BYTES")) bytes = atoll(e) > 0 ? atoll(e) : bytes;   // tests: small groups
+  const long long cap = bytes / ((long long)Fc * 6400);
   if (cap >= b->n_streams) return b->n_streams;
   const int wave = b->n_sms * 16;
   long long g = cap / wave * wave;
@@ -240,12 +242,14 @@ int auto_tile(const LPCNetBatch *b) {
   return t < b->max_tile ? t : b->max_tile;
 }
 
-// frame network for frames [f0, f0+F) of the call on stream st, results left in fb
+// frame network for frames [f0, f0+F) of the call, streams [s0, s0+G) of the batch, on stream st; results left in fb
+// (laid out [F][G][...]).  d_features points at the whole batch's rows.
 int run_frames(LPCNetBatch *b, const float *d_features, int stride, int f0, int F, int total_frames,
-               const FrameBuffers &fb, cudaStream_t st) {
+               const FrameBuffers &fb, cudaStream_t st, int s0 = 0, int G = 0) {
+  if (G <= 0) G = b->n_streams - s0;
   FrameArgs fa{};
-  fa.m = b->model.d; fa.st = b->st; fa.fb = fb; fa.n_streams = b->n_streams; fa.n_frames = F;
-  fa.features = d_features; fa.feature_stride = stride; fa.frame0 = f0; fa.total_frames = total_frames;
+  fa.m = b->model.d; fa.st = state_view(b->st, s0); fa.fb = fb; fa.n_streams = G; fa.n_frames = F;
+  fa.features = d_features + (size_t)s0 * total_frames * stride; fa.feature_stride = stride; fa.frame0 = f0; fa.total_frames = total_frames;
   int nl = 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (b->profiling) { CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventRecord(e0, st)); }
@@ -253,9 +257,9 @@ int run_frames(LPCNetBatch *b, const float *d_features, int stride, int f0, int 
   if (b->profiling) { CK(cudaEventRecord(e1, st)); b->ev_frame.emplace_back(e0, e1); }
   b->launches += nl;
   // keep the last frame's conditioning in the stream state (lpcnet_private.h:43-47)
-  const size_t B = b->n_streams;
-  CK(cudaMemcpyAsync(b->st.cond_a, fb.cond_a + (size_t)(F - 1) * B * kRowsAP, B * kRowsAP * 4, cudaMemcpyDeviceToDevice, st));
-  CK(cudaMemcpyAsync(b->st.cond_b, fb.cond_b + (size_t)(F - 1) * B * kRowsB, B * kRowsB * 4, cudaMemcpyDeviceToDevice, st));
+  const size_t B = G;
+  CK(cudaMemcpyAsync(fa.st.cond_a, fb.cond_a + (size_t)(F - 1) * B * kRowsAP, B * kRowsAP * 4, cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemcpyAsync(fa.st.cond_b, fb.cond_b + (size_t)(F - 1) * B * kRowsB, B * kRowsB * 4, cudaMemcpyDeviceToDevice, st));
   return 0;
 }
 int run_frames(LPCNetBatch *b, const float *d_features, int stride, int f0, int F, int total_frames) {
@@ -279,16 +283,19 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
   if (stride < kFeat) return fail("feature_stride must be >= 20");
   CK(cudaSetDevice(b->device));
   const int Fc = chunk_frames(b, n_frames);
-  if (ensure_frame_buffers(b, Fc)) return -1;
+  // large batches: groups of streams, each walked in full chunks (see group_streams); trace / logit runs stay whole
+  const int G = (d_trace || d_logits) ? b->n_streams : group_streams(b, n_frames);
+  const int n_groups = (b->n_streams + G - 1) / G;
+  if (ensure_frame_buffers(b, Fc, false, G)) return -1;
   // no explicit tile: whole waves of 16-stream tiles, the remainder in 8-stream tiles when that is faster (0 = mixed)
   const int tile = (b->tile == 0 && b->max_tile >= 16 && !getenv("LPCNET_B200_NO_MIX")) ? 0 : auto_tile(b);
   // Several chunks: the frame network of chunk k+1 runs on a second stream while the sample kernel works on
   // chunk k (two buffer sets).  It touches only frame-rate state (conv histories, frame counter, LPC delay
   // line); the sample kernel only sample-rate state.  Everything is ordered after the caller's stream at
-  // entry, and the caller's stream ends after all of it.
-  const bool pipe = n_frames > Fc && !getenv("LPCNET_B200_NO_PIPELINE");
+  // entry, and the caller's stream ends after all of it.  The (group, chunk) pairs form one sequence of work items.
+  const bool pipe = (n_frames > Fc || n_groups > 1) && !getenv("LPCNET_B200_NO_PIPELINE");
   if (pipe) {
-    if (ensure_frame_buffers(b, Fc, true)) return -1;
+    if (ensure_frame_buffers(b, Fc, true, G)) return -1;
     if (!b->fstream) {
       CK(cudaStreamCreateWithFlags(&b->fstream, cudaStreamNonBlocking));
       CK(cudaEventCreateWithFlags(&b->ev_entry, cudaEventDisableTiming));
@@ -300,46 +307,51 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
     CK(cudaEventRecord(b->ev_entry, b->stream));
     CK(cudaStreamWaitEvent(b->fstream, b->ev_entry, 0));
   }
-  int chunk = 0;
-  for (int f0 = 0; f0 < n_frames; f0 += Fc, chunk++) {
-    const int F = (n_frames - f0) < Fc ? (n_frames - f0) : Fc;
-    const int buf = pipe ? (chunk & 1) : 0;
-    const FrameBuffers &fbk = buf ? b->fb2 : b->fb;
-    if (pipe) {
-      if (chunk >= 2) CK(cudaStreamWaitEvent(b->fstream, b->ev_samples[buf], 0));   // the buffers are free again
-      if (run_frames(b, d_features, stride, f0, F, n_frames, fbk, b->fstream)) return -1;
-      CK(cudaEventRecord(b->ev_frames[buf], b->fstream));
-      CK(cudaStreamWaitEvent(b->stream, b->ev_frames[buf], 0));
-    } else if (run_frames(b, d_features, stride, f0, F, n_frames)) {
-      return -1;
-    }
-    SampleArgs sa{};
-    sa.m = b->model.d; sa.st = b->st; sa.n_streams = b->n_streams; sa.n_frames = F; sa.spf = spf;
-    sa.frame0 = f0; sa.total_frames = n_frames;
-    sa.cond_a = fbk.cond_a; sa.cond_b = fbk.cond_b; sa.lpc = fbk.lpc; sa.active = fbk.active;
-    sa.pcm = d_pcm; sa.forced = d_forced; sa.trace = d_trace; sa.logits = d_logits;
-#ifdef LPCB_PHASE_CLOCKS
-    if (!g_phase_clk) { CK(cudaMalloc(&g_phase_clk, 16 * 8)); CK(cudaMemset(g_phase_clk, 0, 16 * 8)); }
-    sa.phase_clk = g_phase_clk;
-#endif
-    int nl = 0;
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    if (b->profiling) { CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventRecord(e0, b->stream)); }
-    CK(launch_sample_kernel(sa, tile, b->n_sms, b->stream, &nl));
-    if (b->profiling) { CK(cudaEventRecord(e1, b->stream)); b->ev_sample.emplace_back(e0, e1); b->ev_sample_steps.push_back(F * spf); }
-    if (pipe) CK(cudaEventRecord(b->ev_samples[buf], b->stream));
-    b->launches += nl;
-    if (h_pcm) {
-      if (!b->cstream) {
-        CK(cudaStreamCreateWithFlags(&b->cstream, cudaStreamNonBlocking));
-        CK(cudaEventCreateWithFlags(&b->ev_chunk, cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&b->ev_copied, cudaEventDisableTiming));
+  const size_t row_len = (size_t)n_frames * spf;
+  int item = 0;
+  for (int s0 = 0; s0 < b->n_streams; s0 += G) {
+    const int Gs = (b->n_streams - s0) < G ? (b->n_streams - s0) : G;
+    for (int f0 = 0; f0 < n_frames; f0 += Fc, item++) {
+      const int F = (n_frames - f0) < Fc ? (n_frames - f0) : Fc;
+      const int buf = pipe ? (item & 1) : 0;
+      const FrameBuffers &fbk = buf ? b->fb2 : b->fb;
+      if (pipe) {
+        if (item >= 2) CK(cudaStreamWaitEvent(b->fstream, b->ev_samples[buf], 0));   // the buffers are free again
+        if (run_frames(b, d_features, stride, f0, F, n_frames, fbk, b->fstream, s0, Gs)) return -1;
+        CK(cudaEventRecord(b->ev_frames[buf], b->fstream));
+        CK(cudaStreamWaitEvent(b->stream, b->ev_frames[buf], 0));
+      } else if (run_frames(b, d_features, stride, f0, F, n_frames, b->fb, b->stream, s0, Gs)) {
+        return -1;
       }
-      const size_t row = (size_t)n_frames * spf * sizeof(short), off = (size_t)f0 * spf;
-      CK(cudaEventRecord(b->ev_chunk, b->stream));
-      CK(cudaStreamWaitEvent(b->cstream, b->ev_chunk, 0));
-      CK(cudaMemcpy2DAsync(h_pcm + off, row, d_pcm + off, row, (size_t)F * spf * sizeof(short), b->n_streams,
-                           cudaMemcpyDeviceToHost, b->cstream));
+      SampleArgs sa{};
+      sa.m = b->model.d; sa.st = state_view(b->st, s0); sa.n_streams = Gs; sa.n_frames = F; sa.spf = spf;
+      sa.frame0 = f0; sa.total_frames = n_frames;
+      sa.cond_a = fbk.cond_a; sa.cond_b = fbk.cond_b; sa.lpc = fbk.lpc; sa.active = fbk.active;
+      sa.pcm = d_pcm + (size_t)s0 * row_len; sa.forced = d_forced ? d_forced + (size_t)s0 * row_len : nullptr;
+      sa.trace = d_trace; sa.logits = d_logits;     // whole-batch runs only (G = n_streams above)
+#ifdef LPCB_PHASE_CLOCKS
+      if (!g_phase_clk) { CK(cudaMalloc(&g_phase_clk, 16 * 8)); CK(cudaMemset(g_phase_clk, 0, 16 * 8)); }
+      sa.phase_clk = g_phase_clk;
+#endif
+      int nl = 0;
+      cudaEvent_t e0 = nullptr, e1 = nullptr;
+      if (b->profiling) { CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventRecord(e0, b->stream)); }
+      CK(launch_sample_kernel(sa, tile, b->n_sms, b->stream, &nl));
+      if (b->profiling) { CK(cudaEventRecord(e1, b->stream)); b->ev_sample.emplace_back(e0, e1); b->ev_sample_steps.push_back(F * spf); }
+      if (pipe) CK(cudaEventRecord(b->ev_samples[buf], b->stream));
+      b->launches += nl;
+      if (h_pcm) {
+        if (!b->cstream) {
+          CK(cudaStreamCreateWithFlags(&b->cstream, cudaStreamNonBlocking));
+          CK(cudaEventCreateWithFlags(&b->ev_chunk, cudaEventDisableTiming));
+          CK(cudaEventCreateWithFlags(&b->ev_copied, cudaEventDisableTiming));
+        }
+        const size_t row = row_len * sizeof(short), off = (size_t)s0 * row_len + (size_t)f0 * spf;
+        CK(cudaEventRecord(b->ev_chunk, b->stream));
+        CK(cudaStreamWaitEvent(b->cstream, b->ev_chunk, 0));
+        CK(cudaMemcpy2DAsync(h_pcm + off, row, d_pcm + off, row, (size_t)F * spf * sizeof(short), Gs,
+                             cudaMemcpyDeviceToHost, b->cstream));
+      }
     }
   }
   if (h_pcm) {
@@ -705,7 +717,8 @@ int lpcnet_batch_frame_network(LPCNetBatch *b, const float *features, int stride
   const size_t fbytes = B * n_frames * (size_t)stride * 4;
   if (grow(&b->d_feat, &b->d_feat_bytes, fbytes)) return -1;
   CK(cudaMemcpyAsync(b->d_feat, features, fbytes, cudaMemcpyHostToDevice, b->stream));
-  const int Fc = chunk_frames(b, n_frames);
+  long long cap = kChunkBytes / ((long long)b->n_streams * 6400);      // a test entry point: whole batch, smaller chunks
+  const int Fc = (int)(cap < 1 ? 1 : (cap < chunk_frames(b, n_frames) ? cap : chunk_frames(b, n_frames)));
   if (ensure_frame_buffers(b, Fc)) return -1;
   for (int f0 = 0; f0 < n_frames; f0 += Fc) {
     const int F = (n_frames - f0) < Fc ? (n_frames - f0) : Fc;

@@ -351,3 +351,33 @@ def test_mixed_tile_schedule_is_invisible(eng, model_blob, orc_model):
     for s in (0, 2367, 2368, B - 1):
         ref = orcpy.OrcStream(orc_model, blob.stream_seed(s % 64)).run(feats[s])[0]
         assert np.array_equal(out[0][s], ref), s
+
+
+def test_stream_groups_are_invisible(eng, model_blob, orc_model, monkeypatch):
+    """Large batches are walked in groups of whole 16-stream-tile waves, each in full 32-frame chunks (api.cu
+    group_streams).  With the group budget lowered to one wave: 5000 streams x 40 frames (3 groups x 2 chunks, the
+    frame network of the next work item running beside the sample kernel) must give the PCM of the ungrouped run,
+    and the streams either side of the group boundaries must match the oracle."""
+    B, F = 5000, 40
+    base = np.stack([blob.synthetic_features(F, s) for s in range(64)])
+    feats = base[np.arange(B) % 64]
+    out = []
+    for chunk_bytes in ("500000000", None):
+        if chunk_bytes:
+            monkeypatch.setenv("LPCNET_B200_CHUNK_BYTES", chunk_bytes)     # 2441 streams x 32 frames -> one 2368-stream wave
+        else:
+            monkeypatch.delenv("LPCNET_B200_CHUNK_BYTES")
+        bt = eng.Batch(model_blob, B)
+        for s in range(B):
+            bt.set_seed(s, blob.stream_seed(s % 97))
+        out.append(bt.synthesize(feats)[0])
+        last = bt.get_state(B - 1)
+        bt.close()
+    assert np.array_equal(out[0], out[1])
+    for s in (0, 2367, 2368, 4735, 4736, B - 1):
+        st = orcpy.OrcStream(orc_model, blob.stream_seed(s % 97))
+        ref = st.run(feats[s])[0]
+        assert np.array_equal(out[0][s], ref), s
+    osnap = st.snapshot()
+    for name in last.dtype.names:
+        assert np.array_equal(np.asarray(last[name]), np.asarray(osnap[name])), name
