@@ -181,6 +181,21 @@ LPCNET_B200_EXPORT int lpcnet_batch_read_profile(LPCNetBatch *b, double *sample_
  * 4608-byte rows (one embedding row) from an L2-resident 3.5 MB table with 128-bit loads. */
 LPCNET_B200_EXPORT int lpcnet_b200_measure_l2_gather(int device, double *gbytes_per_s);
 
+/* Cepstrum -> LPC without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Computes what the frame network computes per frame before its delay line (lpc_from_cepstrum and
+ * everything below it): d_cepstrum [n_rows][stride >= 18] floats and d_lpc [n_rows][16] floats are DEVICE buffers of
+ * the caller; the launch is asynchronous on cuda_stream (NULL = the default stream).  The kernel's FFT scratch is a
+ * static device array inside the library (10 MiB, held by every GPU that loads the library until exit), so
+ * n_rows <= LPCNET_B200_NOALLOC_MAX_ROWS; more is rejected (-1, lpcnet_b200_last_error()): split the call.
+ * device -1 = the current device.  The first call on a device looks up the array's device address and uploads 4 KB
+ * of tables (no allocation either); n_rows = 0 does only that, e.g. before a capture starts.  Every call shares the
+ * array; each row clears its own part before use, so nothing is carried from call to call -- but calls whose kernels
+ * OVERLAP on the GPU (different streams, no ordering) race on it. */
+#define LPCNET_B200_NOALLOC_MAX_ROWS 4096
+LPCNET_B200_EXPORT int lpcnet_b200_lpc_from_cepstrum_noalloc(int device, const float *d_cepstrum, int stride,
+                                                             float *d_lpc, int n_rows, void *cuda_stream);
+
 /* ------------------------------------------------------------------------------------
  * 3. Feature analysis (the step before the synthesis path)
  * ------------------------------------------------------------------------------------ */

@@ -43,7 +43,7 @@ EXPORTED_SYMBOLS = [
     "lpcnet_batch_set_state", "lpcnet_batch_sync", "lpcnet_batch_nblocks", "lpcnet_batch_launch_count",
     "lpcnet_batch_set_profiling", "lpcnet_batch_read_profile", "lpcnet_batch_profile_launches", "lpcnet_b200_measure_l2_gather",
     "lpcnet_b200_set_rcp_table", "lpcnet_b200_default_rcp_table", "lpcnet_b200_set_model_constants",
-    "lpcnet_b200_last_error", "lpcnet_b200_device_count",
+    "lpcnet_b200_last_error", "lpcnet_b200_device_count", "lpcnet_b200_lpc_from_cepstrum_noalloc",
     "lpcnet_encoder_get_size", "lpcnet_encoder_init", "lpcnet_encoder_create", "lpcnet_encoder_destroy",
     "lpcnet_compute_single_frame_features", "lpcnet_compute_single_frame_features_float",
     "lpcnet_feature_batch_create", "lpcnet_feature_batch_destroy", "lpcnet_feature_batch_n_streams",
@@ -108,6 +108,7 @@ def load_library() -> C.CDLL:
     L.lpcnet_batch_read_profile.argtypes = [vp, vp, vp, vp, vp]
     L.lpcnet_batch_profile_launches.argtypes = [vp, vp, vp, ci]
     L.lpcnet_b200_measure_l2_gather.argtypes = [ci, vp]
+    L.lpcnet_b200_lpc_from_cepstrum_noalloc.argtypes = [ci, vp, ci, vp, ci, vp]
     L.lpcnet_b200_set_rcp_table.argtypes = [vp]
     L.lpcnet_b200_default_rcp_table.argtypes = [vp]
     L.lpcnet_b200_set_model_constants.argtypes = [ci, cf]
@@ -206,6 +207,18 @@ def measure_l2_gather(device: int = 0) -> float:
     if load_library().lpcnet_b200_measure_l2_gather(device, C.byref(v)) != 0:
         raise LPCNetError(f"lpcnet_b200_measure_l2_gather: {last_error()}")
     return v.value
+
+
+NOALLOC_MAX_ROWS = 4096      # LPCNET_B200_NOALLOC_MAX_ROWS
+
+
+def lpc_from_cepstrum_noalloc(d_cepstrum: int, stride: int, d_lpc: int, n_rows: int, cuda_stream: int = 0,
+                              device: int = -1) -> None:
+    """lpcnet_b200_lpc_from_cepstrum_noalloc: device pointers in and out, no allocation inside the call."""
+    rc = load_library().lpcnet_b200_lpc_from_cepstrum_noalloc(device, C.c_void_p(d_cepstrum), stride, C.c_void_p(d_lpc),
+                                                              n_rows, C.c_void_p(cuda_stream) if cuda_stream else None)
+    if rc != 0:
+        raise LPCNetError(f"lpcnet_b200_lpc_from_cepstrum_noalloc: {last_error()}")
 
 
 def _check(rc: int, what: str) -> None:
