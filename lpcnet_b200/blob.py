@@ -336,3 +336,14 @@ def random_dred_decoder_model(seed: int = 8765, cond: int = 256, latent: int = 8
     for k in list(A.keys()):
         A[k] = np.ascontiguousarray(A[k]).reshape(-1)
     return A
+
+
+def saturating_models(qmax: int = 127) -> bytes:
+    """One blob (LPCNet + PLC predictor + RDOVAE decoder) whose int8 matrices use the whole range [-qmax, qmax], like
+    trained models may (the training-time WeightClip bounds adjacent OUTPUT weights; the pairs vpmaddubsw adds are
+    adjacent INPUT weights): pairs with |q0| + |q1| > 128 saturate its s16 sum whenever both activations are large
+    (src/vec_avx.h:814-818).  The parity tests on it pin that behaviour (engine.h DevSat)."""
+    A = random_model(seed=77, qmax=(qmax, qmax, qmax), qmax_b_in=qmax, qmax_b_rec=qmax)
+    A.update(random_plc_model(seed=78, qmax_in=qmax, qmax_rec=qmax))
+    A.update(random_dred_decoder_model(seed=79, qmax_in=qmax, qmax_rec=qmax))
+    return write_blob(A)

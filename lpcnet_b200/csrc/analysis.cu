@@ -732,6 +732,13 @@ int lpcnet_feature_batch_compute_features(LPCNetFeatureBatch *b, const short *pc
   return superframe_host(b, pcm, n_packets, nullptr, features);
 }
 
+}  // extern "C"
+std::vector<float> lpcb::default_codebooks() {
+  std::lock_guard<std::mutex> lk(g_cb_mu);
+  return g_codebooks;
+}
+extern "C" {
+
 int lpcnet_b200_set_codebooks(const float *codebooks, int n_floats) {
   std::lock_guard<std::mutex> lk(g_cb_mu);
   if (!codebooks) { g_codebooks.clear(); return 0; }
@@ -752,7 +759,7 @@ int lpcnet_encoder_get_size(void) { return (int)sizeof(LPCNetEncState); }
 int lpcnet_encoder_init(LPCNetEncState *st) {
   if (!st) return -1;
   st->magic = kEncMagic;
-  st->batch = lpcnet_feature_batch_create(1, 0);
+  st->batch = lpcnet_feature_batch_create(1, current_device());   // like lpcnet_load_model: the caller's current GPU
   return st->batch ? 0 : -1;
 }
 

@@ -369,6 +369,16 @@ int lpcb::default_features_delay() {
   return g_default_delay;
 }
 
+float lpcb::default_lpc_gamma() {
+  std::lock_guard<std::mutex> lk(g_cfg_mu);
+  return g_default_gamma;
+}
+int lpcb::current_device() {
+  int d = 0;
+  if (cudaGetDevice(&d) != cudaSuccess) { cudaGetLastError(); d = 0; }
+  return d;
+}
+
 BatchView lpcb::batch_view(LPCNetBatch *b) { return BatchView{b->st, &b->model, b->stream, b->n_streams, b->device}; }
 
 int lpcb::batch_frame_network_masked(LPCNetBatch *b, const float *d_features, int stride, const uint8_t *d_mask,
@@ -549,6 +559,7 @@ int lpcnet_batch_nblocks(const LPCNetBatch *b, int which) {
     case 2: return b->model.d.rcp_arith;               // 1: reciprocal estimate computed, 0: table lookup
     case 3: return b->model.d.a_rec.slots[2] != 0;     // 1: GRU-A runs the unrolled fixed-slot path
     case 4: return b->model.d.a_rec.n_chunks;
+    case 6: return b->model.d.a_rec.sat.n + b->model.d.b_in.sat.n + b->model.d.b_rec.sat.n;   // int8 pairs on the exact s16 pass
     case 5: return auto_tile(b);                        // streams per CTA the next synthesize call will use
     case 8: case 16: case 32: return (int)sample_kernel_smem(which, b->model.d);   // bytes of shared memory per CTA
     default: return 0;
@@ -922,7 +933,15 @@ void lpcnet_decoder_destroy(LPCNetDecState *st) {
   free(st);
 }
 int lpcnet_decoder_load_model(LPCNetDecState *st, const unsigned char *data, int len) {
-  return lpcnet_load_model(&st->lpcnet_state, data, len);
+  if (lpcnet_load_model(&st->lpcnet_state, data, len)) return -1;
+  // the reference links its VQ tables into the library (ceps_codebooks.c); here they come with the blob or, for an
+  // opaque decoder state that cannot reach lpcnet_batch_set_codebooks, from lpcnet_b200_set_codebooks
+  LPCNetBatch *b = st->lpcnet_state.batch;
+  if (!b->model.has_codebooks) {
+    const std::vector<float> cb = default_codebooks();
+    if (!cb.empty() && lpcnet_batch_set_codebooks(b, cb.data(), (int)cb.size())) return -1;
+  }
+  return 0;
 }
 int lpcnet_decode(LPCNetDecState *st, const unsigned char *buf, short *pcm) {
   if (!st || !st->lpcnet_state.batch) return fail("lpcnet_decode: no model loaded");

@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(256) dred_decode_kernel(DredArgs A) {
     for (int k = 0; k < 3; k++) {
       // compute_gruB (zero conditioning) on the previous dense output; the new state is the next layer's input
       plc_gru(D.g_in[k], D.g_rec[k], D.g_subias[k], buf + 2 * k * kPlcUnits, kPlcUnits, g[k], xq_in, xq_st,
-              buf + (2 * k + 1) * kPlcUnits, A.rcp_tab, t);
+              buf + (2 * k + 1) * kPlcUnits, A.rcp_tab, t, D.sat_in[k], D.sat_rec[k]);
       dred_dense_tanh(D.dense_w[k + 1], D.dense_b[k + 1], buf + (2 * k + 1) * kPlcUnits, kPlcUnits,
                       buf + (2 * k + 2) * kPlcUnits, A.rcp_tab, t);
       __syncthreads();

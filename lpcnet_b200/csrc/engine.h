@@ -60,11 +60,31 @@ struct PackedSparse {
   // off: per chunk, per lane%4, the two gather byte offsets and the gate: lo | hi << 16 | gate << 30.
   // off_fixed: the same words of the fixed chunks regrouped [ug][lane%4][8] (ST <= 8 used) for 16-byte loads.
   int slots[3] = {0, 0, 0};
+  std::vector<uint32_t> sat_start;    // saturating pairs (DevSat): [lists + 1]
+  std::vector<uint2> sat;
   std::vector<uint32_t> off;          // [n_chunks][4]
   std::vector<uint32_t> off_fixed;    // [unit groups][4][8]
 };
 
+// vpmaddubsw (src/vec_avx.h:814-818) adds the two u8 x s8 products of an adjacent input pair in a SATURATING s16;
+// integer MMA / dp4a sums cannot saturate.  A pair can only saturate when both weights have the same sign and
+// 255*(|w0|+|w1|) > 32767; such pairs are taken out of the tensor-core operands at load (weights zeroed there) and
+// listed here, and the kernels add sat16(u0*w0 + u1*w1) for them -- exact for every int8 model, free when the list
+// is empty (clipped models).  entry.x = column | row_in_group << 16 | gate << 20, entry.y = w0 & 255 | (w1 & 255) << 8.
+struct DevSat {
+  int n;                  // entries in total (0: the kernels skip the pass)
+  const uint32_t *start;  // [lists + 1]
+  const uint2 *e;
+};
+__host__ __device__ inline int sat16_pair(uint2 f, const unsigned char *x) {
+  const int col = f.x & 0xffff;
+  const int w0 = (int)(signed char)(f.y & 0xffu), w1 = (int)(signed char)((f.y >> 8) & 0xffu);
+  const int p = (int)x[col] * w0 + (int)x[col + 1] * w1;
+  return p > 32767 ? 32767 : (p < -32768 ? -32768 : p);
+}
+
 struct DevSparse {
+  DevSat sat;                   // lists per unit group (GRU-A) or per 8-row group
   int n_groups, n_chunks;
   const uint32_t *chunk_start;  // device
   const uint2 *pos;             // device, [n_chunks]
@@ -78,6 +98,7 @@ struct DevSparse {
 // GRU matrices re-tiled as words of four consecutive inputs, [input/4][3*256 rows]: thread = row, coalesced.
 constexpr int kPlcIn = 57, kPlcCond = 128, kPlcUnits = 256, kPlcRows = 3 * kPlcUnits;
 struct DevPlc {
+  DevSat sat_g1_in, sat_g1_rec, sat_g2_in, sat_g2_rec;   // per output row (lists = 768), entry.x = column
   const float *dense1_w, *dense1_b;     // [57][128], [128]
   const float *out_w, *out_b;           // [256][20], [20]
   const uint32_t *g1_in, *g1_rec;       // [128/4][768], [256/4][768]
@@ -88,6 +109,7 @@ struct DevPlc {
 // RDOVAE decoder of DRED (src/dred_rdovae_dec.c): cond_size = cond_size2 = 256, i.e. the PLC predictor's GRU geometry
 constexpr int kDredLatent = 80, kDredState = 24, kDredOut = 80;
 struct DevDred {
+  DevSat sat_in[3], sat_rec[3];             // per output row
   const float *state_w[3], *state_b[3];     // state1..3: [24][256], [256]
   const float *dense_w[5], *dense_b[5];     // dec_dense1 [80][256]; dec_dense3/5/7/8 [256][256]
   const float *final_w, *final_b;           // dec_final [2048][80], [80]
@@ -114,6 +136,7 @@ struct DevModel {
   DevSparse b_rec;                          // 48 x 16 dense
   const float *fc_w, *fc_bias, *fc_factor;  // [256][2][16], [2][256], [2][256]
   const uint32_t *rcp_tab;                  // [2048]
+  int has_sat;                              // 1: some int8 pair can saturate vpmaddubsw's s16 (DevSat lists are not empty)
   int rcp_arith;                            // 1: the table equals mid-point MUFU.RCP rounded to 12 bits (checked on this GPU)
   const float *ulaw2lin_tab;                // [256]
   const float *logit_tab;                   // [256]
@@ -149,6 +172,7 @@ struct DevState {
 struct Model {
   DevModel d{};
   void *dev_blob = nullptr;
+  void *dev_codebooks = nullptr;   // tables installed after load (install_codebooks); NULL when they came with the blob
   size_t dev_bytes = 0;
   int nblocks_a = 0, nblocks_b = 0;
   bool has_codebooks = false;
@@ -247,6 +271,10 @@ struct BatchView {
 };
 BatchView batch_view(LPCNetBatch *b);
 int default_features_delay();   // lpcnet_b200_set_model_constants (default 2)
+float default_lpc_gamma();      // ... (default 1.0)
+int current_device();           // the calling thread's current CUDA device (0 if there is none to ask)
+// the process-wide VQ tables of lpcnet_b200_set_codebooks (analysis.cu), empty if none were set
+std::vector<float> default_codebooks();
 // run_frame_network for one frame of the streams with mask != 0 (features: device [B][stride]); the conditioning
 // stays in the batch's frame buffers for the sample segments that follow.
 // state_only: run_frame_network_flush -- the outputs go to a scratch set, the streams' conditioning stays.

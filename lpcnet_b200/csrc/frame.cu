@@ -39,7 +39,10 @@ __global__ void frame_inputs_kernel(FrameArgs A) {
   const int f = r - 2;
   const float *feat = A.features + ((size_t)s * A.total_frames + A.frame0 + f) * A.feature_stride;
   // pitch = (int)floor(.1 + 50*features[18] + 100), clamped to [33,255] (src/lpcnet.c:93-94)
-  int pitch = (int)floor(.1 + (double)(50.f * feat[18]) + 100);
+  // (the conversion of an out-of-range or NaN double is x86's cvttsd2si, INT_MIN, so that a huge or infinite
+  // features[18] clamps to 33 as in the reference build -- CUDA's own conversion saturates to INT_MAX)
+  const double pd = floor(.1 + (double)(50.f * feat[18]) + 100);
+  int pitch = (pd != pd || pd >= 2147483648.0 || pd <= -2147483649.0) ? (int)0x80000000 : (int)pd;
   pitch = pitch > 255 ? 255 : (pitch < 33 ? 33 : pitch);
   if (tid < kFeat) dst[tid] = feat[tid];
   else if (tid < kConvIn) dst[tid] = A.m.embed_pitch[pitch * kPitchEmb + tid - kFeat];

@@ -55,7 +55,8 @@ struct Builder {
 // find_idx_check (parse_lpcnet_weights.c:90-113) + re-tiling.  `idx` NULL means a dense
 // dotp-layout matrix [rows/8][cols/4][8][4] (dump_lpcnet.py:56-60).
 bool pack_sparse(PackedSparse &ps, const int32_t *idx, int idx_len, const int8_t *w, int w_bytes, int rows,
-                 int cols, std::string &err, const char *what, bool slotted = false, int parts = 1, int pad_to = 1) {
+                 int cols, std::string &err, const char *what, bool slotted = false, int parts = 1, int pad_to = 1,
+                 bool no_slots = false) {
   ps.n_groups = rows / 8;
   ps.chunk_start.assign(ps.n_groups + 1, 0);
   std::vector<std::vector<int>> gpos(ps.n_groups);
@@ -65,7 +66,7 @@ bool pack_sparse(PackedSparse &ps, const int32_t *idx, int idx_len, const int8_t
     const int32_t *p = idx;
     while (remain > 0) {
       int nb = *p++;
-      if (nb < 0 || remain < nb + 1 || grp >= ps.n_groups) { err = std::string(what) + ": bad block index stream"; return false; }
+      if (nb < 0 || nb > remain - 1 || grp >= ps.n_groups) { err = std::string(what) + ": bad block index stream"; return false; }
       for (int k = 0; k < nb; k++) {
         int pos = *p++;
         if (pos + 3 >= cols || (pos & 3) || pos < 0) { err = std::string(what) + ": bad block position"; return false; }
@@ -82,13 +83,42 @@ bool pack_sparse(PackedSparse &ps, const int32_t *idx, int idx_len, const int8_t
     total = ps.n_groups * (cols / 4);
   }
   if (w_bytes != 32 * total) { err = std::string(what) + ": weight array size does not match the block count"; return false; }
-  // The AVX2 kernel sums adjacent input pairs in a saturating s16 (vpmaddubsw,
-  // src/vec_avx.h:814-818).  Integer tensor-core accumulation cannot saturate, so bit-exactness
-  // needs 255*(|q0|+|q1|) <= 32767 for every pair -- guaranteed by the training-time WeightClip
-  // (training_tf2/lpcnet.py:287-309).  Refuse blobs that violate it.
-  for (int i = 0; i + 1 < w_bytes; i += 2) {
-    int s = abs((int)w[i]) + abs((int)w[i + 1]);
-    if (255 * s > 32767) { err = std::string(what) + ": int8 pair would saturate vpmaddubsw; not representable bit-exactly"; return false; }
+  // The AVX2 kernel sums adjacent input pairs in a saturating s16 (vpmaddubsw, src/vec_avx.h:814-818); integer
+  // tensor-core accumulation cannot saturate.  Pairs that can saturate (same sign, 255*(|q0|+|q1|) > 32767 -- the
+  // training-time WeightClip bounds adjacent OUTPUTS, not these adjacent inputs, so trained models may hold some) are
+  // zeroed in the MMA operands and listed for the kernels' exact s16 pass (engine.h DevSat).
+  std::vector<int8_t> wz(w, w + w_bytes);
+  struct SatRaw { int grp, r, col; uint32_t ww; };
+  std::vector<SatRaw> sat_raw;
+  {
+    int blk = 0;
+    for (int g = 0; g < ps.n_groups; g++)
+      for (size_t b = 0; b < gpos[g].size(); b++, blk++)
+        for (int r = 0; r < 8; r++)
+          for (int pr = 0; pr < 2; pr++) {
+            const int i = blk * 32 + r * 4 + 2 * pr, q0 = w[i], q1 = w[i + 1];
+            if ((q0 > 0) == (q1 > 0) && q0 != 0 && q1 != 0 && 255 * (abs(q0) + abs(q1)) > 32767) {
+              sat_raw.push_back(SatRaw{g, r, gpos[g][b] + 2 * pr, (uint32_t)(uint8_t)q0 | (uint32_t)(uint8_t)q1 << 8});
+              wz[i] = wz[i + 1] = 0;
+            }
+          }
+  }
+  w = wz.data();      // everything below packs the copy
+  {
+    // lists per unit group (GRU-A: rows are gate-major, group = gate * nug + ug) or per row group
+    const int nug = slotted ? ps.n_groups / 3 : ps.n_groups;
+    std::vector<std::vector<uint2>> lists(nug);
+    for (const SatRaw &e : sat_raw) {
+      const int list = slotted ? e.grp % nug : e.grp, gate = slotted ? e.grp / nug : 0;
+      lists[list].push_back(make_uint2((uint32_t)e.col | (uint32_t)e.r << 16 | (uint32_t)gate << 20, e.ww));
+    }
+    ps.sat_start.assign(nug + 1, 0);
+    ps.sat.clear();
+    for (int l = 0; l < nug; l++) {
+      ps.sat_start[l] = (uint32_t)ps.sat.size();
+      ps.sat.insert(ps.sat.end(), lists[l].begin(), lists[l].end());
+    }
+    ps.sat_start[nug] = (uint32_t)ps.sat.size();
   }
   ps.n_blocks = total;
   // weight pointer of every block, in stream order
@@ -172,7 +202,7 @@ bool pack_sparse(PackedSparse &ps, const int32_t *idx, int idx_len, const int8_t
       ps.slots[gate] = sl < 1 ? 1 : (sl > 3 ? 3 : sl);
     }
     // the kernel's unrolled fast path is built for (1,1,3); anything else runs the generic lists
-    if (!(ps.slots[0] == 1 && ps.slots[1] == 1 && ps.slots[2] == 3) || getenv("LPCNET_B200_NO_SLOTS"))
+    if (!(ps.slots[0] == 1 && ps.slots[1] == 1 && ps.slots[2] == 3) || getenv("LPCNET_B200_NO_SLOTS") || no_slots)
       ps.slots[0] = ps.slots[1] = ps.slots[2] = 0;
     const int ST = ps.slots[0] + ps.slots[1] + ps.slots[2];
     int nchunks = nug * ST;
@@ -241,7 +271,9 @@ __global__ void rcp_check_kernel(const uint32_t *tab, int *mismatch) {
 
 void free_model(Model &m) {
   if (m.dev_blob) cudaFree(m.dev_blob);
+  if (m.dev_codebooks) cudaFree(m.dev_codebooks);
   m.dev_blob = nullptr;
+  m.dev_codebooks = nullptr;
 }
 
 // kiss_fft tables for nfft = 320 (src/kiss_fft.c:409-424, 312-345; factors {5,64,4,16,4,4,4,1}
@@ -387,6 +419,16 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
     if (!pack_sparse(pr, nullptr, 0, reinterpret_cast<const int8_t *>(wr), kRowsB * kNB, kRowsB, kNB, err, "gru_b_recurrent"))
       return false;
   }
+  // models with pairs that can saturate vpmaddubsw run the kernel variant with the exact s16 pass, which is built on
+  // the generic chunk lists and the rcpps table (sample_kernel.cuh launch_tile): re-tile GRU-A without the fixed slots
+  d.has_sat = (pa.sat.size() + pb.sat.size() + pr.sat.size()) > 0 ? 1 : 0;
+  if (d.has_sat && pa.slots[2] != 0) {
+    auto ia = A.find("sparse_gru_a_recurrent_weights_idx"), wa = A.find("sparse_gru_a_recurrent_weights");
+    pa = PackedSparse();
+    if (!pack_sparse(pa, reinterpret_cast<const int32_t *>(ia->second.data), ia->second.size / 4,
+                     reinterpret_cast<const int8_t *>(wa->second.data), wa->second.size, kRowsA, kN, err, "sparse_gru_a", true, 1, 1, true))
+      return false;
+  }
   m.nblocks_a = pa.n_blocks;
   m.nblocks_b = pb.n_blocks;
   auto put_sparse = [&](DevSparse &ds, const PackedSparse &ps) {
@@ -396,6 +438,10 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
     put(reinterpret_cast<const void **>(&ds.pos), ps.pos.data(), ps.pos.size());
     put(reinterpret_cast<const void **>(&ds.w), ps.w.data(), ps.w.size() * 4);
     ds.off = ds.off_fixed = nullptr;
+    ds.sat.n = (int)ps.sat.size();
+    ds.sat.start = nullptr; ds.sat.e = nullptr;
+    put(reinterpret_cast<const void **>(&ds.sat.start), ps.sat_start.data(), ps.sat_start.size() * 4);
+    if (!ps.sat.empty()) put(reinterpret_cast<const void **>(&ds.sat.e), ps.sat.data(), ps.sat.size() * 8);
     for (int k = 0; k < 3; k++) ds.slots[k] = ps.slots[k];
     if (!ps.off.empty()) put(reinterpret_cast<const void **>(&ds.off), ps.off.data(), ps.off.size() * 4);
     if (!ps.off_fixed.empty()) put(reinterpret_cast<const void **>(&ds.off_fixed), ps.off_fixed.data(), ps.off_fixed.size() * 4);
@@ -448,19 +494,27 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
     }
   }
   // [input/4][row] words from the block-sparse stream (absent blocks = 0) or the dense 8x4 layout
-  auto retile = [&](const uint32_t **dst, const char *wname, const char *iname, int cols) -> bool {
+  auto retile = [&](const uint32_t **dst, DevSat *sat, const char *wname, const char *iname, int cols) -> bool {
     auto wi = A.find(wname);
     if (wi == A.end()) { if (err.empty()) err = std::string("missing array ") + wname; return false; }
     const int8_t *w = reinterpret_cast<const int8_t *>(wi->second.data);
     const int wb = wi->second.size;
-    for (int i = 0; i + 1 < wb; i += 2)
-      if (255 * (abs((int)w[i]) + abs((int)w[i + 1])) > 32767) {
-        err = std::string(wname) + ": int8 pair would saturate vpmaddubsw; not representable bit-exactly";
-        return false;
-      }
     std::vector<uint32_t> t((size_t)(cols / 4) * kPlcRows, 0u);
+    // pairs that can saturate vpmaddubsw's s16 leave the dp4a words and go to per-row lists (engine.h DevSat)
+    std::vector<std::vector<uint2>> rows_sat(kPlcRows);
     auto place = [&](int grp, int pos, const int8_t *blk) {
-      for (int r = 0; r < 8; r++) memcpy(&t[(size_t)(pos / 4) * kPlcRows + grp * 8 + r], blk + 4 * r, 4);
+      for (int r = 0; r < 8; r++) {
+        int8_t q[4];
+        memcpy(q, blk + 4 * r, 4);
+        for (int pr = 0; pr < 2; pr++) {
+          const int q0 = q[2 * pr], q1 = q[2 * pr + 1];
+          if ((q0 > 0) == (q1 > 0) && q0 != 0 && q1 != 0 && 255 * (abs(q0) + abs(q1)) > 32767) {
+            rows_sat[grp * 8 + r].push_back(make_uint2((uint32_t)(pos + 2 * pr), (uint32_t)(uint8_t)q0 | (uint32_t)(uint8_t)q1 << 8));
+            q[2 * pr] = q[2 * pr + 1] = 0;
+          }
+        }
+        memcpy(&t[(size_t)(pos / 4) * kPlcRows + grp * 8 + r], q, 4);
+      }
     };
     if (iname) {
       auto ii = A.find(iname);
@@ -469,7 +523,7 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
       int remain = ii->second.size / 4, grp = 0, total = 0;
       while (remain > 0) {
         const int nb = *p++;
-        if (nb < 0 || remain < nb + 1 || grp >= kPlcRows / 8 || (total + nb) * 32 > wb) { err = std::string(iname) + ": bad block index stream"; return false; }
+        if (nb < 0 || nb > remain - 1 || grp >= kPlcRows / 8 || (long long)nb > (long long)wb / 32 - total) { err = std::string(iname) + ": bad block index stream"; return false; }
         for (int k = 0; k < nb; k++) {
           const int pos = *p++;
           if (pos < 0 || (pos & 3) || pos + 3 >= cols) { err = std::string(iname) + ": bad block position"; return false; }
@@ -484,6 +538,13 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
         for (int pos = 0; pos < cols; pos += 4) place(grp, pos, w + ((size_t)grp * (cols / 4) + pos / 4) * 32);
     }
     put(reinterpret_cast<const void **>(dst), t.data(), t.size() * 4);
+    std::vector<uint32_t> start(kPlcRows + 1, 0);
+    std::vector<uint2> flat;
+    for (int r = 0; r < kPlcRows; r++) { start[r] = (uint32_t)flat.size(); flat.insert(flat.end(), rows_sat[r].begin(), rows_sat[r].end()); }
+    start[kPlcRows] = (uint32_t)flat.size();
+    sat->n = (int)flat.size(); sat->start = nullptr; sat->e = nullptr;
+    put(reinterpret_cast<const void **>(&sat->start), start.data(), start.size() * 4);
+    if (!flat.empty()) put(reinterpret_cast<const void **>(&sat->e), flat.data(), flat.size() * 8);
     return true;
   };
   // optional PLC predictor arrays (init_plc_model, training_tf2/dump_plc.py:319-330): all or none
@@ -498,10 +559,10 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
     pk &= put_f(&P.g2_subias, "plc_gru2_subias", 2 * kPlcRows);
     pk &= need("plc_gru1_bias", 2 * kPlcRows * 4) != nullptr;
     pk &= need("plc_gru2_bias", 2 * kPlcRows * 4) != nullptr;
-    pk = pk && retile(&P.g1_in, "plc_gru1_weights", "plc_gru1_weights_idx", kPlcCond);
-    pk = pk && retile(&P.g1_rec, "plc_gru1_recurrent_weights", nullptr, kPlcUnits);
-    pk = pk && retile(&P.g2_in, "plc_gru2_weights", "plc_gru2_weights_idx", kPlcUnits);
-    pk = pk && retile(&P.g2_rec, "plc_gru2_recurrent_weights", nullptr, kPlcUnits);
+    pk = pk && retile(&P.g1_in, &P.sat_g1_in, "plc_gru1_weights", "plc_gru1_weights_idx", kPlcCond);
+    pk = pk && retile(&P.g1_rec, &P.sat_g1_rec, "plc_gru1_recurrent_weights", nullptr, kPlcUnits);
+    pk = pk && retile(&P.g2_in, &P.sat_g2_in, "plc_gru2_weights", "plc_gru2_weights_idx", kPlcUnits);
+    pk = pk && retile(&P.g2_rec, &P.sat_g2_rec, "plc_gru2_recurrent_weights", nullptr, kPlcUnits);
     if (!pk) return false;
     m.has_plc = true;
   }
@@ -526,8 +587,8 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
       const std::string n = gn[k];
       pk &= put_f(&R.g_subias[k], (n + "_subias").c_str(), 2 * kPlcRows);
       pk &= need((n + "_bias").c_str(), 2 * kPlcRows * 4) != nullptr;
-      pk = pk && retile(&R.g_in[k], (n + "_weights").c_str(), (n + "_weights_idx").c_str(), kPlcUnits);
-      pk = pk && retile(&R.g_rec[k], (n + "_recurrent_weights").c_str(), nullptr, kPlcUnits);
+      pk = pk && retile(&R.g_in[k], &R.sat_in[k], (n + "_weights").c_str(), (n + "_weights_idx").c_str(), kPlcUnits);
+      pk = pk && retile(&R.g_rec[k], &R.sat_rec[k], (n + "_recurrent_weights").c_str(), nullptr, kPlcUnits);
     }
     if (!pk) return false;
     m.has_dred = true;
@@ -564,7 +625,9 @@ bool install_codebooks(Model &m, const float *cb, int n, std::string &err) {
   cudaError_t e = cudaMalloc(&dcb, (size_t)want * 4);
   if (e == cudaSuccess) e = cudaMemcpy(dcb, cb, (size_t)want * 4, cudaMemcpyHostToDevice);
   if (e != cudaSuccess) { err = std::string("codebooks: ") + cudaGetErrorString(e); return false; }
-  m.d.codebooks = dcb;  // lives until process exit or the next install (small; intentionally not freed with the model blob)
+  if (m.dev_codebooks) cudaFree(m.dev_codebooks);   // a re-install replaces the earlier tables
+  m.dev_codebooks = dcb;                            // freed with the model (free_model)
+  m.d.codebooks = dcb;
   m.has_codebooks = true;
   return true;
 }

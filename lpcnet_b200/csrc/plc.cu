@@ -307,22 +307,36 @@ __device__ __forceinline__ int32_t dp4a_u8s8(uint32_t a, uint32_t b, int32_t c) 
   return d;
 }
 
+// the pairs of `row` that can saturate vpmaddubsw's s16 (engine.h DevSat; none for clipped models): their weights are
+// zero in the dp4a words and the saturated pair sums are added here
+__device__ __forceinline__ int32_t plc_sat_row(const DevSat &sat, int row, const uint32_t *xq) {
+  int32_t add = 0;
+  if (sat.n) {
+    const int e1 = (int)__ldg(sat.start + row + 1);
+    for (int e = (int)__ldg(sat.start + row); e < e1; e++) add += sat16_pair(__ldg(sat.e + e), reinterpret_cast<const unsigned char *>(xq));
+  }
+  return add;
+}
+
 __device__ __forceinline__ float plc_gru_row(const uint32_t *__restrict__ w_in, const uint32_t *xq_in, int nin4,
                                               const uint32_t *__restrict__ w_rec, const uint32_t *xq_st, float bias_in,
-                                              float bias_rec, int row, float &recur_out) {
+                                              float bias_rec, int row, float &recur_out, const DevSat &sat_in,
+                                              const DevSat &sat_rec) {
   // compute_gruB (nnet.c:326-372): zrh = subias[row] + 0 -> int8 dot products on int32 accumulators seeded
   // with cvtps2dq(16256*t), back to float by * 1/16256 (vec_avx.h:690-755, 790-860)
   int32_t acc = cvt_rne_ref((bias_in + 0.f) * LPCB_SCALE);
   for (int k = 0; k < nin4; k++) acc = dp4a_u8s8(xq_in[k], __ldg(w_in + (size_t)k * kPlcRows + row), acc);
+  acc = (int32_t)((uint32_t)acc + (uint32_t)plc_sat_row(sat_in, row, xq_in));
   int32_t acr = cvt_rne_ref(bias_rec * LPCB_SCALE);
   for (int k = 0; k < kPlcUnits / 4; k++) acr = dp4a_u8s8(xq_st[k], __ldg(w_rec + (size_t)k * kPlcRows + row), acr);
+  acr = (int32_t)((uint32_t)acr + (uint32_t)plc_sat_row(sat_rec, row, xq_st));
   recur_out = (float)acr * LPCB_SCALE_1;
   return (float)acc * LPCB_SCALE_1;
 }
 
 __device__ void plc_gru(const uint32_t *w_in, const uint32_t *w_rec, const float *subias, const float *x_in, int nin,
                         float *state /*global [256]*/, uint32_t *xq_in, uint32_t *xq_st, float *s_state,
-                        const uint32_t *rcp, int t) {
+                        const uint32_t *rcp, int t, const DevSat &sat_in, const DevSat &sat_rec) {
   // vector_ps_to_epi8 of the input and of the state
   unsigned char *qi = reinterpret_cast<unsigned char *>(xq_in), *qs = reinterpret_cast<unsigned char *>(xq_st);
   if (t < nin) qi[t] = (unsigned char)quant_u8_ref(x_in[t]);
@@ -330,11 +344,11 @@ __device__ void plc_gru(const uint32_t *w_in, const uint32_t *w_rec, const float
   qs[t] = (unsigned char)quant_u8_ref(st);
   __syncthreads();
   float rz, rr, rh;
-  float z = plc_gru_row(w_in, xq_in, nin / 4, w_rec, xq_st, subias[t], subias[kPlcRows + t], t, rz);
+  float z = plc_gru_row(w_in, xq_in, nin / 4, w_rec, xq_st, subias[t], subias[kPlcRows + t], t, rz, sat_in, sat_rec);
   float r = plc_gru_row(w_in, xq_in, nin / 4, w_rec, xq_st, subias[kPlcUnits + t], subias[kPlcRows + kPlcUnits + t],
-                        kPlcUnits + t, rr);
+                        kPlcUnits + t, rr, sat_in, sat_rec);
   float h = plc_gru_row(w_in, xq_in, nin / 4, w_rec, xq_st, subias[2 * kPlcUnits + t],
-                        subias[kPlcRows + 2 * kPlcUnits + t], 2 * kPlcUnits + t, rh);
+                        subias[kPlcRows + 2 * kPlcUnits + t], 2 * kPlcUnits + t, rh, sat_in, sat_rec);
   z = sigmoid_ref(z + rz, rcp);
   r = sigmoid_ref(r + rr, rcp);
   h = tanh_ref(h + rh * r, rcp);
@@ -374,9 +388,9 @@ __global__ void __launch_bounds__(256) plc_pred_kernel(PlcArgs A, int fg_pass) {
   }
   __syncthreads();
   plc_gru(A.net.g1_in, A.net.g1_rec, A.net.g1_subias, s_d1, kPlcCond, A.st.gru1 + (size_t)s * kPlcUnits, xq_in, xq_st,
-          s_g1, A.rcp_tab, t);
+          s_g1, A.rcp_tab, t, A.net.sat_g1_in, A.net.sat_g1_rec);
   plc_gru(A.net.g2_in, A.net.g2_rec, A.net.g2_subias, s_g1, kPlcUnits, A.st.gru2 + (size_t)s * kPlcUnits, xq_in, xq_st,
-          s_g2, A.rcp_tab, t);
+          s_g2, A.rcp_tab, t, A.net.sat_g2_in, A.net.sat_g2_rec);
   // plc_out, 256 -> 20, linear: 20 rows is not a multiple of 16, so the reference takes sgemv_accum's scalar
   // loop (vec_avx.h:73-86 of nnet.c) -- separate multiply and add
   if (t < 20) {
@@ -1212,7 +1226,7 @@ void lpcnet_plc_destroy(LPCNetPLCState *st) {
 int lpcnet_plc_load_model(LPCNetPLCState *st, const unsigned char *data, int len) {
   if (!st || st->magic != kPlcMagic) return set_last_error("lpcnet_plc_load_model: state not initialised");
   if (st->batch) { lpcnet_plc_batch_destroy(st->batch); st->batch = nullptr; }
-  st->batch = lpcnet_plc_batch_create(data, len, 1, 0, st->options, 1.0f);
+  st->batch = lpcnet_plc_batch_create(data, len, 1, current_device(), st->options, default_lpc_gamma());   // as lpcnet_load_model
   return st->batch ? 0 : -1;
 }
 

@@ -99,9 +99,9 @@ __global__ void __launch_bounds__(256) c_pred_kernel(PlcArgs A, const uint8_t *m
   }
   __syncthreads();
   plc_gru(A.net.g1_in, A.net.g1_rec, A.net.g1_subias, s_d1, kPlcCond, A.st.gru1 + (size_t)s * kPlcUnits, xq_in, xq_st,
-          s_g1, A.rcp_tab, t);
+          s_g1, A.rcp_tab, t, A.net.sat_g1_in, A.net.sat_g1_rec);
   plc_gru(A.net.g2_in, A.net.g2_rec, A.net.g2_subias, s_g1, kPlcUnits, A.st.gru2 + (size_t)s * kPlcUnits, xq_in, xq_st,
-          s_g2, A.rcp_tab, t);
+          s_g2, A.rcp_tab, t, A.net.sat_g2_in, A.net.sat_g2_rec);
   if (t < 20) {
     float acc;
     if (mode == 4) {

@@ -157,8 +157,12 @@ __device__ __forceinline__ uint32_t fnv1a_bytes(const unsigned char *p, int n) {
 // SUB: the launch advances a sub-range of the batch (SampleArgs::stream_begin / stream_end).  A template parameter
 // because carrying the two bounds in the whole-batch kernel cost 3.5 % at 8 streams per CTA (4.18 -> 4.33 us per
 // step, A/B on one B200): the whole-batch instantiation keeps the constants.
-template <int MT, int VR, bool DEBUG, bool FIX, bool RA, bool SUB = false>
+// SAT: the model holds int8 pairs that can saturate vpmaddubsw's s16 (engine.h DevSat); their weights are zero in the
+// MMA operands and the saturated pair sums are added by a scalar pass after each product.  Built only on the generic
+// variants (FIX = RA = false), so the instantiations clipped models run are unchanged.
+template <int MT, int VR, bool DEBUG, bool FIX, bool RA, bool SUB = false, bool SAT = false>
 __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A) {
+  static_assert(!SAT || (!FIX && !RA), "the s16 pass is built on the generic variants only");
   constexpr int NS = MT * VR;
   constexpr int NV = (VR == 16) ? 4 : 2;   // accumulator registers in use per thread
   constexpr bool CREG = (MT == 1 && VR == 8);   // frame conditioning of GRU-A held in registers (18 per thread)
@@ -256,6 +260,24 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
       if (gate == 0) chunk(acc[0], lo, hi, bw);
       else if (gate == 1) chunk(acc[1], lo, hi, bw);
       else chunk(acc[2], lo, hi, bw);
+    }
+    if (SAT && M.a_rec.sat.n) {
+      // lane (g, t) holds outputs 2t, 2t+1 of the 8-row group for stream g (and g + 8): entry row r belongs to t = r / 2
+      const int e1 = (int)__ldg(M.a_rec.sat.start + ug + 1);
+      for (int e = (int)__ldg(M.a_rec.sat.start + ug); e < e1; e++) {
+        const uint2 f = __ldg(M.a_rec.sat.e + e);
+        const int r = (f.x >> 16) & 7, gate = f.x >> 20;
+        if ((r >> 1) != t) continue;
+        const int v0 = sat16_pair(f, xrowb), v1 = VR == 16 ? sat16_pair(f, xrowb + 8 * kXaStride * 4) : 0;
+#pragma unroll
+        for (int gt = 0; gt < 3; gt++)
+#pragma unroll
+          for (int q = 0; q < 2; q++) {
+            const bool hit = gate == gt && (r & 1) == q;
+            acc[gt][q] += hit ? v0 : 0;
+            acc[gt][2 + q] += hit ? v1 : 0;
+          }
+      }
     }
   };
 
@@ -594,6 +616,24 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
                 for (int mt = 0; mt < MT; mt++)
 #pragma unroll
                   for (int q = 0; q < 4; q++) acc[mt][q] += accn[n][mt][q];
+              if (SAT && M.b_in.sat.n && job % kPartsB == 0) {      // once per row group: on the first K range's job
+                const int rg = job / kPartsB, e1 = (int)__ldg(M.b_in.sat.start + rg + 1);
+                for (int e = (int)__ldg(M.b_in.sat.start + rg); e < e1; e++) {
+                  const uint2 f = __ldg(M.b_in.sat.e + e);
+                  const int r = (f.x >> 16) & 7;
+                  if ((r >> 1) != t) continue;
+#pragma unroll
+                  for (int mt = 0; mt < MT; mt++) {
+                    const unsigned char *xr = xb0 + mt * VR * kXaStride * 4;
+                    const int v0 = sat16_pair(f, xr), v1 = VR == 16 ? sat16_pair(f, xr + 8 * kXaStride * 4) : 0;
+#pragma unroll
+                    for (int q = 0; q < 2; q++) {
+                      acc[mt][q] += (r & 1) == q ? v0 : 0;
+                      acc[mt][2 + q] += (r & 1) == q ? v1 : 0;
+                    }
+                  }
+                }
+              }
               // s_part index: [mt][kind][rg] with job = rg * kPartsB + kind
               slot = (job % kPartsB) * kRGroupsB + job / kPartsB;
             } else {
@@ -613,6 +653,24 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
                     a3 = *reinterpret_cast<const uint32_t *>(xr + 8 * kXbStride * 4 + hi2);
                   }
                   mma_u8s8(acc[mt], a0, a1, a2, a3, bw.x, bw.y);
+                }
+              }
+              if (SAT && M.b_rec.sat.n) {
+                const int e1 = (int)__ldg(M.b_rec.sat.start + rg + 1);
+                for (int e = (int)__ldg(M.b_rec.sat.start + rg); e < e1; e++) {
+                  const uint2 f = __ldg(M.b_rec.sat.e + e);
+                  const int r = (f.x >> 16) & 7;
+                  if ((r >> 1) != t) continue;
+#pragma unroll
+                  for (int mt = 0; mt < MT; mt++) {
+                    const unsigned char *xr = xb0 + mt * VR * kXbStride * 4;
+                    const int v0 = sat16_pair(f, xr), v1 = VR == 16 ? sat16_pair(f, xr + 8 * kXbStride * 4) : 0;
+#pragma unroll
+                    for (int q = 0; q < 2; q++) {
+                      acc[mt][q] += (r & 1) == q ? v0 : 0;
+                      acc[mt][2 + q] += (r & 1) == q ? v1 : 0;
+                    }
+                  }
                 }
               }
               slot = kPartsB * kRGroupsB + rg;
@@ -801,14 +859,17 @@ static cudaError_t launch_tile(const SampleArgs &a, int n_sms, cudaStream_t s) {
   const int NS = MT * VR;
   const size_t smem = make_layout(NS, MT, a.m.a_rec.n_chunks, a.m.b_in.n_chunks, a.m.b_rec.n_chunks).total;
   const bool dbg = a.trace || a.logits;
-  const bool fix = a.m.a_rec.slots[2] != 0;
+  const bool sat = a.m.has_sat != 0;                // exact s16 pass: generic chunk lists, rcpps table (model.cu)
+  const bool fix = a.m.a_rec.slots[2] != 0 && !sat;
   // Arithmetic rcpps when it was verified against the table on this GPU (model.cu): no shared-memory lookups,
   // 2-4 % faster at every tile size (measured).  The trace/logit variants always use the table.
-  const bool ra = a.m.rcp_arith != 0;
+  const bool ra = a.m.rcp_arith != 0 && !sat;
   const bool sub = a.stream_begin != 0 || a.stream_end != 0;
   if (sub && dbg) return cudaErrorInvalidValue;     // the trace / logit builds advance whole batches only
   void (*kern)(const SampleArgs) =
-      dbg ? (fix ? sample_kernel<MT, VR, true, true, false> : sample_kernel<MT, VR, true, false, false>)
+      sat ? (dbg ? sample_kernel<MT, VR, true, false, false, false, true>
+                 : sub ? sample_kernel<MT, VR, false, false, false, true, true> : sample_kernel<MT, VR, false, false, false, false, true>)
+      : dbg ? (fix ? sample_kernel<MT, VR, true, true, false> : sample_kernel<MT, VR, true, false, false>)
       : sub ? (ra ? (fix ? sample_kernel<MT, VR, false, true, true, true> : sample_kernel<MT, VR, false, false, true, true>)
                   : (fix ? sample_kernel<MT, VR, false, true, false, true> : sample_kernel<MT, VR, false, false, false, true>))
       : ra ? (fix ? sample_kernel<MT, VR, false, true, true> : sample_kernel<MT, VR, false, false, true>)

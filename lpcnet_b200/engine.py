@@ -289,6 +289,11 @@ class Batch:
         return bool(self.L.lpcnet_batch_nblocks(self.h, 3))
 
     @property
+    def saturating_pairs(self):
+        """int8 input pairs of the sample network that can saturate vpmaddubsw's s16 (0 for clipped models)"""
+        return self.L.lpcnet_batch_nblocks(self.h, 6)
+
+    @property
     def launch_count(self):
         return int(self.L.lpcnet_batch_launch_count(self.h))
 

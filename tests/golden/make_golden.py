@@ -309,10 +309,32 @@ def bench_hashes(R):
     json.dump(d, open(os.path.join(OUT, "bench_pcm_hashes.json"), "w"), indent=1)
 
 
+def sat(R):
+    """Models whose int8 weights use the whole range (blob.saturating_models): vpmaddubsw's s16 pair sums saturate.
+    Synthesis (3 streams x 10 frames, traces), non-causal PLC with the DC filter (FEATURES_DELAY 0 build, 30 frames) and
+    the RDOVAE decoder through the unmodified reference."""
+    b = blob.saturating_models()
+    d = {"blob_sha256": np.frombuffer(hashlib.sha256(b).digest(), np.uint8)}
+    for s in (0, 5, 9):
+        f = blob.synthetic_features(10, 400 + s)
+        pcm, tr, _ = refpy.RefStream(R, b, blob.stream_seed(s)).run(f, trace=True)
+        d[f"pcm_{s}"], d[f"trace_{s}"] = pcm, tr
+    R0 = refpy.RefLib(0)
+    for s in range(2):
+        x = blob.synthetic_pcm(30, 40 + s)
+        lost = blob.synthetic_loss_pattern(30, 40 + s)
+        d[f"plc_in_{s}"], d[f"plc_lost_{s}"] = x, lost
+        d[f"plc_out_{s}"] = refpy.RefPLC(R0, b, 5, blob.stream_seed(s)).run(x, lost)
+    st, z = dred_inputs()[1]
+    d["dred_state"], d["dred_latents"] = st, z
+    d["dred_features"] = refpy.ref_dred_decode_all(R, b, st, z)
+    np.savez_compressed(os.path.join(OUT, "sat.npz"), **d)
+
+
 if __name__ == "__main__":
     R = refpy.RefLib(2)
-    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc", "encode", "plc_causal", "dred", "plc_edges", "bench"]
+    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc", "encode", "plc_causal", "dred", "plc_edges", "bench", "sat"]
     for name in which:
-        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc, "encode": encode, "plc_causal": plc_causal, "dred": dred, "plc_edges": plc_edges, "bench": bench_hashes}[name](R)
+        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc, "encode": encode, "plc_causal": plc_causal, "dred": dred, "plc_edges": plc_edges, "bench": bench_hashes, "sat": sat}[name](R)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))

@@ -454,3 +454,46 @@ def test_plc_in_place_ignores_the_content_of_lost_frames(eng, plc_blob, opt):
             outs.append(pb.process(x, lost))
         pb.close()
     assert np.array_equal(outs[0], outs[1])
+
+
+def test_out_of_range_pitch_feature_follows_x86(model_blob, orc_model):
+    """features[18] huge: the reference's (int)floor(...) is x86's cvttsd2si (INT_MIN for everything out of range), so
+    the pitch index clamps to 33 -- not to 255 as CUDA's saturating conversion would give (src/lpcnet.c:93-94).
+    Conditioning compared bit for bit with the oracle (which runs the host's own conversion).  Finite values only: an
+    infinite or NaN feature also enters the convolution as a value, and the reference's conditioning is then NaN
+    throughout (its SSE min/max let NaN through) -- noise either way, outside the contract."""
+    F = 6
+    feats = np.stack([blob.synthetic_features(F, 60 + s) for s in range(5)])
+    feats[0, :, 18] = 1e9
+    feats[1, :, 18] = 3e38
+    feats[2, :, 18] = -1e9
+    feats[3, 2:, 18] = -3e38
+    feats[4, :, 18] = 4.2e7            # 50*x + 100 just below 2^31: in range, clamps to 255
+    bt = engine.Batch(model_blob, 5)
+    ga, gb, lpc = bt.frame_network(feats)
+    for s in range(5):
+        st = orcpy.OrcStream(orc_model)
+        for f in range(F):
+            oga, ogb, olpc = st.frame_network(feats[s, f])
+            assert np.array_equal(ga[s, f].view(np.uint32), oga.view(np.uint32)), (s, f)
+            assert np.array_equal(gb[s, f].view(np.uint32), ogb.view(np.uint32)), (s, f)
+    bt.close()
+
+
+def test_single_stream_decoder_takes_process_wide_codebooks(model_blob, golden_decode, codebooks, orc_model):
+    """lpcnet_decoder_create + lpcnet_decoder_load_model of a blob WITHOUT ceps_codebook* arrays: the tables of
+    lpcnet_b200_set_codebooks are installed (an opaque LPCNetDecState cannot reach lpcnet_batch_set_codebooks)."""
+    engine.set_codebooks(codebooks)
+    try:
+        dec = engine.Decoder(model_blob)
+        pk = golden_decode["packets"][:2]
+        got = np.concatenate([dec.decode(p.tobytes()) for p in pk])
+        feats = golden_decode["features"][:2].reshape(8, 36)
+        assert np.array_equal(got, orcpy.OrcStream(orc_model).run(feats)[0])
+        dec.close()
+    finally:
+        engine.set_codebooks(None)
+    dec = engine.Decoder(model_blob)              # no tables anywhere: an error, not a crash
+    with pytest.raises(engine.LPCNetError):
+        dec.decode(golden_decode["packets"][0].tobytes())
+    dec.close()

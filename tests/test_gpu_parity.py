@@ -233,8 +233,12 @@ def test_rejects_bad_blobs(eng, model_blob):
     with pytest.raises(eng.LPCNetError):
         eng.Batch(blob.write_blob(B4), 1)                       # position not a multiple of 4
     B5 = dict(A); w = A["gru_b_recurrent_weights"].copy(); w[:2] = 100; B5["gru_b_recurrent_weights"] = w
+    bt = eng.Batch(blob.write_blob(B5), 1)                      # a pair that can saturate vpmaddubsw: accepted now,
+    assert bt.saturating_pairs == 1 and not bt.fixed_slots      # on the exact s16 pass (tests/test_saturation.py)
+    bt.close()
+    B6 = dict(A); idx = A["gru_b_weights_idx"].copy(); idx[0] = 2**31 - 1; B6["gru_b_weights_idx"] = idx
     with pytest.raises(eng.LPCNetError):
-        eng.Batch(blob.write_blob(B5), 1)                       # would saturate vpmaddubsw
+        eng.Batch(blob.write_blob(B6), 1)                       # block count INT_MAX: no overflow in the bounds check
 
 
 def test_decode_matches_reference_golden(eng, model_blob, golden_decode, codebooks, orc_model):

@@ -145,3 +145,21 @@ def test_oracle_against_reference_over_10s(orc_model, model_blob):
         n = g["block_samples"]
         got = [hashlib.sha256(pcm[k * n:(k + 1) * n].astype("<i2").tobytes()).hexdigest() for k in range(len(pcm) // n)]
         assert got == g["streams"][str(s)], s
+
+
+@pytest.mark.skipif(not refpy.available(2), reason="oracle/_ref not built (needs /root/reference)")
+def test_out_of_range_pitch_feature_against_reference(orclib, model_blob):
+    """features[18] huge / inf / NaN: (int)floor(...) is the host's cvttsd2si in the reference and in the oracle
+    (src/lpcnet.c:93-94): the same conditioning, bit for bit."""
+    import ctypes as C
+    R = refpy.RefLib(2)
+    om = orcpy.OrcModel(orclib, model_blob, 2, 1.0, None)
+    for bad in (1e9, np.inf, -np.inf, np.nan, 4.2e7):
+        f = blob.synthetic_features(4, 60)
+        f[:, 18] = bad
+        rs, st = refpy.RefStream(R, model_blob), orcpy.OrcStream(om)
+        for k in range(4):
+            ga = np.zeros(1152, np.float32); gb = np.zeros(48, np.float32); lp = np.zeros(16, np.float32)
+            R.lib.ref_frame_network(C.c_void_p(rs.h), refpy._p(np.ascontiguousarray(f[k])), refpy._p(ga), refpy._p(gb), refpy._p(lp))
+            oga, ogb, olpc = st.frame_network(f[k])
+            assert np.array_equal(bits(ga), bits(oga)) and np.array_equal(bits(gb), bits(ogb)), (bad, k)
