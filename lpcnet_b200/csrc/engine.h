@@ -28,8 +28,12 @@ constexpr int kRowsB = 3 * kNB;  // 48
 constexpr int kXaStride = kN / 4 + 4;    // words per stream (100)
 constexpr int kXbStride = kNB / 4;       // 4: eight streams x four words = 32 distinct banks
 
-// Phase B1 of the sample kernel: the GRU-B input product of a row group is split into kPartsB K ranges
-// (one warp job each); model.cu pads every range to a multiple of kPadB chunks (the unroll factors 3, 2, 1).
+// GRU-B input product (48 x 384) in the sample kernel: warp w of the 16 forms the K slice of its own 24 units (unit
+// groups w, w+16, w+32) straight from the state bytes it has just produced, one mma.m16n8k32 per 8-row group with the
+// K order [ug w: 2t 2t+1 | ug w+16: 2t 2t+1] (k = 4t..4t+3) and [ug w+32: 2t 2t+1 | 0 0] (k = 16+4t..), t = lane % 4;
+// DevModel::b_in_frag holds the matching B fragments [warp][row group][lane] (absent blocks are zeros).
+constexpr int kBinFragWords = 16 * 6 * 32 * 2;
+// (the block-list form of the same matrix, DevModel::b_in, keeps these packing parameters; the kernel no longer reads it)
 constexpr int kPartsB = 2;
 constexpr int kPadB = 6;
 
@@ -132,7 +136,8 @@ struct DevModel {
   const float *a_diag;                      // [1152]
   DevSparse a_rec;                          // 1152 x 384 block-sparse
   const float *b_subias;                    // [96]
-  DevSparse b_in;                           // 48 x 384 (sparse stream format, dense by default)
+  DevSparse b_in;                           // 48 x 384 (sparse stream format, dense by default): block count, DevSat lists
+  const uint2 *b_in_frag;                   // the same matrix as register-operand B fragments [16][6][32] (see kBinFragWords)
   DevSparse b_rec;                          // 48 x 16 dense
   const float *fc_w, *fc_bias, *fc_factor;  // [256][2][16], [2][256], [2][256]
   const uint32_t *rcp_tab;                  // [2048]

@@ -414,6 +414,39 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
     if (!pack_sparse(pb, reinterpret_cast<const int32_t *>(ib->second.data), ib->second.size / 4,
                      reinterpret_cast<const int8_t *>(wb->second.data), wb->second.size, kRowsB, kN, err, "gru_b", false, kPartsB, kPadB))
       return false;
+    // dense 48 x 384 copy of the GRU-B input matrix (absent blocks and the pairs on the s16 pass are zeros), cut into
+    // the B fragments of the kernel's register-operand product (engine.h kBinFragWords)
+    {
+      std::vector<int8_t> W((size_t)kRowsB * kN, 0);
+      const int32_t *ip = reinterpret_cast<const int32_t *>(ib->second.data);
+      const int8_t *wp = reinterpret_cast<const int8_t *>(wb->second.data);
+      for (int rg = 0; rg < kRowsB / 8; rg++) {
+        const int nb = *ip++;
+        for (int k = 0; k < nb; k++, wp += 32) {
+          const int pos = *ip++;
+          for (int r = 0; r < 8; r++)
+            for (int c = 0; c < 4; c++) W[(size_t)(rg * 8 + r) * kN + pos + c] = wp[r * 4 + c];
+        }
+      }
+      for (int rg = 0; rg < kRowsB / 8; rg++)
+        for (uint32_t e = pb.sat_start[rg]; e < pb.sat_start[rg + 1]; e++) {
+          const int col = pb.sat[e].x & 0xffff, r = (pb.sat[e].x >> 16) & 7;
+          W[(size_t)(rg * 8 + r) * kN + col] = W[(size_t)(rg * 8 + r) * kN + col + 1] = 0;
+        }
+      std::vector<uint32_t> frag(kBinFragWords, 0u);
+      for (int w = 0; w < 16; w++)
+        for (int rg = 0; rg < 6; rg++)
+          for (int lane = 0; lane < 32; lane++) {
+            const int n = lane >> 2, t = lane & 3;
+            const int8_t *row = &W[(size_t)(rg * 8 + n) * kN];
+            auto byte = [&](int ug, int j) { return (uint32_t)(uint8_t)row[ug * 8 + 2 * t + j]; };
+            const uint32_t b0 = byte(w, 0) | byte(w, 1) << 8 | byte(w + 16, 0) << 16 | byte(w + 16, 1) << 24;
+            const uint32_t b1 = byte(w + 32, 0) | byte(w + 32, 1) << 8;
+            frag[((size_t)(w * 6 + rg) * 32 + lane) * 2] = b0;
+            frag[((size_t)(w * 6 + rg) * 32 + lane) * 2 + 1] = b1;
+          }
+      put(reinterpret_cast<const void **>(&d.b_in_frag), frag.data(), frag.size() * 4);
+    }
     const unsigned char *wr = need("gru_b_recurrent_weights", kRowsB * kNB);
     if (!wr) return false;
     if (!pack_sparse(pr, nullptr, 0, reinterpret_cast<const int8_t *>(wr), kRowsB * kNB, kRowsB, kNB, err, "gru_b_recurrent"))

@@ -9,8 +9,11 @@
 //            runs the block-sparse u8 x s8 product as mma.sync.m16n8k32 (streams = M, the 8 rows of a
 //            row group = N, 8 blocks of 4 inputs = K; activations gathered from shared memory),
 //            applies the Pade/rcpps gates in registers and keeps the fp32 state in registers.
-//   phase B1 (all warps)  GRU-B input (48x384) and recurrent (48x16) products, K-split into jobs,
-//            partial int32 sums to shared memory (integer addition is associative, so the split is exact).
+//            The GRU-B input product (48x384) rides on phase A: a warp multiplies the state bytes it has just
+//            produced (its own 24 units, still in registers) with its K slice of the matrix, one MMA per 8-row
+//            group, and adds the partial int32 sums into shared memory (red.shared.add; integer addition is
+//            associative, so the K split over the 16 warps is exact).  The recurrent 48x16 product runs on six
+//            warps at the start of phase A.  No separate product phase, two barriers per step.
 //   phase B2+T (16 lanes per stream) GRU-B gates, then the 8-level dual-FC tree sampler evaluated
 //            speculatively in two rounds of 15 nodes (identical decisions to the sequential descent),
 //            kiss99, mu-law, LPC prediction, de-emphasis and the PCM store.
@@ -31,7 +34,7 @@ constexpr int kRGroupsB = kRowsB / 8;      // 6
 
 struct SmemLayout {
   // byte offsets
-  unsigned wA, posA, offF, csA, wBi, posBi, csBi, wBr, posBr, csBr;
+  unsigned wA, posA, offF, csA, binF, wBr, posBr, csBr;
   unsigned sdA, subB, rcp, u2l, logit;
   unsigned xa, xb, bst, condb, part;
   unsigned usig, upred, lexc, deemph, rng, act, ix, tst, accx;
@@ -53,7 +56,7 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
     // offset lists follow: 4.17 -> 4.13 us per step.  The larger tiles measured 2 % slower in this order
     // (register allocation) and keep the lists in front.
     L.offF = take(kN / 8 * 32 * 4); L.csA = take((kN / 8 + 1) * 4);
-    L.csBi = take((kRGroupsB * kPartsB + 1) * 4);
+    L.binF = take(kBinFragWords * 4);
     L.csBr = take((kRGroupsB + 1) * 4);
     L.sdA = take(kRowsA * 8); L.subB = take(2 * kRowsB * 4);
     L.rcp = take(2048 * 4); L.u2l = take(256 * 4); L.logit = take(256 * 4);
@@ -61,7 +64,7 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
     L.xb = take(NS * kXbStride * 4);
     L.bst = take(NS * 20 * 4);
     L.condb = take(NS * kRowsB * 4);
-    L.part = take(MT * (kPartsB + 1) * kRGroupsB * 128 * 4);
+    L.part = take(MT * 2 * kRGroupsB * 128 * 4);
     L.usig = take(NS * 4); L.upred = take(NS * 4); L.lexc = take(NS * 4);
     L.deemph = take(NS * 4); L.rng = take(4 * NS * 4); L.act = take(NS * 4); L.ix = take(NS * 4);
     L.tst = 0;
@@ -69,13 +72,13 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
     L.fcb = take(4 * 256 * 4);
     L.fcw = take(256 * kFcStride * 4);
     L.wA = take(chA * 256); L.posA = take(chA * 16);
-    L.wBi = take(chBi * 256); L.posBi = take(chBi * 16);
     L.wBr = take(chBr * 256); L.posBr = take(chBr * 16);
     L.total = o;
     return L;
   }
+  (void)chBi;
   L.wA = take(chA * 256); L.posA = take(chA * 16); L.offF = take(kN / 8 * 32 * 4); L.csA = take((kN / 8 + 1) * 4);
-  L.wBi = take(chBi * 256); L.posBi = take(chBi * 16); L.csBi = take((kRGroupsB * kPartsB + 1) * 4);
+  L.binF = take(kBinFragWords * 4);
   L.wBr = take(chBr * 256); L.posBr = take(chBr * 16); L.csBr = take((kRGroupsB + 1) * 4);
   L.sdA = take(kRowsA * 8); L.subB = take(2 * kRowsB * 4);
   L.rcp = take(2048 * 4); L.u2l = take(256 * 4); L.logit = take(256 * 4);
@@ -83,7 +86,7 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
   L.xb = take(NS * kXbStride * 4);
   L.bst = take(NS * 20 * 4);
   L.condb = take(NS * kRowsB * 4);
-  L.part = take(MT * (kPartsB + 1) * kRGroupsB * 128 * 4);
+  L.part = take(MT * 2 * kRGroupsB * 128 * 4);
   L.usig = take(NS * 4); L.upred = take(NS * 4); L.lexc = take(NS * 4);
   L.deemph = take(NS * 4); L.rng = take(4 * NS * 4); L.act = take(NS * 4); L.ix = take(NS * 4);
   L.tst = NS >= 32 ? take(3 * kThreads * 4) : 0;
@@ -182,9 +185,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   uint32_t *s_offA = reinterpret_cast<uint32_t *>(smem + L.posA);   // [chunk][4] packed gather offsets
   uint32_t *s_offF = reinterpret_cast<uint32_t *>(smem + L.offF);   // [ug][lane%4][8] offsets of the fixed chunks
   uint32_t *s_csA = reinterpret_cast<uint32_t *>(smem + L.csA);     // [ug + 1] overflow chunk lists
-  uint32_t *s_wBi = reinterpret_cast<uint32_t *>(smem + L.wBi);
-  uint32_t *s_offBi = reinterpret_cast<uint32_t *>(smem + L.posBi);   // [chunk][lane%4] packed gather offsets
-  uint32_t *s_csBi = reinterpret_cast<uint32_t *>(smem + L.csBi);
+  uint32_t *s_binF = reinterpret_cast<uint32_t *>(smem + L.binF);     // GRU-B input B fragments [warp][row group][lane][2]
   uint32_t *s_wBr = reinterpret_cast<uint32_t *>(smem + L.wBr);
   uint32_t *s_offBr = reinterpret_cast<uint32_t *>(smem + L.posBr);
   uint32_t *s_csBr = reinterpret_cast<uint32_t *>(smem + L.csBr);
@@ -290,9 +291,9 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
     copy_words(s_offA, M.a_rec.off, M.a_rec.n_chunks * 4);
     if (FIX) copy_words(s_offF, M.a_rec.off_fixed, kUGroups * 32);
     copy_words(s_csA, M.a_rec.chunk_start, kUGroups + 1);
-    copy_words(s_wBi, M.b_in.w, M.b_in.n_chunks * 64);
-    copy_words(s_offBi, M.b_in.off, M.b_in.n_chunks * 4);
-    copy_words(s_csBi, M.b_in.chunk_start, kRGroupsB * kPartsB + 1);
+    copy_words(s_binF, reinterpret_cast<const uint32_t *>(M.b_in_frag), kBinFragWords);
+    for (int i = tid; i < MT * 2 * kRGroupsB * 128; i += kThreads) s_part[i] = 0;   // the sums of the GRU-B input product
+                                                                                    // start at zero; phase B2 re-zeroes
     copy_words(s_wBr, M.b_rec.w, M.b_rec.n_chunks * 64);
     copy_words(s_offBr, M.b_rec.off, M.b_rec.n_chunks * 4);
     copy_words(s_csBr, M.b_rec.chunk_start, kRGroupsB + 1);
@@ -473,6 +474,59 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               rp[mt][h][2] = M.e_exc + ((w >> 16) & 0xffu) * kRowsAP + lane_off;
             }
           }
+        // GRU-B recurrent product (48 x 16 on the GRU-B state of the previous step, src/nnet.c:355-361): one row group
+        // per warp on warps 10..15 (never sampler warps at 8 or 16 streams per CTA); phase B2 reads the sums after
+        // the barrier
+        if (warp >= kWarps - kRGroupsB) {
+          const int rg = warp - (kWarps - kRGroupsB);
+          int32_t acc[MT][4];
+#pragma unroll
+          for (int mt = 0; mt < MT; mt++) acc[mt][0] = acc[mt][1] = acc[mt][2] = acc[mt][3] = 0;
+          const unsigned char *xb0 = reinterpret_cast<const unsigned char *>(s_xb + g * kXbStride);
+          for (int c = s_csBr[rg]; c < (int)s_csBr[rg + 1]; c++) {
+            const uint32_t pk = s_offBr[c * 4 + t];
+            const uint2 bw = reinterpret_cast<const uint2 *>(s_wBr)[c * 32 + lane];
+            const uint32_t lo = pk & 0xffffu, hi2 = pk >> 16;
+#pragma unroll
+            for (int mt = 0; mt < MT; mt++) {
+              const unsigned char *xr = xb0 + mt * VR * kXbStride * 4;
+              const uint32_t a0 = *reinterpret_cast<const uint32_t *>(xr + lo), a2 = *reinterpret_cast<const uint32_t *>(xr + hi2);
+              uint32_t a1 = 0, a3 = 0;
+              if (VR == 16) {
+                a1 = *reinterpret_cast<const uint32_t *>(xr + 8 * kXbStride * 4 + lo);
+                a3 = *reinterpret_cast<const uint32_t *>(xr + 8 * kXbStride * 4 + hi2);
+              }
+              mma_u8s8(acc[mt], a0, a1, a2, a3, bw.x, bw.y);
+            }
+          }
+          if (SAT && M.b_rec.sat.n) {
+            const int e1 = (int)__ldg(M.b_rec.sat.start + rg + 1);
+            for (int e = (int)__ldg(M.b_rec.sat.start + rg); e < e1; e++) {
+              const uint2 f = __ldg(M.b_rec.sat.e + e);
+              const int r = (f.x >> 16) & 7;
+              if ((r >> 1) != t) continue;
+#pragma unroll
+              for (int mt = 0; mt < MT; mt++) {
+                const unsigned char *xr = xb0 + mt * VR * kXbStride * 4;
+                const int v0 = sat16_pair(f, xr), v1 = VR == 16 ? sat16_pair(f, xr + 8 * kXbStride * 4) : 0;
+#pragma unroll
+                for (int q = 0; q < 2; q++) {
+                  acc[mt][q] += (r & 1) == q ? v0 : 0;
+                  acc[mt][2 + q] += (r & 1) == q ? v1 : 0;
+                }
+              }
+            }
+          }
+#pragma unroll
+          for (int mt = 0; mt < MT; mt++) {
+            int32_t *dst = s_part + ((mt * 2 + 1) * kRGroupsB + rg) * 128;
+            *reinterpret_cast<int2 *>(dst + g * 8 + 2 * t) = make_int2(acc[mt][0], acc[mt][1]);
+            if (VR == 16) *reinterpret_cast<int2 *>(dst + (g + 8) * 8 + 2 * t) = make_int2(acc[mt][2], acc[mt][3]);
+          }
+        }
+        // the new state bytes of this lane, as A fragments of the GRU-B input product (engine.h kBinFragWords):
+        // qa0 = [ug w: 2t 2t+1 | ug w+16: 2t 2t+1], qa2 = [ug w+32: 2t 2t+1 | 0 0], per stream row
+        uint32_t qa0[MT][NV / 2], qa2[MT][NV / 2];
 #pragma unroll
         for (int u = 0; u < 3; u++) {
           const int ug = warp + u * kWarps;
@@ -547,12 +601,43 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               const float2 za = f2_mul(z, a_old), zh = f2_mul(f2_add(f2_set(1.f), make_float2(-z.x, -z.y)), hh);
               const float2 a_nw = make_float2(za.x + zh.x, za.y + zh.y);
               unsigned short *dst = reinterpret_cast<unsigned short *>(xa_new) + (((sA + 8 * h) * kXaStride * 4 + ug * 8 + 2 * t) >> 1);
+              uint32_t pv;
               if (ixw[mt][h] >> 24) {
                 a_reg[u][mt][h] = a_nw;
-                *dst = (unsigned short)(quant_u8_unit(a_nw.x) | (quant_u8_unit(a_nw.y) << 8));
+                pv = quant_u8_unit(a_nw.x) | (quant_u8_unit(a_nw.y) << 8);
               } else {
                 // an inactive stream keeps its state and the byte pair it already has
-                *dst = reinterpret_cast<const unsigned short *>(xa_cur)[((sA + 8 * h) * kXaStride * 4 + ug * 8 + 2 * t) >> 1];
+                pv = reinterpret_cast<const unsigned short *>(xa_cur)[((sA + 8 * h) * kXaStride * 4 + ug * 8 + 2 * t) >> 1];
+              }
+              *dst = (unsigned short)pv;
+              if (u == 0) qa0[mt][h] = pv;
+              else if (u == 1) qa0[mt][h] |= pv << 16;
+              else qa2[mt][h] = pv;
+            }
+          }
+        }
+        // GRU-B input product (src/nnet.c:353) of this warp's 24 units, operands from registers; the 16 warps' partial
+        // sums meet in shared memory
+        {
+          const uint2 *bf = reinterpret_cast<const uint2 *>(s_binF) + warp * kRGroupsB * 32 + lane;
+          constexpr int PF = NS == 8 ? kRGroupsB : 2;     // B fragments fetched ahead (registers are short above 8 streams)
+          uint2 bw[PF];
+#pragma unroll
+          for (int k = 0; k < PF; k++) bw[k] = bf[k * 32];
+#pragma unroll
+          for (int rg = 0; rg < kRGroupsB; rg++) {
+            const uint2 bcur = bw[rg % PF];
+            if (rg + PF < kRGroupsB) bw[rg % PF] = bf[(rg + PF) * 32];
+#pragma unroll
+            for (int mt = 0; mt < MT; mt++) {
+              int32_t c[4] = {0, 0, 0, 0};
+              mma_u8s8(c, qa0[mt][0], NV == 4 ? qa0[mt][NV / 2 - 1] : 0u, qa2[mt][0], NV == 4 ? qa2[mt][NV / 2 - 1] : 0u, bcur.x, bcur.y);
+              int32_t *dst = s_part + ((mt * 2 + 0) * kRGroupsB + rg) * 128;
+              atomicAdd(dst + g * 8 + 2 * t, c[0]);
+              atomicAdd(dst + g * 8 + 2 * t + 1, c[1]);
+              if (VR == 16) {
+                atomicAdd(dst + (g + 8) * 8 + 2 * t, c[2]);
+                atomicAdd(dst + (g + 8) * 8 + 2 * t + 1, c[3]);
               }
             }
           }
@@ -560,132 +645,6 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
         LPCB_MARK(1);   // phase A (this warp)
         __syncthreads();
         LPCB_MARK(2);   // wait for the other warps
-        // ================= phase B1: GRU-B products =================
-        // jobs 0..11: (row group, K half) of the input product on the new GRU-A state, on warps 0..11; jobs
-        // 12..17: the recurrent product, on warps 12..15 and again 12, 13.  Every job covers all M tiles so
-        // the B fragments are fetched once; the input ranges are padded to whole unroll groups (model.cu),
-        // and the loads of a group are issued before its MMAs.
-        {
-          constexpr int NIN = kRGroupsB * kPartsB, JOBS = NIN + kRGroupsB;
-          constexpr int UB = NS == 8 ? 6 : (MT == 1 ? 3 : (MT == 2 ? 2 : 1));   // chunks in flight
-          constexpr int NA = NS == 8 ? 3 : 1;                                   // independent accumulators
-          static_assert(kPadB % UB == 0, "padding must cover the unroll factor");
-          for (int job = warp; job < JOBS; job = (job >= NIN && job + 4 < JOBS) ? job + 4 : JOBS) {
-            int32_t acc[MT][4];
-#pragma unroll
-            for (int mt = 0; mt < MT; mt++) acc[mt][0] = acc[mt][1] = acc[mt][2] = acc[mt][3] = 0;
-            int slot;
-            if (job < NIN) {
-              int32_t accn[NA][MT][4];
-#pragma unroll
-              for (int n = 0; n < NA; n++)
-#pragma unroll
-                for (int mt = 0; mt < MT; mt++) accn[n][mt][0] = accn[n][mt][1] = accn[n][mt][2] = accn[n][mt][3] = 0;
-              const unsigned char *xb0 = reinterpret_cast<const unsigned char *>(xa_new + g * kXaStride);
-              const int hi = s_csBi[job + 1];
-              for (int c = s_csBi[job]; c < hi; c += UB) {
-                uint2 bw[UB];
-                uint32_t pk[UB], a[UB][MT][4];
-#pragma unroll
-                for (int k = 0; k < UB; k++) {
-                  pk[k] = s_offBi[(c + k) * 4 + t];
-                  bw[k] = reinterpret_cast<const uint2 *>(s_wBi)[(c + k) * 32 + lane];
-                }
-#pragma unroll
-                for (int k = 0; k < UB; k++)
-#pragma unroll
-                  for (int mt = 0; mt < MT; mt++) {
-                    const unsigned char *xr = xb0 + mt * VR * kXaStride * 4;
-                    const uint32_t lo = pk[k] & 0xffffu, hi2 = pk[k] >> 16;
-                    a[k][mt][0] = *reinterpret_cast<const uint32_t *>(xr + lo);
-                    a[k][mt][2] = *reinterpret_cast<const uint32_t *>(xr + hi2);
-                    a[k][mt][1] = a[k][mt][3] = 0;
-                    if (VR == 16) {
-                      a[k][mt][1] = *reinterpret_cast<const uint32_t *>(xr + 8 * kXaStride * 4 + lo);
-                      a[k][mt][3] = *reinterpret_cast<const uint32_t *>(xr + 8 * kXaStride * 4 + hi2);
-                    }
-                  }
-#pragma unroll
-                for (int k = 0; k < UB; k++)
-#pragma unroll
-                  for (int mt = 0; mt < MT; mt++) mma_u8s8(accn[k % NA][mt], a[k][mt][0], a[k][mt][1], a[k][mt][2], a[k][mt][3], bw[k].x, bw[k].y);
-              }
-#pragma unroll
-              for (int n = 0; n < NA; n++)
-#pragma unroll
-                for (int mt = 0; mt < MT; mt++)
-#pragma unroll
-                  for (int q = 0; q < 4; q++) acc[mt][q] += accn[n][mt][q];
-              if (SAT && M.b_in.sat.n && job % kPartsB == 0) {      // once per row group: on the first K range's job
-                const int rg = job / kPartsB, e1 = (int)__ldg(M.b_in.sat.start + rg + 1);
-                for (int e = (int)__ldg(M.b_in.sat.start + rg); e < e1; e++) {
-                  const uint2 f = __ldg(M.b_in.sat.e + e);
-                  const int r = (f.x >> 16) & 7;
-                  if ((r >> 1) != t) continue;
-#pragma unroll
-                  for (int mt = 0; mt < MT; mt++) {
-                    const unsigned char *xr = xb0 + mt * VR * kXaStride * 4;
-                    const int v0 = sat16_pair(f, xr), v1 = VR == 16 ? sat16_pair(f, xr + 8 * kXaStride * 4) : 0;
-#pragma unroll
-                    for (int q = 0; q < 2; q++) {
-                      acc[mt][q] += (r & 1) == q ? v0 : 0;
-                      acc[mt][2 + q] += (r & 1) == q ? v1 : 0;
-                    }
-                  }
-                }
-              }
-              // s_part index: [mt][kind][rg] with job = rg * kPartsB + kind
-              slot = (job % kPartsB) * kRGroupsB + job / kPartsB;
-            } else {
-              const int rg = job - NIN;
-              const unsigned char *xb0 = reinterpret_cast<const unsigned char *>(s_xb + g * kXbStride);
-              for (int c = s_csBr[rg]; c < (int)s_csBr[rg + 1]; c++) {
-                const uint32_t pk = s_offBr[c * 4 + t];
-                const uint2 bw = reinterpret_cast<const uint2 *>(s_wBr)[c * 32 + lane];
-                const uint32_t lo = pk & 0xffffu, hi2 = pk >> 16;
-#pragma unroll
-                for (int mt = 0; mt < MT; mt++) {
-                  const unsigned char *xr = xb0 + mt * VR * kXbStride * 4;
-                  const uint32_t a0 = *reinterpret_cast<const uint32_t *>(xr + lo), a2 = *reinterpret_cast<const uint32_t *>(xr + hi2);
-                  uint32_t a1 = 0, a3 = 0;
-                  if (VR == 16) {
-                    a1 = *reinterpret_cast<const uint32_t *>(xr + 8 * kXbStride * 4 + lo);
-                    a3 = *reinterpret_cast<const uint32_t *>(xr + 8 * kXbStride * 4 + hi2);
-                  }
-                  mma_u8s8(acc[mt], a0, a1, a2, a3, bw.x, bw.y);
-                }
-              }
-              if (SAT && M.b_rec.sat.n) {
-                const int e1 = (int)__ldg(M.b_rec.sat.start + rg + 1);
-                for (int e = (int)__ldg(M.b_rec.sat.start + rg); e < e1; e++) {
-                  const uint2 f = __ldg(M.b_rec.sat.e + e);
-                  const int r = (f.x >> 16) & 7;
-                  if ((r >> 1) != t) continue;
-#pragma unroll
-                  for (int mt = 0; mt < MT; mt++) {
-                    const unsigned char *xr = xb0 + mt * VR * kXbStride * 4;
-                    const int v0 = sat16_pair(f, xr), v1 = VR == 16 ? sat16_pair(f, xr + 8 * kXbStride * 4) : 0;
-#pragma unroll
-                    for (int q = 0; q < 2; q++) {
-                      acc[mt][q] += (r & 1) == q ? v0 : 0;
-                      acc[mt][2 + q] += (r & 1) == q ? v1 : 0;
-                    }
-                  }
-                }
-              }
-              slot = kPartsB * kRGroupsB + rg;
-            }
-#pragma unroll
-            for (int mt = 0; mt < MT; mt++) {
-              int32_t *dst = s_part + (mt * (kPartsB + 1) * kRGroupsB + slot) * 128;
-              *reinterpret_cast<int2 *>(dst + g * 8 + 2 * t) = make_int2(acc[mt][0], acc[mt][1]);
-              if (VR == 16) *reinterpret_cast<int2 *>(dst + (g + 8) * 8 + 2 * t) = make_int2(acc[mt][2], acc[mt][3]);
-            }
-          }
-        }
-        LPCB_MARK(3);   // phase B1
-        __syncthreads();
-        LPCB_MARK(4);
         // ================= phase B2 + T: GRU-B gates, sampling, signal update =================
         {
           if (twarp) {
@@ -712,10 +671,20 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               const int rg = gate * 2 + (l16 >> 3);
               const int e = row * 8 + (l16 & 7);
               int32_t ai = acc_seed(s_subB[i] + s_condb[s * kRowsB + i]);
-#pragma unroll
-              for (int kind = 0; kind < kPartsB; kind++) ai += s_part[((mt * (kPartsB + 1) + kind) * kRGroupsB + rg) * 128 + e];
+              int32_t *pin = s_part + ((mt * 2 + 0) * kRGroupsB + rg) * 128 + e;
+              ai += *pin;
+              *pin = 0;                                   // the next step's partial sums add up from zero
+              if (SAT && M.b_in.sat.n) {
+                // pairs on the exact s16 pass: this lane's row is row l16 % 8 of row group rg
+                const unsigned char *xr = reinterpret_cast<const unsigned char *>(xa_new + s * kXaStride);
+                const int e1 = (int)__ldg(M.b_in.sat.start + rg + 1);
+                for (int q = (int)__ldg(M.b_in.sat.start + rg); q < e1; q++) {
+                  const uint2 f = __ldg(M.b_in.sat.e + q);
+                  if (((f.x >> 16) & 7) == (uint32_t)(l16 & 7)) ai += sat16_pair(f, xr);
+                }
+              }
               zrh[gate] = acc_out(ai);
-              const int32_t ar = acc_seed(s_subB[kRowsB + i]) + s_part[((mt * (kPartsB + 1) + kPartsB) * kRGroupsB + rg) * 128 + e];
+              const int32_t ar = acc_seed(s_subB[kRowsB + i]) + s_part[((mt * 2 + 1) * kRGroupsB + rg) * 128 + e];
               rec[gate] = acc_out(ar);
             }
             const float z = sigmoid_ref(zrh[0] + rec[0], s_rcp);
