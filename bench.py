@@ -280,6 +280,20 @@ def run_aux(args, dev, local_rank, model_blob):
                 "ms_per_call": med_d * 1e3, "gpu_launches": launches, "clocks": clk,
                 "cpu_baseline": "the headline's cpu_baseline (same mode: lpcnet_demo -synthesis per core)"})
     bt.close()
+
+    # ---- north_star's target as stated: CONCURRENT REAL-TIME streams -- 12 500 per GPU (10^5 per 8-GPU box), one
+    # lpcnet_batch_synthesize(n_frames = 1) call per 10 ms frame (the reference's own calling convention,
+    # src/lpcnet.c:279-281), host buffers; sustainable when the p99 wall time of a call stays under 10 ms ----
+    from tools.bench_stream import run as stream_run
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    sr = stream_run(12500, 200, device=local_rank, warm=10)
+    sr["clocks"] = clocks.stop()
+    sr["config"] = "real-time streaming: 12500 live streams on one B200, one 10 ms frame per call"
+    sr["metric"], sr["unit"], sr["value"] = "p99 wall time of one 10 ms frame of all streams", "ms", sr["ms_per_call_p99"]
+    sr["higher_is_better"] = False
+    sr["cpu_baseline"] = "one stream per host core in real time by definition when the headline's per_core_min >= 16000 samples/s"
+    out.append(sr)
     return out
 
 

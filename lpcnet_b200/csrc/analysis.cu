@@ -659,8 +659,12 @@ LPCNetFeatureBatch *lpcnet_feature_batch_create(int n_streams, int device) {
   b->st.e_hist = (float *)(p + o_e); b->st.path = (float *)(p + o_pa); b->st.path_all = (float *)(p + o_al);
   b->st.best_i = (int *)(p + o_bi); b->st.vq_mem = (float *)(p + o_vq);
   {
+    // the VQ tables: lpcnet_b200_set_codebooks, else the ceps_codebook* arrays of the default blob file (the stand-in
+    // for what the reference compiles in, ceps_codebooks.c; api.cu file_codebooks), else none (lpcnet_encode fails)
     std::lock_guard<std::mutex> lk(g_cb_mu);
-    if (!g_codebooks.empty() && upload_codebooks(b, g_codebooks.data(), (int)g_codebooks.size())) {
+    const std::vector<float> from_file = g_codebooks.empty() ? file_codebooks() : std::vector<float>();
+    const std::vector<float> &cb = g_codebooks.empty() ? from_file : g_codebooks;
+    if (!cb.empty() && upload_codebooks(b, cb.data(), (int)cb.size())) {
       lpcnet_feature_batch_destroy(b);
       return nullptr;
     }

@@ -379,6 +379,37 @@ int lpcb::current_device() {
   return d;
 }
 
+std::vector<float> lpcb::file_codebooks() {
+  const char *path = getenv("LPCNET_B200_WEIGHTS");
+  if (!path || !*path) path = "weights_blob.bin";
+  std::vector<float> out;
+  FILE *f = fopen(path, "rb");
+  if (!f) return out;
+  std::vector<unsigned char> data;
+  unsigned char buf[65536];
+  size_t n;
+  while ((n = fread(buf, 1, sizeof(buf), f)) > 0) data.insert(data.end(), buf, buf + n);
+  fclose(f);
+  // DNNw records (src/nnet.h:41-61): 64-byte head {"DNNw", version, type, size, block_size, name[44]} + payload
+  static const char *names[4] = {"ceps_codebook1", "ceps_codebook2", "ceps_codebook3", "ceps_codebook_diff4"};
+  const size_t want[4] = {1024 * 17 * 4, 1024 * 17 * 4, 1024 * 17 * 4, 4096 * 18 * 4};
+  const unsigned char *found[4] = {nullptr, nullptr, nullptr, nullptr};
+  for (size_t off = 0; off + 64 <= data.size();) {
+    int32_t size, block;
+    memcpy(&size, &data[off + 12], 4);
+    memcpy(&block, &data[off + 16], 4);
+    if (size <= 0 || block < size || (size_t)block > data.size() - off - 64 || data[off + 63] != 0) break;
+    for (int k = 0; k < 4; k++)
+      if (!strcmp(reinterpret_cast<const char *>(&data[off + 20]), names[k]) && (size_t)size == want[k]) found[k] = &data[off + 64];
+    off += 64 + (size_t)block;
+  }
+  if (!found[0] || !found[1] || !found[2] || !found[3]) return out;
+  out.resize((want[0] + want[1] + want[2] + want[3]) / 4);
+  size_t o = 0;
+  for (int k = 0; k < 4; k++) { memcpy(reinterpret_cast<char *>(out.data()) + o, found[k], want[k]); o += want[k]; }
+  return out;
+}
+
 BatchView lpcb::batch_view(LPCNetBatch *b) { return BatchView{b->st, &b->model, b->stream, b->n_streams, b->device}; }
 
 int lpcb::batch_frame_network_masked(LPCNetBatch *b, const float *d_features, int stride, const uint8_t *d_mask,
@@ -559,6 +590,7 @@ int lpcnet_batch_nblocks(const LPCNetBatch *b, int which) {
     case 2: return b->model.d.rcp_arith;               // 1: reciprocal estimate computed, 0: table lookup
     case 3: return b->model.d.a_rec.slots[2] != 0;     // 1: GRU-A runs the unrolled fixed-slot path
     case 4: return b->model.d.a_rec.n_chunks;
+    case 7: return b->model.d.small_acc;               // 1: conversion-free seeds (int32 sums proven inside +-2^22)
     case 6: return b->model.d.a_rec.sat.n + b->model.d.b_in.sat.n + b->model.d.b_rec.sat.n;   // int8 pairs on the exact s16 pass
     case 5: return auto_tile(b);                        // streams per CTA the next synthesize call will use
     case 8: case 16: case 32: return (int)sample_kernel_smem(which, b->model.d);   // bytes of shared memory per CTA
@@ -575,8 +607,8 @@ int lpcnet_batch_set_cuda_stream(LPCNetBatch *b, void *s) {
 
 int lpcnet_batch_set_tile(LPCNetBatch *b, int t) {
   if (!b) return fail("null batch");
-  if (t != 0 && t != 8 && t != 16 && t != 32) return fail("tile must be 0, 8, 16 or 32");
-  if (t > b->max_tile) return fail("tile does not fit in shared memory for this model");
+  if (t != 0 && t != 8 && t != 16 && t != 32 && t != 28) return fail("tile must be 0, 8, 16, 32 or 28 (two 8-stream tiles per CTA)");
+  if ((t == 28 ? 16 : t) > b->max_tile) return fail("tile does not fit in shared memory for this model");
   b->tile = t;
   return 0;
 }
@@ -848,8 +880,12 @@ int lpcnet_batch_set_state(LPCNetBatch *b, int s, const LPCNetB200StreamState *i
 /* ---------------------------------------------------------------------------------------------
  * Drop-in lpcnet.h symbols: a one-stream batch behind the reference's opaque state.
  * ------------------------------------------------------------------------------------------- */
+// The state is a handle to device-resident data, not the relocatable POD of the reference (lpcnet_private.h:28-53): a
+// copy by value (memcpy / struct assignment into other memory) would alias one device slot from two places.  `self`
+// makes that detectable: every entry point refuses a state whose address is not the one lpcnet_init wrote.
 struct LPCNetState {
   uint32_t magic;
+  LPCNetState *self;
   LPCNetBatch *batch;
   float *pinned_feat;   // 36 floats
   short *pinned_pcm;    // 160 samples
@@ -864,6 +900,7 @@ int lpcnet_get_size(void) { return (int)sizeof(LPCNetState); }
 int lpcnet_init(LPCNetState *st) {
   memset(st, 0, sizeof(*st));
   st->magic = kMagic;
+  st->self = st;
   return 0;
 }
 
@@ -871,6 +908,16 @@ LPCNetState *lpcnet_create(void) {
   LPCNetState *st = static_cast<LPCNetState *>(calloc(1, sizeof(LPCNetState)));
   if (st) lpcnet_init(st);
   return st;
+}
+
+static bool state_ok(const LPCNetState *st, const char *who) {
+  if (!st) { fail(std::string(who) + ": null state"); return false; }
+  if (st->magic != kMagic) { fail(std::string(who) + ": state not initialised (lpcnet_init / lpcnet_create)"); return false; }
+  if (st->self != st) {
+    fail(std::string(who) + ": this LPCNetState was copied by value; it is a handle to device-resident state and cannot be relocated (INTEGRATION.md)");
+    return false;
+  }
+  return true;
 }
 
 static void state_release(LPCNetState *st) {
@@ -882,12 +929,12 @@ static void state_release(LPCNetState *st) {
 
 void lpcnet_destroy(LPCNetState *st) {
   if (!st) return;
-  state_release(st);
+  if (st->magic == kMagic && st->self == st) state_release(st);   // a by-value copy does not own the device state
   free(st);
 }
 
 int lpcnet_load_model(LPCNetState *st, const unsigned char *data, int len) {
-  if (!st || st->magic != kMagic) return fail("lpcnet_load_model: state not initialised"), -1;
+  if (!state_ok(st, "lpcnet_load_model")) return -1;
   state_release(st);
   int delay; float gamma;
   { std::lock_guard<std::mutex> lk(g_cfg_mu); delay = g_default_delay; gamma = g_default_gamma; }
@@ -900,12 +947,32 @@ int lpcnet_load_model(LPCNetState *st, const unsigned char *data, int len) {
   return 0;
 }
 
+// The reference's lpcnet_create() returns a state with the COMPILED-IN model ready (src/lpcnet.c:184-200, unless it was
+// built -DUSE_WEIGHTS_FILE); callers such as `lpcnet_demo -decode` (src/lpcnet_demo.c:176-189) never load one.  The
+// stand-in for the compiled-in model is a blob file: $LPCNET_B200_WEIGHTS, else ./weights_blob.bin (the name the
+// reference's own USE_WEIGHTS_FILE build reads, src/lpcnet_demo.c:113), loaded on first use.  -1 if there is none.
+static int ensure_default_model(LPCNetState *st, bool decoder) {
+  if (st->batch) return 0;
+  const char *path = getenv("LPCNET_B200_WEIGHTS");
+  if (!path || !*path) path = "weights_blob.bin";
+  FILE *f = fopen(path, "rb");
+  if (!f) return fail(std::string("no model loaded (call lpcnet_load_model first, or provide ") + path + ")");
+  std::vector<unsigned char> data;
+  unsigned char buf[65536];
+  size_t n;
+  while ((n = fread(buf, 1, sizeof(buf), f)) > 0) data.insert(data.end(), buf, buf + n);
+  fclose(f);
+  if (data.empty() || data.size() > 0x7fffffffu) return fail(std::string("cannot use ") + path + " as a model blob");
+  return decoder ? lpcnet_decoder_load_model(reinterpret_cast<LPCNetDecState *>(st), data.data(), (int)data.size())
+                 : lpcnet_load_model(st, data.data(), (int)data.size());
+}
+
 void lpcnet_reset(LPCNetState *st) {
-  if (st && st->batch) lpcnet_batch_reset(st->batch, -1);
+  if (st && st->batch && state_ok(st, "lpcnet_reset")) lpcnet_batch_reset(st->batch, -1);
 }
 
 void lpcnet_synthesize(LPCNetState *st, const float *features, short *output, int N) {
-  if (!st || !st->batch) { fail("lpcnet_synthesize: no model loaded (call lpcnet_load_model first)"); return; }
+  if (!state_ok(st, "lpcnet_synthesize") || (!st->batch && ensure_default_model(st, false))) return;
   if (N <= 0) return;
   if (N > kFrame) { fail("lpcnet_synthesize: N > 160"); return; }
   LPCNetBatch *b = st->batch;
@@ -929,7 +996,7 @@ LPCNetDecState *lpcnet_decoder_create(void) {
 }
 void lpcnet_decoder_destroy(LPCNetDecState *st) {
   if (!st) return;
-  state_release(&st->lpcnet_state);
+  if (st->lpcnet_state.magic == kMagic && st->lpcnet_state.self == &st->lpcnet_state) state_release(&st->lpcnet_state);
   free(st);
 }
 int lpcnet_decoder_load_model(LPCNetDecState *st, const unsigned char *data, int len) {
@@ -938,13 +1005,15 @@ int lpcnet_decoder_load_model(LPCNetDecState *st, const unsigned char *data, int
   // opaque decoder state that cannot reach lpcnet_batch_set_codebooks, from lpcnet_b200_set_codebooks
   LPCNetBatch *b = st->lpcnet_state.batch;
   if (!b->model.has_codebooks) {
-    const std::vector<float> cb = default_codebooks();
+    std::vector<float> cb = default_codebooks();
+    if (cb.empty()) cb = file_codebooks();
     if (!cb.empty() && lpcnet_batch_set_codebooks(b, cb.data(), (int)cb.size())) return -1;
   }
   return 0;
 }
 int lpcnet_decode(LPCNetDecState *st, const unsigned char *buf, short *pcm) {
-  if (!st || !st->lpcnet_state.batch) return fail("lpcnet_decode: no model loaded");
+  if (!st || !state_ok(&st->lpcnet_state, "lpcnet_decode")) return st ? -1 : fail("lpcnet_decode: null state");
+  if (!st->lpcnet_state.batch && ensure_default_model(&st->lpcnet_state, true)) return -1;
   return lpcnet_batch_decode(st->lpcnet_state.batch, buf, 1, pcm, nullptr);
 }
 

@@ -149,6 +149,18 @@ __device__ __forceinline__ uint32_t quant_u8_unit(float x) {
 __device__ __forceinline__ int32_t acc_seed(float v) { return __float2int_rn(v * LPCB_SCALE); }
 __device__ __forceinline__ float acc_out(int32_t acc) { return (float)acc * LPCB_SCALE_1; }
 
+// The same without conversion instructions (F2I / I2F share the 16-lane pipe of MUFU; these run on the FP32 / integer
+// pipes), for models whose int32 sums stay inside (-2^22, 2^22) -- model.cu proves it per model (DevModel::small_acc).
+// v + 1.5*2^23 has ulp 1, so the add itself rounds v to the nearest-even integer k and the bits are 0x4B400000 + k; the
+// integer sums ride on those bits, and subtracting 1.5*2^23 from the result read as a float returns float(sum), exact.
+#define LPCB_MAGIC 12582912.f
+__device__ __forceinline__ int32_t acc_seed_small(float v) {   // rne(v*16256) + 0x4B400000
+  return (int32_t)__float_as_uint(__fadd_rn(v * LPCB_SCALE, LPCB_MAGIC));
+}
+__device__ __forceinline__ float acc_out_small(int32_t biased) {   // float(sum) / 16256 for sum = biased - 0x4B400000
+  return __fadd_rn(__uint_as_float((uint32_t)biased), -LPCB_MAGIC) * LPCB_SCALE_1;
+}
+
 // D += A(u8, 16x32 row) * B(s8, 32x8 col), int32 accumulate.  SASS: IMMA.16832.U8.S8
 __device__ __forceinline__ void mma_u8s8(int32_t (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
                                          uint32_t b0, uint32_t b1) {

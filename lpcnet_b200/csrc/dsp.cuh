@@ -122,7 +122,9 @@ struct DspTables {
 };
 
 // lpc_from_cepstrum (src/freq.c:310-320) and everything below it; one thread per (stream, frame).
-__device__ void lpc_from_cepstrum_dev(const DspTables &M, const float *cepstrum, float *lpc, const Scratch &S) {
+// err_out (optional): the prediction error lpcn_lpc returns (the return value of the reference's lpc_from_cepstrum)
+__device__ void lpc_from_cepstrum_dev(const DspTables &M, const float *cepstrum, float *lpc, const Scratch &S,
+                                      float *err_out = nullptr) {
   float tmp[18], Ex[18];
   for (int i = 0; i < 18; i++) tmp[i] = cepstrum[i];
   tmp[0] += 4;
@@ -181,6 +183,7 @@ __device__ void lpc_from_cepstrum_dev(const DspTables &M, const float *cepstrum,
       if (error < .001f * ac[0]) break;
     }
   }
+  if (err_out) *err_out = error;
 }
 
 }  // namespace

@@ -141,6 +141,7 @@ struct DevModel {
   DevSparse b_rec;                          // 48 x 16 dense
   const float *fc_w, *fc_bias, *fc_factor;  // [256][2][16], [2][256], [2][256]
   const uint32_t *rcp_tab;                  // [2048]
+  int small_acc;                            // 1: every int32 sum of the sample network stays inside (-2^22, 2^22) (proven at load)
   int has_sat;                              // 1: some int8 pair can saturate vpmaddubsw's s16 (DevSat lists are not empty)
   int rcp_arith;                            // 1: the table equals mid-point MUFU.RCP rounded to 12 bits (checked on this GPU)
   const float *ulaw2lin_tab;                // [256]
@@ -280,6 +281,9 @@ float default_lpc_gamma();      // ... (default 1.0)
 int current_device();           // the calling thread's current CUDA device (0 if there is none to ask)
 // the process-wide VQ tables of lpcnet_b200_set_codebooks (analysis.cu), empty if none were set
 std::vector<float> default_codebooks();
+// ... and the ceps_codebook1/2/3 + ceps_codebook_diff4 arrays of $LPCNET_B200_WEIGHTS or ./weights_blob.bin (the file
+// that stands in for the reference's compiled-in model and tables), empty if there is no such file or no such arrays
+std::vector<float> file_codebooks();
 // run_frame_network for one frame of the streams with mask != 0 (features: device [B][stride]); the conditioning
 // stays in the batch's frame buffers for the sample segments that follow.
 // state_only: run_frame_network_flush -- the outputs go to a scratch set, the streams' conditioning stays.

@@ -375,6 +375,7 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
 
   // The kernels seed their int32 accumulators with cvt.rni(16256*t) and skip the out-of-range fix-up of
   // cvtps2dq (-> 0x80000000): prove here that no pre-activation t can reach 2^31/16256 for states in [-1,1].
+  double ta_bound = 0, tb_bound = 0;
   {
     auto amax = [](const unsigned char *p, size_t n) {
       const float *f = reinterpret_cast<const float *>(p);
@@ -399,6 +400,7 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
     const double tb = amax(A["gru_b_subias"].data, 2 * kRowsB) + cond_bound("gru_b_dense_feature_bias", "gru_b_dense_feature_weights", kRowsB);
     const double lim = 2147483648.0 / 16256.0 * 0.99;
     if (!(ta < lim) || !(tb < lim)) { err = "model pre-activations can exceed the int32 accumulator seed range (or contain NaN)"; return false; }
+    ta_bound = ta; tb_bound = tb;
   }
 
   // int8 matrices
@@ -451,6 +453,31 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
     if (!wr) return false;
     if (!pack_sparse(pr, nullptr, 0, reinterpret_cast<const int8_t *>(wr), kRowsB * kNB, kRowsB, kNB, err, "gru_b_recurrent"))
       return false;
+  }
+  // The fast kernel variants seed and read their int32 sums through float bit patterns (bitexact.cuh acc_seed_small),
+  // which is exact while |seed + sum of products| < 2^22: bound it per row (u8 activations are at most 255).
+  {
+    auto row_l1 = [](const int32_t *idx, const int8_t *w, int n_groups, int dense_blocks) {   // max over rows of sum |w|
+      double worst = 0;
+      for (int g = 0; g < n_groups; g++) {
+        const int nb = idx ? *idx++ : dense_blocks;
+        double l1[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int k = 0; k < nb; k++, w += 32) {
+          if (idx) idx++;
+          for (int r = 0; r < 8; r++)
+            for (int c = 0; c < 4; c++) l1[r] += abs((int)w[r * 4 + c]);
+        }
+        for (int r = 0; r < 8; r++) worst = l1[r] > worst ? l1[r] : worst;
+      }
+      return worst;
+    };
+    auto ia = A.find("sparse_gru_a_recurrent_weights_idx"), wa = A.find("sparse_gru_a_recurrent_weights");
+    auto ib = A.find("gru_b_weights_idx"), wb = A.find("gru_b_weights");
+    const double la = row_l1(reinterpret_cast<const int32_t *>(ia->second.data), reinterpret_cast<const int8_t *>(wa->second.data), kRowsA / 8, 0);
+    const double lb = row_l1(reinterpret_cast<const int32_t *>(ib->second.data), reinterpret_cast<const int8_t *>(wb->second.data), kRowsB / 8, 0);
+    const double lr = row_l1(nullptr, reinterpret_cast<const int8_t *>(A["gru_b_recurrent_weights"].data), kRowsB / 8, kNB / 4);
+    const double lim22 = 4194304.0 * 0.98;
+    d.small_acc = (ta_bound * 16256.0 + 255.0 * la < lim22) && (tb_bound * 16256.0 + 255.0 * (lb > lr ? lb : lr) < lim22) ? 1 : 0;
   }
   // models with pairs that can saturate vpmaddubsw run the kernel variant with the exact s16 pass, which is built on
   // the generic chunk lists and the rcpps table (sample_kernel.cuh launch_tile): re-tile GRU-A without the fixed slots

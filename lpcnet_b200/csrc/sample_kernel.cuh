@@ -46,11 +46,12 @@ struct SmemLayout {
 constexpr int kFcStride = 36;   // 32 weights per node padded so that 8 lanes' 16-byte reads hit disjoint banks
 __host__ __device__ inline bool fc_resident(int NS) { return NS <= 32; }
 
-__host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int chBi, int chBr) {
+// G: tiles per CTA (1, or 2 as two groups of 8 warps: the per-tile buffers then exist once per group)
+__host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int chBi, int chBr, int G = 1) {
   SmemLayout L;
   unsigned o = 0;
   auto take = [&](unsigned bytes) { unsigned r = o; o += (bytes + 15u) & ~15u; return r; };
-  if (NS == 8) {
+  if (NS == 8 && G == 1) {
     // 8 streams per CTA: the arrays whose size depends on the tile shape only come first, so their offsets fold to
     // constants (immediate operands instead of live registers or re-computed sums); the model-sized weight and
     // offset lists follow: 4.17 -> 4.13 us per step.  The larger tiles measured 2 % slower in this order
@@ -82,15 +83,15 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
   L.wBr = take(chBr * 256); L.posBr = take(chBr * 16); L.csBr = take((kRGroupsB + 1) * 4);
   L.sdA = take(kRowsA * 8); L.subB = take(2 * kRowsB * 4);
   L.rcp = take(2048 * 4); L.u2l = take(256 * 4); L.logit = take(256 * 4);
-  L.xa = take(2 * NS * kXaStride * 4);
-  L.xb = take(NS * kXbStride * 4);
-  L.bst = take(NS * 20 * 4);
-  L.condb = take(NS * kRowsB * 4);
-  L.part = take(MT * 2 * kRGroupsB * 128 * 4);
-  L.usig = take(NS * 4); L.upred = take(NS * 4); L.lexc = take(NS * 4);
-  L.deemph = take(NS * 4); L.rng = take(4 * NS * 4); L.act = take(NS * 4); L.ix = take(NS * 4);
+  L.xa = take(G * 2 * NS * kXaStride * 4);
+  L.xb = take(G * NS * kXbStride * 4);
+  L.bst = take(G * NS * 20 * 4);
+  L.condb = take(G * NS * kRowsB * 4);
+  L.part = take(G * MT * 2 * kRGroupsB * 128 * 4);
+  L.usig = take(G * NS * 4); L.upred = take(G * NS * 4); L.lexc = take(G * NS * 4);
+  L.deemph = take(G * NS * 4); L.rng = take(G * 4 * NS * 4); L.act = take(G * NS * 4); L.ix = take(G * NS * 4);
   L.tst = NS >= 32 ? take(3 * kThreads * 4) : 0;
-  L.accx = NS == 8 ? take(12 * 3 * 32 * 8) : 0;   // GRU-A sums computed ahead for the sampler warps' unit groups
+  L.accx = NS == 8 && G == 1 ? take(12 * 3 * 32 * 8) : 0;   // GRU-A sums computed ahead for the sampler warps' unit groups
   L.fcb = take(4 * 256 * 4);
   L.fcw = fc_resident(NS) ? take(256 * kFcStride * 4) : 0;
   L.total = o;
@@ -163,12 +164,20 @@ __device__ __forceinline__ uint32_t fnv1a_bytes(const unsigned char *p, int n) {
 // SAT: the model holds int8 pairs that can saturate vpmaddubsw's s16 (engine.h DevSat); their weights are zero in the
 // MMA operands and the saturated pair sums are added by a scalar pass after each product.  Built only on the generic
 // variants (FIX = RA = false), so the instantiations clipped models run are unchanged.
-template <int MT, int VR, bool DEBUG, bool FIX, bool RA, bool SUB = false, bool SAT = false>
+// G = 2: two independent 8-stream tiles per CTA, each advanced by its own group of 8 warps on its own named barrier,
+// sharing the one resident copy of the weights (two CTAs per SM cannot fit: 184 KB of shared memory each).  The
+// groups run out of phase, so the serial sampler phase of one tile (2 busy warps of its 8) hides under the gate
+// phase of the other: the throughput schedule for batches of more than one 8-stream tile per SM.
+template <int MT, int VR, bool DEBUG, bool FIX, bool RA, bool SUB = false, bool SAT = false, int G = 1>
 __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A) {
   static_assert(!SAT || (!FIX && !RA), "the s16 pass is built on the generic variants only");
+  static_assert(G == 1 || (G == 2 && MT == 1 && VR == 8 && !DEBUG), "two groups: 8-stream tiles, production kernel");
+  constexpr int WG = kWarps / G, TG = kThreads / G;   // warps / threads that advance one tile
+  constexpr int UW = kUGroups / WG;                   // unit groups per warp (3, or 6 with two groups)
+  constexpr int US = UW / 3;                          // K slices of the GRU-B input product per warp
   constexpr int NS = MT * VR;
   constexpr int NV = (VR == 16) ? 4 : 2;   // accumulator registers in use per thread
-  constexpr bool CREG = (MT == 1 && VR == 8);   // frame conditioning of GRU-A held in registers (18 per thread)
+  constexpr bool CREG = (MT == 1 && VR == 8 && G == 1);   // frame conditioning of GRU-A held in registers (18 per thread)
   constexpr bool FCS = NS <= 32;            // dual_fc resident in shared memory (fc_resident)
   // 32 streams per CTA: phase A has no registers to spare, so the three phase-T values each thread carries
   // from step to step wait in shared memory while phase A runs (measured +2 %; -2 % for the smaller tiles)
@@ -176,10 +185,10 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   // 8 streams per CTA: while four warps run phase T of step i, the other twelve already form the recurrent GRU-A
   // sums of step i+1 (they need only the state of step i): their own three unit groups into registers and one
   // of the sampler warps' twelve into shared memory.  Phase A of step i+1 then starts at the gates.
-  constexpr bool OVL = (MT == 1 && VR == 8);
+  constexpr bool OVL = (MT == 1 && VR == 8 && G == 1);
   extern __shared__ __align__(16) unsigned char smem[];
   const DevModel &M = A.m;
-  const SmemLayout L = make_layout(NS, MT, M.a_rec.n_chunks, M.b_in.n_chunks, M.b_rec.n_chunks);
+  const SmemLayout L = make_layout(NS, MT, M.a_rec.n_chunks, M.b_in.n_chunks, M.b_rec.n_chunks, G);
 
   uint32_t *s_wA = reinterpret_cast<uint32_t *>(smem + L.wA);
   uint32_t *s_offA = reinterpret_cast<uint32_t *>(smem + L.posA);   // [chunk][4] packed gather offsets
@@ -214,8 +223,20 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   const int fc_stride = FCS ? kFcStride : 32;
   const float *fc_bf = reinterpret_cast<const float *>(smem + L.fcb);
 
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // tid / warp: position within the group that advances this thread's tile (the whole CTA when G = 1)
+  const int tid0 = threadIdx.x, grp_id = G == 1 ? 0 : tid0 / TG;
+  const int tid = tid0 - grp_id * TG, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2, t = lane & 3;
+  if (G > 1) {
+    s_xa += grp_id * 2 * NS * kXaStride; s_xb += grp_id * NS * kXbStride; s_bst += grp_id * NS * 20;
+    s_condb += grp_id * NS * kRowsB; s_part += grp_id * MT * 2 * kRGroupsB * 128;
+    s_usig += grp_id * NS; s_upred += grp_id * NS; s_lexc += grp_id * NS; s_deemph += grp_id * NS;
+    s_rng += grp_id * 4 * NS; s_act += grp_id * NS; s_ix += grp_id * NS;
+  }
+  auto gsync = [&]() {
+    if (G == 1) __syncthreads();
+    else asm volatile("bar.sync %0, %1;" ::"r"(1 + grp_id), "n"(TG) : "memory");
+  };
   const int B = A.n_streams;                                   // row stride of the per-frame arrays
   const int Bend = SUB && A.stream_end ? A.stream_end : B;      // this launch advances streams [sbegin, Bend)
   const int sbegin = SUB ? A.stream_begin : 0;
@@ -285,19 +306,19 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   // ---- one-time: weights, index lists and tables into shared memory ----
   {
     auto copy_words = [&](uint32_t *dst, const uint32_t *src, int n) {
-      for (int i = tid; i < n; i += kThreads) dst[i] = __ldg(src + i);
+      for (int i = tid0; i < n; i += kThreads) dst[i] = __ldg(src + i);
     };
     copy_words(s_wA, M.a_rec.w, M.a_rec.n_chunks * 64);
     copy_words(s_offA, M.a_rec.off, M.a_rec.n_chunks * 4);
     if (FIX) copy_words(s_offF, M.a_rec.off_fixed, kUGroups * 32);
     copy_words(s_csA, M.a_rec.chunk_start, kUGroups + 1);
     copy_words(s_binF, reinterpret_cast<const uint32_t *>(M.b_in_frag), kBinFragWords);
-    for (int i = tid; i < MT * 2 * kRGroupsB * 128; i += kThreads) s_part[i] = 0;   // the sums of the GRU-B input product
+    for (int i = tid0; i < G * MT * 2 * kRGroupsB * 128; i += kThreads) (s_part - grp_id * MT * 2 * kRGroupsB * 128)[i] = 0;   // the sums of the GRU-B input product
                                                                                     // start at zero; phase B2 re-zeroes
     copy_words(s_wBr, M.b_rec.w, M.b_rec.n_chunks * 64);
     copy_words(s_offBr, M.b_rec.off, M.b_rec.n_chunks * 4);
     copy_words(s_csBr, M.b_rec.chunk_start, kRGroupsB + 1);
-    for (int i = tid; i < kRowsA; i += kThreads) {
+    for (int i = tid0; i < kRowsA; i += kThreads) {
       const int k = (i >> 3) * 16 + ((i & 7) >> 1) * 4 + (i & 1);   // [gate*48 + ug][lane%4][.]
       s_sdA[k] = __ldg(M.a_subias_rec + i);
       s_sdA[k + 2] = __ldg(M.a_diag + i);
@@ -308,27 +329,29 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
     copy_words(reinterpret_cast<uint32_t *>(s_logit), reinterpret_cast<const uint32_t *>(M.logit_tab), 256);
     {
       float *fb = reinterpret_cast<float *>(smem + L.fcb);
-      for (int i = tid; i < 512; i += kThreads) { fb[i] = __ldg(M.fc_bias + i); fb[512 + i] = __ldg(M.fc_factor + i); }
+      for (int i = tid0; i < 512; i += kThreads) { fb[i] = __ldg(M.fc_bias + i); fb[512 + i] = __ldg(M.fc_factor + i); }
     }
     if (FCS) {
       float *fw = reinterpret_cast<float *>(smem + L.fcw);
-      for (int i = tid; i < 256 * 32; i += kThreads) fw[(i >> 5) * kFcStride + (i & 31)] = __ldg(M.fc_w + i);
+      for (int i = tid0; i < 256 * 32; i += kThreads) fw[(i >> 5) * kFcStride + (i & 31)] = __ldg(M.fc_w + i);
     }
   }
+  __syncthreads();     // the groups go their own ways from here
 
 #ifdef LPCB_PHASE_CLOCKS
   long long clk_[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, last_ = clock64();
 #endif
   const int n_tiles = (Bend - sbegin + NS - 1) / NS;
-  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+  if (G > 1 && grp_id == 1) __nanosleep(1800);     // start half a step apart; the phases keep the groups apart afterwards
+  for (int tile = blockIdx.x * G + grp_id; tile < n_tiles; tile += gridDim.x * G) {
     const int stream0 = sbegin + tile * NS;
-    __syncthreads();
+    gsync();
     // ---- load the tile's stream state ----
-    float2 a_reg[3][MT][NV / 2];
+    float2 a_reg[UW][MT][NV / 2];
     int cur = 0;
 #pragma unroll
-    for (int u = 0; u < 3; u++) {
-      const int ug = warp + u * kWarps;
+    for (int u = 0; u < UW; u++) {
+      const int ug = warp + u * WG;
 #pragma unroll
       for (int mt = 0; mt < MT; mt++) {
 #pragma unroll
@@ -343,7 +366,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
         }
       }
     }
-    for (int i = tid; i < NS * 16; i += kThreads) {
+    for (int i = tid; i < NS * 16; i += TG) {
       const int s = i >> 4, j = i & 15;
       const int gs = min(stream0 + s, Bend - 1);
       float v = A.st.gru_b[(size_t)gs * kNB + j];
@@ -365,29 +388,29 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
       int32_t acc[3][4];
 #pragma unroll
       for (int u = 0; u < 3; u++) {
-        gru_a_product(warp + u * kWarps, xa_buf, acc);
+        gru_a_product(warp + u * WG, xa_buf, acc);
 #pragma unroll
         for (int gate = 0; gate < 3; gate++) { accp[OVL ? u : 0][gate][0] = acc[gate][0]; accp[OVL ? u : 0][gate][1] = acc[gate][1]; }
       }
       const int e = warp - 4;                              // 0..11: job e / 4 of sampler warp e % 4
-      gru_a_product((e & 3) + kWarps * (e >> 2), xa_buf, acc);
+      gru_a_product((e & 3) + WG * (e >> 2), xa_buf, acc);
 #pragma unroll
       for (int gate = 0; gate < 3; gate++) s_accx[(e * 3 + gate) * 32 + lane] = make_int2(acc[gate][0], acc[gate][1]);
     };
-    for (int s = tid; s < NS; s += kThreads) {
+    for (int s = tid; s < NS; s += TG) {
       const int gs = min(stream0 + s, Bend - 1);
       s_deemph[s] = A.st.deemph[gs];
       s_lexc[s] = A.st.last_exc[gs];
 #pragma unroll
       for (int k = 0; k < 4; k++) s_rng[k * NS + s] = A.st.rng[(size_t)gs * 4 + k];
     }
-    __syncthreads();
+    gsync();
     if (OVL && !twarp) product_ahead(s_xa + cur * NS * kXaStride);   // sums for the tile's first step
 
     for (int f = 0; f < A.n_frames; f++) {
       // ---- frame prologue: LPC, GRU-B conditioning, active flags ----
       t_lpc = A.lpc[((size_t)f * B + tgs) * 16 + l16];
-      for (int i = tid; i < NS * kRowsB; i += kThreads) {
+      for (int i = tid; i < NS * kRowsB; i += TG) {
         const int s = i / kRowsB, j = i % kRowsB;
         const int gs = min(stream0 + s, Bend - 1);
         s_condb[i] = A.cond_b[((size_t)f * B + gs) * kRowsB + j];
@@ -398,12 +421,20 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
         my_act = (gs < Bend) ? (int)A.active[(size_t)f * B + gs] : 0;
         s_act[tid] = my_act;
       }
-      const int any_act = __syncthreads_or(my_act);
+      int any_act;
+      if (G == 1) {
+        any_act = __syncthreads_or(my_act);
+      } else {
+        gsync();
+        any_act = 0;
+#pragma unroll
+        for (int k = 0; k < NS; k++) any_act |= s_act[k];
+      }
       const size_t out_base = (size_t)(A.frame0 + f) * A.spf;
       if (!any_act) {
         // warm-up frames: N zeros, nothing else moves (src/lpcnet.c:239-243)
         {
-          for (int i = tid; i < NS * A.spf; i += kThreads) {
+          for (int i = tid; i < NS * A.spf; i += TG) {
             const int s = i / A.spf, k = i % A.spf;
             if (stream0 + s < Bend) {
               A.pcm[(size_t)(stream0 + s) * row_len + out_base + k] = 0;
@@ -414,7 +445,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             }
           }
           if (DEBUG && A.logits) {
-            for (size_t i = tid; i < (size_t)NS * A.spf * 256; i += kThreads) {
+            for (size_t i = tid; i < (size_t)NS * A.spf * 256; i += TG) {
               const int s = (int)(i / ((size_t)A.spf * 256));
               const size_t r = i % ((size_t)A.spf * 256);
               if (stream0 + s < Bend) A.logits[((size_t)(stream0 + s) * row_len + out_base) * 256 + r] = 0.f;
@@ -438,16 +469,16 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
         }
       };
       if (twarp) predict();
-      if (TST) { s_tst[tid] = t_x; s_tst[kThreads + tid] = t_lpc; s_tst[2 * kThreads + tid] = t_pred; }
-      __syncthreads();
+      if (TST) { s_tst[tid] = t_x; s_tst[TG + tid] = t_lpc; s_tst[2 * TG + tid] = t_pred; }
+      gsync();
 
       const float *condA_f = A.cond_a + (size_t)f * B * kRowsAP;
-      float2 cond_reg[3][3];
+      float2 cond_reg[UW][3];
       if (CREG) {
         const int gs = min(stream0 + g, Bend - 1);
 #pragma unroll
         for (int u = 0; u < 3; u++)
-          ldg_zrh(condA_f + (size_t)gs * kRowsAP + ((warp + u * kWarps) * 4 + t) * 8, cond_reg[u][0], cond_reg[u][1], cond_reg[u][2]);
+          ldg_zrh(condA_f + (size_t)gs * kRowsAP + ((warp + u * WG) * 4 + t) * 8, cond_reg[u][0], cond_reg[u][1], cond_reg[u][2]);
       }
 
       LPCB_MARK(0);   // frame prologue and everything outside the step loop
@@ -477,8 +508,8 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
         // GRU-B recurrent product (48 x 16 on the GRU-B state of the previous step, src/nnet.c:355-361): one row group
         // per warp on warps 10..15 (never sampler warps at 8 or 16 streams per CTA); phase B2 reads the sums after
         // the barrier
-        if (warp >= kWarps - kRGroupsB) {
-          const int rg = warp - (kWarps - kRGroupsB);
+        if (warp >= WG - kRGroupsB) {
+          const int rg = warp - (WG - kRGroupsB);
           int32_t acc[MT][4];
 #pragma unroll
           for (int mt = 0; mt < MT; mt++) acc[mt][0] = acc[mt][1] = acc[mt][2] = acc[mt][3] = 0;
@@ -526,10 +557,11 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
         }
         // the new state bytes of this lane, as A fragments of the GRU-B input product (engine.h kBinFragWords):
         // qa0 = [ug w: 2t 2t+1 | ug w+16: 2t 2t+1], qa2 = [ug w+32: 2t 2t+1 | 0 0], per stream row
-        uint32_t qa0[MT][NV / 2], qa2[MT][NV / 2];
+        // (with two groups a warp owns two such K slices: unit groups w + 8*set + 16*slot)
+        uint32_t qa0[US][MT][NV / 2], qa2[US][MT][NV / 2];
 #pragma unroll
-        for (int u = 0; u < 3; u++) {
-          const int ug = warp + u * kWarps;
+        for (int u = 0; u < UW; u++) {
+          const int ug = warp + u * WG;
 #pragma unroll
           for (int mt = 0; mt < MT; mt++) {
             const int sA = mt * VR + g;
@@ -540,14 +572,14 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             for (int h = 0; h < NV / 2; h++) {
               const int gs = min(stream0 + sA + 8 * h, Bend - 1);
               if (CREG) { cv[0][h] = cond_reg[u][0]; cv[1][h] = cond_reg[u][1]; cv[2][h] = cond_reg[u][2]; }
-              else ldg_zrh(condA_f + (size_t)gs * kRowsAP + lane_off + u * (kWarps * 32), cv[0][h], cv[1][h], cv[2][h]);
+              else ldg_zrh(condA_f + (size_t)gs * kRowsAP + lane_off + u * (WG * 32), cv[0][h], cv[1][h], cv[2][h]);
               if (PH) {
-                ldg_zrh(rp[mt][h][0] + u * (kWarps * 32), e1[0][h], e1[1][h], e1[2][h]);
-                ldg_zrh(rp[mt][h][1] + u * (kWarps * 32), e2[0][h], e2[1][h], e2[2][h]);
-                ldg_zrh(rp[mt][h][2] + u * (kWarps * 32), e3[0][h], e3[1][h], e3[2][h]);
+                ldg_zrh(rp[mt][h][0] + u * (WG * 32), e1[0][h], e1[1][h], e1[2][h]);
+                ldg_zrh(rp[mt][h][1] + u * (WG * 32), e2[0][h], e2[1][h], e2[2][h]);
+                ldg_zrh(rp[mt][h][2] + u * (WG * 32), e3[0][h], e3[1][h], e3[2][h]);
               } else {
                 const uint32_t w = ixw[mt][h];
-                const int off = lane_off + u * (kWarps * 32);
+                const int off = lane_off + u * (WG * 32);
                 ldg_zrh(M.e_sig + (w & 0xffu) * kRowsAP + off, e1[0][h], e1[1][h], e1[2][h]);
                 ldg_zrh(M.e_pred + ((w >> 8) & 0xffu) * kRowsAP + off, e2[0][h], e2[1][h], e2[2][h]);
                 ldg_zrh(M.e_exc + ((w >> 16) & 0xffu) * kRowsAP + off, e3[0][h], e3[1][h], e3[2][h]);
@@ -584,16 +616,25 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
                 if (gate < 2) tx = f2_add(tx, gx);                        // (+ input for z, r)
                 else gh[h] = gx;
                 const float2 sd = f2_mul(tx, f2_set(LPCB_SCALE));
-                acc[gate][2 * h] = (int32_t)((uint32_t)acc[gate][2 * h] + (uint32_t)__float2int_rn(sd.x));
-                acc[gate][2 * h + 1] = (int32_t)((uint32_t)acc[gate][2 * h + 1] + (uint32_t)__float2int_rn(sd.y));
+                if (RA) {   // (RA variants run only on models with small sums: bitexact.cuh acc_seed_small)
+                  acc[gate][2 * h] = (int32_t)((uint32_t)acc[gate][2 * h] + __float_as_uint(__fadd_rn(sd.x, LPCB_MAGIC)));
+                  acc[gate][2 * h + 1] = (int32_t)((uint32_t)acc[gate][2 * h + 1] + __float_as_uint(__fadd_rn(sd.y, LPCB_MAGIC)));
+                } else {
+                  acc[gate][2 * h] = (int32_t)((uint32_t)acc[gate][2 * h] + (uint32_t)__float2int_rn(sd.x));
+                  acc[gate][2 * h + 1] = (int32_t)((uint32_t)acc[gate][2 * h + 1] + (uint32_t)__float2int_rn(sd.y));
+                }
               }
             }
 #pragma unroll
             for (int h = 0; h < NV / 2; h++) {
               const float2 k1 = f2_set(LPCB_SCALE_1);
-              const float2 z = sigmoid2_ref(f2_mul(make_float2((float)acc[0][2 * h], (float)acc[0][2 * h + 1]), k1), s_rcp);
-              const float2 r = sigmoid2_ref(f2_mul(make_float2((float)acc[1][2 * h], (float)acc[1][2 * h + 1]), k1), s_rcp);
-              float2 hh = f2_mul(make_float2((float)acc[2][2 * h], (float)acc[2][2 * h + 1]), k1);
+              auto sum_f = [&](int gate) {   // the gate's two int32 sums as floats
+                if (RA) return f2_add(make_float2(__uint_as_float((uint32_t)acc[gate][2 * h]), __uint_as_float((uint32_t)acc[gate][2 * h + 1])), f2_set(-LPCB_MAGIC));
+                return make_float2((float)acc[gate][2 * h], (float)acc[gate][2 * h + 1]);
+              };
+              const float2 z = sigmoid2_ref(f2_mul(sum_f(0), k1), s_rcp);
+              const float2 r = sigmoid2_ref(f2_mul(sum_f(1), k1), s_rcp);
+              float2 hh = f2_mul(sum_f(2), k1);
               const float2 hr = f2_mul(hh, r);
               hh = tanh2_ref(make_float2(hr.x + gh[h].x, hr.y + gh[h].y), s_rcp);   // packed product, scalar sums
               const float2 a_old = a_reg[u][mt][h];
@@ -610,47 +651,59 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
                 pv = reinterpret_cast<const unsigned short *>(xa_cur)[((sA + 8 * h) * kXaStride * 4 + ug * 8 + 2 * t) >> 1];
               }
               *dst = (unsigned short)pv;
-              if (u == 0) qa0[mt][h] = pv;
-              else if (u == 1) qa0[mt][h] |= pv << 16;
-              else qa2[mt][h] = pv;
+              if (u / US == 0) qa0[u % US][mt][h] = pv;
+              else if (u / US == 1) qa0[u % US][mt][h] |= pv << 16;
+              else qa2[u % US][mt][h] = pv;
             }
           }
         }
         // GRU-B input product (src/nnet.c:353) of this warp's 24 units, operands from registers; the 16 warps' partial
         // sums meet in shared memory
         {
+          // fragment set w + WG*set of engine.h kBinFragWords = unit groups {w, w+16, w+32} + 8*set
           const uint2 *bf = reinterpret_cast<const uint2 *>(s_binF) + warp * kRGroupsB * 32 + lane;
-          constexpr int PF = NS == 8 ? kRGroupsB : 2;     // B fragments fetched ahead (registers are short above 8 streams)
+          constexpr int NJ = kRGroupsB * US;              // (row group, K slice) products of this warp
+          constexpr int PF = NS == 8 ? 6 : 2;             // B fragments fetched ahead (registers are short above 8 streams)
+          auto frag = [&](int j) { return bf[((j % US) * WG * kRGroupsB + j / US) * 32]; };
           uint2 bw[PF];
 #pragma unroll
-          for (int k = 0; k < PF; k++) bw[k] = bf[k * 32];
+          for (int k = 0; k < PF; k++) bw[k] = frag(k);
 #pragma unroll
           for (int rg = 0; rg < kRGroupsB; rg++) {
-            const uint2 bcur = bw[rg % PF];
-            if (rg + PF < kRGroupsB) bw[rg % PF] = bf[(rg + PF) * 32];
+            int32_t c[MT][4];
+#pragma unroll
+            for (int mt = 0; mt < MT; mt++) c[mt][0] = c[mt][1] = c[mt][2] = c[mt][3] = 0;
+#pragma unroll
+            for (int set = 0; set < US; set++) {
+              const int j = rg * US + set;
+              const uint2 bcur = bw[j % PF];
+              if (j + PF < NJ) bw[j % PF] = frag(j + PF);
+#pragma unroll
+              for (int mt = 0; mt < MT; mt++)
+                mma_u8s8(c[mt], qa0[set][mt][0], NV == 4 ? qa0[set][mt][NV / 2 - 1] : 0u, qa2[set][mt][0],
+                         NV == 4 ? qa2[set][mt][NV / 2 - 1] : 0u, bcur.x, bcur.y);
+            }
 #pragma unroll
             for (int mt = 0; mt < MT; mt++) {
-              int32_t c[4] = {0, 0, 0, 0};
-              mma_u8s8(c, qa0[mt][0], NV == 4 ? qa0[mt][NV / 2 - 1] : 0u, qa2[mt][0], NV == 4 ? qa2[mt][NV / 2 - 1] : 0u, bcur.x, bcur.y);
               int32_t *dst = s_part + ((mt * 2 + 0) * kRGroupsB + rg) * 128;
-              atomicAdd(dst + g * 8 + 2 * t, c[0]);
-              atomicAdd(dst + g * 8 + 2 * t + 1, c[1]);
+              atomicAdd(dst + g * 8 + 2 * t, c[mt][0]);
+              atomicAdd(dst + g * 8 + 2 * t + 1, c[mt][1]);
               if (VR == 16) {
-                atomicAdd(dst + (g + 8) * 8 + 2 * t, c[2]);
-                atomicAdd(dst + (g + 8) * 8 + 2 * t + 1, c[3]);
+                atomicAdd(dst + (g + 8) * 8 + 2 * t, c[mt][2]);
+                atomicAdd(dst + (g + 8) * 8 + 2 * t + 1, c[mt][3]);
               }
             }
           }
         }
         LPCB_MARK(1);   // phase A (this warp)
-        __syncthreads();
+        gsync();
         LPCB_MARK(2);   // wait for the other warps
         // ================= phase B2 + T: GRU-B gates, sampling, signal update =================
         {
           if (twarp) {
             // pairs of streams share a warp; NS is even so both halves are valid together
             const int s = grp;
-            if (TST) { t_x = s_tst[tid]; t_lpc = s_tst[kThreads + tid]; t_pred = s_tst[2 * kThreads + tid]; }
+            if (TST) { t_x = s_tst[tid]; t_lpc = s_tst[TG + tid]; t_pred = s_tst[2 * TG + tid]; }
             const int mt = s / VR, row = s % VR;
             const int act = s_act[s];
             // the step's two kiss99 draws, by every lane of the stream from broadcast loads (no branch, no shuffle;
@@ -670,7 +723,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               const int i = gate * kNB + l16;
               const int rg = gate * 2 + (l16 >> 3);
               const int e = row * 8 + (l16 & 7);
-              int32_t ai = acc_seed(s_subB[i] + s_condb[s * kRowsB + i]);
+              int32_t ai = RA ? acc_seed_small(s_subB[i] + s_condb[s * kRowsB + i]) : acc_seed(s_subB[i] + s_condb[s * kRowsB + i]);
               int32_t *pin = s_part + ((mt * 2 + 0) * kRGroupsB + rg) * 128 + e;
               ai += *pin;
               *pin = 0;                                   // the next step's partial sums add up from zero
@@ -683,9 +736,10 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
                   if (((f.x >> 16) & 7) == (uint32_t)(l16 & 7)) ai += sat16_pair(f, xr);
                 }
               }
-              zrh[gate] = acc_out(ai);
-              const int32_t ar = acc_seed(s_subB[kRowsB + i]) + s_part[((mt * 2 + 1) * kRGroupsB + rg) * 128 + e];
-              rec[gate] = acc_out(ar);
+              zrh[gate] = RA ? acc_out_small(ai) : acc_out(ai);
+              const int32_t ar = (RA ? acc_seed_small(s_subB[kRowsB + i]) : acc_seed(s_subB[kRowsB + i])) +
+                                 s_part[((mt * 2 + 1) * kRGroupsB + rg) * 128 + e];
+              rec[gate] = RA ? acc_out_small(ar) : acc_out(ar);
             }
             const float z = sigmoid_ref(zrh[0] + rec[0], s_rcp);
             const float r = sigmoid_ref(zrh[1] + rec[1], s_rcp);
@@ -699,6 +753,10 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
             }
             __syncwarp();
             LPCB_MARK(5);   // GRU-B gates
+            // the product warps start now: holding their shared-memory burst back until the GRU-B gates are through
+            // keeps it off the sampler's most latency-bound stretch (measured 3.67 -> 3.63 us per step; releasing
+            // after the first sampler round gives the same, after the second 3.81)
+            if (OVL) asm volatile("bar.arrive 1, %0;" ::"n"(kThreads) : "memory");
             // sample_mdense (src/nnet.c:163-214)
             float bv[16];
 #pragma unroll
@@ -776,14 +834,15 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               }
               __syncwarp();
               if (step + 1 < A.spf) predict();
-              if (TST) { s_tst[tid] = t_x; s_tst[2 * kThreads + tid] = t_pred; }
+              if (TST) { s_tst[tid] = t_x; s_tst[2 * TG + tid] = t_pred; }
             }
           } else if (OVL) {
+            asm volatile("bar.sync 1, %0;" ::"n"(kThreads) : "memory");   // released by the sampler warps after the GRU-B gates
             product_ahead(xa_new);   // the next step's recurrent sums, while warps 0-3 sample
           }
         }
         LPCB_MARK(8);   // signal update
-        __syncthreads();
+        gsync();
         LPCB_MARK(9);
         cur ^= 1;
       }  // step
@@ -791,8 +850,8 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
 
     // ---- store the tile's stream state ----
 #pragma unroll
-    for (int u = 0; u < 3; u++) {
-      const int ug = warp + u * kWarps;
+    for (int u = 0; u < UW; u++) {
+      const int ug = warp + u * WG;
 #pragma unroll
       for (int mt = 0; mt < MT; mt++)
 #pragma unroll
@@ -801,14 +860,14 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
           if (stream0 + s < Bend) *reinterpret_cast<float2 *>(A.st.gru_a + (size_t)(stream0 + s) * kN + ug * 8 + 2 * t) = a_reg[u][mt][h];
         }
     }
-    for (int i = tid; i < NS * 16; i += kThreads) {
+    for (int i = tid; i < NS * 16; i += TG) {
       const int s = i >> 4, j = i & 15;
       if (stream0 + s < Bend) {
         A.st.gru_b[(size_t)(stream0 + s) * kNB + j] = s_bst[s * 20 + j];
       }
     }
     if (grp < NS && stream0 + grp < Bend) A.st.last_sig[(size_t)(stream0 + grp) * 16 + l16] = t_x;
-    for (int s = tid; s < NS; s += kThreads) {
+    for (int s = tid; s < NS; s += TG) {
       if (stream0 + s < Bend) {
         A.st.deemph[stream0 + s] = s_deemph[s];
         A.st.last_exc[stream0 + s] = s_lexc[s];
@@ -831,8 +890,10 @@ static cudaError_t launch_tile(const SampleArgs &a, int n_sms, cudaStream_t s) {
   const bool sat = a.m.has_sat != 0;                // exact s16 pass: generic chunk lists, rcpps table (model.cu)
   const bool fix = a.m.a_rec.slots[2] != 0 && !sat;
   // Arithmetic rcpps when it was verified against the table on this GPU (model.cu): no shared-memory lookups,
-  // 2-4 % faster at every tile size (measured).  The trace/logit variants always use the table.
-  const bool ra = a.m.rcp_arith != 0 && !sat;
+  // 2-4 % faster at every tile size (measured); the same variants seed and read the int32 sums without conversion
+  // instructions, which needs the model's sums to stay inside (-2^22, 2^22) (DevModel::small_acc).  The trace/logit
+  // variants always use the table and the conversions.
+  const bool ra = a.m.rcp_arith != 0 && a.m.small_acc != 0 && !sat;
   const bool sub = a.stream_begin != 0 || a.stream_end != 0;
   if (sub && dbg) return cudaErrorInvalidValue;     // the trace / logit builds advance whole batches only
   void (*kern)(const SampleArgs) =
@@ -847,6 +908,25 @@ static cudaError_t launch_tile(const SampleArgs &a, int n_sms, cudaStream_t s) {
   if (e != cudaSuccess) return e;
   const int n_tiles = ((a.stream_end ? a.stream_end : a.n_streams) - a.stream_begin + NS - 1) / NS;
   const int grid = n_tiles < n_sms ? n_tiles : n_sms;
+  kern<<<grid, kThreads, smem, s>>>(a);
+  return cudaGetLastError();
+}
+
+// Two 8-stream tiles per CTA (G = 2): production kernel only (no trace / logits, no s16 pass).
+static cudaError_t launch_tile_pairs(const SampleArgs &a, int n_sms, cudaStream_t s) {
+  const size_t smem = make_layout(8, 1, a.m.a_rec.n_chunks, a.m.b_in.n_chunks, a.m.b_rec.n_chunks, 2).total;
+  if (a.trace || a.logits || a.m.has_sat) return cudaErrorInvalidValue;
+  const bool fix = a.m.a_rec.slots[2] != 0, ra = a.m.rcp_arith != 0 && a.m.small_acc != 0;
+  const bool sub = a.stream_begin != 0 || a.stream_end != 0;
+  void (*kern)(const SampleArgs) =
+      sub ? (ra ? (fix ? sample_kernel<1, 8, false, true, true, true, false, 2> : sample_kernel<1, 8, false, false, true, true, false, 2>)
+                : (fix ? sample_kernel<1, 8, false, true, false, true, false, 2> : sample_kernel<1, 8, false, false, false, true, false, 2>))
+      : ra ? (fix ? sample_kernel<1, 8, false, true, true, false, false, 2> : sample_kernel<1, 8, false, false, true, false, false, 2>)
+           : (fix ? sample_kernel<1, 8, false, true, false, false, false, 2> : sample_kernel<1, 8, false, false, false, false, false, 2>);
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  const int n_tiles = ((a.stream_end ? a.stream_end : a.n_streams) - a.stream_begin + 7) / 8;
+  const int ctas = (n_tiles + 1) / 2, grid = ctas < n_sms ? ctas : n_sms;
   kern<<<grid, kThreads, smem, s>>>(a);
   return cudaGetLastError();
 }

@@ -282,7 +282,9 @@ class Batch:
 
     @property
     def rcp_arith(self):
-        return bool(self.L.lpcnet_batch_nblocks(self.h, 2))
+        """the fast kernel variants run: rcpps computed (verified on this GPU) and conversion-free int32 seeds (the
+        model's sums proven inside +-2^22)"""
+        return bool(self.L.lpcnet_batch_nblocks(self.h, 2)) and bool(self.L.lpcnet_batch_nblocks(self.h, 7))
 
     @property
     def fixed_slots(self):

@@ -331,10 +331,64 @@ def sat(R):
     np.savez_compressed(os.path.join(OUT, "sat.npz"), **d)
 
 
+def demo_blob():
+    """weights_blob.bin for the demo tests: the model compiled into oracle/_ref/lpcnet_demo_parity_d* (random LPCNet +
+    PLC predictor) plus the VQ codebooks the reference links in (ceps_codebooks.c), as arrays under their C names."""
+    A = blob.random_model()
+    A.update(blob.random_plc_model())
+    cb = blob.synthetic_codebooks()
+    A["ceps_codebook1"], A["ceps_codebook2"], A["ceps_codebook3"] = cb[:1024 * 17], cb[1024 * 17:2 * 1024 * 17], cb[2 * 1024 * 17:3 * 1024 * 17]
+    A["ceps_codebook_diff4"] = cb[3 * 1024 * 17:]
+    return blob.write_blob(A)
+
+
+def demo_inputs():
+    """{mode: (argv after the binary, {file name: bytes})} for every mode of src/lpcnet_demo.c"""
+    feats = blob.synthetic_features(20, 3)
+    pk = np.random.default_rng(21).integers(0, 256, size=(6, 8), dtype=np.uint8)
+    pcm = blob.synthetic_pcm(40, 11)
+    lost = blob.synthetic_loss_pattern(40, 11)
+    loss_txt = ("\n".join(str(int(x)) for x in lost[::2]) + "\n").encode()
+    nolpc = blob.synthetic_features(12, 8)
+    return {
+        "synthesis": (["-synthesis", "in", "out"], {"in": feats.tobytes()}),
+        "decode": (["-decode", "in", "out"], {"in": pk.tobytes()}),
+        "features": (["-features", "in", "out"], {"in": pcm.tobytes()}),
+        "encode": (["-encode", "in", "out"], {"in": pcm.tobytes()}),
+        "addlpc": (["-addlpc", "in", "out"], {"in": nolpc.tobytes()}),
+        "plc_noncausal_dc": (["-plc_file", "noncausal_dc", "loss", "in", "out"], {"in": pcm.tobytes(), "loss": loss_txt}),
+        "plc_causal_dc": (["-plc_file", "causal_dc", "loss", "in", "out"], {"in": pcm.tobytes(), "loss": loss_txt}),
+    }
+
+
+def run_demo(binary, argv, files, extra=None):
+    import subprocess
+    import tempfile
+    with tempfile.TemporaryDirectory() as d:
+        for name, data in {**files, **(extra or {})}.items():
+            with open(os.path.join(d, name), "wb") as f:
+                f.write(data)
+        r = subprocess.run([binary] + argv, cwd=d, capture_output=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"{binary} {argv}: rc {r.returncode}: {r.stderr.decode()[-400:]}")
+        return open(os.path.join(d, "out"), "rb").read()
+
+
+def demo(R):
+    """Every mode of the reference's own command-line program (src/lpcnet_demo.c, unmodified, pinned-semantics flags,
+    compiled-in model: oracle/_ref/lpcnet_demo_parity_d2; _d0, the FEATURES_DELAY 0 build, for the non-causal PLC)."""
+    ref = os.path.join(ROOT, "oracle", "_ref")
+    d = {"blob_sha256": np.frombuffer(hashlib.sha256(demo_blob()).digest(), np.uint8)}
+    for mode, (argv, files) in demo_inputs().items():
+        binary = os.path.join(ref, "lpcnet_demo_parity_d0" if mode == "plc_noncausal_dc" else "lpcnet_demo_parity_d2")
+        d[mode] = np.frombuffer(run_demo(binary, argv, files), np.uint8)
+    np.savez_compressed(os.path.join(OUT, "demo.npz"), **d)
+
+
 if __name__ == "__main__":
     R = refpy.RefLib(2)
-    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc", "encode", "plc_causal", "dred", "plc_edges", "bench", "sat"]
+    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc", "encode", "plc_causal", "dred", "plc_edges", "bench", "sat", "demo"]
     for name in which:
-        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc, "encode": encode, "plc_causal": plc_causal, "dred": dred, "plc_edges": plc_edges, "bench": bench_hashes, "sat": sat}[name](R)
+        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc, "encode": encode, "plc_causal": plc_causal, "dred": dred, "plc_edges": plc_edges, "bench": bench_hashes, "sat": sat, "demo": demo}[name](R)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
