@@ -27,6 +27,7 @@ constexpr int kRowsB = 3 * kNB;  // 48
 // positions have distinct residues -- model.cu orders every chunk's blocks that way.
 constexpr int kXaStride = kN / 4 + 4;    // words per stream (100)
 constexpr int kXbStride = kNB / 4;       // 4: eight streams x four words = 32 distinct banks
+constexpr int kFcStride = 36;            // dual_fc node stride in shared memory: 32 weights padded so that 8 lanes' 16-byte reads hit disjoint banks
 
 // GRU-B input product (48 x 384) in the sample kernel: warp w of the 16 forms the K slice of its own 24 units (unit
 // groups w, w+16, w+32) straight from the state bytes it has just produced, one mma.m16n8k32 per 8-row group with the
@@ -134,6 +135,9 @@ struct DevModel {
   const float *e_sig, *e_pred, *e_exc;      // [256][kRowsAP], columns in gru_a_col_index order
   const float *a_subias_rec;                // [1152] = &sparse_gru_a_subias[3N]
   const float *a_diag;                      // [1152]
+  const float *a_sd_packed;                 // [gate*48 + ug][lane%4][sub0 sub1 diag0 diag1]: the kernel's shared-memory image
+  const float *fc_w_padded;                 // dual_fc weights at node stride kFcStride (36 floats): shared-memory image
+  const float *fc_bf;                       // dual_fc bias [2][256] | factor [2][256]: shared-memory image
   DevSparse a_rec;                          // 1152 x 384 block-sparse
   const float *b_subias;                    // [96]
   DevSparse b_in;                           // 48 x 384 (sparse stream format, dense by default): block count, DevSat lists

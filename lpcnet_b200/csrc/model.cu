@@ -46,7 +46,7 @@ struct Builder {
   std::vector<unsigned char> buf;
   size_t add(const void *p, size_t bytes) {
     size_t off = (buf.size() + 255) & ~size_t(255);
-    buf.resize(off + bytes);
+    buf.resize(off + ((bytes + 15) & ~size_t(15)));   // bulk copies move whole 16-byte blocks: the tail is readable zeros
     if (bytes) memcpy(buf.data() + off, p, bytes);
     return off;
   }
@@ -372,6 +372,26 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
   ok &= sub_a != nullptr;
   if (!ok) return false;
   put(reinterpret_cast<const void **>(&d.a_subias_rec), sub_a + kRowsA * 4, kRowsA * 4);
+  // the sample kernel's shared-memory images of three arrays, laid out here so that the kernel stages them with plain
+  // bulk copies: [gate*48 + ug][lane%4][sub0 sub1 diag0 diag1]; dual_fc weights at node stride kFcStride; bias | factor
+  {
+    const float *sub = reinterpret_cast<const float *>(sub_a) + kRowsA, *diag = reinterpret_cast<const float *>(A["sparse_gru_a_recurrent_weights_diag"].data);
+    std::vector<float> sd((size_t)kRowsA * 2);
+    for (int i = 0; i < kRowsA; i++) {
+      const int k = (i >> 3) * 16 + ((i & 7) >> 1) * 4 + (i & 1);
+      sd[k] = sub[i];
+      sd[k + 2] = diag[i];
+    }
+    put(reinterpret_cast<const void **>(&d.a_sd_packed), sd.data(), sd.size() * 4);
+    const float *fw = reinterpret_cast<const float *>(A["dual_fc_weights"].data);
+    std::vector<float> fp((size_t)256 * kFcStride, 0.f);
+    for (int i = 0; i < 256 * 32; i++) fp[(size_t)(i >> 5) * kFcStride + (i & 31)] = fw[i];
+    put(reinterpret_cast<const void **>(&d.fc_w_padded), fp.data(), fp.size() * 4);
+    std::vector<float> fb(1024);
+    memcpy(fb.data(), A["dual_fc_bias"].data, 512 * 4);
+    memcpy(fb.data() + 512, A["dual_fc_factor"].data, 512 * 4);
+    put(reinterpret_cast<const void **>(&d.fc_bf), fb.data(), fb.size() * 4);
+  }
 
   // The kernels seed their int32 accumulators with cvt.rni(16256*t) and skip the out-of-range fix-up of
   // cvtps2dq (-> 0x80000000): prove here that no pre-activation t can reach 2^31/16256 for states in [-1,1].

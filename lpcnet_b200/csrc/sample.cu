@@ -12,10 +12,10 @@ cudaError_t launch_sample_pp(const SampleArgs &a, int n_sms, cudaStream_t s);
 constexpr int kTilePairs = 28;
 
 size_t sample_kernel_smem(int tile_streams, const DevModel &m) {
-  if (tile_streams == kTilePairs) return make_layout(8, 1, m.a_rec.n_chunks, m.b_in.n_chunks, m.b_rec.n_chunks, 2).total;
+  if (tile_streams == kTilePairs) return make_layout(8, 1, m.a_rec.n_chunks, m.a_rec.slots[2] != 0, m.b_rec.n_chunks, 2).total;
   const int VR = tile_streams == 8 ? 8 : 16;
   const int MT = tile_streams / VR;
-  return make_layout(tile_streams, MT, m.a_rec.n_chunks, m.b_in.n_chunks, m.b_rec.n_chunks).total;
+  return make_layout(tile_streams, MT, m.a_rec.n_chunks, m.a_rec.slots[2] != 0 && !m.has_sat, m.b_rec.n_chunks).total;
 }
 
 cudaError_t launch_sample_kernel(const SampleArgs &a, int tile_streams, int n_sms, cudaStream_t s, int *n_launches) {

@@ -24,6 +24,8 @@
 #include "../../include/lpcnet_b200.h"
 #include "bitexact.cuh"
 #include "engine.h"
+#include "tma.cuh"
+
 
 namespace lpcb {
 
@@ -35,19 +37,19 @@ constexpr int kRGroupsB = kRowsB / 8;      // 6
 struct SmemLayout {
   // byte offsets
   unsigned wA, posA, offF, csA, binF, wBr, posBr, csBr;
-  unsigned sdA, subB, rcp, u2l, logit;
+  unsigned sdA, subB, u2l, logit;
   unsigned xa, xb, bst, condb, part;
   unsigned usig, upred, lexc, deemph, rng, act, ix, tst, accx;
+  unsigned bar, lpcb, condb1;  // mbarriers [1 + 2*G]; landing buffers of the bulk copies: LPC rows [G][2][NS][16], GRU-B conditioning [G][2][NS][48]
   unsigned fcw, fcb;   // dual_fc weights (node stride kFcStride floats) and bias|factor, when resident
   unsigned total;
 };
 
 
-constexpr int kFcStride = 36;   // 32 weights per node padded so that 8 lanes' 16-byte reads hit disjoint banks
 __host__ __device__ inline bool fc_resident(int NS) { return NS <= 32; }
 
 // G: tiles per CTA (1, or 2 as two groups of 8 warps: the per-tile buffers then exist once per group)
-__host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int chBi, int chBr, int G = 1) {
+__host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, bool fixed, int chBr, int G = 1) {
   SmemLayout L;
   unsigned o = 0;
   auto take = [&](unsigned bytes) { unsigned r = o; o += (bytes + 15u) & ~15u; return r; };
@@ -56,11 +58,11 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
     // constants (immediate operands instead of live registers or re-computed sums); the model-sized weight and
     // offset lists follow: 4.17 -> 4.13 us per step.  The larger tiles measured 2 % slower in this order
     // (register allocation) and keep the lists in front.
-    L.offF = take(kN / 8 * 32 * 4); L.csA = take((kN / 8 + 1) * 4);
+    L.offF = take(fixed ? kN / 8 * 32 * 4 : 0); L.csA = take((kN / 8 + 1) * 4);
     L.binF = take(kBinFragWords * 4);
     L.csBr = take((kRGroupsB + 1) * 4);
     L.sdA = take(kRowsA * 8); L.subB = take(2 * kRowsB * 4);
-    L.rcp = take(2048 * 4); L.u2l = take(256 * 4); L.logit = take(256 * 4);
+    L.u2l = take(256 * 4); L.logit = take(256 * 4);
     L.xa = take(2 * NS * kXaStride * 4);
     L.xb = take(NS * kXbStride * 4);
     L.bst = take(NS * 20 * 4);
@@ -74,15 +76,16 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
     L.fcw = take(256 * kFcStride * 4);
     L.wA = take(chA * 256); L.posA = take(chA * 16);
     L.wBr = take(chBr * 256); L.posBr = take(chBr * 16);
+    // (after everything else, so that the arrays of the step loop keep the offsets they were tuned with)
+    L.condb1 = take(2 * NS * kRowsB * 4); L.lpcb = take(2 * NS * 16 * 4); L.bar = take((1 + 2) * 8);
     L.total = o;
     return L;
   }
-  (void)chBi;
-  L.wA = take(chA * 256); L.posA = take(chA * 16); L.offF = take(kN / 8 * 32 * 4); L.csA = take((kN / 8 + 1) * 4);
+  L.wA = take(chA * 256); L.posA = take(chA * 16); L.offF = take(fixed ? kN / 8 * 32 * 4 : 0); L.csA = take((kN / 8 + 1) * 4);
   L.binF = take(kBinFragWords * 4);
   L.wBr = take(chBr * 256); L.posBr = take(chBr * 16); L.csBr = take((kRGroupsB + 1) * 4);
   L.sdA = take(kRowsA * 8); L.subB = take(2 * kRowsB * 4);
-  L.rcp = take(2048 * 4); L.u2l = take(256 * 4); L.logit = take(256 * 4);
+  L.u2l = take(256 * 4); L.logit = take(256 * 4);
   L.xa = take(G * 2 * NS * kXaStride * 4);
   L.xb = take(G * NS * kXbStride * 4);
   L.bst = take(G * NS * 20 * 4);
@@ -94,6 +97,7 @@ __host__ __device__ inline SmemLayout make_layout(int NS, int MT, int chA, int c
   L.accx = NS == 8 && G == 1 ? take(12 * 3 * 32 * 8) : 0;   // GRU-A sums computed ahead for the sampler warps' unit groups
   L.fcb = take(4 * 256 * 4);
   L.fcw = fc_resident(NS) ? take(256 * kFcStride * 4) : 0;
+  L.condb1 = take(G * 2 * NS * kRowsB * 4); L.lpcb = take(G * 2 * NS * 16 * 4); L.bar = take((1 + 2 * G) * 8);
   L.total = o;
   return L;
 }
@@ -186,9 +190,13 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   // sums of step i+1 (they need only the state of step i): their own three unit groups into registers and one
   // of the sampler warps' twelve into shared memory.  Phase A of step i+1 then starts at the gates.
   constexpr bool OVL = (MT == 1 && VR == 8 && G == 1);
+  constexpr bool TMAW = (NS == 16 && G == 1);   // weights staged by bulk copies (see the prologue)
+  // per-frame conditioning fetched one frame ahead by bulk copies: everywhere but at 16 streams per CTA, where the same
+  // A/B gives 6.44 us per step without it and 6.59 with it (8 streams per CTA: 3.58 either way)
+  constexpr bool TMAF = !(NS == 16 && G == 1);
   extern __shared__ __align__(16) unsigned char smem[];
   const DevModel &M = A.m;
-  const SmemLayout L = make_layout(NS, MT, M.a_rec.n_chunks, M.b_in.n_chunks, M.b_rec.n_chunks, G);
+  const SmemLayout L = make_layout(NS, MT, M.a_rec.n_chunks, FIX, M.b_rec.n_chunks, G);
 
   uint32_t *s_wA = reinterpret_cast<uint32_t *>(smem + L.wA);
   uint32_t *s_offA = reinterpret_cast<uint32_t *>(smem + L.posA);   // [chunk][4] packed gather offsets
@@ -200,14 +208,18 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   uint32_t *s_csBr = reinterpret_cast<uint32_t *>(smem + L.csBr);
   float *s_sdA = reinterpret_cast<float *>(smem + L.sdA);   // [gate][ug][lane%4][sub0 sub1 diag0 diag1]
   float *s_subB = reinterpret_cast<float *>(smem + L.subB);
-  uint32_t *s_rcp_tab = reinterpret_cast<uint32_t *>(smem + L.rcp);
-  const typename RcpSel<RA>::type s_rcp = RcpSel<RA>::make(s_rcp_tab);   // table in shared memory, or arithmetic
+  // rcpps: arithmetic, or (trace / logit builds, models on the s16 pass, GPUs where the arithmetic form failed its
+  // check) the 2048-entry table read through L1 -- not worth 8 KB of shared memory any more
+  const typename RcpSel<RA>::type s_rcp = RcpSel<RA>::make(M.rcp_tab);
   float *s_u2l = reinterpret_cast<float *>(smem + L.u2l);
   float *s_logit = reinterpret_cast<float *>(smem + L.logit);
   uint32_t *s_xa = reinterpret_cast<uint32_t *>(smem + L.xa);
   uint32_t *s_xb = reinterpret_cast<uint32_t *>(smem + L.xb);
   float *s_bst = reinterpret_cast<float *>(smem + L.bst);
-  float *s_condb = reinterpret_cast<float *>(smem + L.condb);
+  float *s_condb = reinterpret_cast<float *>(smem + L.condb);   // [stream][48] of the frame in progress (fixed offset: phase B2 reads it every step)
+  float *s_condb1 = reinterpret_cast<float *>(smem + L.condb1); // [frame & 1][stream][48]: where the bulk copies land
+  float *s_lpcb = reinterpret_cast<float *>(smem + L.lpcb);     // [frame & 1][stream][16]
+  uint64_t *s_bar = reinterpret_cast<uint64_t *>(smem + L.bar);  // [0] weights; [1 + 2*group + (frame & 1)] conditioning
   int32_t *s_part = reinterpret_cast<int32_t *>(smem + L.part);
   int *s_usig = reinterpret_cast<int *>(smem + L.usig);
   int *s_upred = reinterpret_cast<int *>(smem + L.upred);
@@ -229,7 +241,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   const int g = lane >> 2, t = lane & 3;
   if (G > 1) {
     s_xa += grp_id * 2 * NS * kXaStride; s_xb += grp_id * NS * kXbStride; s_bst += grp_id * NS * 20;
-    s_condb += grp_id * NS * kRowsB; s_part += grp_id * MT * 2 * kRGroupsB * 128;
+    s_condb += grp_id * NS * kRowsB; s_condb1 += grp_id * 2 * NS * kRowsB; s_lpcb += grp_id * 2 * NS * 16; s_part += grp_id * MT * 2 * kRGroupsB * 128;
     s_usig += grp_id * NS; s_upred += grp_id * NS; s_lexc += grp_id * NS; s_deemph += grp_id * NS;
     s_rng += grp_id * 4 * NS; s_act += grp_id * NS; s_ix += grp_id * NS;
   }
@@ -303,38 +315,64 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
     }
   };
 
-  // ---- one-time: weights, index lists and tables into shared memory ----
+  // ---- one-time: weights, index lists and tables into shared memory, as bulk asynchronous copies (tma.cuh): one
+  // thread arms the barrier with the byte count and issues them; everybody waits on the barrier ----
   {
-    auto copy_words = [&](uint32_t *dst, const uint32_t *src, int n) {
-      for (int i = tid0; i < n; i += kThreads) dst[i] = __ldg(src + i);
-    };
-    copy_words(s_wA, M.a_rec.w, M.a_rec.n_chunks * 64);
-    copy_words(s_offA, M.a_rec.off, M.a_rec.n_chunks * 4);
-    if (FIX) copy_words(s_offF, M.a_rec.off_fixed, kUGroups * 32);
-    copy_words(s_csA, M.a_rec.chunk_start, kUGroups + 1);
-    copy_words(s_binF, reinterpret_cast<const uint32_t *>(M.b_in_frag), kBinFragWords);
-    for (int i = tid0; i < G * MT * 2 * kRGroupsB * 128; i += kThreads) (s_part - grp_id * MT * 2 * kRGroupsB * 128)[i] = 0;   // the sums of the GRU-B input product
-                                                                                    // start at zero; phase B2 re-zeroes
-    copy_words(s_wBr, M.b_rec.w, M.b_rec.n_chunks * 64);
-    copy_words(s_offBr, M.b_rec.off, M.b_rec.n_chunks * 4);
-    copy_words(s_csBr, M.b_rec.chunk_start, kRGroupsB + 1);
-    for (int i = tid0; i < kRowsA; i += kThreads) {
-      const int k = (i >> 3) * 16 + ((i & 7) >> 1) * 4 + (i & 1);   // [gate*48 + ug][lane%4][.]
-      s_sdA[k] = __ldg(M.a_subias_rec + i);
-      s_sdA[k + 2] = __ldg(M.a_diag + i);
+    if (tid0 == 0) {
+      for (int k = 0; k < 1 + 2 * G; k++) mbar_init(s_bar + k, 1);
+      mbar_fence_init();
     }
-    copy_words(reinterpret_cast<uint32_t *>(s_subB), reinterpret_cast<const uint32_t *>(M.b_subias), 2 * kRowsB);
-    if (!RA) copy_words(s_rcp_tab, M.rcp_tab, 2048);
-    copy_words(reinterpret_cast<uint32_t *>(s_u2l), reinterpret_cast<const uint32_t *>(M.ulaw2lin_tab), 256);
-    copy_words(reinterpret_cast<uint32_t *>(s_logit), reinterpret_cast<const uint32_t *>(M.logit_tab), 256);
-    {
-      float *fb = reinterpret_cast<float *>(smem + L.fcb);
-      for (int i = tid0; i < 512; i += kThreads) { fb[i] = __ldg(M.fc_bias + i); fb[512 + i] = __ldg(M.fc_factor + i); }
+    __syncthreads();
+    // Staged by bulk copies where that is also the faster build: the step loop is the same source either way, but the
+    // two prologues steer the register allocation of the whole kernel differently -- measured A/B on one B200, bulk
+    // copies: 6.52 -> 6.44 us per step at 16 streams per CTA, 3.58 -> 3.75 at 8 (where the threads copy, as before).
+    if (!TMAW) {
+      auto copy_words = [&](void *dstv, const void *srcv, uint32_t bytes) {
+        uint32_t *dst = (uint32_t *)dstv; const uint32_t *src = (const uint32_t *)srcv;
+        for (int i = tid0; i < (int)(bytes / 4); i += kThreads) dst[i] = __ldg(src + i);
+      };
+      copy_words(s_wA, M.a_rec.w, (uint32_t)M.a_rec.n_chunks * 256u);
+      copy_words(s_offA, M.a_rec.off, (uint32_t)M.a_rec.n_chunks * 16u);
+      if (FIX) copy_words(s_offF, M.a_rec.off_fixed, kUGroups * 32u * 4u);
+      copy_words(s_csA, M.a_rec.chunk_start, (kUGroups + 1) * 4u);
+      copy_words(s_binF, M.b_in_frag, kBinFragWords * 4u);
+      copy_words(s_wBr, M.b_rec.w, (uint32_t)M.b_rec.n_chunks * 256u);
+      copy_words(s_offBr, M.b_rec.off, (uint32_t)M.b_rec.n_chunks * 16u);
+      copy_words(s_csBr, M.b_rec.chunk_start, (kRGroupsB + 1) * 4u);
+      copy_words(s_sdA, M.a_sd_packed, kRowsA * 8u);
+      copy_words(s_subB, M.b_subias, 2u * kRowsB * 4u);
+      copy_words(s_u2l, M.ulaw2lin_tab, 256u * 4u);
+      copy_words(s_logit, M.logit_tab, 256u * 4u);
+      copy_words(smem + L.fcb, M.fc_bf, 1024u * 4u);
+      if (FCS) copy_words(smem + L.fcw, M.fc_w_padded, 256u * kFcStride * 4u);
     }
-    if (FCS) {
-      float *fw = reinterpret_cast<float *>(smem + L.fcw);
-      for (int i = tid0; i < 256 * 32; i += kThreads) fw[(i >> 5) * kFcStride + (i & 31)] = __ldg(M.fc_w + i);
+    if (TMAW && tid0 == 0) {
+      struct Job { void *dst; const void *src; uint32_t bytes; };
+      const Job jobs[] = {
+          {s_wA, M.a_rec.w, (uint32_t)M.a_rec.n_chunks * 256u},
+          {s_offA, M.a_rec.off, (uint32_t)M.a_rec.n_chunks * 16u},
+          {s_offF, M.a_rec.off_fixed, FIX ? kUGroups * 32u * 4u : 0u},
+          {s_csA, M.a_rec.chunk_start, (kUGroups + 1) * 4u},
+          {s_binF, M.b_in_frag, kBinFragWords * 4u},
+          {s_wBr, M.b_rec.w, (uint32_t)M.b_rec.n_chunks * 256u},
+          {s_offBr, M.b_rec.off, (uint32_t)M.b_rec.n_chunks * 16u},
+          {s_csBr, M.b_rec.chunk_start, (kRGroupsB + 1) * 4u},
+          {s_sdA, M.a_sd_packed, kRowsA * 8u},
+          {s_subB, M.b_subias, 2u * kRowsB * 4u},
+          {s_u2l, M.ulaw2lin_tab, 256u * 4u},
+          {s_logit, M.logit_tab, 256u * 4u},
+          {smem + L.fcb, M.fc_bf, 1024u * 4u},
+          {smem + L.fcw, M.fc_w_padded, FCS ? 256u * kFcStride * 4u : 0u},
+      };
+      uint32_t total = 0;
+      for (const Job &j : jobs) total += (j.bytes + 15u) & ~15u;     // (the model's arrays are readable to the next 16 bytes)
+      mbar_arrive_expect_tx(s_bar, total);
+      for (const Job &j : jobs)
+        if (j.bytes) bulk_g2s(j.dst, j.src, (j.bytes + 15u) & ~15u, s_bar);
     }
+    // the sums of the GRU-B input product start at zero; phase B2 re-zeroes them
+    for (int i = tid0; i < G * MT * 2 * kRGroupsB * 128; i += kThreads) (s_part - grp_id * MT * 2 * kRGroupsB * 128)[i] = 0;
+    if (TMAW) mbar_wait(s_bar, 0);
   }
   __syncthreads();     // the groups go their own ways from here
 
@@ -342,6 +380,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
   long long clk_[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, last_ = clock64();
 #endif
   const int n_tiles = (Bend - sbegin + NS - 1) / NS;
+  uint32_t bar_phase = 0;      // bit b: the phase the next wait on conditioning buffer b expects
   if (G > 1 && grp_id == 1) __nanosleep(1800);     // start half a step apart; the phases keep the groups apart afterwards
   for (int tile = blockIdx.x * G + grp_id; tile < n_tiles; tile += gridDim.x * G) {
     const int stream0 = sbegin + tile * NS;
@@ -404,16 +443,41 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
 #pragma unroll
       for (int k = 0; k < 4; k++) s_rng[k * NS + s] = A.st.rng[(size_t)gs * 4 + k];
     }
+    // The frame-rate inputs of the tile -- GRU-B conditioning [stream][48] and LPC [stream][16], contiguous over the
+    // tile's streams -- arrive by bulk copy into one of two buffers: frame f + 1 is fetched while frame f's 160 steps
+    // run.  A last, part-filled tile copies its own rows only; the rest of the buffers is cleared once.
+    const int tile_rows = min(NS, Bend - stream0);
+    if (tile_rows < NS) {
+      for (int i = tid; i < 2 * NS * kRowsB; i += TG) if ((i % (NS * kRowsB)) >= tile_rows * kRowsB) s_condb1[i] = 0.f;
+      for (int i = tid; i < 2 * NS * 16; i += TG) if ((i % (NS * 16)) >= tile_rows * 16) s_lpcb[i] = 0.f;
+    }
+    auto fetch_frame = [&](int f) {   // one thread of the group
+      uint64_t *bar = s_bar + 1 + 2 * grp_id + (f & 1);
+      fence_proxy_async();            // the buffer's earlier reads (two frames ago) are ordered before the engine's writes
+      mbar_arrive_expect_tx(bar, (uint32_t)tile_rows * (kRowsB + 16) * 4u);
+      bulk_g2s(s_condb1 + (f & 1) * NS * kRowsB, A.cond_b + ((size_t)f * B + stream0) * kRowsB, (uint32_t)tile_rows * kRowsB * 4u, bar);
+      bulk_g2s(s_lpcb + (f & 1) * NS * 16, A.lpc + ((size_t)f * B + stream0) * 16, (uint32_t)tile_rows * 16u * 4u, bar);
+    };
     gsync();
+    if (TMAF && tid == 0) fetch_frame(0);
     if (OVL && !twarp) product_ahead(s_xa + cur * NS * kXaStride);   // sums for the tile's first step
 
     for (int f = 0; f < A.n_frames; f++) {
       // ---- frame prologue: LPC, GRU-B conditioning, active flags ----
-      t_lpc = A.lpc[((size_t)f * B + tgs) * 16 + l16];
-      for (int i = tid; i < NS * kRowsB; i += TG) {
-        const int s = i / kRowsB, j = i % kRowsB;
-        const int gs = min(stream0 + s, Bend - 1);
-        s_condb[i] = A.cond_b[((size_t)f * B + gs) * kRowsB + j];
+      // (every thread of the group is past frame f - 1 here: its reads of the other buffer ended before the last barrier)
+      if (TMAF) {
+        if (tid == 0 && f + 1 < A.n_frames) fetch_frame(f + 1);
+        mbar_wait(s_bar + 1 + 2 * grp_id + (f & 1), (bar_phase >> (f & 1)) & 1u);
+        bar_phase ^= 1u << (f & 1);
+        t_lpc = s_lpcb[(f & 1) * NS * 16 + min(grp, NS - 1) * 16 + l16];
+        for (int i = tid; i < NS * kRowsB; i += TG) s_condb[i] = s_condb1[(f & 1) * NS * kRowsB + i];   // (ordered by the barrier below)
+      } else {
+        t_lpc = A.lpc[((size_t)f * B + tgs) * 16 + l16];
+        for (int i = tid; i < NS * kRowsB; i += TG) {
+          const int s = i / kRowsB, j = i % kRowsB;
+          const int gs = min(stream0 + s, Bend - 1);
+          s_condb[i] = A.cond_b[((size_t)f * B + gs) * kRowsB + j];
+        }
       }
       int my_act = 0;
       if (tid < NS) {
@@ -885,7 +949,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
 template <int MT, int VR>
 static cudaError_t launch_tile(const SampleArgs &a, int n_sms, cudaStream_t s) {
   const int NS = MT * VR;
-  const size_t smem = make_layout(NS, MT, a.m.a_rec.n_chunks, a.m.b_in.n_chunks, a.m.b_rec.n_chunks).total;
+  const size_t smem = make_layout(NS, MT, a.m.a_rec.n_chunks, a.m.a_rec.slots[2] != 0 && !a.m.has_sat, a.m.b_rec.n_chunks).total;
   const bool dbg = a.trace || a.logits;
   const bool sat = a.m.has_sat != 0;                // exact s16 pass: generic chunk lists, rcpps table (model.cu)
   const bool fix = a.m.a_rec.slots[2] != 0 && !sat;
@@ -914,7 +978,7 @@ static cudaError_t launch_tile(const SampleArgs &a, int n_sms, cudaStream_t s) {
 
 // Two 8-stream tiles per CTA (G = 2): production kernel only (no trace / logits, no s16 pass).
 static cudaError_t launch_tile_pairs(const SampleArgs &a, int n_sms, cudaStream_t s) {
-  const size_t smem = make_layout(8, 1, a.m.a_rec.n_chunks, a.m.b_in.n_chunks, a.m.b_rec.n_chunks, 2).total;
+  const size_t smem = make_layout(8, 1, a.m.a_rec.n_chunks, a.m.a_rec.slots[2] != 0, a.m.b_rec.n_chunks, 2).total;
   if (a.trace || a.logits || a.m.has_sat) return cudaErrorInvalidValue;
   const bool fix = a.m.a_rec.slots[2] != 0, ra = a.m.rcp_arith != 0 && a.m.small_acc != 0;
   const bool sub = a.stream_begin != 0 || a.stream_end != 0;
