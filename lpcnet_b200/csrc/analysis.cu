@@ -95,11 +95,10 @@ __global__ void preemph_kernel(AnalysisArgs A) {
 __global__ void spectral_kernel(AnalysisArgs A) {
   const int B = A.n_streams, F = A.n_frames;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  const size_t nthreads = (size_t)gridDim.x * blockDim.x;
   if (idx >= B * F) return;
   const int s = idx / F, f = idx % F;
   if (A.stream_mask && !A.stream_mask[s]) return;
-  Scratch S{A.fft_scratch + idx, nthreads};
+  const Scratch S = block_scratch();
   const float *x = A.P + (size_t)s * (kOverlap + F * kFrame) + (size_t)f * kFrame;   // [analysis_mem | frame]
   // apply_window (freq.c:322-328) and opus_fft_c's scaled bit-reversed copy (kiss_fft.c:566-585)
   const float scale = 1.f / 320;
@@ -492,9 +491,7 @@ int analysis_device(LPCNetFeatureBatch *b, const short *d16, const float *df, in
   CKA(cudaSetDevice(b->device));
   const int Fc = feature_chunk_frames(B, n_frames, mode != 0);
   const size_t nP = (size_t)B * (kOverlap + Fc * kFrame), nS = (size_t)B * (1 + Fc * kFrame);
-  const int lpc_threads = 64;
-  const size_t n_fft_threads = (size_t)((B * Fc + lpc_threads - 1) / lpc_threads) * lpc_threads;
-  const size_t want = (nP + nS + n_fft_threads * 640) * 4 + 1024;
+  const size_t want = (nP + nS) * 4 + 1024;      // (the transforms' scratch lives in shared memory: dsp.cuh block_scratch)
   if (grow_buf(&b->work, &b->work_bytes, want)) return -1;
   for (int f0 = 0; f0 < n_frames; f0 += Fc) {
     const int F = n_frames - f0 < Fc ? n_frames - f0 : Fc;
@@ -508,7 +505,8 @@ int analysis_device(LPCNetFeatureBatch *b, const short *d16, const float *df, in
     A.fft_scratch = A.S + (((size_t)B * (1 + F * kFrame) + 63) & ~size_t(63));
     const size_t np = (size_t)B * (kOverlap + F * kFrame);
     preemph_kernel<<<(unsigned)((np + 255) / 256 > 65535 * 16 ? 65535 * 16 : (np + 255) / 256), 256, 0, b->stream>>>(A);
-    spectral_kernel<<<(B * F + lpc_threads - 1) / lpc_threads, lpc_threads, 0, b->stream>>>(A);
+    if (fft_opt_in(spectral_kernel) != cudaSuccess) return set_last_error("spectral_kernel: shared-memory opt-in failed");
+    spectral_kernel<<<(B * F + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, b->stream>>>(A);
     const size_t nr = (size_t)B * F * kFrame;
     residual_kernel<<<(unsigned)((nr + 255) / 256 > 65535 * 16 ? 65535 * 16 : (nr + 255) / 256), 256, 0, b->stream>>>(A);
     if (mode) pitch_kernel<true><<<B, kPT, pitch_smem(F, 8), b->stream>>>(A);

@@ -221,8 +221,7 @@ int ensure_frame_buffers(LPCNetBatch *b, int F, bool second = false, int streams
   const size_t o_iv = take(B * (F + 2) * kConvIn * 4), o_c1 = take(B * (F + 2) * kC * 4);
   const size_t o_ca = take((size_t)F * B * kRowsAP * 4), o_cb = take((size_t)F * B * kRowsB * 4);
   const size_t o_lpc = take((size_t)F * B * 16 * 4), o_act = take((size_t)F * B);
-  const size_t fft_threads = ((B * F + 63) / 64) * 64;
-  const size_t o_fft = take(fft_threads * 640 * 4);
+  const size_t o_fft = take(16);       // (the transforms' scratch lives in shared memory now: dsp.cuh block_scratch)
   CK(cudaMalloc(&alloc, off));
   char *p = static_cast<char *>(alloc);
   fb.in_vec = (float *)(p + o_iv); fb.c1 = (float *)(p + o_c1); fb.cond_a = (float *)(p + o_ca);
@@ -413,7 +412,7 @@ std::vector<float> lpcb::file_codebooks() {
 BatchView lpcb::batch_view(LPCNetBatch *b) { return BatchView{b->st, &b->model, b->stream, b->n_streams, b->device}; }
 
 int lpcb::batch_frame_network_masked(LPCNetBatch *b, const float *d_features, int stride, const uint8_t *d_mask,
-                                     bool state_only) {
+                                     bool state_only, const int *d_rows, int n_rows) {
   CK(cudaSetDevice(b->device));
   if (ensure_frame_buffers(b, 1) || (state_only && ensure_frame_buffers(b, 1, true))) return -1;
   FrameArgs fa{};
@@ -421,6 +420,7 @@ int lpcb::batch_frame_network_masked(LPCNetBatch *b, const float *d_features, in
   fa.state_only = state_only ? 1 : 0;
   fa.features = d_features; fa.feature_stride = stride; fa.frame0 = 0; fa.total_frames = 1;
   fa.stream_mask = d_mask;
+  if (d_rows && !getenv("LPCNET_B200_NO_COMPACT")) { fa.rows = d_rows; fa.n_rows = n_rows; fa.stream_mask = nullptr; }
   int nl = 0;
   CK(launch_frame_network(fa, b->stream, &nl));
   b->launches += nl;

@@ -22,6 +22,21 @@ struct Scratch {
   __device__ __forceinline__ void st(int k, Cpx c) const { base[(size_t)(2 * k) * stride] = c.r; base[(size_t)(2 * k + 1) * stride] = c.i; }
 };
 
+// The transforms run one per thread with the scratch of a block in SHARED memory, interleaved over its threads
+// ([320][2][kFftBlock]: conflict-free, 80 KB per block): every butterfly access is a 30-cycle shared-memory access
+// instead of an L2 round trip (the scratch used to be a global array: 133 us per single-frame lpc_kernel launch,
+// latency-bound whatever the row count).  Launch with kFftBlock threads and kFftSmem bytes; fft_opt_in() first.
+constexpr int kFftBlock = 32;
+constexpr size_t kFftSmem = (size_t)kFftBlock * 640 * sizeof(float);
+__device__ __forceinline__ Scratch block_scratch() {
+  extern __shared__ __align__(16) float fft_smem[];
+  return Scratch{fft_smem + threadIdx.x, (size_t)kFftBlock};
+}
+template <class K>
+inline cudaError_t fft_opt_in(K kernel) {   // > 48 KB of dynamic shared memory needs the opt-in (per device; cheap to repeat)
+  return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFftSmem);
+}
+
 __device__ __forceinline__ Cpx twd(const float *tw, int k) { Cpx c; c.r = __ldg(tw + 2 * k); c.i = __ldg(tw + 2 * k + 1); return c; }
 
 // kf_bfly4 (src/kiss_fft.c:96-162)

@@ -254,6 +254,8 @@ struct FrameArgs {
   int feature_stride;
   int frame0, total_frames;
   const uint8_t *stream_mask;  // nullable [B]: streams with 0 keep their frame-rate state and their conditioning rows
+  const int *rows = nullptr;   // nullable device list of n_rows stream indices: only these streams run (instead of a mask:
+  int n_rows = 0;              //   the kernels are launched over the list, not over the batch); layouts stay those of the batch
   int state_only = 0;          // run_frame_network_flush (lpcnet.c:134-144): only the frame-rate state moves
 };
 cudaError_t launch_frame_network(const FrameArgs &a, cudaStream_t s, int *n_launches);
@@ -291,8 +293,10 @@ std::vector<float> file_codebooks();
 // run_frame_network for one frame of the streams with mask != 0 (features: device [B][stride]); the conditioning
 // stays in the batch's frame buffers for the sample segments that follow.
 // state_only: run_frame_network_flush -- the outputs go to a scratch set, the streams' conditioning stays.
+// d_rows / n_rows (optional): the device list of the streams the mask selects -- the kernels then run over the list
+// (the PLC's small classes: a tenth of the batch) instead of testing the mask for every stream.
 int batch_frame_network_masked(LPCNetBatch *b, const float *d_features, int stride, const uint8_t *d_mask,
-                               bool state_only = false);
+                               bool state_only = false, const int *d_rows = nullptr, int n_rows = 0);
 // n sample steps (lpcnet_synthesize_tail_impl) on the conditioning of the last frame network.  flags [B]: 0 the
 // stream does not move, 1 free-running, 3 teacher-forced on d_forced [B][n]; d_out [B][n].
 // d_perm (nullable): device list of the n_act streams whose flag is not 0, ascending; when they are at most half of

@@ -21,11 +21,15 @@ constexpr int kPrefetch = 16;   // weight loads in flight per thread in the dens
 
 __device__ __forceinline__ int frame_count_at(int fc0, int f) { return min(fc0 + f, 1000); }
 
+// streams this launch covers: the whole batch, or the list FrameArgs::rows (k-th entry -> stream index)
+__device__ __forceinline__ int n_active(const FrameArgs &A) { return A.rows ? A.n_rows : A.n_streams; }
+__device__ __forceinline__ int stream_of(const FrameArgs &A, int k) { return A.rows ? __ldg(A.rows + k) : k; }
+
 // K0: in_vec rows (history + features|pitch embedding) and the per-frame active flags.
 __global__ void frame_inputs_kernel(FrameArgs A) {
   const int B = A.n_streams, F = A.n_frames;
   const int row = blockIdx.x;  // (stream, r) with r in [0, F+2)
-  const int s = row / (F + 2), r = row % (F + 2);
+  const int s = stream_of(A, row / (F + 2)), r = row % (F + 2);
   float *dst = A.fb.in_vec + ((size_t)s * (F + 2) + r) * kConvIn;
   const int tid = threadIdx.x;
   if (r < 2) {
@@ -101,10 +105,10 @@ __device__ __forceinline__ void dense_rows(const float *__restrict__ W, const fl
 // true when every row of this block belongs to a stream the mask leaves out (nothing to compute or store)
 __device__ __forceinline__ bool block_masked_out(const FrameArgs &A, int R) {
   if (!A.stream_mask) return false;
-  const int F = A.n_frames, total = A.n_streams * F;
+  const int F = A.n_frames, total = n_active(A) * F;
   for (int r = 0; r < R; r++) {
     const int row = blockIdx.x * R + r;
-    if (row < total && A.stream_mask[row / F]) return false;
+    if (row < total && A.stream_mask[stream_of(A, row / F)]) return false;
   }
   return true;
 }
@@ -115,13 +119,13 @@ __global__ void __launch_bounds__(kFT) conv1_kernel(FrameArgs A) {
   __shared__ float y[R][kC];
   __shared__ bool zero[R];
   __shared__ uint32_t rcp[2048];
-  const int F = A.n_frames, total = A.n_streams * F;
+  const int F = A.n_frames, total = n_active(A) * F;
   const int tid = threadIdx.x;
   if (block_masked_out(A, R)) return;
   for (int i = tid; i < 2048; i += kFT) rcp[i] = A.m.rcp_tab[i];
   for (int r = 0; r < R; r++) {
     const int row = min(blockIdx.x * R + r, total - 1);
-    const int s = row / F, f = row % F;
+    const int s = stream_of(A, row / F), f = row % F;
     const float *src = A.fb.in_vec + ((size_t)s * (F + 2) + f) * kConvIn;  // rows f, f+1, f+2 are contiguous
     for (int i = tid; i < 3 * kConvIn; i += kFT) xt[i][r] = src[i];
     if (tid == 0) zero[r] = frame_count_at(A.st.frame_count[s], f) < 1;  // FEATURE_CONV1_DELAY (src/lpcnet.c:99)
@@ -132,7 +136,7 @@ __global__ void __launch_bounds__(kFT) conv1_kernel(FrameArgs A) {
   for (int r = 0; r < R; r++) {
     const int row = blockIdx.x * R + r;
     if (row >= total) break;
-    const int s = row / F, f = row % F;
+    const int s = stream_of(A, row / F), f = row % F;
     for (int i = tid; i < kC; i += kFT) A.fb.c1[((size_t)s * (F + 2) + f + 2) * kC + i] = y[r][i];
   }
 }
@@ -146,13 +150,13 @@ __global__ void __launch_bounds__(kFT) cond_kernel(FrameArgs A) {
   __shared__ bool zero[R];
   __shared__ int row_s[R], row_f[R];
   __shared__ uint32_t rcp[2048];
-  const int F = A.n_frames, B = A.n_streams, total = B * F;
+  const int F = A.n_frames, B = A.n_streams, total = n_active(A) * F;
   const int tid = threadIdx.x;
   if (block_masked_out(A, R)) return;
   for (int i = tid; i < 2048; i += kFT) rcp[i] = A.m.rcp_tab[i];
   for (int r = 0; r < R; r++) {
     const int row = min(blockIdx.x * R + r, total - 1);
-    const int s = row / F, f = row % F;
+    const int s = stream_of(A, row / F), f = row % F;
     const float *src = A.fb.c1 + ((size_t)s * (F + 2) + f) * kC;
     for (int i = tid; i < 3 * kC; i += kFT) xt[i][r] = src[i];
     if (tid == 0) {
@@ -222,11 +226,10 @@ __global__ void __launch_bounds__(kFT) cond_kernel(FrameArgs A) {
 __global__ void lpc_kernel(FrameArgs A) {
   const int B = A.n_streams, F = A.n_frames;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  const size_t nthreads = (size_t)gridDim.x * blockDim.x;
-  if (idx >= B * F) return;
-  const int s = idx / F, f = idx % F;
+  if (idx >= n_active(A) * F) return;
+  const int s = stream_of(A, idx / F), f = idx % F;
   if (A.stream_mask && !A.stream_mask[s]) return;      // keeps its LPC (see cond_kernel)
-  Scratch S{A.fb.fft_scratch + idx, nthreads};
+  const Scratch S = block_scratch();
   const float *feat = A.features + ((size_t)s * A.total_frames + A.frame0 + f) * A.feature_stride;
   float lpc[16];
   lpc_from_cepstrum_dev(DspTables{A.m.fft_tw, A.m.fft_bitrev, A.m.dct}, feat, lpc, S);
@@ -235,46 +238,43 @@ __global__ void lpc_kernel(FrameArgs A) {
 }
 
 // K3b: the FEATURES_DELAY delay line (src/lpcnet.c:109-115), lpc_weighting (freq.c:299-308), and the
-// per-stream frame-state update (conv histories, old_lpc, frame_count).  One thread per stream,
-// frames walked newest to oldest so the in-place shift never reads an overwritten row.
+// per-stream frame-state update (conv histories, old_lpc, frame_count).  One WARP per stream: lane i < 16 owns LPC
+// coefficient i through the whole chunk (every operation here is per coefficient; frames walked newest to oldest so
+// the in-place shift never reads an overwritten row), all 32 lanes copy the history rows.  (One thread per stream
+// took 94 us per launch whatever the batch: a serial walk over 440 floats of L2 round trips.)
 __global__ void frame_finalize_kernel(FrameArgs A) {
   const int B = A.n_streams, F = A.n_frames, D = A.m.features_delay;
-  const int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= B) return;
+  const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (k >= n_active(A)) return;
+  const int s = stream_of(A, k);
   if (A.stream_mask && !A.stream_mask[s]) return;   // this stream did not run a frame network
-  if (D > 0) {
-    float newest[kMaxDelay][16];   // new_lpc[F-1-k]
-    for (int k = 0; k < D; k++)
-      for (int i = 0; i < 16; i++)
-        newest[k][i] = (F - 1 - k >= 0) ? A.fb.lpc[((size_t)(F - 1 - k) * B + s) * 16 + i]
-                                        : A.st.old_lpc[((size_t)s * kMaxDelay + (k - F)) * 16 + i];
-    for (int f = F - 1; f >= 0; f--) {
-      float *dst = A.fb.lpc + ((size_t)f * B + s) * 16;
-      const float *src = (f - D >= 0) ? A.fb.lpc + ((size_t)(f - D) * B + s) * 16
-                                      : A.st.old_lpc + ((size_t)s * kMaxDelay + (D - 1 - f)) * 16;
-      float v[16];
-      for (int i = 0; i < 16; i++) v[i] = src[i];
-      for (int i = 0; i < 16; i++) dst[i] = v[i];
+  if (lane < 16) {
+    const int i = lane;
+    if (D > 0) {
+      float newest[kMaxDelay];   // new_lpc[F-1-k][i]
+      for (int q = 0; q < D; q++)
+        newest[q] = (F - 1 - q >= 0) ? A.fb.lpc[((size_t)(F - 1 - q) * B + s) * 16 + i]
+                                     : A.st.old_lpc[((size_t)s * kMaxDelay + (q - F)) * 16 + i];
+      for (int f = F - 1; f >= 0; f--)
+        A.fb.lpc[((size_t)f * B + s) * 16 + i] = (f - D >= 0) ? A.fb.lpc[((size_t)(f - D) * B + s) * 16 + i]
+                                                              : A.st.old_lpc[((size_t)s * kMaxDelay + (D - 1 - f)) * 16 + i];
+      for (int q = 0; q < D; q++) A.st.old_lpc[((size_t)s * kMaxDelay + q) * 16 + i] = newest[q];
     }
-    for (int k = 0; k < D; k++)
-      for (int i = 0; i < 16; i++) A.st.old_lpc[((size_t)s * kMaxDelay + k) * 16 + i] = newest[k][i];
+    float gamma_i = A.m.lpc_gamma;                   // gamma^(i+1) by the reference's running product
+    for (int q = 0; q < i; q++) gamma_i = gamma_i * A.m.lpc_gamma;
+    for (int f = 0; f < F; f++) {
+      float *dst = A.fb.lpc + ((size_t)f * B + s) * 16 + i;
+      *dst = *dst * gamma_i;
+    }
+    // current-frame conditioning kept in the stream state like the reference (lpcnet_private.h:43-47)
+    if (!A.state_only) A.st.lpc[(size_t)s * 16 + i] = A.fb.lpc[((size_t)(F - 1) * B + s) * 16 + i];
   }
-  for (int f = 0; f < F; f++) {
-    float *dst = A.fb.lpc + ((size_t)f * B + s) * 16;
-    float gamma_i = A.m.lpc_gamma;
-    for (int i = 0; i < 16; i++) { dst[i] = dst[i] * gamma_i; gamma_i = gamma_i * A.m.lpc_gamma; }
-  }
-  // histories: the last two in_vec / c1 rows (rows F and F+1 of the [F+2] buffers)
-  for (int r = 0; r < 2; r++) {
-    const float *iv = A.fb.in_vec + ((size_t)s * (F + 2) + F + r) * kConvIn;
-    for (int i = 0; i < kConvIn; i++) A.st.conv1_state[(size_t)s * 2 * kConvIn + r * kConvIn + i] = iv[i];
-    const float *cv = A.fb.c1 + ((size_t)s * (F + 2) + F + r) * kC;
-    for (int i = 0; i < kC; i++) A.st.conv2_state[(size_t)s * 2 * kC + r * kC + i] = cv[i];
-  }
-  // current-frame conditioning kept in the stream state like the reference (lpcnet_private.h:43-47)
-  if (!A.state_only)
-    for (int i = 0; i < 16; i++) A.st.lpc[(size_t)s * 16 + i] = A.fb.lpc[((size_t)(F - 1) * B + s) * 16 + i];
-  A.st.frame_count[s] = frame_count_at(A.st.frame_count[s], F);
+  // histories: the last two in_vec / c1 rows (rows F and F+1 of the [F+2] buffers), contiguous in both places
+  const float *iv = A.fb.in_vec + ((size_t)s * (F + 2) + F) * kConvIn;
+  for (int i = lane; i < 2 * kConvIn; i += 32) A.st.conv1_state[(size_t)s * 2 * kConvIn + i] = iv[i];
+  const float *cv = A.fb.c1 + ((size_t)s * (F + 2) + F) * kC;
+  for (int i = lane; i < 2 * kC; i += 32) A.st.conv2_state[(size_t)s * 2 * kC + i] = cv[i];
+  if (lane == 0) A.st.frame_count[s] = frame_count_at(A.st.frame_count[s], F);
 }
 
 // ---- packet decoder (src/lpcnet_dec.c:59-155, src/common.c:37-65), one thread per stream ----
@@ -347,13 +347,16 @@ __global__ void decode_packets_kernel(DecodeArgs A) {
 }  // namespace
 
 cudaError_t launch_frame_network(const FrameArgs &a, cudaStream_t s, int *n_launches) {
-  const int B = a.n_streams, F = a.n_frames;
+  const int B = a.rows ? a.n_rows : a.n_streams, F = a.n_frames;     // streams this launch covers
+  if (B <= 0) return cudaSuccess;
   const int rows = B * F;
   frame_inputs_kernel<<<B * (F + 2), 128, 0, s>>>(a);
   conv1_kernel<<<(rows + kRowsPerBlock - 1) / kRowsPerBlock, kFT, 0, s>>>(a);
   cond_kernel<<<(rows + kRowsPerBlock - 1) / kRowsPerBlock, kFT, 0, s>>>(a);
-  lpc_kernel<<<(rows + 63) / 64, 64, 0, s>>>(a);
-  frame_finalize_kernel<<<(B + 127) / 128, 128, 0, s>>>(a);
+  cudaError_t e = fft_opt_in(lpc_kernel);
+  if (e != cudaSuccess) return e;
+  lpc_kernel<<<(rows + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, s>>>(a);
+  frame_finalize_kernel<<<(B * 32 + 127) / 128, 128, 0, s>>>(a);
   if (n_launches) *n_launches += 5;
   return cudaGetLastError();
 }

@@ -279,10 +279,9 @@ __device__ void burg_cepstrum(const PlcArgs &A, const short *pcm, float *out, co
 // are combined into mean / difference (freq.c:188-199) by plc_burg_combine_kernel
 __global__ void plc_burg_kernel(PlcArgs A) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  const size_t nthreads = (size_t)gridDim.x * blockDim.x;
   const int s = idx >> 1, half = idx & 1;
   if (s >= A.n_streams || !A.masks[mUpd * A.n_streams + s]) return;
-  Scratch S{A.fft_scratch + idx, nthreads};
+  const Scratch S = block_scratch();
   burg_cepstrum(A, A.w.in + (size_t)s * kFrame + half * kTOff, A.w.encf2 + (size_t)s * 36 + half * kBands, S);
 }
 
@@ -778,23 +777,24 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
     // Q: process_queued_update (lpcnet_plc.c:342-347)
     if (a.q) {
       plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, cs>>>(A, mQ, 0);
-      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mQ * B)) return -1;
+      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mQ * B, false, permQ, a.nq)) return -1;
       if (batch_sample_segment(p->syn, kFrame, M + (size_t)fQ * B, p->st.queued, p->w.sego, permQ, a.nq)) return -1;
     }
     if (a.upd) {
       plc_pre_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A);
-      plc_burg_kernel<<<(2 * B + 63) / 64, 64, 0, cs>>>(A);
+      CKP(fft_opt_in(plc_burg_kernel));
+      plc_burg_kernel<<<(2 * B + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, cs>>>(A);
       plc_burg_combine_kernel<<<(B * kBands + 255) / 256, 256, 0, cs>>>(A);
     }
     if (a.fg) {
       plc_pred_kernel<<<B, 256, 0, cs>>>(A, 1);
       plc_state_copy_kernel<<<B, 128, 0, cs>>>(p->snap, V.st, M + (size_t)mFG * B, B);
       plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, cs>>>(A, mFG, 0);
-      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B)) return -1;
+      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B, false, permFG, a.nfg)) return -1;
       if (batch_sample_segment(p->syn, kTOff, M + (size_t)fFgFree * B, nullptr, p->w.sego, permFG, a.nfg)) return -1;
       plc_fg_mid_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A);
       plc_clear_state_kernel<<<B, 128, 0, cs>>>(V.st, M + (size_t)mFG * B, B);
-      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B)) return -1;
+      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B, false, permFG, a.nfg)) return -1;
       if (batch_sample_segment(p->syn, kFrame, M + (size_t)fFgForced * B, p->w.segf, p->w.sego, permFG, a.nfg)) return -1;
       if (batch_sample_segment(p->syn, kTOff, M + (size_t)fFgFree * B, nullptr, p->w.sego2, permFG, a.nfg)) return -1;
       plc_fg_end_kernel<<<gs, tb, 0, cs>>>(A);
@@ -805,7 +805,7 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
     if (a.main_) {
       plc_pred_kernel<<<B, 256, 0, cs>>>(A, 0);
       plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, cs>>>(A, mMain, 1);
-      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mMain * B)) return -1;
+      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mMain * B, false, permMain, a.nmain)) return -1;
       plc_seg_prep_kernel<<<(B * kTOff + 255) / 256, 256, 0, cs>>>(A, 0);
       if (batch_sample_segment(p->syn, kTOff, M + (size_t)fA * B, p->w.segf, p->w.sego, permMain, a.nmain)) return -1;
       plc_seg_prep_kernel<<<(B * kTOff + 255) / 256, 256, 0, cs>>>(A, 1);
@@ -1006,7 +1006,8 @@ int plc_run_causal(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_f
     // ---- received frames (lpcnet_plc_update_causal) ----
     if (a.u) {
       c_pre_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A, row(cU));
-      plc_burg_kernel<<<(2 * B + 63) / 64, 64, 0, cs>>>(A);
+      CKP(fft_opt_in(plc_burg_kernel));
+      plc_burg_kernel<<<(2 * B + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, cs>>>(A);
       plc_burg_combine_kernel<<<(B * kBands + 255) / 256, 256, 0, cs>>>(A);
     }
     if (a.sb) {

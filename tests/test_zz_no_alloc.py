@@ -46,7 +46,8 @@ def test_noalloc_matches_frame_network_twice(eng, model_blob):
         free0 = torch.cuda.mem_get_info(dev)[0]
         eng.lpc_from_cepstrum_noalloc(d_in.data_ptr(), 36, d_lpc.data_ptr(), n, device=0)
         torch.cuda.synchronize()
-        assert torch.cuda.mem_get_info(dev)[0] == free0, "device memory in use changed across the call"
+        # (from the second call on: the first launch of a kernel may make the driver load its code, lazily)
+        assert call == 0 or torch.cuda.mem_get_info(dev)[0] == free0, "device memory in use changed across the call"
         got = d_lpc.cpu().numpy().reshape(B, F, 16)
         assert np.isfinite(got).all()
         assert np.array_equal(bits(got), bits(want)), f"call {call}: differs from lpcnet_batch_frame_network"
