@@ -181,6 +181,27 @@ LPCNET_B200_EXPORT int lpcnet_batch_read_profile(LPCNetBatch *b, double *sample_
  * 4608-byte rows (one embedding row) from an L2-resident 3.5 MB table with 128-bit loads. */
 LPCNET_B200_EXPORT int lpcnet_b200_measure_l2_gather(int device, double *gbytes_per_s);
 
+/* One handle over several GPUs of one box (no counterpart in the reference, which is single-stream
+ * and CPU-only): n_streams are split into contiguous shards (sizes differ by at most 1) over the devices whose bit is
+ * set in device_mask (0 = every visible device), one lpcnet_batch per GPU, one feeder thread per GPU.  Streams never
+ * interact, so nothing crosses NVLink; a call hands every feeder its rows of the caller's HOST buffers (layouts of
+ * lpcnet_batch_synthesize / _decode over all n_streams) and returns when every GPU is done.  Pinned buffers let each
+ * GPU stream its chunks out while it computes.  Errors: -1 / NULL with the failing GPU named in lpcnet_b200_last_error(). */
+typedef struct LPCNetMultiBatch LPCNetMultiBatch;
+LPCNET_B200_EXPORT LPCNetMultiBatch *lpcnet_batch_create_multi(const unsigned char *blob, int len, int n_streams,
+                                                               unsigned device_mask, int features_delay, float lpc_gamma);
+LPCNET_B200_EXPORT void lpcnet_multi_destroy(LPCNetMultiBatch *mb);
+LPCNET_B200_EXPORT int lpcnet_multi_n_streams(const LPCNetMultiBatch *mb);
+LPCNET_B200_EXPORT int lpcnet_multi_n_devices(const LPCNetMultiBatch *mb);
+/* shard k: the GPU it runs on and its stream range */
+LPCNET_B200_EXPORT int lpcnet_multi_shard(const LPCNetMultiBatch *mb, int k, int *device, int *first_stream, int *n_streams);
+LPCNET_B200_EXPORT int lpcnet_multi_set_seed(LPCNetMultiBatch *mb, int stream, const unsigned char *data, int n);
+LPCNET_B200_EXPORT int lpcnet_multi_reset(LPCNetMultiBatch *mb, int stream /* -1: all */);
+LPCNET_B200_EXPORT int lpcnet_multi_set_codebooks(LPCNetMultiBatch *mb, const float *codebooks, int n_floats);
+LPCNET_B200_EXPORT int lpcnet_multi_synthesize(LPCNetMultiBatch *mb, const float *features, int feature_stride,
+                                               int n_frames, short *pcm);
+LPCNET_B200_EXPORT int lpcnet_multi_decode(LPCNetMultiBatch *mb, const unsigned char *packets, int n_packets, short *pcm);
+
 /* Cepstrum -> LPC without any allocation.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
  * that forbid it).  Computes what the frame network computes per frame before its delay line (lpc_from_cepstrum and

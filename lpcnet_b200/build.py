@@ -15,7 +15,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "liblpcnet_b200.so")
 SOURCES = ["model.cu", "frame.cu", "sample.cu", "sample_t8.cu", "sample_t16.cu", "sample_t32.cu", "sample_pp.cu",
-           "api.cu", "probe.cu", "analysis.cu", "plc.cu", "noalloc.cu", "demo_shims.cu"]
+           "api.cu", "probe.cu", "analysis.cu", "plc.cu", "noalloc.cu", "demo_shims.cu", "multi.cu"]
 HEADERS = ["engine.h", "bitexact.cuh", "sample_kernel.cuh", "dsp.cuh", "vq.cuh", "plc_causal.cuh", "dred.cuh", os.path.join("..", "..", "include", "lpcnet_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-fmad=false", "-Xcompiler", "-fPIC,-fvisibility=hidden"]

@@ -44,6 +44,9 @@ EXPORTED_SYMBOLS = [
     "lpcnet_batch_set_profiling", "lpcnet_batch_read_profile", "lpcnet_batch_profile_launches", "lpcnet_b200_measure_l2_gather",
     "lpcnet_b200_set_rcp_table", "lpcnet_b200_default_rcp_table", "lpcnet_b200_set_model_constants",
     "lpcnet_b200_last_error", "lpcnet_b200_device_count", "lpcnet_b200_lpc_from_cepstrum_noalloc",
+    "lpcnet_batch_create_multi", "lpcnet_multi_destroy", "lpcnet_multi_n_streams", "lpcnet_multi_n_devices",
+    "lpcnet_multi_shard", "lpcnet_multi_set_seed", "lpcnet_multi_reset", "lpcnet_multi_set_codebooks",
+    "lpcnet_multi_synthesize", "lpcnet_multi_decode",
     "lpcnet_encoder_get_size", "lpcnet_encoder_init", "lpcnet_encoder_create", "lpcnet_encoder_destroy",
     "lpcnet_compute_single_frame_features", "lpcnet_compute_single_frame_features_float",
     "lpcnet_feature_batch_create", "lpcnet_feature_batch_destroy", "lpcnet_feature_batch_n_streams",
@@ -109,6 +112,17 @@ def load_library() -> C.CDLL:
     L.lpcnet_batch_profile_launches.argtypes = [vp, vp, vp, ci]
     L.lpcnet_b200_measure_l2_gather.argtypes = [ci, vp]
     L.lpcnet_b200_lpc_from_cepstrum_noalloc.argtypes = [ci, vp, ci, vp, ci, vp]
+    L.lpcnet_batch_create_multi.restype = vp
+    L.lpcnet_batch_create_multi.argtypes = [vp, ci, ci, C.c_uint, ci, cf]
+    L.lpcnet_multi_destroy.argtypes = [vp]
+    L.lpcnet_multi_n_streams.argtypes = [vp]
+    L.lpcnet_multi_n_devices.argtypes = [vp]
+    L.lpcnet_multi_shard.argtypes = [vp, ci, vp, vp, vp]
+    L.lpcnet_multi_set_seed.argtypes = [vp, ci, C.c_char_p, ci]
+    L.lpcnet_multi_reset.argtypes = [vp, ci]
+    L.lpcnet_multi_set_codebooks.argtypes = [vp, vp, ci]
+    L.lpcnet_multi_synthesize.argtypes = [vp, vp, ci, ci, vp]
+    L.lpcnet_multi_decode.argtypes = [vp, vp, ci, vp]
     L.lpcnet_b200_set_rcp_table.argtypes = [vp]
     L.lpcnet_b200_default_rcp_table.argtypes = [vp]
     L.lpcnet_b200_set_model_constants.argtypes = [ci, cf]
@@ -378,6 +392,62 @@ class Batch:
         s = np.zeros(1, STATE_DTYPE)
         s[0] = state
         _check(self.L.lpcnet_batch_set_state(self.h, stream, _p(s)), "lpcnet_batch_set_state")
+
+
+class MultiBatch:
+    """n_streams sharded over the GPUs of one box behind one handle (lpcnet_batch_create_multi): contiguous shards,
+    one feeder thread per GPU, host buffers in and out."""
+
+    def __init__(self, blob: bytes, n_streams: int, device_mask: int = 0, features_delay: int = 2, lpc_gamma: float = 1.0):
+        self.L = load_library()
+        self._blob = np.frombuffer(blob, np.uint8)
+        self.h = self.L.lpcnet_batch_create_multi(_p(self._blob), len(blob), n_streams, device_mask, features_delay,
+                                                  C.c_float(lpc_gamma))
+        if not self.h:
+            raise LPCNetError(f"lpcnet_batch_create_multi: {last_error()}")
+        self.n_streams = n_streams
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.lpcnet_multi_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    @property
+    def shards(self):
+        """[(device, first_stream, n_streams)]"""
+        out = []
+        for k in range(self.L.lpcnet_multi_n_devices(self.h)):
+            d, f, n = C.c_int(0), C.c_int(0), C.c_int(0)
+            _check(self.L.lpcnet_multi_shard(self.h, k, C.byref(d), C.byref(f), C.byref(n)), "lpcnet_multi_shard")
+            out.append((d.value, f.value, n.value))
+        return out
+
+    def set_seed(self, stream: int, seed: bytes):
+        _check(self.L.lpcnet_multi_set_seed(self.h, stream, seed, len(seed)), "lpcnet_multi_set_seed")
+
+    def reset(self, stream: int = -1):
+        _check(self.L.lpcnet_multi_reset(self.h, stream), "lpcnet_multi_reset")
+
+    def set_codebooks(self, codebooks):
+        cb = np.ascontiguousarray(codebooks, np.float32).reshape(-1)
+        _check(self.L.lpcnet_multi_set_codebooks(self.h, _p(cb), cb.size), "lpcnet_multi_set_codebooks")
+
+    def synthesize(self, features, pcm_out=None):
+        f = np.ascontiguousarray(features, np.float32)
+        assert f.ndim == 3 and f.shape[0] == self.n_streams, f.shape
+        pcm = pcm_out if pcm_out is not None else np.zeros((self.n_streams, f.shape[1] * FRAME_SIZE), np.int16)
+        _check(self.L.lpcnet_multi_synthesize(self.h, _p(f), f.shape[2], f.shape[1], _p(pcm)), "lpcnet_multi_synthesize")
+        return pcm
+
+    def decode(self, packets, pcm_out=None):
+        pk = np.ascontiguousarray(packets, np.uint8)
+        assert pk.ndim == 3 and pk.shape[0] == self.n_streams and pk.shape[2] == 8
+        pcm = pcm_out if pcm_out is not None else np.zeros((self.n_streams, pk.shape[1] * 640), np.int16)
+        _check(self.L.lpcnet_multi_decode(self.h, _p(pk), pk.shape[1], _p(pcm)), "lpcnet_multi_decode")
+        return pcm
 
 
 class Synth:
