@@ -78,6 +78,7 @@ __global__ void preemph_kernel(AnalysisArgs A) {
   const size_t total = (size_t)A.n_streams * L;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int s = (int)(i / L), k = (int)(i % L);
+    if (A.stream_mask && !A.stream_mask[s]) continue;   // (its rows may belong to a concurrent call on another CUDA stream)
     float v;
     if (k < kOverlap) {
       v = A.st.p_hist[(size_t)s * kOverlap + k];
@@ -156,6 +157,7 @@ __global__ void residual_kernel(AnalysisArgs A) {
   const size_t total = (size_t)A.n_streams * L;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int s = (int)(i / L), n = (int)(i % L), f = n / kFrame;
+    if (A.stream_mask && !A.stream_mask[s]) continue;
     const float *a = A.P + (size_t)s * (kOverlap + L) + kTOff + n;
     const float *lpc = A.features + ((size_t)s * A.total_frames + A.frame0 + f) * kNF + kBands + 2;
     float sum = a[0];

@@ -101,6 +101,7 @@ struct LPCNetBatch {
   void *d_packets = nullptr; size_t d_packets_bytes = 0;
   // compact copy of the streams one PLC sample segment moves (batch_sample_segment with a stream list)
   void *d_compact = nullptr; size_t d_compact_bytes = 0;
+  void *d_compact2 = nullptr; size_t d_compact2_bytes = 0;   // ... of a segment on a side stream (beside one on `stream`)
 };
 
 namespace {
@@ -412,7 +413,7 @@ std::vector<float> lpcb::file_codebooks() {
 BatchView lpcb::batch_view(LPCNetBatch *b) { return BatchView{b->st, &b->model, b->stream, b->n_streams, b->device}; }
 
 int lpcb::batch_frame_network_masked(LPCNetBatch *b, const float *d_features, int stride, const uint8_t *d_mask,
-                                     bool state_only, const int *d_rows, int n_rows) {
+                                     bool state_only, const int *d_rows, int n_rows, cudaStream_t side) {
   CK(cudaSetDevice(b->device));
   if (ensure_frame_buffers(b, 1) || (state_only && ensure_frame_buffers(b, 1, true))) return -1;
   FrameArgs fa{};
@@ -422,13 +423,14 @@ int lpcb::batch_frame_network_masked(LPCNetBatch *b, const float *d_features, in
   fa.stream_mask = d_mask;
   if (d_rows && !getenv("LPCNET_B200_NO_COMPACT")) { fa.rows = d_rows; fa.n_rows = n_rows; fa.stream_mask = nullptr; }
   int nl = 0;
-  CK(launch_frame_network(fa, b->stream, &nl));
+  CK(launch_frame_network(fa, side ? side : b->stream, &nl));
   b->launches += nl;
   return 0;
 }
 
 int lpcb::batch_sample_segment(LPCNetBatch *b, int n, const uint8_t *d_flags, const short *d_forced, short *d_out,
-                               const int *d_perm, int n_act) {
+                               const int *d_perm, int n_act, cudaStream_t side, int tile_override) {
+  cudaStream_t cs = side ? side : b->stream;
   if (n <= 0 || n > kFrame) return fail("sample segment must be 1..160 steps");
   CK(cudaSetDevice(b->device));
   if (d_perm && n_act == 0) return 0;
@@ -439,24 +441,24 @@ int lpcb::batch_sample_segment(LPCNetBatch *b, int n, const uint8_t *d_flags, co
     const size_t o_ca = take(A * kRowsAP * 4), o_ga = take(A * kN * 4), o_cb = take(A * kRowsB * 4), o_gb = take(A * kNB * 4),
                  o_ls = take(A * 16 * 4), o_lpc = take(A * 16 * 4), o_rng = take(A * 16), o_de = take(A * 4), o_le = take(A * 4),
                  o_fl = take(A), o_fo = take(A * kFrame * 2), o_out = take(A * kFrame * 2);
-    if (grow(&b->d_compact, &b->d_compact_bytes, off)) return -1;
-    char *p = static_cast<char *>(b->d_compact);
+    if (side ? grow(&b->d_compact2, &b->d_compact2_bytes, off) : grow(&b->d_compact, &b->d_compact_bytes, off)) return -1;
+    char *p = static_cast<char *>(side ? b->d_compact2 : b->d_compact);
     CompactView c{};
     c.cond_a = (float *)(p + o_ca); c.st.gru_a = (float *)(p + o_ga); c.cond_b = (float *)(p + o_cb); c.st.gru_b = (float *)(p + o_gb);
     c.st.last_sig = (float *)(p + o_ls); c.lpc = (float *)(p + o_lpc); c.st.rng = (uint32_t *)(p + o_rng);
     c.st.deemph = (float *)(p + o_de); c.st.last_exc = (int *)(p + o_le); c.flags = (uint8_t *)(p + o_fl);
     c.forced = (short *)(p + o_fo); c.out = (short *)(p + o_out);
-    compact_gather_kernel<<<n_act, 128, 0, b->stream>>>(c, b->st, b->fb.cond_a, b->fb.cond_b, b->fb.lpc, d_flags, d_forced, d_perm, n);
+    compact_gather_kernel<<<n_act, 128, 0, cs>>>(c, b->st, b->fb.cond_a, b->fb.cond_b, b->fb.lpc, d_flags, d_forced, d_perm, n);
     SampleArgs sa{};
     sa.m = b->model.d; sa.st = c.st; sa.n_streams = n_act; sa.n_frames = 1; sa.spf = n;
     sa.frame0 = 0; sa.total_frames = 1;
     sa.cond_a = c.cond_a; sa.cond_b = c.cond_b; sa.lpc = c.lpc; sa.active = c.flags;
     sa.pcm = c.out; sa.forced = d_forced ? c.forced : nullptr; sa.forced_by_flag = 1;
     int nl = 0;
-    int tile = b->tile ? b->tile : (n_act <= 8 * b->n_sms ? 8 : 16);
+    int tile = tile_override > 0 ? tile_override : b->tile ? b->tile : (n_act <= 8 * b->n_sms ? 8 : 16);
     tile = tile < b->max_tile ? tile : b->max_tile;
-    CK(launch_sample_kernel(sa, tile, b->n_sms, b->stream, &nl));
-    compact_scatter_kernel<<<n_act, 128, 0, b->stream>>>(c, b->st, d_out, d_perm, n);
+    CK(launch_sample_kernel(sa, tile, b->n_sms, cs, &nl));
+    compact_scatter_kernel<<<n_act, 128, 0, cs>>>(c, b->st, d_out, d_perm, n);
     CK(cudaGetLastError());
     b->launches += nl + 2;
     return 0;
@@ -467,7 +469,9 @@ int lpcb::batch_sample_segment(LPCNetBatch *b, int n, const uint8_t *d_flags, co
   sa.cond_a = b->fb.cond_a; sa.cond_b = b->fb.cond_b; sa.lpc = b->fb.lpc; sa.active = d_flags;
   sa.pcm = d_out; sa.forced = d_forced; sa.forced_by_flag = 1;
   int nl = 0;
-  CK(launch_sample_kernel(sa, auto_tile(b), b->n_sms, b->stream, &nl));
+  int tile = tile_override > 0 ? tile_override : auto_tile(b);
+  tile = tile < b->max_tile ? tile : b->max_tile;
+  CK(launch_sample_kernel(sa, tile, b->n_sms, cs, &nl));
   b->launches += nl;
   return 0;
 }
@@ -574,7 +578,7 @@ void lpcnet_batch_destroy(LPCNetBatch *b) {
     cudaEventDestroy(b->ev_entry);
     for (int k = 0; k < 2; k++) { cudaEventDestroy(b->ev_frames[k]); cudaEventDestroy(b->ev_samples[k]); }
   }
-  void *ptrs[] = {b->st_alloc, b->fb_alloc, b->fb2_alloc, b->d_feat, b->d_pcm, b->d_forced, b->d_trace, b->d_logits, b->d_packets, b->d_compact};
+  void *ptrs[] = {b->st_alloc, b->fb_alloc, b->fb2_alloc, b->d_feat, b->d_pcm, b->d_forced, b->d_trace, b->d_logits, b->d_packets, b->d_compact, b->d_compact2};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (b->cstream) { cudaStreamSynchronize(b->cstream); cudaStreamDestroy(b->cstream); cudaEventDestroy(b->ev_chunk); cudaEventDestroy(b->ev_copied); }
   if (b->own_stream) cudaStreamDestroy(b->own_stream);

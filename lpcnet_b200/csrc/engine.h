@@ -296,13 +296,17 @@ std::vector<float> file_codebooks();
 // d_rows / n_rows (optional): the device list of the streams the mask selects -- the kernels then run over the list
 // (the PLC's small classes: a tenth of the batch) instead of testing the mask for every stream.
 int batch_frame_network_masked(LPCNetBatch *b, const float *d_features, int stride, const uint8_t *d_mask,
-                               bool state_only = false, const int *d_rows = nullptr, int n_rows = 0);
+                               bool state_only = false, const int *d_rows = nullptr, int n_rows = 0,
+                               cudaStream_t side = nullptr);
 // n sample steps (lpcnet_synthesize_tail_impl) on the conditioning of the last frame network.  flags [B]: 0 the
 // stream does not move, 1 free-running, 3 teacher-forced on d_forced [B][n]; d_out [B][n].
 // d_perm (nullable): device list of the n_act streams whose flag is not 0, ascending; when they are at most half of
 // the batch they are advanced as a dense batch of their own (gather, sample kernel, scatter).
+// side (both functions): run on this CUDA stream instead of the batch's, with a gather buffer of its own, so that a
+// segment of other streams can run on the batch's stream at the same time (the caller orders the two with events;
+// the frame buffers are rows per stream, and the sample kernel stores the state of the streams it moved only).
 int batch_sample_segment(LPCNetBatch *b, int n, const uint8_t *d_flags, const short *d_forced, short *d_out,
-                         const int *d_perm = nullptr, int n_act = 0);
+                         const int *d_perm = nullptr, int n_act = 0, cudaStream_t side = nullptr, int tile_override = 0);
 // one frame of analysis for the streams with mask != 0: d_pcm16 [B][160] -> d_features [B][36] (others untouched)
 int feature_batch_frame_masked(LPCNetFeatureBatch *b, const short *d_pcm16, const uint8_t *d_mask, float *d_features,
                                cudaStream_t stream);

@@ -8,10 +8,13 @@
 // lost before, an update queued), which the host knows: it sorts the streams of every frame into classes and
 // uploads one byte mask per stage; all streams then walk the same sequence of stages, and a stage moves only
 // the streams of its class:
-//   Q   queued update            frame network + 160 teacher-forced samples
 //   FG  first good frame after a loss: prediction, 80 free samples, the backward pass on the reversed frame
 //       (clear_state, frame network, 160 forced + 80 free samples), cross-fade, state restore, analysis
+//   Q   the update FG queues for the stream's next call: frame network + 160 teacher-forced samples, run at once
 //   M   good frame (2 x 80 forced samples) or lost frame (80 forced-or-free + 80 free samples)
+// FG and Q move few streams (those leaving a loss burst) through a long chain of sample steps (320 + 160), M moves
+// all the others through 160: the FG + Q chain runs on a side CUDA stream of higher priority, beside M on the batch's
+// stream, with segment buffers of its own; events order it against the stages that feed it and the frame's end.
 // The sample steps are the synthesis engine's persistent kernel (sample_kernel.cuh) with per-stream flags:
 // inactive / free-running / teacher-forced.  Frame-rate arithmetic (DC filter in double, Burg cepstrum, the
 // int8 predictor GRUs, cross-fade) follows the reference operation by operation; -fmad=false.
@@ -36,7 +39,7 @@ constexpr int kTOff = 80, kBands = 18;
 
 // stream classes of one frame (host side) and the per-stage byte masks derived from them
 enum Cls : uint8_t { kG0 = 0, kFG = 1, kL0 = 2, kL1 = 3 };   // good, first good after loss, first lost, lost again
-enum Mask { mQ = 0, mUpd, mFG, mMain, mL1, fQ, fFgFree, fFgForced, fA, fB, mCls, kNMasks };
+enum Mask { mUpdM = 0 /* update && !FG */, mUpd, mFG, mMain, mL1, fFgFree, fFgForced, fA, fB, mCls, kNMasks };
 
 struct PlcState {        // per stream, device
   short *pcm;            // [B][160]  st->pcm[0..160)
@@ -628,6 +631,10 @@ struct LPCNetPLCBatch {
   void *d_io = nullptr; size_t d_io_bytes = 0;
   void *d_ctl = nullptr; size_t d_ctl_bytes = 0;
   long long frames_done = 0;
+  // side chain (Q and FG streams): CUDA stream, segment buffers [B][160] x 3, events
+  cudaStream_t side = nullptr;
+  PlcWork w_side{};
+  cudaEvent_t ev_pre = nullptr, ev_side = nullptr, ev_fin = nullptr;
   // causal / codec modes (lpcnet_plc.c:185-340): device buffers and the host's copy of the control state
   bool causal = false;
   int enable_blending = 1, delay = 0;
@@ -669,7 +676,8 @@ int plc_alloc(LPCNetPLCBatch *p) {
   const size_t o_in = take(B * kFrame * 2), o_save = take(B * kFrame * 2), o_lp = take(B * kFrame * 2),
                o_mb = take(B * 8), o_de = take(B * 4), o_burg = take(B * 36 * 4), o_e1 = take(B * 36 * 4),
                o_e2 = take(B * 36 * 4), o_fn = take(B * 20 * 4), o_sf = take(B * kFrame * 2), o_so = take(B * kFrame * 2),
-               o_so2 = take(B * kFrame * 2), o_out = take(B * kFrame * 2);
+               o_so2 = take(B * kFrame * 2), o_out = take(B * kFrame * 2), o_sf1 = take(B * kFrame * 2),
+               o_so1 = take(B * kFrame * 2), o_so21 = take(B * kFrame * 2);
   const size_t o_c1 = take(B * 2 * kConvIn * 4), o_c2 = take(B * 2 * kC * 4), o_ga = take(B * kN * 4), o_gb = take(B * kNB * 4),
                o_ls = take(B * 16 * 4), o_lpc = take(B * 16 * 4), o_rng = take(B * 16), o_dm = take(B * 4),
                o_le = take(B * 4), o_fc = take(B * 4), o_ol = take(B * kMaxDelay * 16 * 4);
@@ -687,6 +695,12 @@ int plc_alloc(LPCNetPLCBatch *p) {
   p->w.encf = (float *)(b + o_e1); p->w.encf2 = (float *)(b + o_e2); p->w.fnfeat = (float *)(b + o_fn);
   p->w.segf = (short *)(b + o_sf); p->w.sego = (short *)(b + o_so); p->w.sego2 = (short *)(b + o_so2);
   p->w.out = (short *)(b + o_out);
+  p->w_side = p->w;
+  p->w_side.segf = (short *)(b + o_sf1); p->w_side.sego = (short *)(b + o_so1); p->w_side.sego2 = (short *)(b + o_so21);
+  int lo = 0, hi = 0;
+  CKP(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+  CKP(cudaStreamCreateWithPriority(&p->side, cudaStreamNonBlocking, hi));
+  for (cudaEvent_t *e : {&p->ev_pre, &p->ev_side, &p->ev_fin}) CKP(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
   p->snap.conv1_state = (float *)(b + o_c1); p->snap.conv2_state = (float *)(b + o_c2); p->snap.gru_a = (float *)(b + o_ga);
   p->snap.gru_b = (float *)(b + o_gb); p->snap.last_sig = (float *)(b + o_ls); p->snap.lpc = (float *)(b + o_lpc);
   p->snap.rng = (uint32_t *)(b + o_rng); p->snap.deemph = (float *)(b + o_dm); p->snap.last_exc = (int *)(b + o_le);
@@ -722,39 +736,35 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
   cudaStream_t cs = V.stream;
   // classes, masks and loss counters of every frame (they depend on the loss pattern only)
   const size_t lc_off = ((size_t)kNMasks * B + 15) & ~size_t(15);           // the uint16 counters sit aligned
-  // stream lists of the three sample-segment groups (queued update, first good frame, main), for the compact path
+  // stream lists of the two sample-segment groups (first good frame, main), for the compact path
   const size_t perm_off = (lc_off + (size_t)B * 2 + 15) & ~size_t(15);
-  const size_t per_frame = (perm_off + (size_t)3 * B * 4 + 15) & ~size_t(15);
+  const size_t per_frame = (perm_off + (size_t)2 * B * 4 + 15) & ~size_t(15);
   std::vector<uint8_t> ctl(per_frame * n_frames);
-  struct Any { bool q, upd, fg, main_, l1; int nq, nfg, nmain; };
+  struct Any { bool upd, fg, main_, l1, updm; int nfg, nmain; };
   std::vector<Any> any(n_frames);
   for (int f = 0; f < n_frames; f++) {
     uint8_t *m = ctl.data() + per_frame * f;
     uint16_t *lc = reinterpret_cast<uint16_t *>(m + lc_off);
     int *perm = reinterpret_cast<int *>(m + perm_off);
-    Any a{false, false, false, false, false, 0, 0, 0};
+    Any a{false, false, false, false, false, 0, 0};
     for (int s = 0; s < B; s++) {
       const bool is_lost = lost[(size_t)s * total_frames + f0 + f] != 0;
       const int c = p->loss_count[s];
       const uint8_t cls = is_lost ? (c == 0 ? kL0 : kL1) : (c == 0 ? kG0 : kFG);
-      const bool q = p->queued[s] != 0;
       m[mCls * B + s] = cls;
-      m[mQ * B + s] = q;
-      m[fQ * B + s] = q ? 3 : 0;
       m[mUpd * B + s] = !is_lost;
       m[mFG * B + s] = cls == kFG;
       m[fFgFree * B + s] = cls == kFG ? 1 : 0;
       m[fFgForced * B + s] = cls == kFG ? 3 : 0;
       m[mMain * B + s] = cls != kFG;
       m[mL1 * B + s] = cls == kL1;
+      m[mUpdM * B + s] = !is_lost && cls != kFG;
       m[fA * B + s] = cls == kG0 || cls == kL0 ? 3 : (cls == kL1 ? 1 : 0);
       m[fB * B + s] = cls == kG0 ? 3 : (cls == kFG ? 0 : 1);
       lc[s] = (uint16_t)(c > 60000 ? 60000 : c);
-      a.q |= q; a.upd |= !is_lost; a.fg |= cls == kFG; a.main_ |= cls != kFG; a.l1 |= cls == kL1;
-      if (q) perm[a.nq++] = s;
-      if (cls == kFG) perm[B + a.nfg++] = s; else perm[2 * B + a.nmain++] = s;
-      // process_queued_update runs at the start of both entry points; only the FG branch queues a new one
-      p->queued[s] = cls == kFG;
+      a.upd |= !is_lost; a.fg |= cls == kFG; a.main_ |= cls != kFG; a.l1 |= cls == kL1;
+      a.updm |= !is_lost && cls != kFG;
+      if (cls == kFG) perm[a.nfg++] = s; else perm[B + a.nmain++] = s;
       p->loss_count[s] = is_lost ? c + 1 : 0;
     }
     any[f] = a;
@@ -767,19 +777,25 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
   A.tab = p->tab; A.fft_scratch = p->fft_scratch; A.fade = p->fade;
   A.pcm_io = static_cast<short *>(p->d_io); A.n_streams = B; A.total_frames = total_frames; A.remove_dc = p->remove_dc;
   const int tb = 128, gs = (B + tb - 1) / tb;
+  // The side chain: Q and FG streams on p->side (or on the batch's stream: LPCNET_B200_PLC_ONE_STREAM, the sequential
+  // order of the reference's branches, kept for A/B runs).  A1 = the stage arguments with the side chain's buffers.
+  const char *one = getenv("LPCNET_B200_PLC_ONE_STREAM");
+  const bool two = !(one && atoi(one));
+  cudaStream_t ss = two ? p->side : cs;
+  int main_tile = 0;
+  if (const char *e = getenv("LPCNET_B200_PLC_MAIN_TILE")) main_tile = atoi(e);
+  PlcArgs A1 = A;
+  if (two) A1.w = p->w_side;
+  if (two) CKP(cudaEventRecord(p->ev_fin, cs));            // the control rows are uploaded, the last call's frames done
   for (int f = 0; f < n_frames; f++) {
     const uint8_t *M = static_cast<const uint8_t *>(p->d_ctl) + per_frame * f;
-    A.masks = M;
-    A.lossc = reinterpret_cast<const uint16_t *>(M + lc_off);
-    A.frame = f0 + f;
+    A.masks = A1.masks = M;
+    A.lossc = A1.lossc = reinterpret_cast<const uint16_t *>(M + lc_off);
+    A.frame = A1.frame = f0 + f;
     const Any a = any[f];
-    const int *permQ = reinterpret_cast<const int *>(M + perm_off), *permFG = permQ + B, *permMain = permQ + 2 * B;
-    // Q: process_queued_update (lpcnet_plc.c:342-347)
-    if (a.q) {
-      plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, cs>>>(A, mQ, 0);
-      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mQ * B, false, permQ, a.nq)) return -1;
-      if (batch_sample_segment(p->syn, kFrame, M + (size_t)fQ * B, p->st.queued, p->w.sego, permQ, a.nq)) return -1;
-    }
+    const int *permFG = reinterpret_cast<const int *>(M + perm_off), *permMain = permFG + B;
+    const bool side_work = two && a.fg;
+    if (side_work) CKP(cudaStreamWaitEvent(ss, p->ev_fin, 0));
     if (a.upd) {
       plc_pre_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A);
       CKP(fft_opt_in(plc_burg_kernel));
@@ -787,33 +803,47 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
       plc_burg_combine_kernel<<<(B * kBands + 255) / 256, 256, 0, cs>>>(A);
     }
     if (a.fg) {
-      plc_pred_kernel<<<B, 256, 0, cs>>>(A, 1);
-      plc_state_copy_kernel<<<B, 128, 0, cs>>>(p->snap, V.st, M + (size_t)mFG * B, B);
-      plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, cs>>>(A, mFG, 0);
-      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B, false, permFG, a.nfg)) return -1;
-      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fFgFree * B, nullptr, p->w.sego, permFG, a.nfg)) return -1;
-      plc_fg_mid_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A);
-      plc_clear_state_kernel<<<B, 128, 0, cs>>>(V.st, M + (size_t)mFG * B, B);
-      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B, false, permFG, a.nfg)) return -1;
-      if (batch_sample_segment(p->syn, kFrame, M + (size_t)fFgForced * B, p->w.segf, p->w.sego, permFG, a.nfg)) return -1;
-      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fFgFree * B, nullptr, p->w.sego2, permFG, a.nfg)) return -1;
-      plc_fg_end_kernel<<<gs, tb, 0, cs>>>(A);
-      plc_state_copy_kernel<<<B, 128, 0, cs>>>(V.st, p->snap, M + (size_t)mFG * B, B);
-      if (feature_batch_frame_masked(p->ana, p->st.pcm, M + (size_t)mFG * B, p->w.encf2, cs)) return -1;
+      if (two) { CKP(cudaEventRecord(p->ev_pre, cs)); CKP(cudaStreamWaitEvent(ss, p->ev_pre, 0)); }
+      plc_pred_kernel<<<B, 256, 0, ss>>>(A1, 1);
+      plc_state_copy_kernel<<<B, 128, 0, ss>>>(p->snap, V.st, M + (size_t)mFG * B, B);
+      plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, ss>>>(A1, mFG, 0);
+      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B, false, permFG, a.nfg, two ? ss : nullptr)) return -1;
+      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fFgFree * B, nullptr, A1.w.sego, permFG, a.nfg, two ? ss : nullptr)) return -1;
+      plc_fg_mid_kernel<<<wps_grid(B), kWpsThreads, 0, ss>>>(A1);
+      plc_clear_state_kernel<<<B, 128, 0, ss>>>(V.st, M + (size_t)mFG * B, B);
+      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B, false, permFG, a.nfg, two ? ss : nullptr)) return -1;
+      if (batch_sample_segment(p->syn, kFrame, M + (size_t)fFgForced * B, A1.w.segf, A1.w.sego, permFG, a.nfg, two ? ss : nullptr)) return -1;
+      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fFgFree * B, nullptr, A1.w.sego2, permFG, a.nfg, two ? ss : nullptr)) return -1;
+      plc_fg_end_kernel<<<gs, tb, 0, ss>>>(A1);
+      plc_state_copy_kernel<<<B, 128, 0, ss>>>(V.st, p->snap, M + (size_t)mFG * B, B);
+      if (feature_batch_frame_masked(p->ana, p->st.pcm, M + (size_t)mFG * B, p->w.encf2, ss)) return -1;
+      // (the analysis of an FG stream's input frame follows that of its concealment buffer: same chain)
+      if (two && feature_batch_frame_masked(p->ana, p->w.in, M + (size_t)mFG * B, p->w.encf, ss)) return -1;
+      // Q: process_queued_update (lpcnet_plc.c:342-347) -- the update the FG branch queues for the stream's next call
+      // (frame network on st->features + 160 samples forced on queued_samples) touches the synthesis state only, and
+      // nothing between here and that call does: it runs now, at the end of the side chain, beside the main class.
+      plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, ss>>>(A1, mFG, 0);
+      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B, false, permFG, a.nfg, two ? ss : nullptr)) return -1;
+      if (batch_sample_segment(p->syn, kFrame, M + (size_t)fFgForced * B, p->st.queued, A1.w.sego, permFG, a.nfg, two ? ss : nullptr)) return -1;
     }
-    if (a.upd && feature_batch_frame_masked(p->ana, p->w.in, M + (size_t)mUpd * B, p->w.encf, cs)) return -1;
+    if (side_work) CKP(cudaEventRecord(p->ev_side, ss));
+    if (two) {
+      if (a.updm && feature_batch_frame_masked(p->ana, p->w.in, M + (size_t)mUpdM * B, p->w.encf, cs)) return -1;
+    } else if (a.upd && feature_batch_frame_masked(p->ana, p->w.in, M + (size_t)mUpd * B, p->w.encf, cs)) return -1;
     if (a.main_) {
       plc_pred_kernel<<<B, 256, 0, cs>>>(A, 0);
       plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, cs>>>(A, mMain, 1);
       if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mMain * B, false, permMain, a.nmain)) return -1;
       plc_seg_prep_kernel<<<(B * kTOff + 255) / 256, 256, 0, cs>>>(A, 0);
-      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fA * B, p->w.segf, p->w.sego, permMain, a.nmain)) return -1;
+      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fA * B, p->w.segf, p->w.sego, permMain, a.nmain, nullptr, main_tile)) return -1;
       plc_seg_prep_kernel<<<(B * kTOff + 255) / 256, 256, 0, cs>>>(A, 1);
-      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fB * B, p->w.segf, p->w.sego2, permMain, a.nmain)) return -1;
+      if (batch_sample_segment(p->syn, kTOff, M + (size_t)fB * B, p->w.segf, p->w.sego2, permMain, a.nmain, nullptr, main_tile)) return -1;
       plc_lost_mid_kernel<<<gs, tb, 0, cs>>>(A);
       if (a.l1 && feature_batch_frame_masked(p->ana, p->st.pcm, M + (size_t)mL1 * B, p->w.encf2, cs)) return -1;
     }
+    if (side_work) CKP(cudaStreamWaitEvent(cs, p->ev_side, 0));
     plc_finish_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A);
+    if (two) CKP(cudaEventRecord(p->ev_fin, cs));
     CKP(cudaGetLastError());
     p->frames_done++;
   }
@@ -1083,6 +1113,8 @@ LPCNetPLCBatch *lpcnet_plc_batch_create(const unsigned char *blob, int len, int 
 void lpcnet_plc_batch_destroy(LPCNetPLCBatch *p) {
   if (!p) return;
   if (p->syn) lpcnet_batch_sync(p->syn);
+  if (p->side) { cudaStreamSynchronize(p->side); cudaStreamDestroy(p->side); }
+  for (cudaEvent_t e : {p->ev_pre, p->ev_side, p->ev_fin}) if (e) cudaEventDestroy(e);
   cudaFree(p->alloc); cudaFree(p->tab_alloc); cudaFree(p->d_io); cudaFree(p->d_ctl); cudaFree(p->causal_alloc);
   if (p->ana) lpcnet_feature_batch_destroy(p->ana);
   if (p->syn) lpcnet_batch_destroy(p->syn);

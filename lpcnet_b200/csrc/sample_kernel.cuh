@@ -462,6 +462,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
     if (TMAF && tid == 0) fetch_frame(0);
     if (OVL && !twarp) product_ahead(s_xa + cur * NS * kXaStride);   // sums for the tile's first step
 
+    int ever_act = 0;   // (threads < NS) was this stream active in any frame of the launch?
     for (int f = 0; f < A.n_frames; f++) {
       // ---- frame prologue: LPC, GRU-B conditioning, active flags ----
       // (every thread of the group is past frame f - 1 here: its reads of the other buffer ended before the last barrier)
@@ -484,6 +485,7 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
         const int gs = stream0 + tid;
         my_act = (gs < Bend) ? (int)A.active[(size_t)f * B + gs] : 0;
         s_act[tid] = my_act;
+        ever_act |= my_act;
       }
       int any_act;
       if (G == 1) {
@@ -913,6 +915,10 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
     }    // frame
 
     // ---- store the tile's stream state ----
+    // Only of the streams the launch moved: a stream that stayed inactive may be advanced by another launch on
+    // another CUDA stream at the same time (the PLC's side chain, plc.cu), whose stores these would overwrite.
+    if (tid < NS) s_act[tid] = ever_act;
+    gsync();
 #pragma unroll
     for (int u = 0; u < UW; u++) {
       const int ug = warp + u * WG;
@@ -921,18 +927,18 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
 #pragma unroll
         for (int h = 0; h < NV / 2; h++) {
           const int s = mt * VR + g + h * 8;
-          if (stream0 + s < Bend) *reinterpret_cast<float2 *>(A.st.gru_a + (size_t)(stream0 + s) * kN + ug * 8 + 2 * t) = a_reg[u][mt][h];
+          if (stream0 + s < Bend && s_act[s]) *reinterpret_cast<float2 *>(A.st.gru_a + (size_t)(stream0 + s) * kN + ug * 8 + 2 * t) = a_reg[u][mt][h];
         }
     }
     for (int i = tid; i < NS * 16; i += TG) {
       const int s = i >> 4, j = i & 15;
-      if (stream0 + s < Bend) {
+      if (stream0 + s < Bend && s_act[s]) {
         A.st.gru_b[(size_t)(stream0 + s) * kNB + j] = s_bst[s * 20 + j];
       }
     }
-    if (grp < NS && stream0 + grp < Bend) A.st.last_sig[(size_t)(stream0 + grp) * 16 + l16] = t_x;
+    if (grp < NS && stream0 + grp < Bend && s_act[grp]) A.st.last_sig[(size_t)(stream0 + grp) * 16 + l16] = t_x;
     for (int s = tid; s < NS; s += TG) {
-      if (stream0 + s < Bend) {
+      if (stream0 + s < Bend && s_act[s]) {
         A.st.deemph[stream0 + s] = s_deemph[s];
         A.st.last_exc[stream0 + s] = s_lexc[s];
 #pragma unroll

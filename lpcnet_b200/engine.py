@@ -478,6 +478,7 @@ class Synth:
         f = np.ascontiguousarray(features, np.float32)
         assert f.size >= NB_FEATURES
         out = np.zeros(n, np.int16)
+        last_error()      # (a void entry point: its failure shows as a new error text, so drop any stale one first)
         self.L.lpcnet_synthesize(self.h, _p(f), _p(out), n)
         err = last_error()
         if err:

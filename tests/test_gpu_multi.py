@@ -91,4 +91,5 @@ def test_multi_errors(eng, model_blob):
     mb = eng.MultiBatch(model_blob, 3, device_mask=1)
     assert L.lpcnet_multi_set_seed(mb.h, 3, b"x", 1) == -1
     assert L.lpcnet_multi_shard(mb.h, 1, None, None, None) == -1
+    assert "no such shard" in eng.last_error()
     mb.close()
