@@ -443,8 +443,9 @@ def run_gpu(args):
         except Exception:
             l2_peak = None
         hbm_bytes_per_sample = 2.0 + (stride * 4 + (1152 + 48 + 16) * 4 * 2) / FRAME   # pcm + features + conditioning w/r
-        # DRAM bytes of one sample_kernel launch from the committed ncu --set full capture of this command
-        # (profiles/traffic.json, refreshed with every committed capture); null when the workload differs from it.
+        # DRAM bytes of one sample_kernel launch from the committed ncu list of this workload (profiles/traffic.json:
+        # caches left alone, because the conditioning rows are meant to be found in L2; the cold-cache figure of the
+        # `--set full` capture is in the same file); null when the workload differs from it.
         traffic = None
         tile_used = bt.tile
         n_sms = torch.cuda.get_device_properties(dev).multi_processor_count

@@ -102,6 +102,8 @@ struct LPCNetBatch {
   // compact copy of the streams one PLC sample segment moves (batch_sample_segment with a stream list)
   void *d_compact = nullptr; size_t d_compact_bytes = 0;
   void *d_compact2 = nullptr; size_t d_compact2_bytes = 0;   // ... of a segment on a side stream (beside one on `stream`)
+  size_t l2_window_max = 0;       // > 0: L2's persisting carve-out in bytes; a chunk's conditioning rows are kept in it
+  size_t l2_window_bytes = 0;     // the device's largest access-policy window
 };
 
 namespace {
@@ -180,22 +182,63 @@ int alloc_state(LPCNetBatch *b) {
 constexpr long long kChunkBytes = 1ll << 30;
 constexpr int kChunkFrames = 32;
 
-int chunk_frames(const LPCNetBatch *b, int n_frames) {
-  (void)b;
-  return n_frames < kChunkFrames ? n_frames : kChunkFrames;
+// Round 2: the chunk is sized for L2 instead.  The frame network writes a chunk's GRU-A conditioning (6 KB per
+// stream-frame) and the sample kernel reads it back; at 32 frames x 1024 streams that is 201 MB per buffer and every
+// byte made the round trip through HBM (ncu: 53 + 91 B per output sample of DRAM traffic for the two kernels against
+// 2.5 algorithmic).  With both buffer sets of the pipeline inside L2's persisting carve-out (cudaLimitPersistingL2-
+// CacheSize, an access-policy window on the writing and on the reading CUDA stream) the rows never leave the chip:
+// 5.1 + 2.4 B per sample measured at 4 frames x 1024 streams, for 0.5 % of throughput (8x the launches).
+// Only where it is (nearly) free: batches whose two buffer sets of >= 2 frames fit two thirds of the carve-out (2140 streams
+// on a B200) -- the latency regime, where the frame network of the next chunk runs on the SMs the sample kernel leaves
+// idle.  A saturated batch has no idle SM: its frame network runs between sample-kernel launches, and short chunks
+// cost 5.7 % there (measured at 4736 and 65 536 streams, one-wave groups of 2 frames), so those keep the 32-frame
+// chunks and their 140 B per sample of HBM traffic (50 GB/s, 0.8 % of the bandwidth).  Calls shorter than
+// kL2MinFrames (frame-by-frame streaming) keep one chunk per call.
+// LPCNET_B200_L2_PERSIST_MB sets the carve-out (default: the device's maximum, 79 MB of 126); 0 = the round-1 chunking.
+constexpr int kL2MinFrames = 8;
+constexpr long long kCondRowBytes = (long long)kRowsAP * 4;
+
+long long l2_budget(const LPCNetBatch *b) { return (long long)(b->l2_window_max / 3 * 2); }   // (measured: fuller evicts)
+bool l2_sized(const LPCNetBatch *b, int n_frames) {
+  return b->l2_window_max > 0 && n_frames >= kL2MinFrames && b->n_streams <= l2_budget(b) / (4 * kCondRowBytes);
+}
+
+int l2_window(const LPCNetBatch *b, cudaStream_t st, const void *base, size_t bytes) {
+  if (!b->l2_window_max) return 0;
+  cudaStreamAttrValue v{};
+  v.accessPolicyWindow.base_ptr = const_cast<void *>(base);
+  v.accessPolicyWindow.num_bytes = bytes < b->l2_window_bytes ? bytes : b->l2_window_bytes;
+  // both buffer sets share the carve-out; a window that is larger (short calls on large batches) persists in part
+  v.accessPolicyWindow.hitRatio = 2 * bytes <= b->l2_window_max ? 1.f : (float)b->l2_window_max / (float)(2 * bytes);
+  v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+  v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+  CK(cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v));
+  return 0;
 }
 
 // streams per group for a call of n_frames frames (n_streams = no grouping)
 int group_streams(const LPCNetBatch *b, int n_frames) {
-  const int Fc = chunk_frames(b, n_frames);
+  const int wave = b->n_sms * 16;
+  if (l2_sized(b, n_frames) && !getenv("LPCNET_B200_CHUNK_BYTES")) return b->n_streams;
+  const int Fc = n_frames < kChunkFrames ? n_frames : kChunkFrames;
   long long bytes = kChunkBytes;
   if (const char *e = getenv("LPCNET_B200_CHUNK_BYTES")) bytes = atoll(e) > 0 ? atoll(e) : bytes;   // tests: small groups
   const long long cap = bytes / ((long long)Fc * 6400);
   if (cap >= b->n_streams) return b->n_streams;
-  const int wave = b->n_sms * 16;
   long long g = cap / wave * wave;
   if (g < wave) g = wave;
   return (int)g;
+}
+
+// frames per chunk for groups of G streams
+int chunk_frames(const LPCNetBatch *b, int n_frames, int G) {
+  int fc = kChunkFrames;
+  if (l2_sized(b, n_frames) && !getenv("LPCNET_B200_CHUNK_BYTES")) {
+    const long long fit = l2_budget(b) / (2 * kCondRowBytes * G);
+    fc = (int)(fit < 1 ? 1 : fit > kChunkFrames ? kChunkFrames : fit);
+  }
+  if (const char *e = getenv("LPCNET_B200_CHUNK_FRAMES")) fc = atoi(e) > 0 ? atoi(e) : fc;
+  return n_frames < fc ? n_frames : fc;
 }
 
 // the stream state of streams [s0, ...) as a batch of its own: every array is [stream][field]
@@ -282,9 +325,9 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
   if (spf <= 0 || spf > kFrame) return fail("samples_per_frame must be 1..160");
   if (stride < kFeat) return fail("feature_stride must be >= 20");
   CK(cudaSetDevice(b->device));
-  const int Fc = chunk_frames(b, n_frames);
   // large batches: groups of streams, each walked in full chunks (see group_streams); trace / logit runs stay whole
   const int G = (d_trace || d_logits) ? b->n_streams : group_streams(b, n_frames);
+  const int Fc = chunk_frames(b, n_frames, G);
   const int n_groups = (b->n_streams + G - 1) / G;
   if (ensure_frame_buffers(b, Fc, false, G)) return -1;
   // no explicit tile: whole waves of 16-stream tiles, the remainder in 8-stream tiles when that is faster (0 = mixed)
@@ -317,6 +360,7 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
       const FrameBuffers &fbk = buf ? b->fb2 : b->fb;
       if (pipe) {
         if (item >= 2) CK(cudaStreamWaitEvent(b->fstream, b->ev_samples[buf], 0));   // the buffers are free again
+        if (l2_window(b, b->fstream, fbk.cond_a, (size_t)F * Gs * kRowsAP * 4)) return -1;
         if (run_frames(b, d_features, stride, f0, F, n_frames, fbk, b->fstream, s0, Gs)) return -1;
         CK(cudaEventRecord(b->ev_frames[buf], b->fstream));
         CK(cudaStreamWaitEvent(b->stream, b->ev_frames[buf], 0));
@@ -336,6 +380,7 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
       int nl = 0;
       cudaEvent_t e0 = nullptr, e1 = nullptr;
       if (b->profiling) { CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventRecord(e0, b->stream)); }
+      if (l2_window(b, b->stream, fbk.cond_a, (size_t)F * Gs * kRowsAP * 4)) return -1;
       CK(launch_sample_kernel(sa, tile, b->n_sms, b->stream, &nl));
       if (b->profiling) { CK(cudaEventRecord(e1, b->stream)); b->ev_sample.emplace_back(e0, e1); b->ev_sample_steps.push_back(F * spf); }
       if (pipe) CK(cudaEventRecord(b->ev_samples[buf], b->stream));
@@ -534,6 +579,21 @@ LPCNetBatch *lpcnet_batch_create(const unsigned char *blob, int len, int n_strea
   cudaDeviceProp prop;
   cudaGetDeviceProperties(&prop, device);
   b->n_sms = prop.multiProcessorCount;
+  {
+    // L2 carve-out for the conditioning rows (see group_streams): what the device allows, unless the caller says less
+    size_t want = (size_t)prop.persistingL2CacheMaxSize;
+    if (const char *e = getenv("LPCNET_B200_L2_PERSIST_MB")) want = (size_t)(atoi(e) > 0 ? atoi(e) : 0) << 20;
+    if (want > (size_t)prop.persistingL2CacheMaxSize) want = prop.persistingL2CacheMaxSize;
+    if (want && prop.accessPolicyMaxWindowSize > 0 && cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) {
+      b->l2_window_max = want;
+      b->l2_window_bytes = prop.accessPolicyMaxWindowSize;
+    } else {
+      cudaGetLastError();
+    }
+    if (getenv("LPCNET_B200_DEBUG"))
+      fprintf(stderr, "L2 %d MB, persisting max %d MB, window max %d MB, carve-out %zu MB\n", prop.l2CacheSize >> 20,
+              prop.persistingL2CacheMaxSize >> 20, prop.accessPolicyMaxWindowSize >> 20, b->l2_window_max >> 20);
+  }
   uint32_t rcp[2048];
   bool have;
   {
@@ -571,6 +631,12 @@ void lpcnet_batch_destroy(LPCNetBatch *b) {
   if (!b) return;
   cudaSetDevice(b->device);
   if (b->stream) cudaStreamSynchronize(b->stream);
+  if (b->l2_window_max) {                      // hand the conditioning rows' lines back to normal caching
+    cudaStreamAttrValue v{};                   // (num_bytes 0 disables the window; the stream may be the caller's)
+    if (b->stream) cudaStreamSetAttribute(b->stream, cudaStreamAttributeAccessPolicyWindow, &v);
+    cudaCtxResetPersistingL2Cache();
+    cudaGetLastError();
+  }
   free_model(b->model);
   if (b->fstream) {
     cudaStreamSynchronize(b->fstream);
@@ -765,7 +831,8 @@ int lpcnet_batch_frame_network(LPCNetBatch *b, const float *features, int stride
   if (grow(&b->d_feat, &b->d_feat_bytes, fbytes)) return -1;
   CK(cudaMemcpyAsync(b->d_feat, features, fbytes, cudaMemcpyHostToDevice, b->stream));
   long long cap = kChunkBytes / ((long long)b->n_streams * 6400);      // a test entry point: whole batch, smaller chunks
-  const int Fc = (int)(cap < 1 ? 1 : (cap < chunk_frames(b, n_frames) ? cap : chunk_frames(b, n_frames)));
+  const int Fc0 = n_frames < kChunkFrames ? n_frames : kChunkFrames;
+  const int Fc = (int)(cap < 1 ? 1 : (cap < Fc0 ? cap : Fc0));
   if (ensure_frame_buffers(b, Fc)) return -1;
   for (int f0 = 0; f0 < n_frames; f0 += Fc) {
     const int F = (n_frames - f0) < Fc ? (n_frames - f0) : Fc;
