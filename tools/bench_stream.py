@@ -61,9 +61,25 @@ def main():
     ap.add_argument("--calls", type=int, default=1000)
     ap.add_argument("--sweep", default="")
     ap.add_argument("--device", type=int, default=0)
+    ap.add_argument("--gpus", type=int, default=1, help="run the same stream count on N GPUs at once, one process each")
     a = ap.parse_args()
     if engine.device_count() == 0:
         raise SystemExit("no CUDA device (the engine has no CPU fallback)")
+    if a.gpus > 1:
+        # the box's real-time capacity: every GPU holds --streams live streams at the same time (processes are
+        # independent, as the streams are); the figure that counts is the worst GPU's p99
+        import subprocess
+        procs = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "--streams", str(a.streams), "--calls", str(a.calls),
+                                   "--device", str(k)], stdout=subprocess.PIPE, text=True) for k in range(a.gpus)]
+        per = [json.loads(p.communicate()[0].strip().splitlines()[-1]) for p in procs]
+        print(json.dumps({"workload": per[0]["workload"], "n_gpus": a.gpus, "streams_per_gpu": a.streams,
+                          "streams_total": a.streams * a.gpus, "calls": a.calls,
+                          "ms_per_call_p50_worst_gpu": max(x["ms_per_call_p50"] for x in per),
+                          "ms_per_call_p99_worst_gpu": max(x["ms_per_call_p99"] for x in per),
+                          "ms_per_call_max_worst_gpu": max(x["ms_per_call_max"] for x in per),
+                          "real_time": all(x["real_time"] for x in per),
+                          "per_gpu_p99": [x["ms_per_call_p99"] for x in per]}), flush=True)
+        return
     for B in ([int(x) for x in a.sweep.split(",")] if a.sweep else [a.streams]):
         print(json.dumps(run(B, a.calls, a.device)), flush=True)
 
