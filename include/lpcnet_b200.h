@@ -347,6 +347,11 @@ LPCNET_B200_EXPORT void lpcnet_b200_default_rcp_table(uint32_t *table2048);
 /* FEATURES_DELAY / LPC_GAMMA used by the drop-in lpcnet_load_model (compile-time constants of
  * the reference's generated nnet_data.h; default 2 and 1.0). */
 LPCNET_B200_EXPORT void lpcnet_b200_set_model_constants(int features_delay, float lpc_gamma);
+/* The reference's -DEND2END build (src/lpcnet.c:57-78, 108: the frame's LPC are rc2lpc of the first 16 outputs of
+ * feature_dense2 instead of lpc_from_cepstrum through the FEATURES_DELAY line) as a run-time switch: process-wide
+ * default for states / batches created later (0), and per batch. */
+LPCNET_B200_EXPORT void lpcnet_b200_set_end2end(int on);
+LPCNET_B200_EXPORT int lpcnet_batch_set_end2end(LPCNetBatch *b, int on);
 
 /* Last error message of the calling thread ("" if none); sticky until read. */
 LPCNET_B200_EXPORT const char *lpcnet_b200_last_error(void);

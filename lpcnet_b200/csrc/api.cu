@@ -33,6 +33,7 @@ bool g_have_rcp = false;
 uint32_t g_rcp[2048];
 int g_default_delay = 2;
 float g_default_gamma = 1.0f;
+int g_default_end2end = 0;
 
 int fail(const std::string &msg) { return lpcb::set_last_error(msg); }
 int fail_cuda(const char *what, cudaError_t e) { return fail(std::string(what) + ": " + cudaGetErrorString(e)); }
@@ -559,6 +560,19 @@ void lpcnet_b200_set_model_constants(int features_delay, float lpc_gamma) {
   g_default_gamma = lpc_gamma;
 }
 
+void lpcnet_b200_set_end2end(int on) {
+  std::lock_guard<std::mutex> lk(g_cfg_mu);
+  g_default_end2end = on ? 1 : 0;
+}
+
+int lpcnet_batch_set_end2end(LPCNetBatch *b, int on) {
+  if (!b) return fail("null batch");
+  CK(cudaSetDevice(b->device));
+  CK(cudaStreamSynchronize(b->stream));
+  b->model.d.end2end = on ? 1 : 0;
+  return 0;
+}
+
 LPCNetBatch *lpcnet_batch_create(const unsigned char *blob, int len, int n_streams, int device, int features_delay,
                                  float lpc_gamma) {
   if (n_streams <= 0) { fail("n_streams must be positive"); return nullptr; }
@@ -608,6 +622,7 @@ LPCNetBatch *lpcnet_batch_create(const unsigned char *blob, int len, int n_strea
     return nullptr;
   }
   // largest streams-per-CTA tile whose resident weights + per-stream buffers fit this GPU's shared memory
+  { std::lock_guard<std::mutex> lk(g_cfg_mu); b->model.d.end2end = g_default_end2end; }
   b->max_tile = 0;
   for (int t : {32, 16, 8})
     if (!b->max_tile && sample_kernel_smem(t, b->model.d) <= (size_t)prop.sharedMemPerBlockOptin) b->max_tile = t;

@@ -157,6 +157,7 @@ struct DevModel {
   const float *codebooks;                   // cb1|cb2|cb3|diff4 or NULL
   int features_delay;
   float lpc_gamma;
+  int end2end;               // the reference's -DEND2END build: LPC = rc2lpc(condition[0..16)) (src/lpcnet.c:57-78, 108)
   DevPlc plc;                               // valid when Model::has_plc
   DevDred dred;                             // valid when Model::has_dred
 };

@@ -171,6 +171,24 @@ __global__ void __launch_bounds__(kFT) cond_kernel(FrameArgs A) {
   __syncthreads();
   dense_rows<R, true>(A.m.dense2_w, A.m.dense2_b, kC, kC, &zt[0][0], &yt[0][0], 0, true, rcp, tid, kFT, nullptr);
   __syncthreads();
+  // END2END models (src/lpcnet.c:57-78, 108): the frame's LPC are the step-up recursion over the first 16 outputs of
+  // dense2, taken as reflection coefficients -- no cepstrum, no delay line.  One thread per row; separate multiply and
+  // add as in the reference build.
+  if (A.m.end2end && tid < R && blockIdx.x * R + tid < total && !(A.stream_mask && !A.stream_mask[row_s[tid]])) {
+    float cur[16], nxt[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) cur[i] = yt[i][tid];
+#pragma unroll
+    for (int i = 1; i < 16; i++) {
+#pragma unroll
+      for (int j = 0; j < i; j++) nxt[j] = cur[j] + cur[i] * cur[i - j - 1];
+#pragma unroll
+      for (int j = 0; j < i; j++) cur[j] = nxt[j];
+    }
+    float *dst = A.fb.lpc + ((size_t)row_f[tid] * B + row_s[tid]) * 16;
+#pragma unroll
+    for (int i = 0; i < 16; i++) dst[i] = cur[i];
+  }
   // linear heads, written straight to [F][B][*]; two output columns per thread share the activation loads
   constexpr int NH = kRowsA + kRowsB;
   for (int i0 = tid; i0 < NH; i0 += 2 * kFT) {
@@ -243,7 +261,7 @@ __global__ void lpc_kernel(FrameArgs A) {
 // the in-place shift never reads an overwritten row), all 32 lanes copy the history rows.  (One thread per stream
 // took 94 us per launch whatever the batch: a serial walk over 440 floats of L2 round trips.)
 __global__ void frame_finalize_kernel(FrameArgs A) {
-  const int B = A.n_streams, F = A.n_frames, D = A.m.features_delay;
+  const int B = A.n_streams, F = A.n_frames, D = A.m.end2end ? 0 : A.m.features_delay;   // (END2END has no delay line)
   const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (k >= n_active(A)) return;
   const int s = stream_of(A, k);
@@ -353,11 +371,13 @@ cudaError_t launch_frame_network(const FrameArgs &a, cudaStream_t s, int *n_laun
   frame_inputs_kernel<<<B * (F + 2), 128, 0, s>>>(a);
   conv1_kernel<<<(rows + kRowsPerBlock - 1) / kRowsPerBlock, kFT, 0, s>>>(a);
   cond_kernel<<<(rows + kRowsPerBlock - 1) / kRowsPerBlock, kFT, 0, s>>>(a);
-  cudaError_t e = fft_opt_in(lpc_kernel);
-  if (e != cudaSuccess) return e;
-  lpc_kernel<<<(rows + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, s>>>(a);
+  if (!a.m.end2end) {                     // (END2END: cond_kernel wrote the LPC already)
+    cudaError_t e = fft_opt_in(lpc_kernel);
+    if (e != cudaSuccess) return e;
+    lpc_kernel<<<(rows + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, s>>>(a);
+  }
   frame_finalize_kernel<<<(B * 32 + 127) / 128, 128, 0, s>>>(a);
-  if (n_launches) *n_launches += 5;
+  if (n_launches) *n_launches += a.m.end2end ? 4 : 5;
   return cudaGetLastError();
 }
 

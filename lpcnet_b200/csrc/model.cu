@@ -675,6 +675,7 @@ bool load_model(Model &m, const unsigned char *blob, int len, int features_delay
   }
   d.features_delay = features_delay;
   d.lpc_gamma = lpc_gamma;
+  d.end2end = 0;                       // lpcnet_batch_set_end2end / lpcnet_b200_set_end2end (api.cu)
 
   cudaError_t e = cudaMalloc(&m.dev_blob, B.buf.size());
   if (e != cudaSuccess) { err = std::string("cudaMalloc(model): ") + cudaGetErrorString(e); return false; }

@@ -43,6 +43,7 @@ EXPORTED_SYMBOLS = [
     "lpcnet_batch_set_state", "lpcnet_batch_sync", "lpcnet_batch_nblocks", "lpcnet_batch_launch_count",
     "lpcnet_batch_set_profiling", "lpcnet_batch_read_profile", "lpcnet_batch_profile_launches", "lpcnet_b200_measure_l2_gather",
     "lpcnet_b200_set_rcp_table", "lpcnet_b200_default_rcp_table", "lpcnet_b200_set_model_constants",
+    "lpcnet_b200_set_end2end", "lpcnet_batch_set_end2end",
     "lpcnet_b200_last_error", "lpcnet_b200_device_count", "lpcnet_b200_lpc_from_cepstrum_noalloc",
     "lpcnet_batch_create_multi", "lpcnet_multi_destroy", "lpcnet_multi_n_streams", "lpcnet_multi_n_devices",
     "lpcnet_multi_shard", "lpcnet_multi_set_seed", "lpcnet_multi_reset", "lpcnet_multi_set_codebooks",
@@ -126,6 +127,8 @@ def load_library() -> C.CDLL:
     L.lpcnet_b200_set_rcp_table.argtypes = [vp]
     L.lpcnet_b200_default_rcp_table.argtypes = [vp]
     L.lpcnet_b200_set_model_constants.argtypes = [ci, cf]
+    L.lpcnet_b200_set_end2end.argtypes = [ci]
+    L.lpcnet_batch_set_end2end.argtypes = [vp, ci]
     L.lpcnet_create.restype = vp
     L.lpcnet_destroy.argtypes = [vp]
     L.lpcnet_reset.argtypes = [vp]
@@ -267,6 +270,10 @@ class Batch:
 
     def set_seed(self, stream: int, seed: bytes):
         _check(self.L.lpcnet_batch_set_seed(self.h, stream, seed, len(seed)), "lpcnet_batch_set_seed")
+
+    def set_end2end(self, on: bool = True):
+        """the reference's -DEND2END build: LPC from rc2lpc(condition[0..16)) (src/lpcnet.c:57-78, 108)"""
+        _check(self.L.lpcnet_batch_set_end2end(self.h, 1 if on else 0), "lpcnet_batch_set_end2end")
 
     def set_tile(self, streams_per_cta: int):
         _check(self.L.lpcnet_batch_set_tile(self.h, streams_per_cta), "lpcnet_batch_set_tile")

@@ -63,6 +63,8 @@ typedef struct {
 OrcModel *orc_model_load(const unsigned char *blob, int len, int features_delay, float lpc_gamma,
                          const uint32_t *rcp_table);
 void orc_model_free(OrcModel *m);
+/* the reference's -DEND2END build: LPC = rc2lpc(condition[0..16)) (lpcnet.c:57-78, 108); default off */
+void orc_model_set_end2end(OrcModel *m, int on);
 int orc_model_nblocks_a(const OrcModel *m);
 int orc_model_nblocks_b(const OrcModel *m);
 

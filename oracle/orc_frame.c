@@ -250,6 +250,21 @@ void orc_lpc_from_cepstrum(float *lpc, const float *cepstrum) {
   orc_levinson(lpc, ac, 16);
 }
 
+/* rc2lpc (lpcnet.c:57-78, the END2END build): step-up recursion from reflection coefficients; the pass for i = 0 of
+ * the reference's loop moves nothing */
+static void orc_rc2lpc(float *lpc, const float *rc) {
+  float cur[16], nxt[16];
+  int i, j;
+  memcpy(cur, rc, sizeof(cur));
+  for (i = 1; i < 16; i++) {
+    for (j = 0; j < i; j++) nxt[j] = cur[j] + cur[i] * cur[i - j - 1];
+    memcpy(cur, nxt, i * sizeof(float));
+  }
+  memcpy(lpc, cur, sizeof(cur));
+}
+
+void orc_model_set_end2end(OrcModel *m, int on) { m->end2end = on ? 1 : 0; }
+
 /* run_frame_network (lpcnet.c:82-120) */
 void orc_frame_network(const OrcModel *m, OrcState *s, const float *features, float *ga, float *gb, float *lpc) {
   float in[84], conv1_out[128], conv2_out[128], dense1_out[128], condition[128];
@@ -266,7 +281,9 @@ void orc_frame_network(const OrcModel *m, OrcState *s, const float *features, fl
   orc_dense(&m->dense2, condition, dense1_out);
   orc_dense(&m->a_feat, ga, condition);
   orc_dense(&m->b_feat, gb, condition);
-  if (m->features_delay > 0) {
+  if (m->end2end) {                       /* lpcnet.c:107-108 */
+    orc_rc2lpc(lpc, condition);
+  } else if (m->features_delay > 0) {
     int D = m->features_delay;
     memcpy(lpc, s->old_lpc[D - 1], 16 * sizeof(float));
     memmove(s->old_lpc[1], s->old_lpc[0], (D - 1) * 16 * sizeof(float));

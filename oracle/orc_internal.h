@@ -20,6 +20,7 @@ enum { ORC_LINEAR = 0, ORC_SIGMOID = 1, ORC_TANH = 2 };
 struct OrcModel {
   unsigned char *blob; int len;
   int features_delay; float lpc_gamma;
+  int end2end;             /* the reference's -DEND2END build (lpcnet.c:57-78, 108) */
   OrcEmbed e_sig, e_pred, e_exc, e_pitch;
   OrcDense a_feat, b_feat, dense1, dense2;
   OrcConv conv1, conv2;

@@ -26,6 +26,7 @@ class OrcLib:
         L.orc_model_load.restype = C.c_void_p
         L.orc_model_load.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_float, C.c_void_p]
         L.orc_model_free.argtypes = [C.c_void_p]
+        L.orc_model_set_end2end.argtypes = [C.c_void_p, C.c_int]
         L.orc_model_nblocks_a.argtypes = [C.c_void_p]
         L.orc_model_nblocks_b.argtypes = [C.c_void_p]
         L.orc_state_new.restype = C.c_void_p
@@ -111,7 +112,8 @@ class OrcLib:
 
 
 class OrcModel:
-    def __init__(self, lib: OrcLib, blob: bytes, features_delay: int = 2, lpc_gamma: float = 1.0, rcp_table=None):
+    def __init__(self, lib: OrcLib, blob: bytes, features_delay: int = 2, lpc_gamma: float = 1.0, rcp_table=None,
+                 end2end: bool = False):
         self.L = lib
         tab = np.ascontiguousarray(rcp_table, np.uint32) if rcp_table is not None else None
         self.h = lib.lib.orc_model_load(blob, len(blob), features_delay, C.c_float(lpc_gamma),
@@ -119,6 +121,8 @@ class OrcModel:
         if not self.h:
             raise RuntimeError("oracle rejected the blob")
         self.features_delay = features_delay
+        if end2end:
+            lib.lib.orc_model_set_end2end(self.h, 1)
 
     def __del__(self):
         if getattr(self, "h", None):

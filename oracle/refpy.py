@@ -32,7 +32,8 @@ def available(delay: int = 2) -> bool:
 
 
 class RefLib:
-    def __init__(self, delay: int = 2):
+    def __init__(self, delay=2):
+        # delay: 2 or 0 (FEATURES_DELAY of the build), or "2_e2e": FEATURES_DELAY 2 with -DEND2END
         self.lib = C.CDLL(os.path.join(HERE, "_ref", f"libref_d{delay}.so"))
         L = self.lib
         L.ref_new.restype = C.c_void_p
@@ -58,7 +59,7 @@ class RefLib:
         L.ref_rcp_ss.argtypes = [C.c_float]
         L.ref_kiss99_rand.restype = C.c_uint32
         assert L.ref_snapshot_size() == SNAP_DTYPE.itemsize, (L.ref_snapshot_size(), SNAP_DTYPE.itemsize)
-        assert L.ref_features_delay() == delay
+        assert L.ref_features_delay() == int(str(delay).split("_")[0])
 
     # -- kernel-level helpers --
     def vec(self, name, x):

@@ -385,10 +385,32 @@ def demo(R):
     np.savez_compressed(os.path.join(OUT, "demo.npz"), **d)
 
 
+def end2end(_R):
+    """The reference built -DEND2END (oracle/_ref/libref_d2_e2e.so; src/lpcnet.c:57-78, 108): the frame network's LPC of
+    six frames, and the PCM and per-step trace of three streams over 10 frames."""
+    R = refpy.RefLib("2_e2e")
+    b = blob.write_blob(blob.random_model())
+    d = {"blob_sha256": np.frombuffer(hashlib.sha256(b).digest(), np.uint8)}
+    streams = [0, 5, 9]
+    d["streams"] = np.array(streams)
+    for s in streams:
+        f = blob.synthetic_features(10, s)
+        rs = refpy.RefStream(R, b, blob.stream_seed(s))
+        pcm, tr, _ = rs.run(f, trace=True, logits=False)
+        d[f"pcm_{s}"], d[f"trace_{s}"] = pcm, tr
+    rs = refpy.RefStream(R, b)
+    f = blob.synthetic_features(6, 0)
+    ga = np.zeros((6, 1152), np.float32); gb = np.zeros((6, 48), np.float32); lp = np.zeros((6, 16), np.float32)
+    for k in range(6):
+        R.lib.ref_frame_network(refpy.C.c_void_p(rs.h), refpy._p(np.ascontiguousarray(f[k])), refpy._p(ga[k]), refpy._p(gb[k]), refpy._p(lp[k]))
+    d["fn_lpc"], d["fn_gb"] = lp, gb
+    np.savez_compressed(os.path.join(OUT, "end2end.npz"), **d)
+
+
 if __name__ == "__main__":
     R = refpy.RefLib(2)
-    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc", "encode", "plc_causal", "dred", "plc_edges", "bench", "sat", "demo"]
+    which = sys.argv[1:] or ["prims", "synth", "decode", "analysis", "plc", "encode", "plc_causal", "dred", "plc_edges", "bench", "sat", "demo", "end2end"]
     for name in which:
-        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc, "encode": encode, "plc_causal": plc_causal, "dred": dred, "plc_edges": plc_edges, "bench": bench_hashes, "sat": sat, "demo": demo}[name](R)
+        {"prims": prims, "synth": synth, "decode": decode, "analysis": analysis, "plc": plc, "encode": encode, "plc_causal": plc_causal, "dred": dred, "plc_edges": plc_edges, "bench": bench_hashes, "sat": sat, "demo": demo, "end2end": end2end}[name](R)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
