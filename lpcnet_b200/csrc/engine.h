@@ -238,6 +238,10 @@ struct SampleArgs {
   void *trace;               // nullable LPCNetB200Trace [B][total_frames*spf]
   float *logits;             // nullable [B][total_frames*spf][256]
   unsigned long long *phase_clk;   // development builds (-DLPCB_PHASE_CLOCKS) only: per-phase cycle sums of CTA 0
+  // 1.0f, 1.0f -- as a kernel argument, i.e. a value ptxas cannot see: fma.rn.f32x2(p, one, c) is the exactly rounded
+  // packed sum p + c, and unlike add.rn.f32x2 it is not contracted with the packed multiply that produced p
+  // (ptxas fuses mul.rn.f32x2 -> add.rn.f32x2 into FFMA2, which would drop the product's rounding)
+  float2 one2 = {1.f, 1.f};
 };
 
 // tile_streams 8 / 16 / 32, or 0: 16-stream tiles in whole waves of one tile per SM, and the remainder in 8-stream

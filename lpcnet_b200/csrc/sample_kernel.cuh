@@ -625,6 +625,14 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
         // qa0 = [ug w: 2t 2t+1 | ug w+16: 2t 2t+1], qa2 = [ug w+32: 2t 2t+1 | 0 0], per stream row
         // (with two groups a warp owns two such K slices: unit groups w + 8*set + 16*slot)
         uint32_t qa0[US][MT][NV / 2], qa2[US][MT][NV / 2];
+        // p + c for a p that comes out of a packed multiply.  ptxas contracts mul.rn.f32x2 -> add.rn.f32x2 into FFMA2
+        // (it never contracts the scalar .rn forms), which would drop the product's rounding; an fma with a one it
+        // cannot see (SampleArgs::one2, a kernel argument) is the exactly rounded packed sum and stays apart.  Worth
+        // 0.6 % at 16 and 1.6 % at 32 streams per CTA; at 8 the two extra registers cost 2 %, so the sums stay scalar.
+        auto padd = [&](float2 p, float2 c) {
+          if (NS > 8) return f2_fma(p, A.one2, c);
+          return make_float2(p.x + c.x, p.y + c.y);
+        };
 #pragma unroll
         for (int u = 0; u < UW; u++) {
           const int ug = warp + u * WG;
@@ -674,11 +682,10 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
 #pragma unroll
               for (int h = 0; h < NV / 2; h++) {
                 const float2 gx = f2_add(f2_add(f2_add(cv[gate][h], e1[gate][h]), e2[gate][h]), e3[gate][h]);
-                // bias + diag*state: a multiply feeding an add stays scalar -- ptxas contracts
-                // mul.rn.f32x2 + add.rn.f32x2 into FFMA2 (it never contracts the scalar .rn forms)
+                // bias + diag*state: a packed product feeding a sum goes through padd (above)
                 const float2 a2 = a_reg[u][mt][h];
-                const float2 da = f2_mul(dg, a2);                         // packed product, scalar sums (see above)
-                float2 tx = make_float2(sub.x + da.x, sub.y + da.y);
+                const float2 da = f2_mul(dg, a2);
+                float2 tx = padd(da, sub);                                // = sub + da
                 if (gate < 2) tx = f2_add(tx, gx);                        // (+ input for z, r)
                 else gh[h] = gx;
                 const float2 sd = f2_mul(tx, f2_set(LPCB_SCALE));
@@ -702,11 +709,11 @@ __global__ void __launch_bounds__(kThreads, 1) sample_kernel(const SampleArgs A)
               const float2 r = sigmoid2_ref(f2_mul(sum_f(1), k1), s_rcp);
               float2 hh = f2_mul(sum_f(2), k1);
               const float2 hr = f2_mul(hh, r);
-              hh = tanh2_ref(make_float2(hr.x + gh[h].x, hr.y + gh[h].y), s_rcp);   // packed product, scalar sums
+              hh = tanh2_ref(padd(hr, gh[h]), s_rcp);                       // = hr + gh
               const float2 a_old = a_reg[u][mt][h];
-              // z*state + (1-z)*h, scalar for the same reason
+              // z*state + (1-z)*h, summed the same way
               const float2 za = f2_mul(z, a_old), zh = f2_mul(f2_add(f2_set(1.f), make_float2(-z.x, -z.y)), hh);
-              const float2 a_nw = make_float2(za.x + zh.x, za.y + zh.y);
+              const float2 a_nw = padd(zh, za);                             // = za + zh
               unsigned short *dst = reinterpret_cast<unsigned short *>(xa_new) + (((sA + 8 * h) * kXaStride * 4 + ug * 8 + 2 * t) >> 1);
               uint32_t pv;
               if (ixw[mt][h] >> 24) {
