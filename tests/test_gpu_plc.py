@@ -144,6 +144,40 @@ def test_full_size_config4_compaction_is_invisible(eng, plc_blob, plc_model):
         assert first_diff(got[s], want) is None, (s, first_diff(got[s], want))
 
 
+def test_side_stream_is_invisible_and_deterministic(eng, plc_blob, plc_model):
+    """The first-good-frame chain runs on a side CUDA stream beside the main class (plc.cu).  Streams of the two
+    chains share tiles, scratch rows and the analysis state arrays, so a missing event or an unmasked write would show
+    as a difference from the sequential order (LPCNET_B200_PLC_ONE_STREAM=1) or between repeated runs.  Loss patterns
+    with many recoveries per frame (bursts of 1-2 frames at a 35 % loss rate) keep both chains busy in every frame;
+    every stream is compared between the modes, sampled ones with the oracle."""
+    B, F, opt = 2500, 30, 5
+    base = [blob.synthetic_pcm(F, 300 + s) for s in range(32)]
+    pcm = np.stack([base[s % 32] for s in range(B)])
+    lost = np.stack([blob.synthetic_loss_pattern(F, 900 + s, 0.45, 0.7) for s in range(B)])
+    assert 0.2 < lost.mean() < 0.6
+
+    def run():
+        pb = eng.PLCBatch(plc_blob, B, opt)
+        for s in range(0, B, 5):
+            pb.set_seed(s, blob.stream_seed(s))
+        out = pb.process(pcm, lost)
+        pb.close()
+        return out
+
+    runs = [run() for _ in range(3)]
+    os.environ["LPCNET_B200_PLC_ONE_STREAM"] = "1"
+    try:
+        seq = run()
+    finally:
+        del os.environ["LPCNET_B200_PLC_ONE_STREAM"]
+    for k, r in enumerate(runs):
+        assert first_diff(r, seq) is None, (k, first_diff(r, seq))
+    for s in (0, 5, 1249, 2499):
+        seed = blob.stream_seed(s) if s % 5 == 0 else b"LPCNet"
+        want = orcpy.OrcPLC(plc_model, opt, seed).run(pcm[s], lost[s])
+        assert first_diff(runs[0][s], want) is None, (s, first_diff(runs[0][s], want))
+
+
 def run_with_fec(pb, pcm, lost, fec):
     """frame by frame, handing each stream's FEC vectors to the queue before the frame they precede"""
     B, F = lost.shape
