@@ -54,6 +54,8 @@ struct AnalysisArgs {
   float *S;                   // [B][1 + 160F]    previous residual | LPC residual
   float *fft_scratch;         // [320][2][B*F]
   const uint8_t *stream_mask; // nullable [B]: streams with 0 keep their state and their feature rows
+  const int *rows;            // nullable: device list of the n_rows streams to process -- the grids then cover the list
+  int n_rows;                 //   (the PLC's small classes: a masked grid over the whole batch costs a wave per kernel)
   // superframe modes (lpcnet_encode / lpcnet_compute_features, lpcnet_enc.c:882-911): frames come in packets of four
   int quantize;               // 1: process_superframe(encode = quantize = 1), 0: (0, 0)
   int *ids;                   // [B][total_frames/4][kIds] bit-field values of the packet (quantize mode)
@@ -72,13 +74,17 @@ __device__ __forceinline__ float pcm_at(const AnalysisArgs &A, int s, int n) {
   return A.pcm16 ? (float)A.pcm16[i] : A.pcmf[i];
 }
 
+__device__ __forceinline__ int an_count(const AnalysisArgs &A) { return A.rows ? A.n_rows : A.n_streams; }
+__device__ __forceinline__ int an_stream(const AnalysisArgs &A, int k) { return A.rows ? __ldg(A.rows + k) : k; }
+
 // preemphasis (lpcnet_enc.c:872-880): y[n] = x[n] + mem, mem = -0.85f * x[n]
 __global__ void preemph_kernel(AnalysisArgs A) {
   const int L = kOverlap + A.n_frames * kFrame;
-  const size_t total = (size_t)A.n_streams * L;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int s = (int)(i / L), k = (int)(i % L);
+  const size_t total = (size_t)an_count(A) * L;
+  for (size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < total; i0 += (size_t)gridDim.x * blockDim.x) {
+    const int s = an_stream(A, (int)(i0 / L)), k = (int)(i0 % L);
     if (A.stream_mask && !A.stream_mask[s]) continue;   // (its rows may belong to a concurrent call on another CUDA stream)
+    const size_t i = (size_t)s * L + k;
     float v;
     if (k < kOverlap) {
       v = A.st.p_hist[(size_t)s * kOverlap + k];
@@ -96,8 +102,8 @@ __global__ void preemph_kernel(AnalysisArgs A) {
 __global__ void spectral_kernel(AnalysisArgs A) {
   const int B = A.n_streams, F = A.n_frames;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= B * F) return;
-  const int s = idx / F, f = idx % F;
+  if (idx >= an_count(A) * F) return;
+  const int s = an_stream(A, idx / F), f = idx % F;
   if (A.stream_mask && !A.stream_mask[s]) return;
   const Scratch S = block_scratch();
   const float *x = A.P + (size_t)s * (kOverlap + F * kFrame) + (size_t)f * kFrame;   // [analysis_mem | frame]
@@ -154,9 +160,9 @@ __global__ void spectral_kernel(AnalysisArgs A) {
 // S[s][1 + n] = a[n] + sum_j lpc[j] * a[n-1-j], a[n] = P[80 + n]; S[s][0] = the previous call's last value.
 __global__ void residual_kernel(AnalysisArgs A) {
   const int F = A.n_frames, L = F * kFrame;
-  const size_t total = (size_t)A.n_streams * L;
+  const size_t total = (size_t)an_count(A) * L;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int s = (int)(i / L), n = (int)(i % L), f = n / kFrame;
+    const int s = an_stream(A, (int)(i / L)), n = (int)(i % L), f = n / kFrame;
     if (A.stream_mask && !A.stream_mask[s]) continue;
     const float *a = A.P + (size_t)s * (kOverlap + L) + kTOff + n;
     const float *lpc = A.features + ((size_t)s * A.total_frames + A.frame0 + f) * kNF + kBands + 2;
@@ -186,7 +192,7 @@ template <bool SUPER>
 __global__ void __launch_bounds__(kPT) pitch_kernel(AnalysisArgs A) {
   constexpr int NR = SUPER ? 8 : 2;         // correlation rows (half-frames) per Viterbi pass
   extern __shared__ float sm[];
-  const int s = blockIdx.x, t = threadIdx.x, F = A.n_frames, L = F * kFrame;
+  const int s = an_stream(A, blockIdx.x), t = threadIdx.x, F = A.n_frames, L = F * kFrame;
   if (A.stream_mask && !A.stream_mask[s]) return;
   const int GR = F < kGroup ? F : kGroup;   // frames per group
   const bool lagthr = t < kPMax;
@@ -488,8 +494,10 @@ int feature_chunk_frames(int B, int n_frames, bool super) {
 // mode 0: single-frame analysis; 1: superframes (n_frames a multiple of 4), unquantised (lpcnet_compute_features);
 // 2: superframes with the pitch / correlation fields quantised into b->d_ids (lpcnet_encode)
 int analysis_device(LPCNetFeatureBatch *b, const short *d16, const float *df, int n_frames, float *d_features,
-                    const uint8_t *d_mask = nullptr, int mode = 0) {
+                    const uint8_t *d_mask = nullptr, int mode = 0, const int *d_rows = nullptr, int n_rows = 0) {
   const int B = b->n_streams;
+  const int NA = d_rows ? n_rows : B;            // streams the grids cover
+  if (NA <= 0) return 0;
   CKA(cudaSetDevice(b->device));
   const int Fc = feature_chunk_frames(B, n_frames, mode != 0);
   const size_t nP = (size_t)B * (kOverlap + Fc * kFrame), nS = (size_t)B * (1 + Fc * kFrame);
@@ -500,19 +508,20 @@ int analysis_device(LPCNetFeatureBatch *b, const short *d16, const float *df, in
     AnalysisArgs A{};
     A.st = b->st; A.tab = b->tab; A.half_window = b->half_window;
     A.n_streams = B; A.n_frames = F; A.frame0 = f0; A.total_frames = n_frames;
-    A.pcm16 = d16; A.pcmf = df; A.features = d_features; A.stream_mask = d_mask;
+    A.pcm16 = d16; A.pcmf = df; A.features = d_features; A.stream_mask = d_rows ? nullptr : d_mask;
+    A.rows = d_rows; A.n_rows = n_rows;
     A.quantize = mode == 2; A.ids = static_cast<int *>(b->d_ids); A.pitch_pow = b->pitch_pow;
     A.P = static_cast<float *>(b->work);
     A.S = A.P + (((size_t)B * (kOverlap + F * kFrame) + 63) & ~size_t(63));
     A.fft_scratch = A.S + (((size_t)B * (1 + F * kFrame) + 63) & ~size_t(63));
-    const size_t np = (size_t)B * (kOverlap + F * kFrame);
+    const size_t np = (size_t)NA * (kOverlap + F * kFrame);
     preemph_kernel<<<(unsigned)((np + 255) / 256 > 65535 * 16 ? 65535 * 16 : (np + 255) / 256), 256, 0, b->stream>>>(A);
     if (fft_opt_in(spectral_kernel) != cudaSuccess) return set_last_error("spectral_kernel: shared-memory opt-in failed");
-    spectral_kernel<<<(B * F + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, b->stream>>>(A);
-    const size_t nr = (size_t)B * F * kFrame;
+    spectral_kernel<<<(NA * F + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, b->stream>>>(A);
+    const size_t nr = (size_t)NA * F * kFrame;
     residual_kernel<<<(unsigned)((nr + 255) / 256 > 65535 * 16 ? 65535 * 16 : (nr + 255) / 256), 256, 0, b->stream>>>(A);
-    if (mode) pitch_kernel<true><<<B, kPT, pitch_smem(F, 8), b->stream>>>(A);
-    else pitch_kernel<false><<<B, kPT, pitch_smem(F, 2), b->stream>>>(A);    // (> 48 KB: opted in at create)
+    if (mode) pitch_kernel<true><<<NA, kPT, pitch_smem(F, 8), b->stream>>>(A);
+    else pitch_kernel<false><<<NA, kPT, pitch_smem(F, 2), b->stream>>>(A);    // (> 48 KB: opted in at create)
     b->launches += 4;
     CKA(cudaGetLastError());
   }
@@ -590,10 +599,10 @@ std::vector<float> g_codebooks;     // process-wide default (the reference links
 }  // namespace
 
 int lpcb::feature_batch_frame_masked(LPCNetFeatureBatch *b, const short *d_pcm16, const uint8_t *d_mask, float *d_features,
-                                     cudaStream_t stream) {
+                                     cudaStream_t stream, const int *d_rows, int n_rows) {
   cudaStream_t keep = b->stream;
   b->stream = stream;
-  const int r = analysis_device(b, d_pcm16, nullptr, 1, d_features, d_mask);
+  const int r = analysis_device(b, d_pcm16, nullptr, 1, d_features, d_mask, 0, d_rows, n_rows);
   b->stream = keep;
   return r;
 }

@@ -103,6 +103,7 @@ struct LPCNetBatch {
   // compact copy of the streams one PLC sample segment moves (batch_sample_segment with a stream list)
   void *d_compact = nullptr; size_t d_compact_bytes = 0;
   void *d_compact2 = nullptr; size_t d_compact2_bytes = 0;   // ... of a segment on a side stream (beside one on `stream`)
+  std::vector<std::pair<cudaStream_t, FrameFork>> forks;   // per CUDA stream that launches frame networks (fork_for)
   size_t l2_window_max = 0;       // > 0: L2's persisting carve-out in bytes; a chunk's conditioning rows are kept in it
   size_t l2_window_bytes = 0;     // the device's largest access-policy window
 };
@@ -286,6 +287,23 @@ int auto_tile(const LPCNetBatch *b) {
   return t < b->max_tile ? t : b->max_tile;
 }
 
+// the auxiliary stream + events of the frame networks launched on `st` (engine.h FrameFork); nullptr = no fork
+const FrameFork *fork_for(LPCNetBatch *b, cudaStream_t st) {
+  if (getenv("LPCNET_B200_NO_FORK")) return nullptr;
+  for (auto &f : b->forks) if (f.first == st) return &f.second;
+  FrameFork f;
+  int lo = 0, hi = 0;
+  if (cudaDeviceGetStreamPriorityRange(&lo, &hi) != cudaSuccess ||
+      cudaStreamCreateWithPriority(&f.aux, cudaStreamNonBlocking, hi) != cudaSuccess ||
+      cudaEventCreateWithFlags(&f.begin, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&f.done, cudaEventDisableTiming) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  b->forks.emplace_back(st, f);
+  return &b->forks.back().second;
+}
+
 // frame network for frames [f0, f0+F) of the call, streams [s0, s0+G) of the batch, on stream st; results left in fb
 // (laid out [F][G][...]).  d_features points at the whole batch's rows.
 int run_frames(LPCNetBatch *b, const float *d_features, int stride, int f0, int F, int total_frames,
@@ -297,7 +315,7 @@ int run_frames(LPCNetBatch *b, const float *d_features, int stride, int f0, int 
   int nl = 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (b->profiling) { CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventRecord(e0, st)); }
-  CK(launch_frame_network(fa, st, &nl));
+  CK(launch_frame_network(fa, st, &nl, fork_for(b, st)));
   if (b->profiling) { CK(cudaEventRecord(e1, st)); b->ev_frame.emplace_back(e0, e1); }
   b->launches += nl;
   // keep the last frame's conditioning in the stream state (lpcnet_private.h:43-47)
@@ -469,7 +487,7 @@ int lpcb::batch_frame_network_masked(LPCNetBatch *b, const float *d_features, in
   fa.stream_mask = d_mask;
   if (d_rows && !getenv("LPCNET_B200_NO_COMPACT")) { fa.rows = d_rows; fa.n_rows = n_rows; fa.stream_mask = nullptr; }
   int nl = 0;
-  CK(launch_frame_network(fa, side ? side : b->stream, &nl));
+  CK(launch_frame_network(fa, side ? side : b->stream, &nl, fork_for(b, side ? side : b->stream)));
   b->launches += nl;
   return 0;
 }
@@ -659,6 +677,7 @@ void lpcnet_batch_destroy(LPCNetBatch *b) {
     cudaEventDestroy(b->ev_entry);
     for (int k = 0; k < 2; k++) { cudaEventDestroy(b->ev_frames[k]); cudaEventDestroy(b->ev_samples[k]); }
   }
+  for (auto &f : b->forks) { cudaStreamSynchronize(f.second.aux); cudaStreamDestroy(f.second.aux); cudaEventDestroy(f.second.begin); cudaEventDestroy(f.second.done); }
   void *ptrs[] = {b->st_alloc, b->fb_alloc, b->fb2_alloc, b->d_feat, b->d_pcm, b->d_forced, b->d_trace, b->d_logits, b->d_packets, b->d_compact, b->d_compact2};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (b->cstream) { cudaStreamSynchronize(b->cstream); cudaStreamDestroy(b->cstream); cudaEventDestroy(b->ev_chunk); cudaEventDestroy(b->ev_copied); }

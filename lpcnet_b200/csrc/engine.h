@@ -263,7 +263,11 @@ struct FrameArgs {
   int n_rows = 0;              //   the kernels are launched over the list, not over the batch); layouts stay those of the batch
   int state_only = 0;          // run_frame_network_flush (lpcnet.c:134-144): only the frame-rate state moves
 };
-cudaError_t launch_frame_network(const FrameArgs &a, cudaStream_t s, int *n_launches);
+// fork (optional): an auxiliary CUDA stream and two events.  The cepstrum -> LPC kernel depends on the features only,
+// not on the conv / dense chain, and both are latency-bound at small sizes: with a fork it runs on `aux` beside
+// conv1 + cond (joined before the finalize kernel) instead of behind them.
+struct FrameFork { cudaStream_t aux = nullptr; cudaEvent_t begin = nullptr, done = nullptr; };
+cudaError_t launch_frame_network(const FrameArgs &a, cudaStream_t s, int *n_launches, const FrameFork *fork = nullptr);
 
 struct DecodeArgs {
   DevModel m;
@@ -313,7 +317,8 @@ int batch_frame_network_masked(LPCNetBatch *b, const float *d_features, int stri
 int batch_sample_segment(LPCNetBatch *b, int n, const uint8_t *d_flags, const short *d_forced, short *d_out,
                          const int *d_perm = nullptr, int n_act = 0, cudaStream_t side = nullptr, int tile_override = 0);
 // one frame of analysis for the streams with mask != 0: d_pcm16 [B][160] -> d_features [B][36] (others untouched)
+// d_rows / n_rows (optional): the device list of those streams -- the kernels' grids then cover the list only
 int feature_batch_frame_masked(LPCNetFeatureBatch *b, const short *d_pcm16, const uint8_t *d_mask, float *d_features,
-                               cudaStream_t stream);
+                               cudaStream_t stream, const int *d_rows = nullptr, int n_rows = 0);
 
 }  // namespace lpcb

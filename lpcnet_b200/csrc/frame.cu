@@ -364,20 +364,29 @@ __global__ void decode_packets_kernel(DecodeArgs A) {
 
 }  // namespace
 
-cudaError_t launch_frame_network(const FrameArgs &a, cudaStream_t s, int *n_launches) {
+cudaError_t launch_frame_network(const FrameArgs &a, cudaStream_t s, int *n_launches, const FrameFork *fork) {
   const int B = a.rows ? a.n_rows : a.n_streams, F = a.n_frames;     // streams this launch covers
   if (B <= 0) return cudaSuccess;
   const int rows = B * F;
+  cudaError_t e;
+  const bool lpc = !a.m.end2end;          // (END2END: cond_kernel writes the LPC itself)
+  const bool forked = lpc && fork && fork->aux;
+  if (lpc) {
+    if ((e = fft_opt_in(lpc_kernel)) != cudaSuccess) return e;
+    if (forked) {
+      if ((e = cudaEventRecord(fork->begin, s)) != cudaSuccess) return e;
+      if ((e = cudaStreamWaitEvent(fork->aux, fork->begin, 0)) != cudaSuccess) return e;
+      lpc_kernel<<<(rows + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, fork->aux>>>(a);
+      if ((e = cudaEventRecord(fork->done, fork->aux)) != cudaSuccess) return e;
+    }
+  }
   frame_inputs_kernel<<<B * (F + 2), 128, 0, s>>>(a);
   conv1_kernel<<<(rows + kRowsPerBlock - 1) / kRowsPerBlock, kFT, 0, s>>>(a);
   cond_kernel<<<(rows + kRowsPerBlock - 1) / kRowsPerBlock, kFT, 0, s>>>(a);
-  if (!a.m.end2end) {                     // (END2END: cond_kernel wrote the LPC already)
-    cudaError_t e = fft_opt_in(lpc_kernel);
-    if (e != cudaSuccess) return e;
-    lpc_kernel<<<(rows + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, s>>>(a);
-  }
+  if (lpc && !forked) lpc_kernel<<<(rows + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, s>>>(a);
+  if (forked && (e = cudaStreamWaitEvent(s, fork->done, 0)) != cudaSuccess) return e;
   frame_finalize_kernel<<<(B * 32 + 127) / 128, 128, 0, s>>>(a);
-  if (n_launches) *n_launches += a.m.end2end ? 4 : 5;
+  if (n_launches) *n_launches += lpc ? 5 : 4;
   return cudaGetLastError();
 }
 

@@ -19,6 +19,7 @@
 // inactive / free-running / teacher-forced.  Frame-rate arithmetic (DC filter in double, Burg cepstrum, the
 // int8 predictor GRUs, cross-fade) follows the reference operation by operation; -fmad=false.
 #include <math.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -79,7 +80,15 @@ struct PlcArgs {
   const uint16_t *lossc; // [B] loss_count before this frame
   short *pcm_io;         // [B][total_frames*160]
   int n_streams, frame, total_frames, remove_dc;
+  // side chain: the device list of the frame's first-good-frame streams -- its per-stream kernels run over the list
+  // (a grid over the whole batch that mostly returns at the mask costs a wave of blocks per kernel, and the side
+  // chain has only the SMs the main class's persistent kernels leave)
+  const int *list;
+  int n_list;
 };
+__device__ __forceinline__ int plc_count(const PlcArgs &A) { return A.list ? A.n_list : A.n_streams; }
+__device__ __forceinline__ int plc_stream(const PlcArgs &A, int k) { return A.list ? __ldg(A.list + k) : k; }
+inline int plc_n(const PlcArgs &A) { return A.list ? A.n_list : A.n_streams; }
 
 #define DC_CONST 0.003
 
@@ -362,7 +371,7 @@ __device__ void plc_gru(const uint32_t *w_in, const uint32_t *w_rec, const float
 }
 
 __global__ void __launch_bounds__(256) plc_pred_kernel(PlcArgs A, int fg_pass) {
-  const int s = blockIdx.x, t = threadIdx.x, B = A.n_streams;
+  const int s = plc_stream(A, blockIdx.x), t = threadIdx.x, B = A.n_streams;
   const uint8_t cls = A.masks[mCls * B + s];
   int mode;   // 1 zeros, 2 burg only, 3 burg + features
   if (fg_pass) {
@@ -414,9 +423,9 @@ __global__ void __launch_bounds__(256) plc_pred_kernel(PlcArgs A, int fg_pass) {
 // ---- small per-stream moves ----
 // frame-network input rows: `from_enc` streams take the analysis features, the others st->features
 __global__ void plc_gather_feat_kernel(PlcArgs A, int mask_row, int main_pass) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= A.n_streams * 20) return;
-  const int s = i / 20, k = i % 20;
+  const int i0 = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i0 >= plc_count(A) * 20) return;
+  const int s = plc_stream(A, i0 / 20), k = i0 % 20, i = s * 20 + k;
   if (!A.masks[mask_row * A.n_streams + s]) return;
   const bool enc = main_pass && A.masks[mCls * A.n_streams + s] == kG0;
   A.w.fnfeat[i] = enc ? A.w.encf[(size_t)s * 36 + k] : A.st.features[i];
@@ -434,8 +443,8 @@ __global__ void plc_copy_kernel(const uint8_t *mask, const uint8_t *cls, int wan
 }
 
 // snapshot / restore of the synthesis state (`copy = st->lpcnet`, `st->lpcnet = copy`), and clear_state
-__global__ void plc_state_copy_kernel(DevState dst, DevState src, const uint8_t *mask, int B) {
-  const int s = blockIdx.x, t = threadIdx.x;
+__global__ void plc_state_copy_kernel(DevState dst, DevState src, const uint8_t *mask, int B, const int *list = nullptr) {
+  const int s = list ? __ldg(list + blockIdx.x) : blockIdx.x, t = threadIdx.x;
   if (!mask[s]) return;
   for (int i = t; i < 2 * kConvIn; i += blockDim.x) dst.conv1_state[(size_t)s * 2 * kConvIn + i] = src.conv1_state[(size_t)s * 2 * kConvIn + i];
   for (int i = t; i < 2 * kC; i += blockDim.x) dst.conv2_state[(size_t)s * 2 * kC + i] = src.conv2_state[(size_t)s * 2 * kC + i];
@@ -455,8 +464,8 @@ __global__ void plc_state_copy_kernel(DevState dst, DevState src, const uint8_t 
   }
 }
 
-__global__ void plc_clear_state_kernel(DevState st, const uint8_t *mask, int B) {
-  const int s = blockIdx.x, t = threadIdx.x;
+__global__ void plc_clear_state_kernel(DevState st, const uint8_t *mask, int B, const int *list = nullptr) {
+  const int s = list ? __ldg(list + blockIdx.x) : blockIdx.x, t = threadIdx.x;
   if (!mask[s]) return;
   for (int i = t; i < kN; i += blockDim.x) st.gru_a[(size_t)s * kN + i] = 0.f;
   if (t < kNB) st.gru_b[(size_t)s * kNB + t] = 0.f;
@@ -469,8 +478,10 @@ __global__ void plc_clear_state_kernel(DevState st, const uint8_t *mask, int B) 
 __global__ void __launch_bounds__(kWpsThreads) plc_fg_mid_kernel(PlcArgs A) {
   __shared__ short xs[kWpsThreads / 32][kFrame], ls[kWpsThreads / 32][kFrame], ys[kWpsThreads / 32][kTOff];
   int lane, w;
-  const int s = wps_stream(lane, w);
-  if (s >= A.n_streams || !A.masks[mFG * A.n_streams + s]) return;
+  const int k = wps_stream(lane, w);
+  if (k >= plc_count(A)) return;
+  const int s = plc_stream(A, k);
+  if (!A.masks[mFG * A.n_streams + s]) return;
   short *pcm = A.st.pcm + (size_t)s * kFrame, *in = A.w.in + (size_t)s * kFrame, *lp = A.w.lp + (size_t)s * kFrame;
   const short *syn = A.w.sego + (size_t)s * kTOff;   // an 80-sample segment: rows of 80
   for (int i = lane; i < kTOff; i += 32) { const short v = syn[i]; ys[w][i] = v; pcm[kFrame - kTOff + i] = v; }
@@ -504,8 +515,10 @@ __global__ void __launch_bounds__(kWpsThreads) plc_fg_mid_kernel(PlcArgs A) {
 
 // FG: cross-fade of the forward and the backward synthesis, and the queued update (lpcnet_plc.c:403-419)
 __global__ void plc_fg_end_kernel(PlcArgs A) {
-  const int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= A.n_streams || !A.masks[mFG * A.n_streams + s]) return;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= plc_count(A)) return;
+  const int s = plc_stream(A, k);
+  if (!A.masks[mFG * A.n_streams + s]) return;
   short *pcm = A.st.pcm + (size_t)s * kFrame;
   const short *rev = A.w.sego2 + (size_t)s * kTOff, *in = A.w.in + (size_t)s * kFrame;
   const int delta = A.w.delta[s];
@@ -786,6 +799,13 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
   if (const char *e = getenv("LPCNET_B200_PLC_MAIN_TILE")) main_tile = atoi(e);
   PlcArgs A1 = A;
   if (two) A1.w = p->w_side;
+  // LPCNET_B200_PLC_TIMING=1 (development): CUDA events between the stages of the batch's stream, printed per call
+  const bool timing = getenv("LPCNET_B200_PLC_TIMING") != nullptr;
+  static const char *kMark[] = {"start", "pre+burg", "upd analysis", "pred+gather+fn", "segment A", "segment B",
+                                "lost_mid+L1 analysis", "wait side", "finish"};
+  constexpr int kMarks = sizeof(kMark) / sizeof(kMark[0]);
+  std::vector<cudaEvent_t> tev;
+  auto mark = [&](int) { if (timing) { cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, cs); tev.push_back(e); } };
   if (two) CKP(cudaEventRecord(p->ev_fin, cs));            // the control rows are uploaded, the last call's frames done
   for (int f = 0; f < n_frames; f++) {
     const uint8_t *M = static_cast<const uint8_t *>(p->d_ctl) + per_frame * f;
@@ -795,6 +815,7 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
     const Any a = any[f];
     const int *permFG = reinterpret_cast<const int *>(M + perm_off), *permMain = permFG + B;
     const bool side_work = two && a.fg;
+    mark(0);
     if (side_work) CKP(cudaStreamWaitEvent(ss, p->ev_fin, 0));
     if (a.upd) {
       plc_pre_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A);
@@ -802,50 +823,79 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
       plc_burg_kernel<<<(2 * B + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, cs>>>(A);
       plc_burg_combine_kernel<<<(B * kBands + 255) / 256, 256, 0, cs>>>(A);
     }
+    mark(1);
     if (a.fg) {
       if (two) { CKP(cudaEventRecord(p->ev_pre, cs)); CKP(cudaStreamWaitEvent(ss, p->ev_pre, 0)); }
-      plc_pred_kernel<<<B, 256, 0, ss>>>(A1, 1);
-      plc_state_copy_kernel<<<B, 128, 0, ss>>>(p->snap, V.st, M + (size_t)mFG * B, B);
-      plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, ss>>>(A1, mFG, 0);
-      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B, false, permFG, a.nfg, two ? ss : nullptr)) return -1;
+      // every kernel of the chain runs over the list of the frame's first-good-frame streams
+      A1.list = permFG; A1.n_list = a.nfg;
+      const int nl = a.nfg;
+      const uint8_t *mfg = M + (size_t)mFG * B;
+      plc_pred_kernel<<<nl, 256, 0, ss>>>(A1, 1);
+      plc_state_copy_kernel<<<nl, 128, 0, ss>>>(p->snap, V.st, mfg, B, permFG);
+      plc_gather_feat_kernel<<<(nl * 20 + 255) / 256, 256, 0, ss>>>(A1, mFG, 0);
+      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, mfg, false, permFG, a.nfg, two ? ss : nullptr)) return -1;
       if (batch_sample_segment(p->syn, kTOff, M + (size_t)fFgFree * B, nullptr, A1.w.sego, permFG, a.nfg, two ? ss : nullptr)) return -1;
-      plc_fg_mid_kernel<<<wps_grid(B), kWpsThreads, 0, ss>>>(A1);
-      plc_clear_state_kernel<<<B, 128, 0, ss>>>(V.st, M + (size_t)mFG * B, B);
-      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B, false, permFG, a.nfg, two ? ss : nullptr)) return -1;
+      plc_fg_mid_kernel<<<wps_grid(nl), kWpsThreads, 0, ss>>>(A1);
+      plc_clear_state_kernel<<<nl, 128, 0, ss>>>(V.st, mfg, B, permFG);
+      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, mfg, false, permFG, a.nfg, two ? ss : nullptr)) return -1;
       if (batch_sample_segment(p->syn, kFrame, M + (size_t)fFgForced * B, A1.w.segf, A1.w.sego, permFG, a.nfg, two ? ss : nullptr)) return -1;
       if (batch_sample_segment(p->syn, kTOff, M + (size_t)fFgFree * B, nullptr, A1.w.sego2, permFG, a.nfg, two ? ss : nullptr)) return -1;
-      plc_fg_end_kernel<<<gs, tb, 0, ss>>>(A1);
-      plc_state_copy_kernel<<<B, 128, 0, ss>>>(V.st, p->snap, M + (size_t)mFG * B, B);
-      if (feature_batch_frame_masked(p->ana, p->st.pcm, M + (size_t)mFG * B, p->w.encf2, ss)) return -1;
+      plc_fg_end_kernel<<<(nl + tb - 1) / tb, tb, 0, ss>>>(A1);
+      plc_state_copy_kernel<<<nl, 128, 0, ss>>>(V.st, p->snap, mfg, B, permFG);
+      if (feature_batch_frame_masked(p->ana, p->st.pcm, mfg, p->w.encf2, ss, permFG, a.nfg)) return -1;
       // (the analysis of an FG stream's input frame follows that of its concealment buffer: same chain)
-      if (two && feature_batch_frame_masked(p->ana, p->w.in, M + (size_t)mFG * B, p->w.encf, ss)) return -1;
+      if (two && feature_batch_frame_masked(p->ana, p->w.in, mfg, p->w.encf, ss, permFG, a.nfg)) return -1;
       // Q: process_queued_update (lpcnet_plc.c:342-347) -- the update the FG branch queues for the stream's next call
       // (frame network on st->features + 160 samples forced on queued_samples) touches the synthesis state only, and
       // nothing between here and that call does: it runs now, at the end of the side chain, beside the main class.
-      plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, ss>>>(A1, mFG, 0);
-      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mFG * B, false, permFG, a.nfg, two ? ss : nullptr)) return -1;
+      plc_gather_feat_kernel<<<(nl * 20 + 255) / 256, 256, 0, ss>>>(A1, mFG, 0);
+      if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, mfg, false, permFG, a.nfg, two ? ss : nullptr)) return -1;
       if (batch_sample_segment(p->syn, kFrame, M + (size_t)fFgForced * B, p->st.queued, A1.w.sego, permFG, a.nfg, two ? ss : nullptr)) return -1;
     }
     if (side_work) CKP(cudaEventRecord(p->ev_side, ss));
     if (two) {
       if (a.updm && feature_batch_frame_masked(p->ana, p->w.in, M + (size_t)mUpdM * B, p->w.encf, cs)) return -1;
     } else if (a.upd && feature_batch_frame_masked(p->ana, p->w.in, M + (size_t)mUpd * B, p->w.encf, cs)) return -1;
+    mark(2);
     if (a.main_) {
       plc_pred_kernel<<<B, 256, 0, cs>>>(A, 0);
       plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, cs>>>(A, mMain, 1);
       if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mMain * B, false, permMain, a.nmain)) return -1;
       plc_seg_prep_kernel<<<(B * kTOff + 255) / 256, 256, 0, cs>>>(A, 0);
+      mark(3);
       if (batch_sample_segment(p->syn, kTOff, M + (size_t)fA * B, p->w.segf, p->w.sego, permMain, a.nmain, nullptr, main_tile)) return -1;
       plc_seg_prep_kernel<<<(B * kTOff + 255) / 256, 256, 0, cs>>>(A, 1);
+      mark(4);
       if (batch_sample_segment(p->syn, kTOff, M + (size_t)fB * B, p->w.segf, p->w.sego2, permMain, a.nmain, nullptr, main_tile)) return -1;
+      mark(5);
       plc_lost_mid_kernel<<<gs, tb, 0, cs>>>(A);
       if (a.l1 && feature_batch_frame_masked(p->ana, p->st.pcm, M + (size_t)mL1 * B, p->w.encf2, cs)) return -1;
-    }
+    } else { mark(3); mark(4); mark(5); }
+    mark(6);
     if (side_work) CKP(cudaStreamWaitEvent(cs, p->ev_side, 0));
+    mark(7);
     plc_finish_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A);
+    mark(8);
     if (two) CKP(cudaEventRecord(p->ev_fin, cs));
     CKP(cudaGetLastError());
     p->frames_done++;
+  }
+  if (timing && !tev.empty()) {
+    CKP(cudaStreamSynchronize(cs));
+    double sum[kMarks] = {0};
+    for (int f = 0; f < n_frames; f++)
+      for (int k = 1; k < kMarks; k++) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, tev[(size_t)f * kMarks + k - 1], tev[(size_t)f * kMarks + k]);
+        sum[k] += ms;
+      }
+    double tot = 0;
+    for (int k = 1; k < kMarks; k++) tot += sum[k];
+    fprintf(stderr, "plc_run %d frames x %d streams, ms per frame on the batch's stream (%s): total %.3f |", n_frames, B,
+            two ? "side stream on" : "one stream", tot / n_frames);
+    for (int k = 1; k < kMarks; k++) fprintf(stderr, " %s %.3f |", kMark[k], sum[k] / n_frames);
+    fprintf(stderr, "\n");
+    for (cudaEvent_t e : tev) cudaEventDestroy(e);
   }
   return 0;
 }
