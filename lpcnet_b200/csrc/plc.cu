@@ -647,7 +647,9 @@ struct LPCNetPLCBatch {
   // side chain (Q and FG streams): CUDA stream, segment buffers [B][160] x 3, events
   cudaStream_t side = nullptr;
   PlcWork w_side{};
-  cudaEvent_t ev_pre = nullptr, ev_side = nullptr, ev_fin = nullptr;
+  cudaEvent_t ev_pre = nullptr, ev_side = nullptr, ev_fin = nullptr, ev_q[2] = {nullptr, nullptr};
+  bool q_pending = false;
+  int q_slot = 0;
   // causal / codec modes (lpcnet_plc.c:185-340): device buffers and the host's copy of the control state
   bool causal = false;
   int enable_blending = 1, delay = 0;
@@ -713,7 +715,7 @@ int plc_alloc(LPCNetPLCBatch *p) {
   int lo = 0, hi = 0;
   CKP(cudaDeviceGetStreamPriorityRange(&lo, &hi));
   CKP(cudaStreamCreateWithPriority(&p->side, cudaStreamNonBlocking, hi));
-  for (cudaEvent_t *e : {&p->ev_pre, &p->ev_side, &p->ev_fin}) CKP(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+  for (cudaEvent_t *e : {&p->ev_pre, &p->ev_side, &p->ev_fin, &p->ev_q[0], &p->ev_q[1]}) CKP(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
   p->snap.conv1_state = (float *)(b + o_c1); p->snap.conv2_state = (float *)(b + o_c2); p->snap.gru_a = (float *)(b + o_ga);
   p->snap.gru_b = (float *)(b + o_gb); p->snap.last_sig = (float *)(b + o_ls); p->snap.lpc = (float *)(b + o_lpc);
   p->snap.rng = (uint32_t *)(b + o_rng); p->snap.deemph = (float *)(b + o_dm); p->snap.last_exc = (int *)(b + o_le);
@@ -815,6 +817,12 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
     const Any a = any[f];
     const int *permFG = reinterpret_cast<const int *>(M + perm_off), *permMain = permFG + B;
     const bool side_work = two && a.fg;
+    bool side_recorded = false;
+    // an update of an earlier frame may still be running (two events, used in turn: this frame's side chain records
+    // the other one before the batch's stream gets to wait for this one)
+    const bool q_before = p->q_pending;
+    cudaEvent_t q_event = p->ev_q[p->q_slot];
+    p->q_pending = false;
     mark(0);
     if (side_work) CKP(cudaStreamWaitEvent(ss, p->ev_fin, 0));
     if (a.upd) {
@@ -847,17 +855,23 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
       if (two && feature_batch_frame_masked(p->ana, p->w.in, mfg, p->w.encf, ss, permFG, a.nfg)) return -1;
       // Q: process_queued_update (lpcnet_plc.c:342-347) -- the update the FG branch queues for the stream's next call
       // (frame network on st->features + 160 samples forced on queued_samples) touches the synthesis state only, and
-      // nothing between here and that call does: it runs now, at the end of the side chain, beside the main class.
+      // nothing between here and that call does: it runs now, at the end of the side chain.  The frame's end does not
+      // wait for it (ev_side is recorded here): it runs on beside plc_finish and the next frame's first stages, and
+      // the batch's stream joins it (ev_q) before the next main-class predictor, the first kernel that touches what
+      // the update reads (st->features) or writes (the synthesis state) for these streams.
+      if (two) { CKP(cudaEventRecord(p->ev_side, ss)); side_recorded = true; }
       plc_gather_feat_kernel<<<(nl * 20 + 255) / 256, 256, 0, ss>>>(A1, mFG, 0);
       if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, mfg, false, permFG, a.nfg, two ? ss : nullptr)) return -1;
       if (batch_sample_segment(p->syn, kFrame, M + (size_t)fFgForced * B, p->st.queued, A1.w.sego, permFG, a.nfg, two ? ss : nullptr)) return -1;
+      if (two) { p->q_slot ^= 1; CKP(cudaEventRecord(p->ev_q[p->q_slot], ss)); p->q_pending = true; }
     }
-    if (side_work) CKP(cudaEventRecord(p->ev_side, ss));
+    if (side_work && !side_recorded) CKP(cudaEventRecord(p->ev_side, ss));
     if (two) {
       if (a.updm && feature_batch_frame_masked(p->ana, p->w.in, M + (size_t)mUpdM * B, p->w.encf, cs)) return -1;
     } else if (a.upd && feature_batch_frame_masked(p->ana, p->w.in, M + (size_t)mUpd * B, p->w.encf, cs)) return -1;
     mark(2);
     if (a.main_) {
+      if (q_before) CKP(cudaStreamWaitEvent(cs, q_event, 0));
       plc_pred_kernel<<<B, 256, 0, cs>>>(A, 0);
       plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, cs>>>(A, mMain, 1);
       if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mMain * B, false, permMain, a.nmain)) return -1;
@@ -872,6 +886,7 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
       if (a.l1 && feature_batch_frame_masked(p->ana, p->st.pcm, M + (size_t)mL1 * B, p->w.encf2, cs)) return -1;
     } else { mark(3); mark(4); mark(5); }
     mark(6);
+    if (q_before && !a.main_) CKP(cudaStreamWaitEvent(cs, q_event, 0));
     if (side_work) CKP(cudaStreamWaitEvent(cs, p->ev_side, 0));
     mark(7);
     plc_finish_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A);
@@ -879,6 +894,10 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
     if (two) CKP(cudaEventRecord(p->ev_fin, cs));
     CKP(cudaGetLastError());
     p->frames_done++;
+  }
+  if (p->q_pending) {       // the call returns with every stream's state final
+    CKP(cudaStreamWaitEvent(cs, p->ev_q[p->q_slot], 0));
+    p->q_pending = false;
   }
   if (timing && !tev.empty()) {
     CKP(cudaStreamSynchronize(cs));
@@ -1164,7 +1183,7 @@ void lpcnet_plc_batch_destroy(LPCNetPLCBatch *p) {
   if (!p) return;
   if (p->syn) lpcnet_batch_sync(p->syn);
   if (p->side) { cudaStreamSynchronize(p->side); cudaStreamDestroy(p->side); }
-  for (cudaEvent_t e : {p->ev_pre, p->ev_side, p->ev_fin}) if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : {p->ev_pre, p->ev_side, p->ev_fin, p->ev_q[0], p->ev_q[1]}) if (e) cudaEventDestroy(e);
   cudaFree(p->alloc); cudaFree(p->tab_alloc); cudaFree(p->d_io); cudaFree(p->d_ctl); cudaFree(p->causal_alloc);
   if (p->ana) lpcnet_feature_batch_destroy(p->ana);
   if (p->syn) lpcnet_batch_destroy(p->syn);
