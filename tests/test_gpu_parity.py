@@ -357,6 +357,57 @@ def test_mixed_tile_schedule_is_invisible(eng, model_blob, orc_model):
         assert np.array_equal(out[0][s], ref), s
 
 
+def test_two_tiles_per_cta_variant(eng, model_blob, orc_model):
+    """lpcnet_batch_set_tile(28): two 8-stream tiles per CTA on named barriers (measured slower, kept
+    selectable).  A ragged batch over several CTAs and two calls must give the oracle's PCM."""
+    B, F = 8 * 37 + 5, 5
+    base = np.stack([blob.synthetic_features(F, s) for s in range(64)])
+    feats = base[np.arange(B) % 64]
+    bt = eng.Batch(model_blob, B)
+    bt.set_tile(28)
+    for s in range(B):
+        bt.set_seed(s, blob.stream_seed(s % 64))
+    a = bt.synthesize(feats[:, :2])[0]
+    b = bt.synthesize(feats[:, 2:])[0]
+    bt.close()
+    out = np.concatenate([a, b], axis=1)
+    for s in (0, 7, 8, 15, 16, 150, B - 6, B - 1):
+        ref = orcpy.OrcStream(orc_model, blob.stream_seed(s % 64)).run(feats[s])[0]
+        assert np.array_equal(out[s], ref), s
+
+
+def test_l2_sized_chunks_are_invisible(eng, model_blob, orc_model, monkeypatch):
+    """Calls of >= 8 frames on batches that fit L2's persisting carve-out run in short chunks with an access-policy
+    window over the conditioning rows (api.cu group_streams / chunk_frames); LPCNET_B200_L2_PERSIST_MB=0 is the
+    32-frame chunking.  Same PCM either way, over two calls, and the oracle's on sampled streams."""
+    B, F = 300, 21
+    base = np.stack([blob.synthetic_features(F, s) for s in range(64)])
+    feats = base[np.arange(B) % 64]
+
+    def run():
+        bt = eng.Batch(model_blob, B)
+        for s in range(B):
+            bt.set_seed(s, blob.stream_seed(s % 64))
+        n0 = bt.launch_count
+        a = bt.synthesize(feats[:, :12])[0]
+        n1 = bt.launch_count - n0
+        b = bt.synthesize(feats[:, 12:])[0]
+        bt.close()
+        return np.concatenate([a, b], axis=1), n1
+
+    monkeypatch.setenv("LPCNET_B200_L2_PERSIST_MB", "12")         # 12 MB carve-out: 300 streams in 2-frame chunks
+    small, n_small = run()
+    monkeypatch.setenv("LPCNET_B200_L2_PERSIST_MB", "0")
+    plain, n_plain = run()
+    monkeypatch.delenv("LPCNET_B200_L2_PERSIST_MB")
+    default, _ = run()
+    assert n_small > 2 * n_plain                                   # it did run in short chunks
+    assert np.array_equal(small, plain) and np.array_equal(default, plain)
+    for s in (0, 63, 64, 299):
+        ref = orcpy.OrcStream(orc_model, blob.stream_seed(s % 64)).run(feats[s])[0]
+        assert np.array_equal(plain[s], ref), s
+
+
 def test_stream_groups_are_invisible(eng, model_blob, orc_model, monkeypatch):
     """Large batches are walked in groups of whole 16-stream-tile waves, each in full 32-frame chunks (api.cu
     group_streams).  With the group budget lowered to one wave: 5000 streams x 40 frames (3 groups x 2 chunks, the
