@@ -22,6 +22,7 @@
 
 #include "../../include/lpcnet_b200.h"
 #include "dsp.cuh"
+#include "dsp_warp.cuh"
 #include "engine.h"
 
 namespace lpcb {
@@ -98,62 +99,60 @@ __global__ void preemph_kernel(AnalysisArgs A) {
 }
 
 // frame_analysis + the spectral half of compute_frame_features (lpcnet_enc.c:488-527): window, forward FFT,
-// band energies, log smoothing, DCT, LPC from the cepstrum.  One thread per (stream, frame).
-__global__ void spectral_kernel(AnalysisArgs A) {
-  const int B = A.n_streams, F = A.n_frames;
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+// band energies, log smoothing, DCT, LPC from the cepstrum.  One WARP per (stream, frame) (dsp_warp.cuh): lanes share
+// the transform's butterflies, one band per lane for the band sums / logs / DCT.
+constexpr int kSpecWarps = 8;
+__global__ void __launch_bounds__(kSpecWarps * 32) spectral_kernel(AnalysisArgs A) {
+  __shared__ __align__(16) float sm[kSpecWarps * kWarpDspFloats];
+  const int F = A.n_frames;
+  const int lane = threadIdx.x & 31, wi = threadIdx.x >> 5;
+  const int idx = blockIdx.x * kSpecWarps + wi;
   if (idx >= an_count(A) * F) return;
   const int s = an_stream(A, idx / F), f = idx % F;
   if (A.stream_mask && !A.stream_mask[s]) return;
-  const Scratch S = block_scratch();
+  const WarpDsp W = warp_dsp(sm, wi, lane);
   const float *x = A.P + (size_t)s * (kOverlap + F * kFrame) + (size_t)f * kFrame;   // [analysis_mem | frame]
   // apply_window (freq.c:322-328) and opus_fft_c's scaled bit-reversed copy (kiss_fft.c:566-585)
   const float scale = 1.f / 320;
-  for (int k = 0; k < kWin; k++) {
+  for (int k = lane; k < kWin; k += 32) {
     const float w = __ldg(A.half_window + (k < kOverlap ? k : kWin - 1 - k));
-    Cpx c;
-    c.r = scale * (x[k] * w); c.i = scale * 0.f;
-    S.st(__ldg(A.tab.fft_bitrev + k), c);
+    W.x[__ldg(A.tab.fft_bitrev + k)] = make_float2(scale * (x[k] * w), scale * 0.f);
   }
-  fft320_butterflies(S, A.tab.fft_tw);
-  // lpcn_compute_band_energy (freq.c:128-150)
-  float sum[kBands];
-  for (int i = 0; i < kBands; i++) sum[i] = 0;
-  for (int i = 0; i < kBands - 1; i++) {
-    const int band_size = (c_eband5ms[i + 1] - c_eband5ms[i]) * 4;
-    for (int j = 0; j < band_size; j++) {
-      const float frac = (float)j / (float)band_size;
-      const Cpx X = S.ld(c_eband5ms[i] * 4 + j);
-      float tmp = X.r * X.r;
-      tmp += X.i * X.i;
-      sum[i] += (1.f - frac) * tmp;
-      sum[i + 1] += frac * tmp;
-    }
-  }
-  sum[0] *= 2;
-  sum[kBands - 1] *= 2;
-  // lpcnet_enc.c:514-522
-  float Ly[kBands], logMax = -2, follow = -2;
+  __syncwarp();
+  wfft320(W, A.tab.fft_tw);
+  // lpcn_compute_band_energy (freq.c:128-150), band `lane`; its log (lpcnet_enc.c:516)
+  const float sum = w_band_energy<false>(W);
+  float *Ly = W.f + 18, *ceps = Ly;                  // (W.f[0..18) and [36..53) belong to w_lpc_from_cepstrum)
+  if (lane < kBands) Ly[lane] = (float)log10(1e-2 + (double)sum);
+  __syncwarp();
+  // lpcnet_enc.c:514-522: the smoothing walks the bands in order (every lane runs it; lane i keeps band i's value)
+  float mine = 0.f, logMax = -2, follow = -2;
   for (int i = 0; i < kBands; i++) {
-    float l = (float)log10(1e-2 + (double)sum[i]);
+    float l = Ly[i];
     l = fmaxf(logMax - 8, fmaxf(follow - 2.5f, l));
-    Ly[i] = l;
+    if (i == lane) mine = l;
     logMax = fmaxf(logMax, l);
     follow = fmaxf(follow - 2.5f, l);
   }
+  __syncwarp();
+  if (lane < kBands) Ly[lane] = mine;
+  __syncwarp();
   // dct (freq.c:218-228)
-  float ceps[kBands];
-  for (int i = 0; i < kBands; i++) {
-    float acc = 0;
-    for (int j = 0; j < kBands; j++) acc += Ly[j] * __ldg(A.tab.dct + j * kBands + i);
-    ceps[i] = (float)((double)acc * sqrt(2. / kBands));
-  }
-  ceps[0] -= 4;
+  float c = w_dct(A.tab.dct, Ly, lane);
+  if (lane == 0) c -= 4;
+  __syncwarp();
+  if (lane < kBands) ceps[lane] = c;
+  __syncwarp();
   float lpc[16];
-  lpc_from_cepstrum_dev(A.tab, ceps, lpc, S);
+  w_lpc_from_cepstrum(A.tab, W, ceps, lpc);
   float *out = A.features + ((size_t)s * A.total_frames + A.frame0 + f) * kNF;
-  for (int i = 0; i < kBands; i++) out[i] = ceps[i];
-  for (int i = 0; i < 16; i++) out[kBands + 2 + i] = lpc[i];
+  if (lane < kBands) out[lane] = c;
+  if (lane < 16) {
+    float v = lpc[0];
+#pragma unroll
+    for (int i = 1; i < 16; i++) v = lane == i ? lpc[i] : v;
+    out[kBands + 2 + lane] = v;
+  }
 }
 
 // The LPC residual of the 80-sample-delayed signal (lpcnet_enc.c:528-539): an FIR, so every sample is independent.
@@ -516,8 +515,7 @@ int analysis_device(LPCNetFeatureBatch *b, const short *d16, const float *df, in
     A.fft_scratch = A.S + (((size_t)B * (1 + F * kFrame) + 63) & ~size_t(63));
     const size_t np = (size_t)NA * (kOverlap + F * kFrame);
     preemph_kernel<<<(unsigned)((np + 255) / 256 > 65535 * 16 ? 65535 * 16 : (np + 255) / 256), 256, 0, b->stream>>>(A);
-    if (fft_opt_in(spectral_kernel) != cudaSuccess) return set_last_error("spectral_kernel: shared-memory opt-in failed");
-    spectral_kernel<<<(NA * F + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, b->stream>>>(A);
+    spectral_kernel<<<(NA * F + kSpecWarps - 1) / kSpecWarps, kSpecWarps * 32, 0, b->stream>>>(A);
     const size_t nr = (size_t)NA * F * kFrame;
     residual_kernel<<<(unsigned)((nr + 255) / 256 > 65535 * 16 ? 65535 * 16 : (nr + 255) / 256), 256, 0, b->stream>>>(A);
     if (mode) pitch_kernel<true><<<NA, kPT, pitch_smem(F, 8), b->stream>>>(A);

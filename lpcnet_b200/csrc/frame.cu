@@ -10,6 +10,7 @@
 #include "bitexact.cuh"
 #include "engine.h"
 #include "dsp.cuh"
+#include "dsp_warp.cuh"
 
 namespace lpcb {
 
@@ -240,19 +241,26 @@ __global__ void __launch_bounds__(kFT) cond_kernel(FrameArgs A) {
   }
 }
 
-// K3a: raw LPC per (stream, frame) into fb.lpc[f][s] (delay line applied by K3b).
-__global__ void lpc_kernel(FrameArgs A) {
+// K3a: raw LPC per (stream, frame) into fb.lpc[f][s] (delay line applied by K3b).  One warp per row (dsp_warp.cuh).
+constexpr int kDspWarps = 8;
+__device__ __forceinline__ float lane_pick16(const float (&v)[16], int lane) {   // v[lane] without a local-memory array
+  float r = v[0];
+#pragma unroll
+  for (int i = 1; i < 16; i++) r = lane == i ? v[i] : r;
+  return r;
+}
+__global__ void __launch_bounds__(kDspWarps * 32) lpc_kernel(FrameArgs A) {
+  __shared__ __align__(16) float sm[kDspWarps * kWarpDspFloats];
   const int B = A.n_streams, F = A.n_frames;
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int idx = blockIdx.x * kDspWarps + w;
   if (idx >= n_active(A) * F) return;
   const int s = stream_of(A, idx / F), f = idx % F;
   if (A.stream_mask && !A.stream_mask[s]) return;      // keeps its LPC (see cond_kernel)
-  const Scratch S = block_scratch();
   const float *feat = A.features + ((size_t)s * A.total_frames + A.frame0 + f) * A.feature_stride;
   float lpc[16];
-  lpc_from_cepstrum_dev(DspTables{A.m.fft_tw, A.m.fft_bitrev, A.m.dct}, feat, lpc, S);
-  float *dst = A.fb.lpc + ((size_t)f * B + s) * 16;
-  for (int i = 0; i < 16; i++) dst[i] = lpc[i];
+  w_lpc_from_cepstrum(DspTables{A.m.fft_tw, A.m.fft_bitrev, A.m.dct}, warp_dsp(sm, w, lane), feat, lpc);
+  if (lane < 16) A.fb.lpc[((size_t)f * B + s) * 16 + lane] = lane_pick16(lpc, lane);
 }
 
 // K3b: the FEATURES_DELAY delay line (src/lpcnet.c:109-115), lpc_weighting (freq.c:299-308), and the
@@ -372,18 +380,17 @@ cudaError_t launch_frame_network(const FrameArgs &a, cudaStream_t s, int *n_laun
   const bool lpc = !a.m.end2end;          // (END2END: cond_kernel writes the LPC itself)
   const bool forked = lpc && fork && fork->aux;
   if (lpc) {
-    if ((e = fft_opt_in(lpc_kernel)) != cudaSuccess) return e;
     if (forked) {
       if ((e = cudaEventRecord(fork->begin, s)) != cudaSuccess) return e;
       if ((e = cudaStreamWaitEvent(fork->aux, fork->begin, 0)) != cudaSuccess) return e;
-      lpc_kernel<<<(rows + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, fork->aux>>>(a);
+      lpc_kernel<<<(rows + kDspWarps - 1) / kDspWarps, kDspWarps * 32, 0, fork->aux>>>(a);
       if ((e = cudaEventRecord(fork->done, fork->aux)) != cudaSuccess) return e;
     }
   }
   frame_inputs_kernel<<<B * (F + 2), 128, 0, s>>>(a);
   conv1_kernel<<<(rows + kRowsPerBlock - 1) / kRowsPerBlock, kFT, 0, s>>>(a);
   cond_kernel<<<(rows + kRowsPerBlock - 1) / kRowsPerBlock, kFT, 0, s>>>(a);
-  if (lpc && !forked) lpc_kernel<<<(rows + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, s>>>(a);
+  if (lpc && !forked) lpc_kernel<<<(rows + kDspWarps - 1) / kDspWarps, kDspWarps * 32, 0, s>>>(a);
   if (forked && (e = cudaStreamWaitEvent(s, fork->done, 0)) != cudaSuccess) return e;
   frame_finalize_kernel<<<(B * 32 + 127) / 128, 128, 0, s>>>(a);
   if (n_launches) *n_launches += lpc ? 5 : 4;

@@ -31,6 +31,7 @@
 #include "../../include/lpcnet_b200.h"
 #include "bitexact.cuh"
 #include "dsp.cuh"
+#include "dsp_warp.cuh"
 #include "engine.h"
 
 namespace lpcb {
@@ -143,13 +144,15 @@ __device__ double inner_flp(const float *a, const float *b, int n) {
   return r;
 }
 
-__device__ float burg_analysis(float *Aout, const float *x, float minInvGain, int len, int D) {
+// corr (optional): the 1 + D autocorrelation sums inner_flp(x, x + n, len - n), n = 0..D, formed elsewhere (one lag
+// per lane in plc_burg_kernel: each is a serial sum in the reference's order, and they do not depend on each other)
+__device__ float burg_analysis(float *Aout, const float *x, float minInvGain, int len, int D, const double *corr = nullptr) {
   double C0, invGain, num, nrg_f, nrg_b, rc, Atmp, tmp1, tmp2;
   double Cf[16], Cl[16], CAf[17], CAb[17], Af[16];
   bool reached = false;
-  C0 = inner_flp(x, x, len);
+  C0 = corr ? corr[0] : inner_flp(x, x, len);
   for (int n = 0; n < 16; n++) Cf[n] = 0;
-  for (int n = 1; n < D + 1; n++) Cf[n - 1] += inner_flp(x, x + n, len - n);
+  for (int n = 1; n < D + 1; n++) Cf[n - 1] += corr ? corr[n] : inner_flp(x, x + n, len - n);
   for (int n = 0; n < 16; n++) Cl[n] = Cf[n];
   CAb[0] = CAf[0] = C0 + (double)1e-5f * C0 + (double)1e-9f;
   invGain = 1.0;
@@ -232,69 +235,91 @@ __device__ float burg_analysis(float *Aout, const float *x, float minInvGain, in
 
 __constant__ double c_pow995[16];   // pow(.995, i+1), filled by the host's libm at start-up
 
-__device__ void burg_cepstrum(const PlcArgs &A, const short *pcm, float *out, const Scratch &S) {
-  float bin[kTOff], blpc[16];
-  for (int i = 0; i < kTOff - 1; i++) bin[i] = (float)pcm[i + 1] - 0.85f * (float)pcm[i];
-  float g = burg_analysis(blpc, bin, (float)1e-3, kTOff - 1, 16);
-  g /= (float)(kTOff - 2 * (16 - 1));
+// burg_cepstral_analysis (freq.c:152-186), 32 half frames per block of 32 warps, in three steps:
+//  1. warp w, half frame w: pre-emphasis, then the 17 autocorrelation sums of Burg's method one lag per lane (each a
+//     serial double-precision sum in the reference's order; they do not depend on each other);
+//  2. warp 0, lane l: Burg's recursion for half frame l -- serial and in double precision, so the 32 of the block run
+//     side by side on the lanes of one warp (one per warp would leave 31 lanes idle: measured 2.5x slower per frame);
+//  3. warp w again: the transform, band sums, logs and DCT as in dsp_warp.cuh.
+constexpr int kBurgWarps = 32;
+constexpr size_t kBurgSmem = (size_t)kBurgWarps * kWarpDspFloats * sizeof(float);
+__global__ void __launch_bounds__(kBurgWarps * 32) plc_burg_kernel(PlcArgs A) {
+  extern __shared__ __align__(16) float burg_sm[];
+  __shared__ int valid_s[kBurgWarps];
+  const int lane = threadIdx.x & 31, wi = threadIdx.x >> 5;
+  const int idx = blockIdx.x * kBurgWarps + wi;
+  const int s = idx >> 1, half = idx & 1;
+  const bool valid = s < A.n_streams && A.masks[mUpd * A.n_streams + s];
+  const WarpDsp W = warp_dsp(burg_sm, wi, lane);
+  // per-warp layout until step 3 overwrites it: bin [79] floats, corr [17] doubles behind it, in the transform's buffer
+  auto bin_of = [&](int w) { return burg_sm + (size_t)w * kWarpDspFloats; };
+  auto corr_of = [&](int w) { return reinterpret_cast<double *>(burg_sm + (size_t)w * kWarpDspFloats) + 48; };
+  auto blpc_of = [&](int w) { return burg_sm + (size_t)w * kWarpDspFloats + 640 + 18; };      // W.f + 18: [16], then g
+  if (lane == 0) valid_s[wi] = valid;
+  if (valid) {
+    const short *pcm = A.w.in + (size_t)s * kFrame + half * kTOff;
+    float *bin = bin_of(wi);
+    for (int i = lane; i < kTOff - 1; i += 32) bin[i] = (float)pcm[i + 1] - 0.85f * (float)pcm[i];
+    __syncwarp();
+    if (lane <= 16) corr_of(wi)[lane] = inner_flp(bin, bin + lane, kTOff - 1 - lane);
+  }
+  __syncthreads();
+  if (wi == 0 && valid_s[lane]) {
+    float a[16];
+    float g = burg_analysis(a, bin_of(lane), (float)1e-3, kTOff - 1, 16, corr_of(lane));
+    g /= (float)(kTOff - 2 * (16 - 1));
+    float *o = blpc_of(lane);
+    for (int i = 0; i < 16; i++) o[i] = a[i];
+    o[16] = g;
+  }
+  __syncthreads();
+  if (!valid) return;
+  const float *blpc = blpc_of(wi);
+  const float g = blpc[16];
+  float *out = A.w.encf2 + (size_t)s * 36 + half * kBands;
   // forward_transform of [1, -lpc[i]*.995^(i+1), 0...]: opus_fft_c's scaled bit-reversed copy
   const float scale = 1.f / 320;
-  for (int k = 0; k < 320; k++) {
+  float vin[10];
+#pragma unroll
+  for (int q = 0; q < 10; q++) {        // (read before the buffer is overwritten: bin / corr live in it)
+    const int k = lane + 32 * q;
     float v = 0.f;
     if (k == 0) v = 1.f;
     else if (k <= 16) v = (float)((double)(-blpc[k - 1]) * c_pow995[k - 1]);
-    Cpx c;
-    c.r = scale * v; c.i = scale * 0.f;
-    S.st(__ldg(A.tab.fft_bitrev + k), c);
+    vin[q] = v;
   }
-  fft320_butterflies(S, A.tab.fft_tw);
-  // compute_band_energy_inverse (freq.c:59-84)
-  float sum[kBands];
-  for (int i = 0; i < kBands; i++) sum[i] = 0;
-  for (int i = 0; i < kBands - 1; i++) {
-    const int band_size = (c_eband5ms[i + 1] - c_eband5ms[i]) * 4;
-    for (int j = 0; j < band_size; j++) {
-      const float frac = (float)j / (float)band_size;
-      const Cpx X = S.ld(c_eband5ms[i] * 4 + j);
-      float tmp = X.r * X.r;
-      tmp += X.i * X.i;
-      tmp = (float)((double)1.f / ((double)tmp + 1e-9));
-      sum[i] += (1.f - frac) * tmp;
-      sum[i + 1] += frac * tmp;
-    }
-  }
-  sum[0] *= 2;
-  sum[kBands - 1] *= 2;
+  __syncwarp();
+#pragma unroll
+  for (int q = 0; q < 10; q++) W.x[__ldg(A.tab.fft_bitrev + lane + 32 * q)] = make_float2(scale * vin[q], scale * 0.f);
+  __syncwarp();
+  wfft320(W, A.tab.fft_tw);
+  // compute_band_energy_inverse (freq.c:59-84), band `lane`
+  const float sum = w_band_energy<true>(W);
   const double gain = (.45 * (double)g) * (double)(1.f / ((float)320 * 320 * 320));
-  float Ly[kBands], logMax = -2, follow = -2;
+  float *Ly = W.f + 36;
+  if (lane < kBands) {
+    const float E = (float)((double)sum * gain);
+    Ly[lane] = (float)log10(1e-2 + (double)E);
+  }
+  __syncwarp();
+  float mine = 0.f, logMax = -2, follow = -2;
   for (int i = 0; i < kBands; i++) {
-    const float E = (float)((double)sum[i] * gain);
-    float l = (float)log10(1e-2 + (double)E);
+    float l = Ly[i];
     // freq.c:180-183: the constant 2.5 is a double there, so these comparisons run in double
     const double f25 = (double)follow - 2.5;
     const double inner = f25 > (double)l ? f25 : (double)l;
     const float lm8 = logMax - 8;
     l = (float)((double)lm8 > inner ? (double)lm8 : inner);
-    Ly[i] = l;
+    if (i == lane) mine = l;
     logMax = fmaxf(logMax, l);
     follow = (float)(f25 > (double)l ? f25 : (double)l);
   }
-  for (int i = 0; i < kBands; i++) {
-    float acc = 0;
-    for (int j = 0; j < kBands; j++) acc += Ly[j] * __ldg(A.tab.dct + j * kBands + i);
-    out[i] = (float)((double)acc * sqrt(2. / kBands));
-  }
-  out[0] += -4;
-}
-
-// one thread per (update stream, half frame); the two cepstra go to encf2 (free at this point of the frame) and
-// are combined into mean / difference (freq.c:188-199) by plc_burg_combine_kernel
-__global__ void plc_burg_kernel(PlcArgs A) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  const int s = idx >> 1, half = idx & 1;
-  if (s >= A.n_streams || !A.masks[mUpd * A.n_streams + s]) return;
-  const Scratch S = block_scratch();
-  burg_cepstrum(A, A.w.in + (size_t)s * kFrame + half * kTOff, A.w.encf2 + (size_t)s * 36 + half * kBands, S);
+  __syncwarp();
+  if (lane < kBands) Ly[lane] = mine;
+  __syncwarp();
+  float c = w_dct(A.tab.dct, Ly, lane);
+  if (lane == 0) c += -4;
+  if (lane < kBands) out[lane] = c;
 }
 
 __global__ void plc_burg_combine_kernel(PlcArgs A) {
@@ -827,8 +852,8 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
     if (side_work) CKP(cudaStreamWaitEvent(ss, p->ev_fin, 0));
     if (a.upd) {
       plc_pre_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A);
-      CKP(fft_opt_in(plc_burg_kernel));
-      plc_burg_kernel<<<(2 * B + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, cs>>>(A);
+      CKP(cudaFuncSetAttribute(plc_burg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBurgSmem));
+      plc_burg_kernel<<<(2 * B + kBurgWarps - 1) / kBurgWarps, kBurgWarps * 32, kBurgSmem, cs>>>(A);
       plc_burg_combine_kernel<<<(B * kBands + 255) / 256, 256, 0, cs>>>(A);
     }
     mark(1);
@@ -1105,8 +1130,8 @@ int plc_run_causal(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_f
     // ---- received frames (lpcnet_plc_update_causal) ----
     if (a.u) {
       c_pre_kernel<<<wps_grid(B), kWpsThreads, 0, cs>>>(A, row(cU));
-      CKP(fft_opt_in(plc_burg_kernel));
-      plc_burg_kernel<<<(2 * B + kFftBlock - 1) / kFftBlock, kFftBlock, kFftSmem, cs>>>(A);
+      CKP(cudaFuncSetAttribute(plc_burg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBurgSmem));
+      plc_burg_kernel<<<(2 * B + kBurgWarps - 1) / kBurgWarps, kBurgWarps * 32, kBurgSmem, cs>>>(A);
       plc_burg_combine_kernel<<<(B * kBands + 255) / 256, 256, 0, cs>>>(A);
     }
     if (a.sb) {
