@@ -235,13 +235,13 @@ __device__ float burg_analysis(float *Aout, const float *x, float minInvGain, in
 
 __constant__ double c_pow995[16];   // pow(.995, i+1), filled by the host's libm at start-up
 
-// burg_cepstral_analysis (freq.c:152-186), 32 half frames per block of 32 warps, in three steps:
+// burg_cepstral_analysis (freq.c:152-186), kBurgWarps half frames per block of as many warps, in three steps:
 //  1. warp w, half frame w: pre-emphasis, then the 17 autocorrelation sums of Burg's method one lag per lane (each a
 //     serial double-precision sum in the reference's order; they do not depend on each other);
 //  2. warp 0, lane l: Burg's recursion for half frame l -- serial and in double precision, so the 32 of the block run
-//     side by side on the lanes of one warp (one per warp would leave 31 lanes idle: measured 2.5x slower per frame);
+//     side by side on the lanes of one warp (one per warp leaves 31 lanes idle: measured 2.5x slower per frame);
 //  3. warp w again: the transform, band sums, logs and DCT as in dsp_warp.cuh.
-constexpr int kBurgWarps = 32;
+constexpr int kBurgWarps = 16;   // (32 warps per block cap the recursion at 64 registers: 157 us per launch against 1xx)
 constexpr size_t kBurgSmem = (size_t)kBurgWarps * kWarpDspFloats * sizeof(float);
 __global__ void __launch_bounds__(kBurgWarps * 32) plc_burg_kernel(PlcArgs A) {
   extern __shared__ __align__(16) float burg_sm[];
@@ -264,7 +264,7 @@ __global__ void __launch_bounds__(kBurgWarps * 32) plc_burg_kernel(PlcArgs A) {
     if (lane <= 16) corr_of(wi)[lane] = inner_flp(bin, bin + lane, kTOff - 1 - lane);
   }
   __syncthreads();
-  if (wi == 0 && valid_s[lane]) {
+  if (wi == 0 && lane < kBurgWarps && valid_s[lane]) {
     float a[16];
     float g = burg_analysis(a, bin_of(lane), (float)1e-3, kTOff - 1, 16, corr_of(lane));
     g /= (float)(kTOff - 2 * (16 - 1));
