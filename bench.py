@@ -486,6 +486,21 @@ def run_gpu(args):
         roof_onchip = {"bound": "on_chip_bytes_algorithmic", "achieved": algo_bytes * samples_per_launch / kernel_s / 1e9,
                        "peak": smem_peak, "unit": "GB/s", "frac": algo_bytes * samples_per_launch / kernel_s / 1e9 / smem_peak,
                        "bytes_per_stream_sample": algo_bytes}
+        # issue slots: what this kernel is bound by.  Warp-instructions per stream-sample from the
+        # committed ncu capture of this workload (profiles/traffic.json), executed per second in this run, against one
+        # instruction per scheduler and clock on the SMs of the device.
+        roof_issue = None
+        try:
+            if traffic is not None and tj.get("warp_instructions_per_launch"):
+                wi = tj["warp_instructions_per_launch"] / (tj["streams"] * tj["frames_per_launch"] * FRAME)
+                ach = wi * samples_per_launch / kernel_s
+                peak_i = 4.0 * n_sms * sm_clock * 1e6
+                roof_issue = {"bound": "issue_slots", "achieved": ach / 1e9, "peak": peak_i / 1e9, "unit": "G warp-inst/s",
+                              "frac": ach / peak_i, "warp_instructions_per_stream_sample": wi,
+                              "frac_of_sms_in_use": ach / (peak_i * min(1.0, -(-B // tile_used) / n_sms)),
+                              "peak_source": f"4 schedulers x {n_sms} SMs x {sm_clock:.0f} MHz"}
+        except Exception:
+            roof_issue = None
         roof_hbm = {"bound": "hbm", "achieved": hbm_bytes_per_sample * value / world / 1e9, "peak": pk["hbm_gbs"],
                     "unit": "GB/s", "frac": hbm_bytes_per_sample * value / world / 1e9 / pk["hbm_gbs"]}
         # ---- CPU baseline: bounded sample of the same workload on the host cores ----
@@ -520,7 +535,7 @@ def run_gpu(args):
                     "d2h_bytes_per_step": h_pcm.numel() * 2 * world, "steps": k_e2e},
             "gpu_launches": launches, "clocks": clk,
             "parity_check": parity,
-            "roofline": roofline, "roofline_onchip": roof_onchip, "roofline_smem": roof_smem, "roofline_l2": roof_l2,
+            "roofline": roofline, "roofline_issue": roof_issue, "roofline_onchip": roof_onchip, "roofline_smem": roof_smem, "roofline_l2": roof_l2,
             "roofline_hbm": roof_hbm,
             # the frame network of chunk k+1 runs on a second stream beside the sample kernel of chunk k: its time
             # (here as a fraction of the step) is concurrent with the sample kernel, not additive
