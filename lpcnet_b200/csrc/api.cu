@@ -85,6 +85,8 @@ struct LPCNetBatch {
   cudaStream_t fstream = nullptr;
   cudaStream_t cstream = nullptr;                       // device->host copies of finished chunks (pinned destination)
   cudaEvent_t ev_chunk = nullptr, ev_copied = nullptr;
+  cudaStream_t hstream = nullptr;                       // host->device copies of the chunks' feature rows (pinned source)
+  cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_h2d_entry = nullptr;
   cudaEvent_t ev_entry = nullptr, ev_frames[2] = {nullptr, nullptr}, ev_samples[2] = {nullptr, nullptr};
   cudaStream_t own_stream = nullptr;
   cudaStream_t stream = nullptr;
@@ -337,8 +339,12 @@ bool is_pinned_host(const void *p) {
 
 // h_pcm (optional, pinned host memory [B][n_frames * spf]): every chunk's samples are copied out on a third stream
 // as soon as its sample kernel is done, beside the next chunk's kernel; the caller's stream ends after the last copy.
+// h_features (optional, pinned host memory [B][n_frames][stride], with d_features the device buffer of that shape to
+// fill): every chunk's feature rows are copied in on a fourth stream just ahead of its frame network, so that the call
+// starts computing after the first chunk's rows instead of after the whole upload.
 int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_frames, int spf, short *d_pcm,
-                 const short *d_forced, LPCNetB200Trace *d_trace, float *d_logits, short *h_pcm = nullptr) {
+                 const short *d_forced, LPCNetB200Trace *d_trace, float *d_logits, short *h_pcm = nullptr,
+                 const float *h_features = nullptr) {
   if (!b) return fail("null batch");
   if (n_frames <= 0) return 0;
   if (spf <= 0 || spf > kFrame) return fail("samples_per_frame must be 1..160");
@@ -370,6 +376,15 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
     CK(cudaStreamWaitEvent(b->fstream, b->ev_entry, 0));
   }
   const size_t row_len = (size_t)n_frames * spf;
+  if (h_features) {
+    if (!b->hstream) {
+      CK(cudaStreamCreateWithFlags(&b->hstream, cudaStreamNonBlocking));
+      for (int k = 0; k < 2; k++) CK(cudaEventCreateWithFlags(&b->ev_h2d[k], cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&b->ev_h2d_entry, cudaEventDisableTiming));
+    }
+    CK(cudaEventRecord(b->ev_h2d_entry, b->stream));      // the feature buffer's last readers are ordered before it
+    CK(cudaStreamWaitEvent(b->hstream, b->ev_h2d_entry, 0));
+  }
   int item = 0;
   for (int s0 = 0; s0 < b->n_streams; s0 += G) {
     const int Gs = (b->n_streams - s0) < G ? (b->n_streams - s0) : G;
@@ -377,6 +392,14 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
       const int F = (n_frames - f0) < Fc ? (n_frames - f0) : Fc;
       const int buf = pipe ? (item & 1) : 0;
       const FrameBuffers &fbk = buf ? b->fb2 : b->fb;
+      if (h_features) {
+        // rows [s0, s0 + Gs), frames [f0, f0 + F) of [B][n_frames][stride]: a 2-D copy
+        const size_t pitch = (size_t)n_frames * stride * 4, off = ((size_t)s0 * n_frames + f0) * stride;
+        CK(cudaMemcpy2DAsync(const_cast<float *>(d_features) + off, pitch, h_features + off, pitch, (size_t)F * stride * 4, Gs,
+                             cudaMemcpyHostToDevice, b->hstream));
+        CK(cudaEventRecord(b->ev_h2d[item & 1], b->hstream));
+        CK(cudaStreamWaitEvent(pipe ? b->fstream : b->stream, b->ev_h2d[item & 1], 0));
+      }
       if (pipe) {
         if (item >= 2) CK(cudaStreamWaitEvent(b->fstream, b->ev_samples[buf], 0));   // the buffers are free again
         if (l2_window(b, b->fstream, fbk.cond_a, (size_t)F * Gs * kRowsAP * 4)) return -1;
@@ -680,6 +703,7 @@ void lpcnet_batch_destroy(LPCNetBatch *b) {
   for (auto &f : b->forks) { cudaStreamSynchronize(f.second.aux); cudaStreamDestroy(f.second.aux); cudaEventDestroy(f.second.begin); cudaEventDestroy(f.second.done); }
   void *ptrs[] = {b->st_alloc, b->fb_alloc, b->fb2_alloc, b->d_feat, b->d_pcm, b->d_forced, b->d_trace, b->d_logits, b->d_packets, b->d_compact, b->d_compact2};
   for (void *p : ptrs) if (p) cudaFree(p);
+  if (b->hstream) { cudaStreamSynchronize(b->hstream); cudaStreamDestroy(b->hstream); cudaEventDestroy(b->ev_h2d[0]); cudaEventDestroy(b->ev_h2d[1]); cudaEventDestroy(b->ev_h2d_entry); }
   if (b->cstream) { cudaStreamSynchronize(b->cstream); cudaStreamDestroy(b->cstream); cudaEventDestroy(b->ev_chunk); cudaEventDestroy(b->ev_copied); }
   if (b->own_stream) cudaStreamDestroy(b->own_stream);
   delete b;
@@ -832,7 +856,9 @@ int lpcnet_batch_synthesize(LPCNetBatch *b, const float *features, int stride, i
   const size_t B = b->n_streams, T = (size_t)n_frames * kFrame;
   const size_t fbytes = B * n_frames * (size_t)stride * 4, pbytes = B * T * 2;
   if (grow(&b->d_feat, &b->d_feat_bytes, fbytes) || grow(&b->d_pcm, &b->d_pcm_bytes, pbytes)) return -1;
-  CK(cudaMemcpyAsync(b->d_feat, features, fbytes, cudaMemcpyHostToDevice, b->stream));
+  // pinned features go in chunk by chunk beside the computation (synth_device); pageable ones in one staged copy
+  const bool feat_pinned = is_pinned_host(features) && !getenv("LPCNET_B200_NO_H2D_PIPELINE");
+  if (!feat_pinned) CK(cudaMemcpyAsync(b->d_feat, features, fbytes, cudaMemcpyHostToDevice, b->stream));
   if (forced) {
     if (grow(&b->d_forced, &b->d_forced_bytes, pbytes)) return -1;
     CK(cudaMemcpyAsync(b->d_forced, forced, pbytes, cudaMemcpyHostToDevice, b->stream));
@@ -845,7 +871,8 @@ int lpcnet_batch_synthesize(LPCNetBatch *b, const float *features, int stride, i
   if (synth_device(b, static_cast<const float *>(b->d_feat), stride, n_frames, kFrame, static_cast<short *>(b->d_pcm),
                    forced ? static_cast<const short *>(b->d_forced) : nullptr,
                    trace ? static_cast<LPCNetB200Trace *>(b->d_trace) : nullptr,
-                   logits ? static_cast<float *>(b->d_logits) : nullptr, pinned ? pcm : nullptr))
+                   logits ? static_cast<float *>(b->d_logits) : nullptr, pinned ? pcm : nullptr,
+                   feat_pinned ? features : nullptr))
     return -1;
   if (!pinned) CK(cudaMemcpyAsync(pcm, b->d_pcm, pbytes, cudaMemcpyDeviceToHost, b->stream));
   if (trace) CK(cudaMemcpyAsync(trace, b->d_trace, B * T * sizeof(LPCNetB200Trace), cudaMemcpyDeviceToHost, b->stream));

@@ -408,6 +408,39 @@ def test_l2_sized_chunks_are_invisible(eng, model_blob, orc_model, monkeypatch):
         assert np.array_equal(plain[s], ref), s
 
 
+def test_pinned_host_buffers_take_the_pipelined_copies(eng, model_blob):
+    """lpcnet_batch_synthesize with page-locked features / PCM: the feature rows go in chunk by chunk on a copy stream
+    and the PCM comes out chunk by chunk (api.cu synth_device); same PCM as with pageable buffers, over two calls."""
+    import torch
+    B, F = 200, 21
+    base = np.stack([blob.synthetic_features(F, s) for s in range(64)])
+    feats = np.ascontiguousarray(base[np.arange(B) % 64])
+    tf = torch.empty(feats.shape, dtype=torch.float32, pin_memory=True)
+    tf.numpy()[...] = feats
+    tp = torch.empty((B, F * 160), dtype=torch.int16, pin_memory=True)
+
+    def run(pinned):
+        bt = eng.Batch(model_blob, B)
+        for s in range(B):
+            bt.set_seed(s, blob.stream_seed(s % 64))
+        if pinned:
+            f = tf.numpy()
+            a = bt.synthesize(f[:, :9], pcm_out=None)[0]          # (a strided view is copied by the wrapper: pageable)
+            fb = torch.empty((B, F - 9, feats.shape[2]), dtype=torch.float32, pin_memory=True)
+            fb.numpy()[...] = feats[:, 9:]
+            out = tp.numpy()[:, : (F - 9) * 160]
+            ob = torch.empty((B, (F - 9) * 160), dtype=torch.int16, pin_memory=True)
+            b = bt.synthesize(fb.numpy(), pcm_out=ob.numpy())[0]
+            del out
+        else:
+            a = bt.synthesize(feats[:, :9])[0]
+            b = bt.synthesize(feats[:, 9:])[0]
+        bt.close()
+        return np.concatenate([np.asarray(a), np.asarray(b)], axis=1)
+
+    assert np.array_equal(run(True), run(False))
+
+
 def test_stream_groups_are_invisible(eng, model_blob, orc_model, monkeypatch):
     """Large batches are walked in groups of whole 16-stream-tile waves, each in full 32-frame chunks (api.cu
     group_streams).  With the group budget lowered to one wave: 5000 streams x 40 frames (3 groups x 2 chunks, the
