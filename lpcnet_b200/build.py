@@ -58,6 +58,22 @@ def build(force: bool = False, verbose: bool = False, extra_flags=(), tag: str =
         if r.returncode != 0:
             sys.stderr.write(r.stdout + r.stderr)
             raise RuntimeError("link failed for liblpcnet_b200.so")
+    if not tag:
+        # The reference installs `liblpcnet` with a pkg-config file `lpcnet.pc` (Makefile.am:9, lpcnet.pc.in): the same
+        # names beside the library, so that a program's `-llpcnet` / `pkg-config --libs lpcnet` resolve to this
+        # library without a change to its build.
+        alias = os.path.join(HERE, "liblpcnet.so")
+        if not os.path.islink(alias) or os.readlink(alias) != os.path.basename(LIB):
+            if os.path.lexists(alias):
+                os.remove(alias)
+            os.symlink(os.path.basename(LIB), alias)
+        pc = os.path.join(HERE, "lpcnet.pc")
+        text = ("# lpcnet_b200 standing in for the reference's liblpcnet (lpcnet.pc.in)\n"
+                f"libdir={HERE}\nincludedir={os.path.join(os.path.dirname(HERE), 'include')}\n\n"
+                "Name: lpcnet\nDescription: LPCNet synthesis path on B200 GPUs (drop-in for liblpcnet)\nVersion: 0.2\n"
+                "Libs: -L${libdir} -llpcnet -Wl,-rpath,${libdir}\nCflags: -I${includedir}\n")
+        if not os.path.exists(pc) or open(pc).read() != text:
+            open(pc, "w").write(text)
     return LIB
 
 

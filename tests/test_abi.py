@@ -5,6 +5,7 @@ import os
 import re
 
 import numpy as np
+import pytest
 
 from lpcnet_b200 import engine
 
@@ -61,3 +62,30 @@ def test_fails_loudly_without_gpu_or_on_bad_blob(engine_lib, model_blob):
             raise AssertionError("truncated blob accepted")
         except engine.LPCNetError:
             pass
+
+
+def test_links_as_liblpcnet(engine_lib, tmp_path):
+    """The reference installs `liblpcnet` + `lpcnet.pc` (Makefile.am:9, lpcnet.pc.in); the build leaves the same names
+    beside the library so that a program's `-llpcnet` resolves to it.  A C program that uses only the reference's API
+    (declared here as include/lpcnet.h:160-215 declares it) links that way and runs -- no compute: get_size only, and
+    create + destroy, which need no GPU."""
+    import shutil
+    import subprocess
+    here = os.path.dirname(engine.LIB_PATH)
+    assert os.path.islink(os.path.join(here, "liblpcnet.so")) and os.path.exists(os.path.join(here, "lpcnet.pc"))
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    src = tmp_path / "user.c"
+    src.write_text(
+        "#include <stdio.h>\n"
+        "typedef struct LPCNetState LPCNetState;\n"
+        "int lpcnet_get_size(void); LPCNetState *lpcnet_create(void); void lpcnet_destroy(LPCNetState *st);\n"
+        "int lpcnet_plc_get_size(void); int lpcnet_encoder_get_size(void); int lpcnet_decoder_get_size(void);\n"
+        "int main(void) { LPCNetState *st = lpcnet_create(); printf(\"%d %d %d %d %d\\n\", lpcnet_get_size(),\n"
+        "  lpcnet_decoder_get_size(), lpcnet_encoder_get_size(), lpcnet_plc_get_size(), st != NULL); lpcnet_destroy(st); return 0; }\n")
+    exe = tmp_path / "user"
+    libs = open(os.path.join(here, "lpcnet.pc")).read()
+    assert "-llpcnet" in libs
+    subprocess.run(["gcc", "-o", str(exe), str(src), f"-L{here}", "-llpcnet", f"-Wl,-rpath,{here}"], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
+    assert all(int(v) > 0 for v in out), out
