@@ -89,7 +89,6 @@ struct PlcArgs {
 };
 __device__ __forceinline__ int plc_count(const PlcArgs &A) { return A.list ? A.n_list : A.n_streams; }
 __device__ __forceinline__ int plc_stream(const PlcArgs &A, int k) { return A.list ? __ldg(A.list + k) : k; }
-inline int plc_n(const PlcArgs &A) { return A.list ? A.n_list : A.n_streams; }
 
 #define DC_CONST 0.003
 
@@ -454,17 +453,6 @@ __global__ void plc_gather_feat_kernel(PlcArgs A, int mask_row, int main_pass) {
   if (!A.masks[mask_row * A.n_streams + s]) return;
   const bool enc = main_pass && A.masks[mCls * A.n_streams + s] == kG0;
   A.w.fnfeat[i] = enc ? A.w.encf[(size_t)s * 36 + k] : A.st.features[i];
-}
-
-// copies n shorts per stream for the streams of a mask row (optionally only those of one class)
-__global__ void plc_copy_kernel(const uint8_t *mask, const uint8_t *cls, int want_cls, int B, int n, short *dst,
-                                int dst_stride, int dst_off, const short *src, int src_stride, int src_off, int reverse) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= B * n) return;
-  const int s = i / n, k = i % n;
-  if (mask && !mask[s]) return;
-  if (cls && cls[s] != want_cls) return;
-  dst[(size_t)s * dst_stride + dst_off + k] = src[(size_t)s * src_stride + src_off + (reverse ? n - 1 - k : k)];
 }
 
 // snapshot / restore of the synthesis state (`copy = st->lpcnet`, `st->lpcnet = copy`), and clear_state
@@ -1087,7 +1075,7 @@ int plc_run_causal(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_f
   A.st = p->st; A.w = p->w; A.lp = V.st; A.lp_copy = p->snap; A.net = V.model->d.plc; A.rcp_tab = V.model->d.rcp_tab;
   A.tab = p->tab; A.fft_scratch = p->fft_scratch; A.fade = p->fade;
   A.pcm_io = static_cast<short *>(p->d_io); A.n_streams = B; A.total_frames = total_frames; A.remove_dc = p->remove_dc;
-  const int tb = 128, gs = (B + tb - 1) / tb, g20 = (B * 20 + 255) / 256;
+  const int g20 = (B * 20 + 255) / 256;
   const CausalState C = p->cst;
   std::vector<float> stage((size_t)4 * B * 20);
   size_t fu = 0;
