@@ -395,8 +395,12 @@ int synth_device(LPCNetBatch *b, const float *d_features, int stride, int n_fram
       if (h_features) {
         // rows [s0, s0 + Gs), frames [f0, f0 + F) of [B][n_frames][stride]: a 2-D copy
         const size_t pitch = (size_t)n_frames * stride * 4, off = ((size_t)s0 * n_frames + f0) * stride;
-        CK(cudaMemcpy2DAsync(const_cast<float *>(d_features) + off, pitch, h_features + off, pitch, (size_t)F * stride * 4, Gs,
+        if (F == n_frames)      // whole rows: one contiguous block (a 2-D copy of short rows pays per row: 0.8 ms for
+          CK(cudaMemcpyAsync(const_cast<float *>(d_features) + off, h_features + off, pitch * Gs,   // 12 500 rows of 144 B)
                              cudaMemcpyHostToDevice, b->hstream));
+        else
+          CK(cudaMemcpy2DAsync(const_cast<float *>(d_features) + off, pitch, h_features + off, pitch, (size_t)F * stride * 4, Gs,
+                               cudaMemcpyHostToDevice, b->hstream));
         CK(cudaEventRecord(b->ev_h2d[item & 1], b->hstream));
         CK(cudaStreamWaitEvent(pipe ? b->fstream : b->stream, b->ev_h2d[item & 1], 0));
       }
