@@ -1,6 +1,6 @@
 """Diagnostic run on a GPU box: CUDA engine vs the CPU oracle, layer by layer."""
 import os, sys, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np
 from lpcnet_b200 import blob, engine
 from oracle import orcpy

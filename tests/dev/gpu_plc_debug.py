@@ -1,6 +1,6 @@
 """Per-frame comparison of the CUDA PLC with the oracle, outputs and frame-rate state (development aid)."""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np
 from lpcnet_b200 import blob, engine
 from oracle import orcpy

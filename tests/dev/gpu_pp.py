@@ -1,6 +1,6 @@
 """Two 8-stream tiles per CTA (tile code 28) against 16-stream tiles: parity vs the oracle, then timing."""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np
 from lpcnet_b200 import blob, engine
 from oracle import orcpy

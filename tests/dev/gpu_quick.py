@@ -1,6 +1,6 @@
 """Quick GPU iteration check: parity on every tile size, then sample-kernel timing."""
 import os, sys, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np
 from lpcnet_b200 import blob, engine
 from oracle import orcpy
