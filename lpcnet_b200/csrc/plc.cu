@@ -394,53 +394,142 @@ __device__ void plc_gru(const uint32_t *w_in, const uint32_t *w_rec, const float
   __syncthreads();
 }
 
-__global__ void __launch_bounds__(256) plc_pred_kernel(PlcArgs A, int fg_pass) {
-  const int s = plc_stream(A, blockIdx.x), t = threadIdx.x, B = A.n_streams;
-  const uint8_t cls = A.masks[mCls * B + s];
-  int mode;   // 1 zeros, 2 burg only, 3 burg + features
-  if (fg_pass) {
-    if (cls != kFG) return;
-    mode = 2;
-  } else {
-    if (cls == kFG) return;
-    mode = cls == kG0 ? 3 : 1;
+// compute_plc_pred for kPredR streams per block: thread t owns unit t of the GRUs for all of them, so every weight word
+// is loaded once per kPredR streams (one stream per block was bound by the L1/TEX pipe: 0.7 MB of weights per stream,
+// `profiles/r2_v3_plc_pred_full.txt`: l1tex 82 %, 22 long-scoreboard stalls per issue).  Per stream the arithmetic and
+// its order are those of plc_gru / plc_gru_row above.
+constexpr int kPredR = 4;
+struct PredSmem {
+  float in[kPredR][kPlcIn + 3], d1[kPredR][kPlcCond], g1[kPredR][kPlcUnits], g2[kPredR][kPlcUnits];
+  uint32_t xq_in[kPredR][kPlcUnits / 4], xq_st[kPredR][kPlcUnits / 4];
+};
+
+__device__ void plc_gru_r(const uint32_t *__restrict__ w_in, const uint32_t *__restrict__ w_rec, const float *subias,
+                          const float *x_in, int x_stride, int nin, float *const (&state)[kPredR], const bool (&valid)[kPredR],
+                          PredSmem &S, float *s_out, const uint32_t *rcp, int t, const DevSat &sat_in, const DevSat &sat_rec) {
+  float st[kPredR];
+#pragma unroll
+  for (int r = 0; r < kPredR; r++) {
+    if (t < nin) reinterpret_cast<unsigned char *>(S.xq_in[r])[t] = (unsigned char)quant_u8_ref(x_in[r * x_stride + t]);
+    st[r] = valid[r] ? state[r][t] : 0.f;
+    reinterpret_cast<unsigned char *>(S.xq_st[r])[t] = (unsigned char)quant_u8_ref(st[r]);
   }
-  __shared__ float s_in[kPlcIn + 3], s_d1[kPlcCond], s_g1[kPlcUnits], s_g2[kPlcUnits];
-  __shared__ uint32_t xq_in[kPlcUnits / 4], xq_st[kPlcUnits / 4];
+  __syncthreads();
+  float gi[3][kPredR], gr[3][kPredR];
+#pragma unroll
+  for (int kind = 0; kind < 3; kind++) {
+    const int row = kind * kPlcUnits + t;
+    int32_t acc[kPredR], acr[kPredR];
+    const int32_t seed_in = cvt_rne_ref((subias[row] + 0.f) * LPCB_SCALE), seed_rec = cvt_rne_ref(subias[kPlcRows + row] * LPCB_SCALE);
+#pragma unroll
+    for (int r = 0; r < kPredR; r++) { acc[r] = seed_in; acr[r] = seed_rec; }
+    // (the loads do not depend on each other: 16 in flight per thread, or the loops run at L2 latency per word)
+#pragma unroll 16
+    for (int k = 0; k < nin / 4; k++) {
+      const uint32_t w = __ldg(w_in + (size_t)k * kPlcRows + row);
+#pragma unroll
+      for (int r = 0; r < kPredR; r++) acc[r] = dp4a_u8s8(S.xq_in[r][k], w, acc[r]);
+    }
+#pragma unroll 16
+    for (int k = 0; k < kPlcUnits / 4; k++) {
+      const uint32_t w = __ldg(w_rec + (size_t)k * kPlcRows + row);
+#pragma unroll
+      for (int r = 0; r < kPredR; r++) acr[r] = dp4a_u8s8(S.xq_st[r][k], w, acr[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < kPredR; r++) {
+      acc[r] = (int32_t)((uint32_t)acc[r] + (uint32_t)plc_sat_row(sat_in, row, S.xq_in[r]));
+      acr[r] = (int32_t)((uint32_t)acr[r] + (uint32_t)plc_sat_row(sat_rec, row, S.xq_st[r]));
+      gi[kind][r] = (float)acc[r] * LPCB_SCALE_1;
+      gr[kind][r] = (float)acr[r] * LPCB_SCALE_1;
+    }
+  }
+  float nv[kPredR];
+#pragma unroll
+  for (int r = 0; r < kPredR; r++) {
+    const float z = sigmoid_ref(gi[0][r] + gr[0][r], rcp);
+    const float rg = sigmoid_ref(gi[1][r] + gr[1][r], rcp);
+    const float h = tanh_ref(gi[2][r] + gr[2][r] * rg, rcp);
+    nv[r] = z * st[r] + (1.f - z) * h;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < kPredR; r++) {
+    if (valid[r]) state[r][t] = nv[r];
+    s_out[r * kPlcUnits + t] = nv[r];
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(256) plc_pred_kernel(PlcArgs A, int fg_pass) {
+  __shared__ PredSmem S;
+  const int t = threadIdx.x, B = A.n_streams, n = plc_count(A);
+  int sid[kPredR], mode[kPredR];   // mode: 0 not this pass, 1 zeros, 2 burg only, 3 burg + features
+  bool valid[kPredR];
+  float *g1[kPredR], *g2[kPredR];
+  bool any = false;
+#pragma unroll
+  for (int r = 0; r < kPredR; r++) {
+    const int e = blockIdx.x * kPredR + r;
+    sid[r] = e < n ? plc_stream(A, e) : 0;
+    const uint8_t cls = A.masks[mCls * B + sid[r]];
+    mode[r] = e >= n ? 0 : fg_pass ? (cls == kFG ? 2 : 0) : (cls == kFG ? 0 : (cls == kG0 ? 3 : 1));
+    valid[r] = mode[r] != 0;
+    any |= valid[r];
+    g1[r] = A.st.gru1 + (size_t)sid[r] * kPlcUnits;
+    g2[r] = A.st.gru2 + (size_t)sid[r] * kPlcUnits;
+  }
+  if (!any) return;
   if (t < kPlcIn) {
-    float v = 0.f;
-    if (mode >= 2 && t < 2 * kBands) v = A.w.burg[(size_t)s * 2 * kBands + t];
-    else if (mode == 3 && t < 2 * kBands + 20) v = A.w.encf[(size_t)s * 36 + t - 2 * kBands];
-    else if (mode >= 2 && t == kPlcIn - 1) v = 1.f;
-    s_in[t] = v;
+#pragma unroll
+    for (int r = 0; r < kPredR; r++) {
+      float v = 0.f;
+      if (mode[r] >= 2 && t < 2 * kBands) v = A.w.burg[(size_t)sid[r] * 2 * kBands + t];
+      else if (mode[r] == 3 && t < 2 * kBands + 20) v = A.w.encf[(size_t)sid[r] * 36 + t - 2 * kBands];
+      else if (mode[r] >= 2 && t == kPlcIn - 1) v = 1.f;
+      S.in[r][t] = v;
+    }
   }
   __syncthreads();
   // _lpcnet_compute_dense, 57 -> 128, tanh: sgemv_accum16 = fmaf in input order from the bias
   if (t < kPlcCond) {
-    float acc = __ldg(A.net.dense1_b + t);
-    for (int j = 0; j < kPlcIn; j++) acc = fmaf(__ldg(A.net.dense1_w + j * kPlcCond + t), s_in[j], acc);
-    s_d1[t] = tanh_ref(acc, A.rcp_tab);
+    float acc[kPredR];
+    const float b = __ldg(A.net.dense1_b + t);
+#pragma unroll
+    for (int r = 0; r < kPredR; r++) acc[r] = b;
+#pragma unroll 19
+    for (int j = 0; j < kPlcIn; j++) {
+      const float w = __ldg(A.net.dense1_w + j * kPlcCond + t);
+#pragma unroll
+      for (int r = 0; r < kPredR; r++) acc[r] = fmaf(w, S.in[r][j], acc[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < kPredR; r++) S.d1[r][t] = tanh_ref(acc[r], A.rcp_tab);
   }
   __syncthreads();
-  plc_gru(A.net.g1_in, A.net.g1_rec, A.net.g1_subias, s_d1, kPlcCond, A.st.gru1 + (size_t)s * kPlcUnits, xq_in, xq_st,
-          s_g1, A.rcp_tab, t, A.net.sat_g1_in, A.net.sat_g1_rec);
-  plc_gru(A.net.g2_in, A.net.g2_rec, A.net.g2_subias, s_g1, kPlcUnits, A.st.gru2 + (size_t)s * kPlcUnits, xq_in, xq_st,
-          s_g2, A.rcp_tab, t, A.net.sat_g2_in, A.net.sat_g2_rec);
+  plc_gru_r(A.net.g1_in, A.net.g1_rec, A.net.g1_subias, &S.d1[0][0], kPlcCond, kPlcCond, g1, valid, S, &S.g1[0][0], A.rcp_tab, t,
+            A.net.sat_g1_in, A.net.sat_g1_rec);
+  plc_gru_r(A.net.g2_in, A.net.g2_rec, A.net.g2_subias, &S.g1[0][0], kPlcUnits, kPlcUnits, g2, valid, S, &S.g2[0][0], A.rcp_tab, t,
+            A.net.sat_g2_in, A.net.sat_g2_rec);
   // plc_out, 256 -> 20, linear: 20 rows is not a multiple of 16, so the reference takes sgemv_accum's scalar
   // loop (vec_avx.h:73-86 of nnet.c) -- separate multiply and add
-  if (t < 20) {
-    float acc = __ldg(A.net.out_b + t);
-    for (int j = 0; j < kPlcUnits; j++) acc += __ldg(A.net.out_w + j * 20 + t) * s_g2[j];
-    if (t == 19) acc = fminf(.5f, acc + .1f);
-    if (t == 0 && mode == 1) {
-      const int lc = A.lossc[s];
-      const float att[10] = {0, 0, -.2f, -.2f, -.4f, -.4f, -.8f, -.8f, -1.6f, -1.6f};
-      float v;
-      if (lc >= 10) v = acc + att[9] - (float)(2 * (lc - 9));
-      else v = acc + att[lc];
-      acc = fmaxf(-10.f, v);
+  if (t < 20 * kPredR) {
+    const int r = t / 20, o = t % 20;
+    if (valid[r]) {
+      float acc = __ldg(A.net.out_b + o);
+#pragma unroll 16
+      for (int j = 0; j < kPlcUnits; j++) acc += __ldg(A.net.out_w + j * 20 + o) * S.g2[r][j];
+      if (o == 19) acc = fminf(.5f, acc + .1f);
+      if (o == 0 && mode[r] == 1) {
+        const int lc = A.lossc[sid[r]];
+        const float att[10] = {0, 0, -.2f, -.2f, -.4f, -.4f, -.8f, -.8f, -1.6f, -1.6f};
+        float v;
+        if (lc >= 10) v = acc + att[9] - (float)(2 * (lc - 9));
+        else v = acc + att[lc];
+        acc = fmaxf(-10.f, v);
+      }
+      A.st.features[(size_t)sid[r] * 20 + o] = acc;
     }
-    A.st.features[(size_t)s * 20 + t] = acc;
   }
 }
 
@@ -851,7 +940,7 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
       A1.list = permFG; A1.n_list = a.nfg;
       const int nl = a.nfg;
       const uint8_t *mfg = M + (size_t)mFG * B;
-      plc_pred_kernel<<<nl, 256, 0, ss>>>(A1, 1);
+      plc_pred_kernel<<<(nl + kPredR - 1) / kPredR, 256, 0, ss>>>(A1, 1);
       plc_state_copy_kernel<<<nl, 128, 0, ss>>>(p->snap, V.st, mfg, B, permFG);
       plc_gather_feat_kernel<<<(nl * 20 + 255) / 256, 256, 0, ss>>>(A1, mFG, 0);
       if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, mfg, false, permFG, a.nfg, two ? ss : nullptr)) return -1;
@@ -885,7 +974,7 @@ int plc_run(LPCNetPLCBatch *p, const unsigned char *lost, int f0, int n_frames, 
     mark(2);
     if (a.main_) {
       if (q_before) CKP(cudaStreamWaitEvent(cs, q_event, 0));
-      plc_pred_kernel<<<B, 256, 0, cs>>>(A, 0);
+      plc_pred_kernel<<<(B + kPredR - 1) / kPredR, 256, 0, cs>>>(A, 0);
       plc_gather_feat_kernel<<<(B * 20 + 255) / 256, 256, 0, cs>>>(A, mMain, 1);
       if (batch_frame_network_masked(p->syn, p->w.fnfeat, 20, M + (size_t)mMain * B, false, permMain, a.nmain)) return -1;
       plc_seg_prep_kernel<<<(B * kTOff + 255) / 256, 256, 0, cs>>>(A, 0);
